@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""Generate the golden fixtures in this directory by running the UNMODIFIED reference
+(/root/reference, brithbutter/mat-dcml) in the build container.
+
+    python tests/golden/make_golden.py            # regenerates every *.npz here
+
+The reference ships no tests or golden vectors, so these fixtures are
+what pins the oracle: ``tests/test_oracle_golden.py`` checks ``oracle/`` against them on CPU,
+``tests/test_*_gpu.py`` check the CUDA path against them on the GPU box (where
+``/root/reference`` does not exist).  Nothing is copied from the reference: it is imported
+from where it lies, its RNG entry points (``random`` / ``np.random`` module globals of the
+four simulator modules) are replaced by shims that return the named Philox draws of
+``oracle/philox.py``, and only inputs and outputs are stored.
+
+Each family runs in a subprocess because the simulator star-imports its constants
+(``DCML_BID_FIRST_MA_ENV_SingleProcess.py:4``) and W != 100 needs them patched before import.
+"""
+import argparse
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+sys.path.insert(0, ROOT)
+sys.dont_write_bytecode = True
+
+
+def _ref_paths():
+    sys.path[:0] = [REF, os.path.join(REF, "mat_src")]
+    stub = types.ModuleType("tensorboardX")
+    stub.SummaryWriter = type("SummaryWriter", (), {"__init__": lambda self, *a, **k: None})
+    sys.modules["tensorboardX"] = stub
+
+
+def _args(**over):
+    from mat.config import get_config
+    a = get_config().parse_known_args([])[0]
+    a.algorithm_name, a.env_name = "mat", "DCML"
+    for k, v in over.items():
+        setattr(a, k, v)
+    return a
+
+
+# ------------------------------------------------------------------------------------------
+# policy
+# ------------------------------------------------------------------------------------------
+def synth_policy_inputs(B, L, seed):
+    """Env-like observations: features in [0,1.1], ~40% workers disabled (ava [1,0])."""
+    rng = np.random.RandomState(seed)
+    obs = rng.uniform(0.0, 1.1, size=(B, L, 7))
+    dis = rng.uniform(size=(B, L)) < 0.4
+    dis[:, -1] = False
+    obs[dis, 2:6] = 1.0
+    ava = np.ones((B, L, 2), np.int64)
+    ava[dis, 1] = 0
+    return obs.reshape(B * L, 7), ava.reshape(B * L, 2)
+
+
+def gen_policy(out, L, B, profile, wseed, semi=True):
+    _ref_paths()
+    import torch
+    from mat.algorithms.mat.algorithm.transformer_policy import TransformerPolicy
+    from DCML_ENVs.DCML_utils.DCML_ActionSpace import Action_Space
+    from oracle import mat_oracle as mo
+
+    W = L - 1
+    space = Action_Space(2, semi_index=-1 if semi else 0, extra=True)
+    pol = TransformerPolicy(_args(), [7], [W + 2], space, L)
+    assert pol.action_type == ("Semi_Discrete" if semi else "Discrete")
+    sd = mo.make_weights(wseed, L, profile=profile, semi=semi)
+    pol.transformer.load_state_dict(mo.full_state_dict(sd, L), strict=True)
+    pol.eval()
+    obs, ava = synth_policy_inputs(B, L, 100 + wseed)
+    cent = np.zeros((B * L, W + 2))
+    res = {"obs": obs, "ava": ava, "L": L, "B": B, "wseed": wseed, "profile": profile, "semi": int(semi)}
+    with torch.no_grad():
+        res["values"] = pol.get_values(cent, obs, None, None, ava).numpy()
+        strides = [1, 2, 10, L] if semi else [4]
+        for s in strides:
+            v, a, lp, _, _ = pol.get_actions(cent, obs, None, None, None, ava.copy(), deterministic=True, stride=s)
+            res["det%d_values" % s], res["det%d_actions" % s], res["det%d_logp" % s] = v.numpy(), a.numpy(), lp.numpy()
+        # stochastic sample from the reference's own RNG, to be re-scored by evaluate_actions
+        torch.manual_seed(7)
+        v, a, lp, _, _ = pol.get_actions(cent, obs, None, None, None, ava.copy(), deterministic=False)
+        res["smp_actions"], res["smp_logp"] = a.numpy(), lp.numpy()
+    active = np.ones((B * L, 1), np.float32)
+    active[::5] = 0.0
+    for tagname, acts in (("det", res["det1_actions" if semi else "det4_actions"]), ("smp", res["smp_actions"])):
+        acts = acts.astype(np.float32)
+        lp_t, v_t, ent_t = pol.transformer(cent.reshape(B, L, -1), obs.reshape(B, L, 7), acts.reshape(B, L, 1),
+                                           ava.reshape(B, L, 2).copy())
+        v2, lp2, ent_s = pol.evaluate_actions(cent, obs, None, None, acts, None, ava.copy(), torch.from_numpy(active))
+        res["ev_%s_logp" % tagname] = lp_t.detach().numpy().reshape(-1, 1)
+        res["ev_%s_entropy" % tagname] = ent_t.detach().numpy().reshape(-1, 1)
+        res["ev_%s_values" % tagname] = v2.detach().numpy()
+        res["ev_%s_entropy_scalar" % tagname] = ent_s.detach().numpy()
+    res["active"] = active
+    np.savez_compressed(out, **res)
+    print("wrote", out)
+
+
+# ------------------------------------------------------------------------------------------
+# env (reference Env + ShareDummyVecEnv with injected named draws)
+# ------------------------------------------------------------------------------------------
+class _Ctx:
+    pass
+
+
+def gen_env(out, W, B, steps, seed, real_workloads):
+    _ref_paths()
+    import DCML_ENVs.DCML_utils.DCML_Config as cfg
+    if W != 100:                                   # constants are star-imported
+        cfg.WORKER_NUMBER_MAX = W
+        cfg.SOB_DIM = W + 2
+    from oracle import philox as px
+    from oracle import env_oracle as eo
+
+    if real_workloads:
+        os.chdir(REF)
+        base = []
+        with open("data/workloads.txt", "rb") as f:
+            for _ in range(W):
+                base.append(np.load(f, allow_pickle=True))
+        base = np.asarray(base, np.float64)
+    else:
+        base = eo.synthetic_workloads(W, seed=11)
+        tmp = tempfile.mkdtemp()
+        os.makedirs(os.path.join(tmp, "data"))
+        with open(os.path.join(tmp, "data", "workloads.txt"), "wb") as f:
+            for row in base:
+                np.save(f, row)
+        os.chdir(tmp)
+
+    import DCML_Master
+    import DCML_Worker_TIMESLOT_MultiProcess as WK
+    import DCML_ENVs.DCML_Basic_Env as BE
+    import DCML_BID_FIRST_MA_ENV_SingleProcess as ENV
+    from mat.envs.env_wrappers import ShareDummyVecEnv
+
+    ctx = _Ctx()
+    ctx.t, ctx.e, ctx.w, ctx.k, ctx.in_reset = 0, 0, 0, 0, False
+    ctx.r = {}
+    ctx.draws = {}
+    kmax = int(math.floor(0.8 * W))
+
+    def draw():
+        key = (ctx.e, ctx.t)
+        if key not in ctx.draws:
+            ctx.draws[key] = eo._Draws(seed, ctx.e, ctx.t, W)
+            ctx.draws[key]._jit = ctx.draws[key].jitter()
+        return ctx.draws[key]
+
+    class PyRandom:
+        @staticmethod
+        def uniform(a, b):
+            if b == 1:                              # geometric retry draw, Worker.process
+                v = draw().retry(ctx.w, ctx.k)
+                ctx.k += 1
+                return float(v)
+            return 0.5 * (a + b)                    # master Pr: never observed (HETEROGENEOUS)
+
+        @staticmethod
+        def random():
+            if ctx.in_reset:
+                return 0.5                          # update_local_workload_delay: value unused
+            return draw().done_coin()
+
+        @staticmethod
+        def randint(a, b):
+            x = draw().reset_scalars(ctx.r.get(ctx.e, 0))
+            if (a, b) == (1, 80):
+                return 1 + int(px.bounded(x[0], kmax))
+            if (a, b) == (0, 19):
+                return int(px.bounded(x[1], 20))
+            if (a, b) == (eo.R_MIN, eo.R_HI):
+                return eo.R_MIN + int(px.bounded(x[2], eo.R_HI - eo.R_MIN + 1))
+            if (a, b) == (eo.C_MIN, eo.C_HI):
+                return eo.C_MIN + int(px.bounded(x[3], eo.C_HI - eo.C_MIN + 1))
+            return a                                # Master.__init__: overwritten by the first reset
+
+        @staticmethod
+        def seed(*a):
+            pass
+
+    class NpRandom:
+        @staticmethod
+        def uniform(lo, hi, size=None):
+            if (lo, hi) == (0.8, 1.2):
+                return lo + (hi - lo) * draw()._jit[ctx.w]
+            if (lo, hi) == (0, 0.95):
+                u, _ = draw().worker_block(ctx.r.get(ctx.e, 0))
+                return lo + (hi - lo) * u
+            raise AssertionError(("unexpected np.random.uniform", lo, hi, size))
+
+        @staticmethod
+        def poisson(lam=1.0, size=None):
+            return np.full(size, 3)                 # feeds Worker.price only (DYNAMIC_PRICE False)
+
+        @staticmethod
+        def choice(n, k, replace=True):
+            assert n == W and not replace
+            _, key = draw().worker_block(ctx.r.get(ctx.e, 0))
+            return np.lexsort((np.arange(W), key))[:k]
+
+    class NpProxy:
+        random = NpRandom
+
+        def __getattr__(self, name):
+            return getattr(np, name)
+
+    for mod in (DCML_Master, WK, BE, ENV):
+        if hasattr(mod, "random"):
+            mod.random = PyRandom
+        if hasattr(mod, "np"):
+            mod.np = NpProxy()
+
+    w_init, w_process, e_reset, e_step = WK.Worker.__init__, WK.Worker.process, ENV.Env.reset, ENV.Env.step
+
+    def worker_init(self, *a, **k):
+        self._idx = ctx.w
+        w_init(self, *a, **k)
+        ctx.w += 1
+
+    def worker_process(self, *a, **k):
+        ctx.w, ctx.k = self._idx, 0
+        return w_process(self, *a, **k)
+
+    def env_reset(self, *a, **k):
+        ctx.e, ctx.in_reset = self._e, True
+        try:
+            return e_reset(self, *a, **k)
+        finally:
+            ctx.in_reset = False
+            ctx.r[self._e] = ctx.r.get(self._e, 0) + 1
+
+    def env_step(self, *a, **k):
+        ctx.e = self._e
+        ctx.r[self._e] = 0
+        return e_step(self, *a, **k)
+
+    WK.Worker.__init__, WK.Worker.process = worker_init, worker_process
+    ENV.Env.reset, ENV.Env.step = env_reset, env_step
+
+    def make(e):
+        def fn():
+            ctx.e, ctx.w = e, 0
+            env = ENV.Env()
+            env._e = e
+            return env
+        return fn
+
+    vec = ShareDummyVecEnv([make(e) for e in range(B)])
+    L = W + 1
+    res = {"W": W, "B": B, "steps": steps, "seed": seed, "base": base}
+    obs, sob, ava = vec.reset()
+    assert obs.shape == (B, L, 7) and sob.shape == (B, L, W + 2) and ava.shape == (B, L, 2)
+    res["obs0"], res["sob0"], res["ava0"] = obs, sob[:, 0, :], ava
+    assert np.all(sob == sob[:, :1, :])
+    rng = np.random.RandomState(seed + 5)
+    for t in range(1, steps + 1):
+        ctx.t = t
+        sel = (rng.uniform(size=(B, W)) < rng.uniform(0.2, 0.9, size=(B, 1))).astype(np.float32)
+        sel = sel * ava[:, :W, 1]                   # the policy never selects a disabled worker
+        ratio = rng.uniform(0.05, 1.2, size=(B, 1)).astype(np.float32)
+        if t == 2:
+            sel[0] = 0.0                            # the N == 0 branch (ENV:81-92)
+        if t == 3:
+            ratio[0] = -0.3                         # K clamped up to 1
+        act = np.concatenate([sel, ratio], axis=1).astype(np.float32)[:, :, None]
+        obs, sob, rew, dones, infos, ava = vec.step(act)
+        assert np.all(sob == sob[:, :1, :]) and np.all(rew == rew[:, :1, :]) and np.all(dones == dones[:, :1])
+        res["act%d" % t] = act
+        res["obs%d" % t], res["sob%d" % t], res["ava%d" % t] = obs, sob[:, 0, :], ava
+        res["rew%d" % t], res["done%d" % t] = rew[:, 0, 0], dones[:, 0]
+        res["delay%d" % t] = np.array([i[0]["delay"] for i in infos], np.float64)
+        res["pay%d" % t] = np.array([i[0]["payment"] for i in infos], np.float64)
+    np.savez_compressed(out, **res)
+    print("wrote", out)
+
+
+# ------------------------------------------------------------------------------------------
+# GAE + PPO update
+# ------------------------------------------------------------------------------------------
+def gen_gae(out):
+    _ref_paths()
+    import torch
+    from mat.utils.shared_buffer import SharedReplayBuffer
+    from mat.utils.valuenorm import ValueNorm
+    from DCML_ENVs.DCML_utils.DCML_ActionSpace import Action_Space
+
+    T, N, L = 12, 5, 7
+    rng = np.random.RandomState(3)
+    res = {}
+    for case, use_vn in (("vn", True), ("raw", False)):
+        args = _args(episode_length=T, n_rollout_threads=N, use_valuenorm=use_vn, use_popart=False)
+        buf = SharedReplayBuffer(args, L, [7], [L + 1], Action_Space(2, semi_index=-1, extra=True), "DCML")
+        buf.rewards[:] = rng.standard_normal(buf.rewards.shape) * 50 - 200
+        buf.value_preds[:] = rng.standard_normal(buf.value_preds.shape)
+        buf.masks[:] = (rng.uniform(size=(T + 1, N, 1, 1)) > 0.8)
+        nxt = rng.standard_normal((N, L, 1)).astype(np.float32)
+        vn = None
+        if use_vn:
+            vn = ValueNorm(1)
+            for _ in range(3):
+                vn.update(torch.from_numpy((rng.standard_normal((64, 1)) * 40 - 150).astype(np.float32)))
+            res["vn_stats"] = np.array([vn.running_mean.item(), vn.running_mean_sq.item(), vn.debiasing_term.item()],
+                                       np.float32)
+        res[case + "_rewards"], res[case + "_values_in"] = buf.rewards.copy(), buf.value_preds.copy()
+        res[case + "_masks"], res[case + "_next"] = buf.masks.copy(), nxt
+        buf.compute_returns(nxt, vn)
+        res[case + "_adv"], res[case + "_ret"] = buf.advantages.copy(), buf.returns.copy()
+    np.savez_compressed(out, **res)
+    print("wrote", out)
+
+
+def gen_ppo(out, L, M, wseed):
+    """One MATTrainer.ppo_update on the reference with lr=0 and no effective grad clipping:
+    stores the losses and per-tensor gradient statistics (full gradients of tensors <= 128 el.)."""
+    _ref_paths()
+    import torch
+    from mat.algorithms.mat.algorithm.transformer_policy import TransformerPolicy
+    from mat.algorithms.mat.mat_trainer import MATTrainer
+    from DCML_ENVs.DCML_utils.DCML_ActionSpace import Action_Space
+    from oracle import mat_oracle as mo
+
+    W = L - 1
+    args = _args(lr=0.0, use_valuenorm=True, max_grad_norm=1e9, n_rollout_threads=1)
+    pol = TransformerPolicy(args, [7], [W + 2], Action_Space(2, semi_index=-1, extra=True), L)
+    sd = mo.make_weights(wseed, L, profile="trained")
+    pol.transformer.load_state_dict(mo.full_state_dict(sd, L), strict=True)
+    tr = MATTrainer(args, pol, L)
+    obs, ava = synth_policy_inputs(M, L, 200 + wseed)
+    rng = np.random.RandomState(17)
+    cent = np.zeros((M * L, W + 2), np.float32)
+    with torch.no_grad():
+        torch.manual_seed(3)
+        v, a, lp, _, _ = pol.get_actions(cent, obs, None, None, None, ava.copy(), deterministic=False)
+    actions = a.numpy().astype(np.float32)
+    old_lp = (lp.numpy() + 0.3 * rng.standard_normal(lp.shape)).astype(np.float32)
+    adv = rng.standard_normal((M * L, 1)).astype(np.float32)
+    vpred = (v.numpy() + 0.3 * rng.standard_normal(v.shape)).astype(np.float32)
+    ret = (rng.standard_normal((M * L, 1)) * 30 - 100).astype(np.float32)
+    active = np.ones((M * L, 1), np.float32)
+    active[::7] = 0.0
+    for _ in range(2):
+        tr.value_normalizer.update(torch.from_numpy((rng.standard_normal((64, 1)) * 30 - 100).astype(np.float32)))
+    vn0 = np.array([tr.value_normalizer.running_mean.item(), tr.value_normalizer.running_mean_sq.item(),
+                    tr.value_normalizer.debiasing_term.item()], np.float32)
+    sample = (cent, obs.astype(np.float32), None, None, actions, vpred, ret, None, active, old_lp, adv,
+              ava.astype(np.float32))
+    pol.train()
+    vl, gn, pl, ent, _, ratio = tr.ppo_update(sample)
+    res = {"L": L, "M": M, "wseed": wseed, "obs": obs, "ava": ava, "actions": actions, "old_logp": old_lp,
+           "adv": adv, "value_preds": vpred, "returns": ret, "active": active, "vn_stats_before": vn0,
+           "value_loss": vl.item(), "policy_loss": pl.item(), "entropy": ent.item(), "grad_norm": float(gn),
+           "ratio_mean": ratio.mean().item()}
+    proj = np.random.RandomState(99)
+    names, stats = [], []
+    for name, p in pol.transformer.named_parameters():
+        g = np.zeros(p.shape, np.float32) if p.grad is None else p.grad.numpy()
+        r = proj.standard_normal(g.shape)
+        names.append(name)
+        stats.append([g.sum(dtype=np.float64), np.sqrt((g.astype(np.float64) ** 2).sum()), (g * r).sum(dtype=np.float64),
+                      0.0 if p.grad is None else 1.0])
+        if g.size <= 128:
+            res["grad/" + name] = g
+    res["grad_names"], res["grad_stats"] = np.array(names), np.array(stats)
+    np.savez_compressed(out, **res)
+    print("wrote", out)
+
+
+FAMILIES = {
+    "policy_L21_trained": lambda o: gen_policy(o, 21, 5, "trained", 3),
+    "policy_L21_init": lambda o: gen_policy(o, 21, 5, "init", 4),
+    "policy_L101_trained": lambda o: gen_policy(o, 101, 2, "trained", 5),
+    "policy_L13_discrete": lambda o: gen_policy(o, 13, 4, "trained", 6, semi=False),
+    "env_W100": lambda o: gen_env(o, 100, 3, 6, 1, True),
+    "env_W20": lambda o: gen_env(o, 20, 6, 8, 2, False),
+    "gae": gen_gae,
+    "ppo_L11": lambda o: gen_ppo(o, 11, 6, 8),
+}
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("family", nargs="?")
+    ns = ap.parse_args()
+    if ns.family:
+        FAMILIES[ns.family](os.path.join(HERE, ns.family + ".npz"))
+    else:
+        for fam in FAMILIES:
+            subprocess.check_call([sys.executable, os.path.abspath(__file__), fam],
+                                  env=dict(os.environ, PYTHONDONTWRITEBYTECODE="1"))
