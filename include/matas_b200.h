@@ -1,0 +1,155 @@
+/*
+ * matas_b200.h -- C ABI of the B200-native MAT-AS decision-and-rollout hot path.
+ *
+ * The reference (brithbutter/mat-dcml) is pure Python and has no FFI; its boundary for this
+ * path is the duck-typed policy / vec-env / buffer contract cited per function below (paths are
+ * relative to the reference root).  A Python host binds these entry points with ctypes
+ * (mat_dcml_b200/_cabi.py; INTEGRATION.md shows the stub a reference maintainer would add).
+ *
+ * Conventions
+ *  - every function returns 0 on success, non-zero otherwise; matas_last_error() then returns a
+ *    thread-local, human-readable message.  No exception crosses the boundary.
+ *  - all array arguments are DEVICE pointers to contiguous fp32 (or the stated type) unless the
+ *    name ends in _host; they are borrowed for the duration of the call.  `stream` is a
+ *    cudaStream_t passed as void*; work is enqueued, not synchronised.
+ *  - handles belong to the CUDA device that was current at creation, are not thread-safe and
+ *    must be used with that device current.  Functions that take a handle may allocate device
+ *    scratch (cudaMalloc) the first time a larger batch is seen.
+ *  - layouts are env-major / agent-minor, exactly the reference's flattened (B*L, dim) arrays.
+ */
+#ifndef MATAS_B200_H
+#define MATAS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MATAS_MODE_SEMI 0     /* 'Semi_Discrete': L-1 binary agents + 1 Gaussian agent (every DCML config) */
+#define MATAS_MODE_DISCRETE 1 /* 'Discrete': L binary agents */
+
+const char* matas_last_error(void);
+int matas_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Policy: replaces MultiAgentTransformer (mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:233-339)
+ * behind TransformerPolicy (.../transformer_policy.py:9-255).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct matas_policy matas_policy;
+
+typedef struct {
+    int n_agent;   /* L = workers + 1 */
+    int obs_dim;   /* 7 for DCML (DCML_ENVs/DCML_utils/DCML_Config.py:13-17); <= 8 supported */
+    int state_dim; /* share_obs width W+2; only sizes the unused encoder.state_encoder parameters */
+    int act_dim;   /* 2 */
+    int n_block;   /* 2  (mat_src/mat/config.py:305) */
+    int n_embd;    /* 64 (config.py:306) */
+    int n_head;    /* 2  (config.py:307) */
+    int mode;      /* MATAS_MODE_* ; transformer_policy.py:27-37 */
+} matas_model_cfg;
+
+/* transformer_policy.py:82-86 (model construction). */
+int matas_policy_create(const matas_model_cfg* cfg, matas_policy** out);
+int matas_policy_destroy(matas_policy* p);
+
+/* Number of trainable parameters, i.e. the length of the flat vector below (151,469 at L=101). */
+long matas_policy_param_count(const matas_policy* p);
+
+/* Load parameters from ONE flat fp32 device vector holding every nn.Parameter of the reference
+ * model in state_dict order (mask buffers excluded).  Replaces load_state_dict /
+ * the implicit sharing of module parameters (transformer_policy.py:246-248); call again after
+ * every optimizer step. */
+int matas_policy_set_weights(matas_policy* p, const float* flat_params, void* stream);
+
+/* MultiAgentTransformer.get_values, ma_transformer.py:331-339 (encoder only).
+ * obs [B*L*obs_dim] -> values [B*L]. */
+int matas_policy_get_values(matas_policy* p, const float* obs, long B, float* values, void* stream);
+
+/* MultiAgentTransformer.get_actions, ma_transformer.py:298-329, i.e. encoder +
+ * semi_discrete_autoregreesive_act / discrete_autoregreesive_act
+ * (mat_src/mat/algorithms/utils/transformer_act.py:30-100, 131-173), including the stride-block
+ * deterministic schedule.
+ *   ava    [B*L*2] availability (1/0) or NULL
+ *   u, z   injected randomness of the stochastic branch: u [B*L] uniforms in [0,1), z [B*2]
+ *          standard normals; NULL = draw them in-kernel from Philox(seed, env_offset+env, step)
+ *   out    values [B*L], actions [B*L] (0/1 as float; the Gaussian agent's real value),
+ *          logp [B*L] */
+int matas_policy_get_actions(matas_policy* p, const float* obs, const float* ava, long B, int deterministic,
+                             int stride, uint64_t seed, uint32_t step, long env_offset, const float* u,
+                             const float* z, float* values, float* actions, float* logp, void* stream);
+
+/* MultiAgentTransformer.forward, ma_transformer.py:257-295, i.e. encoder +
+ * semi_discrete_parallel_act / discrete_parallel_act (transformer_act.py:103-129, 176-189).
+ * actions [M*L] -> values [M*L], logp [M*L], entropy [M*L] (per agent; the masked mean of
+ * transformer_policy.py:212-215 is the caller's). */
+int matas_policy_evaluate(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
+                          float* values, float* logp, float* entropy, void* stream);
+
+/* Encoder.forward, ma_transformer.py:141-154: obs -> values [B*L] and obs_rep [B*L*64]. */
+int matas_policy_encode(matas_policy* p, const float* obs, long B, float* values, float* obs_rep, void* stream);
+
+/* The reference's second-level entry points, which start from obs_rep:
+ * semi_discrete_autoregreesive_act / discrete_autoregreesive_act (transformer_act.py:30-100, 131-173);
+ * arguments as matas_policy_get_actions. */
+int matas_policy_act_autoregressive(matas_policy* p, const float* obs_rep, const float* ava, long B, int deterministic,
+                                    int stride, uint64_t seed, uint32_t step, long env_offset, const float* u,
+                                    const float* z, float* actions, float* logp, void* stream);
+
+/* semi_discrete_parallel_act / discrete_parallel_act (transformer_act.py:103-129, 176-189). */
+int matas_policy_act_parallel(matas_policy* p, const float* obs_rep, const float* ava, const float* actions, long M,
+                              float* logp, float* entropy, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Vectorised DCML simulator: replaces Env.step / Env.reset
+ * (DCML_BID_FIRST_MA_ENV_SingleProcess.py:57-144, 157-274), Worker.process / bid
+ * (DCML_Worker_TIMESLOT_MultiProcess.py:46-135), Master.reset / get_workload (DCML_Master.py:35-56)
+ * and ShareDummyVecEnv (mat_src/mat/envs/env_wrappers.py:713-744) for B envs at once.
+ * Random quantities are the named Philox draws documented in DESIGN.md ("Random streams").
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dcml_env dcml_env;
+
+typedef struct {
+    long n_envs;
+    int n_workers;     /* W; agents L = W+1 */
+    uint64_t seed;
+    long env_offset;   /* global index of env 0 (rank * n_envs when sharded) */
+    int double_reset;  /* 1 = ShareDummyVecEnv's second reset on done (env_wrappers.py:730-736) */
+} dcml_env_cfg;
+
+/* Env.__init__ (…SingleProcess.py:16-55): base_workload_host is the workloads.txt table,
+ * [W][20] float64 on the HOST. */
+int dcml_env_create(const dcml_env_cfg* cfg, const double* base_workload_host, dcml_env** out);
+int dcml_env_destroy(dcml_env* e);
+
+/* Env.reset: obs [B*L*7], share_obs [B*(W+2)] (ONE row per env; the reference replicates it over
+ * the L agents, …SingleProcess.py:270), ava [B*L*2]. */
+int dcml_env_reset(dcml_env* e, float* obs, float* share_obs, float* ava, void* stream);
+
+/* Env.step: actions [B*L] -> next obs/share_obs/ava plus reward [B], done [B] (uint8),
+ * delay [B], payment [B] (the info dict, …SingleProcess.py:143); the reference broadcasts
+ * reward/done over the L agents (DCML_ENVs/DCML_Basic_Env.py:9-13). */
+int dcml_env_step(dcml_env* e, const float* actions, float* obs, float* share_obs, float* ava, float* reward,
+                  uint8_t* done, float* delay, float* payment, void* stream);
+
+/* Preset contexts (Env(preset=True) / modify_preset, …SingleProcess.py:25-32,174-194,344-353):
+ * overwrite the context the next step will run against and re-emit the observation.
+ * R, C [B] float64; worker_pr [B*W] float64; n_disabled [B] int32; any may be NULL (= keep). */
+int dcml_env_set_context(dcml_env* e, const double* R, const double* C, const double* worker_pr,
+                         const int32_t* n_disabled, float* obs, float* share_obs, float* ava, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * GAE / returns: replaces SharedReplayBuffer.compute_returns + ValueNorm.denormalize
+ * (mat_src/mat/utils/shared_buffer.py:207-238, mat_src/mat/utils/valuenorm.py:32-36,69-79).
+ *   rewards [T][n], value_preds [T+1][n] (row T = bootstrap value, already written),
+ *   masks [T+1][n], n = N*L;  vn_stats = {running_mean, running_mean_sq, debiasing_term}
+ *   device fp32[3] or NULL (no ValueNorm) -> advantages [T][n], returns [T+1][n] (row T untouched).
+ * ------------------------------------------------------------------------------------------ */
+int matas_gae(const float* rewards, const float* value_preds, const float* masks, const float* vn_stats,
+              double gamma, double gae_lambda, int T, long n, float* advantages, float* returns, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MATAS_B200_H */

@@ -1,0 +1,278 @@
+// extern "C" entry points of libmatas_b200.so (declared in include/matas_b200.h): policy handle,
+// weight repacking, scratch management.  The DCML simulator and GAE entry points live in env.cu
+// and gae.cu.
+#include <stdarg.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/matas_b200.h"
+#include "layout.h"
+#include "policy_fwd.h"
+
+static thread_local char g_err[512] = "";
+
+void matas_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* matas_last_error(void) { return g_err; }
+extern "C" int matas_version(void) { return 100; }
+
+// one repack instruction: copy a vector (cols == 0) or transpose W[rows][cols] -> dst[c*64 + r]
+struct PackEntry { int src, dst, rows, cols; };
+
+__global__ void pack_kernel(const float* __restrict__ flat, float* __restrict__ packed, const PackEntry* __restrict__ tab) {
+    const PackEntry e = tab[blockIdx.x];
+    if (e.cols == 0) {
+        for (int i = threadIdx.x; i < e.rows; i += blockDim.x) packed[e.dst + i] = flat[e.src + i];
+    } else {
+        const int n = e.rows * e.cols;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const int r = i / e.cols, c = i - r * e.cols;
+            packed[e.dst + c * 64 + r] = flat[e.src + i];
+        }
+    }
+}
+
+struct matas_policy {
+    matas_model_cfg cfg;
+    int device;
+    int n_sm;
+    long n_params;
+    std::vector<PackEntry> table;
+    PackEntry* d_table = nullptr;
+    float* d_packed = nullptr;
+    bool weights_set = false;
+    // scratch
+    long tok_cap = 0;
+    float* d_tok = nullptr;      // 17 token buffers [cap][64]
+    size_t kv_cap = 0;
+    float* d_kv = nullptr;
+    PolicyBufs bufs;
+};
+
+namespace {
+
+// walks the parameters in the reference's state_dict order (ma_transformer.py:119-203)
+struct LayoutBuilder {
+    std::vector<PackEntry>& tab;
+    int src = 0;
+    explicit LayoutBuilder(std::vector<PackEntry>& t) : tab(t) {}
+    void vec(int n, int dst) { if (dst >= 0) tab.push_back({src, dst, n, 0}); src += n; }
+    void mat(int rows, int cols, int dst) { if (dst >= 0) tab.push_back({src, dst, rows, cols}); src += rows * cols; }
+    void linear(int out, int in, int dst_wt, int dst_b, bool bias = true) {
+        mat(out, in, dst_wt);
+        if (bias) vec(out, dst_b);
+    }
+    void blob_linear(int blob) { linear(64, 64, blob, blob + lay::B_BIAS); }
+    void blob_ln(int blob) { vec(64, blob + lay::B_LNW); vec(64, blob + lay::B_LNB); }
+};
+
+long build_layout(const matas_model_cfg& c, std::vector<PackEntry>& tab) {
+    LayoutBuilder b(tab);
+    using namespace lay;
+    // encoder.state_encoder (unused when encode_state=False, ma_transformer.py:144-149)
+    b.vec(c.state_dim, -1); b.vec(c.state_dim, -1); b.linear(64, c.state_dim, -1, -1);
+    b.vec(c.obs_dim, ENC_EMB + ENC_EMB_LNW); b.vec(c.obs_dim, ENC_EMB + ENC_EMB_LNB);
+    b.linear(64, c.obs_dim, ENC_EMB + ENC_EMB_WT, ENC_EMB + ENC_EMB_B);
+    b.vec(64, ENC_EMB + ENC_EMB_LN2W); b.vec(64, ENC_EMB + ENC_EMB_LN2B);
+    for (int k = 0; k < 2; ++k) {
+        b.blob_ln(enc_blob(k, EP));
+        b.blob_ln(enc_blob(k, EM2));
+        b.blob_linear(enc_blob(k, EK)); b.blob_linear(enc_blob(k, EQ)); b.blob_linear(enc_blob(k, EV)); b.blob_linear(enc_blob(k, EP));
+        b.blob_linear(enc_blob(k, EM0)); b.blob_linear(enc_blob(k, EM2));
+    }
+    b.blob_linear(ENC_H0); b.blob_ln(ENC_H0);
+    b.vec(64, ENC_H3); b.vec(1, ENC_H3 + 64);
+    if (c.mode == MATAS_MODE_SEMI) b.vec(c.act_dim, DEC_H3 + DEC_H3_LOGSTD);
+    b.mat(64, c.act_dim + 1, DEC_EMB + DEC_EMB_WT);
+    // decoder.obs_encoder (unused unless dec_actor, ma_transformer.py:198-199)
+    b.vec(c.obs_dim, -1); b.vec(c.obs_dim, -1); b.linear(64, c.obs_dim, -1, -1);
+    b.vec(64, DEC_EMB + DEC_EMB_LNW); b.vec(64, DEC_EMB + DEC_EMB_LNB);
+    for (int k = 0; k < 2; ++k) {
+        b.blob_ln(dec_blob(k, DP1)); b.blob_ln(dec_blob(k, DP2)); b.blob_ln(dec_blob(k, DM2));
+        b.blob_linear(dec_blob(k, DK1)); b.blob_linear(dec_blob(k, DQ1)); b.blob_linear(dec_blob(k, DV1)); b.blob_linear(dec_blob(k, DP1));
+        b.blob_linear(dec_blob(k, DK2)); b.blob_linear(dec_q2(k)); b.blob_linear(dec_blob(k, DV2)); b.blob_linear(dec_blob(k, DP2));
+        b.blob_linear(dec_blob(k, DM0)); b.blob_linear(dec_blob(k, DM2));
+    }
+    b.blob_linear(DEC_H0); b.blob_ln(DEC_H0);
+    b.vec(2 * 64, DEC_H3); b.vec(2, DEC_H3 + DEC_H3_B);
+    return b.src;
+}
+
+int check_handle(const matas_policy* p) {
+    ARG_CHECK(p != nullptr, "null policy handle");
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    ARG_CHECK(dev == p->device, "policy handle belongs to device %d but device %d is current", p->device, dev);
+    ARG_CHECK(p->weights_set, "matas_policy_set_weights has not been called");
+    return MATAS_OK;
+}
+
+}  // namespace
+
+extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** out) {
+    ARG_CHECK(cfg && out, "null argument");
+    if (cfg->n_embd != 64 || cfg->n_head != 2 || cfg->n_block != 2 || cfg->act_dim != 2) {
+        matas_set_error("unsupported model: kernels are built for n_embd=64 n_head=2 n_block=2 act_dim=2 "
+                        "(got %d %d %d %d)", cfg->n_embd, cfg->n_head, cfg->n_block, cfg->act_dim);
+        return MATAS_ERR_UNSUPPORTED;
+    }
+    ARG_CHECK(cfg->obs_dim >= 1 && cfg->obs_dim <= 8, "obs_dim %d not in [1,8]", cfg->obs_dim);
+    ARG_CHECK(cfg->n_agent >= 2, "n_agent %d < 2", cfg->n_agent);
+    ARG_CHECK(cfg->state_dim >= 1, "state_dim %d < 1", cfg->state_dim);
+    ARG_CHECK(cfg->mode == MATAS_MODE_SEMI || cfg->mode == MATAS_MODE_DISCRETE, "bad mode %d", cfg->mode);
+    int depth, lpad; size_t bytes;
+    int rc = policy_launch_geometry(cfg->n_agent, &depth, &lpad, &bytes);
+    if (rc) return rc;
+    matas_policy* p = new matas_policy();
+    p->cfg = *cfg;
+    memset(&p->bufs, 0, sizeof(p->bufs));
+    if (cudaGetDevice(&p->device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device) != cudaSuccess) {
+        matas_set_error("no usable CUDA device: %s", cudaGetErrorString(cudaGetLastError()));
+        delete p;
+        return MATAS_ERR_CUDA;
+    }
+    p->n_params = build_layout(p->cfg, p->table);
+    auto fail = [&](cudaError_t e, const char* what) {
+        matas_set_error("%s: %s", what, cudaGetErrorString(e));
+        matas_policy_destroy(p);
+        return MATAS_ERR_CUDA;
+    };
+    cudaError_t e;
+    if ((e = cudaMalloc(&p->d_table, p->table.size() * sizeof(PackEntry))) != cudaSuccess) return fail(e, "cudaMalloc(table)");
+    if ((e = cudaMemcpy(p->d_table, p->table.data(), p->table.size() * sizeof(PackEntry), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return fail(e, "cudaMemcpy(table)");
+    if ((e = cudaMalloc(&p->d_packed, lay::TOTAL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMalloc(packed)");
+    if ((e = cudaMemset(p->d_packed, 0, lay::TOTAL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMemset(packed)");
+    p->bufs.w = p->d_packed;
+    if ((rc = policy_init_constants())) { matas_policy_destroy(p); return rc; }
+    *out = p;
+    return MATAS_OK;
+}
+
+extern "C" int matas_policy_destroy(matas_policy* p) {
+    if (!p) return MATAS_OK;
+    cudaFree(p->d_table); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv);
+    delete p;
+    return MATAS_OK;
+}
+
+extern "C" long matas_policy_param_count(const matas_policy* p) { return p ? p->n_params : -1; }
+
+extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void* stream) {
+    ARG_CHECK(p && flat, "null argument");
+    pack_kernel<<<(unsigned)p->table.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_table);
+    CUDA_TRY(cudaGetLastError());
+    p->weights_set = true;
+    return MATAS_OK;
+}
+
+static int alloc_tokens(matas_policy* p, long n_tok) {
+    if (n_tok <= p->tok_cap) return MATAS_OK;
+    if (p->d_tok) CUDA_TRY(cudaFree(p->d_tok));
+    p->d_tok = nullptr; p->tok_cap = 0;
+    const long cap = n_tok + 64;
+    constexpr int NBUF = 17;
+    CUDA_TRY(cudaMalloc(&p->d_tok, (size_t)cap * 64 * sizeof(float) * NBUF));
+    float* f = p->d_tok;
+    auto take = [&]() { float* r = f; f += cap * 64; return r; };
+    PolicyBufs& b = p->bufs;
+    b.X = take(); b.Q = take(); b.rep = take(); b.Q2[0] = take(); b.Q2[1] = take();
+    for (int k = 0; k < 2; ++k) { b.K[k] = take(); b.V[k] = take(); b.K1[k] = take(); b.V1[k] = take(); b.K2[k] = take(); b.V2[k] = take(); }
+    p->tok_cap = cap;
+    return MATAS_OK;
+}
+
+extern "C" int matas_policy_get_values(matas_policy* p, const float* obs, long B, float* values, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs && values && B > 0, "bad argument (B=%ld)", B);
+    if ((rc = alloc_tokens(p, B * p->cfg.n_agent))) return rc;
+    return launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream);
+}
+
+static int run_decode(matas_policy* p, const float* ava, long B, int deterministic, int stride, uint64_t seed,
+                      uint32_t step, long env_offset, const float* u, const float* z, float* actions, float* logp,
+                      cudaStream_t stream) {
+    const int L = p->cfg.n_agent;
+    const long n_tiles = (B + 63) / 64;
+    const int grid = (int)(n_tiles < p->n_sm ? n_tiles : p->n_sm);
+    const size_t need = (size_t)grid * 64 * 8 * L * 64 * sizeof(float);
+    if (need > p->kv_cap) {
+        if (p->d_kv) CUDA_TRY(cudaFree(p->d_kv));
+        p->d_kv = nullptr; p->kv_cap = 0;
+        CUDA_TRY(cudaMalloc(&p->d_kv, need));
+        p->kv_cap = need;
+    }
+    p->bufs.kv = p->d_kv;
+    DecodeArgs a;
+    a.B = B; a.L = L; a.mode = p->cfg.mode; a.deterministic = deterministic ? 1 : 0; a.stride = stride;
+    a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
+    a.seed = seed; a.step = step; a.env_offset = env_offset;
+    a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
+    return launch_decode(p->bufs, a, grid, stream);
+}
+
+extern "C" int matas_policy_get_actions(matas_policy* p, const float* obs, const float* ava, long B, int deterministic,
+                                        int stride, uint64_t seed, uint32_t step, long env_offset, const float* u,
+                                        const float* z, float* values, float* actions, float* logp, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs && values && actions && logp && B > 0, "bad argument (B=%ld)", B);
+    if ((rc = alloc_tokens(p, B * p->cfg.n_agent))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream))) return rc;
+    return run_decode(p, ava, B, deterministic, stride, seed, step, env_offset, u, z, actions, logp, (cudaStream_t)stream);
+}
+
+extern "C" int matas_policy_act_autoregressive(matas_policy* p, const float* obs_rep, const float* ava, long B,
+                                               int deterministic, int stride, uint64_t seed, uint32_t step,
+                                               long env_offset, const float* u, const float* z, float* actions,
+                                               float* logp, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs_rep && actions && logp && B > 0, "bad argument (B=%ld)", B);
+    if ((rc = alloc_tokens(p, B * p->cfg.n_agent))) return rc;
+    if ((rc = launch_q2_from_rep(p->bufs, obs_rep, B, p->cfg.n_agent, (cudaStream_t)stream))) return rc;
+    return run_decode(p, ava, B, deterministic, stride, seed, step, env_offset, u, z, actions, logp, (cudaStream_t)stream);
+}
+
+extern "C" int matas_policy_act_parallel(matas_policy* p, const float* obs_rep, const float* ava, const float* actions,
+                                         long M, float* logp, float* entropy, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs_rep && actions && logp && entropy && M > 0, "bad argument (M=%ld)", M);
+    const int L = p->cfg.n_agent;
+    if ((rc = alloc_tokens(p, M * L))) return rc;
+    if ((rc = launch_q2_from_rep(p->bufs, obs_rep, M, L, (cudaStream_t)stream))) return rc;
+    return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream);
+}
+
+/* encoder only, exposing obs_rep (Encoder.forward, ma_transformer.py:141-154) */
+extern "C" int matas_policy_encode(matas_policy* p, const float* obs, long B, float* values, float* obs_rep, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs && values && obs_rep && B > 0, "bad argument (B=%ld)", B);
+    const long n_tok = B * p->cfg.n_agent;
+    if ((rc = alloc_tokens(p, n_tok))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(obs_rep, p->bufs.rep, (size_t)n_tok * 64 * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return MATAS_OK;
+}
+
+extern "C" int matas_policy_evaluate(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
+                                     float* values, float* logp, float* entropy, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs && actions && values && logp && entropy && M > 0, "bad argument (M=%ld)", M);
+    const int L = p->cfg.n_agent;
+    if ((rc = alloc_tokens(p, M * L))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, M, L, p->cfg.obs_dim, (cudaStream_t)stream))) return rc;
+    return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream);
+}

@@ -1,0 +1,478 @@
+// Vectorised DCML simulator for sm_100a: one thread per (env, worker), whole envs per CTA.
+//
+// Restates Env.step / Env.reset (DCML_BID_FIRST_MA_ENV_SingleProcess.py:57-144,157-274),
+// Worker.process / bid (DCML_Worker_TIMESLOT_MultiProcess.py:46-135), Master.reset /
+// get_workload (DCML_Master.py:35-56) and the ShareDummyVecEnv double reset
+// (mat_src/mat/envs/env_wrappers.py:730-736).  All scalar time arithmetic is float64 in the
+// reference's evaluation order (this file is compiled with -fmad=false), because the simulator
+// branches on floor/ceil/compare of those values.  Randomness: named
+// Philox draws (common.cuh / DESIGN.md).  HBM traffic per env-step is the 160 B/worker workload
+// table read + written, the Pr / flag state, and the observation rows.
+#include "../../include/matas_b200.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int PERIOD = 20;
+constexpr double DATA_RATE = 157286400.0;   // 150 * 2^20
+constexpr double FREQUENCY = 2e9;
+constexpr double PR_MAX = 0.95;
+constexpr double DONE_P = 0.8;
+constexpr int R_MIN = 1024, R_MAX = 1048576, C_MIN = 32, C_MAX = 1024;
+constexpr int R_HI = 1153434, C_HI = 1126;   // round(1.1 * max), DCML_Master.py:47-48
+constexpr int RETRY_CAP = 4096, SLOT_CAP = 4096;
+constexpr int LWS = 21;                      // padded per-thread stride of the shared workload copy
+
+enum { ENV_INIT = 0, ENV_STEP = 1, ENV_OBSERVE = 2 };
+
+struct EnvState {
+    long B;
+    int W, tpe;            // threads per env (W rounded up to a warp multiple)
+    uint64_t seed;
+    long env_offset;
+    int double_reset;
+    const double* base;    // [W][20]
+    double* lw;            // [B][W][20] current jittered workload == next step's local workload
+    double* R;             // [B]
+    double* C;             // [B]
+    double* Pr;            // [B][W]
+    int* arrive;           // [B]
+    int* kdis;             // [B]
+    uint8_t* disabled;     // [B][W]
+};
+
+struct EnvIO {
+    const float* actions;  // [B][L]
+    float* obs;            // [B][L][7]
+    float* sob;            // [B][W+2]
+    float* ava;            // [B][L][2]
+    float* reward;         // [B]
+    uint8_t* done;         // [B]
+    float* delay;          // [B]
+    float* payment;        // [B]
+};
+
+struct RetryStream {
+    uint32_t env, step, tag;
+    uint64_t seed;
+    uint4 cur;
+    int k;
+    __device__ void init(uint32_t env_, uint32_t step_, int w, uint64_t seed_) {
+        env = env_; step = step_; tag = rng_tag(S_RETRY, (uint32_t)w); seed = seed_; k = 0;
+    }
+    __device__ double next() {
+        if ((k & 3) == 0) cur = philox4x32(env, step, tag, (uint32_t)(k >> 2), seed);
+        const double u = u01d(lane_of(cur, k & 3));
+        ++k;
+        return u;
+    }
+};
+
+struct ProcOut { double delay, price0; int tp0, nslots; };
+
+// Worker.process, DCML_Worker_TIMESLOT_MultiProcess.py:46-112; lw = this worker's 20 local slots
+__device__ ProcOut process(const double* lw, double Pr, double r, double c, int arrive, RetryStream& rs) {
+    ProcOut o;
+    double cost = ceil((9.0 * r - 3.0) * c) / FREQUENCY;                    // :49-50
+    int n = 1;
+    while (rs.next() < Pr && n < RETRY_CAP) ++n;                            // :54-56
+    const double t_down = ((ceil((r + 1.0) * c) * 1.0 * 4.0) / DATA_RATE + 0.001) * (double)n;   // :60
+    double price = floor(t_down) * 0.1;                                     // :65
+    const int slot = (int)floor(t_down + (double)arrive);                   // :66
+    int tp = slot % PERIOD;                                                 // :67-69
+    int finish = slot;
+    double avail = 0.0;
+    const double frac = fmod(t_down, 1.0);
+    if (frac > lw[tp]) cost += frac - lw[tp];                               // :85-86
+    o.price0 = price; o.tp0 = tp;
+    int nslots = 0;
+    double t_up = 0.0;
+    while (avail < cost && nslots < SLOT_CAP) {                             // :87-106
+        const double fr = 1.0 - lw[tp];
+        price += fr * 1.0;
+        avail += fr;
+        ++nslots; ++finish; ++tp;
+        if (tp > PERIOD - 1) tp -= PERIOD;
+        while (rs.next() < Pr && n < RETRY_CAP) ++n;
+        t_up = ((ceil(r) * 1.0 * 4.0) / DATA_RATE + 0.001) * (double)n + 0.02;
+    }
+    o.nslots = nslots;
+    o.delay = (double)(finish - arrive) - (avail - cost) + t_up;            // :108
+    return o;
+}
+
+// cumulative price after m compute slots (the reference's prices[m-1]), same addition order
+__device__ double price_after(const double* lw, const ProcOut& o, int m) {
+    double price = o.price0;
+    int tp = o.tp0;
+    for (int s = 0; s < m; ++s) {
+        price += (1.0 - lw[tp]) * 1.0;
+        if (++tp > PERIOD - 1) tp -= PERIOD;
+    }
+    return price;
+}
+
+__global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int W = st.W, L = W + 1, tpe = st.tpe;
+    const int epb = blockDim.x / tpe;
+    const int le = threadIdx.x / tpe;            // local env
+    const int w = threadIdx.x - le * tpe;        // worker (>= W: idle lane)
+    const long env = (long)blockIdx.x * epb + le;
+    const bool env_ok = env < st.B;
+    const bool active = env_ok && w < W;
+    const uint32_t genv = (uint32_t)(st.env_offset + env);
+
+    // shared carve-up (per block)
+    double* s_lw = reinterpret_cast<double*>(smem_raw);                 // [threads][LWS] old workload
+    double* s_d = s_lw + (size_t)blockDim.x * LWS;                      // [threads] delay, later price / Pr
+    double* s_f = s_d + blockDim.x;                                     // [threads][3] observed slots
+    double* s_sc = s_f + (size_t)blockDim.x * 3;                        // [epb][8] scalars
+    uint32_t* s_key = reinterpret_cast<uint32_t*>(s_sc + (size_t)epb * 8);   // [threads]
+    float* s_sel = reinterpret_cast<float*>(s_key + blockDim.x);        // [threads]
+    int* s_i = reinterpret_cast<int*>(s_sel + blockDim.x);              // [epb][8] int scalars
+    uint8_t* s_dis = reinterpret_cast<uint8_t*>(s_i + (size_t)epb * 8); // [threads]
+
+    double* my_lw = s_lw + (size_t)threadIdx.x * LWS;
+    double* sc = s_sc + le * 8;     // 0 final delay, 1 payment, 2 R, 3 C
+    int* si = s_i + le * 8;         // 0 N, 1 K, 2 n0 flag, 3 arrive, 4 kdis, 5 done
+    double* e_d = s_d + le * tpe;
+    float* e_sel = s_sel + le * tpe;
+    uint32_t* e_key = s_key + le * tpe;
+    uint8_t* e_dis = s_dis + le * tpe;
+    double* glw = st.lw + (env * W + w) * PERIOD;
+
+    if (what == ENV_INIT) {
+        // Worker.__init__ :39  all_workload = clip(base * U(0.8,1.2), 0, 1), step-0 jitter stream
+        if (active) {
+            for (int blk = 0; blk < 5; ++blk) {
+                const uint4 x = philox4x32(genv, 0u, rng_tag(S_JITTER, (uint32_t)w), (uint32_t)blk, st.seed);
+                for (int i = 0; i < 4; ++i) {
+                    const double v = st.base[w * PERIOD + blk * 4 + i] * (0.8 + (1.2 - 0.8) * u01d(lane_of(x, i)));
+                    glw[blk * 4 + i] = fmin(fmax(v, 0.0), 1.0);
+                }
+            }
+        }
+    }
+
+    if (what == ENV_STEP) {
+        // ---- Env.step :65-74, 96-105 ---------------------------------------------------------
+        if (active) {
+            e_sel[w] = io.actions[env * L + w];
+            for (int i = 0; i < PERIOD; i += 2) {
+                const double2 v = *reinterpret_cast<const double2*>(glw + i);
+                my_lw[i] = v.x; my_lw[i + 1] = v.y;
+            }
+        }
+        __syncthreads();
+        if (env_ok && w == 0) {
+            float sum = 0.f;
+            for (int i = 0; i < W; ++i) sum = __fadd_rn(sum, e_sel[i]);
+            int N = (int)sum;                                              // :71
+            const float ratio = io.actions[env * L + W];
+            int K = (int)ceilf(__fmul_rn((float)N, ratio));               // :72 (fp32 product of fp32 actions)
+            si[2] = N == 0;
+            N = min(max(N, 1), W);
+            K = min(max(K, 1), N);
+            if (si[2]) K = 1;                                              // :82 update_strategy(K=1,N=1)
+            si[0] = N; si[1] = K;
+            sc[0] = 0.0;
+            sc[2] = st.R[env]; sc[3] = st.C[env];
+            si[3] = st.arrive[env];
+        }
+        __syncthreads();
+        const bool n0 = env_ok && si[2];
+        ProcOut po;
+        po.delay = 0.0; po.price0 = 0.0; po.tp0 = 0; po.nslots = 0;
+        const bool runs = active && (!n0 || w == 0);                       // :83 vs :106-111
+        if (runs) {
+            RetryStream rs;
+            rs.init(genv, t, w, st.seed);
+            const double r = ceil(sc[2] / (double)si[1]);                  // Master.get_workload, DCML_Master.py:39-40
+            po = process(my_lw, st.Pr[env * W + w], r, sc[3], si[3], rs);
+            e_d[w] = po.delay;
+            // Worker.process :111 redraw the workload (step-t jitter stream)
+            for (int blk = 0; blk < 5; ++blk) {
+                const uint4 x = philox4x32(genv, t, rng_tag(S_JITTER, (uint32_t)w), (uint32_t)blk, st.seed);
+                double nv[4];
+                for (int i = 0; i < 4; ++i) {
+                    const double v = st.base[w * PERIOD + blk * 4 + i] * (0.8 + (1.2 - 0.8) * u01d(lane_of(x, i)));
+                    nv[i] = fmin(fmax(v, 0.0), 1.0);
+                }
+                *reinterpret_cast<double2*>(glw + blk * 4) = make_double2(nv[0], nv[1]);
+                *reinterpret_cast<double2*>(glw + blk * 4 + 2) = make_double2(nv[2], nv[3]);
+            }
+        }
+        __syncthreads();
+        // ---- k-of-n completion order statistic :128-129 -------------------------------------
+        if (env_ok && n0) {
+            if (w == 0) sc[0] = po.delay;
+        } else if (active && e_sel[w] != 0.f) {
+            const double d = po.delay;
+            int rank = 0;
+            for (int j = 0; j < W; ++j)
+                if (e_sel[j] != 0.f) {
+                    const double dj = e_d[j];
+                    rank += (dj < d) || (dj == d && j < w);
+                }
+            if (rank == si[1] - 1) sc[0] = d;
+        }
+        __syncthreads();
+        // ---- payment :130-137 ----------------------------------------------------------------
+        if (runs) {
+            const int e = (int)ceil(sc[0]);
+            const int m = n0 ? po.nslots : (po.nslots >= e ? e : po.nslots);
+            e_d[w] = price_after(my_lw, po, m);
+        }
+        __syncthreads();
+        if (env_ok && w == 0) {
+            double pay = 0.0;
+            if (n0) pay = e_d[0];
+            else for (int i = 0; i < W; ++i) pay += (double)e_sel[i] * e_d[i];
+            const double fd = sc[0];
+            double rew = -(fd * 99.0) - (pay * 1.0);                       // DCML_ENV_Functions.py:15-17
+            if (n0) rew = 1.5 * rew;                                       // :88
+            io.reward[env] = (float)rew;
+            io.delay[env] = (float)fd;
+            io.payment[env] = (float)pay;
+            const uint4 x = philox4x32(genv, t, rng_tag(S_RESET, 0), 1u, st.seed);
+            const int dn = u01d(x.y) < DONE_P;                             // :142
+            si[5] = dn;
+            io.done[env] = (uint8_t)dn;
+        }
+        __syncthreads();
+    }
+
+    // ---- Env.reset :157-199 (twice when done under ShareDummyVecEnv) ---------------------------
+    if (what != ENV_OBSERVE) {
+        for (int r = 0; r < 2; ++r) {
+            const bool apply = env_ok && (r == 0 || (what == ENV_STEP && st.double_reset && si[5]));
+            if (apply && w == 0) {
+                const uint4 x = philox4x32(genv, t, rng_tag(S_RESET, 0), (uint32_t)(16 * r), st.seed);
+                const int kmax = (int)floor(0.8 * (double)W);
+                si[4] = 1 + (int)bounded(x.x, (uint32_t)kmax);                              // :158
+                si[3] = (int)bounded(x.y, PERIOD);                                           // :160
+                sc[2] = (double)(R_MIN + (int)bounded(x.z, (uint32_t)(R_HI - R_MIN + 1)));   // DCML_Master.py:47
+                sc[3] = (double)(C_MIN + (int)bounded(x.w, (uint32_t)(C_HI - C_MIN + 1)));   // DCML_Master.py:48
+            }
+            if (apply && w < W) {
+                const uint4 x = philox4x32(genv, t, rng_tag(S_WORKER, (uint32_t)w), (uint32_t)r, st.seed);
+                e_d[w] = 0.0 + (PR_MAX - 0.0) * u01d(x.x);                                   // :197
+                e_key[w] = x.y;
+            }
+            __syncthreads();
+            if (apply && w < W) {
+                // :199 choice(W, k, replace=False): the k smallest (key, index) pairs are disabled
+                const uint32_t key = e_key[w];
+                int rank = 0;
+                for (int j = 0; j < W; ++j) rank += (e_key[j] < key) || (e_key[j] == key && j < w);
+                e_dis[w] = rank < si[4];
+            }
+            __syncthreads();
+        }
+        if (active) {
+            st.Pr[env * W + w] = e_d[w];
+            st.disabled[env * W + w] = e_dis[w];
+        }
+        if (env_ok && w == 0) {
+            st.R[env] = sc[2]; st.C[env] = sc[3]; st.arrive[env] = si[3]; st.kdis[env] = si[4];
+        }
+    } else {
+        if (active) { e_d[w] = st.Pr[env * W + w]; e_dis[w] = st.disabled[env * W + w]; }
+        if (env_ok && w == 0) { sc[2] = st.R[env]; sc[3] = st.C[env]; si[3] = st.arrive[env]; si[4] = st.kdis[env]; }
+        __syncthreads();
+    }
+
+    // ---- observation :180-271 -------------------------------------------------------------------
+    const double Rn = env_ok ? (sc[2] - (double)R_MIN) / (double)(R_MAX - R_MIN) : 0.0;   // DCML_Master.py:54
+    const double Cn = env_ok ? (sc[3] - (double)C_MIN) / (double)(C_MAX - C_MIN) : 0.0;
+    double* my_f = s_f + (size_t)threadIdx.x * 3;
+    if (active) {
+        const int a = si[3];
+        const bool dis = e_dis[w];
+        int en_before = 0;
+        for (int j = 0; j < w; ++j) en_before += !e_dis[j];
+        const int n_en = W - si[4];
+        float* o = io.obs + (env * L + w) * 7;
+        o[0] = (float)Rn; o[1] = (float)Cn;
+        if (dis) {
+            // :207-213: ones, then the previous row's 7th feature (0 for the first row)
+            const double f7 = en_before > 0 ? (double)(en_before - 1) / (double)n_en : 0.0;
+            o[2] = 1.f; o[3] = 1.f; o[4] = 1.f; o[5] = 1.f; o[6] = (float)f7;
+            my_f[0] = 0.0; my_f[1] = 0.0; my_f[2] = 0.0;
+        } else {
+            for (int s = 0; s < 3; ++s) {                                  // :222
+                const double v = glw[(a + s) % PERIOD];
+                my_f[s] = v;
+                o[2 + s] = (float)v;
+            }
+            o[5] = (float)e_d[w];
+            o[6] = (float)((double)en_before / (double)n_en);              // :226
+        }
+        io.ava[(env * L + w) * 2] = 1.f;                                   // Worker.get_availability :144-148
+        io.ava[(env * L + w) * 2 + 1] = dis ? 0.f : 1.f;
+        io.sob[env * (W + 2) + 2 + w] = (float)e_d[w];                     // :252-253
+    }
+    __syncthreads();
+    if (env_ok && w == 0) {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, sp = 0.0;
+        const double* ef = s_f + (size_t)(le * tpe) * 3;
+        for (int j = 0; j < W; ++j)
+            if (!e_dis[j]) { s0 += ef[j * 3]; s1 += ef[j * 3 + 1]; s2 += ef[j * 3 + 2]; sp += e_d[j]; }
+        const double n_en = (double)(W - si[4]);
+        float* o = io.obs + (env * L + W) * 7;                             // :235-239
+        o[0] = (float)Rn; o[1] = (float)Cn;
+        o[2] = (float)(s0 / n_en); o[3] = (float)(s1 / n_en); o[4] = (float)(s2 / n_en);
+        o[5] = (float)(sp / n_en); o[6] = 1.1f;
+        io.ava[(env * L + W) * 2] = 1.f; io.ava[(env * L + W) * 2 + 1] = 1.f;
+        io.sob[env * (W + 2)] = (float)Rn; io.sob[env * (W + 2) + 1] = (float)Cn;
+    }
+}
+
+__global__ void set_context_kernel(EnvState st, const double* R, const double* C, const double* pr, const int32_t* nd) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < st.B) {
+        if (R) st.R[i] = R[i];
+        if (C) st.C[i] = C[i];
+        if (nd) st.kdis[i] = nd[i];
+    }
+    if (pr && i < st.B * st.W) st.Pr[i] = pr[i];
+}
+
+// preset disable counts: re-rank the stored keys is not possible (keys are not kept), so the
+// disabled set for a new count is re-drawn from the WORKER stream of the env's current step.
+__global__ void redraw_disabled_kernel(EnvState st, uint32_t t) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= st.B * st.W) return;
+    const long env = i / st.W;
+    const int w = (int)(i - env * st.W);
+    const uint32_t genv = (uint32_t)(st.env_offset + env);
+    const uint32_t key = philox4x32(genv, t, rng_tag(S_WORKER, (uint32_t)w), 0u, st.seed).y;
+    int rank = 0;
+    for (int j = 0; j < st.W; ++j) {
+        const uint32_t kj = philox4x32(genv, t, rng_tag(S_WORKER, (uint32_t)j), 0u, st.seed).y;
+        rank += (kj < key) || (kj == key && j < w);
+    }
+    st.disabled[i] = rank < st.kdis[env];
+}
+
+}  // namespace
+
+struct dcml_env {
+    dcml_env_cfg cfg;
+    int device;
+    EnvState st;
+    double* d_base = nullptr;
+    void* d_state = nullptr;
+    uint32_t t = 0;
+    int block, epb;
+    size_t smem;
+    bool reset_done = false;
+};
+
+static int env_launch(dcml_env* e, const EnvIO& io, int what, cudaStream_t stream) {
+    const unsigned grid = (unsigned)((e->cfg.n_envs + e->epb - 1) / e->epb);
+    env_kernel<<<grid, e->block, e->smem, stream>>>(e->st, io, what, e->t);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
+static int env_check(dcml_env* e) {
+    ARG_CHECK(e != nullptr, "null env handle");
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    ARG_CHECK(dev == e->device, "env handle belongs to device %d but device %d is current", e->device, dev);
+    return MATAS_OK;
+}
+
+extern "C" int dcml_env_create(const dcml_env_cfg* cfg, const double* base_host, dcml_env** out) {
+    ARG_CHECK(cfg && base_host && out, "null argument");
+    ARG_CHECK(cfg->n_envs > 0, "n_envs %ld <= 0", cfg->n_envs);
+    ARG_CHECK(cfg->n_workers >= 2 && cfg->n_workers <= 1024, "n_workers %d not in [2,1024]", cfg->n_workers);
+    dcml_env* e = new dcml_env();
+    e->cfg = *cfg;
+    const int W = cfg->n_workers;
+    const long B = cfg->n_envs;
+    if (cudaGetDevice(&e->device) != cudaSuccess) {
+        matas_set_error("no usable CUDA device");
+        delete e;
+        return MATAS_ERR_CUDA;
+    }
+    const int tpe = (W + 31) / 32 * 32;
+    e->epb = tpe >= 256 ? 1 : 256 / tpe;
+    e->block = e->epb * tpe;
+    e->smem = (size_t)e->block * (LWS + 1 + 3) * 8 + (size_t)e->epb * 8 * 8 + (size_t)e->block * (4 + 4) +
+              (size_t)e->epb * 8 * 4 + e->block + 16;
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t o_lw = carve((size_t)B * W * PERIOD * 8), o_R = carve(B * 8), o_C = carve(B * 8), o_Pr = carve((size_t)B * W * 8),
+                 o_arr = carve(B * 4), o_k = carve(B * 4), o_dis = carve((size_t)B * W);
+    auto fail = [&](const char* what, cudaError_t err) {
+        matas_set_error("%s: %s", what, cudaGetErrorString(err));
+        dcml_env_destroy(e);
+        return MATAS_ERR_CUDA;
+    };
+    cudaError_t err;
+    if ((err = cudaMalloc(&e->d_state, off)) != cudaSuccess) return fail("cudaMalloc(env state)", err);
+    if ((err = cudaMemset(e->d_state, 0, off)) != cudaSuccess) return fail("cudaMemset(env state)", err);
+    if ((err = cudaMalloc(&e->d_base, (size_t)W * PERIOD * 8)) != cudaSuccess) return fail("cudaMalloc(base)", err);
+    if ((err = cudaMemcpy(e->d_base, base_host, (size_t)W * PERIOD * 8, cudaMemcpyHostToDevice)) != cudaSuccess)
+        return fail("cudaMemcpy(base)", err);
+    if ((err = cudaFuncSetAttribute(env_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->smem)) != cudaSuccess)
+        return fail("cudaFuncSetAttribute(env_kernel)", err);
+    unsigned char* s = static_cast<unsigned char*>(e->d_state);
+    EnvState& st = e->st;
+    st.B = B; st.W = W; st.tpe = tpe; st.seed = cfg->seed; st.env_offset = cfg->env_offset; st.double_reset = cfg->double_reset;
+    st.base = e->d_base;
+    st.lw = reinterpret_cast<double*>(s + o_lw); st.R = reinterpret_cast<double*>(s + o_R); st.C = reinterpret_cast<double*>(s + o_C);
+    st.Pr = reinterpret_cast<double*>(s + o_Pr); st.arrive = reinterpret_cast<int*>(s + o_arr); st.kdis = reinterpret_cast<int*>(s + o_k);
+    st.disabled = s + o_dis;
+    *out = e;
+    return MATAS_OK;
+}
+
+extern "C" int dcml_env_destroy(dcml_env* e) {
+    if (!e) return MATAS_OK;
+    cudaFree(e->d_state); cudaFree(e->d_base);
+    delete e;
+    return MATAS_OK;
+}
+
+extern "C" int dcml_env_reset(dcml_env* e, float* obs, float* share_obs, float* ava, void* stream) {
+    int rc = env_check(e);
+    if (rc) return rc;
+    ARG_CHECK(obs && share_obs && ava, "null output");
+    EnvIO io = {};
+    io.obs = obs; io.sob = share_obs; io.ava = ava;
+    e->t = 0;
+    e->reset_done = true;
+    return env_launch(e, io, ENV_INIT, (cudaStream_t)stream);
+}
+
+extern "C" int dcml_env_step(dcml_env* e, const float* actions, float* obs, float* share_obs, float* ava, float* reward,
+                             uint8_t* done, float* delay, float* payment, void* stream) {
+    int rc = env_check(e);
+    if (rc) return rc;
+    ARG_CHECK(e->reset_done, "dcml_env_step before dcml_env_reset");
+    ARG_CHECK(actions && obs && share_obs && ava && reward && done && delay && payment, "null argument");
+    EnvIO io;
+    io.actions = actions; io.obs = obs; io.sob = share_obs; io.ava = ava; io.reward = reward; io.done = done;
+    io.delay = delay; io.payment = payment;
+    e->t += 1;
+    return env_launch(e, io, ENV_STEP, (cudaStream_t)stream);
+}
+
+extern "C" int dcml_env_set_context(dcml_env* e, const double* R, const double* C, const double* worker_pr,
+                                    const int32_t* n_disabled, float* obs, float* share_obs, float* ava, void* stream) {
+    int rc = env_check(e);
+    if (rc) return rc;
+    ARG_CHECK(e->reset_done, "dcml_env_set_context before dcml_env_reset");
+    ARG_CHECK(obs && share_obs && ava, "null output");
+    const long n = e->cfg.n_envs * e->cfg.n_workers;
+    set_context_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(e->st, R, C, worker_pr, n_disabled);
+    if (n_disabled) redraw_disabled_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(e->st, e->t);
+    CUDA_TRY(cudaGetLastError());
+    EnvIO io = {};
+    io.obs = obs; io.sob = share_obs; io.ava = ava;
+    return env_launch(e, io, ENV_OBSERVE, (cudaStream_t)stream);
+}

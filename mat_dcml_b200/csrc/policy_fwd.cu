@@ -1,0 +1,663 @@
+// MAT-AS policy forward kernels for sm_100a (fp32 SIMT GEMMs fed by a TMA bulk-copy weight ring).
+//
+//   encoder      : enc_embed_qkv -> enc_block<0> -> enc_block<1>            (token-parallel tiles)
+//   evaluate     : encoder + dec_embed_qkv -> {dec_attn1 -> dec_attn2} x 2   (teacher forcing)
+//   get_actions  : encoder + decode_kernel (persistent, 64 envs per CTA, sequential over agents,
+//                  K/V cache in global scratch, stride-block deterministic schedule in-kernel)
+//
+// Reference semantics: mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:24-230 and
+// mat_src/mat/algorithms/utils/transformer_act.py:8-189.
+#include "policy_fwd.h"
+#include "tile.cuh"
+
+using namespace tile;
+
+namespace {
+
+constexpr float MASK_LOGIT = -1e10f;
+constexpr float HALF_LOG_2PI = 0.91893853320467274178f;
+
+// dynamic shared memory carve-up common to all tile kernels
+struct Smem {
+    float* ring;       // depth * BLOB
+    float* sX;         // stream
+    float* sA;
+    float* sB;
+    float* sScore;     // TM*2*lpad
+    float* sInv;       // TM*2
+    float* sSmall;     // 1280 floats of small params / scratch
+    const float** kptr;
+    const float** vptr;
+    int* nt;
+    uint32_t* bits;    // TM*8 words: per-env action bitset (decode)
+    uint64_t* bars;    // ring barriers
+};
+
+__host__ __device__ inline size_t smem_bytes(int depth, int lpad) {
+    size_t f = (size_t)depth * lay::BLOB + 3 * TILE_F + (size_t)TM * 2 * lpad + TM * 2 + 1280;
+    f = (f + 3) & ~(size_t)3;
+    return f * 4 + TM * 8 * 2 + TM * 4 + TM * 8 * 4 + 8 * 8 + 16;
+}
+
+__device__ inline Smem carve(unsigned char* base, int depth, int lpad) {
+    Smem s;
+    float* f = reinterpret_cast<float*>(base);
+    s.ring = f; f += (size_t)depth * lay::BLOB;
+    s.sX = f; f += TILE_F;
+    s.sA = f; f += TILE_F;
+    s.sB = f; f += TILE_F;
+    s.sSmall = f; f += 1280;
+    s.sInv = f; f += TM * 2;
+    s.sScore = f; f += (size_t)TM * 2 * lpad;
+    uintptr_t p = (reinterpret_cast<uintptr_t>(f) + 15) & ~(uintptr_t)15;
+    s.bars = reinterpret_cast<uint64_t*>(p); p += 8 * 8;
+    s.kptr = reinterpret_cast<const float**>(p); p += TM * 8;
+    s.vptr = reinterpret_cast<const float**>(p); p += TM * 8;
+    s.nt = reinterpret_cast<int*>(p); p += TM * 4;
+    s.bits = reinterpret_cast<uint32_t*>(p);
+    return s;
+}
+
+__device__ __forceinline__ void store_tile(float* __restrict__ dst, long stride, const float* __restrict__ src, int n_valid) {
+    for (int idx = threadIdx.x; idx < TM * 16; idx += NT) {
+        const int r = idx >> 4, c = idx & 15;
+        if (r < n_valid)
+            *reinterpret_cast<float4*>(dst + (long)r * stride + c * 4) = *reinterpret_cast<const float4*>(src + r * XS + c * 4);
+    }
+}
+
+// blob sequences (float offsets into the packed weights)
+__constant__ int c_seq_enc_embed[3] = {lay::enc_blob(0, lay::EQ), lay::enc_blob(0, lay::EK), lay::enc_blob(0, lay::EV)};
+__constant__ int c_seq_enc_blk0[6] = {lay::enc_blob(0, lay::EP), lay::enc_blob(0, lay::EM0), lay::enc_blob(0, lay::EM2),
+                                      lay::enc_blob(1, lay::EQ), lay::enc_blob(1, lay::EK), lay::enc_blob(1, lay::EV)};
+__constant__ int c_seq_enc_blk1[6] = {lay::enc_blob(1, lay::EP), lay::enc_blob(1, lay::EM0), lay::enc_blob(1, lay::EM2),
+                                      lay::ENC_H0, lay::dec_q2(0), lay::dec_q2(1)};
+__constant__ int c_seq_dec_embed[3] = {lay::dec_blob(0, lay::DQ1), lay::dec_blob(0, lay::DK1), lay::dec_blob(0, lay::DV1)};
+__constant__ int c_seq_dec_attn1[2][3] = {
+    {lay::dec_blob(0, lay::DP1), lay::dec_blob(0, lay::DK2), lay::dec_blob(0, lay::DV2)},
+    {lay::dec_blob(1, lay::DP1), lay::dec_blob(1, lay::DK2), lay::dec_blob(1, lay::DV2)}};
+__constant__ int c_seq_dec_attn2[2][6] = {
+    {lay::dec_blob(0, lay::DP2), lay::dec_blob(0, lay::DM0), lay::dec_blob(0, lay::DM2), lay::dec_blob(1, lay::DQ1),
+     lay::dec_blob(1, lay::DK1), lay::dec_blob(1, lay::DV1)},
+    {lay::dec_blob(1, lay::DP2), lay::dec_blob(1, lay::DM0), lay::dec_blob(1, lay::DM2), lay::DEC_H0, 0, 0}};
+__constant__ int c_seq_q2[2] = {lay::dec_q2(0), lay::dec_q2(1)};
+__constant__ int c_seq_decode[lay::DEC_STEP_BLOBS];   // filled by host: DEC_STEP + i*BLOB
+
+// per-row metadata for token-parallel tiles: row r <-> token g = tile0 + r = env*L + pos
+__device__ __forceinline__ void token_rows(const Smem& s, long tile0, long n_tok, int L, const float* K, const float* V,
+                                           bool causal) {
+    const int r = threadIdx.x;
+    if (r < TM) {
+        const long g = tile0 + r;
+        if (g < n_tok) {
+            const long env = g / L;
+            const int pos = (int)(g - env * L);
+            s.kptr[r] = K + env * L * 64;
+            s.vptr[r] = V + env * L * 64;
+            s.nt[r] = causal ? pos + 1 : L;
+        } else {
+            s.kptr[r] = K; s.vptr[r] = V; s.nt[r] = 0;
+        }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// encoder stage 1: obs LayerNorm -> Linear(obs_dim->64) -> GELU -> LayerNorm -> X ; QKV of block 0
+// (ma_transformer.py:133-136,148-151 and :50-52)
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT, 1)
+enc_embed_qkv(PolicyBufs b, const float* __restrict__ obs, long n_tok, int obs_dim, int depth, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem s = carve(smem_raw, depth, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long tile0 = (long)blockIdx.x * TM;
+    const int n_valid = (int)min((long)TM, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_seq_enc_embed, 3, 3, depth);
+    for (int i = tid; i < lay::ENC_EMB_SIZE; i += NT) s.sSmall[i] = b.w[lay::ENC_EMB + i];
+    __syncthreads();
+    ring.prefetch();
+    float* sObs = s.sSmall + 768;   // [TM][8]
+    if (tid < TM) {
+        float v[8];
+        float mean = 0.f;
+        for (int k = 0; k < 8; ++k) {
+            v[k] = (k < obs_dim && tid < n_valid) ? obs[(tile0 + tid) * obs_dim + k] : 0.f;
+            mean += v[k];
+        }
+        mean /= (float)obs_dim;
+        float var = 0.f;
+        for (int k = 0; k < obs_dim; ++k) var += (v[k] - mean) * (v[k] - mean);
+        const float rs = rsqrtf(var / (float)obs_dim + 1e-5f);
+        for (int k = 0; k < 8; ++k)
+            sObs[tid * 8 + k] = k < obs_dim ? (v[k] - mean) * rs * s.sSmall[lay::ENC_EMB_LNW + k] + s.sSmall[lay::ENC_EMB_LNB + k] : 0.f;
+    }
+    __syncthreads();
+    {
+        const float* Wt = s.sSmall + lay::ENC_EMB_WT;
+        const float4 bb = *reinterpret_cast<const float4*>(s.sSmall + lay::ENC_EMB_B + cg * 4);
+        const float4 lw = *reinterpret_cast<const float4*>(s.sSmall + lay::ENC_EMB_LN2W + cg * 4);
+        const float4 lb = *reinterpret_cast<const float4*>(s.sSmall + lay::ENC_EMB_LN2B + cg * 4);
+        for (int i = 0; i < 4; ++i) {
+            const int r = rg * 4 + i;
+            float v0 = bb.x, v1 = bb.y, v2 = bb.z, v3 = bb.w;
+            for (int k = 0; k < obs_dim; ++k) {
+                const float o = sObs[r * 8 + k];
+                const float4 w = *reinterpret_cast<const float4*>(Wt + k * 64 + cg * 4);
+                v0 = fmaf(o, w.x, v0); v1 = fmaf(o, w.y, v1); v2 = fmaf(o, w.z, v2); v3 = fmaf(o, w.w, v3);
+            }
+            v0 = gelu_erf(v0); v1 = gelu_erf(v1); v2 = gelu_erf(v2); v3 = gelu_erf(v3);
+            const float mean = half_warp_sum(v0 + v1 + v2 + v3) * (1.0f / 64.0f);
+            const float d0 = v0 - mean, d1 = v1 - mean, d2 = v2 - mean, d3 = v3 - mean;
+            const float var = half_warp_sum(d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3) * (1.0f / 64.0f);
+            const float rs = rsqrtf(var + 1e-5f);
+            const float4 o4 = make_float4(d0 * rs * lw.x + lb.x, d1 * rs * lw.y + lb.y, d2 * rs * lw.z + lb.z, d3 * rs * lw.w + lb.w);
+            *reinterpret_cast<float4*>(s.sX + r * XS + cg * 4) = o4;
+            if (r < n_valid) *reinterpret_cast<float4*>(b.X + (tile0 + r) * 64 + cg * 4) = o4;
+        }
+    }
+    __syncthreads();
+    stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, b.K[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, b.V[0] + tile0 * 64, 64, n_valid, rg, cg);
+}
+
+// -------------------------------------------------------------------------------------------------
+// encoder block: attention (bidirectional) + proj + LN1 + MLP + LN2 (ma_transformer.py:89-92);
+// BLK 0 then emits QKV of block 1; BLK 1 emits obs_rep, the value head (:138-139) and the decoder's
+// cross-attention queries Q2 = attn2.query(obs_rep) for both decoder blocks (:114, :51).
+// -------------------------------------------------------------------------------------------------
+template <int BLK>
+__global__ void __launch_bounds__(NT, 1)
+enc_block(PolicyBufs b, float* __restrict__ values, long n_tok, int L, int depth, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem s = carve(smem_raw, depth, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long tile0 = (long)blockIdx.x * TM;
+    const int n_valid = (int)min((long)TM, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_seq_enc_blk0 : c_seq_enc_blk1, 6, 6, depth);
+    token_rows(s, tile0, n_tok, L, b.K[BLK], b.V[BLK], false);
+    load_tile(s.sX, b.X + tile0 * 64, 64, n_valid);
+    load_tile(s.sA, b.Q + tile0 * 64, 64, n_valid);
+    if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::ENC_H3 + i];
+    __syncthreads();
+    ring.prefetch();
+    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L);
+    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    __syncthreads(); ring.prefetch();
+    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg);
+    __syncthreads(); ring.prefetch();
+    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    __syncthreads(); ring.prefetch();
+    if (BLK == 0) {
+        store_tile(b.X + tile0 * 64, 64, s.sX, n_valid);
+        stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0>(ring, s.sX, b.K[1] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0>(ring, s.sX, b.V[1] + tile0 * 64, 64, n_valid, rg, cg);
+    } else {
+        store_tile(b.rep + tile0 * 64, 64, s.sX, n_valid);
+        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg);
+        stage<0>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+        __syncthreads();
+        if (tid < n_valid) values[tile0 + tid] = row_dot(s.sA, tid, s.sSmall) + s.sSmall[64];
+    }
+}
+
+// cross-attention queries from a caller-supplied obs_rep (the transformer_act entry points start
+// from obs_rep, transformer_act.py:30,103,131,176): rep_in -> b.rep copy, Q2[blk] = attn2.query(rep)
+__global__ void __launch_bounds__(NT, 1)
+q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int depth, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem s = carve(smem_raw, depth, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long tile0 = (long)blockIdx.x * TM;
+    const int n_valid = (int)min((long)TM, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_seq_q2, 2, 2, depth);
+    load_tile(s.sX, rep_in + tile0 * 64, 64, n_valid);
+    __syncthreads();
+    ring.prefetch();
+    if (rep_in != b.rep) store_tile(b.rep + tile0 * 64, 64, s.sX, n_valid);
+    stage<0>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+}
+
+// -------------------------------------------------------------------------------------------------
+// action-token embedding table: emb[c] = LN(GELU(Wa . vec(c))) (ma_transformer.py:224-225)
+//   code 0: zero row, 1: start token (1,0,0), 2/3: one-hot of action 0/1, 4/5: start + one-hot
+// written to dst[6][64] by the first 96 threads (one half-warp per code)
+// -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void build_emb_table(float* __restrict__ dst, const float* __restrict__ w) {
+    const int tid = threadIdx.x;
+    if (tid < 96) {
+        const int c = tid >> 4, cg = tid & 15;
+        const float f0 = (c == 1 || c >= 4) ? 1.f : 0.f, f1 = (c == 2 || c == 4) ? 1.f : 0.f, f2 = (c == 3 || c == 5) ? 1.f : 0.f;
+        const float* Wt = w + lay::DEC_EMB + lay::DEC_EMB_WT;
+        float v[4];
+        for (int i = 0; i < 4; ++i) {
+            const int col = cg * 4 + i;
+            v[i] = gelu_erf(f0 * Wt[col] + f1 * Wt[64 + col] + f2 * Wt[128 + col]);
+        }
+        const float mean = half_warp_sum(v[0] + v[1] + v[2] + v[3]) * (1.0f / 64.0f);
+        float var = 0.f;
+        for (int i = 0; i < 4; ++i) { v[i] -= mean; var += v[i] * v[i]; }
+        var = half_warp_sum(var) * (1.0f / 64.0f);
+        const float rs = rsqrtf(var + 1e-5f);
+        for (int i = 0; i < 4; ++i) {
+            const int col = cg * 4 + i;
+            dst[c * 64 + col] = v[i] * rs * w[lay::DEC_EMB + lay::DEC_EMB_LNW + col] + w[lay::DEC_EMB + lay::DEC_EMB_LNB + col];
+        }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// teacher-forced decoder, stage 1: shifted-action embedding -> X ; QKV1 of block 0
+// (transformer_act.py:103-111,176-181)
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT, 1)
+dec_embed_qkv(PolicyBufs b, const float* __restrict__ actions, long n_tok, int L, int depth, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem s = carve(smem_raw, depth, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long tile0 = (long)blockIdx.x * TM;
+    const int n_valid = (int)min((long)TM, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_seq_dec_embed, 3, 3, depth);
+    build_emb_table(s.sSmall, b.w);
+    __syncthreads();
+    ring.prefetch();
+    for (int idx = tid; idx < TM * 16; idx += NT) {
+        const int r = idx >> 4, c = idx & 15;
+        const long g = tile0 + r;
+        int code = 0;
+        if (g < n_tok) {
+            const int pos = (int)(g % L);
+            code = pos == 0 ? 1 : (actions[g - 1] != 0.f ? 3 : 2);
+        }
+        const float4 v = *reinterpret_cast<const float4*>(s.sSmall + code * 64 + c * 4);
+        *reinterpret_cast<float4*>(s.sX + r * XS + c * 4) = v;
+        if (r < n_valid) *reinterpret_cast<float4*>(b.X + g * 64 + c * 4) = v;
+    }
+    __syncthreads();
+    stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, b.K1[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, b.V1[0] + tile0 * 64, 64, n_valid, rg, cg);
+}
+
+// decoder block, first half: causal self-attention + proj + LN1, then K2/V2 of the result
+// (ma_transformer.py:113 and the key/value side of :114)
+__global__ void __launch_bounds__(NT, 1)
+dec_attn1(PolicyBufs b, int blk, long n_tok, int L, int depth, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem s = carve(smem_raw, depth, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long tile0 = (long)blockIdx.x * TM;
+    const int n_valid = (int)min((long)TM, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_seq_dec_attn1[blk], 3, 3, depth);
+    token_rows(s, tile0, n_tok, L, b.K1[blk], b.V1[blk], true);
+    load_tile(s.sX, b.X + tile0 * 64, 64, n_valid);
+    load_tile(s.sA, b.Q + tile0 * 64, 64, n_valid);
+    __syncthreads();
+    ring.prefetch();
+    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L);
+    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    __syncthreads();
+    stage<0>(ring, s.sX, b.K2[blk] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, b.V2[blk] + tile0 * 64, 64, n_valid, rg, cg);
+}
+
+// per-token distribution head shared by evaluate and decode (transformer_act.py:8-28,112-128)
+struct HeadParams { float w0[64]; float w1[64]; float b0, b1, ls0, ls1; };
+
+__device__ __forceinline__ void masked_logz(float l0, float l1, const float* ava2, float& z0, float& z1) {
+    if (ava2) {
+        if (ava2[0] == 0.f) l0 = MASK_LOGIT;
+        if (ava2[1] == 0.f) l1 = MASK_LOGIT;
+    }
+    const float m = fmaxf(l0, l1);
+    const float lse = m + logf(expf(l0 - m) + expf(l1 - m));
+    z0 = l0 - lse;
+    z1 = l1 - lse;
+}
+
+// decoder block, second half: cross-attention (query = obs_rep) + proj + LN2(rep + .) + MLP + LN3;
+// block 0 then emits QKV1 of block 1, block 1 the logits head and the per-token log-prob / entropy.
+__global__ void __launch_bounds__(NT, 1)
+dec_attn2(PolicyBufs b, int blk, const float* __restrict__ actions, const float* __restrict__ ava,
+          float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, int depth, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem s = carve(smem_raw, depth, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long tile0 = (long)blockIdx.x * TM;
+    const int n_valid = (int)min((long)TM, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_seq_dec_attn2[blk], blk == 0 ? 6 : 4, blk == 0 ? 6 : 4, depth);
+    token_rows(s, tile0, n_tok, L, b.K2[blk], b.V2[blk], true);
+    load_tile(s.sA, b.Q2[blk] + tile0 * 64, 64, n_valid);
+    if (blk == 1) for (int i = tid; i < lay::DEC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::DEC_H3 + i];
+    __syncthreads();
+    ring.prefetch();
+    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L);
+    stage<EP_RES | EP_LN>(ring, s.sB, b.rep + tile0 * 64, 64, n_valid, s.sX, XS, TM, rg, cg);
+    __syncthreads(); ring.prefetch();
+    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg);
+    __syncthreads(); ring.prefetch();
+    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    __syncthreads(); ring.prefetch();
+    if (blk == 0) {
+        store_tile(b.X + tile0 * 64, 64, s.sX, n_valid);
+        stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0>(ring, s.sX, b.K1[1] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0>(ring, s.sX, b.V1[1] + tile0 * 64, 64, n_valid, rg, cg);
+    } else {
+        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg);
+        __syncthreads();
+        if (tid < n_valid) {
+            const long g = tile0 + tid;
+            const int pos = (int)(g % L);
+            const float l0 = row_dot(s.sA, tid, s.sSmall) + s.sSmall[lay::DEC_H3_B];
+            const float l1 = row_dot(s.sA, tid, s.sSmall + 64) + s.sSmall[lay::DEC_H3_B + 1];
+            const float a = actions[g];
+            if (pos < n_disc) {
+                float z0, z1;
+                masked_logz(l0, l1, ava ? ava + g * 2 : nullptr, z0, z1);
+                logp[g] = a != 0.f ? z1 : z0;
+                const float c0 = fmaxf(z0, -3.4028234663852886e38f), c1 = fmaxf(z1, -3.4028234663852886e38f);
+                entropy[g] = -(expf(c0) * c0 + expf(c1) * c1);
+            } else {
+                const float sd = 0.5f / (1.0f + expf(-s.sSmall[lay::DEC_H3_LOGSTD + 1]));
+                const float d = a - l1;
+                logp[g] = -(d * d) / (2.0f * sd * sd) - logf(sd) - HALF_LOG_2PI;
+                entropy[g] = 0.5f + HALF_LOG_2PI + logf(sd);
+            }
+        }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// autoregressive decode schedule (transformer_act.py:37-98 and :138-172), shared by host and device
+// -------------------------------------------------------------------------------------------------
+struct DecStep { int j; int kind; int emit; };   // kind 0: true predecessor, 1: speculative zero row, 2: own action
+
+struct DecSched {
+    int L, nd, stride, mode, det;
+    int s, e, j, phase, go, started;
+    __host__ __device__ void init(int L_, int mode_, int det_, int stride_) {
+        L = L_; mode = mode_; det = det_; stride = stride_ < 1 ? 1 : stride_;
+        nd = mode == MATAS_MODE_SEMI ? L - 1 : L;
+        s = 0; e = 1; j = 0; phase = 0; go = 1; started = 0;
+    }
+    __host__ __device__ bool next(DecStep& st) {
+        if (!det) {
+            if (j >= L) return false;
+            st.j = j++; st.kind = 0; st.emit = 1;
+            return true;
+        }
+        for (;;) {
+            if (phase == 0) {           // entering a block
+                if (!(e <= L && go)) return false;
+                if (e == L) go = 0;
+                phase = 1; j = s;
+            }
+            if (phase == 1) {           // speculative pass over [s, e)
+                if (j < e) {
+                    st.j = j; st.emit = 1;
+                    st.kind = mode == MATAS_MODE_SEMI ? (j == s ? 0 : 1) : 1;
+                    ++j;
+                    return true;
+                }
+                const bool more = mode == MATAS_MODE_SEMI ? (go != 0) : (e < L);
+                if (!more) return false;
+                phase = 2; j = mode == MATAS_MODE_SEMI ? s + 1 : s;
+            }
+            if (phase == 2) {           // commit pass: recompute with the decided actions
+                if (j < e) {
+                    st.j = j; st.emit = 0; st.kind = mode == MATAS_MODE_SEMI ? 0 : 2;
+                    ++j;
+                    return true;
+                }
+                if (mode == MATAS_MODE_SEMI) {
+                    if (e < nd) { s = e; e = min(e + stride, nd); }
+                    else { s = e; e = min(e + 1, L); }
+                } else {
+                    s = e; e = min(e + 4, L);
+                }
+                phase = 0;
+            }
+        }
+    }
+};
+
+// -------------------------------------------------------------------------------------------------
+// persistent KV-cached decode: one CTA owns 64 envs at a time and walks the schedule.
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT, 1)
+decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem s = carve(smem_raw, depth, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const int L = a.L;
+    const long n_tiles = (a.B + TM - 1) / TM;
+    long my_tiles = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++my_tiles;
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_seq_decode, lay::DEC_STEP_BLOBS, (int)(my_tiles * a.n_steps * lay::DEC_STEP_BLOBS), depth);
+    float* sEmb = s.sSmall;            // [6][64]
+    float* sHead = s.sSmall + 384;     // DEC_H3 block
+    int* sCode = reinterpret_cast<int*>(s.sSmall + 640);   // [TM]
+    build_emb_table(sEmb, b.w);
+    for (int i = tid; i < lay::DEC_H3_SIZE; i += NT) sHead[i] = b.w[lay::DEC_H3 + i];
+    __syncthreads();
+    ring.prefetch();
+
+    const long slot0 = (long)blockIdx.x * TM;
+    const long slot_stride = 8L * L * 64;
+    float* kv0 = b.kv + slot0 * slot_stride;
+    const int nd = a.mode == MATAS_MODE_SEMI ? L - 1 : L;
+    const float sd1 = 0.5f / (1.0f + expf(-sHead[lay::DEC_H3_LOGSTD + 1]));
+
+    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long env0 = tile * TM;
+        const int n_valid = (int)min((long)TM, a.B - env0);
+        for (int i = tid; i < TM * 8; i += NT) s.bits[i] = 0u;
+        DecSched sched;
+        sched.init(L, a.mode, a.deterministic, a.stride);
+        DecStep st;
+        __syncthreads();
+        while (sched.next(st)) {
+            const int j = st.j;
+            // ---- inputs of this position: token embedding, obs_rep row -----------------------------
+            if (tid < TM) {
+                int code;
+                const uint32_t* bt = s.bits + tid * 8;
+                if (st.kind == 1) code = j == 0 ? 1 : 0;
+                else if (st.kind == 0) code = j == 0 ? 1 : 2 + (int)((bt[(j - 1) >> 5] >> ((j - 1) & 31)) & 1u);
+                else code = (j == 0 ? 4 : 2) + (int)((bt[j >> 5] >> (j & 31)) & 1u);
+                sCode[tid] = code;
+            }
+            __syncthreads();
+            for (int idx = tid; idx < TM * 16; idx += NT) {
+                const int r = idx >> 4, c = idx & 15;
+                *reinterpret_cast<float4*>(s.sX + r * XS + c * 4) = *reinterpret_cast<const float4*>(sEmb + sCode[r] * 64 + c * 4);
+            }
+            __syncthreads();
+            for (int blk = 0; blk < 2; ++blk) {
+                float* k1 = kv0 + ((blk * 2 + 0) * 2 + 0) * (long)L * 64;
+                float* v1 = kv0 + ((blk * 2 + 0) * 2 + 1) * (long)L * 64;
+                float* k2 = kv0 + ((blk * 2 + 1) * 2 + 0) * (long)L * 64;
+                float* v2 = kv0 + ((blk * 2 + 1) * 2 + 1) * (long)L * 64;
+                // ---- self-attention over the cache --------------------------------------------------
+                stage<0>(ring, s.sX, s.sA, XS, TM, rg, cg);
+                stage<0>(ring, s.sX, k1 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                stage<0>(ring, s.sX, v1 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                if (tid < TM) {
+                    s.kptr[tid] = k1 + tid * slot_stride;
+                    s.vptr[tid] = v1 + tid * slot_stride;
+                    s.nt[tid] = tid < n_valid ? j + 1 : 0;
+                }
+                __syncthreads(); ring.prefetch();
+                attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
+                stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+                __syncthreads(); ring.prefetch();
+                // ---- cross-attention: keys/values from the decoder stream, query from obs_rep ------
+                stage<0>(ring, s.sX, k2 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                stage<0>(ring, s.sX, v2 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                load_tile(s.sA, b.Q2[blk] + (env0 * L + j) * 64, (long)L * 64, n_valid);
+                if (tid < TM) {
+                    s.kptr[tid] = k2 + tid * slot_stride;
+                    s.vptr[tid] = v2 + tid * slot_stride;
+                }
+                __syncthreads(); ring.prefetch();
+                attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
+                stage<EP_RES | EP_LN>(ring, s.sB, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid, s.sX, XS, TM, rg, cg);
+                __syncthreads(); ring.prefetch();
+                stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg);
+                __syncthreads(); ring.prefetch();
+                stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+                __syncthreads(); ring.prefetch();
+            }
+            // ---- logits head + action pick ---------------------------------------------------------
+            if (st.emit) {
+                stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg);
+            } else {
+                ring.acquire(); ring.release();
+            }
+            __syncthreads(); ring.prefetch();
+            if (st.emit && tid < n_valid) {
+                const long env = env0 + tid;
+                const long g = env * L + j;
+                const float l0 = row_dot(s.sA, tid, sHead) + sHead[lay::DEC_H3_B];
+                const float l1 = row_dot(s.sA, tid, sHead + 64) + sHead[lay::DEC_H3_B + 1];
+                if (j < nd) {
+                    float z0, z1;
+                    masked_logz(l0, l1, a.ava ? a.ava + g * 2 : nullptr, z0, z1);
+                    int act;
+                    if (a.deterministic) {
+                        act = z1 > z0;
+                    } else {
+                        const float zm = fmaxf(z0, z1);
+                        const float e0 = expf(z0 - zm), e1 = expf(z1 - zm);
+                        const float p0 = e0 / (e0 + e1);
+                        const float u = a.u ? a.u[g]
+                                            : u01f(philox4x32((uint32_t)(a.env_offset + env), a.step, rng_tag(S_POLICY, j), 0, a.seed).x);
+                        act = u >= p0;
+                    }
+                    a.actions[g] = (float)act;
+                    a.logp[g] = act ? z1 : z0;
+                    if (act) s.bits[tid * 8 + (j >> 5)] |= 1u << (j & 31);
+                    else s.bits[tid * 8 + (j >> 5)] &= ~(1u << (j & 31));
+                } else {
+                    float z = 0.f;
+                    if (!a.deterministic) {
+                        if (a.z) z = a.z[env * 2 + 1];
+                        else {
+                            const uint4 x = philox4x32((uint32_t)(a.env_offset + env), a.step, rng_tag(S_POLICY, j), 0, a.seed);
+                            const float r1 = sqrtf(-2.0f * logf(((float)(x.z >> 8) + 1.0f) * (1.0f / 16777216.0f)));
+                            z = r1 * cospif(2.0f * ((float)(x.w >> 8) * (1.0f / 16777216.0f)));
+                        }
+                    }
+                    const float act = l1 + sd1 * z;
+                    const float d = act - l1;
+                    a.actions[g] = act;
+                    a.logp[g] = -(d * d) / (2.0f * sd1 * sd1) - logf(sd1) - HALF_LOG_2PI;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+template <typename K>
+int set_smem(K kernel, size_t bytes) {
+    CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return MATAS_OK;
+}
+
+}  // namespace
+
+// -------------------------------------------------------------------------------------------------
+// host launchers
+// -------------------------------------------------------------------------------------------------
+int policy_launch_geometry(int L, int* depth, int* lpad, size_t* bytes) {
+    *lpad = L | 1;
+    for (int d = 4; d >= 3; --d) {
+        const size_t sb = smem_bytes(d, *lpad);
+        if (sb <= 232448) { *depth = d; *bytes = sb; return MATAS_OK; }
+    }
+    matas_set_error("n_agent %d needs more shared memory than a B200 SM has (max supported 201)", L);
+    return MATAS_ERR_LIMIT;
+}
+
+int policy_decode_steps(int L, int mode, int deterministic, int stride) {
+    DecSched s; s.init(L, mode, deterministic, stride);
+    DecStep st; int n = 0;
+    while (s.next(st)) ++n;
+    return n;
+}
+
+int policy_init_constants() {
+    int seq[lay::DEC_STEP_BLOBS];
+    for (int i = 0; i < lay::DEC_STEP_BLOBS; ++i) seq[i] = lay::DEC_STEP + i * lay::BLOB;
+    CUDA_TRY(cudaMemcpyToSymbol(c_seq_decode, seq, sizeof(seq)));
+    return MATAS_OK;
+}
+
+int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st) {
+    int depth, lpad; size_t bytes;
+    int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
+    if (rc) return rc;
+    const long n_tok = B * L;
+    const unsigned grid = (unsigned)((n_tok + TM - 1) / TM);
+    if ((rc = set_smem(enc_embed_qkv, bytes))) return rc;
+    if ((rc = set_smem(enc_block<0>, bytes))) return rc;
+    if ((rc = set_smem(enc_block<1>, bytes))) return rc;
+    enc_embed_qkv<<<grid, NT, bytes, st>>>(b, obs, n_tok, obs_dim, depth, lpad);
+    enc_block<0><<<grid, NT, bytes, st>>>(b, values, n_tok, L, depth, lpad);
+    enc_block<1><<<grid, NT, bytes, st>>>(b, values, n_tok, L, depth, lpad);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
+int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st) {
+    int depth, lpad; size_t bytes;
+    int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
+    if (rc) return rc;
+    const long n_tok = B * L;
+    if ((rc = set_smem(q2_from_rep, bytes))) return rc;
+    q2_from_rep<<<(unsigned)((n_tok + TM - 1) / TM), NT, bytes, st>>>(b, rep_in, n_tok, depth, lpad);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
+int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
+                          long B, int L, int mode, cudaStream_t st) {
+    int depth, lpad; size_t bytes;
+    int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
+    if (rc) return rc;
+    const long n_tok = B * L;
+    const unsigned grid = (unsigned)((n_tok + TM - 1) / TM);
+    const int n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
+    if ((rc = set_smem(dec_embed_qkv, bytes))) return rc;
+    if ((rc = set_smem(dec_attn1, bytes))) return rc;
+    if ((rc = set_smem(dec_attn2, bytes))) return rc;
+    dec_embed_qkv<<<grid, NT, bytes, st>>>(b, actions, n_tok, L, depth, lpad);
+    for (int blk = 0; blk < 2; ++blk) {
+        dec_attn1<<<grid, NT, bytes, st>>>(b, blk, n_tok, L, depth, lpad);
+        dec_attn2<<<grid, NT, bytes, st>>>(b, blk, actions, ava, logp, entropy, n_tok, L, n_disc, depth, lpad);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
+int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st) {
+    int depth, lpad; size_t bytes;
+    int rc = policy_launch_geometry(a.L, &depth, &lpad, &bytes);
+    if (rc) return rc;
+    if ((rc = set_smem(decode_kernel, bytes))) return rc;
+    decode_kernel<<<grid, NT, bytes, st>>>(b, a, depth, lpad);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}

@@ -1,0 +1,232 @@
+// 64-row tile primitives shared by every policy kernel: TMA-fed weight ring, fp32 SIMT GEMM
+// [64 x 64] * [64 x 64] with fused bias/GELU/residual/LayerNorm epilogue, and row-wise attention
+// over K/V that live in global memory (L2-resident scratch).
+#pragma once
+#include "common.cuh"
+#include "layout.h"
+
+namespace tile {
+constexpr int TM = 64;        // rows (tokens or envs) per tile
+constexpr int XS = 68;        // padded row stride of activation tiles in shared memory (floats)
+constexpr int NT = 256;       // threads per CTA: 16 row groups x 16 column groups, 4x4 outputs each
+constexpr int TILE_F = TM * XS;
+
+enum { EP_GELU = 1, EP_RES = 2, EP_LN = 4 };
+
+// ---------------------------------------------------------------------------------------------
+// weight ring: thread 0 streams the kernel's blob sequence global -> shared with cp.async.bulk,
+// completion tracked by one mbarrier per slot; consumers are all NT threads.
+// Contract: at most `depth` acquire()s between two prefetch() calls, and a __syncthreads() between the
+// last use of a slot and the prefetch() that refills it.
+// ---------------------------------------------------------------------------------------------
+struct Ring {
+    float* slots; uint64_t* bars; const float* gw; const int* seq;   // seq: float offsets of the blobs, cyclic
+    int seq_len, total, head, tail, depth;   // total: blobs this CTA consumes in its lifetime; tail: thread 0 only
+
+    __device__ void init(float* slots_, uint64_t* bars_, const float* gw_, const int* seq_, int seq_len_, int total_,
+                         int depth_) {
+        slots = slots_; bars = bars_; gw = gw_; seq = seq_; seq_len = seq_len_; total = total_; depth = depth_;
+        head = 0; tail = 0;
+        if (threadIdx.x == 0) {
+            for (int i = 0; i < depth; ++i) mbar_init(&bars[i], 1);
+            mbar_fence_init();
+        }
+    }
+    __device__ void prefetch() {
+        if (threadIdx.x == 0) {
+            while (tail < head + depth && tail < total) {
+                const int s = tail % depth;
+                mbar_expect_tx(&bars[s], lay::BLOB_BYTES);
+                bulk_g2s(slots + (size_t)s * lay::BLOB, gw + seq[tail % seq_len], lay::BLOB_BYTES, &bars[s]);
+                ++tail;
+            }
+        }
+    }
+    __device__ const float* acquire() {
+        const int s = head % depth;
+        mbar_wait(&bars[s], (head / depth) & 1);
+        return slots + (size_t)s * lay::BLOB;
+    }
+    __device__ void release() { ++head; }
+};
+
+// ---------------------------------------------------------------------------------------------
+// GEMM: acc[i][j] = sum_k X[4*rg+i][k] * Wt[k][4*cg+j]
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void gemm(const float* __restrict__ X, const float* __restrict__ Wt, float (&acc)[4][4],
+                                     int rg, int cg) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    const float* xr = X + rg * 4 * XS;
+    const float* wc = Wt + cg * 4;
+#pragma unroll 4
+    for (int k = 0; k < 64; k += 4) {
+        float4 a[4], w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(xr + i * XS + k);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) w[kk] = *reinterpret_cast<const float4*>(wc + (k + kk) * 64);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w};
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                acc[i][0] = fmaf(av[kk], w[kk].x, acc[i][0]);
+                acc[i][1] = fmaf(av[kk], w[kk].y, acc[i][1]);
+                acc[i][2] = fmaf(av[kk], w[kk].z, acc[i][2]);
+                acc[i][3] = fmaf(av[kk], w[kk].w, acc[i][3]);
+            }
+        }
+    }
+}
+
+// Epilogue order: + bias -> GELU -> + residual -> LayerNorm (eps 1e-5, biased variance).
+// The residual tile (shared, stride XS, or global) is read into registers BEFORE the GEMM so that
+// out may alias it and global latency hides behind the FMAs; rows >= res_valid read as 0.
+// Output row r goes to out + r*out_stride (shared or global); rows >= n_valid are not stored.
+template <int FLAGS>
+__device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, const float* res, long res_stride,
+                                      int res_valid, float* out, long out_stride, int n_valid, int rg, int cg) {
+    float4 rr[4];
+    if (FLAGS & EP_RES) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = rg * 4 + i;
+            rr[i] = r < res_valid ? *reinterpret_cast<const float4*>(res + (long)r * res_stride + cg * 4)
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    const float* blob = ring.acquire();
+    float acc[4][4];
+    gemm(X, blob, acc, rg, cg);
+    const float4 b = *reinterpret_cast<const float4*>(blob + lay::B_BIAS + cg * 4);
+    float4 lw, lb;
+    if (FLAGS & EP_LN) {
+        lw = *reinterpret_cast<const float4*>(blob + lay::B_LNW + cg * 4);
+        lb = *reinterpret_cast<const float4*>(blob + lay::B_LNB + cg * 4);
+    }
+    ring.release();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = rg * 4 + i;
+        float v0 = acc[i][0] + b.x, v1 = acc[i][1] + b.y, v2 = acc[i][2] + b.z, v3 = acc[i][3] + b.w;
+        if (FLAGS & EP_GELU) { v0 = gelu_erf(v0); v1 = gelu_erf(v1); v2 = gelu_erf(v2); v3 = gelu_erf(v3); }
+        if (FLAGS & EP_RES) { v0 += rr[i].x; v1 += rr[i].y; v2 += rr[i].z; v3 += rr[i].w; }
+        if (FLAGS & EP_LN) {
+            const float mean = half_warp_sum(v0 + v1 + v2 + v3) * (1.0f / 64.0f);
+            const float d0 = v0 - mean, d1 = v1 - mean, d2 = v2 - mean, d3 = v3 - mean;
+            const float var = half_warp_sum(d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3) * (1.0f / 64.0f);
+            const float rs = rsqrtf(var + 1e-5f);
+            v0 = d0 * rs * lw.x + lb.x; v1 = d1 * rs * lw.y + lb.y; v2 = d2 * rs * lw.z + lb.z; v3 = d3 * rs * lw.w + lb.w;
+        }
+        if (r < n_valid) *reinterpret_cast<float4*>(out + (long)r * out_stride + cg * 4) = make_float4(v0, v1, v2, v3);
+    }
+}
+// plain stage (no residual)
+template <int FLAGS>
+__device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, float* out, long out_stride, int n_valid,
+                                      int rg, int cg) {
+    stage<FLAGS>(ring, X, nullptr, 0, 0, out, out_stride, n_valid, rg, cg);
+}
+
+// ---------------------------------------------------------------------------------------------
+// attention for a tile of query rows.  Row r attends to nt[r] keys K[r][t][:], V[r][t][:]
+// (t-major, 64 floats per key: head h uses columns 32h..32h+31) found at kptr[r] / vptr[r].
+// sScore: TM*2*lpad floats (lpad odd), sInv: TM*2 floats.  Three phases with CTA barriers.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void attention(const float* __restrict__ sQ, float* __restrict__ sOut,
+                                          float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
+                                          const float* const* __restrict__ kptr, const float* const* __restrict__ vptr,
+                                          const int* __restrict__ nt, int nt_max) {
+    const int tid = threadIdx.x;
+    const float scale = 0.17677669529663687f;   // 1/sqrt(32)
+    // phase A: scores
+    for (int idx = tid; idx < TM * 2 * nt_max; idx += NT) {
+        const int t = idx % nt_max, rh = idx / nt_max, r = rh >> 1, h = rh & 1;
+        if (t < nt[r]) {
+            const float4* kp = reinterpret_cast<const float4*>(kptr[r] + (long)t * 64 + h * 32);
+            const float4* qp = reinterpret_cast<const float4*>(sQ + r * XS + h * 32);
+            float4 kk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) kk[i] = __ldcg(kp + i);
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 q = qp[i];
+                s = fmaf(q.x, kk[i].x, s); s = fmaf(q.y, kk[i].y, s); s = fmaf(q.z, kk[i].z, s); s = fmaf(q.w, kk[i].w, s);
+            }
+            sScore[rh * lpad + t] = s * scale;
+        }
+    }
+    __syncthreads();
+    // phase B: softmax numerators + 1/sum
+    for (int rh = tid; rh < TM * 2; rh += NT) {
+        const int n = nt[rh >> 1];
+        float* sc = sScore + rh * lpad;
+        float m = -INFINITY;
+        for (int t = 0; t < n; ++t) m = fmaxf(m, sc[t]);
+        float sum = 0.f;
+        for (int t = 0; t < n; ++t) {
+            const float e = expf(sc[t] - m);
+            sc[t] = e;
+            sum += e;
+        }
+        sInv[rh] = n > 0 ? 1.0f / sum : 0.f;
+    }
+    __syncthreads();
+    // phase C: P.V  (8 threads per (row, head), 4 dims each)
+    for (int idx = tid; idx < TM * 2 * 8; idx += NT) {
+        const int dq = idx & 7, rh = idx >> 3, r = rh >> 1, h = rh & 1;
+        const int n = nt[r];
+        const float* sc = sScore + rh * lpad;
+        const float* vp = vptr[r] + h * 32 + dq * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int t = 0;
+        for (; t + 4 <= n; t += 4) {
+            float4 v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(vp + (long)(t + i) * 64));
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float p = sc[t + i];
+                acc.x = fmaf(p, v[i].x, acc.x); acc.y = fmaf(p, v[i].y, acc.y);
+                acc.z = fmaf(p, v[i].z, acc.z); acc.w = fmaf(p, v[i].w, acc.w);
+            }
+        }
+        for (; t < n; ++t) {
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(vp + (long)t * 64));
+            const float p = sc[t];
+            acc.x = fmaf(p, v.x, acc.x); acc.y = fmaf(p, v.y, acc.y); acc.z = fmaf(p, v.z, acc.z); acc.w = fmaf(p, v.w, acc.w);
+        }
+        const float inv = sInv[rh];
+        *reinterpret_cast<float4*>(sOut + r * XS + h * 32 + dq * 4) =
+            make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+    }
+    __syncthreads();
+}
+
+// load a [TM][64] tile from global rows (row r at src + r*stride) into a shared tile; invalid rows -> 0
+__device__ __forceinline__ void load_tile(float* __restrict__ dst, const float* __restrict__ src, long stride, int n_valid) {
+    for (int idx = threadIdx.x; idx < TM * 16; idx += NT) {
+        const int r = idx >> 4, c = idx & 15;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < n_valid) v = __ldcg(reinterpret_cast<const float4*>(src + (long)r * stride + c * 4));
+        *reinterpret_cast<float4*>(dst + r * XS + c * 4) = v;
+    }
+}
+
+// out[r] = dot(X[r][0:64], w) + b for r < n_valid (one thread per row)
+__device__ __forceinline__ float row_dot(const float* __restrict__ X, int r, const float* __restrict__ w) {
+    const float4* xp = reinterpret_cast<const float4*>(X + r * XS);
+    const float4* wp = reinterpret_cast<const float4*>(w);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float4 x = xp[i], ww = wp[i];
+        s = fmaf(x.x, ww.x, s); s = fmaf(x.y, ww.y, s); s = fmaf(x.z, ww.z, s); s = fmaf(x.w, ww.w, s);
+    }
+    return s;
+}
+}  // namespace tile

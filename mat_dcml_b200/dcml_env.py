@@ -1,0 +1,158 @@
+"""Vectorised DCML environment behind the reference's vec-env contract
+(mat_src/mat/envs/env_wrappers.py:713-744 ShareDummyVecEnv over
+DCML_BID_FIRST_MA_ENV_SingleProcess.py:15-355): ``reset() -> (obs, share_obs, ava)``,
+``step(actions (N,L,1)) -> (obs, share_obs, rews (N,L,1), dones (N,L), infos, ava)``.
+
+All N envs live on the GPU and advance in one kernel launch (libmatas_b200.so, csrc/env.cu).
+``step`` / ``reset`` return host numpy arrays like the reference; ``step_device`` /
+``reset_device`` return device tensors and are what a device-resident rollout loop uses
+(``share_obs`` is then a stride-0 expand of the one (W+2) row per env).
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _cabi
+
+PERIOD = 20
+
+
+class Action_Space:
+    """DCML_ENVs/DCML_utils/DCML_ActionSpace.py:1-9 (descriptor the policy dispatches on)."""
+
+    def __init__(self, dim, semi_index=0, extra=False, multi_discrete=False, high=None, low=None, mixed=True,
+                 continuous=True):
+        self.continuous, self.mixed, self.n, self.extra = continuous, mixed, dim, extra
+        self.semi_index, self.multi_discrete, self.high, self.low = semi_index, multi_discrete, high, low
+
+
+def synthetic_workloads(W, seed=1):
+    """``data/workloads.txt``-shaped base table: W rows x 20 slots, multiples of 0.05 in [0,1],
+    row means ~0.5, no all-ones row."""
+    rng = np.random.RandomState(seed)
+    centre = rng.uniform(0.45, 0.6, size=(W, 1))
+    raw = np.clip(centre + 0.28 * rng.standard_normal((W, PERIOD)), 0.0, 1.0)
+    idx = np.rint(raw / 0.05).astype(np.int64)
+    idx[:, 0] = np.minimum(idx[:, 0], 16)
+    return (np.arange(21) * 0.05)[idx]
+
+
+def load_workloads(path, W):
+    """Read the reference's ``workloads.txt`` (W consecutive ``np.save`` records, …SingleProcess.py:33-37)."""
+    rows = []
+    with open(path, "rb") as f:
+        for _ in range(W):
+            rows.append(np.load(f, allow_pickle=True))
+    return np.asarray(rows, np.float64)
+
+
+class _Infos:
+    """Lazy ``[[{"delay":…, "payment":…}], …]`` (dcml_runner.py:63-64 reads info[0]["delay"])."""
+
+    def __init__(self, delay, payment):
+        self._d, self._p = delay, payment
+
+    def __len__(self):
+        return len(self._d)
+
+    def __getitem__(self, i):
+        return [{"delay": float(self._d[i]), "payment": float(self._p[i])}]
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
+class DcmlVecEnv:
+    def __init__(self, n_envs, n_workers=100, base_workload=None, seed=1, device="cuda", double_reset=True,
+                 env_offset=0):
+        self.num_envs = self.N = int(n_envs)
+        self.W, self.L = int(n_workers), int(n_workers) + 1
+        self.n_agents = self.L
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _cabi.MatasError("DcmlVecEnv needs a CUDA device (there is no CPU fallback)")
+        base = synthetic_workloads(self.W) if base_workload is None else np.asarray(base_workload, np.float64)
+        if base.shape != (self.W, PERIOD):
+            raise ValueError("base_workload must be (%d, %d)" % (self.W, PERIOD))
+        self.base_workload = np.ascontiguousarray(base)
+        self.observation_space = [[7]] * self.L                       # …SingleProcess.py:41
+        self.share_observation_space = [[self.W + 2]]                 # :45
+        self.action_space = [Action_Space(2, semi_index=-1, extra=True)]   # :48-49
+        cfg = _cabi.EnvCfg(self.N, self.W, int(seed) & 0xFFFFFFFFFFFFFFFF, int(env_offset), int(bool(double_reset)))
+        h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().dcml_env_create(ctypes.byref(cfg), self.base_workload.ctypes.data_as(ctypes.c_void_p),
+                                                    ctypes.byref(h)))
+        self._h = h
+        f32 = dict(dtype=torch.float32, device=self.device)
+        self.obs = torch.empty(self.N, self.L, 7, **f32)
+        self.sob = torch.empty(self.N, self.W + 2, **f32)
+        self.ava = torch.empty(self.N, self.L, 2, **f32)
+        self.reward = torch.empty(self.N, **f32)
+        self.done = torch.empty(self.N, dtype=torch.uint8, device=self.device)
+        self.delay = torch.empty(self.N, **f32)
+        self.payment = torch.empty(self.N, **f32)
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h is not None:
+            _cabi.lib().dcml_env_destroy(h)
+
+    __del__ = close
+
+    # ---- device-resident API ----------------------------------------------------------------
+    def reset_device(self):
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().dcml_env_reset(self._h, _cabi.ptr(self.obs), _cabi.ptr(self.sob), _cabi.ptr(self.ava),
+                                                   _cabi.stream_ptr()))
+        return self.obs, self.share_obs_view(), self.ava
+
+    def step_device(self, actions):
+        """actions: device fp32 (N, L, 1) or (N, L).  Returns views of the env's own output buffers
+        (overwritten by the next call): obs, share_obs, reward (N,), done (N,) uint8, delay, payment, ava."""
+        a = actions.to(device=self.device, dtype=torch.float32).reshape(self.N, self.L).contiguous()
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().dcml_env_step(self._h, _cabi.ptr(a), _cabi.ptr(self.obs), _cabi.ptr(self.sob),
+                                                  _cabi.ptr(self.ava), _cabi.ptr(self.reward), _cabi.ptr(self.done),
+                                                  _cabi.ptr(self.delay), _cabi.ptr(self.payment), _cabi.stream_ptr()))
+        return self.obs, self.share_obs_view(), self.reward, self.done, self.delay, self.payment, self.ava
+
+    def share_obs_view(self):
+        return self.sob.unsqueeze(1).expand(self.N, self.L, self.W + 2)
+
+    def set_context(self, R=None, C=None, worker_pr=None, n_disabled=None):
+        """Preset contexts (Env(preset=True) / modify_preset); arrays per env, None keeps the current value."""
+        def dev(x, dt, shape):
+            if x is None:
+                return None
+            return torch.as_tensor(np.broadcast_to(np.asarray(x), shape).copy()).to(device=self.device, dtype=dt).contiguous()
+        R = dev(R, torch.float64, (self.N,))
+        C = dev(C, torch.float64, (self.N,))
+        pr = dev(worker_pr, torch.float64, (self.N, self.W))
+        nd = dev(n_disabled, torch.int32, (self.N,))
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().dcml_env_set_context(self._h, _cabi.ptr(R), _cabi.ptr(C), _cabi.ptr(pr), _cabi.ptr(nd),
+                                                         _cabi.ptr(self.obs), _cabi.ptr(self.sob), _cabi.ptr(self.ava),
+                                                         _cabi.stream_ptr()))
+        return self.obs, self.share_obs_view(), self.ava
+
+    # ---- the reference's host-side contract -------------------------------------------------
+    def _host_obs(self):
+        obs = self.obs.cpu().numpy().astype(np.float64)
+        sob = np.repeat(self.sob.cpu().numpy().astype(np.float64)[:, None, :], self.L, axis=1)
+        ava = self.ava.cpu().numpy().astype(np.int64)
+        return obs, sob, ava
+
+    def reset(self):
+        self.reset_device()
+        return self._host_obs()
+
+    def step(self, actions):
+        a = torch.as_tensor(np.asarray(actions, dtype=np.float32)) if not torch.is_tensor(actions) else actions
+        self.step_device(a)
+        obs, sob, ava = self._host_obs()
+        rew = np.repeat(self.reward.cpu().numpy().astype(np.float64)[:, None, None], self.L, axis=1)
+        dones = np.repeat(self.done.cpu().numpy().astype(bool)[:, None], self.L, axis=1)
+        infos = _Infos(self.delay.cpu().numpy(), self.payment.cpu().numpy())
+        return obs, sob, rew, dones, infos, ava

@@ -1,0 +1,125 @@
+"""Device-resident rollout store with the reference's ``SharedReplayBuffer`` interface
+(mat_src/mat/utils/shared_buffer.py:22-314): same array names and (T+1 | T, N, L, dim) shapes,
+``insert`` / ``compute_returns`` / ``after_update`` / ``feed_forward_generator_transformer``.
+
+Differences, all layout-only: arrays are fp32 torch tensors on the GPU instead of numpy;
+``share_obs`` keeps ONE (W+2) row per (t, env) and is exposed as a stride-0 expand
+(the model ignores it, ma_transformer.py:144-149); the dead ``rnn_states*`` arrays are
+(T+1, N, L, 1, 1) zeros.  ``compute_returns`` is the GAE kernel (csrc/gae.cu).
+"""
+import numpy as np
+import torch
+
+from . import _cabi
+
+
+def _shape(space):
+    return space.shape if space.__class__.__name__ == "Box" else space
+
+
+class SharedReplayBuffer:
+    def __init__(self, args, num_agents, obs_space, cent_obs_space, act_space, env_name, device="cuda"):
+        self.episode_length, self.n_rollout_threads = args.episode_length, args.n_rollout_threads
+        self.gamma, self.gae_lambda = args.gamma, args.gae_lambda
+        self._use_gae, self._use_popart, self._use_valuenorm = args.use_gae, args.use_popart, args.use_valuenorm
+        self.num_agents, self.env_name = num_agents, env_name
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _cabi.MatasError("SharedReplayBuffer needs a CUDA device (there is no CPU fallback)")
+        if not self._use_gae:
+            raise NotImplementedError("only the GAE branch of compute_returns is built (config.py:260 default)")
+        T, N, L = self.episode_length, self.n_rollout_threads, num_agents
+        obs_dim = _shape(obs_space)[0] if not isinstance(_shape(obs_space)[-1], list) else _shape(obs_space)[0][0]
+        sob_dim = _shape(cent_obs_space)[0] if not isinstance(_shape(cent_obs_space)[-1], list) else _shape(cent_obs_space)[0][0]
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=self.device)
+        o = lambda *s: torch.ones(*s, dtype=torch.float32, device=self.device)
+        self._share_obs = z(T + 1, N, sob_dim)
+        self.obs = z(T + 1, N, L, obs_dim)
+        self.rnn_states = z(T + 1, N, L, 1, 1)
+        self.rnn_states_critic = self.rnn_states
+        self.value_preds = z(T + 1, N, L, 1)
+        self.returns = z(T + 1, N, L, 1)
+        self.advantages = z(T, N, L, 1)
+        self.available_actions = o(T + 1, N, L, act_space.n)
+        self.actions = z(T, N, L, 1)
+        self.action_log_probs = z(T, N, L, 1)
+        self.rewards = z(T, N, L, 1)
+        self.masks = o(T + 1, N, L, 1)
+        self.bad_masks = o(T + 1, N, L, 1)
+        self.active_masks = o(T + 1, N, L, 1)
+        self.step = 0
+
+    @property
+    def share_obs(self):
+        T1, N, D = self._share_obs.shape
+        return self._share_obs.unsqueeze(2).expand(T1, N, self.num_agents, D)
+
+    def _put(self, dst, src):
+        src = torch.as_tensor(src) if not torch.is_tensor(src) else src
+        dst.copy_(src.to(device=self.device, dtype=torch.float32).reshape(dst.shape), non_blocking=True)
+
+    def insert(self, share_obs, obs, rnn_states_actor, rnn_states_critic, actions, action_log_probs, value_preds,
+               rewards, masks, bad_masks=None, active_masks=None, available_actions=None):
+        """shared_buffer.py:118-151.  ``share_obs`` may be (N, L, D) (the reference's replicated form;
+        row 0 is kept) or (N, D); ``rewards`` / ``masks`` may be per env (N,) or (N, L, 1)."""
+        s = self.step
+        so = torch.as_tensor(share_obs) if not torch.is_tensor(share_obs) else share_obs
+        self._put(self._share_obs[s + 1], so[:, 0, :] if so.dim() == 3 else so)
+        self._put(self.obs[s + 1], obs)
+        self._put(self.actions[s], actions)
+        self._put(self.action_log_probs[s], action_log_probs)
+        self._put(self.value_preds[s], value_preds)
+        self._bcast(self.rewards[s], rewards)
+        self._bcast(self.masks[s + 1], masks)
+        if bad_masks is not None:
+            self._bcast(self.bad_masks[s + 1], bad_masks)
+        if active_masks is not None:
+            self._bcast(self.active_masks[s + 1], active_masks)
+        if available_actions is not None:
+            self._put(self.available_actions[s + 1], available_actions)
+        self.step = (self.step + 1) % self.episode_length
+
+    def _bcast(self, dst, src):
+        src = torch.as_tensor(src) if not torch.is_tensor(src) else src
+        src = src.to(device=self.device, dtype=torch.float32)
+        if src.numel() == dst.shape[0]:
+            src = src.reshape(-1, 1, 1).expand_as(dst)
+        dst.copy_(src.reshape(dst.shape) if src.numel() == dst.numel() else src)
+
+    def after_update(self):
+        """shared_buffer.py:188-198"""
+        for a in (self._share_obs, self.obs, self.masks, self.bad_masks, self.active_masks, self.available_actions):
+            a[0].copy_(a[-1])
+
+    def compute_returns(self, next_value, value_normalizer=None):
+        """shared_buffer.py:207-238 (GAE branch) on the device, ValueNorm denormalisation fused."""
+        self._put(self.value_preds[-1], next_value)
+        use_vn = (self._use_popart or self._use_valuenorm) and value_normalizer is not None
+        T, N, L = self.episode_length, self.n_rollout_threads, self.num_agents
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().matas_gae(_cabi.ptr(self.rewards), _cabi.ptr(self.value_preds), _cabi.ptr(self.masks),
+                                              _cabi.ptr(value_normalizer.stats) if use_vn else None,
+                                              float(self.gamma), float(self.gae_lambda), T, N * L,
+                                              _cabi.ptr(self.advantages), _cabi.ptr(self.returns), _cabi.stream_ptr()))
+
+    def feed_forward_generator_transformer(self, advantages, num_mini_batch=None, mini_batch_size=None):
+        """shared_buffer.py:240-314: rows are (t, env) pairs carrying all L agents; one global
+        permutation split into contiguous minibatches; yields the reference's 12-tuple (device tensors)."""
+        T, N, L = self.episode_length, self.n_rollout_threads, self.num_agents
+        batch_size = N * T
+        if mini_batch_size is None:
+            assert batch_size >= num_mini_batch, "PPO requires N*T >= num_mini_batch"
+            mini_batch_size = batch_size // num_mini_batch
+        rand = torch.randperm(batch_size, device=self.device)
+        flat = lambda x: x.reshape(batch_size, *x.shape[2:])
+        share = flat(self._share_obs[:-1])
+        obs, act, ava = flat(self.obs[:-1]), flat(self.actions), flat(self.available_actions[:-1])
+        vp, ret, msk = flat(self.value_preds[:-1]), flat(self.returns[:-1]), flat(self.masks[:-1])
+        am, lp = flat(self.active_masks[:-1]), flat(self.action_log_probs)
+        adv = None if advantages is None else flat(torch.as_tensor(advantages).to(self.device))
+        for i in range(num_mini_batch):
+            idx = rand[i * mini_batch_size:(i + 1) * mini_batch_size]
+            g = lambda x: x[idx].reshape(-1, *x.shape[2:])
+            so = share[idx].unsqueeze(1).expand(-1, L, -1).reshape(-1, share.shape[-1])
+            yield (so, g(obs), None, None, g(act), g(vp), g(ret), g(msk), g(am), g(lp),
+                   None if adv is None else g(adv), g(ava))

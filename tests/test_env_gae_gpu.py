@@ -1,0 +1,150 @@
+"""GPU parity of the DCML simulator and the GAE kernel, through the C ABI, against reference
+outputs (golden fixtures) and the CPU oracle."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden
+from oracle import env_oracle as eo
+from oracle import ppo_oracle as po
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5          # BASELINE.json: env outputs and rewards within 1e-5 relative in fp32
+
+
+def _close(got, want, name=""):
+    np.testing.assert_allclose(np.asarray(got, np.float64), np.asarray(want, np.float64), rtol=RTOL, atol=1e-6, err_msg=name)
+
+
+@pytest.mark.parametrize("case", ["env_W20", "env_W100"])
+def test_env_vs_reference(case, cuda_device):
+    from mat_dcml_b200 import DcmlVecEnv
+    g = golden(case)
+    W, B, steps = int(g["W"]), int(g["B"]), int(g["steps"])
+    env = DcmlVecEnv(B, W, g["base"], seed=int(g["seed"]), double_reset=True)
+    obs, sob, ava = env.reset()
+    assert obs.shape == (B, W + 1, 7) and sob.shape == (B, W + 1, W + 2) and ava.shape == (B, W + 1, 2)
+    assert obs.dtype == np.float64 and ava.dtype == np.int64
+    _close(obs, g["obs0"], "obs0"); _close(sob[:, 0], g["sob0"], "sob0")
+    np.testing.assert_array_equal(ava, g["ava0"])
+    for t in range(1, steps + 1):
+        obs, sob, rew, dones, infos, ava = env.step(g["act%d" % t])
+        assert rew.shape == (B, W + 1, 1) and dones.shape == (B, W + 1) and dones.dtype == bool
+        _close([i[0]["delay"] for i in infos], g["delay%d" % t], "delay")
+        _close([i[0]["payment"] for i in infos], g["pay%d" % t], "payment")
+        _close(rew[:, 0, 0], g["rew%d" % t], "reward")
+        np.testing.assert_array_equal(dones[:, 0], g["done%d" % t])
+        _close(obs, g["obs%d" % t], "obs"); _close(sob[:, 0], g["sob%d" % t], "sob")
+        np.testing.assert_array_equal(ava, g["ava%d" % t])
+
+
+@pytest.mark.parametrize("W,B,dbl", [(10, 37, True), (50, 9, False), (200, 3, True)])
+def test_env_vs_oracle_random(W, B, dbl, cuda_device):
+    from mat_dcml_b200 import DcmlVecEnv
+    base = eo.synthetic_workloads(W, seed=W)
+    env = DcmlVecEnv(B, W, base, seed=77, double_reset=dbl, env_offset=1000)
+    ora = eo.DcmlEnvOracle(B, W, base, seed=77, double_reset=dbl, env0=1000)
+    o1, s1, a1 = env.reset()
+    o2, s2, a2 = ora.reset()
+    _close(o1, o2); _close(s1, s2); np.testing.assert_array_equal(a1, a2)
+    rng = np.random.RandomState(W)
+    for t in range(4):
+        sel = (rng.uniform(size=(B, W)) < 0.5).astype(np.float32) * a2[:, :W, 1]
+        if t == 1:
+            sel[0] = 0
+        act = np.concatenate([sel, rng.uniform(-0.2, 1.3, size=(B, 1)).astype(np.float32)], 1)[:, :, None]
+        o1, s1, r1, d1, i1, a1 = env.step(act)
+        o2, s2, r2, d2, i2, a2 = ora.step(act)
+        _close(r1, r2, "reward"); np.testing.assert_array_equal(d1, d2)
+        _close([i[0]["delay"] for i in i1], [i[0]["delay"] for i in i2])
+        _close([i[0]["payment"] for i in i1], [i[0]["payment"] for i in i2])
+        _close(o1, o2, "obs"); _close(s1, s2, "sob"); np.testing.assert_array_equal(a1, a2)
+
+
+def test_env_preset_context(cuda_device):
+    from mat_dcml_b200 import DcmlVecEnv
+    W, B = 20, 5
+    env = DcmlVecEnv(B, W, seed=3)
+    env.reset()
+    pr = np.full((B, W), 0.25)
+    obs, sob, ava = env.set_context(R=2 ** 19, C=921.6, worker_pr=pr, n_disabled=np.array([0, 1, 8, 16, 16]))
+    obs, ava = obs.cpu().numpy(), ava.cpu().numpy()
+    np.testing.assert_allclose(obs[:, :, 0], (2 ** 19 - 1024) / (2 ** 20 - 1024), rtol=1e-6)
+    np.testing.assert_allclose(obs[:, :, 1], (921.6 - 32) / (1024 - 32), rtol=1e-6)
+    np.testing.assert_array_equal((ava[:, :W, 1] == 0).sum(1), [0, 1, 8, 16, 16])
+    ora = eo.DcmlEnvOracle(B, W, env.base_workload, seed=3)
+    ora.reset()
+    ora.set_context(R=2 ** 19, C=921.6, Pr=pr, k_dis=np.array([0, 1, 8, 16, 16]), disabled=(ava[:, :W, 1] == 0))
+    act = np.concatenate([ava[:, :W, 1], np.full((B, 1), 0.7, np.float32)], 1).astype(np.float32)
+    _, _, r1, _, i1, _ = env.step(act)
+    _, _, r2, _, i2, _ = ora.step(act)
+    _close(r1, r2); _close([i[0]["delay"] for i in i1], [i[0]["delay"] for i in i2])
+
+
+def test_env_full_size_properties(cuda_device):
+    """C3 shape (16384 x 50): invariants of the simulator that hold at any size."""
+    from mat_dcml_b200 import DcmlVecEnv
+    W, B = 50, 16384
+    env = DcmlVecEnv(B, W, seed=5)
+    obs, sob, ava = env.reset_device()
+    dones = []
+    for t in range(3):
+        sel = ava[:, :W, 1] * (torch.rand(B, W, device="cuda") < 0.6)
+        act = torch.cat([sel, torch.full((B, 1), 0.7, device="cuda")], 1)
+        obs, sob, rew, done, delay, pay, ava = env.step_device(act)
+        n_sel = sel.sum(1)
+        scale = torch.where(n_sel == 0, 1.5, 1.0)
+        assert torch.allclose(rew, scale * (-99 * delay - pay), rtol=1e-5, atol=1e-4)
+        assert bool((delay > 0).all()) and bool((pay >= 0).all()) and torch.isfinite(rew).all()
+        k = (ava[:, :W, 1] == 0).sum(1)
+        assert int(k.min()) >= 1 and int(k.max()) <= 40
+        assert bool((obs[:, :W, 2:6][ava[:, :W, 1] == 0] == 1).all())
+        assert bool((obs[:, W, 6] == 1.1).all()) and bool((ava[:, W] == 1).all())
+        assert float(obs[:, :W, 6].max()) < 1.0 and float(obs.min()) >= 0
+        dones.append(done.float().mean().item())
+    assert abs(np.mean(dones) - 0.8) < 0.02
+
+
+def _vn(stats, device):
+    from mat_dcml_b200 import ValueNorm
+    vn = ValueNorm(1, device=device)
+    vn.stats.copy_(torch.as_tensor(stats))
+    return vn
+
+
+def test_gae_vs_reference_bit_exact(cuda_device):
+    from mat_dcml_b200 import SharedReplayBuffer, Action_Space
+    import argparse
+    g = golden("gae")
+    for case in ("vn", "raw"):
+        T, N, L, _ = g[case + "_rewards"].shape
+        args = argparse.Namespace(episode_length=T, n_rollout_threads=N, hidden_size=64, recurrent_N=1, gamma=0.99,
+                                  gae_lambda=0.95, use_gae=True, use_popart=False, use_valuenorm=case == "vn",
+                                  use_proper_time_limits=False, algorithm_name="mat")
+        buf = SharedReplayBuffer(args, L, [7], [L + 1], Action_Space(2, semi_index=-1), "DCML")
+        buf.rewards.copy_(torch.from_numpy(g[case + "_rewards"]))
+        buf.value_preds.copy_(torch.from_numpy(g[case + "_values_in"]))
+        buf.masks.copy_(torch.from_numpy(g[case + "_masks"]))
+        buf.compute_returns(g[case + "_next"], _vn(g["vn_stats"], "cuda") if case == "vn" else None)
+        np.testing.assert_array_equal(buf.advantages.cpu().numpy(), g[case + "_adv"])
+        np.testing.assert_array_equal(buf.returns.cpu().numpy()[:-1], g[case + "_ret"][:-1])
+
+
+@pytest.mark.parametrize("T,n", [(50, 8192 * 21), (7, 13), (3, 4097)])
+def test_gae_vs_oracle(T, n, cuda_device):
+    import ctypes
+    from mat_dcml_b200 import _cabi
+    rng = np.random.RandomState(n % 1000)
+    r = (rng.standard_normal((T, n)) * 50 - 200).astype(np.float32)
+    v = rng.standard_normal((T + 1, n)).astype(np.float32)
+    m = (rng.uniform(size=(T + 1, n)) > 0.8).astype(np.float32)
+    vn = po.ValueNormState()
+    vn.update(torch.from_numpy((rng.standard_normal((64, 1)) * 40 - 150).astype(np.float32)))
+    adv, ret, _ = po.compute_returns(r[..., None, None], v[..., None, None], m[..., None, None], v[-1][..., None, None], vn)
+    d = lambda x: torch.from_numpy(x).cuda()
+    dr, dv, dm, ds = d(r), d(v), d(m), d(vn.stats())
+    da, dret = torch.zeros_like(dr), torch.zeros_like(dv)
+    _cabi.check(_cabi.lib().matas_gae(_cabi.ptr(dr), _cabi.ptr(dv), _cabi.ptr(dm), _cabi.ptr(ds), 0.99, 0.95, T, n,
+                                      _cabi.ptr(da), _cabi.ptr(dret), _cabi.stream_ptr()))
+    np.testing.assert_array_equal(da.cpu().numpy(), adv[..., 0, 0])
+    np.testing.assert_array_equal(dret.cpu().numpy()[:-1], ret[:-1, :, 0, 0])
