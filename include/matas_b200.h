@@ -101,6 +101,16 @@ int matas_policy_act_autoregressive(matas_policy* p, const float* obs_rep, const
 int matas_policy_act_parallel(matas_policy* p, const float* obs_rep, const float* ava, const float* actions, long M,
                               float* logp, float* entropy, void* stream);
 
+/* Measurement hooks (no counterpart in the reference): when enabled, every launch of the
+ * autoregressive decode kernel is bracketed by CUDA events on its stream; matas_policy_decode_time
+ * waits for them and returns the summed device time and the launch count since enabling. */
+int matas_policy_timing(matas_policy* p, int enable);
+int matas_policy_decode_time(matas_policy* p, double* ms_total, long* launches);
+
+/* Measured fp32 FFMA throughput of the current device in TFLOP/s (no counterpart in the reference;
+ * the roofline denominator of the SIMT kernels, which MEASURED_PEAKS.json does not hold). */
+int matas_fp32_peak(int iters, double* tflops);
+
 /* ------------------------------------------------------------------------------------------
  * Vectorised DCML simulator: replaces Env.step / Env.reset
  * (DCML_BID_FIRST_MA_ENV_SingleProcess.py:57-144, 157-274), Worker.process / bid

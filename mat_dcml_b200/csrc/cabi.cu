@@ -54,7 +54,25 @@ struct matas_policy {
     size_t kv_cap = 0;
     float* d_kv = nullptr;
     PolicyBufs bufs;
+    // optional per-launch timing of the decode kernel (CUDA events on the launching stream)
+    static constexpr int NEV = 64;
+    bool timing = false;
+    cudaEvent_t ev0[NEV], ev1[NEV];
+    bool ev_made = false, ev_pending[NEV];
+    int ev_next = 0;
+    double t_ms = 0.0;
+    long t_n = 0;
 };
+
+static int harvest(matas_policy* p, int i) {
+    if (p->ev_pending[i]) {
+        float ms = 0.f;
+        CUDA_TRY(cudaEventSynchronize(p->ev1[i]));
+        CUDA_TRY(cudaEventElapsedTime(&ms, p->ev0[i], p->ev1[i]));
+        p->t_ms += ms; p->t_n += 1; p->ev_pending[i] = false;
+    }
+    return MATAS_OK;
+}
 
 namespace {
 
@@ -160,6 +178,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
     cudaFree(p->d_table); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv);
+    if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
 }
@@ -217,7 +236,82 @@ static int run_decode(matas_policy* p, const float* ava, long B, int determinist
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
     a.seed = seed; a.step = step; a.env_offset = env_offset;
     a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
-    return launch_decode(p->bufs, a, grid, stream);
+    if (!p->timing) return launch_decode(p->bufs, a, grid, stream);
+    const int i = p->ev_next;
+    p->ev_next = (i + 1) % matas_policy::NEV;
+    int rc = harvest(p, i);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(p->ev0[i], stream));
+    rc = launch_decode(p->bufs, a, grid, stream);
+    CUDA_TRY(cudaEventRecord(p->ev1[i], stream));
+    p->ev_pending[i] = true;
+    return rc;
+}
+
+extern "C" int matas_policy_timing(matas_policy* p, int enable) {
+    ARG_CHECK(p != nullptr, "null policy handle");
+    if (enable && !p->ev_made) {
+        for (int i = 0; i < matas_policy::NEV; ++i) {
+            CUDA_TRY(cudaEventCreate(&p->ev0[i]));
+            CUDA_TRY(cudaEventCreate(&p->ev1[i]));
+            p->ev_pending[i] = false;
+        }
+        p->ev_made = true;
+    }
+    if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { int rc = harvest(p, i); if (rc) return rc; }
+    p->timing = enable != 0;
+    p->t_ms = 0.0; p->t_n = 0;
+    return MATAS_OK;
+}
+
+extern "C" int matas_policy_decode_time(matas_policy* p, double* ms_total, long* launches) {
+    ARG_CHECK(p && ms_total && launches, "null argument");
+    if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { int rc = harvest(p, i); if (rc) return rc; }
+    *ms_total = p->t_ms; *launches = p->t_n;
+    return MATAS_OK;
+}
+
+// dependent-FFMA probe: 8 independent chains per thread, 2 FLOP per FFMA
+__global__ void fp32_peak_kernel(float* out, int iters) {
+    float a[8];
+    for (int i = 0; i < 8; ++i) a[i] = threadIdx.x * 1e-3f + i;
+    const float b = 1.0000001f, c = 1e-7f;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = fmaf(a[i], b, c);
+    }
+    float s = 0.f;
+    for (int i = 0; i < 8; ++i) s += a[i];
+    if (s == 123.456f) out[0] = s;
+}
+
+extern "C" int matas_fp32_peak(int iters, double* tflops) {
+    ARG_CHECK(iters > 0 && tflops, "bad argument");
+    int dev = 0, n_sm = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+    float* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, 4));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    const int grid = n_sm * 8, block = 256;
+    fp32_peak_kernel<<<grid, block>>>(d, iters / 10 + 1);
+    double best = 0.0;
+    for (int rep = 0; rep < 3; ++rep) {
+        CUDA_TRY(cudaEventRecord(e0));
+        fp32_peak_kernel<<<grid, block>>>(d, iters);
+        CUDA_TRY(cudaEventRecord(e1));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        const double fl = 2.0 * 64.0 * (double)iters * (double)grid * block;
+        if (fl / (ms * 1e-3) / 1e12 > best) best = fl / (ms * 1e-3) / 1e12;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    *tflops = best;
+    return MATAS_OK;
 }
 
 extern "C" int matas_policy_get_actions(matas_policy* p, const float* obs, const float* ava, long B, int deterministic,
