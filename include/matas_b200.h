@@ -101,6 +101,21 @@ int matas_policy_act_autoregressive(matas_policy* p, const float* obs_rep, const
 int matas_policy_act_parallel(matas_policy* p, const float* obs_rep, const float* ava, const float* actions, long M,
                               float* logp, float* entropy, void* stream);
 
+/* Allocation-free variant of matas_policy_act_autoregressive (no counterpart in the reference).
+ * For callers that must not allocate device memory after start-up -- e.g. a decision server sharing
+ * the GPU with another framework's caching allocator, or a latency-critical loop that cannot take
+ * the device-wide synchronisation of cudaMalloc/cudaFree.  Its scratch (cross-attention queries +
+ * decode K/V cache) is a fixed 5 MiB array inside the library image, resident on every GPU that
+ * loads the library until the process exits.  Limit: B * n_agent <= 2048 (env, agent) pairs per
+ * call; larger calls fail with an error.  The first call on each device resolves the array's device
+ * address (make it before any stream capture).  All calls on a device share the array: calls that
+ * overlap on the GPU race, so serialise them on one stream; nothing needs clearing between calls.
+ * Arguments and results as matas_policy_act_autoregressive. */
+int matas_policy_act_autoregressive_static(matas_policy* p, const float* obs_rep, const float* ava, long B,
+                                           int deterministic, int stride, uint64_t seed, uint32_t step,
+                                           long env_offset, const float* u, const float* z, float* actions,
+                                           float* logp, void* stream);
+
 /* Measurement hooks (no counterpart in the reference): when enabled, every launch of the
  * autoregressive decode kernel is bracketed by CUDA events on its stream; matas_policy_decode_time
  * waits for them and returns the summed device time and the launch count since enabling. */

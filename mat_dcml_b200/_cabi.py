@@ -38,6 +38,8 @@ _SIGNATURES = {
     "matas_policy_encode": (ctypes.c_int, [_P, _P, ctypes.c_long, _P, _P, _P]),
     "matas_policy_act_autoregressive": (ctypes.c_int, [_P, _P, _P, ctypes.c_long, ctypes.c_int, ctypes.c_int, ctypes.c_uint64,
                                                        ctypes.c_uint32, ctypes.c_long, _P, _P, _P, _P, _P]),
+    "matas_policy_act_autoregressive_static": (ctypes.c_int, [_P, _P, _P, ctypes.c_long, ctypes.c_int, ctypes.c_int,
+                                                              ctypes.c_uint64, ctypes.c_uint32, ctypes.c_long, _P, _P, _P, _P, _P]),
     "matas_policy_act_parallel": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, _P, _P, _P]),
     "matas_policy_timing": (ctypes.c_int, [_P, ctypes.c_int]),
     "matas_policy_decode_time": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_long)]),

@@ -185,6 +185,14 @@ extern "C" int matas_policy_destroy(matas_policy* p) {
 
 extern "C" long matas_policy_param_count(const matas_policy* p) { return p ? p->n_params : -1; }
 
+// read-only view of a handle for entry points that live in other translation units
+int matas_policy_view(const matas_policy* p, PolicyView* v) {
+    ARG_CHECK(p && v, "null policy handle");
+    v->n_agent = p->cfg.n_agent; v->mode = p->cfg.mode; v->device = p->device; v->n_sm = p->n_sm;
+    v->weights_set = p->weights_set ? 1 : 0; v->packed = p->d_packed;
+    return MATAS_OK;
+}
+
 extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void* stream) {
     ARG_CHECK(p && flat, "null argument");
     pack_kernel<<<(unsigned)p->table.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_table);

@@ -34,6 +34,10 @@ struct DecodeArgs {
     float* logp;         // [B][L]
 };
 
+struct matas_policy;
+struct PolicyView { int n_agent, mode, device, n_sm, weights_set; const float* packed; };
+int matas_policy_view(const matas_policy* p, PolicyView* v);
+
 int policy_launch_geometry(int L, int* depth, int* lpad, size_t* bytes);
 int policy_decode_steps(int L, int mode, int deterministic, int stride);
 int policy_init_constants();
