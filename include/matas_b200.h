@@ -87,6 +87,18 @@ int matas_policy_get_actions(matas_policy* p, const float* obs, const float* ava
 int matas_policy_evaluate(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
                           float* values, float* logp, float* entropy, void* stream);
 
+/* Training-mode forward + backward of MultiAgentTransformer.forward, replacing torch autograd in
+ * MATTrainer.ppo_update (mat_src/mat/algorithms/mat/mat_trainer.py:120-147).
+ * matas_policy_evaluate_train = matas_policy_evaluate that also keeps the activations;
+ * matas_policy_evaluate_backward must directly follow it with the same batch: given dLoss/dvalues,
+ * dLoss/dlogp, dLoss/dentropy [M*L] it ACCUMULATES dLoss/dparams into flat_grad (fp32, laid out like
+ * the flat parameter vector; unused parameters keep zero).  n_agent <= 128. */
+int matas_policy_evaluate_train(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
+                                float* values, float* logp, float* entropy, void* stream);
+int matas_policy_evaluate_backward(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
+                                   const float* d_values, const float* d_logp, const float* d_entropy,
+                                   float* flat_grad, void* stream);
+
 /* Encoder.forward, ma_transformer.py:141-154: obs -> values [B*L] and obs_rep [B*L*64]. */
 int matas_policy_encode(matas_policy* p, const float* obs, long B, float* values, float* obs_rep, void* stream);
 

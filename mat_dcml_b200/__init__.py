@@ -13,7 +13,7 @@ def __getattr__(name):
     import importlib
     table = {"TransformerPolicy": "transformer_policy", "MultiAgentTransformer": "ma_transformer",
              "DcmlVecEnv": "dcml_env", "Action_Space": "dcml_env", "SharedReplayBuffer": "shared_buffer",
-             "ValueNorm": "valuenorm"}
+             "ValueNorm": "valuenorm", "MATTrainer": "mat_trainer"}
     if name in table:
         return getattr(importlib.import_module("." + table[name], __name__), name)
     raise AttributeError(name)

@@ -35,6 +35,8 @@ _SIGNATURES = {
     "matas_policy_get_actions": (ctypes.c_int, [_P, _P, _P, ctypes.c_long, ctypes.c_int, ctypes.c_int, ctypes.c_uint64,
                                                 ctypes.c_uint32, ctypes.c_long, _P, _P, _P, _P, _P, _P]),
     "matas_policy_evaluate": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, _P, _P, _P, _P]),
+    "matas_policy_evaluate_train": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, _P, _P, _P, _P]),
+    "matas_policy_evaluate_backward": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, _P, _P, _P, _P, _P]),
     "matas_policy_encode": (ctypes.c_int, [_P, _P, ctypes.c_long, _P, _P, _P]),
     "matas_policy_act_autoregressive": (ctypes.c_int, [_P, _P, _P, ctypes.c_long, ctypes.c_int, ctypes.c_int, ctypes.c_uint64,
                                                        ctypes.c_uint32, ctypes.c_long, _P, _P, _P, _P, _P]),

@@ -1,6 +1,6 @@
-"""Teacher-forced evaluation (MultiAgentTransformer.forward) as a torch.autograd.Function over the
-C-ABI kernels.  Forward: matas_policy_evaluate.  Backward: matas_policy_evaluate_backward when the
-library exports it; otherwise asking for gradients is an error (there is no eager fallback)."""
+"""Teacher-forced evaluation (MultiAgentTransformer.forward) over the C-ABI kernels.  Without grad
+mode: matas_policy_evaluate.  With grad mode: a torch.autograd.Function whose backward is the
+hand-written CUDA backward (autograd_bwd.py); there is no eager fallback."""
 import torch
 
 from . import _cabi
@@ -25,4 +25,4 @@ def evaluate(model, obs, action, ava):
     if not needs_grad:
         return _forward(model, obs, action, ava)
     from .autograd_bwd import EvaluateFn
-    return EvaluateFn.apply(model, obs, action, ava, model.flat_parameters())
+    return EvaluateFn.apply(model, obs, action, ava, model._anchor())

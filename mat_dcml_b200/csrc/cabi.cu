@@ -9,6 +9,7 @@
 
 #include "../../include/matas_b200.h"
 #include "layout.h"
+#include "policy_bwd.h"
 #include "policy_fwd.h"
 
 static thread_local char g_err[512] = "";
@@ -54,6 +55,12 @@ struct matas_policy {
     size_t kv_cap = 0;
     float* d_kv = nullptr;
     PolicyBufs bufs;
+    // training: saved activations + backward work buffers, gradient offsets
+    GradMap gm;
+    TrainBufs tb;
+    long train_cap = 0;
+    float* d_train = nullptr;
+    long train_tokens = 0;        // > 0: the saved activations belong to a training forward of that many tokens
     // optional per-launch timing of the decode kernel (CUDA events on the launching stream)
     static constexpr int NEV = 64;
     bool timing = false;
@@ -79,25 +86,39 @@ namespace {
 // walks the parameters in the reference's state_dict order (ma_transformer.py:119-203)
 struct LayoutBuilder {
     std::vector<PackEntry>& tab;
+    GradMap& gm;
     int src = 0;
-    explicit LayoutBuilder(std::vector<PackEntry>& t) : tab(t) {}
+    LayoutBuilder(std::vector<PackEntry>& t, GradMap& g) : tab(t), gm(g) {
+        for (int i = 0; i < lay::N_BLOBS; ++i) gm.w[i] = gm.b[i] = gm.lnw[i] = gm.lnb[i] = -1;
+    }
+    static int idx(int blob) { return (blob - lay::ENC_BLOBS) / lay::BLOB; }
     void vec(int n, int dst) { if (dst >= 0) tab.push_back({src, dst, n, 0}); src += n; }
     void mat(int rows, int cols, int dst) { if (dst >= 0) tab.push_back({src, dst, rows, cols}); src += rows * cols; }
     void linear(int out, int in, int dst_wt, int dst_b, bool bias = true) {
         mat(out, in, dst_wt);
         if (bias) vec(out, dst_b);
     }
-    void blob_linear(int blob) { linear(64, 64, blob, blob + lay::B_BIAS); }
-    void blob_ln(int blob) { vec(64, blob + lay::B_LNW); vec(64, blob + lay::B_LNB); }
+    void blob_linear(int blob) {
+        tab.push_back({src, lay::bw(blob), 4096, 0});      // untransposed copy for the backward pass
+        gm.w[idx(blob)] = src; gm.b[idx(blob)] = src + 4096;
+        linear(64, 64, blob, blob + lay::B_BIAS);
+    }
+    void blob_ln(int blob) {
+        gm.lnw[idx(blob)] = src; gm.lnb[idx(blob)] = src + 64;
+        vec(64, blob + lay::B_LNW); vec(64, blob + lay::B_LNB);
+    }
 };
 
-long build_layout(const matas_model_cfg& c, std::vector<PackEntry>& tab) {
-    LayoutBuilder b(tab);
+long build_layout(const matas_model_cfg& c, std::vector<PackEntry>& tab, GradMap& gm) {
+    LayoutBuilder b(tab, gm);
     using namespace lay;
     // encoder.state_encoder (unused when encode_state=False, ma_transformer.py:144-149)
     b.vec(c.state_dim, -1); b.vec(c.state_dim, -1); b.linear(64, c.state_dim, -1, -1);
+    gm.enc_ln7_w = b.src; gm.enc_ln7_b = b.src + c.obs_dim;
     b.vec(c.obs_dim, ENC_EMB + ENC_EMB_LNW); b.vec(c.obs_dim, ENC_EMB + ENC_EMB_LNB);
+    gm.enc_wobs = b.src; gm.enc_bobs = b.src + 64 * c.obs_dim;
     b.linear(64, c.obs_dim, ENC_EMB + ENC_EMB_WT, ENC_EMB + ENC_EMB_B);
+    gm.enc_ln_w = b.src; gm.enc_ln_b = b.src + 64;
     b.vec(64, ENC_EMB + ENC_EMB_LN2W); b.vec(64, ENC_EMB + ENC_EMB_LN2B);
     for (int k = 0; k < 2; ++k) {
         b.blob_ln(enc_blob(k, EP));
@@ -106,11 +127,15 @@ long build_layout(const matas_model_cfg& c, std::vector<PackEntry>& tab) {
         b.blob_linear(enc_blob(k, EM0)); b.blob_linear(enc_blob(k, EM2));
     }
     b.blob_linear(ENC_H0); b.blob_ln(ENC_H0);
+    gm.enc_h3_w = b.src; gm.enc_h3_b = b.src + 64;
     b.vec(64, ENC_H3); b.vec(1, ENC_H3 + 64);
-    if (c.mode == MATAS_MODE_SEMI) b.vec(c.act_dim, DEC_H3 + DEC_H3_LOGSTD);
+    gm.log_std = -1;
+    if (c.mode == MATAS_MODE_SEMI) { gm.log_std = b.src; b.vec(c.act_dim, DEC_H3 + DEC_H3_LOGSTD); }
+    gm.dec_wa = b.src;
     b.mat(64, c.act_dim + 1, DEC_EMB + DEC_EMB_WT);
     // decoder.obs_encoder (unused unless dec_actor, ma_transformer.py:198-199)
     b.vec(c.obs_dim, -1); b.vec(c.obs_dim, -1); b.linear(64, c.obs_dim, -1, -1);
+    gm.dec_ln_w = b.src; gm.dec_ln_b = b.src + 64;
     b.vec(64, DEC_EMB + DEC_EMB_LNW); b.vec(64, DEC_EMB + DEC_EMB_LNB);
     for (int k = 0; k < 2; ++k) {
         b.blob_ln(dec_blob(k, DP1)); b.blob_ln(dec_blob(k, DP2)); b.blob_ln(dec_blob(k, DM2));
@@ -119,6 +144,7 @@ long build_layout(const matas_model_cfg& c, std::vector<PackEntry>& tab) {
         b.blob_linear(dec_blob(k, DM0)); b.blob_linear(dec_blob(k, DM2));
     }
     b.blob_linear(DEC_H0); b.blob_ln(DEC_H0);
+    gm.dec_h3_w = b.src; gm.dec_h3_b = b.src + 128;
     b.vec(2 * 64, DEC_H3); b.vec(2, DEC_H3 + DEC_H3_B);
     return b.src;
 }
@@ -157,7 +183,8 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
         delete p;
         return MATAS_ERR_CUDA;
     }
-    p->n_params = build_layout(p->cfg, p->table);
+    memset(&p->tb, 0, sizeof(p->tb));
+    p->n_params = build_layout(p->cfg, p->table, p->gm);
     auto fail = [&](cudaError_t e, const char* what) {
         matas_set_error("%s: %s", what, cudaGetErrorString(e));
         matas_policy_destroy(p);
@@ -167,8 +194,8 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     if ((e = cudaMalloc(&p->d_table, p->table.size() * sizeof(PackEntry))) != cudaSuccess) return fail(e, "cudaMalloc(table)");
     if ((e = cudaMemcpy(p->d_table, p->table.data(), p->table.size() * sizeof(PackEntry), cudaMemcpyHostToDevice)) != cudaSuccess)
         return fail(e, "cudaMemcpy(table)");
-    if ((e = cudaMalloc(&p->d_packed, lay::TOTAL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMalloc(packed)");
-    if ((e = cudaMemset(p->d_packed, 0, lay::TOTAL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMemset(packed)");
+    if ((e = cudaMalloc(&p->d_packed, lay::TOTAL_ALL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMalloc(packed)");
+    if ((e = cudaMemset(p->d_packed, 0, lay::TOTAL_ALL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMemset(packed)");
     p->bufs.w = p->d_packed;
     if ((rc = policy_init_constants())) { matas_policy_destroy(p); return rc; }
     *out = p;
@@ -177,7 +204,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
 
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
-    cudaFree(p->d_table); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv);
+    cudaFree(p->d_table); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train);
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
@@ -202,6 +229,7 @@ extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void
 }
 
 static int alloc_tokens(matas_policy* p, long n_tok) {
+    p->train_tokens = 0;            // any other forward overwrites K/V/rep that a pending backward would need
     if (n_tok <= p->tok_cap) return MATAS_OK;
     if (p->d_tok) CUDA_TRY(cudaFree(p->d_tok));
     p->d_tok = nullptr; p->tok_cap = 0;
@@ -354,6 +382,68 @@ extern "C" int matas_policy_act_parallel(matas_policy* p, const float* obs_rep, 
     if ((rc = alloc_tokens(p, M * L))) return rc;
     if ((rc = launch_q2_from_rep(p->bufs, obs_rep, M, L, (cudaStream_t)stream))) return rc;
     return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream);
+}
+
+static int alloc_train(matas_policy* p, long n_tok) {
+    if (n_tok > p->train_cap) {
+        if (p->d_train) CUDA_TRY(cudaFree(p->d_train));
+        p->d_train = nullptr; p->train_cap = 0;
+        const long cap = n_tok + 64;
+        constexpr int WIDE = 36, NARROW = 27;
+        CUDA_TRY(cudaMalloc(&p->d_train, (size_t)cap * (WIDE * 64 + NARROW + 5) * sizeof(float)));
+        float* f = p->d_train;
+        auto wide = [&]() { float* r = f; f += cap * 64; return r; };
+        TrainBufs& t = p->tb;
+        t.e_h0 = wide(); t.e_xh0 = wide(); t.e_x0 = wide(); t.d_x0 = wide(); t.e_hh = wide(); t.e_xhh = wide();
+        t.d_hh = wide(); t.d_xhh = wide(); t.gX = wide(); t.gRep = wide(); t.gYa = wide(); t.gYb = wide();
+        for (int k = 0; k < 2; ++k) {
+            t.e_q[k] = wide(); t.e_y[k] = wide(); t.e_xh1[k] = wide(); t.e_m0[k] = wide(); t.e_xh2[k] = wide();
+            t.d_q1[k] = wide(); t.d_y1[k] = wide(); t.d_xh1[k] = wide(); t.d_y2[k] = wide(); t.d_xh2[k] = wide();
+            t.d_m0[k] = wide(); t.d_xh3[k] = wide();
+        }
+        auto narrow = [&](int w) { float* r = f; f += ((cap * w + 3) & ~3L); return r; };
+        t.e_rs0 = narrow(1); t.e_rsh = narrow(1); t.d_rsh = narrow(1); t.gDa = narrow(2); t.gDb = narrow(2);
+        for (int k = 0; k < 2; ++k) {
+            t.e_rs1[k] = narrow(1); t.e_rs2[k] = narrow(1); t.e_lse[k] = narrow(2);
+            t.d_rs1[k] = narrow(1); t.d_rs2[k] = narrow(1); t.d_rs3[k] = narrow(1); t.d_lse1[k] = narrow(2); t.d_lse2[k] = narrow(2);
+        }
+        p->train_cap = cap;
+    }
+    p->tb.on = 1;
+    return MATAS_OK;
+}
+
+/* MultiAgentTransformer.forward in training mode: as matas_policy_evaluate, and additionally keeps the
+ * activations the backward needs (until the next call on this handle that runs a forward). */
+extern "C" int matas_policy_evaluate_train(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
+                                           float* values, float* logp, float* entropy, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs && actions && values && logp && entropy && M > 0, "bad argument (M=%ld)", M);
+    const int L = p->cfg.n_agent;
+    if (L > 128) { matas_set_error("training supports n_agent <= 128 (got %d)", L); return MATAS_ERR_LIMIT; }
+    if ((rc = alloc_tokens(p, M * L))) return rc;
+    if ((rc = alloc_train(p, M * L))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, M, L, p->cfg.obs_dim, (cudaStream_t)stream, &p->tb))) return rc;
+    if ((rc = launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream, &p->tb))) return rc;
+    p->train_tokens = M * L;
+    return MATAS_OK;
+}
+
+/* loss.backward() through MultiAgentTransformer.forward (mat_trainer.py:146-147): given the
+ * gradients of the loss w.r.t. values / log-probs / entropies [M*L], ACCUMULATES the gradient w.r.t.
+ * every parameter into flat_grad (same layout as the flat parameter vector). */
+extern "C" int matas_policy_evaluate_backward(matas_policy* p, const float* obs, const float* ava, const float* actions,
+                                              long M, const float* d_values, const float* d_logp, const float* d_entropy,
+                                              float* flat_grad, void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs && actions && d_values && d_logp && d_entropy && flat_grad && M > 0, "bad argument (M=%ld)", M);
+    const int L = p->cfg.n_agent;
+    ARG_CHECK(p->train_tokens == M * L, "matas_policy_evaluate_backward must directly follow matas_policy_evaluate_train "
+              "with the same batch (saved %ld tokens, asked %ld)", p->train_tokens, M * L);
+    return launch_evaluate_backward(p->bufs, p->tb, p->gm, flat_grad, obs, actions, ava, d_values, d_logp, d_entropy, M, L,
+                                    p->cfg.obs_dim, p->cfg.mode, p->n_sm, (cudaStream_t)stream);
 }
 
 /* encoder only, exposing obs_rep (Encoder.forward, ma_transformer.py:141-154) */

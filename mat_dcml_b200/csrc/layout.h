@@ -35,6 +35,13 @@ constexpr int ENC_H0 = ENC_BLOBS + 2 * ENC_PER_BLOCK * BLOB;
 constexpr int DEC_STEP = ENC_H0 + BLOB;                             // DEC_STEP_BLOBS blobs in usage order
 constexpr int DEC_Q2 = DEC_STEP + DEC_STEP_BLOBS * BLOB;            // [2] blobs
 constexpr int TOTAL = DEC_Q2 + 2 * BLOB;
+// backward region: the same 34 Linear weights, untransposed ([out][in] = the [k][n] layout of dx = dy.W)
+constexpr int N_BLOBS = (TOTAL - ENC_BLOBS) / BLOB;       // 34
+constexpr int BW_BASE = TOTAL;
+constexpr int BW_MAT = 4096;
+constexpr int BW_BYTES = BW_MAT * 4;
+__host__ __device__ constexpr int bw(int blob_off) { return BW_BASE + ((blob_off - ENC_BLOBS) / BLOB) * BW_MAT; }
+constexpr int TOTAL_ALL = BW_BASE + N_BLOBS * BW_MAT;
 
 __host__ __device__ constexpr int enc_blob(int blk, int which) { return ENC_BLOBS + (blk * ENC_PER_BLOCK + which) * BLOB; }
 __host__ __device__ constexpr int dec_blob(int blk, int which) { return DEC_STEP + (blk * DEC_PER_BLOCK + which) * BLOB; }

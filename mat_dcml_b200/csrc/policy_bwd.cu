@@ -1,0 +1,937 @@
+// Backward pass of the teacher-forced MAT-AS forward (MultiAgentTransformer.forward,
+// mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:257-295) for sm_100a.  The reference gets
+// these gradients from torch autograd inside MATTrainer.ppo_update (mat_trainer.py:146-147); here
+// they are hand-written kernels that accumulate into ONE flat fp32 gradient vector laid out like
+// the flat parameter vector (state_dict order), which is also what the multi-GPU all-reduce sees.
+//
+// Structure: persistent CTAs walk 64-token tiles; weight gradients (dW = dY^T X) live in registers
+// across tiles and are flushed with atomics once per CTA; dX = dY W streams the untransposed
+// weights through the same TMA ring as the forward.  Attention backward recomputes probabilities
+// from the saved Q/K and log-sum-exp (query side for dQ, key side for dK/dV; D = rowsum(dY*Y)).
+#include <string.h>
+
+#include "policy_bwd.h"
+#include "tile.cuh"
+
+using namespace tile;
+
+namespace {
+
+constexpr float HALF_LOG_2PI = 0.91893853320467274178f;
+constexpr float MASK_LOGIT = -1e10f;
+constexpr float SCALE = 0.17677669529663687f;   // 1/sqrt(32)
+constexpr int BDEPTH = 3;
+
+struct BSmem {
+    float* ring;      // BDEPTH * BLOB
+    float* T[5];      // tiles [TM][XS]
+    float* sScore;    // TM*2*lpad
+    float* sSmall;    // 1024 floats
+    const float** p0; // per-row pointers
+    const float** p1;
+    int* r0;          // per-row ranges / metadata
+    int* r1;
+    long* env0;       // per-row first token of the env
+    uint64_t* bars;
+};
+
+__host__ __device__ inline size_t bsmem_bytes(int lpad) {
+    size_t f = (size_t)BDEPTH * lay::BLOB + 5 * TILE_F + (size_t)TM * 2 * lpad + 1024;
+    f = (f + 3) & ~(size_t)3;
+    return f * 4 + TM * 8 * 3 + TM * 4 * 2 + 8 * 8 + 32;
+}
+
+__device__ inline BSmem bcarve(unsigned char* base, int lpad) {
+    BSmem s;
+    float* f = reinterpret_cast<float*>(base);
+    s.ring = f; f += (size_t)BDEPTH * lay::BLOB;
+    for (int i = 0; i < 5; ++i) { s.T[i] = f; f += TILE_F; }
+    s.sSmall = f; f += 1024;
+    s.sScore = f; f += (size_t)TM * 2 * lpad;
+    uintptr_t p = (reinterpret_cast<uintptr_t>(f) + 15) & ~(uintptr_t)15;
+    s.bars = reinterpret_cast<uint64_t*>(p); p += 8 * 8;
+    s.p0 = reinterpret_cast<const float**>(p); p += TM * 8;
+    s.p1 = reinterpret_cast<const float**>(p); p += TM * 8;
+    s.env0 = reinterpret_cast<long*>(p); p += TM * 8;
+    s.r0 = reinterpret_cast<int*>(p); p += TM * 4;
+    s.r1 = reinterpret_cast<int*>(p);
+    return s;
+}
+
+// ---- register fragments: thread (rg, cg) owns rows 4rg..4rg+3, cols 4cg..4cg+3 of a tile --------
+struct Frag { float v[4][4]; };
+
+__device__ __forceinline__ void frag_load_g(Frag& f, const float* __restrict__ g, long row0, int n_valid, int rg, int cg) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = rg * 4 + i;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < n_valid) x = __ldcg(reinterpret_cast<const float4*>(g + (row0 + r) * 64 + cg * 4));
+        f.v[i][0] = x.x; f.v[i][1] = x.y; f.v[i][2] = x.z; f.v[i][3] = x.w;
+    }
+}
+__device__ __forceinline__ void frag_store_g(const Frag& f, float* __restrict__ g, long row0, int n_valid, int rg, int cg, bool add) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = rg * 4 + i;
+        if (r < n_valid) {
+            float4* p = reinterpret_cast<float4*>(g + (row0 + r) * 64 + cg * 4);
+            float4 x = make_float4(f.v[i][0], f.v[i][1], f.v[i][2], f.v[i][3]);
+            if (add) { const float4 o = *p; x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
+            *p = x;
+        }
+    }
+}
+__device__ __forceinline__ void frag_store_s(const Frag& f, float* __restrict__ t, int rg, int cg) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(t + (rg * 4 + i) * XS + cg * 4) = make_float4(f.v[i][0], f.v[i][1], f.v[i][2], f.v[i][3]);
+}
+__device__ __forceinline__ void frag_load_s(Frag& f, const float* __restrict__ t, int rg, int cg) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float4 x = *reinterpret_cast<const float4*>(t + (rg * 4 + i) * XS + cg * 4);
+        f.v[i][0] = x.x; f.v[i][1] = x.y; f.v[i][2] = x.z; f.v[i][3] = x.w;
+    }
+}
+__device__ __forceinline__ float4 ld4(const float* p, int cg) { return *reinterpret_cast<const float4*>(p + cg * 4); }
+__device__ __forceinline__ float f4(const float4& a, int j) { return j == 0 ? a.x : (j == 1 ? a.y : (j == 2 ? a.z : a.w)); }
+
+// column-sum accumulator (bias / LayerNorm parameter gradients): 4 columns per thread
+struct Col { float v[4]; __device__ void zero() { v[0] = v[1] = v[2] = v[3] = 0.f; } };
+__device__ __forceinline__ void col_add(Col& c, const Frag& f) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c.v[j] += f.v[0][j] + f.v[1][j] + f.v[2][j] + f.v[3][j];
+}
+__device__ __forceinline__ void col_add_mul(Col& c, const Frag& a, const Frag& b) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c.v[j] += a.v[0][j] * b.v[0][j] + a.v[1][j] * b.v[1][j] + a.v[2][j] * b.v[2][j] + a.v[3][j] * b.v[3][j];
+}
+__device__ __forceinline__ void col_flush(const Col& c, float* __restrict__ grad, int off, int cg) {
+    if (off < 0) return;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) atomicAdd(grad + off + cg * 4 + j, c.v[j]);
+}
+
+// weight-gradient accumulator: dW[4rg+i][4cg+j] += sum_t dY[t][4rg+i] * X[t][4cg+j]
+struct DW { float v[4][4]; __device__ void zero() { for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) v[i][j] = 0.f; } };
+__device__ __forceinline__ void dw_acc(DW& w, const float* __restrict__ dY, const float* __restrict__ X, int n_valid, int rg, int cg) {
+#pragma unroll 4
+    for (int t = 0; t < n_valid; ++t) {
+        const float4 a = *reinterpret_cast<const float4*>(dY + t * XS + rg * 4);
+        const float4 b = *reinterpret_cast<const float4*>(X + t * XS + cg * 4);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            w.v[i][0] = fmaf(av[i], b.x, w.v[i][0]); w.v[i][1] = fmaf(av[i], b.y, w.v[i][1]);
+            w.v[i][2] = fmaf(av[i], b.z, w.v[i][2]); w.v[i][3] = fmaf(av[i], b.w, w.v[i][3]);
+        }
+    }
+}
+__device__ __forceinline__ void dw_flush(const DW& w, float* __restrict__ grad, int off, int rg, int cg) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) atomicAdd(grad + off + (rg * 4 + i) * 64 + cg * 4 + j, w.v[i][j]);
+}
+
+// dX fragment = dY(tile in shared) . W (untransposed weights from the ring)
+__device__ __forceinline__ void gemm_dx(Ring& ring, const float* __restrict__ dY, Frag& out, int rg, int cg, bool accumulate) {
+    const float* W = ring.acquire();
+    float acc[4][4];
+    gemm(dY, W, acc, rg, cg);
+    ring.release();
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) out.v[i][j] = accumulate ? out.v[i][j] + acc[i][j] : acc[i][j];
+}
+
+// y = xhat * w + b (recompute a LayerNorm output from the saved normalised value)
+__device__ __forceinline__ void ln_affine(Frag& y, const Frag& xh, const float* __restrict__ lnw, const float* __restrict__ lnb, int cg) {
+    const float4 w = ld4(lnw, cg), b = ld4(lnb, cg);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) y.v[i][j] = xh.v[i][j] * f4(w, j) + f4(b, j);
+}
+
+// LayerNorm backward on a fragment.  dy -> dx (in place); accumulates d(weight), d(bias).
+__device__ __forceinline__ void ln_bwd(Frag& d, const Frag& xh, const float* __restrict__ rstd_g, long row0, int n_valid,
+                                       const float* __restrict__ lnw, Col& gw, Col& gb, int rg, int cg) {
+    col_add_mul(gw, d, xh);
+    col_add(gb, d);
+    const float4 w = ld4(lnw, cg);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = rg * 4 + i;
+        float g[4], s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { g[j] = d.v[i][j] * f4(w, j); s1 += g[j]; s2 += g[j] * xh.v[i][j]; }
+        s1 = half_warp_sum(s1) * (1.0f / 64.0f);
+        s2 = half_warp_sum(s2) * (1.0f / 64.0f);
+        const float rs = r < n_valid ? rstd_g[row0 + r] : 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) d.v[i][j] = rs * (g[j] - s1 - xh.v[i][j] * s2);
+    }
+}
+
+__device__ __forceinline__ float gelu_grad(float h) {
+    const float cdf = 0.5f * (1.0f + erff(h * 0.70710678118654752f));
+    return cdf + h * 0.3989422804014327f * expf(-0.5f * h * h);
+}
+__device__ __forceinline__ void gelu_bwd(Frag& d, const Frag& h) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) d.v[i][j] *= gelu_grad(h.v[i][j]);
+}
+__device__ __forceinline__ void gelu_fwd(Frag& g, const Frag& h) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g.v[i][j] = gelu_erf(h.v[i][j]);
+}
+
+// projection backward shared by every attention: dS (grad of the proj output, fragment) ->
+// dWp, dbp, dY = dS.Wp stored to gY, D = rowsum_head(dY * Y) stored to gD
+__device__ __forceinline__ void proj_bwd(Ring& ring, const BSmem& s, const Frag& dS, const float* __restrict__ Y_g,
+                                         float* __restrict__ gY, float* __restrict__ gD, long row0, int n_valid,
+                                         DW& dWp, Col& dbp, int rg, int cg) {
+    col_add(dbp, dS);
+    frag_store_s(dS, s.T[0], rg, cg);
+    Frag y;
+    frag_load_g(y, Y_g, row0, n_valid, rg, cg);
+    frag_store_s(y, s.T[1], rg, cg);
+    __syncthreads();
+    dw_acc(dWp, s.T[0], s.T[1], n_valid, rg, cg);
+    Frag dY;
+    gemm_dx(ring, s.T[0], dY, rg, cg, false);
+    frag_store_g(dY, gY, row0, n_valid, rg, cg, false);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float p = dY.v[i][0] * y.v[i][0] + dY.v[i][1] * y.v[i][1] + dY.v[i][2] * y.v[i][2] + dY.v[i][3] * y.v[i][3];
+        p += __shfl_xor_sync(0xffffffffu, p, 4);
+        p += __shfl_xor_sync(0xffffffffu, p, 2);
+        p += __shfl_xor_sync(0xffffffffu, p, 1);
+        const int r = rg * 4 + i;
+        if ((cg & 7) == 0 && r < n_valid) gD[(row0 + r) * 2 + (cg >> 3)] = p;
+    }
+    __syncthreads();
+    ring.prefetch();
+}
+
+struct TailArgs {
+    const float* gOut;     // grad wrt the block output
+    const float *xhF, *rsF, *m0, *xhM, *rsM, *Y;
+    int lnF, lnM;          // packed offsets of the forward blobs that hold these LayerNorm params
+    int seq[3];            // backward weight offsets: W2, W0, Wp   (with_mlp) or Wp only
+    int gW2, gb2, gW0, gb0, gWp, gbp, glnFw, glnFb, glnMw, glnMb;   // flat-gradient offsets
+    float* gRes; int res_add;
+    float *gY, *gD;
+    int with_mlp;
+};
+
+// [LN_F bwd -> MLP bwd ->] LN_M bwd -> residual grad -> projection bwd      (encoder E1, decoder K1 / K2b)
+__global__ void __launch_bounds__(NT, 1)
+bwd_mlp_proj(const float* __restrict__ packed, float* __restrict__ grad, TailArgs a, long n_tok, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BSmem s = bcarve(smem_raw, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long n_tiles = (n_tok + TM - 1) / TM;
+    long mine = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++mine;
+    int* sseq = reinterpret_cast<int*>(s.sSmall + 512);
+    const int nseq = a.with_mlp ? 3 : 1;
+    if (tid < nseq) sseq[tid] = a.with_mlp ? a.seq[tid] : a.seq[2];
+    for (int i = tid; i < 128; i += NT) {
+        s.sSmall[i] = packed[a.lnF + lay::B_LNW + i];        // lnF w | b
+        s.sSmall[128 + i] = packed[a.lnM + lay::B_LNW + i];  // lnM w | b
+    }
+    Ring ring;
+    ring.init(s.ring, s.bars, packed, sseq, nseq, (int)(mine * nseq), BDEPTH, lay::BW_BYTES);
+    __syncthreads();
+    ring.prefetch();
+    const float *lnFw = s.sSmall, *lnMw = s.sSmall + 128, *lnMb = s.sSmall + 192;
+    DW dW2, dW0, dWp; dW2.zero(); dW0.zero(); dWp.zero();
+    Col db2, db0, dbp, gFw, gFb, gMw, gMb;
+    db2.zero(); db0.zero(); dbp.zero(); gFw.zero(); gFb.zero(); gMw.zero(); gMb.zero();
+    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long row0 = tile * TM;
+        const int n_valid = (int)min((long)TM, n_tok - row0);
+        Frag d, xh;
+        frag_load_g(d, a.gOut, row0, n_valid, rg, cg);
+        if (a.with_mlp) {
+            frag_load_g(xh, a.xhF, row0, n_valid, rg, cg);
+            ln_bwd(d, xh, a.rsF, row0, n_valid, lnFw, gFw, gFb, rg, cg);            // d = dS (grad of x_M + mlp(x_M))
+            col_add(db2, d);
+            Frag h, g;
+            frag_load_g(h, a.m0, row0, n_valid, rg, cg);
+            gelu_fwd(g, h);
+            frag_store_s(d, s.T[0], rg, cg);
+            frag_store_s(g, s.T[1], rg, cg);
+            __syncthreads();
+            dw_acc(dW2, s.T[0], s.T[1], n_valid, rg, cg);
+            Frag dm;
+            gemm_dx(ring, s.T[0], dm, rg, cg, false);                                // dG = dS . W2
+            gelu_bwd(dm, h);                                                          // dM0
+            col_add(db0, dm);
+            frag_load_g(xh, a.xhM, row0, n_valid, rg, cg);
+            Frag xm;
+            ln_affine(xm, xh, lnMw, lnMb, cg);
+            frag_store_s(dm, s.T[2], rg, cg);
+            frag_store_s(xm, s.T[3], rg, cg);
+            __syncthreads();
+            ring.prefetch();
+            dw_acc(dW0, s.T[2], s.T[3], n_valid, rg, cg);
+            gemm_dx(ring, s.T[2], d, rg, cg, true);                                  // dX_M = dS + dM0 . W0
+        } else {
+            frag_load_g(xh, a.xhM, row0, n_valid, rg, cg);
+        }
+        ln_bwd(d, xh, a.rsM, row0, n_valid, lnMw, gMw, gMb, rg, cg);                 // d = grad of (residual + proj)
+        frag_store_g(d, a.gRes, row0, n_valid, rg, cg, a.res_add != 0);
+        __syncthreads();          // T[0]/T[1] free again (dw_acc above is done in every thread)
+        ring.prefetch();
+        proj_bwd(ring, s, d, a.Y, a.gY, a.gD, row0, n_valid, dWp, dbp, rg, cg);
+    }
+    if (a.with_mlp) {
+        dw_flush(dW2, grad, a.gW2, rg, cg); dw_flush(dW0, grad, a.gW0, rg, cg);
+        col_flush(db2, grad, a.gb2, cg); col_flush(db0, grad, a.gb0, cg);
+        col_flush(gFw, grad, a.glnFw, cg); col_flush(gFb, grad, a.glnFb, cg);
+    }
+    dw_flush(dWp, grad, a.gWp, rg, cg);
+    col_flush(dbp, grad, a.gbp, cg);
+    col_flush(gMw, grad, a.glnMw, cg); col_flush(gMb, grad, a.glnMb, cg);
+}
+
+// -------------------------------------------------------------------------------------------------
+// attention backward.  KIND 0: q, k, v all project the same input (encoder attention, decoder
+// self-attention); KIND 1: decoder cross-attention (q from obs_rep, k/v from the decoder stream).
+// -------------------------------------------------------------------------------------------------
+struct AttnArgs {
+    const float *Q, *K, *V, *lse, *gY, *gD;     // [tok][64] / [tok][2]
+    const float *xh, *rs;                       // saved LN whose output is the k/v (and, KIND 0, q) input
+    int ln;                                     // packed offset of the blob holding that LN (-1: input is `xin` as is)
+    const float* xin;                           // KIND 0 with ln < 0, or KIND 1 query input (obs_rep)
+    int seq[3];                                 // backward weights Wq, Wk, Wv
+    int gWq, gbq, gWk, gbk, gWv, gbv;
+    float* gX;                                  // KIND 0: += ; KIND 1: = (grad wrt the k/v input)
+    float* gRep;                                // KIND 1: += dq.Wq
+    int causal, L;
+};
+
+// scores for a tile of rows against the tokens [lo[r], hi[r]) of their env.
+// MODE 0 (query side): ds = p * (dY_r.V_t - D_r),  p = exp(scale q_r.K_t - lse_r)        rows are queries
+// MODE 1 (key side)  : p   = exp(scale Q_i.k_r - lse_i)                                   rows are keys
+// MODE 2 (key side)  : ds  = p * (dY_i.v_r - D_i)
+template <int MODE>
+__device__ __forceinline__ void score_pass(const BSmem& s, const AttnArgs& a, const float* __restrict__ tA,
+                                           const float* __restrict__ tB, int lpad, int span_max) {
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < TM * 2 * span_max; idx += NT) {
+        const int o = idx % span_max, rh = idx / span_max, r = rh >> 1, h = rh & 1;
+        const int t = s.r0[r] + o;
+        if (t < s.r1[r]) {
+            const long g = s.env0[r] + t;
+            const float4* ap = reinterpret_cast<const float4*>(tA + r * XS + h * 32);
+            float s1 = 0.f, s2 = 0.f;
+            if (MODE == 0) {
+                const float4* kp = reinterpret_cast<const float4*>(a.K + g * 64 + h * 32);
+                const float4* vp = reinterpret_cast<const float4*>(a.V + g * 64 + h * 32);
+                const float4* bp = reinterpret_cast<const float4*>(tB + r * XS + h * 32);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 k = __ldcg(kp + i), v = __ldcg(vp + i), q = ap[i], dy = bp[i];
+                    s1 += q.x * k.x + q.y * k.y + q.z * k.z + q.w * k.w;
+                    s2 += dy.x * v.x + dy.y * v.y + dy.z * v.z + dy.w * v.w;
+                }
+                const float p = expf(s1 * SCALE - s.sSmall[768 + rh]);
+                s.sScore[rh * lpad + o] = p * (s2 - s.sSmall[896 + rh]);
+            } else {
+                const float4* qp = reinterpret_cast<const float4*>(a.Q + g * 64 + h * 32);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 q = __ldcg(qp + i), k = ap[i];
+                    s1 += q.x * k.x + q.y * k.y + q.z * k.z + q.w * k.w;
+                }
+                const float p = expf(s1 * SCALE - __ldcg(a.lse + g * 2 + h));
+                if (MODE == 1) {
+                    s.sScore[rh * lpad + o] = p;
+                } else {
+                    const float4* dp = reinterpret_cast<const float4*>(a.gY + g * 64 + h * 32);
+                    const float4* vp = reinterpret_cast<const float4*>(tB + r * XS + h * 32);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 dy = __ldcg(dp + i), v = vp[i];
+                        s2 += dy.x * v.x + dy.y * v.y + dy.z * v.z + dy.w * v.w;
+                    }
+                    s.sScore[rh * lpad + o] = p * (s2 - __ldcg(a.gD + g * 2 + h));
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// out[r][h*32+d] = mul * sum_o score[r][h][o] * src[env0[r] + r0[r] + o][h*32+d]
+__device__ __forceinline__ void weighted_sum(const BSmem& s, const float* __restrict__ src, float* __restrict__ out, int lpad, float mul) {
+    for (int idx = threadIdx.x; idx < TM * 2 * 8; idx += NT) {
+        const int dq = idx & 7, rh = idx >> 3, r = rh >> 1, h = rh & 1;
+        const int n = s.r1[r] - s.r0[r];
+        const float* sc = s.sScore + rh * lpad;
+        const float* vp = src + (s.env0[r] + s.r0[r]) * 64 + h * 32 + dq * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int t = 0;
+        for (; t + 4 <= n; t += 4) {
+            float4 v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(vp + (long)(t + i) * 64));
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float p = sc[t + i];
+                acc.x = fmaf(p, v[i].x, acc.x); acc.y = fmaf(p, v[i].y, acc.y); acc.z = fmaf(p, v[i].z, acc.z); acc.w = fmaf(p, v[i].w, acc.w);
+            }
+        }
+        for (; t < n; ++t) {
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(vp + (long)t * 64));
+            const float p = sc[t];
+            acc.x = fmaf(p, v.x, acc.x); acc.y = fmaf(p, v.y, acc.y); acc.z = fmaf(p, v.z, acc.z); acc.w = fmaf(p, v.w, acc.w);
+        }
+        *reinterpret_cast<float4*>(out + r * XS + h * 32 + dq * 4) = make_float4(acc.x * mul, acc.y * mul, acc.z * mul, acc.w * mul);
+    }
+    __syncthreads();
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(NT, 1)
+bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a, long n_tok, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BSmem s = bcarve(smem_raw, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const int L = a.L;
+    const long n_tiles = (n_tok + TM - 1) / TM;
+    long mine = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++mine;
+    int* sseq = reinterpret_cast<int*>(s.sSmall + 512);
+    if (tid < 3) sseq[tid] = a.seq[tid];
+    if (a.ln >= 0) for (int i = tid; i < 128; i += NT) s.sSmall[i] = packed[a.ln + lay::B_LNW + i];
+    Ring ring;
+    ring.init(s.ring, s.bars, packed, sseq, 3, (int)(mine * 3), BDEPTH, lay::BW_BYTES);
+    __syncthreads();
+    ring.prefetch();
+    DW dWq, dWk, dWv; dWq.zero(); dWk.zero(); dWv.zero();
+    Col dbq, dbk, dbv; dbq.zero(); dbk.zero(); dbv.zero();
+    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long row0 = tile * TM;
+        const int n_valid = (int)min((long)TM, n_tok - row0);
+        // ---- query side: dq -------------------------------------------------------------------
+        if (tid < TM) {
+            const long g = row0 + tid;
+            int lo = 0, hi = 0; long e0 = 0;
+            if (g < n_tok) {
+                const long env = g / L; const int pos = (int)(g - env * L);
+                e0 = env * L; lo = 0; hi = a.causal ? pos + 1 : L;
+            }
+            s.r0[tid] = lo; s.r1[tid] = hi; s.env0[tid] = e0;
+        }
+        if (tid < TM * 2) {
+            const long g = row0 + (tid >> 1);
+            s.sSmall[768 + tid] = g < n_tok ? a.lse[g * 2 + (tid & 1)] : 0.f;
+            s.sSmall[896 + tid] = g < n_tok ? a.gD[g * 2 + (tid & 1)] : 0.f;
+        }
+        load_tile(s.T[0], a.Q + row0 * 64, 64, n_valid);
+        load_tile(s.T[1], a.gY + row0 * 64, 64, n_valid);
+        __syncthreads();
+        score_pass<0>(s, a, s.T[0], s.T[1], lpad, L);
+        weighted_sum(s, a.K, s.T[2], lpad, SCALE);                    // dq -> T2
+        // ---- key side: dv, dk ------------------------------------------------------------------
+        if (tid < TM) {
+            const long g = row0 + tid;
+            int lo = 0, hi = 0;
+            if (g < n_tok) { const int pos = (int)(g - s.env0[tid]); lo = a.causal ? pos : 0; hi = L; }
+            s.r0[tid] = lo; s.r1[tid] = hi;
+        }
+        load_tile(s.T[0], a.K + row0 * 64, 64, n_valid);
+        load_tile(s.T[1], a.V + row0 * 64, 64, n_valid);
+        __syncthreads();
+        score_pass<1>(s, a, s.T[0], s.T[1], lpad, L);
+        weighted_sum(s, a.gY, s.T[3], lpad, 1.0f);                    // dv -> T3
+        score_pass<2>(s, a, s.T[0], s.T[1], lpad, L);
+        weighted_sum(s, a.Q, s.T[4], lpad, SCALE);                    // dk -> T4
+        // ---- projections: dW, db, dX -------------------------------------------------------------
+        Frag xin, fq, fk, fv, dx;
+        if (a.ln >= 0) {
+            Frag xh;
+            frag_load_g(xh, a.xh, row0, n_valid, rg, cg);
+            ln_affine(xin, xh, s.sSmall, s.sSmall + 64, cg);
+        } else {
+            frag_load_g(xin, a.xin, row0, n_valid, rg, cg);
+        }
+        frag_store_s(xin, s.T[0], rg, cg);                             // k/v (and KIND 0: q) input
+        if (KIND == 1) load_tile(s.T[1], a.xin + row0 * 64, 64, n_valid);   // obs_rep: q input
+        frag_load_s(fq, s.T[2], rg, cg); frag_load_s(fv, s.T[3], rg, cg); frag_load_s(fk, s.T[4], rg, cg);
+        col_add(dbq, fq); col_add(dbk, fk); col_add(dbv, fv);
+        __syncthreads();
+        dw_acc(dWq, s.T[2], KIND == 1 ? s.T[1] : s.T[0], n_valid, rg, cg);
+        dw_acc(dWk, s.T[4], s.T[0], n_valid, rg, cg);
+        dw_acc(dWv, s.T[3], s.T[0], n_valid, rg, cg);
+        if (KIND == 0) {
+            gemm_dx(ring, s.T[2], dx, rg, cg, false);
+            gemm_dx(ring, s.T[4], dx, rg, cg, true);
+            gemm_dx(ring, s.T[3], dx, rg, cg, true);
+            frag_store_g(dx, a.gX, row0, n_valid, rg, cg, true);
+        } else {
+            gemm_dx(ring, s.T[2], dx, rg, cg, false);
+            frag_store_g(dx, a.gRep, row0, n_valid, rg, cg, true);
+            gemm_dx(ring, s.T[4], dx, rg, cg, false);
+            gemm_dx(ring, s.T[3], dx, rg, cg, true);
+            frag_store_g(dx, a.gX, row0, n_valid, rg, cg, false);
+        }
+        __syncthreads();
+        ring.prefetch();
+    }
+    dw_flush(dWq, grad, a.gWq, rg, cg); dw_flush(dWk, grad, a.gWk, rg, cg); dw_flush(dWv, grad, a.gWv, rg, cg);
+    col_flush(dbq, grad, a.gbq, cg); col_flush(dbk, grad, a.gbk, cg); col_flush(dbv, grad, a.gbv, cg);
+}
+
+// -------------------------------------------------------------------------------------------------
+// heads.  DEC: (d_logp, d_entropy) -> logits head backward -> gX (grad of the last decoder block output)
+//         ENC: d_values -> value head backward -> gRep += (grad of obs_rep)
+// -------------------------------------------------------------------------------------------------
+struct HeadArgs {
+    const float *d_a, *d_b;          // DEC: d_logp, d_entropy [tok];  ENC: d_values [tok], unused
+    const float *actions, *ava;      // DEC only
+    const float *hh, *xhh, *rsh;     // saved pre-GELU, LN xhat, rstd
+    const float *xh_in, *rs_in;      // DEC: LN3 of block 1 (its output is the head input); ENC: null (input = rep)
+    const float* rep;                // ENC head input
+    int ln_in;                       // DEC: packed blob offset holding LN3 params
+    int blob_h0;                     // forward blob of head.0 (holds head.2 LN params); backward weight via lay::bw
+    int h3;                          // packed offset of the head.3 group
+    int gW0, gb0, glnw, glnb, gW3, gb3, glogstd;
+    float* gOut;                     // DEC: gX (store); ENC: gRep (add)
+    int L, n_disc;
+};
+
+template <int DEC>
+__global__ void __launch_bounds__(NT, 1)
+bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a, long n_tok, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BSmem s = bcarve(smem_raw, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long n_tiles = (n_tok + TM - 1) / TM;
+    long mine = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++mine;
+    int* sseq = reinterpret_cast<int*>(s.sSmall + 512);
+    if (tid == 0) sseq[0] = lay::bw(a.blob_h0);
+    for (int i = tid; i < 128; i += NT) {
+        s.sSmall[i] = packed[a.blob_h0 + lay::B_LNW + i];                  // head.2 LN w | b
+        if (DEC) s.sSmall[128 + i] = packed[a.ln_in + lay::B_LNW + i];     // LN3 w | b
+    }
+    for (int i = tid; i < (DEC ? lay::DEC_H3_SIZE : lay::ENC_H3_SIZE); i += NT) s.sSmall[256 + i] = packed[a.h3 + i];
+    Ring ring;
+    ring.init(s.ring, s.bars, packed, sseq, 1, (int)mine, BDEPTH, lay::BW_BYTES);
+    __syncthreads();
+    ring.prefetch();
+    const float* w3 = s.sSmall + 256;     // DEC: w0[64] w1[64] b[2] log_std[2];  ENC: w[64] b[1]
+    float* sdl = s.sSmall + 640;          // [TM][2] d(logits) / d(value)
+    DW dW0; dW0.zero();
+    Col db0, glw, glb, gw3a, gw3b; db0.zero(); glw.zero(); glb.zero(); gw3a.zero(); gw3b.zero();
+    float gb3a = 0.f, gb3b = 0.f, gls = 0.f;
+    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long row0 = tile * TM;
+        const int n_valid = (int)min((long)TM, n_tok - row0);
+        Frag xh, nh;
+        frag_load_g(xh, a.xhh, row0, n_valid, rg, cg);
+        ln_affine(nh, xh, s.sSmall, s.sSmall + 64, cg);
+        frag_store_s(nh, s.T[0], rg, cg);
+        __syncthreads();
+        if (tid < TM) {
+            float dl0 = 0.f, dl1 = 0.f;
+            if (tid < n_valid) {
+                const long g = row0 + tid;
+                if (DEC) {
+                    float l0 = row_dot(s.T[0], tid, w3) + w3[lay::DEC_H3_B];
+                    float l1 = row_dot(s.T[0], tid, w3 + 64) + w3[lay::DEC_H3_B + 1];
+                    const float dlp = a.d_a[g], dent = a.d_b[g], act = a.actions[g];
+                    const int pos = (int)(g % a.L);
+                    if (pos < a.n_disc) {
+                        bool m0 = false, m1 = false;
+                        if (a.ava) { m0 = a.ava[g * 2] == 0.f; m1 = a.ava[g * 2 + 1] == 0.f; }
+                        if (m0) l0 = MASK_LOGIT;
+                        if (m1) l1 = MASK_LOGIT;
+                        const float mx = fmaxf(l0, l1);
+                        const float lse = mx + logf(expf(l0 - mx) + expf(l1 - mx));
+                        const float z0 = l0 - lse, z1 = l1 - lse, p0 = expf(z0), p1 = expf(z1);
+                        const float c0 = fmaxf(z0, -3.4028234663852886e38f), c1 = fmaxf(z1, -3.4028234663852886e38f);
+                        const float H = -(p0 * c0 + p1 * c1);
+                        const int ai = act != 0.f;
+                        // d logp/dl_c = [c==a] - p_c ;  dH/dl_c = -p_c (z_c + H)
+                        dl0 = dlp * ((ai == 0 ? 1.f : 0.f) - p0) + dent * (-p0 * (c0 + H));
+                        dl1 = dlp * ((ai == 1 ? 1.f : 0.f) - p1) + dent * (-p1 * (c1 + H));
+                        if (m0) dl0 = 0.f;       // masked logits were overwritten: no gradient reaches them
+                        if (m1) dl1 = 0.f;
+                    } else {
+                        const float sg = 1.0f / (1.0f + expf(-w3[lay::DEC_H3_LOGSTD + 1]));
+                        const float sd = 0.5f * sg;
+                        const float dd = act - l1;
+                        dl1 = dlp * dd / (sd * sd);
+                        gls += (dlp * (dd * dd / (sd * sd) - 1.0f) + dent) * (1.0f - sg);
+                    }
+                } else {
+                    dl0 = a.d_a[g];
+                }
+            }
+            sdl[tid * 2] = dl0; sdl[tid * 2 + 1] = dl1;
+            gb3a += dl0; gb3b += dl1;
+        }
+        __syncthreads();
+        // d(head.3 weight) and d(nh)
+        Frag d;
+        const float4 wa = ld4(w3, cg), wb = DEC ? ld4(w3 + 64, cg) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = rg * 4 + i;
+            const float a0 = sdl[r * 2], a1 = sdl[r * 2 + 1];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                gw3a.v[j] += a0 * nh.v[i][j];
+                gw3b.v[j] += a1 * nh.v[i][j];
+                d.v[i][j] = a0 * f4(wa, j) + a1 * f4(wb, j);
+            }
+        }
+        ln_bwd(d, xh, a.rsh, row0, n_valid, s.sSmall, glw, glb, rg, cg);
+        Frag h;
+        frag_load_g(h, a.hh, row0, n_valid, rg, cg);
+        gelu_bwd(d, h);                                                    // d = d(pre-GELU of head.0)
+        col_add(db0, d);
+        Frag xin;
+        if (DEC) {
+            frag_load_g(xh, a.xh_in, row0, n_valid, rg, cg);
+            ln_affine(xin, xh, s.sSmall + 128, s.sSmall + 192, cg);
+        } else {
+            frag_load_g(xin, a.rep, row0, n_valid, rg, cg);
+        }
+        frag_store_s(d, s.T[1], rg, cg);
+        frag_store_s(xin, s.T[2], rg, cg);
+        __syncthreads();
+        dw_acc(dW0, s.T[1], s.T[2], n_valid, rg, cg);
+        Frag dx;
+        gemm_dx(ring, s.T[1], dx, rg, cg, false);
+        frag_store_g(dx, a.gOut, row0, n_valid, rg, cg, DEC ? false : true);
+        __syncthreads();
+        ring.prefetch();
+    }
+    dw_flush(dW0, grad, a.gW0, rg, cg);
+    col_flush(db0, grad, a.gb0, cg); col_flush(glw, grad, a.glnw, cg); col_flush(glb, grad, a.glnb, cg);
+    col_flush(gw3a, grad, a.gW3, cg);
+    if (DEC) col_flush(gw3b, grad, a.gW3 + 64, cg);
+    if (tid < TM) {
+        atomicAdd(grad + a.gb3, gb3a);
+        if (DEC) { atomicAdd(grad + a.gb3 + 1, gb3b); if (a.glogstd >= 0) atomicAdd(grad + a.glogstd + 1, gls); }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// embeddings
+// -------------------------------------------------------------------------------------------------
+struct EmbArgs {
+    const float* gX;                  // grad wrt the embedding output
+    const float *h0, *xh0, *rs0;      // ENC saved; DEC recomputed from the action code
+    const float* obs; int obs_dim;    // ENC
+    const float* actions; int L;      // DEC
+    int gln_w, gln_b, gW, gb, gln7_w, gln7_b;
+};
+
+// encoder: x0 = LN(GELU(W_obs . LN7(obs) + b))      (ma_transformer.py:133-136,148-151)
+__global__ void __launch_bounds__(NT, 1)
+bwd_embed_enc(const float* __restrict__ packed, float* __restrict__ grad, EmbArgs a, long n_tok, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BSmem s = bcarve(smem_raw, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long n_tiles = (n_tok + TM - 1) / TM;
+    for (int i = tid; i < lay::ENC_EMB_SIZE; i += NT) s.sSmall[i] = packed[lay::ENC_EMB + i];
+    __syncthreads();
+    float* sO = s.T[1];       // [TM][8] LN7 output
+    float* sOh = s.T[2];      // [TM][8] LN7 normalised
+    const int od = a.obs_dim;
+    Col glw, glb, gb; glw.zero(); glb.zero(); gb.zero();
+    float accW[2] = {0.f, 0.f};       // dW_obs entries (c, k) = (idx/8, idx%8), idx = tid, tid+256
+    float acc7w = 0.f, acc7b = 0.f;   // tid < 8: LN7 weight / bias grads
+    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long row0 = tile * TM;
+        const int n_valid = (int)min((long)TM, n_tok - row0);
+        if (tid < TM) {
+            float v[8], mean = 0.f;
+            for (int k = 0; k < 8; ++k) { v[k] = (k < od && tid < n_valid) ? a.obs[(row0 + tid) * od + k] : 0.f; mean += v[k]; }
+            mean /= (float)od;
+            float var = 0.f;
+            for (int k = 0; k < od; ++k) var += (v[k] - mean) * (v[k] - mean);
+            const float rs = rsqrtf(var / (float)od + 1e-5f);
+            for (int k = 0; k < 8; ++k) {
+                const float xh = k < od ? (v[k] - mean) * rs : 0.f;
+                sOh[tid * 8 + k] = xh;
+                sO[tid * 8 + k] = k < od ? xh * s.sSmall[lay::ENC_EMB_LNW + k] + s.sSmall[lay::ENC_EMB_LNB + k] : 0.f;
+            }
+        }
+        Frag d, xh, h;
+        frag_load_g(d, a.gX, row0, n_valid, rg, cg);
+        frag_load_g(xh, a.xh0, row0, n_valid, rg, cg);
+        ln_bwd(d, xh, a.rs0, row0, n_valid, s.sSmall + lay::ENC_EMB_LN2W, glw, glb, rg, cg);
+        frag_load_g(h, a.h0, row0, n_valid, rg, cg);
+        gelu_bwd(d, h);
+        col_add(gb, d);
+        frag_store_s(d, s.T[0], rg, cg);
+        __syncthreads();
+        for (int q = 0; q < 2; ++q) {
+            const int idx = tid + q * NT, c = idx >> 3, k = idx & 7;
+            float acc = 0.f;
+            for (int r = 0; r < n_valid; ++r) acc += s.T[0][r * XS + c] * sO[r * 8 + k];
+            accW[q] += acc;
+        }
+        // LN7 parameter grads: do7[r][k] = sum_c dh0[r][c] Wobs[c][k]
+        for (int idx = tid; idx < TM * 8; idx += NT) {
+            const int r = idx >> 3, k = idx & 7;
+            float acc = 0.f;
+            if (r < n_valid && k < od) for (int c = 0; c < 64; ++c) acc += s.T[0][r * XS + c] * s.sSmall[lay::ENC_EMB_WT + k * 64 + c];
+            s.T[3][idx] = acc;
+        }
+        __syncthreads();
+        if (tid < 8) for (int r = 0; r < n_valid; ++r) { acc7w += s.T[3][r * 8 + tid] * sOh[r * 8 + tid]; acc7b += s.T[3][r * 8 + tid]; }
+        __syncthreads();
+    }
+    col_flush(glw, grad, a.gln_w, cg); col_flush(glb, grad, a.gln_b, cg); col_flush(gb, grad, a.gb, cg);
+    for (int q = 0; q < 2; ++q) {
+        const int idx = tid + q * NT, c = idx >> 3, k = idx & 7;
+        if (k < od) atomicAdd(grad + a.gW + c * od + k, accW[q]);
+    }
+    if (tid < od) { atomicAdd(grad + a.gln7_w + tid, acc7w); atomicAdd(grad + a.gln7_b + tid, acc7b); }
+}
+
+// decoder: x0 = LN(GELU(W_a . shifted))   (ma_transformer.py:224-225); shifted row = start flag | one-hot(prev action)
+__global__ void __launch_bounds__(NT, 1)
+bwd_embed_dec(const float* __restrict__ packed, float* __restrict__ grad, EmbArgs a, long n_tok, int lpad) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BSmem s = bcarve(smem_raw, lpad);
+    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
+    const long n_tiles = (n_tok + TM - 1) / TM;
+    // tables for the 3 reachable token codes (1 start, 2 action 0, 3 action 1): pre-GELU a, xhat, rstd
+    float* tA = s.sSmall;             // [4][64]
+    float* tXh = s.sSmall + 256;      // [4][64]
+    float* tRs = s.sSmall + 512;      // [4]
+    float* lnw = s.sSmall + 520;      // [64]
+    int* sCode = reinterpret_cast<int*>(s.sSmall + 600);
+    if (tid < 64) {
+        const int c = tid >> 4, cg2 = tid & 15;                 // code index c -> code c+1 ... use c in 0..3 (0 unused)
+        const float* Wt = packed + lay::DEC_EMB + lay::DEC_EMB_WT;
+        float v[4], pre[4];
+        for (int i = 0; i < 4; ++i) {
+            const int col = cg2 * 4 + i;
+            pre[i] = c == 1 ? Wt[col] : (c == 2 ? Wt[64 + col] : (c == 3 ? Wt[128 + col] : 0.f));
+            v[i] = gelu_erf(pre[i]);
+        }
+        const float mean = half_warp_sum(v[0] + v[1] + v[2] + v[3]) * (1.0f / 64.0f);
+        float var = 0.f;
+        for (int i = 0; i < 4; ++i) { v[i] -= mean; var += v[i] * v[i]; }
+        var = half_warp_sum(var) * (1.0f / 64.0f);
+        const float rs = rsqrtf(var + 1e-5f);
+        for (int i = 0; i < 4; ++i) { tA[c * 64 + cg2 * 4 + i] = pre[i]; tXh[c * 64 + cg2 * 4 + i] = v[i] * rs; }
+        if (cg2 == 0) tRs[c] = rs;
+        lnw[tid] = packed[lay::DEC_EMB + lay::DEC_EMB_LNW + tid];
+    }
+    __syncthreads();
+    Col glw, glb, gw0, gw1, gw2; glw.zero(); glb.zero(); gw0.zero(); gw1.zero(); gw2.zero();
+    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long row0 = tile * TM;
+        const int n_valid = (int)min((long)TM, n_tok - row0);
+        if (tid < TM) {
+            const long g = row0 + tid;
+            int code = 0;
+            if (g < n_tok) code = (g % a.L) == 0 ? 1 : (a.actions[g - 1] != 0.f ? 3 : 2);
+            sCode[tid] = code;
+        }
+        __syncthreads();
+        Frag d, xh, h;
+        frag_load_g(d, a.gX, row0, n_valid, rg, cg);
+        float rsl[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int code = sCode[rg * 4 + i];
+            rsl[i] = tRs[code];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { xh.v[i][j] = tXh[code * 64 + cg * 4 + j]; h.v[i][j] = tA[code * 64 + cg * 4 + j]; }
+        }
+        // LN backward with per-row rstd from the table
+        col_add_mul(glw, d, xh); col_add(glb, d);
+        const float4 w = ld4(lnw, cg);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float gv[4], s1 = 0.f, s2 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { gv[j] = d.v[i][j] * f4(w, j); s1 += gv[j]; s2 += gv[j] * xh.v[i][j]; }
+            s1 = half_warp_sum(s1) * (1.0f / 64.0f);
+            s2 = half_warp_sum(s2) * (1.0f / 64.0f);
+            const float rs = (rg * 4 + i) < n_valid ? rsl[i] : 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) d.v[i][j] = rs * (gv[j] - s1 - xh.v[i][j] * s2);
+        }
+        gelu_bwd(d, h);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int code = sCode[rg * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (code == 1) gw0.v[j] += d.v[i][j];
+                else if (code == 2) gw1.v[j] += d.v[i][j];
+                else if (code == 3) gw2.v[j] += d.v[i][j];
+            }
+        }
+        __syncthreads();
+    }
+    col_flush(glw, grad, a.gln_w, cg); col_flush(glb, grad, a.gln_b, cg);
+    // action_encoder.0.weight is [64][3] row-major: element (col, k) at col*3 + k
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int col = cg * 4 + j;
+        atomicAdd(grad + a.gW + col * 3 + 0, gw0.v[j]);
+        atomicAdd(grad + a.gW + col * 3 + 1, gw1.v[j]);
+        atomicAdd(grad + a.gW + col * 3 + 2, gw2.v[j]);
+    }
+}
+
+template <typename K>
+int set_smem(K kernel, size_t bytes) {
+    CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return MATAS_OK;
+}
+
+}  // namespace
+
+// -------------------------------------------------------------------------------------------------
+// host orchestration
+// -------------------------------------------------------------------------------------------------
+int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const GradMap& gm, float* grad, const float* obs,
+                             const float* actions, const float* ava, const float* d_values, const float* d_logp,
+                             const float* d_ent, long M, int L, int obs_dim, int mode, int n_sm, cudaStream_t st) {
+    if (L > 128) {
+        matas_set_error("evaluate backward supports n_agent <= 128 (got %d)", L);
+        return MATAS_ERR_LIMIT;
+    }
+    const int lpad = L | 1;
+    const size_t bytes = bsmem_bytes(lpad);
+    const long n_tok = M * L;
+    const long n_tiles = (n_tok + TM - 1) / TM;
+    const unsigned grid = (unsigned)(n_tiles < n_sm ? n_tiles : n_sm);
+    int rc;
+    if ((rc = set_smem(bwd_mlp_proj, bytes)) || (rc = set_smem(bwd_attn<0>, bytes)) || (rc = set_smem(bwd_attn<1>, bytes)) ||
+        (rc = set_smem(bwd_head<0>, bytes)) || (rc = set_smem(bwd_head<1>, bytes)) || (rc = set_smem(bwd_embed_enc, bytes)) ||
+        (rc = set_smem(bwd_embed_dec, bytes)))
+        return rc;
+    const float* pk = b.w;
+    using namespace lay;
+    auto idx = [](int blob) { return (blob - ENC_BLOBS) / BLOB; };
+    CUDA_TRY(cudaMemsetAsync(t.gRep, 0, (size_t)n_tok * 64 * sizeof(float), st));
+
+    // ---- decoder ---------------------------------------------------------------------------------
+    {
+        HeadArgs h = {};
+        h.d_a = d_logp; h.d_b = d_ent; h.actions = actions; h.ava = ava;
+        h.hh = t.d_hh; h.xhh = t.d_xhh; h.rsh = t.d_rsh; h.xh_in = t.d_xh3[1]; h.rs_in = t.d_rs3[1];
+        h.ln_in = dec_blob(1, DM2); h.blob_h0 = DEC_H0; h.h3 = DEC_H3;
+        h.gW0 = gm.w[idx(DEC_H0)]; h.gb0 = gm.b[idx(DEC_H0)]; h.glnw = gm.lnw[idx(DEC_H0)]; h.glnb = gm.lnb[idx(DEC_H0)];
+        h.gW3 = gm.dec_h3_w; h.gb3 = gm.dec_h3_b; h.glogstd = gm.log_std;
+        h.gOut = t.gX; h.L = L; h.n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
+        bwd_head<1><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok, lpad);
+    }
+    for (int k = 1; k >= 0; --k) {
+        TailArgs ta = {};
+        ta.gOut = t.gX; ta.xhF = t.d_xh3[k]; ta.rsF = t.d_rs3[k]; ta.m0 = t.d_m0[k]; ta.xhM = t.d_xh2[k]; ta.rsM = t.d_rs2[k];
+        ta.Y = t.d_y2[k]; ta.lnF = dec_blob(k, DM2); ta.lnM = dec_blob(k, DP2);
+        ta.seq[0] = bw(dec_blob(k, DM2)); ta.seq[1] = bw(dec_blob(k, DM0)); ta.seq[2] = bw(dec_blob(k, DP2));
+        ta.gW2 = gm.w[idx(dec_blob(k, DM2))]; ta.gb2 = gm.b[idx(dec_blob(k, DM2))];
+        ta.gW0 = gm.w[idx(dec_blob(k, DM0))]; ta.gb0 = gm.b[idx(dec_blob(k, DM0))];
+        ta.gWp = gm.w[idx(dec_blob(k, DP2))]; ta.gbp = gm.b[idx(dec_blob(k, DP2))];
+        ta.glnFw = gm.lnw[idx(dec_blob(k, DM2))]; ta.glnFb = gm.lnb[idx(dec_blob(k, DM2))];
+        ta.glnMw = gm.lnw[idx(dec_blob(k, DP2))]; ta.glnMb = gm.lnb[idx(dec_blob(k, DP2))];
+        ta.gRes = t.gRep; ta.res_add = 1; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
+        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok, lpad);
+
+        AttnArgs a2 = {};
+        a2.Q = b.Q2[k]; a2.K = b.K2[k]; a2.V = b.V2[k]; a2.lse = t.d_lse2[k]; a2.gY = t.gYa; a2.gD = t.gDa;
+        a2.xh = t.d_xh1[k]; a2.rs = t.d_rs1[k]; a2.ln = dec_blob(k, DP1); a2.xin = b.rep;
+        a2.seq[0] = bw(dec_q2(k)); a2.seq[1] = bw(dec_blob(k, DK2)); a2.seq[2] = bw(dec_blob(k, DV2));
+        a2.gWq = gm.w[idx(dec_q2(k))]; a2.gbq = gm.b[idx(dec_q2(k))];
+        a2.gWk = gm.w[idx(dec_blob(k, DK2))]; a2.gbk = gm.b[idx(dec_blob(k, DK2))];
+        a2.gWv = gm.w[idx(dec_blob(k, DV2))]; a2.gbv = gm.b[idx(dec_blob(k, DV2))];
+        a2.gX = t.gX; a2.gRep = t.gRep; a2.causal = 1; a2.L = L;
+        bwd_attn<1><<<grid, NT, bytes, st>>>(pk, grad, a2, n_tok, lpad);       // gX = grad wrt x1 (LN1 output)
+
+        TailArgs tb = {};
+        tb.gOut = t.gX; tb.xhM = t.d_xh1[k]; tb.rsM = t.d_rs1[k]; tb.Y = t.d_y1[k];
+        tb.lnF = dec_blob(k, DP1); tb.lnM = dec_blob(k, DP1);
+        tb.seq[2] = bw(dec_blob(k, DP1));
+        tb.gWp = gm.w[idx(dec_blob(k, DP1))]; tb.gbp = gm.b[idx(dec_blob(k, DP1))];
+        tb.glnMw = gm.lnw[idx(dec_blob(k, DP1))]; tb.glnMb = gm.lnb[idx(dec_blob(k, DP1))];
+        tb.gRes = t.gX; tb.res_add = 0; tb.gY = t.gYb; tb.gD = t.gDb; tb.with_mlp = 0;
+        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, tb, n_tok, lpad);       // gX = grad wrt block input (residual part)
+
+        AttnArgs a1 = {};
+        a1.Q = t.d_q1[k]; a1.K = b.K1[k]; a1.V = b.V1[k]; a1.lse = t.d_lse1[k]; a1.gY = t.gYb; a1.gD = t.gDb;
+        if (k == 1) { a1.xh = t.d_xh3[0]; a1.rs = t.d_rs3[0]; a1.ln = dec_blob(0, DM2); }
+        else { a1.ln = -1; a1.xin = t.d_x0; }
+        a1.seq[0] = bw(dec_blob(k, DQ1)); a1.seq[1] = bw(dec_blob(k, DK1)); a1.seq[2] = bw(dec_blob(k, DV1));
+        a1.gWq = gm.w[idx(dec_blob(k, DQ1))]; a1.gbq = gm.b[idx(dec_blob(k, DQ1))];
+        a1.gWk = gm.w[idx(dec_blob(k, DK1))]; a1.gbk = gm.b[idx(dec_blob(k, DK1))];
+        a1.gWv = gm.w[idx(dec_blob(k, DV1))]; a1.gbv = gm.b[idx(dec_blob(k, DV1))];
+        a1.gX = t.gX; a1.causal = 1; a1.L = L;
+        bwd_attn<0><<<grid, NT, bytes, st>>>(pk, grad, a1, n_tok, lpad);       // gX += attention path
+    }
+    {
+        EmbArgs e = {};
+        e.gX = t.gX; e.actions = actions; e.L = L;
+        e.gln_w = gm.dec_ln_w; e.gln_b = gm.dec_ln_b; e.gW = gm.dec_wa;
+        bwd_embed_dec<<<grid, NT, bytes, st>>>(pk, grad, e, n_tok, lpad);
+    }
+    // ---- encoder ---------------------------------------------------------------------------------
+    {
+        HeadArgs h = {};
+        h.d_a = d_values; h.hh = t.e_hh; h.xhh = t.e_xhh; h.rsh = t.e_rsh; h.rep = b.rep;
+        h.blob_h0 = ENC_H0; h.h3 = ENC_H3;
+        h.gW0 = gm.w[idx(ENC_H0)]; h.gb0 = gm.b[idx(ENC_H0)]; h.glnw = gm.lnw[idx(ENC_H0)]; h.glnb = gm.lnb[idx(ENC_H0)];
+        h.gW3 = gm.enc_h3_w; h.gb3 = gm.enc_h3_b; h.glogstd = -1;
+        h.gOut = t.gRep; h.L = L;
+        bwd_head<0><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok, lpad);
+    }
+    for (int k = 1; k >= 0; --k) {
+        TailArgs ta = {};
+        ta.gOut = k == 1 ? t.gRep : t.gX; ta.xhF = t.e_xh2[k]; ta.rsF = t.e_rs2[k]; ta.m0 = t.e_m0[k];
+        ta.xhM = t.e_xh1[k]; ta.rsM = t.e_rs1[k]; ta.Y = t.e_y[k]; ta.lnF = enc_blob(k, EM2); ta.lnM = enc_blob(k, EP);
+        ta.seq[0] = bw(enc_blob(k, EM2)); ta.seq[1] = bw(enc_blob(k, EM0)); ta.seq[2] = bw(enc_blob(k, EP));
+        ta.gW2 = gm.w[idx(enc_blob(k, EM2))]; ta.gb2 = gm.b[idx(enc_blob(k, EM2))];
+        ta.gW0 = gm.w[idx(enc_blob(k, EM0))]; ta.gb0 = gm.b[idx(enc_blob(k, EM0))];
+        ta.gWp = gm.w[idx(enc_blob(k, EP))]; ta.gbp = gm.b[idx(enc_blob(k, EP))];
+        ta.glnFw = gm.lnw[idx(enc_blob(k, EM2))]; ta.glnFb = gm.lnb[idx(enc_blob(k, EM2))];
+        ta.glnMw = gm.lnw[idx(enc_blob(k, EP))]; ta.glnMb = gm.lnb[idx(enc_blob(k, EP))];
+        ta.gRes = t.gX; ta.res_add = 0; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
+        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok, lpad);
+
+        AttnArgs a1 = {};
+        a1.Q = t.e_q[k]; a1.K = b.K[k]; a1.V = b.V[k]; a1.lse = t.e_lse[k]; a1.gY = t.gYa; a1.gD = t.gDa;
+        if (k == 1) { a1.xh = t.e_xh2[0]; a1.rs = t.e_rs2[0]; a1.ln = enc_blob(0, EM2); }
+        else { a1.ln = -1; a1.xin = t.e_x0; }
+        a1.seq[0] = bw(enc_blob(k, EQ)); a1.seq[1] = bw(enc_blob(k, EK)); a1.seq[2] = bw(enc_blob(k, EV));
+        a1.gWq = gm.w[idx(enc_blob(k, EQ))]; a1.gbq = gm.b[idx(enc_blob(k, EQ))];
+        a1.gWk = gm.w[idx(enc_blob(k, EK))]; a1.gbk = gm.b[idx(enc_blob(k, EK))];
+        a1.gWv = gm.w[idx(enc_blob(k, EV))]; a1.gbv = gm.b[idx(enc_blob(k, EV))];
+        a1.gX = t.gX; a1.causal = 0; a1.L = L;
+        bwd_attn<0><<<grid, NT, bytes, st>>>(pk, grad, a1, n_tok, lpad);
+    }
+    {
+        EmbArgs e = {};
+        e.gX = t.gX; e.h0 = t.e_h0; e.xh0 = t.e_xh0; e.rs0 = t.e_rs0; e.obs = obs; e.obs_dim = obs_dim;
+        e.gln_w = gm.enc_ln_w; e.gln_b = gm.enc_ln_b; e.gW = gm.enc_wobs; e.gb = gm.enc_bobs;
+        e.gln7_w = gm.enc_ln7_w; e.gln7_b = gm.enc_ln7_b;
+        bwd_embed_enc<<<grid, NT, bytes, st>>>(pk, grad, e, n_tok, lpad);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}

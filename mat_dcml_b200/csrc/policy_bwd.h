@@ -1,0 +1,16 @@
+// Internal interface of the evaluate backward (policy_bwd.cu).
+#pragma once
+#include "layout.h"
+#include "policy_fwd.h"
+
+// offsets of every trainable tensor inside the flat parameter / gradient vector (state_dict order)
+struct GradMap {
+    int w[lay::N_BLOBS], b[lay::N_BLOBS];          // the 34 64x64 Linear layers, indexed like the forward blobs
+    int lnw[lay::N_BLOBS], lnb[lay::N_BLOBS];      // LayerNorm fused after that Linear (-1: none)
+    int enc_ln7_w, enc_ln7_b, enc_wobs, enc_bobs, enc_ln_w, enc_ln_b, enc_h3_w, enc_h3_b;
+    int log_std, dec_wa, dec_ln_w, dec_ln_b, dec_h3_w, dec_h3_b;
+};
+
+int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const GradMap& gm, float* grad, const float* obs,
+                             const float* actions, const float* ava, const float* d_values, const float* d_logp,
+                             const float* d_ent, long M, int L, int obs_dim, int mode, int n_sm, cudaStream_t st);

@@ -7,6 +7,8 @@
 //
 // Reference semantics: mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:24-230 and
 // mat_src/mat/algorithms/utils/transformer_act.py:8-189.
+#include <string.h>
+
 #include "policy_fwd.h"
 #include "tile.cuh"
 
@@ -106,7 +108,7 @@ __device__ __forceinline__ void token_rows(const Smem& s, long tile0, long n_tok
 // (ma_transformer.py:133-136,148-151 and :50-52)
 // -------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NT, 1)
-enc_embed_qkv(PolicyBufs b, const float* __restrict__ obs, long n_tok, int obs_dim, int depth, int lpad) {
+enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_tok, int obs_dim, int depth, int lpad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem s = carve(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
@@ -146,18 +148,24 @@ enc_embed_qkv(PolicyBufs b, const float* __restrict__ obs, long n_tok, int obs_d
                 const float4 w = *reinterpret_cast<const float4*>(Wt + k * 64 + cg * 4);
                 v0 = fmaf(o, w.x, v0); v1 = fmaf(o, w.y, v1); v2 = fmaf(o, w.z, v2); v3 = fmaf(o, w.w, v3);
             }
+            if (tb.on && r < n_valid) *reinterpret_cast<float4*>(tb.e_h0 + (tile0 + r) * 64 + cg * 4) = make_float4(v0, v1, v2, v3);
             v0 = gelu_erf(v0); v1 = gelu_erf(v1); v2 = gelu_erf(v2); v3 = gelu_erf(v3);
             const float mean = half_warp_sum(v0 + v1 + v2 + v3) * (1.0f / 64.0f);
             const float d0 = v0 - mean, d1 = v1 - mean, d2 = v2 - mean, d3 = v3 - mean;
             const float var = half_warp_sum(d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3) * (1.0f / 64.0f);
             const float rs = rsqrtf(var + 1e-5f);
+            if (tb.on && r < n_valid) {
+                *reinterpret_cast<float4*>(tb.e_xh0 + (tile0 + r) * 64 + cg * 4) = make_float4(d0 * rs, d1 * rs, d2 * rs, d3 * rs);
+                if (cg == 0) tb.e_rs0[tile0 + r] = rs;
+            }
             const float4 o4 = make_float4(d0 * rs * lw.x + lb.x, d1 * rs * lw.y + lb.y, d2 * rs * lw.z + lb.z, d3 * rs * lw.w + lb.w);
             *reinterpret_cast<float4*>(s.sX + r * XS + cg * 4) = o4;
             if (r < n_valid) *reinterpret_cast<float4*>(b.X + (tile0 + r) * 64 + cg * 4) = o4;
+            if (tb.on && r < n_valid) *reinterpret_cast<float4*>(tb.e_x0 + (tile0 + r) * 64 + cg * 4) = o4;
         }
     }
     __syncthreads();
-    stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, (tb.on ? tb.e_q[0] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
     stage<0>(ring, s.sX, b.K[0] + tile0 * 64, 64, n_valid, rg, cg);
     stage<0>(ring, s.sX, b.V[0] + tile0 * 64, 64, n_valid, rg, cg);
 }
@@ -169,7 +177,7 @@ enc_embed_qkv(PolicyBufs b, const float* __restrict__ obs, long n_tok, int obs_d
 // -------------------------------------------------------------------------------------------------
 template <int BLK>
 __global__ void __launch_bounds__(NT, 1)
-enc_block(PolicyBufs b, float* __restrict__ values, long n_tok, int L, int depth, int lpad) {
+enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int depth, int lpad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem s = carve(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
@@ -179,25 +187,33 @@ enc_block(PolicyBufs b, float* __restrict__ values, long n_tok, int L, int depth
     ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_seq_enc_blk0 : c_seq_enc_blk1, 6, 6, depth);
     token_rows(s, tile0, n_tok, L, b.K[BLK], b.V[BLK], false);
     load_tile(s.sX, b.X + tile0 * 64, 64, n_valid);
-    load_tile(s.sA, b.Q + tile0 * 64, 64, n_valid);
+    load_tile(s.sA, (tb.on ? tb.e_q[BLK] : b.Q) + tile0 * 64, 64, n_valid);
     if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::ENC_H3 + i];
     __syncthreads();
     ring.prefetch();
-    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L);
-    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.e_lse[BLK] + tile0 * 2 : nullptr, n_valid);
+    SaveOut sv1 = {nullptr, nullptr, nullptr}, sv2 = sv1, sv3 = sv1, sv4 = sv1;
+    if (tb.on) {
+        store_tile(tb.e_y[BLK] + tile0 * 64, 64, s.sB, n_valid);
+        sv1.xhat = tb.e_xh1[BLK] + tile0 * 64; sv1.rstd = tb.e_rs1[BLK] + tile0;
+        sv2.pre = tb.e_m0[BLK] + tile0 * 64;
+        sv3.xhat = tb.e_xh2[BLK] + tile0 * 64; sv3.rstd = tb.e_rs2[BLK] + tile0;
+        sv4.pre = tb.e_hh + tile0 * 64; sv4.xhat = tb.e_xhh + tile0 * 64; sv4.rstd = tb.e_rsh + tile0;
+    }
+    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv1, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg);
+    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv2, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv3, n_valid);
     __syncthreads(); ring.prefetch();
     if (BLK == 0) {
         store_tile(b.X + tile0 * 64, 64, s.sX, n_valid);
-        stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0>(ring, s.sX, (tb.on ? tb.e_q[1] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
         stage<0>(ring, s.sX, b.K[1] + tile0 * 64, 64, n_valid, rg, cg);
         stage<0>(ring, s.sX, b.V[1] + tile0 * 64, 64, n_valid, rg, cg);
     } else {
         store_tile(b.rep + tile0 * 64, 64, s.sX, n_valid);
-        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg);
+        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv4, n_valid);
         stage<0>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
         stage<0>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
         __syncthreads();
@@ -257,7 +273,7 @@ __device__ __forceinline__ void build_emb_table(float* __restrict__ dst, const f
 // (transformer_act.py:103-111,176-181)
 // -------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NT, 1)
-dec_embed_qkv(PolicyBufs b, const float* __restrict__ actions, long n_tok, int L, int depth, int lpad) {
+dec_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, long n_tok, int L, int depth, int lpad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem s = carve(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
@@ -279,9 +295,10 @@ dec_embed_qkv(PolicyBufs b, const float* __restrict__ actions, long n_tok, int L
         const float4 v = *reinterpret_cast<const float4*>(s.sSmall + code * 64 + c * 4);
         *reinterpret_cast<float4*>(s.sX + r * XS + c * 4) = v;
         if (r < n_valid) *reinterpret_cast<float4*>(b.X + g * 64 + c * 4) = v;
+        if (tb.on && r < n_valid) *reinterpret_cast<float4*>(tb.d_x0 + g * 64 + c * 4) = v;
     }
     __syncthreads();
-    stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0>(ring, s.sX, (tb.on ? tb.d_q1[0] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
     stage<0>(ring, s.sX, b.K1[0] + tile0 * 64, 64, n_valid, rg, cg);
     stage<0>(ring, s.sX, b.V1[0] + tile0 * 64, 64, n_valid, rg, cg);
 }
@@ -289,7 +306,7 @@ dec_embed_qkv(PolicyBufs b, const float* __restrict__ actions, long n_tok, int L
 // decoder block, first half: causal self-attention + proj + LN1, then K2/V2 of the result
 // (ma_transformer.py:113 and the key/value side of :114)
 __global__ void __launch_bounds__(NT, 1)
-dec_attn1(PolicyBufs b, int blk, long n_tok, int L, int depth, int lpad) {
+dec_attn1(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, int depth, int lpad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem s = carve(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
@@ -299,11 +316,16 @@ dec_attn1(PolicyBufs b, int blk, long n_tok, int L, int depth, int lpad) {
     ring.init(s.ring, s.bars, b.w, c_seq_dec_attn1[blk], 3, 3, depth);
     token_rows(s, tile0, n_tok, L, b.K1[blk], b.V1[blk], true);
     load_tile(s.sX, b.X + tile0 * 64, 64, n_valid);
-    load_tile(s.sA, b.Q + tile0 * 64, 64, n_valid);
+    load_tile(s.sA, (tb.on ? tb.d_q1[blk] : b.Q) + tile0 * 64, 64, n_valid);
     __syncthreads();
     ring.prefetch();
-    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L);
-    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse1[blk] + tile0 * 2 : nullptr, n_valid);
+    SaveOut sv1 = {nullptr, nullptr, nullptr};
+    if (tb.on) {
+        store_tile(tb.d_y1[blk] + tile0 * 64, 64, s.sB, n_valid);
+        sv1.xhat = tb.d_xh1[blk] + tile0 * 64; sv1.rstd = tb.d_rs1[blk] + tile0;
+    }
+    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv1, n_valid);
     __syncthreads();
     stage<0>(ring, s.sX, b.K2[blk] + tile0 * 64, 64, n_valid, rg, cg);
     stage<0>(ring, s.sX, b.V2[blk] + tile0 * 64, 64, n_valid, rg, cg);
@@ -326,7 +348,7 @@ __device__ __forceinline__ void masked_logz(float l0, float l1, const float* ava
 // decoder block, second half: cross-attention (query = obs_rep) + proj + LN2(rep + .) + MLP + LN3;
 // block 0 then emits QKV1 of block 1, block 1 the logits head and the per-token log-prob / entropy.
 __global__ void __launch_bounds__(NT, 1)
-dec_attn2(PolicyBufs b, int blk, const float* __restrict__ actions, const float* __restrict__ ava,
+dec_attn2(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ actions, const float* __restrict__ ava,
           float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, int depth, int lpad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem s = carve(smem_raw, depth, lpad);
@@ -340,20 +362,28 @@ dec_attn2(PolicyBufs b, int blk, const float* __restrict__ actions, const float*
     if (blk == 1) for (int i = tid; i < lay::DEC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::DEC_H3 + i];
     __syncthreads();
     ring.prefetch();
-    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L);
-    stage<EP_RES | EP_LN>(ring, s.sB, b.rep + tile0 * 64, 64, n_valid, s.sX, XS, TM, rg, cg);
+    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse2[blk] + tile0 * 2 : nullptr, n_valid);
+    SaveOut sv1 = {nullptr, nullptr, nullptr}, sv2 = sv1, sv3 = sv1, sv4 = sv1;
+    if (tb.on) {
+        store_tile(tb.d_y2[blk] + tile0 * 64, 64, s.sB, n_valid);
+        sv1.xhat = tb.d_xh2[blk] + tile0 * 64; sv1.rstd = tb.d_rs2[blk] + tile0;
+        sv2.pre = tb.d_m0[blk] + tile0 * 64;
+        sv3.xhat = tb.d_xh3[blk] + tile0 * 64; sv3.rstd = tb.d_rs3[blk] + tile0;
+        sv4.pre = tb.d_hh + tile0 * 64; sv4.xhat = tb.d_xhh + tile0 * 64; sv4.rstd = tb.d_rsh + tile0;
+    }
+    stage<EP_RES | EP_LN>(ring, s.sB, b.rep + tile0 * 64, 64, n_valid, s.sX, XS, TM, rg, cg, &sv1, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg);
+    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv2, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv3, n_valid);
     __syncthreads(); ring.prefetch();
     if (blk == 0) {
         store_tile(b.X + tile0 * 64, 64, s.sX, n_valid);
-        stage<0>(ring, s.sX, b.Q + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0>(ring, s.sX, (tb.on ? tb.d_q1[1] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
         stage<0>(ring, s.sX, b.K1[1] + tile0 * 64, 64, n_valid, rg, cg);
         stage<0>(ring, s.sX, b.V1[1] + tile0 * 64, 64, n_valid, rg, cg);
     } else {
-        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg);
+        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv4, n_valid);
         __syncthreads();
         if (tid < n_valid) {
             const long g = tile0 + tid;
@@ -605,7 +635,15 @@ int policy_init_constants() {
     return MATAS_OK;
 }
 
-int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st) {
+static TrainBufs train_or_off(const TrainBufs* tb) {
+    TrainBufs t;
+    if (tb) t = *tb; else { memset(&t, 0, sizeof(t)); }
+    return t;
+}
+
+int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
+                   const TrainBufs* tbp) {
+    const TrainBufs tb = train_or_off(tbp);
     int depth, lpad; size_t bytes;
     int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
     if (rc) return rc;
@@ -614,9 +652,9 @@ int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B,
     if ((rc = set_smem(enc_embed_qkv, bytes))) return rc;
     if ((rc = set_smem(enc_block<0>, bytes))) return rc;
     if ((rc = set_smem(enc_block<1>, bytes))) return rc;
-    enc_embed_qkv<<<grid, NT, bytes, st>>>(b, obs, n_tok, obs_dim, depth, lpad);
-    enc_block<0><<<grid, NT, bytes, st>>>(b, values, n_tok, L, depth, lpad);
-    enc_block<1><<<grid, NT, bytes, st>>>(b, values, n_tok, L, depth, lpad);
+    enc_embed_qkv<<<grid, NT, bytes, st>>>(b, tb, obs, n_tok, obs_dim, depth, lpad);
+    enc_block<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, depth, lpad);
+    enc_block<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, depth, lpad);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
@@ -633,7 +671,8 @@ int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, 
 }
 
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
-                          long B, int L, int mode, cudaStream_t st) {
+                          long B, int L, int mode, cudaStream_t st, const TrainBufs* tbp) {
+    const TrainBufs tb = train_or_off(tbp);
     int depth, lpad; size_t bytes;
     int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
     if (rc) return rc;
@@ -643,10 +682,10 @@ int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float
     if ((rc = set_smem(dec_embed_qkv, bytes))) return rc;
     if ((rc = set_smem(dec_attn1, bytes))) return rc;
     if ((rc = set_smem(dec_attn2, bytes))) return rc;
-    dec_embed_qkv<<<grid, NT, bytes, st>>>(b, actions, n_tok, L, depth, lpad);
+    dec_embed_qkv<<<grid, NT, bytes, st>>>(b, tb, actions, n_tok, L, depth, lpad);
     for (int blk = 0; blk < 2; ++blk) {
-        dec_attn1<<<grid, NT, bytes, st>>>(b, blk, n_tok, L, depth, lpad);
-        dec_attn2<<<grid, NT, bytes, st>>>(b, blk, actions, ava, logp, entropy, n_tok, L, n_disc, depth, lpad);
+        dec_attn1<<<grid, NT, bytes, st>>>(b, tb, blk, n_tok, L, depth, lpad);
+        dec_attn2<<<grid, NT, bytes, st>>>(b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, depth, lpad);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;

@@ -21,6 +21,21 @@ struct PolicyBufs {
     float* kv;           // decode K/V cache: [grid*64 env slots][blk 2][attn 2][k|v][L][64]
 };
 
+// training-mode saves of the teacher-forced forward + work buffers of the backward; [n_tok][64] fp32
+// unless noted.  xh = LayerNorm-normalised value before the affine map, rs = 1/std per token.
+struct TrainBufs {
+    int on;                                              // 0: inference (nothing is saved)
+    float *e_h0, *e_xh0, *e_rs0, *e_x0;                  // encoder embed: pre-GELU, LN, output
+    float *d_x0;                                         // decoder embed output
+    float *e_q[2], *e_y[2], *e_lse[2];                   // per block: queries, attention output, lse [tok][2]
+    float *e_xh1[2], *e_rs1[2], *e_m0[2], *e_xh2[2], *e_rs2[2];
+    float *e_hh, *e_xhh, *e_rsh;                         // value head: pre-GELU, LN
+    float *d_q1[2], *d_y1[2], *d_lse1[2], *d_xh1[2], *d_rs1[2];
+    float *d_y2[2], *d_lse2[2], *d_xh2[2], *d_rs2[2], *d_m0[2], *d_xh3[2], *d_rs3[2];
+    float *d_hh, *d_xhh, *d_rsh;                         // logits head
+    float *gX, *gRep, *gYa, *gYb, *gDa, *gDb;            // backward: residual-stream / obs_rep / attention-output grads, D [tok][2]
+};
+
 struct DecodeArgs {
     long B;
     int L, mode, deterministic, stride, n_steps;
@@ -41,8 +56,9 @@ int matas_policy_view(const matas_policy* p, PolicyView* v);
 int policy_launch_geometry(int L, int* depth, int* lpad, size_t* bytes);
 int policy_decode_steps(int L, int mode, int deterministic, int stride);
 int policy_init_constants();
-int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st);
+int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
+                   const TrainBufs* tb = nullptr);
 int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st);
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
-                          long B, int L, int mode, cudaStream_t st);
+                          long B, int L, int mode, cudaStream_t st, const TrainBufs* tb = nullptr);
 int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st);

@@ -22,11 +22,12 @@ enum { EP_GELU = 1, EP_RES = 2, EP_LN = 4 };
 struct Ring {
     float* slots; uint64_t* bars; const float* gw; const int* seq;   // seq: float offsets of the blobs, cyclic
     int seq_len, total, head, tail, depth;   // total: blobs this CTA consumes in its lifetime; tail: thread 0 only
+    uint32_t bytes;                          // bytes per blob (forward blobs: BLOB_BYTES)
 
     __device__ void init(float* slots_, uint64_t* bars_, const float* gw_, const int* seq_, int seq_len_, int total_,
-                         int depth_) {
+                         int depth_, uint32_t bytes_ = lay::BLOB_BYTES) {
         slots = slots_; bars = bars_; gw = gw_; seq = seq_; seq_len = seq_len_; total = total_; depth = depth_;
-        head = 0; tail = 0;
+        head = 0; tail = 0; bytes = bytes_;
         if (threadIdx.x == 0) {
             for (int i = 0; i < depth; ++i) mbar_init(&bars[i], 1);
             mbar_fence_init();
@@ -36,8 +37,8 @@ struct Ring {
         if (threadIdx.x == 0) {
             while (tail < head + depth && tail < total) {
                 const int s = tail % depth;
-                mbar_expect_tx(&bars[s], lay::BLOB_BYTES);
-                bulk_g2s(slots + (size_t)s * lay::BLOB, gw + seq[tail % seq_len], lay::BLOB_BYTES, &bars[s]);
+                mbar_expect_tx(&bars[s], bytes);
+                bulk_g2s(slots + (size_t)s * lay::BLOB, gw + seq[tail % seq_len], bytes, &bars[s]);
                 ++tail;
             }
         }
@@ -82,13 +83,19 @@ __device__ __forceinline__ void gemm(const float* __restrict__ X, const float* _
     }
 }
 
+// Optional training-mode outputs of a stage (global, token-major; null = not saved):
+//   pre  [row][64]  bias-added pre-activation (input of GELU)
+//   xhat [row][64]  LayerNorm-normalised value before the affine map;  rstd [row]
+struct SaveOut { float* pre; float* xhat; float* rstd; };
+
 // Epilogue order: + bias -> GELU -> + residual -> LayerNorm (eps 1e-5, biased variance).
 // The residual tile (shared, stride XS, or global) is read into registers BEFORE the GEMM so that
 // out may alias it and global latency hides behind the FMAs; rows >= res_valid read as 0.
 // Output row r goes to out + r*out_stride (shared or global); rows >= n_valid are not stored.
 template <int FLAGS>
 __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, const float* res, long res_stride,
-                                      int res_valid, float* out, long out_stride, int n_valid, int rg, int cg) {
+                                      int res_valid, float* out, long out_stride, int n_valid, int rg, int cg,
+                                      const SaveOut* sv = nullptr, int sv_valid = 0) {
     float4 rr[4];
     if (FLAGS & EP_RES) {
 #pragma unroll
@@ -112,6 +119,8 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, c
     for (int i = 0; i < 4; ++i) {
         const int r = rg * 4 + i;
         float v0 = acc[i][0] + b.x, v1 = acc[i][1] + b.y, v2 = acc[i][2] + b.z, v3 = acc[i][3] + b.w;
+        if ((FLAGS & EP_GELU) && sv && sv->pre && r < sv_valid)
+            *reinterpret_cast<float4*>(sv->pre + (long)r * 64 + cg * 4) = make_float4(v0, v1, v2, v3);
         if (FLAGS & EP_GELU) { v0 = gelu_erf(v0); v1 = gelu_erf(v1); v2 = gelu_erf(v2); v3 = gelu_erf(v3); }
         if (FLAGS & EP_RES) { v0 += rr[i].x; v1 += rr[i].y; v2 += rr[i].z; v3 += rr[i].w; }
         if (FLAGS & EP_LN) {
@@ -119,6 +128,10 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, c
             const float d0 = v0 - mean, d1 = v1 - mean, d2 = v2 - mean, d3 = v3 - mean;
             const float var = half_warp_sum(d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3) * (1.0f / 64.0f);
             const float rs = rsqrtf(var + 1e-5f);
+            if (sv && sv->xhat && r < sv_valid) {
+                *reinterpret_cast<float4*>(sv->xhat + (long)r * 64 + cg * 4) = make_float4(d0 * rs, d1 * rs, d2 * rs, d3 * rs);
+                if (cg == 0) sv->rstd[r] = rs;
+            }
             v0 = d0 * rs * lw.x + lb.x; v1 = d1 * rs * lw.y + lb.y; v2 = d2 * rs * lw.z + lb.z; v3 = d3 * rs * lw.w + lb.w;
         }
         if (r < n_valid) *reinterpret_cast<float4*>(out + (long)r * out_stride + cg * 4) = make_float4(v0, v1, v2, v3);
@@ -127,8 +140,8 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, c
 // plain stage (no residual)
 template <int FLAGS>
 __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, float* out, long out_stride, int n_valid,
-                                      int rg, int cg) {
-    stage<FLAGS>(ring, X, nullptr, 0, 0, out, out_stride, n_valid, rg, cg);
+                                      int rg, int cg, const SaveOut* sv = nullptr, int sv_valid = 0) {
+    stage<FLAGS>(ring, X, nullptr, 0, 0, out, out_stride, n_valid, rg, cg, sv, sv_valid);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -139,7 +152,8 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, f
 __device__ __forceinline__ void attention(const float* __restrict__ sQ, float* __restrict__ sOut,
                                           float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
                                           const float* const* __restrict__ kptr, const float* const* __restrict__ vptr,
-                                          const int* __restrict__ nt, int nt_max) {
+                                          const int* __restrict__ nt, int nt_max, float* lse_out = nullptr,
+                                          int lse_valid = 0) {
     const int tid = threadIdx.x;
     const float scale = 0.17677669529663687f;   // 1/sqrt(32)
     // phase A: scores
@@ -174,6 +188,7 @@ __device__ __forceinline__ void attention(const float* __restrict__ sQ, float* _
             sum += e;
         }
         sInv[rh] = n > 0 ? 1.0f / sum : 0.f;
+        if (lse_out && (rh >> 1) < lse_valid) lse_out[rh] = m + logf(sum);     // [row][head], training only
     }
     __syncthreads();
     // phase C: P.V  (8 threads per (row, head), 4 dims each)

@@ -180,6 +180,13 @@ class MultiAgentTransformer(nn.Module):
     def zero_std(self):
         self.decoder.zero_std()
 
+    def _anchor(self):
+        """A requires-grad scalar that ties the CUDA backward into the autograd graph."""
+        a = getattr(self, "_anchor_t", None)
+        if a is None or a.device != self.device:
+            a = self._anchor_t = torch.zeros((), device=self.device, requires_grad=True)
+        return a
+
     # ---- handle -----------------------------------------------------------------------------
     def _ctx(self):
         """Device guard for kernel calls; raises (never falls back) when the model is not on a GPU."""

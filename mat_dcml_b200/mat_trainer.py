@@ -1,0 +1,158 @@
+"""Drop-in for the reference's ``MATTrainer`` (mat_src/mat/algorithms/mat/mat_trainer.py:11-223):
+same constructor, ``train(buffer)`` / ``ppo_update(sample)`` / ``cal_value_loss`` / ``prep_*``.
+
+The model forward/backward are the CUDA kernels behind ``policy.evaluate_actions``; the PPO
+surrogate, the clipped Huber value loss and the ValueNorm update are the reference's few
+element-wise expressions over (M*L, 1) device vectors.  Gradients accumulate in the model's flat
+buffer; with ``torch.distributed`` initialised they are all-reduced (NCCL) once per minibatch, the
+only collective on the path, together with the scalars the reference computes over
+the global batch (advantage moments, ValueNorm batch moments, active-mask denominators).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from .valuenorm import ValueNorm
+
+
+def _world():
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
+def _allsum(t):
+    if _world() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t
+
+
+def huber_loss(e, d):                       # mat/utils/util.py:23-26
+    a = (abs(e) <= d).float()
+    b = (e > d).float()
+    return a * e ** 2 / 2 + b * d * (abs(e) - d / 2)
+
+
+def mse_loss(e):
+    return e ** 2 / 2
+
+
+class MATTrainer:
+    def __init__(self, args, policy, num_agents, device=torch.device("cpu")):
+        self.device = torch.device(device)
+        self.tpdv = dict(dtype=torch.float32, device=self.device)
+        self.policy, self.num_agents = policy, num_agents
+        self.n_rollout_threads = args.n_rollout_threads
+        self.clip_param, self.ppo_epoch, self.num_mini_batch = args.clip_param, args.ppo_epoch, args.num_mini_batch
+        self.value_loss_coef, self.entropy_coef = args.value_loss_coef, args.entropy_coef
+        self.max_grad_norm, self.huber_delta = args.max_grad_norm, args.huber_delta
+        self._use_max_grad_norm = args.use_max_grad_norm
+        self._use_clipped_value_loss = args.use_clipped_value_loss
+        self._use_huber_loss = args.use_huber_loss
+        self._use_valuenorm = args.use_valuenorm
+        self._use_value_active_masks = args.use_value_active_masks
+        self._use_policy_active_masks = args.use_policy_active_masks
+        self.value_normalizer = ValueNorm(1, device=self.device) if self._use_valuenorm else None
+
+    def _t(self, x):
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(x)
+        return x.to(**self.tpdv)
+
+    def _vn_update(self, returns):
+        """ValueNorm.update over the GLOBAL minibatch (valuenorm.py:39-56)."""
+        if _world() == 1:
+            self.value_normalizer.update(returns)
+            return
+        m = torch.stack([returns.sum(), (returns ** 2).sum(), torch.tensor(float(returns.numel()), **self.tpdv)])
+        _allsum(m)
+        vn, w = self.value_normalizer, self.value_normalizer.beta
+        vn.stats[0:1].mul_(w).add_((m[0] / m[2]) * (1.0 - w))
+        vn.stats[1:2].mul_(w).add_((m[1] / m[2]) * (1.0 - w))
+        vn.stats[2].mul_(w).add_(1.0 * (1.0 - w))
+
+    def cal_value_loss(self, values, value_preds_batch, return_batch, active_masks_batch):
+        """mat_trainer.py:54-94"""
+        value_pred_clipped = value_preds_batch + (values - value_preds_batch).clamp(-self.clip_param, self.clip_param)
+        if self._use_valuenorm:
+            self._vn_update(return_batch)
+            error_clipped = self.value_normalizer.normalize(return_batch) - value_pred_clipped
+            error_original = self.value_normalizer.normalize(return_batch) - values
+        else:
+            error_clipped = return_batch - value_pred_clipped
+            error_original = return_batch - values
+        if self._use_huber_loss:
+            vl_clipped, vl_original = huber_loss(error_clipped, self.huber_delta), huber_loss(error_original, self.huber_delta)
+        else:
+            vl_clipped, vl_original = mse_loss(error_clipped), mse_loss(error_original)
+        value_loss = torch.max(vl_original, vl_clipped) if self._use_clipped_value_loss else vl_original
+        if self._use_value_active_masks:
+            return (value_loss * active_masks_batch).sum() / self._active_sum(active_masks_batch)
+        return value_loss.sum() / self._count(value_loss)
+
+    def _active_sum(self, am):
+        return _allsum(am.sum().detach().clone())
+
+    def _count(self, x):
+        return _allsum(torch.tensor(float(x.numel()), **self.tpdv))
+
+    def ppo_update(self, sample):
+        """mat_trainer.py:96-156.  Under torch.distributed every rank passes its local minibatch; the
+        losses are normalised by global denominators and the flat gradient is summed over ranks, so all
+        replicas take the step the reference would take on the concatenated batch."""
+        share_obs_batch, obs_batch, rnn_states_batch, rnn_states_critic_batch, actions_batch, \
+            value_preds_batch, return_batch, masks_batch, active_masks_batch, old_action_log_probs_batch, \
+            adv_targ, available_actions_batch = sample
+        old_action_log_probs_batch = self._t(old_action_log_probs_batch)
+        adv_targ, value_preds_batch = self._t(adv_targ), self._t(value_preds_batch)
+        return_batch, active_masks_batch = self._t(return_batch), self._t(active_masks_batch)
+        model = self.policy.transformer
+        model.flat_grad(zero=True)                                   # optimizer.zero_grad()
+        values, action_log_probs, dist_entropy = self.policy.evaluate_actions(
+            share_obs_batch, obs_batch, rnn_states_batch, rnn_states_critic_batch, actions_batch, masks_batch,
+            available_actions_batch, active_masks_batch, active_denominator=self._active_sum(active_masks_batch))
+        imp_weights = torch.exp(action_log_probs - old_action_log_probs_batch)
+        surr1 = imp_weights * adv_targ
+        surr2 = torch.clamp(imp_weights, 1.0 - self.clip_param, 1.0 + self.clip_param) * adv_targ
+        if self._use_policy_active_masks:
+            policy_loss = (-torch.sum(torch.min(surr1, surr2) * active_masks_batch, dim=-1, keepdim=True)).sum() \
+                / self._active_sum(active_masks_batch)
+        else:
+            policy_loss = -torch.sum(torch.min(surr1, surr2), dim=-1, keepdim=True).sum() / self._count(surr1)
+        value_loss = self.cal_value_loss(values, value_preds_batch, return_batch, active_masks_batch)
+        loss = policy_loss - dist_entropy * self.entropy_coef + value_loss * self.value_loss_coef
+        loss.backward()                                              # CUDA backward -> flat gradient
+        if _world() > 1:
+            dist.all_reduce(model.flat_grad(), op=dist.ReduceOp.SUM)  # the one collective of the update
+        params = [p for p in model.parameters() if p.grad is not None]
+        if self._use_max_grad_norm:
+            grad_norm = nn.utils.clip_grad_norm_(params, self.max_grad_norm)
+        else:
+            grad_norm = torch.sqrt(sum((p.grad ** 2).sum() for p in params))
+        self.policy.optimizer.step()
+        return value_loss, grad_norm, policy_loss, dist_entropy, grad_norm, imp_weights
+
+    def train(self, buffer):
+        """mat_trainer.py:158-217"""
+        info = dict(value_loss=0.0, policy_loss=0.0, dist_entropy=0.0, actor_grad_norm=0.0, critic_grad_norm=0.0, ratio=0.0)
+        for _ in range(self.ppo_epoch):
+            next_values = self.policy.get_values(None, buffer.obs[-1].reshape(-1, buffer.obs.shape[-1]), None, None)
+            buffer.compute_returns(next_values.reshape(buffer.value_preds[-1].shape), self.value_normalizer)
+            adv = buffer.advantages
+            act = buffer.active_masks[:-1]
+            m = torch.stack([(adv * act).sum(), (adv * adv * act).sum(), act.sum()])   # nanmean / nanstd over active
+            _allsum(m)
+            mean = m[0] / m[2]
+            std = torch.sqrt(torch.clamp(m[1] / m[2] - mean * mean, min=0.0))
+            advantages = (adv - mean) / (std + 1e-5)
+            for sample in buffer.feed_forward_generator_transformer(advantages, self.num_mini_batch):
+                vl, cgn, pl, ent, agn, ratio = self.ppo_update(sample)
+                info["value_loss"] += vl.item(); info["policy_loss"] += pl.item(); info["dist_entropy"] += ent.item()
+                info["actor_grad_norm"] += float(agn); info["critic_grad_norm"] += float(cgn); info["ratio"] += ratio.mean().item()
+        n = self.ppo_epoch * self.num_mini_batch
+        return {k: v / n for k, v in info.items()}
+
+    def prep_training(self):
+        self.policy.train()
+
+    def prep_rollout(self):
+        self.policy.eval()

@@ -87,7 +87,9 @@ class TransformerPolicy:
         return self.transformer.get_values(None, obs, available_actions).view(-1, n_objective)
 
     def evaluate_actions(self, cent_obs, obs, rnn_states_actor, rnn_states_critic, actions, masks,
-                         available_actions=None, active_masks=None, n_objective=1):
+                         available_actions=None, active_masks=None, n_objective=1, active_denominator=None):
+        """transformer_policy.py:181-217.  ``active_denominator`` (optional, not in the reference) replaces
+        ``active_masks.sum()`` by the global count when the minibatch is sharded over ranks."""
         obs = _check(obs).reshape(-1, self.num_agents, self.obs_dim)
         actions = _check(actions).reshape(-1, self.num_agents, self.act_output_num)
         if available_actions is not None:
@@ -98,7 +100,7 @@ class TransformerPolicy:
         values = values.view(-1, n_objective)
         if self._use_policy_active_masks and active_masks is not None:
             am = _check(active_masks).to(**self.tpdv)
-            entropy = (entropy * am).sum() / am.sum()
+            entropy = (entropy * am).sum() / (am.sum() if active_denominator is None else active_denominator)
         else:
             entropy = entropy.mean()
         return values, action_log_probs, entropy
