@@ -243,6 +243,10 @@ def run_ours(ns):
     h2d = B * L * (7 + 2) * 4 + B * L * 4
     d2h = 3 * B * L * 4 + B * L * (7 + 2) * 4 + B * (W + 2) * 4 + B * 13
 
+    # ---- secondary metric: PPO update rows/s (BASELINE configs[3] shape per GPU) ----------------
+    ppo = None
+    if ns.ppo:
+        ppo = ppo_block(ns, torch, dist, dev, world, rank)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -288,10 +292,51 @@ def run_ours(ns):
             "clocks": clk, "gpu_launches": n_launch,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_K, "ms_per_step": e2e_ms / e2e_K},
-            "roofline": roofline, "cpu_baseline": cpu}
+            "roofline": roofline, "cpu_baseline": cpu, "ppo_update": ppo}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def ppo_block(ns, torch, dist, dev, world, rank):
+    """PPO update samples/sec: one epoch (4 minibatches) of MATTrainer.train at BASELINE configs[3]'s
+    per-GPU share (8192 envs x 20 workers x T=50 over 8 GPUs = 1024 envs per GPU), forward + backward +
+    gradient all-reduce + Adam.  A row is one (env, t) sample carrying all 21 agents (shared_buffer.py:248)."""
+    from mat_dcml_b200 import TransformerPolicy, DcmlVecEnv, SharedReplayBuffer, MATTrainer
+    N, W, T = 1024, 20, 50
+    L = W + 1
+    a = model_args(episode_length=T, n_rollout_threads=N, clip_param=0.2, ppo_epoch=1, num_mini_batch=4,
+                   value_loss_coef=1.0, entropy_coef=0.01, max_grad_norm=10.0, huber_delta=10.0, use_max_grad_norm=True,
+                   use_clipped_value_loss=True, use_huber_loss=True, use_value_active_masks=True)
+    env = DcmlVecEnv(N, W, seed=2, device=dev, env_offset=rank * N)
+    pol = TransformerPolicy(a, [7], [W + 2], env.action_space[0], L, device=dev)
+    pol.transformer.output_device = dev
+    pol.transformer.env_offset = rank * N
+    tr = MATTrainer(a, pol, L, device=dev)
+    buf = SharedReplayBuffer(a, L, [7], [W + 2], env.action_space[0], "DCML", device=dev)
+    obs, sob, ava = env.reset_device()
+    buf.obs[0].copy_(obs); buf._share_obs[0].copy_(env.sob); buf.available_actions[0].copy_(ava)
+    for t in range(T):
+        act, lp, v = pol.transformer.get_actions(None, obs, ava)
+        obs, sob, rew, done, delay, pay, ava = env.step_device(act)
+        buf.insert(env.sob, obs, None, None, act, lp, v, rew, 1.0 - done.float(), None, None, ava)
+    tr.train(buf)                                   # warm-up epoch (allocations)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    info = tr.train(buf)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    rows = world * N * T
+    return {"rows_per_s": rows / (ms.item() * 1e-3), "agent_samples_per_s": rows * L / (ms.item() * 1e-3), "ms_per_epoch": ms.item(),
+            "rows_per_epoch": rows, "minibatches": 4, "envs_per_gpu": N, "workers": W, "T": T,
+            "includes": "get_values + GAE + advantage norm + 4 x (forward, backward, grad all-reduce, clip, Adam)",
+            "value_loss": info["value_loss"], "grad_norm": info["actor_grad_norm"]}
 
 
 def main():
@@ -303,6 +348,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-envs", type=int, default=64, help="envs in the bounded CPU sample")
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-ppo", dest="ppo", action="store_false", help="skip the PPO-update block")
     ns = ap.parse_args()
     if ns.impl == "reference":
         run_reference(ns)

@@ -131,19 +131,23 @@ class MATTrainer:
         self.policy.optimizer.step()
         return value_loss, grad_norm, policy_loss, dist_entropy, grad_norm, imp_weights
 
+    def normalize_advantages(self, adv, active):
+        """mat_trainer.py:193-197: (adv - nanmean) / (nanstd + 1e-5) over active entries of the GLOBAL batch."""
+        m = torch.stack([(adv * active).sum(), active.sum()]).double()
+        _allsum(m)
+        mean = m[0] / m[1]
+        v = (((adv.double() - mean) ** 2) * active).sum().reshape(1)
+        _allsum(v)
+        std = torch.sqrt(v[0] / m[1])
+        return ((adv - mean.float()) / (std.float() + 1e-5))
+
     def train(self, buffer):
         """mat_trainer.py:158-217"""
         info = dict(value_loss=0.0, policy_loss=0.0, dist_entropy=0.0, actor_grad_norm=0.0, critic_grad_norm=0.0, ratio=0.0)
         for _ in range(self.ppo_epoch):
             next_values = self.policy.get_values(None, buffer.obs[-1].reshape(-1, buffer.obs.shape[-1]), None, None)
             buffer.compute_returns(next_values.reshape(buffer.value_preds[-1].shape), self.value_normalizer)
-            adv = buffer.advantages
-            act = buffer.active_masks[:-1]
-            m = torch.stack([(adv * act).sum(), (adv * adv * act).sum(), act.sum()])   # nanmean / nanstd over active
-            _allsum(m)
-            mean = m[0] / m[2]
-            std = torch.sqrt(torch.clamp(m[1] / m[2] - mean * mean, min=0.0))
-            advantages = (adv - mean) / (std + 1e-5)
+            advantages = self.normalize_advantages(buffer.advantages, buffer.active_masks[:-1])
             for sample in buffer.feed_forward_generator_transformer(advantages, self.num_mini_batch):
                 vl, cgn, pl, ent, agn, ratio = self.ppo_update(sample)
                 info["value_loss"] += vl.item(); info["policy_loss"] += pl.item(); info["dist_entropy"] += ent.item()
