@@ -153,6 +153,10 @@ class MATTrainer:
                 info["value_loss"] += vl.item(); info["policy_loss"] += pl.item(); info["dist_entropy"] += ent.item()
                 info["actor_grad_norm"] += float(agn); info["critic_grad_norm"] += float(cgn); info["ratio"] += ratio.mean().item()
         n = self.ppo_epoch * self.num_mini_batch
+        if _world() > 1:     # each rank logged its share of the global losses (global denominators)
+            t = torch.tensor([info["value_loss"], info["policy_loss"], info["dist_entropy"]], dtype=torch.float64, device=self.device)
+            _allsum(t)
+            info["value_loss"], info["policy_loss"], info["dist_entropy"] = t.tolist()
         return {k: v / n for k, v in info.items()}
 
     def prep_training(self):

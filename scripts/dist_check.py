@@ -24,15 +24,16 @@ rows = slice(rank * (M // world) * L, (rank + 1) * (M // world) * L)
 f = lambda k, dt=np.float32: g[k][rows].astype(dt)
 sample = (None, f("obs"), None, None, f("actions"), f("value_preds"), f("returns"), None, f("active"), f("old_logp"), f("adv"), f("ava"))
 vl, gn, pl, ent, _, ratio = tr.ppo_update(sample)
-tot = torch.stack([vl.detach(), pl.detach()]); dist.all_reduce(tot)
+tot = torch.stack([vl.detach(), pl.detach(), ent.detach()]); dist.all_reduce(tot)   # each rank holds its share of the global losses
 ok = abs(tot[0].item() - float(g["value_loss"])) < 1e-4 * max(1, abs(float(g["value_loss"]))) and \
-     abs(tot[1].item() - float(g["policy_loss"])) < 1e-4 and abs(ent.item() - float(g["entropy"])) < 1e-4 and \
+     abs(tot[1].item() - float(g["policy_loss"])) < 1e-4 and abs(tot[2].item() - float(g["entropy"])) < 1e-4 and \
      abs(float(gn) - float(g["grad_norm"])) < 2e-3 * float(g["grad_norm"])
 params = dict(pol.transformer.named_parameters())
 for name, st in zip(g["grad_names"], g["grad_stats"]):
     gr = params[str(name)].grad.detach().cpu().numpy()
     scale = max(st[1], 1e-4 * float(g["grad_norm"]))
     ok = ok and abs(np.sqrt((gr.astype(np.float64) ** 2).sum()) - st[1]) < 3e-3 * scale
+print("entropy %.6f (ref %.6f)" % (tot[2].item(), float(g["entropy"])))
 print("rank %d: value_loss %.6f (ref %.6f) policy_loss %.6f (ref %.6f) grad_norm %.5f (ref %.5f) -> %s"
       % (rank, tot[0].item(), float(g["value_loss"]), tot[1].item(), float(g["policy_loss"]), float(gn), float(g["grad_norm"]),
          "OK" if ok else "MISMATCH"), flush=True)
