@@ -26,6 +26,8 @@
 // an address a kernel can use, so the first call on each device (with that device current) asks the
 // runtime for the real device address with cudaGetSymbolAddress and remembers it.  Make that first
 // call before starting any stream capture.
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "../../include/matas_b200.h"
@@ -90,8 +92,11 @@ extern "C" int matas_policy_act_autoregressive_static(matas_policy* p, const flo
     a.B = B; a.L = L; a.mode = v.mode; a.deterministic = deterministic ? 1 : 0; a.stride = stride;
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
     a.seed = seed; a.step = step; a.env_offset = env_offset;
+    { const char* e = getenv("MATAS_PHASED_BELOW"); a.phased_below = e ? atoi(e) : (1 << 30); }
     a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
-    const long n_tiles = (B + 63) / 64;
-    const int grid = (int)(n_tiles < v.n_sm ? n_tiles : v.n_sm);
+    int grid; long slots;
+    if ((rc = policy_decode_geometry(L, B, v.n_sm, &grid, &slots))) return rc;
+    // B*L <= 2048 keeps the tile count far below the resident CTA count: one CTA per tile, env slot ==
+    // env index, and only the B valid slots are ever touched, so the cache fits the array
     return launch_decode(b, a, grid, (cudaStream_t)stream);
 }

@@ -2,6 +2,7 @@
 // weight repacking, scratch management.  The DCML simulator and GAE entry points live in env.cu
 // and gae.cu.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -171,8 +172,8 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     ARG_CHECK(cfg->n_agent >= 2, "n_agent %d < 2", cfg->n_agent);
     ARG_CHECK(cfg->state_dim >= 1, "state_dim %d < 1", cfg->state_dim);
     ARG_CHECK(cfg->mode == MATAS_MODE_SEMI || cfg->mode == MATAS_MODE_DISCRETE, "bad mode %d", cfg->mode);
-    int depth, lpad; size_t bytes;
-    int rc = policy_launch_geometry(cfg->n_agent, &depth, &lpad, &bytes);
+    int rpt, depth, lpad; size_t bytes;
+    int rc = policy_launch_geometry(cfg->n_agent, &rpt, &depth, &lpad, &bytes, 0);
     if (rc) return rc;
     matas_policy* p = new matas_policy();
     p->cfg = *cfg;
@@ -257,9 +258,9 @@ static int run_decode(matas_policy* p, const float* ava, long B, int determinist
                       uint32_t step, long env_offset, const float* u, const float* z, float* actions, float* logp,
                       cudaStream_t stream) {
     const int L = p->cfg.n_agent;
-    const long n_tiles = (B + 63) / 64;
-    const int grid = (int)(n_tiles < p->n_sm ? n_tiles : p->n_sm);
-    const size_t need = (size_t)grid * 64 * 8 * L * 64 * sizeof(float);
+    int grid; long slots;
+    { int rc_ = policy_decode_geometry(L, B, p->n_sm, &grid, &slots); if (rc_) return rc_; }
+    const size_t need = (size_t)slots * 8 * L * 64 * sizeof(float);
     if (need > p->kv_cap) {
         if (p->d_kv) CUDA_TRY(cudaFree(p->d_kv));
         p->d_kv = nullptr; p->kv_cap = 0;
@@ -271,6 +272,7 @@ static int run_decode(matas_policy* p, const float* ava, long B, int determinist
     a.B = B; a.L = L; a.mode = p->cfg.mode; a.deterministic = deterministic ? 1 : 0; a.stride = stride;
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
     a.seed = seed; a.step = step; a.env_offset = env_offset;
+    { const char* e = getenv("MATAS_PHASED_BELOW"); a.phased_below = e ? atoi(e) : (1 << 30); }
     a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
     if (!p->timing) return launch_decode(p->bufs, a, grid, stream);
     const int i = p->ev_next;

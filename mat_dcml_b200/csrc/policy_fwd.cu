@@ -7,6 +7,7 @@
 //
 // Reference semantics: mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:24-230 and
 // mat_src/mat/algorithms/utils/transformer_act.py:8-189.
+#include <stdlib.h>
 #include <string.h>
 
 #include "policy_fwd.h"
@@ -35,13 +36,16 @@ struct Smem {
     uint64_t* bars;    // ring barriers
 };
 
-__host__ __device__ inline size_t smem_bytes(int depth, int lpad) {
-    size_t f = (size_t)depth * lay::BLOB + 3 * TILE_F + (size_t)TM * 2 * lpad + TM * 2 + 1280;
+__host__ __device__ inline size_t smem_bytes(int tm, int depth, int lpad) {
+    size_t f = (size_t)depth * lay::BLOB + 3 * tm * XS + (size_t)tm * 2 * lpad + tm * 2 + 1280;
     f = (f + 3) & ~(size_t)3;
-    return f * 4 + TM * 8 * 2 + TM * 4 + TM * 8 * 4 + 8 * 8 + 16;
+    return f * 4 + tm * 8 * 2 + tm * 4 + tm * 8 * 4 + 8 * 8 + 16;
 }
 
+template <int RPT>
 __device__ inline Smem carve(unsigned char* base, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
+    constexpr int TILE_F = TM * XS;
     Smem s;
     float* f = reinterpret_cast<float*>(base);
     s.ring = f; f += (size_t)depth * lay::BLOB;
@@ -60,8 +64,9 @@ __device__ inline Smem carve(unsigned char* base, int depth, int lpad) {
     return s;
 }
 
+template <int RPT>
 __device__ __forceinline__ void store_tile(float* __restrict__ dst, long stride, const float* __restrict__ src, int n_valid) {
-    for (int idx = threadIdx.x; idx < TM * 16; idx += NT) {
+    for (int idx = threadIdx.x; idx < 16 * RPT * 16; idx += NT) {
         const int r = idx >> 4, c = idx & 15;
         if (r < n_valid)
             *reinterpret_cast<float4*>(dst + (long)r * stride + c * 4) = *reinterpret_cast<const float4*>(src + r * XS + c * 4);
@@ -86,10 +91,11 @@ __constant__ int c_seq_q2[2] = {lay::dec_q2(0), lay::dec_q2(1)};
 __constant__ int c_seq_decode[lay::DEC_STEP_BLOBS];   // filled by host: DEC_STEP + i*BLOB
 
 // per-row metadata for token-parallel tiles: row r <-> token g = tile0 + r = env*L + pos
+template <int RPT>
 __device__ __forceinline__ void token_rows(const Smem& s, long tile0, long n_tok, int L, const float* K, const float* V,
                                            bool causal) {
     const int r = threadIdx.x;
-    if (r < TM) {
+    if (r < 16 * RPT) {
         const long g = tile0 + r;
         if (g < n_tok) {
             const long env = g / L;
@@ -107,10 +113,12 @@ __device__ __forceinline__ void token_rows(const Smem& s, long tile0, long n_tok
 // encoder stage 1: obs LayerNorm -> Linear(obs_dim->64) -> GELU -> LayerNorm -> X ; QKV of block 0
 // (ma_transformer.py:133-136,148-151 and :50-52)
 // -------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(NT, 1)
+template <int RPT>
+__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
 enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_tok, int obs_dim, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -140,8 +148,8 @@ enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_
         const float4 bb = *reinterpret_cast<const float4*>(s.sSmall + lay::ENC_EMB_B + cg * 4);
         const float4 lw = *reinterpret_cast<const float4*>(s.sSmall + lay::ENC_EMB_LN2W + cg * 4);
         const float4 lb = *reinterpret_cast<const float4*>(s.sSmall + lay::ENC_EMB_LN2B + cg * 4);
-        for (int i = 0; i < 4; ++i) {
-            const int r = rg * 4 + i;
+        for (int i = 0; i < RPT; ++i) {
+            const int r = rg * RPT + i;
             float v0 = bb.x, v1 = bb.y, v2 = bb.z, v3 = bb.w;
             for (int k = 0; k < obs_dim; ++k) {
                 const float o = sObs[r * 8 + k];
@@ -165,9 +173,9 @@ enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_
         }
     }
     __syncthreads();
-    stage<0>(ring, s.sX, (tb.on ? tb.e_q[0] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
-    stage<0>(ring, s.sX, b.K[0] + tile0 * 64, 64, n_valid, rg, cg);
-    stage<0>(ring, s.sX, b.V[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, (tb.on ? tb.e_q[0] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, b.K[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, b.V[0] + tile0 * 64, 64, n_valid, rg, cg);
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -175,47 +183,48 @@ enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_
 // BLK 0 then emits QKV of block 1; BLK 1 emits obs_rep, the value head (:138-139) and the decoder's
 // cross-attention queries Q2 = attn2.query(obs_rep) for both decoder blocks (:114, :51).
 // -------------------------------------------------------------------------------------------------
-template <int BLK>
-__global__ void __launch_bounds__(NT, 1)
+template <int BLK, int RPT>
+__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
 enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
     Ring ring;
     ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_seq_enc_blk0 : c_seq_enc_blk1, 6, 6, depth);
-    token_rows(s, tile0, n_tok, L, b.K[BLK], b.V[BLK], false);
-    load_tile(s.sX, b.X + tile0 * 64, 64, n_valid);
-    load_tile(s.sA, (tb.on ? tb.e_q[BLK] : b.Q) + tile0 * 64, 64, n_valid);
+    token_rows<RPT>(s, tile0, n_tok, L, b.K[BLK], b.V[BLK], false);
+    load_tile<RPT>(s.sX, b.X + tile0 * 64, 64, n_valid);
+    load_tile<RPT>(s.sA, (tb.on ? tb.e_q[BLK] : b.Q) + tile0 * 64, 64, n_valid);
     if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::ENC_H3 + i];
     __syncthreads();
     ring.prefetch();
-    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.e_lse[BLK] + tile0 * 2 : nullptr, n_valid);
+    attention<RPT, true>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.e_lse[BLK] + tile0 * 2 : nullptr, n_valid);
     SaveOut sv1 = {nullptr, nullptr, nullptr}, sv2 = sv1, sv3 = sv1, sv4 = sv1;
     if (tb.on) {
-        store_tile(tb.e_y[BLK] + tile0 * 64, 64, s.sB, n_valid);
+        store_tile<RPT>(tb.e_y[BLK] + tile0 * 64, 64, s.sB, n_valid);
         sv1.xhat = tb.e_xh1[BLK] + tile0 * 64; sv1.rstd = tb.e_rs1[BLK] + tile0;
         sv2.pre = tb.e_m0[BLK] + tile0 * 64;
         sv3.xhat = tb.e_xh2[BLK] + tile0 * 64; sv3.rstd = tb.e_rs2[BLK] + tile0;
         sv4.pre = tb.e_hh + tile0 * 64; sv4.xhat = tb.e_xhh + tile0 * 64; sv4.rstd = tb.e_rsh + tile0;
     }
-    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv1, n_valid);
+    stage<EP_RES | EP_LN, RPT>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv1, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv2, n_valid);
+    stage<EP_GELU, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv2, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv3, n_valid);
+    stage<EP_RES | EP_LN, RPT>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv3, n_valid);
     __syncthreads(); ring.prefetch();
     if (BLK == 0) {
-        store_tile(b.X + tile0 * 64, 64, s.sX, n_valid);
-        stage<0>(ring, s.sX, (tb.on ? tb.e_q[1] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
-        stage<0>(ring, s.sX, b.K[1] + tile0 * 64, 64, n_valid, rg, cg);
-        stage<0>(ring, s.sX, b.V[1] + tile0 * 64, 64, n_valid, rg, cg);
+        store_tile<RPT>(b.X + tile0 * 64, 64, s.sX, n_valid);
+        stage<0, RPT>(ring, s.sX, (tb.on ? tb.e_q[1] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.K[1] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.V[1] + tile0 * 64, 64, n_valid, rg, cg);
     } else {
-        store_tile(b.rep + tile0 * 64, 64, s.sX, n_valid);
-        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv4, n_valid);
-        stage<0>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
-        stage<0>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+        store_tile<RPT>(b.rep + tile0 * 64, 64, s.sX, n_valid);
+        stage<EP_GELU | EP_LN, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv4, n_valid);
+        stage<0, RPT>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
         __syncthreads();
         if (tid < n_valid) values[tile0 + tid] = row_dot(s.sA, tid, s.sSmall) + s.sSmall[64];
     }
@@ -223,21 +232,23 @@ enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, in
 
 // cross-attention queries from a caller-supplied obs_rep (the transformer_act entry points start
 // from obs_rep, transformer_act.py:30,103,131,176): rep_in -> b.rep copy, Q2[blk] = attn2.query(rep)
-__global__ void __launch_bounds__(NT, 1)
+template <int RPT>
+__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
 q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
     Ring ring;
     ring.init(s.ring, s.bars, b.w, c_seq_q2, 2, 2, depth);
-    load_tile(s.sX, rep_in + tile0 * 64, 64, n_valid);
+    load_tile<RPT>(s.sX, rep_in + tile0 * 64, 64, n_valid);
     __syncthreads();
     ring.prefetch();
-    if (rep_in != b.rep) store_tile(b.rep + tile0 * 64, 64, s.sX, n_valid);
-    stage<0>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
-    stage<0>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+    if (rep_in != b.rep) store_tile<RPT>(b.rep + tile0 * 64, 64, s.sX, n_valid);
+    stage<0, RPT>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -272,10 +283,12 @@ __device__ __forceinline__ void build_emb_table(float* __restrict__ dst, const f
 // teacher-forced decoder, stage 1: shifted-action embedding -> X ; QKV1 of block 0
 // (transformer_act.py:103-111,176-181)
 // -------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(NT, 1)
+template <int RPT>
+__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
 dec_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, long n_tok, int L, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -298,37 +311,39 @@ dec_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, lon
         if (tb.on && r < n_valid) *reinterpret_cast<float4*>(tb.d_x0 + g * 64 + c * 4) = v;
     }
     __syncthreads();
-    stage<0>(ring, s.sX, (tb.on ? tb.d_q1[0] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
-    stage<0>(ring, s.sX, b.K1[0] + tile0 * 64, 64, n_valid, rg, cg);
-    stage<0>(ring, s.sX, b.V1[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, (tb.on ? tb.d_q1[0] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, b.K1[0] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, b.V1[0] + tile0 * 64, 64, n_valid, rg, cg);
 }
 
 // decoder block, first half: causal self-attention + proj + LN1, then K2/V2 of the result
 // (ma_transformer.py:113 and the key/value side of :114)
-__global__ void __launch_bounds__(NT, 1)
+template <int RPT>
+__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
 dec_attn1(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
     Ring ring;
     ring.init(s.ring, s.bars, b.w, c_seq_dec_attn1[blk], 3, 3, depth);
-    token_rows(s, tile0, n_tok, L, b.K1[blk], b.V1[blk], true);
-    load_tile(s.sX, b.X + tile0 * 64, 64, n_valid);
-    load_tile(s.sA, (tb.on ? tb.d_q1[blk] : b.Q) + tile0 * 64, 64, n_valid);
+    token_rows<RPT>(s, tile0, n_tok, L, b.K1[blk], b.V1[blk], true);
+    load_tile<RPT>(s.sX, b.X + tile0 * 64, 64, n_valid);
+    load_tile<RPT>(s.sA, (tb.on ? tb.d_q1[blk] : b.Q) + tile0 * 64, 64, n_valid);
     __syncthreads();
     ring.prefetch();
-    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse1[blk] + tile0 * 2 : nullptr, n_valid);
+    attention<RPT, true>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse1[blk] + tile0 * 2 : nullptr, n_valid);
     SaveOut sv1 = {nullptr, nullptr, nullptr};
     if (tb.on) {
-        store_tile(tb.d_y1[blk] + tile0 * 64, 64, s.sB, n_valid);
+        store_tile<RPT>(tb.d_y1[blk] + tile0 * 64, 64, s.sB, n_valid);
         sv1.xhat = tb.d_xh1[blk] + tile0 * 64; sv1.rstd = tb.d_rs1[blk] + tile0;
     }
-    stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv1, n_valid);
+    stage<EP_RES | EP_LN, RPT>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv1, n_valid);
     __syncthreads();
-    stage<0>(ring, s.sX, b.K2[blk] + tile0 * 64, 64, n_valid, rg, cg);
-    stage<0>(ring, s.sX, b.V2[blk] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, b.K2[blk] + tile0 * 64, 64, n_valid, rg, cg);
+    stage<0, RPT>(ring, s.sX, b.V2[blk] + tile0 * 64, 64, n_valid, rg, cg);
 }
 
 // per-token distribution head shared by evaluate and decode (transformer_act.py:8-28,112-128)
@@ -347,43 +362,45 @@ __device__ __forceinline__ void masked_logz(float l0, float l1, const float* ava
 
 // decoder block, second half: cross-attention (query = obs_rep) + proj + LN2(rep + .) + MLP + LN3;
 // block 0 then emits QKV1 of block 1, block 1 the logits head and the per-token log-prob / entropy.
-__global__ void __launch_bounds__(NT, 1)
+template <int RPT>
+__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
 dec_attn2(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ actions, const float* __restrict__ ava,
           float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
     Ring ring;
     ring.init(s.ring, s.bars, b.w, c_seq_dec_attn2[blk], blk == 0 ? 6 : 4, blk == 0 ? 6 : 4, depth);
-    token_rows(s, tile0, n_tok, L, b.K2[blk], b.V2[blk], true);
-    load_tile(s.sA, b.Q2[blk] + tile0 * 64, 64, n_valid);
+    token_rows<RPT>(s, tile0, n_tok, L, b.K2[blk], b.V2[blk], true);
+    load_tile<RPT>(s.sA, b.Q2[blk] + tile0 * 64, 64, n_valid);
     if (blk == 1) for (int i = tid; i < lay::DEC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::DEC_H3 + i];
     __syncthreads();
     ring.prefetch();
-    attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse2[blk] + tile0 * 2 : nullptr, n_valid);
+    attention<RPT, true>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse2[blk] + tile0 * 2 : nullptr, n_valid);
     SaveOut sv1 = {nullptr, nullptr, nullptr}, sv2 = sv1, sv3 = sv1, sv4 = sv1;
     if (tb.on) {
-        store_tile(tb.d_y2[blk] + tile0 * 64, 64, s.sB, n_valid);
+        store_tile<RPT>(tb.d_y2[blk] + tile0 * 64, 64, s.sB, n_valid);
         sv1.xhat = tb.d_xh2[blk] + tile0 * 64; sv1.rstd = tb.d_rs2[blk] + tile0;
         sv2.pre = tb.d_m0[blk] + tile0 * 64;
         sv3.xhat = tb.d_xh3[blk] + tile0 * 64; sv3.rstd = tb.d_rs3[blk] + tile0;
         sv4.pre = tb.d_hh + tile0 * 64; sv4.xhat = tb.d_xhh + tile0 * 64; sv4.rstd = tb.d_rsh + tile0;
     }
-    stage<EP_RES | EP_LN>(ring, s.sB, b.rep + tile0 * 64, 64, n_valid, s.sX, XS, TM, rg, cg, &sv1, n_valid);
+    stage<EP_RES | EP_LN, RPT>(ring, s.sB, b.rep + tile0 * 64, 64, n_valid, s.sX, XS, TM, rg, cg, &sv1, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv2, n_valid);
+    stage<EP_GELU, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv2, n_valid);
     __syncthreads(); ring.prefetch();
-    stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv3, n_valid);
+    stage<EP_RES | EP_LN, RPT>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg, &sv3, n_valid);
     __syncthreads(); ring.prefetch();
     if (blk == 0) {
-        store_tile(b.X + tile0 * 64, 64, s.sX, n_valid);
-        stage<0>(ring, s.sX, (tb.on ? tb.d_q1[1] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
-        stage<0>(ring, s.sX, b.K1[1] + tile0 * 64, 64, n_valid, rg, cg);
-        stage<0>(ring, s.sX, b.V1[1] + tile0 * 64, 64, n_valid, rg, cg);
+        store_tile<RPT>(b.X + tile0 * 64, 64, s.sX, n_valid);
+        stage<0, RPT>(ring, s.sX, (tb.on ? tb.d_q1[1] : b.Q) + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.K1[1] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.V1[1] + tile0 * 64, 64, n_valid, rg, cg);
     } else {
-        stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv4, n_valid);
+        stage<EP_GELU | EP_LN, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv4, n_valid);
         __syncthreads();
         if (tid < n_valid) {
             const long g = tile0 + tid;
@@ -464,10 +481,12 @@ struct DecSched {
 // -------------------------------------------------------------------------------------------------
 // persistent KV-cached decode: one CTA owns 64 envs at a time and walks the schedule.
 // -------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(NT, 1)
+template <int RPT>
+__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
 decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
+    constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth, lpad);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const int L = a.L;
     const long n_tiles = (a.B + TM - 1) / TM;
@@ -520,38 +539,42 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
                 float* k2 = kv0 + ((blk * 2 + 1) * 2 + 0) * (long)L * 64;
                 float* v2 = kv0 + ((blk * 2 + 1) * 2 + 1) * (long)L * 64;
                 // ---- self-attention over the cache --------------------------------------------------
-                stage<0>(ring, s.sX, s.sA, XS, TM, rg, cg);
-                stage<0>(ring, s.sX, k1 + (long)j * 64, slot_stride, n_valid, rg, cg);
-                stage<0>(ring, s.sX, v1 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                stage<0, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg);
+                stage<0, RPT>(ring, s.sX, k1 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                stage<0, RPT>(ring, s.sX, v1 + (long)j * 64, slot_stride, n_valid, rg, cg);
                 if (tid < TM) {
                     s.kptr[tid] = k1 + tid * slot_stride;
                     s.vptr[tid] = v1 + tid * slot_stride;
                     s.nt[tid] = tid < n_valid ? j + 1 : 0;
                 }
                 __syncthreads(); ring.prefetch();
-                attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
-                stage<EP_RES | EP_LN>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+                // coherent (L2) loads only: these rows were written by this kernel
+                if (j < a.phased_below) attention_phased<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
+                else attention<RPT, false>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
+                stage<EP_RES | EP_LN, RPT>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
                 // ---- cross-attention: keys/values from the decoder stream, query from obs_rep ------
-                stage<0>(ring, s.sX, k2 + (long)j * 64, slot_stride, n_valid, rg, cg);
-                stage<0>(ring, s.sX, v2 + (long)j * 64, slot_stride, n_valid, rg, cg);
-                load_tile(s.sA, b.Q2[blk] + (env0 * L + j) * 64, (long)L * 64, n_valid);
+                stage<0, RPT>(ring, s.sX, k2 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                stage<0, RPT>(ring, s.sX, v2 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                load_tile<RPT>(s.sA, b.Q2[blk] + (env0 * L + j) * 64, (long)L * 64, n_valid);
                 if (tid < TM) {
                     s.kptr[tid] = k2 + tid * slot_stride;
                     s.vptr[tid] = v2 + tid * slot_stride;
                 }
                 __syncthreads(); ring.prefetch();
-                attention(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
-                stage<EP_RES | EP_LN>(ring, s.sB, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid, s.sX, XS, TM, rg, cg);
+                // coherent (L2) loads only: these rows were written by this kernel
+                if (j < a.phased_below) attention_phased<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
+                else attention<RPT, false>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
+                stage<EP_RES | EP_LN, RPT>(ring, s.sB, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
-                stage<EP_GELU>(ring, s.sX, s.sA, XS, TM, rg, cg);
+                stage<EP_GELU, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
-                stage<EP_RES | EP_LN>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+                stage<EP_RES | EP_LN, RPT>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
             }
             // ---- logits head + action pick ---------------------------------------------------------
             if (st.emit) {
-                stage<EP_GELU | EP_LN>(ring, s.sX, s.sA, XS, TM, rg, cg);
+                stage<EP_GELU | EP_LN, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg);
             } else {
                 ring.acquire(); ring.release();
             }
@@ -611,14 +634,38 @@ int set_smem(K kernel, size_t bytes) {
 // -------------------------------------------------------------------------------------------------
 // host launchers
 // -------------------------------------------------------------------------------------------------
-int policy_launch_geometry(int L, int* depth, int* lpad, size_t* bytes) {
+// Tile geometry: 32-row tiles (2 rows per thread) with two CTAs per SM whenever both fit in shared
+// memory -- one CTA's attention (memory latency) then overlaps the other's GEMMs -- else 64-row tiles.
+int policy_launch_geometry(int L, int* rpt, int* depth, int* lpad, size_t* bytes, int kind) {
     *lpad = L | 1;
+    const size_t two_per_sm = 115712;       // (228 KB - 2 x 1 KB reserved) / 2
+    // kind 0: token-parallel passes -- 64-row tiles, one CTA per SM, the rest of the SM's unified
+    //         L1/shared array caches the K/V rows that the tile's query rows share;
+    // kind 1: decode -- 32-row tiles, two CTAs per SM.  MATAS_RPT_TOKEN / MATAS_RPT_DECODE override (tuning).
+    const char* ov = getenv(kind == 0 ? "MATAS_RPT_TOKEN" : "MATAS_RPT_DECODE");
+    const int want = ov ? atoi(ov) : (kind == 0 ? 4 : 2);
+    if (want == 2 && smem_bytes(32, 3, *lpad) <= two_per_sm) {
+        *rpt = 2; *depth = 3; *bytes = smem_bytes(32, 3, *lpad);
+        return MATAS_OK;
+    }
     for (int d = 4; d >= 3; --d) {
-        const size_t sb = smem_bytes(d, *lpad);
-        if (sb <= 232448) { *depth = d; *bytes = sb; return MATAS_OK; }
+        const size_t sb = smem_bytes(64, d, *lpad);
+        if (sb <= 232448) { *rpt = 4; *depth = d; *bytes = sb; return MATAS_OK; }
     }
     matas_set_error("n_agent %d needs more shared memory than a B200 SM has (max supported 201)", L);
     return MATAS_ERR_LIMIT;
+}
+
+int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots) {
+    int rpt, depth, lpad; size_t bytes;
+    int rc = policy_launch_geometry(L, &rpt, &depth, &lpad, &bytes, 1);
+    if (rc) return rc;
+    const int tm = 16 * rpt;
+    const long n_tiles = (B + tm - 1) / tm;
+    const long resident = (long)n_sm * (rpt == 2 ? 2 : 1);
+    *grid = (int)(n_tiles < resident ? n_tiles : resident);
+    *slots = (long)*grid * tm;
+    return MATAS_OK;
 }
 
 int policy_decode_steps(int L, int mode, int deterministic, int stride) {
@@ -641,31 +688,36 @@ static TrainBufs train_or_off(const TrainBufs* tb) {
     return t;
 }
 
+#define GEOMETRY(L, KIND)                                             \
+    int rpt, depth, lpad; size_t bytes;                               \
+    { int rc_ = policy_launch_geometry(L, &rpt, &depth, &lpad, &bytes, KIND); if (rc_) return rc_; } \
+    const int tm = 16 * rpt
+// launch KERNEL<..., RPT> for the chosen geometry
+#define LAUNCH(KERNEL2, KERNEL4, GRID, ...)                           \
+    do {                                                              \
+        int rc_;                                                      \
+        if (rpt == 2) { if ((rc_ = set_smem(KERNEL2, bytes))) return rc_; KERNEL2<<<GRID, NT, bytes, st>>>(__VA_ARGS__); } \
+        else { if ((rc_ = set_smem(KERNEL4, bytes))) return rc_; KERNEL4<<<GRID, NT, bytes, st>>>(__VA_ARGS__); }          \
+    } while (0)
+
 int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
                    const TrainBufs* tbp) {
     const TrainBufs tb = train_or_off(tbp);
-    int depth, lpad; size_t bytes;
-    int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
-    if (rc) return rc;
+    GEOMETRY(L, 0);
     const long n_tok = B * L;
-    const unsigned grid = (unsigned)((n_tok + TM - 1) / TM);
-    if ((rc = set_smem(enc_embed_qkv, bytes))) return rc;
-    if ((rc = set_smem(enc_block<0>, bytes))) return rc;
-    if ((rc = set_smem(enc_block<1>, bytes))) return rc;
-    enc_embed_qkv<<<grid, NT, bytes, st>>>(b, tb, obs, n_tok, obs_dim, depth, lpad);
-    enc_block<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, depth, lpad);
-    enc_block<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, depth, lpad);
+    const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
+    LAUNCH(enc_embed_qkv<2>, enc_embed_qkv<4>, grid, b, tb, obs, n_tok, obs_dim, depth, lpad);
+    LAUNCH((enc_block<0, 2>), (enc_block<0, 4>), grid, b, tb, values, n_tok, L, depth, lpad);
+    LAUNCH((enc_block<1, 2>), (enc_block<1, 4>), grid, b, tb, values, n_tok, L, depth, lpad);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
 
 int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st) {
-    int depth, lpad; size_t bytes;
-    int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
-    if (rc) return rc;
+    GEOMETRY(L, 0);
     const long n_tok = B * L;
-    if ((rc = set_smem(q2_from_rep, bytes))) return rc;
-    q2_from_rep<<<(unsigned)((n_tok + TM - 1) / TM), NT, bytes, st>>>(b, rep_in, n_tok, depth, lpad);
+    const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
+    LAUNCH(q2_from_rep<2>, q2_from_rep<4>, grid, b, rep_in, n_tok, depth, lpad);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
@@ -673,30 +725,23 @@ int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, 
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
                           long B, int L, int mode, cudaStream_t st, const TrainBufs* tbp) {
     const TrainBufs tb = train_or_off(tbp);
-    int depth, lpad; size_t bytes;
-    int rc = policy_launch_geometry(L, &depth, &lpad, &bytes);
-    if (rc) return rc;
+    GEOMETRY(L, 0);
     const long n_tok = B * L;
-    const unsigned grid = (unsigned)((n_tok + TM - 1) / TM);
+    const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
     const int n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
-    if ((rc = set_smem(dec_embed_qkv, bytes))) return rc;
-    if ((rc = set_smem(dec_attn1, bytes))) return rc;
-    if ((rc = set_smem(dec_attn2, bytes))) return rc;
-    dec_embed_qkv<<<grid, NT, bytes, st>>>(b, tb, actions, n_tok, L, depth, lpad);
+    LAUNCH(dec_embed_qkv<2>, dec_embed_qkv<4>, grid, b, tb, actions, n_tok, L, depth, lpad);
     for (int blk = 0; blk < 2; ++blk) {
-        dec_attn1<<<grid, NT, bytes, st>>>(b, tb, blk, n_tok, L, depth, lpad);
-        dec_attn2<<<grid, NT, bytes, st>>>(b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, depth, lpad);
+        LAUNCH(dec_attn1<2>, dec_attn1<4>, grid, b, tb, blk, n_tok, L, depth, lpad);
+        LAUNCH(dec_attn2<2>, dec_attn2<4>, grid, b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, depth, lpad);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
 
 int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st) {
-    int depth, lpad; size_t bytes;
-    int rc = policy_launch_geometry(a.L, &depth, &lpad, &bytes);
-    if (rc) return rc;
-    if ((rc = set_smem(decode_kernel, bytes))) return rc;
-    decode_kernel<<<grid, NT, bytes, st>>>(b, a, depth, lpad);
+    GEOMETRY(a.L, 1);
+    (void)tm;
+    LAUNCH(decode_kernel<2>, decode_kernel<4>, grid, b, a, depth, lpad);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }

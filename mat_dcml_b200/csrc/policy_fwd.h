@@ -39,6 +39,7 @@ struct TrainBufs {
 struct DecodeArgs {
     long B;
     int L, mode, deterministic, stride, n_steps;
+    int phased_below;    // positions below this use the phased attention (short contexts), the rest the fused one
     uint64_t seed;
     uint32_t step;
     long env_offset;
@@ -53,7 +54,8 @@ struct matas_policy;
 struct PolicyView { int n_agent, mode, device, n_sm, weights_set; const float* packed; };
 int matas_policy_view(const matas_policy* p, PolicyView* v);
 
-int policy_launch_geometry(int L, int* depth, int* lpad, size_t* bytes);
+int policy_launch_geometry(int L, int* rpt, int* depth, int* lpad, size_t* bytes, int kind);
+int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots);
 int policy_decode_steps(int L, int mode, int deterministic, int stride);
 int policy_init_constants();
 int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,

@@ -52,25 +52,26 @@ struct Ring {
 };
 
 // ---------------------------------------------------------------------------------------------
-// GEMM: acc[i][j] = sum_k X[4*rg+i][k] * Wt[k][4*cg+j]
+// GEMM: acc[i][j] = sum_k X[RPT*rg+i][k] * Wt[k][4*cg+j]     (tile of 16*RPT rows; RPT rows per thread)
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void gemm(const float* __restrict__ X, const float* __restrict__ Wt, float (&acc)[4][4],
+template <int RPT>
+__device__ __forceinline__ void gemm(const float* __restrict__ X, const float* __restrict__ Wt, float (&acc)[RPT][4],
                                      int rg, int cg) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < RPT; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    const float* xr = X + rg * 4 * XS;
+    const float* xr = X + rg * RPT * XS;
     const float* wc = Wt + cg * 4;
 #pragma unroll 4
     for (int k = 0; k < 64; k += 4) {
-        float4 a[4], w[4];
+        float4 a[RPT], w[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(xr + i * XS + k);
+        for (int i = 0; i < RPT; ++i) a[i] = *reinterpret_cast<const float4*>(xr + i * XS + k);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) w[kk] = *reinterpret_cast<const float4*>(wc + (k + kk) * 64);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < RPT; ++i) {
             const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w};
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
@@ -92,22 +93,22 @@ struct SaveOut { float* pre; float* xhat; float* rstd; };
 // The residual tile (shared, stride XS, or global) is read into registers BEFORE the GEMM so that
 // out may alias it and global latency hides behind the FMAs; rows >= res_valid read as 0.
 // Output row r goes to out + r*out_stride (shared or global); rows >= n_valid are not stored.
-template <int FLAGS>
+template <int FLAGS, int RPT = 4>
 __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, const float* res, long res_stride,
                                       int res_valid, float* out, long out_stride, int n_valid, int rg, int cg,
                                       const SaveOut* sv = nullptr, int sv_valid = 0) {
-    float4 rr[4];
+    float4 rr[RPT];
     if (FLAGS & EP_RES) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int r = rg * 4 + i;
+        for (int i = 0; i < RPT; ++i) {
+            const int r = rg * RPT + i;
             rr[i] = r < res_valid ? *reinterpret_cast<const float4*>(res + (long)r * res_stride + cg * 4)
                                   : make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
     const float* blob = ring.acquire();
-    float acc[4][4];
-    gemm(X, blob, acc, rg, cg);
+    float acc[RPT][4];
+    gemm<RPT>(X, blob, acc, rg, cg);
     const float4 b = *reinterpret_cast<const float4*>(blob + lay::B_BIAS + cg * 4);
     float4 lw, lb;
     if (FLAGS & EP_LN) {
@@ -116,8 +117,8 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, c
     }
     ring.release();
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int r = rg * 4 + i;
+    for (int i = 0; i < RPT; ++i) {
+        const int r = rg * RPT + i;
         float v0 = acc[i][0] + b.x, v1 = acc[i][1] + b.y, v2 = acc[i][2] + b.z, v3 = acc[i][3] + b.w;
         if ((FLAGS & EP_GELU) && sv && sv->pre && r < sv_valid)
             *reinterpret_cast<float4*>(sv->pre + (long)r * 64 + cg * 4) = make_float4(v0, v1, v2, v3);
@@ -138,10 +139,10 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, c
     }
 }
 // plain stage (no residual)
-template <int FLAGS>
+template <int FLAGS, int RPT = 4>
 __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, float* out, long out_stride, int n_valid,
                                       int rg, int cg, const SaveOut* sv = nullptr, int sv_valid = 0) {
-    stage<FLAGS>(ring, X, nullptr, 0, 0, out, out_stride, n_valid, rg, cg, sv, sv_valid);
+    stage<FLAGS, RPT>(ring, X, nullptr, 0, 0, out, out_stride, n_valid, rg, cg, sv, sv_valid);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -149,11 +150,136 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, f
 // (t-major, 64 floats per key: head h uses columns 32h..32h+31) found at kptr[r] / vptr[r].
 // sScore: TM*2*lpad floats (lpad odd), sInv: TM*2 floats.  Three phases with CTA barriers.
 // ---------------------------------------------------------------------------------------------
+// K/V loads.  CACHED (token-parallel passes): the rows were written by an EARLIER kernel, so the
+// read-only path (ld.global.nc) is legal and the rows of an env are shared by all query rows of a tile.
+// !CACHED (decode): the rows were written earlier in THIS kernel by this CTA, so a plain coherent load
+// is required; it may still hit in L1 (same-SM stores keep L1 coherent), which merges the eight
+// 16-byte requests a thread makes to one 128-byte row.
+template <bool CACHED> __device__ __forceinline__ float4 ld_kv(const float4* p) { return CACHED ? __ldg(p) : *p; }
+
+__device__ __forceinline__ float dot32(const float4 (&q)[8], const float4 (&k)[8]) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;     // four independent chains, 8 deep each
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        s0 = fmaf(q[i].x, k[i].x, s0); s1 = fmaf(q[i].y, k[i].y, s1);
+        s2 = fmaf(q[i].z, k[i].z, s2); s3 = fmaf(q[i].w, k[i].w, s3);
+    }
+    return (s0 + s1) + (s2 + s3);
+}
+
+// One (row, head) pair is owned by G = NT / (2 TM) adjacent lanes, which split its keys round-robin:
+// scores (q in registers, two key rows in flight) -> max / exp / sum with shuffles over the G lanes
+// -> P.V accumulated in registers and all-reduced over the G lanes.  No CTA barrier inside; one at
+// the end publishes sOut.  sScore holds the pair's scores (each lane only re-reads its own entries).
+template <int RPT = 4, bool CACHED = false>
 __device__ __forceinline__ void attention(const float* __restrict__ sQ, float* __restrict__ sOut,
                                           float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
                                           const float* const* __restrict__ kptr, const float* const* __restrict__ vptr,
                                           const int* __restrict__ nt, int nt_max, float* lse_out = nullptr,
                                           int lse_valid = 0) {
+    constexpr int TM = 16 * RPT;
+    constexpr int G = NT / (TM * 2);
+    const float scale = 0.17677669529663687f;   // 1/sqrt(32)
+    const int tid = threadIdx.x, rh = tid / G, sub = tid % G, r = rh >> 1, h = rh & 1;
+    const int n = nt[r];
+    const float4* kp = reinterpret_cast<const float4*>(kptr[r] + h * 32);
+    const float4* vp = reinterpret_cast<const float4*>(vptr[r] + h * 32);
+    float* sc = sScore + rh * lpad;
+    float m = -INFINITY;
+    {
+        float4 q[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q[i] = *reinterpret_cast<const float4*>(sQ + r * XS + h * 32 + i * 4);
+        int t = sub;
+        for (; t + G < n; t += 2 * G) {
+            float4 k0[8], k1[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) k0[i] = ld_kv<CACHED>(kp + (long)t * 16 + i);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) k1[i] = ld_kv<CACHED>(kp + (long)(t + G) * 16 + i);
+            const float a0 = dot32(q, k0) * scale, a1 = dot32(q, k1) * scale;
+            sc[t] = a0; sc[t + G] = a1;
+            m = fmaxf(m, fmaxf(a0, a1));
+        }
+        if (t < n) {
+            float4 k0[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) k0[i] = ld_kv<CACHED>(kp + (long)t * 16 + i);
+            const float a0 = dot32(q, k0) * scale;
+            sc[t] = a0;
+            m = fmaxf(m, a0);
+        }
+    }
+#pragma unroll
+    for (int o = 1; o < G; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float4 acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    float sum = 0.f;
+    {
+        int t = sub;
+        for (; t + G < n; t += 2 * G) {
+            float4 v0[8], v1[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v0[i] = ld_kv<CACHED>(vp + (long)t * 16 + i);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v1[i] = ld_kv<CACHED>(vp + (long)(t + G) * 16 + i);
+            const float p0 = expf(sc[t] - m), p1 = expf(sc[t + G] - m);
+            sum += p0 + p1;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                acc[i].x = fmaf(p0, v0[i].x, acc[i].x); acc[i].y = fmaf(p0, v0[i].y, acc[i].y);
+                acc[i].z = fmaf(p0, v0[i].z, acc[i].z); acc[i].w = fmaf(p0, v0[i].w, acc[i].w);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                acc[i].x = fmaf(p1, v1[i].x, acc[i].x); acc[i].y = fmaf(p1, v1[i].y, acc[i].y);
+                acc[i].z = fmaf(p1, v1[i].z, acc[i].z); acc[i].w = fmaf(p1, v1[i].w, acc[i].w);
+            }
+        }
+        if (t < n) {
+            float4 v0[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v0[i] = ld_kv<CACHED>(vp + (long)t * 16 + i);
+            const float p0 = expf(sc[t] - m);
+            sum += p0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                acc[i].x = fmaf(p0, v0[i].x, acc[i].x); acc[i].y = fmaf(p0, v0[i].y, acc[i].y);
+                acc[i].z = fmaf(p0, v0[i].z, acc[i].z); acc[i].w = fmaf(p0, v0[i].w, acc[i].w);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 1; o < G; o <<= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            acc[i].x += __shfl_xor_sync(0xffffffffu, acc[i].x, o); acc[i].y += __shfl_xor_sync(0xffffffffu, acc[i].y, o);
+            acc[i].z += __shfl_xor_sync(0xffffffffu, acc[i].z, o); acc[i].w += __shfl_xor_sync(0xffffffffu, acc[i].w, o);
+        }
+    }
+    const float inv = n > 0 ? 1.0f / sum : 0.f;
+    // every lane holds the totals; lane `sub` stores its 8/G float4 share of the 32 outputs
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        if (i / (8 / G) == sub)
+            *reinterpret_cast<float4*>(sOut + r * XS + h * 32 + i * 4) =
+                make_float4(acc[i].x * inv, acc[i].y * inv, acc[i].z * inv, acc[i].w * inv);
+    if (sub == 0 && lse_out && r < lse_valid) lse_out[rh] = m + logf(sum);     // [row][head], training only
+    __syncthreads();
+}
+
+// Phased variant (score items flattened over (row, head, key) -> softmax -> P.V with 8 lanes per
+// (row, head)): three CTA barriers, but every thread always has independent items, which wins when the
+// context is short (the decode's first ~64 positions) and the K/V rows stream from HBM.
+template <int RPT = 4>
+__device__ __forceinline__ void attention_phased(const float* __restrict__ sQ, float* __restrict__ sOut,
+                                          float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
+                                          const float* const* __restrict__ kptr, const float* const* __restrict__ vptr,
+                                          const int* __restrict__ nt, int nt_max, float* lse_out = nullptr,
+                                          int lse_valid = 0) {
+    constexpr int TM = 16 * RPT;
     const int tid = threadIdx.x;
     const float scale = 0.17677669529663687f;   // 1/sqrt(32)
     // phase A: scores
@@ -164,31 +290,39 @@ __device__ __forceinline__ void attention(const float* __restrict__ sQ, float* _
             const float4* qp = reinterpret_cast<const float4*>(sQ + r * XS + h * 32);
             float4 kk[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) kk[i] = __ldcg(kp + i);
-            float s = 0.f;
+            for (int i = 0; i < 8; ++i) kk[i] = kp[i];
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const float4 q = qp[i];
-                s = fmaf(q.x, kk[i].x, s); s = fmaf(q.y, kk[i].y, s); s = fmaf(q.z, kk[i].z, s); s = fmaf(q.w, kk[i].w, s);
+                s0 = fmaf(q.x, kk[i].x, s0); s1 = fmaf(q.y, kk[i].y, s1); s2 = fmaf(q.z, kk[i].z, s2); s3 = fmaf(q.w, kk[i].w, s3);
             }
-            sScore[rh * lpad + t] = s * scale;
+            sScore[rh * lpad + t] = ((s0 + s1) + (s2 + s3)) * scale;
         }
     }
     __syncthreads();
-    // phase B: softmax numerators + 1/sum
-    for (int rh = tid; rh < TM * 2; rh += NT) {
+    // phase B: softmax numerators + 1/sum; G = NT / (2 TM) adjacent lanes share one (row, head)
+    {
+        constexpr int G = NT / (TM * 2);
+        const int rh = tid / G, sub = tid % G;
         const int n = nt[rh >> 1];
         float* sc = sScore + rh * lpad;
         float m = -INFINITY;
-        for (int t = 0; t < n; ++t) m = fmaxf(m, sc[t]);
+        for (int t = sub; t < n; t += G) m = fmaxf(m, sc[t]);
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
         float sum = 0.f;
-        for (int t = 0; t < n; ++t) {
+        for (int t = sub; t < n; t += G) {
             const float e = expf(sc[t] - m);
             sc[t] = e;
             sum += e;
         }
-        sInv[rh] = n > 0 ? 1.0f / sum : 0.f;
-        if (lse_out && (rh >> 1) < lse_valid) lse_out[rh] = m + logf(sum);     // [row][head], training only
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (sub == 0) {
+            sInv[rh] = n > 0 ? 1.0f / sum : 0.f;
+            if (lse_out && (rh >> 1) < lse_valid) lse_out[rh] = m + logf(sum);
+        }
     }
     __syncthreads();
     // phase C: P.V  (8 threads per (row, head), 4 dims each)
@@ -202,7 +336,7 @@ __device__ __forceinline__ void attention(const float* __restrict__ sQ, float* _
         for (; t + 4 <= n; t += 4) {
             float4 v[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(vp + (long)(t + i) * 64));
+            for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const float4*>(vp + (long)(t + i) * 64);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const float p = sc[t + i];
@@ -211,7 +345,7 @@ __device__ __forceinline__ void attention(const float* __restrict__ sQ, float* _
             }
         }
         for (; t < n; ++t) {
-            const float4 v = __ldcg(reinterpret_cast<const float4*>(vp + (long)t * 64));
+            const float4 v = *reinterpret_cast<const float4*>(vp + (long)t * 64);
             const float p = sc[t];
             acc.x = fmaf(p, v.x, acc.x); acc.y = fmaf(p, v.y, acc.y); acc.z = fmaf(p, v.z, acc.z); acc.w = fmaf(p, v.w, acc.w);
         }
@@ -222,9 +356,11 @@ __device__ __forceinline__ void attention(const float* __restrict__ sQ, float* _
     __syncthreads();
 }
 
-// load a [TM][64] tile from global rows (row r at src + r*stride) into a shared tile; invalid rows -> 0
+
+// load a [16*RPT][64] tile from global rows (row r at src + r*stride) into a shared tile; invalid rows -> 0
+template <int RPT = 4>
 __device__ __forceinline__ void load_tile(float* __restrict__ dst, const float* __restrict__ src, long stride, int n_valid) {
-    for (int idx = threadIdx.x; idx < TM * 16; idx += NT) {
+    for (int idx = threadIdx.x; idx < 16 * RPT * 16; idx += NT) {
         const int r = idx >> 4, c = idx & 15;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (r < n_valid) v = __ldcg(reinterpret_cast<const float4*>(src + (long)r * stride + c * 4));
