@@ -153,6 +153,9 @@ typedef struct {
     uint64_t seed;
     long env_offset;   /* global index of env 0 (rank * n_envs when sharded) */
     int double_reset;  /* 1 = ShareDummyVecEnv's second reset on done (env_wrappers.py:730-736) */
+    int shannon;       /* 1 = Shannon link rates (reset(shannon_enable=True): DCML_ENVs/DCML_Basic_Env.py:18-27,
+                          DCML_Master.py:41-45, Shannon.py:14-21); share_obs rows are then 2W+2 wide
+                          [Rn, Cn, upload/1e7 (W), download/1e7 (W)], …SingleProcess.py:248-250 */
 } dcml_env_cfg;
 
 /* Env.__init__ (…SingleProcess.py:16-55): base_workload_host is the workloads.txt table,
@@ -160,7 +163,7 @@ typedef struct {
 int dcml_env_create(const dcml_env_cfg* cfg, const double* base_workload_host, dcml_env** out);
 int dcml_env_destroy(dcml_env* e);
 
-/* Env.reset: obs [B*L*7], share_obs [B*(W+2)] (ONE row per env; the reference replicates it over
+/* Env.reset: obs [B*L*7], share_obs [B*(W+2)] ([B*(2W+2)] in Shannon mode; ONE row per env; the reference replicates it over
  * the L agents, …SingleProcess.py:270), ava [B*L*2]. */
 int dcml_env_reset(dcml_env* e, float* obs, float* share_obs, float* ava, void* stream);
 

@@ -20,6 +20,8 @@ constexpr double PR_MAX = 0.95;
 constexpr double DONE_P = 0.8;
 constexpr int R_MIN = 1024, R_MAX = 1048576, C_MIN = 32, C_MAX = 1024;
 constexpr int R_HI = 1153434, C_HI = 1126;   // round(1.1 * max), DCML_Master.py:47-48
+constexpr double NOISE = 0x1.4f8b588e368f1p-17;   // python 10**(-50/10), Shannon.py:9
+constexpr double B_TOTAL = 100e9;                 // DCML_Master.py:29
 constexpr int RETRY_CAP = 4096, SLOT_CAP = 4096;
 constexpr int LWS = 21;                      // padded per-thread stride of the shared workload copy
 
@@ -31,6 +33,9 @@ struct EnvState {
     uint64_t seed;
     long env_offset;
     int double_reset;
+    int shannon;           // Shannon link rates instead of the fixed NON_SHANNON_DATA_RATE
+    double* rate_down;     // [B][W] download rate used by Worker.process for both transfers (Shannon mode)
+    double* rate_up;       // [B][W] upload rate (observed only)
     const double* base;    // [W][20]
     double* lw;            // [B][W][20] current jittered workload == next step's local workload
     double* R;             // [B]
@@ -71,7 +76,7 @@ struct RetryStream {
 struct ProcOut { double delay, price0; int tp0, nslots; };
 
 // Worker.process, DCML_Worker_TIMESLOT_MultiProcess.py:46-112; lw = this worker's 20 local slots
-__device__ ProcOut process(const double* lw, double Pr, double r, double c, int arrive, RetryStream& rs) {
+__device__ ProcOut process(const double* lw, double Pr, double r, double c, int arrive, RetryStream& rs, double DATA_RATE) {
     ProcOut o;
     double cost = ceil((9.0 * r - 3.0) * c) / FREQUENCY;                    // :49-50
     int n = 1;
@@ -127,7 +132,8 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
     double* s_lw = reinterpret_cast<double*>(smem_raw);                 // [threads][LWS] old workload
     double* s_d = s_lw + (size_t)blockDim.x * LWS;                      // [threads] delay, later price / Pr
     double* s_f = s_d + blockDim.x;                                     // [threads][3] observed slots
-    double* s_sc = s_f + (size_t)blockDim.x * 3;                        // [epb][8] scalars
+    double* s_rate = s_f + (size_t)blockDim.x * 3;                      // [2][threads] Shannon down / up rates
+    double* s_sc = s_rate + (size_t)blockDim.x * 2;                     // [epb][8] scalars
     uint32_t* s_key = reinterpret_cast<uint32_t*>(s_sc + (size_t)epb * 8);   // [threads]
     float* s_sel = reinterpret_cast<float*>(s_key + blockDim.x);        // [threads]
     int* s_i = reinterpret_cast<int*>(s_sel + blockDim.x);              // [epb][8] int scalars
@@ -140,6 +146,8 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
     float* e_sel = s_sel + le * tpe;
     uint32_t* e_key = s_key + le * tpe;
     uint8_t* e_dis = s_dis + le * tpe;
+    double* e_rd = s_rate + le * tpe;
+    double* e_ru = s_rate + blockDim.x + le * tpe;
     double* glw = st.lw + (env * W + w) * PERIOD;
 
     if (what == ENV_INIT) {
@@ -189,7 +197,7 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
             RetryStream rs;
             rs.init(genv, t, w, st.seed);
             const double r = ceil(sc[2] / (double)si[1]);                  // Master.get_workload, DCML_Master.py:39-40
-            po = process(my_lw, st.Pr[env * W + w], r, sc[3], si[3], rs);
+            po = process(my_lw, st.Pr[env * W + w], r, sc[3], si[3], rs, st.shannon ? st.rate_down[env * W + w] : DATA_RATE);
             e_d[w] = po.delay;
             // Worker.process :111 redraw the workload (step-t jitter stream)
             for (int blk = 0; blk < 5; ++blk) {
@@ -259,6 +267,17 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
                 const uint4 x = philox4x32(genv, t, rng_tag(S_WORKER, (uint32_t)w), (uint32_t)r, st.seed);
                 e_d[w] = 0.0 + (PR_MAX - 0.0) * u01d(x.x);                                   // :197
                 e_key[w] = x.y;
+                if (st.shannon) {
+                    // update_workers_transmission(True): DCML_Basic_Env.py:18-27, DCML_Master.py:41-45, Shannon.py:14-21
+                    const uint4 xm = philox4x32(genv, t, rng_tag(S_RESET, 0), (uint32_t)(16 * r + 2), st.seed);
+                    const double pm = 50.0 + (60.0 - 50.0) * u01d(xm.x);
+                    const double pw = 10.0 + (20.0 - 10.0) * u01d(x.z);
+                    const double dist = 10.0 + (100.0 - 10.0) * u01d(x.w);
+                    const double d4 = pow(dist, -4.0);
+                    const double bw = B_TOTAL / (double)W;
+                    e_rd[w] = bw * log2(1.0 + (pm * d4) / NOISE);
+                    e_ru[w] = bw * log2(1.0 + (pw * d4) / NOISE);
+                }
             }
             __syncthreads();
             if (apply && w < W) {
@@ -273,12 +292,16 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
         if (active) {
             st.Pr[env * W + w] = e_d[w];
             st.disabled[env * W + w] = e_dis[w];
+            if (st.shannon) { st.rate_down[env * W + w] = e_rd[w]; st.rate_up[env * W + w] = e_ru[w]; }
         }
         if (env_ok && w == 0) {
             st.R[env] = sc[2]; st.C[env] = sc[3]; st.arrive[env] = si[3]; st.kdis[env] = si[4];
         }
     } else {
-        if (active) { e_d[w] = st.Pr[env * W + w]; e_dis[w] = st.disabled[env * W + w]; }
+        if (active) {
+            e_d[w] = st.Pr[env * W + w]; e_dis[w] = st.disabled[env * W + w];
+            if (st.shannon) { e_rd[w] = st.rate_down[env * W + w]; e_ru[w] = st.rate_up[env * W + w]; }
+        }
         if (env_ok && w == 0) { sc[2] = st.R[env]; sc[3] = st.C[env]; si[3] = st.arrive[env]; si[4] = st.kdis[env]; }
         __syncthreads();
     }
@@ -311,7 +334,12 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
         }
         io.ava[(env * L + w) * 2] = 1.f;                                   // Worker.get_availability :144-148
         io.ava[(env * L + w) * 2 + 1] = dis ? 0.f : 1.f;
-        io.sob[env * (W + 2) + 2 + w] = (float)e_d[w];                     // :252-253
+        if (st.shannon) {                                                  // :248-250
+            io.sob[env * (2 * W + 2) + 2 + w] = (float)(e_ru[w] / 1e7);
+            io.sob[env * (2 * W + 2) + 2 + W + w] = (float)(e_rd[w] / 1e7);
+        } else {
+            io.sob[env * (W + 2) + 2 + w] = (float)e_d[w];                 // :252-253
+        }
     }
     __syncthreads();
     if (env_ok && w == 0) {
@@ -325,7 +353,8 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
         o[2] = (float)(s0 / n_en); o[3] = (float)(s1 / n_en); o[4] = (float)(s2 / n_en);
         o[5] = (float)(sp / n_en); o[6] = 1.1f;
         io.ava[(env * L + W) * 2] = 1.f; io.ava[(env * L + W) * 2 + 1] = 1.f;
-        io.sob[env * (W + 2)] = (float)Rn; io.sob[env * (W + 2) + 1] = (float)Cn;
+        const long sw = st.shannon ? 2 * W + 2 : W + 2;
+        io.sob[env * sw] = (float)Rn; io.sob[env * sw + 1] = (float)Cn;
     }
 }
 
@@ -401,12 +430,13 @@ extern "C" int dcml_env_create(const dcml_env_cfg* cfg, const double* base_host,
     const int tpe = (W + 31) / 32 * 32;
     e->epb = tpe >= 256 ? 1 : 256 / tpe;
     e->block = e->epb * tpe;
-    e->smem = (size_t)e->block * (LWS + 1 + 3) * 8 + (size_t)e->epb * 8 * 8 + (size_t)e->block * (4 + 4) +
+    e->smem = (size_t)e->block * (LWS + 1 + 3 + 2) * 8 + (size_t)e->epb * 8 * 8 + (size_t)e->block * (4 + 4) +
               (size_t)e->epb * 8 * 4 + e->block + 16;
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_lw = carve((size_t)B * W * PERIOD * 8), o_R = carve(B * 8), o_C = carve(B * 8), o_Pr = carve((size_t)B * W * 8),
-                 o_arr = carve(B * 4), o_k = carve(B * 4), o_dis = carve((size_t)B * W);
+                 o_arr = carve(B * 4), o_k = carve(B * 4), o_dis = carve((size_t)B * W),
+                 o_rd = carve((size_t)B * W * 8), o_ru = carve((size_t)B * W * 8);
     auto fail = [&](const char* what, cudaError_t err) {
         matas_set_error("%s: %s", what, cudaGetErrorString(err));
         dcml_env_destroy(e);
@@ -427,6 +457,8 @@ extern "C" int dcml_env_create(const dcml_env_cfg* cfg, const double* base_host,
     st.lw = reinterpret_cast<double*>(s + o_lw); st.R = reinterpret_cast<double*>(s + o_R); st.C = reinterpret_cast<double*>(s + o_C);
     st.Pr = reinterpret_cast<double*>(s + o_Pr); st.arrive = reinterpret_cast<int*>(s + o_arr); st.kdis = reinterpret_cast<int*>(s + o_k);
     st.disabled = s + o_dis;
+    st.shannon = cfg->shannon ? 1 : 0;
+    st.rate_down = reinterpret_cast<double*>(s + o_rd); st.rate_up = reinterpret_cast<double*>(s + o_ru);
     *out = e;
     return MATAS_OK;
 }

@@ -65,12 +65,13 @@ class _Infos:
 
 class DcmlVecEnv:
     def __init__(self, n_envs, n_workers=100, base_workload=None, seed=1, device="cuda", double_reset=True,
-                 env_offset=0, host_dtype=np.float64, replicate_share_obs=True):
+                 env_offset=0, host_dtype=np.float64, replicate_share_obs=True, shannon=False):
         """``host_dtype`` / ``replicate_share_obs`` only shape what ``reset`` / ``step`` hand back on the
         host: the reference returns float64 observations and L materialised copies of the share_obs row
         (…SingleProcess.py:270); float32 and a broadcast view avoid 0.35 GB of host copies per step at
         16384 x 50."""
         self.host_dtype, self.replicate_share_obs = host_dtype, replicate_share_obs
+        self.shannon = bool(shannon)      # Shannon link rates on every reset (reference: reset(shannon_enable=True))
         self.num_envs = self.N = int(n_envs)
         self.W, self.L = int(n_workers), int(n_workers) + 1
         self.n_agents = self.L
@@ -82,9 +83,10 @@ class DcmlVecEnv:
             raise ValueError("base_workload must be (%d, %d)" % (self.W, PERIOD))
         self.base_workload = np.ascontiguousarray(base)
         self.observation_space = [[7]] * self.L                       # …SingleProcess.py:41
-        self.share_observation_space = [[self.W + 2]]                 # :45
+        self.sob_dim = 2 * self.W + 2 if self.shannon else self.W + 2
+        self.share_observation_space = [[self.sob_dim]]               # :45
         self.action_space = [Action_Space(2, semi_index=-1, extra=True)]   # :48-49
-        cfg = _cabi.EnvCfg(self.N, self.W, int(seed) & 0xFFFFFFFFFFFFFFFF, int(env_offset), int(bool(double_reset)))
+        cfg = _cabi.EnvCfg(self.N, self.W, int(seed) & 0xFFFFFFFFFFFFFFFF, int(env_offset), int(bool(double_reset)), int(self.shannon))
         h = ctypes.c_void_p()
         with torch.cuda.device(self.device):
             _cabi.check(_cabi.lib().dcml_env_create(ctypes.byref(cfg), self.base_workload.ctypes.data_as(ctypes.c_void_p),
@@ -92,7 +94,7 @@ class DcmlVecEnv:
         self._h = h
         f32 = dict(dtype=torch.float32, device=self.device)
         self.obs = torch.empty(self.N, self.L, 7, **f32)
-        self.sob = torch.empty(self.N, self.W + 2, **f32)
+        self.sob = torch.empty(self.N, self.sob_dim, **f32)
         self.ava = torch.empty(self.N, self.L, 2, **f32)
         self.reward = torch.empty(self.N, **f32)
         self.done = torch.empty(self.N, dtype=torch.uint8, device=self.device)
@@ -128,7 +130,7 @@ class DcmlVecEnv:
         return self.obs, self.share_obs_view(), self.reward, self.done, self.delay, self.payment, self.ava
 
     def share_obs_view(self):
-        return self.sob.unsqueeze(1).expand(self.N, self.L, self.W + 2)
+        return self.sob.unsqueeze(1).expand(self.N, self.L, self.sob_dim)
 
     def set_context(self, R=None, C=None, worker_pr=None, n_disabled=None):
         """Preset contexts (Env(preset=True) / modify_preset); arrays per env, None keeps the current value."""
@@ -156,7 +158,7 @@ class DcmlVecEnv:
         dt = self.host_dtype
         obs = self._host["obs"].numpy().astype(dt)
         row = self._host["sob"].numpy().astype(dt)[:, None, :]
-        sob = np.repeat(row, self.L, axis=1) if self.replicate_share_obs else np.broadcast_to(row, (self.N, self.L, self.W + 2))
+        sob = np.repeat(row, self.L, axis=1) if self.replicate_share_obs else np.broadcast_to(row, (self.N, self.L, self.sob_dim))
         ava = self._host["ava"].numpy().astype(np.int64 if dt == np.float64 else dt)
         return obs, sob, ava
 

@@ -25,6 +25,8 @@ R_MIN, R_MAX, C_MIN, C_MAX = 2 ** 10, 2 ** 20, 2 ** 5, 2 ** 10     # MASTER:6-9
 R_HI = round(R_MAX * 1.1)         # MASTER:47
 C_HI = round(C_MAX * 1.1)         # MASTER:48
 ALPHA, BETA = 99, 1               # DCML_ENV_Functions.py:15-16
+NOISE = 10 ** (-50 / 10)           # Shannon.py:9
+B_TOTAL = 100 * 10 ** 9            # DCML_Master.py:29
 RETRY_CAP = 4096                  # guard for the geometric loops (Pr <= 0.95 -> P(n>4096) ~ 1e-91)
 SLOT_CAP = 4096                   # guard for the compute loop
 
@@ -80,13 +82,28 @@ class _Draws:
         x = px.philox4x32(self.env, self.step, (np.uint64(px.S_WORKER) << np.uint64(16)) | w, r, self.seed)
         return px.u01(x[0]), x[1].astype(np.int64)
 
+    def shannon_block(self, r):
+        """-> (master power uniform, worker power uniforms (W,), distance uniforms (W,))"""
+        w = np.arange(self.W, dtype=np.uint64)
+        x = px.philox4x32(self.env, self.step, (np.uint64(px.S_WORKER) << np.uint64(16)) | w, r, self.seed)
+        pm = float(px.u01(px.block(self.seed, self.env, self.step, px.S_RESET, 0, 16 * r + 2)[0]))
+        return pm, px.u01(x[2]), px.u01(x[3])
+
 
 def jitter_workload(base, u):
     """WORKER:39,111  clip(base * uniform(0.8, 1.2), 0, 1); numpy's uniform is low + (high-low)*u."""
     return np.clip(base * (0.8 + (1.2 - 0.8) * u), 0, 1)
 
 
-def process(lw, Pr, r, c, arrive, draw, w):
+def shannon_rates(n_workers, master_power, worker_power, distance):
+    """Master.get_transmission_rate / Shannon.upload, .download (DCML_Master.py:41-45, Shannon.py:14-21)."""
+    B = B_TOTAL / n_workers
+    down = B * (np.log2(1 + (master_power * (distance ** -4)) / NOISE))
+    up = B * (np.log2(1 + (worker_power * (distance ** -4)) / NOISE))
+    return up, down
+
+
+def process(lw, Pr, r, c, arrive, draw, w, DATA_RATE=DATA_RATE):
     """WORKER:46-112.  -> (n_retry, delay, prices list).  ``lw`` is the worker's 20-slot local
     workload (``local_workload`` is two copies of it, WORKER:131-133, indexed modulo 20)."""
     cost = math.ceil((9 * r - 3) * c) / FREQUENCY                                # WORKER:49-50
@@ -130,8 +147,11 @@ class DcmlEnvOracle:
     ``reset() -> (obs, share_obs, ava)``, ``step(actions) -> (obs, share_obs, rews, dones, infos, ava)``.
     ``double_reset`` reproduces ShareDummyVecEnv's second reset on done (VEC:730-736)."""
 
-    def __init__(self, n_envs, n_workers, base_workload=None, seed=1, double_reset=True, env0=0):
+    def __init__(self, n_envs, n_workers, base_workload=None, seed=1, double_reset=True, env0=0, shannon=False):
         self.B, self.W, self.L = n_envs, n_workers, n_workers + 1
+        self.shannon = shannon
+        self.rate_down = np.full((n_envs, n_workers), float(DATA_RATE))     # BASE:28-33 NON_SHANNON_DATA_RATE
+        self.rate_up = np.full((n_envs, n_workers), float(DATA_RATE))
         self.seed, self.env0, self.double_reset = seed, env0, double_reset
         self.base = synthetic_workloads(n_workers) if base_workload is None else np.asarray(base_workload, np.float64)
         assert self.base.shape == (self.W, PERIOD)
@@ -148,7 +168,7 @@ class DcmlEnvOracle:
         self.disabled = np.zeros((self.B, self.W), bool)
         self.n_agents = self.L
         self.observation_space = [[7]] * self.L
-        self.share_observation_space = [[self.W + 2]]
+        self.share_observation_space = [[2 * self.W + 2 if shannon else self.W + 2]]
 
     # ---- reset (ENV:157-274, MASTER:46-56, WORKER:114-135) -------------------------------
     def _reset_env(self, e, draw, r):
@@ -164,6 +184,10 @@ class DcmlEnvOracle:
         dis = np.zeros(W, bool)
         dis[order[: self.k_dis[e]]] = True
         self.disabled[e] = dis
+        if self.shannon:                                                          # BASE:18-27 (shannon_enable=True)
+            pm, pw, d = draw.shannon_block(r)
+            up, down = shannon_rates(W, 50 + (60 - 50) * pm, 10 + (20 - 10) * pw, 10 + (100 - 10) * d)
+            self.rate_up[e], self.rate_down[e] = up, down
 
     def observe(self, e):
         """ENV:180-271 -> obs (L,7), share_obs row (W+2,), ava (L,2)."""
@@ -192,7 +216,10 @@ class DcmlEnvOracle:
             prev7 = row[6]
             obs[i] = row
         obs[W] = [Rn, Cn, sums[0] / n_en, sums[1] / n_en, sums[2] / n_en, sum_pr / n_en, 1.1]   # ENV:235-239
-        sob = np.concatenate([[Rn, Cn], self.Pr[e]])                              # ENV:252-253
+        if self.shannon:
+            sob = np.concatenate([[Rn, Cn], self.rate_up[e] / 10 ** 7, self.rate_down[e] / 10 ** 7])   # ENV:248-250
+        else:
+            sob = np.concatenate([[Rn, Cn], self.Pr[e]])                          # ENV:252-253
         return obs, sob, ava
 
     def _observe_all(self):
@@ -227,7 +254,7 @@ class DcmlEnvOracle:
         jit = draw.jitter()
         if N == 0:                                                                # ENV:81-92
             r = math.ceil(R / 1)
-            _, delay, prices = process(self.lw[e, 0], self.Pr[e, 0], r, C, arrive, draw, 0)
+            _, delay, prices = process(self.lw[e, 0], self.Pr[e, 0], r, C, arrive, draw, 0, self.rate_down[e, 0])
             self.lw[e, 0] = jitter_workload(self.base[0], jit[0])
             reward = 1.5 * (-(delay * ALPHA) - (prices[-1] * BETA))
             return reward, delay, prices[-1]
@@ -236,7 +263,7 @@ class DcmlEnvOracle:
         r = math.ceil(R / K)                                                      # MASTER:39-40
         delays, costs = [], []
         for i in range(W):                                                        # ENV:106-111
-            _, dl, pr = process(self.lw[e, i], self.Pr[e, i], r, C, arrive, draw, i)
+            _, dl, pr = process(self.lw[e, i], self.Pr[e, i], r, C, arrive, draw, i, self.rate_down[e, i])
             delays.append(dl)
             costs.append(pr)
         self.lw[e] = jitter_workload(self.base, jit)                              # WORKER:111

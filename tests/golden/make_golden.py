@@ -113,12 +113,12 @@ class _Ctx:
     pass
 
 
-def gen_env(out, W, B, steps, seed, real_workloads):
+def gen_env(out, W, B, steps, seed, real_workloads, shannon=False):
     _ref_paths()
     import DCML_ENVs.DCML_utils.DCML_Config as cfg
-    if W != 100:                                   # constants are star-imported
+    if W != 100 or shannon:                        # constants are star-imported
         cfg.WORKER_NUMBER_MAX = W
-        cfg.SOB_DIM = W + 2
+        cfg.SOB_DIM = 2 * W + 2 if shannon else W + 2
     from oracle import philox as px
     from oracle import env_oracle as eo
 
@@ -160,6 +160,9 @@ def gen_env(out, W, B, steps, seed, real_workloads):
     class PyRandom:
         @staticmethod
         def uniform(a, b):
+            if (a, b) == (50, 60):                  # master transmit power, DCML_Master.py:42
+                pm, _, _ = draw().shannon_block(ctx.r.get(ctx.e, 0))
+                return a + (b - a) * pm
             if b == 1:                              # geometric retry draw, Worker.process
                 v = draw().retry(ctx.w, ctx.k)
                 ctx.k += 1
@@ -197,6 +200,10 @@ def gen_env(out, W, B, steps, seed, real_workloads):
             if (lo, hi) == (0, 0.95):
                 u, _ = draw().worker_block(ctx.r.get(ctx.e, 0))
                 return lo + (hi - lo) * u
+            if (lo, hi) == (10, 20):                # worker transmit power, DCML_Basic_Env.py:20
+                return lo + (hi - lo) * draw().shannon_block(ctx.r.get(ctx.e, 0))[1]
+            if (lo, hi) == (10, 100):               # distances, DCML_Master.py:43
+                return lo + (hi - lo) * draw().shannon_block(ctx.r.get(ctx.e, 0))[2]
             raise AssertionError(("unexpected np.random.uniform", lo, hi, size))
 
         @staticmethod
@@ -256,6 +263,30 @@ def gen_env(out, W, B, steps, seed, real_workloads):
             return env
         return fn
 
+    if shannon:
+        # Shannon links (dormant in the shipped config): only an explicit reset(shannon_enable=True) and the
+        # step that follows it see Shannon rates (Env.step re-resets without the flag, ENV:139).
+        L = W + 1
+        res = {"W": W, "B": B, "seed": seed, "base": base}
+        rng = np.random.RandomState(seed + 5)
+        keys = ("obs0", "sob0", "ava0", "act1", "rew1", "delay1", "pay1", "done1")
+        acc = {k: [] for k in keys}
+        for e in range(B):
+            ctx.t = 0                               # construction jitter and the explicit reset are step-0 draws
+            env = make(e)()
+            ctx.r[e] = 0
+            obs, sob, ava = env.reset(shannon_enable=True)
+            assert sob.shape == (L, 2 * W + 2)
+            sel = (rng.uniform(size=W) < 0.6).astype(np.float32) * ava[:W, 1]
+            act = np.concatenate([sel, [np.float32(rng.uniform(0.2, 1.0))]]).astype(np.float32)
+            ctx.t = 1
+            o2, s2, rew, dones, info, a2 = env.step(act.reshape(L, 1))
+            for k, v in zip(keys, (obs, sob[0], ava, act, rew[0, 0], info[0]["delay"], info[0]["payment"], dones[0])):
+                acc[k].append(v)
+        res.update({k: np.asarray(v) for k, v in acc.items()})
+        np.savez_compressed(out, **res)
+        print("wrote", out)
+        return
     vec = ShareDummyVecEnv([make(e) for e in range(B)])
     L = W + 1
     res = {"W": W, "B": B, "steps": steps, "seed": seed, "base": base}
@@ -383,6 +414,7 @@ FAMILIES = {
     "policy_L13_discrete": lambda o: gen_policy(o, 13, 4, "trained", 6, semi=False),
     "env_W100": lambda o: gen_env(o, 100, 3, 6, 1, True),
     "env_W20": lambda o: gen_env(o, 20, 6, 8, 2, False),
+    "env_W12_shannon": lambda o: gen_env(o, 12, 8, 1, 4, False, shannon=True),
     "gae": gen_gae,
     "ppo_L11": lambda o: gen_ppo(o, 11, 6, 8),
 }

@@ -61,6 +61,33 @@ def test_env_vs_oracle_random(W, B, dbl, cuda_device):
         _close(o1, o2, "obs"); _close(s1, s2, "sob"); np.testing.assert_array_equal(a1, a2)
 
 
+def test_env_shannon_vs_reference_and_oracle(cuda_device):
+    """Shannon link rates: reset(shannon_enable=True) + the following step of the reference."""
+    from mat_dcml_b200 import DcmlVecEnv
+    g = golden("env_W12_shannon")
+    W, B = int(g["W"]), int(g["B"])
+    env = DcmlVecEnv(B, W, g["base"], seed=int(g["seed"]), shannon=True)
+    obs, sob, ava = env.reset()
+    assert sob.shape == (B, W + 1, 2 * W + 2)
+    _close(obs, g["obs0"], "obs0"); _close(sob[:, 0], g["sob0"], "sob0")
+    np.testing.assert_array_equal(ava, g["ava0"])
+    _, _, rew, dones, infos, _ = env.step(g["act1"])
+    _close([i[0]["delay"] for i in infos], g["delay1"]); _close([i[0]["payment"] for i in infos], g["pay1"])
+    _close(rew[:, 0, 0], g["rew1"]); np.testing.assert_array_equal(dones[:, 0], g["done1"])
+    # several steps against the oracle with Shannon rates on every reset
+    W, B = 30, 11
+    env = DcmlVecEnv(B, W, seed=9, shannon=True)
+    ora = eo.DcmlEnvOracle(B, W, env.base_workload, seed=9, shannon=True)
+    o1, s1, a1 = env.reset(); o2, s2, a2 = ora.reset()
+    _close(o1, o2); _close(s1, s2); np.testing.assert_array_equal(a1, a2)
+    rng = np.random.RandomState(1)
+    for t in range(3):
+        act = np.concatenate([(rng.uniform(size=(B, W)) < 0.5).astype(np.float32) * a2[:, :W, 1],
+                              rng.uniform(0.1, 1.0, size=(B, 1)).astype(np.float32)], 1)[:, :, None]
+        o1, s1, r1, d1, i1, a1 = env.step(act); o2, s2, r2, d2, i2, a2 = ora.step(act)
+        _close(r1, r2); _close(o1, o2); _close(s1, s2); np.testing.assert_array_equal(d1, d2)
+
+
 def test_env_preset_context(cuda_device):
     from mat_dcml_b200 import DcmlVecEnv
     W, B = 20, 5

@@ -102,6 +102,21 @@ def test_env_matches_reference(case):
         np.testing.assert_array_equal(ava, g["ava%d" % t])
 
 
+def test_env_shannon_matches_reference():
+    g = golden("env_W12_shannon")
+    W, B = int(g["W"]), int(g["B"])
+    env = eo.DcmlEnvOracle(B, W, g["base"], seed=int(g["seed"]), shannon=True)
+    obs, sob, ava = env.reset()
+    np.testing.assert_allclose(obs, g["obs0"], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(sob[:, 0], g["sob0"], rtol=1e-12)
+    np.testing.assert_array_equal(ava, g["ava0"])
+    _, _, rew, dones, infos, _ = env.step(g["act1"])
+    np.testing.assert_allclose([i[0]["delay"] for i in infos], g["delay1"], rtol=1e-12)
+    np.testing.assert_allclose([i[0]["payment"] for i in infos], g["pay1"], rtol=1e-12)
+    np.testing.assert_allclose(rew[:, 0, 0], g["rew1"], rtol=1e-12)
+    np.testing.assert_array_equal(dones[:, 0], g["done1"])
+
+
 def _vn_from(stats):
     vn = po.ValueNormState()
     vn.running_mean[:] = float(stats[0])
