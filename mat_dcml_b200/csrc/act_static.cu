@@ -34,7 +34,8 @@
 #include "policy_fwd.h"
 
 #define MATAS_STATIC_MAX_TOKENS 2048
-// per token: 2 cross-attention query rows (64 floats each) + 8 K/V cache rows
+// per token: up to 10 rows of 64 floats -- 4 folded cross-attention query rows + 4 cached attention-input
+// rows are in use (2 spare)
 #define MATAS_STATIC_FLOATS ((size_t)MATAS_STATIC_MAX_TOKENS * 64 * (2 + 8))
 
 static __device__ __align__(256) float g_static_scratch[MATAS_STATIC_FLOATS];
@@ -84,10 +85,10 @@ extern "C" int matas_policy_act_autoregressive_static(matas_policy* p, const flo
     PolicyBufs b = {};
     b.w = v.packed;
     b.rep = const_cast<float*>(obs_rep);      // read-only here: q2_from_rep copies only when rep_in != rep
-    b.Q2[0] = scratch;
-    b.Q2[1] = scratch + n_tok * 64;
-    b.kv = scratch + (size_t)MATAS_STATIC_MAX_TOKENS * 64 * 2;   // [B env slots][8][L][64] <= MAX_TOKENS*512 floats
-    if ((rc = launch_q2_from_rep(b, obs_rep, B, L, (cudaStream_t)stream))) return rc;
+    for (int k = 0; k < 2; ++k)
+        for (int h = 0; h < 2; ++h) b.Q2p[k][h] = scratch + (size_t)(k * 2 + h) * n_tok * 64;
+    b.kv = scratch + (size_t)MATAS_STATIC_MAX_TOKENS * 64 * 4;   // [B env slots][4][L][64] <= MAX_TOKENS*256 floats
+    if ((rc = launch_q2_from_rep(b, obs_rep, B, L, (cudaStream_t)stream, 1))) return rc;
     DecodeArgs a;
     a.B = B; a.L = L; a.mode = v.mode; a.deterministic = deterministic ? 1 : 0; a.stride = stride;
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);

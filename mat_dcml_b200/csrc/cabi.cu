@@ -41,6 +41,47 @@ __global__ void pack_kernel(const float* __restrict__ flat, float* __restrict__ 
     }
 }
 
+// one folded 64x64 map of the absorbed decode attention (layout.h): built from two Linear layers
+struct FoldEntry {
+    int kind;                // 0: query map  Wt[j][i] = scale * sum_d Wa[32h+d][i] Wb[32h+d][j], bias_i = scale * sum_d Wa[32h+d][i] bb[32h+d]
+                             //    (Wa = key, Wb = query);  1: output map Wt[i][o] = sum_d Wa[o][32h+d] Wb[32h+d][i]  (Wa = proj, Wb = value)
+    int h;                   // head
+    int wa, wb, bb;          // flat-parameter offsets; kind 1: bb = value bias
+    int bp;                  // kind 1, h == 1: proj bias (the constant Wp bv + bp goes into this blob), else -1
+    int lnw, lnb;            // kind 1, h == 1: LayerNorm applied after the attention block, else -1
+    int dst;                 // packed offset of the blob
+};
+
+__global__ void fold_kernel(const float* __restrict__ flat, float* __restrict__ packed, const FoldEntry* __restrict__ tab) {
+    const FoldEntry e = tab[blockIdx.x];
+    const float scale = 0.17677669529663687f;
+    float* blob = packed + e.dst;
+    for (int idx = threadIdx.x; idx < 4096; idx += blockDim.x) {
+        const int k = idx >> 6, n = idx & 63;        // Wt[k][n]
+        float acc = 0.f;
+        if (e.kind == 0) {
+            for (int d = 0; d < 32; ++d) acc += flat[e.wa + (32 * e.h + d) * 64 + n] * flat[e.wb + (32 * e.h + d) * 64 + k];
+            acc *= scale;
+        } else {
+            for (int d = 0; d < 32; ++d) acc += flat[e.wa + n * 64 + 32 * e.h + d] * flat[e.wb + (32 * e.h + d) * 64 + k];
+        }
+        blob[idx] = acc;
+    }
+    for (int n = threadIdx.x; n < 64; n += blockDim.x) {
+        float bias = 0.f;
+        if (e.kind == 0) {
+            for (int d = 0; d < 32; ++d) bias += flat[e.wa + (32 * e.h + d) * 64 + n] * flat[e.bb + 32 * e.h + d];
+            bias *= scale;
+        } else if (e.bp >= 0) {
+            for (int d = 0; d < 64; ++d) bias += flat[e.wa + n * 64 + d] * flat[e.bb + d];      // Wp bv over both heads
+            bias += flat[e.bp + n];
+        }
+        blob[lay::B_BIAS + n] = bias;
+        blob[lay::B_LNW + n] = e.lnw >= 0 ? flat[e.lnw + n] : 1.f;
+        blob[lay::B_LNB + n] = e.lnb >= 0 ? flat[e.lnb + n] : 0.f;
+    }
+}
+
 struct matas_policy {
     matas_model_cfg cfg;
     int device;
@@ -48,11 +89,13 @@ struct matas_policy {
     long n_params;
     std::vector<PackEntry> table;
     PackEntry* d_table = nullptr;
+    std::vector<FoldEntry> folds;
+    FoldEntry* d_folds = nullptr;
     float* d_packed = nullptr;
     bool weights_set = false;
     // scratch
     long tok_cap = 0;
-    float* d_tok = nullptr;      // 17 token buffers [cap][64]
+    float* d_tok = nullptr;      // 21 token buffers [cap][64]
     size_t kv_cap = 0;
     float* d_kv = nullptr;
     PolicyBufs bufs;
@@ -186,6 +229,21 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     }
     memset(&p->tb, 0, sizeof(p->tb));
     p->n_params = build_layout(p->cfg, p->table, p->gm);
+    {
+        using namespace lay;
+        auto ix = [](int blob) { return (blob - ENC_BLOBS) / BLOB; };
+        const GradMap& g = p->gm;
+        for (int k = 0; k < 2; ++k) {
+            const int q1 = ix(dec_blob(k, DQ1)), k1 = ix(dec_blob(k, DK1)), v1 = ix(dec_blob(k, DV1)), p1 = ix(dec_blob(k, DP1));
+            const int q2 = ix(dec_q2(k)), k2 = ix(dec_blob(k, DK2)), v2 = ix(dec_blob(k, DV2)), p2 = ix(dec_blob(k, DP2));
+            for (int h = 0; h < 2; ++h) {
+                p->folds.push_back({0, h, g.w[k1], g.w[q1], g.b[q1], -1, -1, -1, fold_blob(k, FA0 + h)});
+                p->folds.push_back({1, h, g.w[p1], g.w[v1], g.b[v1], h ? g.b[p1] : -1, h ? g.lnw[p1] : -1, h ? g.lnb[p1] : -1, fold_blob(k, FB0 + h)});
+                p->folds.push_back({1, h, g.w[p2], g.w[v2], g.b[v2], h ? g.b[p2] : -1, h ? g.lnw[p2] : -1, h ? g.lnb[p2] : -1, fold_blob(k, FC0 + h)});
+                p->folds.push_back({0, h, g.w[k2], g.w[q2], g.b[q2], -1, -1, -1, fold_blob(k, FQ0 + h)});
+            }
+        }
+    }
     auto fail = [&](cudaError_t e, const char* what) {
         matas_set_error("%s: %s", what, cudaGetErrorString(e));
         matas_policy_destroy(p);
@@ -195,6 +253,9 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     if ((e = cudaMalloc(&p->d_table, p->table.size() * sizeof(PackEntry))) != cudaSuccess) return fail(e, "cudaMalloc(table)");
     if ((e = cudaMemcpy(p->d_table, p->table.data(), p->table.size() * sizeof(PackEntry), cudaMemcpyHostToDevice)) != cudaSuccess)
         return fail(e, "cudaMemcpy(table)");
+    if ((e = cudaMalloc(&p->d_folds, p->folds.size() * sizeof(FoldEntry))) != cudaSuccess) return fail(e, "cudaMalloc(folds)");
+    if ((e = cudaMemcpy(p->d_folds, p->folds.data(), p->folds.size() * sizeof(FoldEntry), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return fail(e, "cudaMemcpy(folds)");
     if ((e = cudaMalloc(&p->d_packed, lay::TOTAL_ALL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMalloc(packed)");
     if ((e = cudaMemset(p->d_packed, 0, lay::TOTAL_ALL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMemset(packed)");
     p->bufs.w = p->d_packed;
@@ -205,7 +266,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
 
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
-    cudaFree(p->d_table); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train);
+    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train);
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
@@ -224,6 +285,7 @@ int matas_policy_view(const matas_policy* p, PolicyView* v) {
 extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void* stream) {
     ARG_CHECK(p && flat, "null argument");
     pack_kernel<<<(unsigned)p->table.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_table);
+    fold_kernel<<<(unsigned)p->folds.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_folds);
     CUDA_TRY(cudaGetLastError());
     p->weights_set = true;
     return MATAS_OK;
@@ -235,12 +297,13 @@ static int alloc_tokens(matas_policy* p, long n_tok) {
     if (p->d_tok) CUDA_TRY(cudaFree(p->d_tok));
     p->d_tok = nullptr; p->tok_cap = 0;
     const long cap = n_tok + 64;
-    constexpr int NBUF = 17;
+    constexpr int NBUF = 21;
     CUDA_TRY(cudaMalloc(&p->d_tok, (size_t)cap * 64 * sizeof(float) * NBUF));
     float* f = p->d_tok;
     auto take = [&]() { float* r = f; f += cap * 64; return r; };
     PolicyBufs& b = p->bufs;
     b.X = take(); b.Q = take(); b.rep = take(); b.Q2[0] = take(); b.Q2[1] = take();
+    for (int k = 0; k < 2; ++k) for (int h = 0; h < 2; ++h) b.Q2p[k][h] = take();
     for (int k = 0; k < 2; ++k) { b.K[k] = take(); b.V[k] = take(); b.K1[k] = take(); b.V1[k] = take(); b.K2[k] = take(); b.V2[k] = take(); }
     p->tok_cap = cap;
     return MATAS_OK;
@@ -260,7 +323,7 @@ static int run_decode(matas_policy* p, const float* ava, long B, int determinist
     const int L = p->cfg.n_agent;
     int grid; long slots;
     { int rc_ = policy_decode_geometry(L, B, p->n_sm, &grid, &slots); if (rc_) return rc_; }
-    const size_t need = (size_t)slots * 8 * L * 64 * sizeof(float);
+    const size_t need = (size_t)slots * 4 * L * 64 * sizeof(float);
     if (need > p->kv_cap) {
         if (p->d_kv) CUDA_TRY(cudaFree(p->d_kv));
         p->d_kv = nullptr; p->kv_cap = 0;
@@ -359,7 +422,7 @@ extern "C" int matas_policy_get_actions(matas_policy* p, const float* obs, const
     if (rc) return rc;
     ARG_CHECK(obs && values && actions && logp && B > 0, "bad argument (B=%ld)", B);
     if ((rc = alloc_tokens(p, B * p->cfg.n_agent))) return rc;
-    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream, nullptr, 1))) return rc;
     return run_decode(p, ava, B, deterministic, stride, seed, step, env_offset, u, z, actions, logp, (cudaStream_t)stream);
 }
 
@@ -371,7 +434,7 @@ extern "C" int matas_policy_act_autoregressive(matas_policy* p, const float* obs
     if (rc) return rc;
     ARG_CHECK(obs_rep && actions && logp && B > 0, "bad argument (B=%ld)", B);
     if ((rc = alloc_tokens(p, B * p->cfg.n_agent))) return rc;
-    if ((rc = launch_q2_from_rep(p->bufs, obs_rep, B, p->cfg.n_agent, (cudaStream_t)stream))) return rc;
+    if ((rc = launch_q2_from_rep(p->bufs, obs_rep, B, p->cfg.n_agent, (cudaStream_t)stream, 1))) return rc;
     return run_decode(p, ava, B, deterministic, stride, seed, step, env_offset, u, z, actions, logp, (cudaStream_t)stream);
 }
 
@@ -382,7 +445,7 @@ extern "C" int matas_policy_act_parallel(matas_policy* p, const float* obs_rep, 
     ARG_CHECK(obs_rep && actions && logp && entropy && M > 0, "bad argument (M=%ld)", M);
     const int L = p->cfg.n_agent;
     if ((rc = alloc_tokens(p, M * L))) return rc;
-    if ((rc = launch_q2_from_rep(p->bufs, obs_rep, M, L, (cudaStream_t)stream))) return rc;
+    if ((rc = launch_q2_from_rep(p->bufs, obs_rep, M, L, (cudaStream_t)stream, 0))) return rc;
     return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream);
 }
 

@@ -41,7 +41,17 @@ constexpr int BW_BASE = TOTAL;
 constexpr int BW_MAT = 4096;
 constexpr int BW_BYTES = BW_MAT * 4;
 __host__ __device__ constexpr int bw(int blob_off) { return BW_BASE + ((blob_off - ENC_BLOBS) / BLOB) * BW_MAT; }
-constexpr int TOTAL_ALL = BW_BASE + N_BLOBS * BW_MAT;
+// decode-only folded blobs ("absorbed" attention: the cache holds the 64-float layer INPUT of each
+// attention instead of its K and V rows).  Per decoder block, per head h:
+//   FA_h : q'_h = scale * Wk_h^T (Wq_h x + bq_h)        self-attention query map          (x -> 64)
+//   FB_h : out += (Wp[:, h] Wv_h) ctx_h   (+ Wp bv + bp and LN1 in FB_1)   self-attention output map
+//   FC_h : the same for cross-attention (+ LN2 in FC_1)
+//   FQ_h : q2'_h = scale * Wk2_h^T (Wq2_h rep + bq2_h)   cross-attention query map, applied ahead of the decode
+enum { FA0 = 0, FA1, FB0, FB1, FC0, FC1, FQ0, FQ1, FOLD_PER_BLOCK };
+constexpr int FOLD_BASE = BW_BASE + N_BLOBS * BW_MAT;
+__host__ __device__ constexpr int fold_blob(int blk, int which) { return FOLD_BASE + (blk * FOLD_PER_BLOCK + which) * BLOB; }
+constexpr int DEC_FOLD_STEP_BLOBS = 2 * 8 + 1;        // per block: FA0 FA1 FB0 FB1 FC0 FC1 M0 M2 ; + head.0
+constexpr int TOTAL_ALL = FOLD_BASE + 2 * FOLD_PER_BLOCK * BLOB;
 
 __host__ __device__ constexpr int enc_blob(int blk, int which) { return ENC_BLOBS + (blk * ENC_PER_BLOCK + which) * BLOB; }
 __host__ __device__ constexpr int dec_blob(int blk, int which) { return DEC_STEP + (blk * DEC_PER_BLOCK + which) * BLOB; }

@@ -88,7 +88,19 @@ __constant__ int c_seq_dec_attn2[2][6] = {
      lay::dec_blob(1, lay::DK1), lay::dec_blob(1, lay::DV1)},
     {lay::dec_blob(1, lay::DP2), lay::dec_blob(1, lay::DM0), lay::dec_blob(1, lay::DM2), lay::DEC_H0, 0, 0}};
 __constant__ int c_seq_q2[2] = {lay::dec_q2(0), lay::dec_q2(1)};
-__constant__ int c_seq_decode[lay::DEC_STEP_BLOBS];   // filled by host: DEC_STEP + i*BLOB
+// folded cross-attention query maps for the decode: q2'_h of block 0, then block 1
+__constant__ int c_seq_q2p[4] = {lay::fold_blob(0, lay::FQ0), lay::fold_blob(0, lay::FQ1), lay::fold_blob(1, lay::FQ0),
+                                 lay::fold_blob(1, lay::FQ1)};
+__constant__ int c_seq_enc_blk1_dec[8] = {lay::enc_blob(1, lay::EP), lay::enc_blob(1, lay::EM0), lay::enc_blob(1, lay::EM2),
+                                          lay::ENC_H0, lay::fold_blob(0, lay::FQ0), lay::fold_blob(0, lay::FQ1),
+                                          lay::fold_blob(1, lay::FQ0), lay::fold_blob(1, lay::FQ1)};
+// decode step: per block FA0 FA1 FB0 FB1 FC0 FC1 M0 M2, then head.0
+__constant__ int c_seq_decode[lay::DEC_FOLD_STEP_BLOBS] = {
+    lay::fold_blob(0, lay::FA0), lay::fold_blob(0, lay::FA1), lay::fold_blob(0, lay::FB0), lay::fold_blob(0, lay::FB1),
+    lay::fold_blob(0, lay::FC0), lay::fold_blob(0, lay::FC1), lay::dec_blob(0, lay::DM0), lay::dec_blob(0, lay::DM2),
+    lay::fold_blob(1, lay::FA0), lay::fold_blob(1, lay::FA1), lay::fold_blob(1, lay::FB0), lay::fold_blob(1, lay::FB1),
+    lay::fold_blob(1, lay::FC0), lay::fold_blob(1, lay::FC1), lay::dec_blob(1, lay::DM0), lay::dec_blob(1, lay::DM2),
+    lay::DEC_H0};
 
 // per-row metadata for token-parallel tiles: row r <-> token g = tile0 + r = env*L + pos
 template <int RPT>
@@ -185,7 +197,7 @@ enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_
 // -------------------------------------------------------------------------------------------------
 template <int BLK, int RPT>
 __global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int depth, int lpad) {
+enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int depth, int lpad, int for_decode) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem s = carve<RPT>(smem_raw, depth, lpad);
@@ -193,7 +205,8 @@ enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, in
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_seq_enc_blk0 : c_seq_enc_blk1, 6, 6, depth);
+    if (BLK == 1 && for_decode) ring.init(s.ring, s.bars, b.w, c_seq_enc_blk1_dec, 8, 8, depth);
+    else ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_seq_enc_blk0 : c_seq_enc_blk1, 6, 6, depth);
     token_rows<RPT>(s, tile0, n_tok, L, b.K[BLK], b.V[BLK], false);
     load_tile<RPT>(s.sX, b.X + tile0 * 64, 64, n_valid);
     load_tile<RPT>(s.sA, (tb.on ? tb.e_q[BLK] : b.Q) + tile0 * 64, 64, n_valid);
@@ -223,8 +236,16 @@ enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, in
     } else {
         store_tile<RPT>(b.rep + tile0 * 64, 64, s.sX, n_valid);
         stage<EP_GELU | EP_LN, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg, &sv4, n_valid);
-        stage<0, RPT>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
-        stage<0, RPT>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+        if (for_decode) {
+            stage<0, RPT>(ring, s.sX, b.Q2p[0][0] + tile0 * 64, 64, n_valid, rg, cg);
+            stage<0, RPT>(ring, s.sX, b.Q2p[0][1] + tile0 * 64, 64, n_valid, rg, cg);
+            __syncthreads(); ring.prefetch();
+            stage<0, RPT>(ring, s.sX, b.Q2p[1][0] + tile0 * 64, 64, n_valid, rg, cg);
+            stage<0, RPT>(ring, s.sX, b.Q2p[1][1] + tile0 * 64, 64, n_valid, rg, cg);
+        } else {
+            stage<0, RPT>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
+            stage<0, RPT>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+        }
         __syncthreads();
         if (tid < n_valid) values[tile0 + tid] = row_dot(s.sA, tid, s.sSmall) + s.sSmall[64];
     }
@@ -234,7 +255,7 @@ enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, in
 // from obs_rep, transformer_act.py:30,103,131,176): rep_in -> b.rep copy, Q2[blk] = attn2.query(rep)
 template <int RPT>
 __global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int depth, int lpad) {
+q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int depth, int lpad, int for_decode) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem s = carve<RPT>(smem_raw, depth, lpad);
@@ -242,13 +263,22 @@ q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int dept
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_seq_q2, 2, 2, depth);
+    if (for_decode) ring.init(s.ring, s.bars, b.w, c_seq_q2p, 4, 4, depth);
+    else ring.init(s.ring, s.bars, b.w, c_seq_q2, 2, 2, depth);
     load_tile<RPT>(s.sX, rep_in + tile0 * 64, 64, n_valid);
     __syncthreads();
     ring.prefetch();
     if (rep_in != b.rep) store_tile<RPT>(b.rep + tile0 * 64, 64, s.sX, n_valid);
-    stage<0, RPT>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
-    stage<0, RPT>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+    if (for_decode) {
+        stage<0, RPT>(ring, s.sX, b.Q2p[0][0] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.Q2p[0][1] + tile0 * 64, 64, n_valid, rg, cg);
+        __syncthreads(); ring.prefetch();
+        stage<0, RPT>(ring, s.sX, b.Q2p[1][0] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.Q2p[1][1] + tile0 * 64, 64, n_valid, rg, cg);
+    } else {
+        stage<0, RPT>(ring, s.sX, b.Q2[0] + tile0 * 64, 64, n_valid, rg, cg);
+        stage<0, RPT>(ring, s.sX, b.Q2[1] + tile0 * 64, 64, n_valid, rg, cg);
+    }
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -493,7 +523,7 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
     long my_tiles = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++my_tiles;
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_seq_decode, lay::DEC_STEP_BLOBS, (int)(my_tiles * a.n_steps * lay::DEC_STEP_BLOBS), depth);
+    ring.init(s.ring, s.bars, b.w, c_seq_decode, lay::DEC_FOLD_STEP_BLOBS, (int)(my_tiles * a.n_steps * lay::DEC_FOLD_STEP_BLOBS), depth);
     float* sEmb = s.sSmall;            // [6][64]
     float* sHead = s.sSmall + 384;     // DEC_H3 block
     int* sCode = reinterpret_cast<int*>(s.sSmall + 640);   // [TM]
@@ -503,7 +533,7 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
     ring.prefetch();
 
     const long slot0 = (long)blockIdx.x * TM;
-    const long slot_stride = 8L * L * 64;
+    const long slot_stride = 4L * L * 64;      // [blk 2][attn 2][L][64] cached attention inputs per env slot
     float* kv0 = b.kv + slot0 * slot_stride;
     const int nd = a.mode == MATAS_MODE_SEMI ? L - 1 : L;
     const float sd1 = 0.5f / (1.0f + expf(-sHead[lay::DEC_H3_LOGSTD + 1]));
@@ -534,38 +564,28 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
             }
             __syncthreads();
             for (int blk = 0; blk < 2; ++blk) {
-                float* k1 = kv0 + ((blk * 2 + 0) * 2 + 0) * (long)L * 64;
-                float* v1 = kv0 + ((blk * 2 + 0) * 2 + 1) * (long)L * 64;
-                float* k2 = kv0 + ((blk * 2 + 1) * 2 + 0) * (long)L * 64;
-                float* v2 = kv0 + ((blk * 2 + 1) * 2 + 1) * (long)L * 64;
-                // ---- self-attention over the cache --------------------------------------------------
+                float* cx1 = kv0 + (blk * 2 + 0) * (long)L * 64;     // self-attention inputs (block input x)
+                float* cx2 = kv0 + (blk * 2 + 1) * (long)L * 64;     // cross-attention key/value inputs (x after LN1)
+                // ---- self-attention: cache x_j, folded queries, attend over the cached inputs -----------
+                store_tile<RPT>(cx1 + (long)j * 64, slot_stride, s.sX, n_valid);
                 stage<0, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg);
-                stage<0, RPT>(ring, s.sX, k1 + (long)j * 64, slot_stride, n_valid, rg, cg);
-                stage<0, RPT>(ring, s.sX, v1 + (long)j * 64, slot_stride, n_valid, rg, cg);
+                stage<0, RPT>(ring, s.sX, s.sB, XS, TM, rg, cg);
                 if (tid < TM) {
-                    s.kptr[tid] = k1 + tid * slot_stride;
-                    s.vptr[tid] = v1 + tid * slot_stride;
+                    s.kptr[tid] = cx1 + tid * slot_stride;
                     s.nt[tid] = tid < n_valid ? j + 1 : 0;
                 }
                 __syncthreads(); ring.prefetch();
-                // coherent (L2) loads only: these rows were written by this kernel
-                if (j < a.phased_below) attention_phased<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
-                else attention<RPT, false>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
-                stage<EP_RES | EP_LN, RPT>(ring, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
+                attention_absorbed<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.nt, j + 1);
+                stage2<EP_RES | EP_LN, RPT>(ring, s.sA, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
-                // ---- cross-attention: keys/values from the decoder stream, query from obs_rep ------
-                stage<0, RPT>(ring, s.sX, k2 + (long)j * 64, slot_stride, n_valid, rg, cg);
-                stage<0, RPT>(ring, s.sX, v2 + (long)j * 64, slot_stride, n_valid, rg, cg);
-                load_tile<RPT>(s.sA, b.Q2[blk] + (env0 * L + j) * 64, (long)L * 64, n_valid);
-                if (tid < TM) {
-                    s.kptr[tid] = k2 + tid * slot_stride;
-                    s.vptr[tid] = v2 + tid * slot_stride;
-                }
-                __syncthreads(); ring.prefetch();
-                // coherent (L2) loads only: these rows were written by this kernel
-                if (j < a.phased_below) attention_phased<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
-                else attention<RPT, false>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, j + 1);
-                stage<EP_RES | EP_LN, RPT>(ring, s.sB, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid, s.sX, XS, TM, rg, cg);
+                // ---- cross-attention: cache x1_j, queries q2' precomputed from obs_rep --------------------
+                store_tile<RPT>(cx2 + (long)j * 64, slot_stride, s.sX, n_valid);
+                load_tile<RPT>(s.sA, b.Q2p[blk][0] + (env0 * L + j) * 64, (long)L * 64, n_valid);
+                load_tile<RPT>(s.sB, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64, n_valid);
+                if (tid < TM) s.kptr[tid] = cx2 + tid * slot_stride;
+                __syncthreads();
+                attention_absorbed<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.nt, j + 1);
+                stage2<EP_RES | EP_LN, RPT>(ring, s.sA, s.sB, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
                 stage<EP_GELU, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
@@ -675,12 +695,7 @@ int policy_decode_steps(int L, int mode, int deterministic, int stride) {
     return n;
 }
 
-int policy_init_constants() {
-    int seq[lay::DEC_STEP_BLOBS];
-    for (int i = 0; i < lay::DEC_STEP_BLOBS; ++i) seq[i] = lay::DEC_STEP + i * lay::BLOB;
-    CUDA_TRY(cudaMemcpyToSymbol(c_seq_decode, seq, sizeof(seq)));
-    return MATAS_OK;
-}
+int policy_init_constants() { return MATAS_OK; }
 
 static TrainBufs train_or_off(const TrainBufs* tb) {
     TrainBufs t;
@@ -701,23 +716,23 @@ static TrainBufs train_or_off(const TrainBufs* tb) {
     } while (0)
 
 int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
-                   const TrainBufs* tbp) {
+                   const TrainBufs* tbp, int for_decode) {
     const TrainBufs tb = train_or_off(tbp);
     GEOMETRY(L, 0);
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
     LAUNCH(enc_embed_qkv<2>, enc_embed_qkv<4>, grid, b, tb, obs, n_tok, obs_dim, depth, lpad);
-    LAUNCH((enc_block<0, 2>), (enc_block<0, 4>), grid, b, tb, values, n_tok, L, depth, lpad);
-    LAUNCH((enc_block<1, 2>), (enc_block<1, 4>), grid, b, tb, values, n_tok, L, depth, lpad);
+    LAUNCH((enc_block<0, 2>), (enc_block<0, 4>), grid, b, tb, values, n_tok, L, depth, lpad, 0);
+    LAUNCH((enc_block<1, 2>), (enc_block<1, 4>), grid, b, tb, values, n_tok, L, depth, lpad, for_decode);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
 
-int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st) {
+int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st, int for_decode) {
     GEOMETRY(L, 0);
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
-    LAUNCH(q2_from_rep<2>, q2_from_rep<4>, grid, b, rep_in, n_tok, depth, lpad);
+    LAUNCH(q2_from_rep<2>, q2_from_rep<4>, grid, b, rep_in, n_tok, depth, lpad, for_decode);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }

@@ -16,9 +16,10 @@ struct PolicyBufs {
     float* V1[2];
     float* K2[2];        // teacher-forced decoder: cross-attention keys / values per block
     float* V2[2];
-    float* Q2[2];        // attn2.query(obs_rep) per decoder block
+    float* Q2[2];        // attn2.query(obs_rep) per decoder block (teacher-forced passes)
+    float* Q2p[2][2];    // decode: folded cross-attention queries q2'_h per block and head
     float* rep;          // encoder output obs_rep
-    float* kv;           // decode K/V cache: [grid*64 env slots][blk 2][attn 2][k|v][L][64]
+    float* kv;           // decode cache: [env slots][blk 2][attn 2][L][64] layer inputs of each attention
 };
 
 // training-mode saves of the teacher-forced forward + work buffers of the backward; [n_tok][64] fp32
@@ -59,8 +60,8 @@ int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots);
 int policy_decode_steps(int L, int mode, int deterministic, int stride);
 int policy_init_constants();
 int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
-                   const TrainBufs* tb = nullptr);
-int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st);
+                   const TrainBufs* tb = nullptr, int for_decode = 0);
+int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st, int for_decode);
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
                           long B, int L, int mode, cudaStream_t st, const TrainBufs* tb = nullptr);
 int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st);

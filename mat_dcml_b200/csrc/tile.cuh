@@ -138,6 +138,50 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, c
         if (r < n_valid) *reinterpret_cast<float4*>(out + (long)r * out_stride + cg * 4) = make_float4(v0, v1, v2, v3);
     }
 }
+// Two-input stage: acc = X0 . W(blob n) + X1 . W(blob n+1); bias / LayerNorm come from the second blob.
+template <int FLAGS, int RPT = 4>
+__device__ __forceinline__ void stage2(Ring& ring, const float* __restrict__ X0, const float* __restrict__ X1,
+                                       const float* res, long res_stride, int res_valid, float* out, long out_stride,
+                                       int n_valid, int rg, int cg) {
+    float4 rr[RPT];
+    if (FLAGS & EP_RES) {
+#pragma unroll
+        for (int i = 0; i < RPT; ++i) {
+            const int r = rg * RPT + i;
+            rr[i] = r < res_valid ? *reinterpret_cast<const float4*>(res + (long)r * res_stride + cg * 4)
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    float acc[RPT][4], acc1[RPT][4];
+    const float* blob0 = ring.acquire();
+    gemm<RPT>(X0, blob0, acc, rg, cg);
+    ring.release();
+    const float* blob = ring.acquire();
+    gemm<RPT>(X1, blob, acc1, rg, cg);
+    const float4 b = *reinterpret_cast<const float4*>(blob + lay::B_BIAS + cg * 4);
+    float4 lw, lb;
+    if (FLAGS & EP_LN) {
+        lw = *reinterpret_cast<const float4*>(blob + lay::B_LNW + cg * 4);
+        lb = *reinterpret_cast<const float4*>(blob + lay::B_LNB + cg * 4);
+    }
+    ring.release();
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+        const int r = rg * RPT + i;
+        float v0 = acc[i][0] + acc1[i][0] + b.x, v1 = acc[i][1] + acc1[i][1] + b.y;
+        float v2 = acc[i][2] + acc1[i][2] + b.z, v3 = acc[i][3] + acc1[i][3] + b.w;
+        if (FLAGS & EP_RES) { v0 += rr[i].x; v1 += rr[i].y; v2 += rr[i].z; v3 += rr[i].w; }
+        if (FLAGS & EP_LN) {
+            const float mean = half_warp_sum(v0 + v1 + v2 + v3) * (1.0f / 64.0f);
+            const float d0 = v0 - mean, d1 = v1 - mean, d2 = v2 - mean, d3 = v3 - mean;
+            const float var = half_warp_sum(d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3) * (1.0f / 64.0f);
+            const float rs = rsqrtf(var + 1e-5f);
+            v0 = d0 * rs * lw.x + lb.x; v1 = d1 * rs * lw.y + lb.y; v2 = d2 * rs * lw.z + lb.z; v3 = d3 * rs * lw.w + lb.w;
+        }
+        if (r < n_valid) *reinterpret_cast<float4*>(out + (long)r * out_stride + cg * 4) = make_float4(v0, v1, v2, v3);
+    }
+}
+
 // plain stage (no residual)
 template <int FLAGS, int RPT = 4>
 __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, float* out, long out_stride, int n_valid,
@@ -356,6 +400,93 @@ __device__ __forceinline__ void attention_phased(const float* __restrict__ sQ, f
     __syncthreads();
 }
 
+
+// Absorbed attention (decode).  The cache row t of query row r is the 64-float INPUT x_t of this
+// attention (xptr[r] + t*64, written earlier by this CTA); sQ0 / sQ1 hold the folded queries q'_h
+// (scale and Wk_h^T already applied), so score_h(t) = q'_h . x_t and ctx_h = sum_t p_h(t) x_t; the
+// folded output maps turn (ctx_0, ctx_1) into the attention block's output.  One cache row serves
+// both heads.  Outputs overwrite sQ0 / sQ1 with ctx_0 / ctx_1.
+template <int RPT = 4>
+__device__ __forceinline__ void attention_absorbed(float* __restrict__ sQ0, float* __restrict__ sQ1,
+                                                   float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
+                                                   const float* const* __restrict__ xptr, const int* __restrict__ nt, int n) {
+    constexpr int TM = 16 * RPT;
+    const int tid = threadIdx.x;
+    // phase A: both heads' scores for item (row, key)
+    for (int idx = tid; idx < TM * n; idx += NT) {
+        const int r = idx / n, t = idx - r * n;
+        if (t < nt[r]) {
+            const float4* xp = reinterpret_cast<const float4*>(xptr[r] + (long)t * 64);
+            float4 x[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) x[i] = xp[i];
+            const float4* q0 = reinterpret_cast<const float4*>(sQ0 + r * XS);
+            const float4* q1 = reinterpret_cast<const float4*>(sQ1 + r * XS);
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float4 qa = q0[i], qb = q1[i];
+                a0 = fmaf(qa.x, x[i].x, a0); a1 = fmaf(qa.y, x[i].y, a1); a2 = fmaf(qa.z, x[i].z, a2); a3 = fmaf(qa.w, x[i].w, a3);
+                b0 = fmaf(qb.x, x[i].x, b0); b1 = fmaf(qb.y, x[i].y, b1); b2 = fmaf(qb.z, x[i].z, b2); b3 = fmaf(qb.w, x[i].w, b3);
+            }
+            sScore[(r * 2) * lpad + t] = (a0 + a1) + (a2 + a3);
+            sScore[(r * 2 + 1) * lpad + t] = (b0 + b1) + (b2 + b3);
+        }
+    }
+    __syncthreads();
+    // phase B: softmax numerators + 1/sum, G adjacent lanes per (row, head)
+    {
+        constexpr int G = NT / (TM * 2);
+        const int rh = tid / G, sub = tid % G;
+        const int m_n = nt[rh >> 1];
+        float* sc = sScore + rh * lpad;
+        float m = -INFINITY;
+        for (int t = sub; t < m_n; t += G) m = fmaxf(m, sc[t]);
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        float sum = 0.f;
+        for (int t = sub; t < m_n; t += G) {
+            const float e = expf(sc[t] - m);
+            sc[t] = e;
+            sum += e;
+        }
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (sub == 0) sInv[rh] = m_n > 0 ? 1.0f / sum : 0.f;
+    }
+    __syncthreads();
+    // phase C: ctx_0, ctx_1 for item (row, 4-column chunk)
+    for (int idx = tid; idx < TM * 16; idx += NT) {
+        const int r = idx >> 4, dq = idx & 15;
+        const int m_n = nt[r];
+        const float* s0 = sScore + (r * 2) * lpad;
+        const float* s1 = s0 + lpad;
+        const float* xp = xptr[r] + dq * 4;
+        float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
+        int t = 0;
+        for (; t + 4 <= m_n; t += 4) {
+            float4 x[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const float4*>(xp + (long)(t + i) * 64);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float p0 = s0[t + i], p1 = s1[t + i];
+                c0.x = fmaf(p0, x[i].x, c0.x); c0.y = fmaf(p0, x[i].y, c0.y); c0.z = fmaf(p0, x[i].z, c0.z); c0.w = fmaf(p0, x[i].w, c0.w);
+                c1.x = fmaf(p1, x[i].x, c1.x); c1.y = fmaf(p1, x[i].y, c1.y); c1.z = fmaf(p1, x[i].z, c1.z); c1.w = fmaf(p1, x[i].w, c1.w);
+            }
+        }
+        for (; t < m_n; ++t) {
+            const float4 x = *reinterpret_cast<const float4*>(xp + (long)t * 64);
+            const float p0 = s0[t], p1 = s1[t];
+            c0.x = fmaf(p0, x.x, c0.x); c0.y = fmaf(p0, x.y, c0.y); c0.z = fmaf(p0, x.z, c0.z); c0.w = fmaf(p0, x.w, c0.w);
+            c1.x = fmaf(p1, x.x, c1.x); c1.y = fmaf(p1, x.y, c1.y); c1.z = fmaf(p1, x.z, c1.z); c1.w = fmaf(p1, x.w, c1.w);
+        }
+        const float i0 = sInv[r * 2], i1 = sInv[r * 2 + 1];
+        *reinterpret_cast<float4*>(sQ0 + r * XS + dq * 4) = make_float4(c0.x * i0, c0.y * i0, c0.z * i0, c0.w * i0);
+        *reinterpret_cast<float4*>(sQ1 + r * XS + dq * 4) = make_float4(c1.x * i1, c1.y * i1, c1.z * i1, c1.w * i1);
+    }
+    __syncthreads();
+}
 
 // load a [16*RPT][64] tile from global rows (row r at src + r*stride) into a shared tile; invalid rows -> 0
 template <int RPT = 4>
