@@ -94,6 +94,8 @@ extern "C" int matas_policy_act_autoregressive_static(matas_policy* p, const flo
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
     a.seed = seed; a.step = step; a.env_offset = env_offset;
     { const char* e = getenv("MATAS_PHASED_BELOW"); a.phased_below = e ? atoi(e) : (1 << 30); }
+    { const char* e = getenv("MATAS_PREFETCH"); a.prefetch = e ? atoi(e) : 0; }
+    a.phase_cycles = nullptr;
     a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
     int grid; long slots;
     if ((rc = policy_decode_geometry(L, B, v.n_sm, &grid, &slots))) return rc;

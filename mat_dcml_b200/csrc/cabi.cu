@@ -54,7 +54,7 @@ struct FoldEntry {
 
 __global__ void fold_kernel(const float* __restrict__ flat, float* __restrict__ packed, const FoldEntry* __restrict__ tab) {
     const FoldEntry e = tab[blockIdx.x];
-    const float scale = 0.17677669529663687f;
+    const float scale = 0.17677669529663687f * 1.4426950408889634f;     // log2(e)/sqrt(32): the decode softmax uses exp2
     float* blob = packed + e.dst;
     for (int idx = threadIdx.x; idx < 4096; idx += blockDim.x) {
         const int k = idx >> 6, n = idx & 63;        // Wt[k][n]
@@ -105,6 +105,7 @@ struct matas_policy {
     long train_cap = 0;
     float* d_train = nullptr;
     long train_tokens = 0;        // > 0: the saved activations belong to a training forward of that many tokens
+    unsigned long long* d_phase = nullptr;   // decode phase profiler counters (matas_policy_decode_phases)
     // optional per-launch timing of the decode kernel (CUDA events on the launching stream)
     static constexpr int NEV = 64;
     bool timing = false;
@@ -215,8 +216,8 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     ARG_CHECK(cfg->n_agent >= 2, "n_agent %d < 2", cfg->n_agent);
     ARG_CHECK(cfg->state_dim >= 1, "state_dim %d < 1", cfg->state_dim);
     ARG_CHECK(cfg->mode == MATAS_MODE_SEMI || cfg->mode == MATAS_MODE_DISCRETE, "bad mode %d", cfg->mode);
-    int rpt, depth, lpad; size_t bytes;
-    int rc = policy_launch_geometry(cfg->n_agent, &rpt, &depth, &lpad, &bytes, 0);
+    int rpt, depth; size_t bytes;
+    int rc = policy_launch_geometry(cfg->n_agent, 1 << 20, &rpt, &depth, &bytes, 0);
     if (rc) return rc;
     matas_policy* p = new matas_policy();
     p->cfg = *cfg;
@@ -266,7 +267,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
 
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
-    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train);
+    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train); cudaFree(p->d_phase);
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
@@ -336,6 +337,8 @@ static int run_decode(matas_policy* p, const float* ava, long B, int determinist
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
     a.seed = seed; a.step = step; a.env_offset = env_offset;
     { const char* e = getenv("MATAS_PHASED_BELOW"); a.phased_below = e ? atoi(e) : (1 << 30); }
+    { const char* e = getenv("MATAS_PREFETCH"); a.prefetch = e ? atoi(e) : 0; }
+    a.phase_cycles = p->d_phase;
     a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
     if (!p->timing) return launch_decode(p->bufs, a, grid, stream);
     const int i = p->ev_next;
@@ -362,6 +365,15 @@ extern "C" int matas_policy_timing(matas_policy* p, int enable) {
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { int rc = harvest(p, i); if (rc) return rc; }
     p->timing = enable != 0;
     p->t_ms = 0.0; p->t_n = 0;
+    return MATAS_OK;
+}
+
+extern "C" int matas_policy_decode_phases(matas_policy* p, int enable, unsigned long long* out16) {
+    ARG_CHECK(p != nullptr, "null policy handle");
+    if (out16 && p->d_phase) CUDA_TRY(cudaMemcpy(out16, p->d_phase, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    if (enable && !p->d_phase) CUDA_TRY(cudaMalloc(&p->d_phase, 16 * sizeof(unsigned long long)));
+    if (p->d_phase) CUDA_TRY(cudaMemset(p->d_phase, 0, 16 * sizeof(unsigned long long)));
+    if (!enable && p->d_phase) { CUDA_TRY(cudaFree(p->d_phase)); p->d_phase = nullptr; }
     return MATAS_OK;
 }
 

@@ -26,8 +26,6 @@ struct Smem {
     float* sX;         // stream
     float* sA;
     float* sB;
-    float* sScore;     // TM*2*lpad
-    float* sInv;       // TM*2
     float* sSmall;     // 1280 floats of small params / scratch
     const float** kptr;
     const float** vptr;
@@ -36,14 +34,14 @@ struct Smem {
     uint64_t* bars;    // ring barriers
 };
 
-__host__ __device__ inline size_t smem_bytes(int tm, int depth, int lpad) {
-    size_t f = (size_t)depth * lay::BLOB + 3 * tm * XS + (size_t)tm * 2 * lpad + tm * 2 + 1280;
+__host__ __device__ inline size_t smem_bytes(int tm, int depth) {
+    size_t f = (size_t)depth * lay::BLOB + 3 * tm * XS + 1280;
     f = (f + 3) & ~(size_t)3;
     return f * 4 + tm * 8 * 2 + tm * 4 + tm * 8 * 4 + 8 * 8 + 16;
 }
 
 template <int RPT>
-__device__ inline Smem carve(unsigned char* base, int depth, int lpad) {
+__device__ inline Smem carve(unsigned char* base, int depth) {
     constexpr int TM = 16 * RPT;
     constexpr int TILE_F = TM * XS;
     Smem s;
@@ -53,8 +51,6 @@ __device__ inline Smem carve(unsigned char* base, int depth, int lpad) {
     s.sA = f; f += TILE_F;
     s.sB = f; f += TILE_F;
     s.sSmall = f; f += 1280;
-    s.sInv = f; f += TM * 2;
-    s.sScore = f; f += (size_t)TM * 2 * lpad;
     uintptr_t p = (reinterpret_cast<uintptr_t>(f) + 15) & ~(uintptr_t)15;
     s.bars = reinterpret_cast<uint64_t*>(p); p += 8 * 8;
     s.kptr = reinterpret_cast<const float**>(p); p += TM * 8;
@@ -126,11 +122,11 @@ __device__ __forceinline__ void token_rows(const Smem& s, long tile0, long n_tok
 // (ma_transformer.py:133-136,148-151 and :50-52)
 // -------------------------------------------------------------------------------------------------
 template <int RPT>
-__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_tok, int obs_dim, int depth, int lpad) {
+__global__ void __launch_bounds__(NT, 2)
+enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_tok, int obs_dim, int depth) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve<RPT>(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -196,11 +192,11 @@ enc_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_
 // cross-attention queries Q2 = attn2.query(obs_rep) for both decoder blocks (:114, :51).
 // -------------------------------------------------------------------------------------------------
 template <int BLK, int RPT>
-__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int depth, int lpad, int for_decode) {
+__global__ void __launch_bounds__(NT, 2)
+enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int depth, int for_decode) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve<RPT>(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -213,7 +209,7 @@ enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, in
     if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::ENC_H3 + i];
     __syncthreads();
     ring.prefetch();
-    attention<RPT, true>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.e_lse[BLK] + tile0 * 2 : nullptr, n_valid);
+    attention_rows<RPT, true>(s.sA, s.sB, s.kptr, s.vptr, s.nt, tb.on ? tb.e_lse[BLK] + tile0 * 2 : nullptr, n_valid);
     SaveOut sv1 = {nullptr, nullptr, nullptr}, sv2 = sv1, sv3 = sv1, sv4 = sv1;
     if (tb.on) {
         store_tile<RPT>(tb.e_y[BLK] + tile0 * 64, 64, s.sB, n_valid);
@@ -254,11 +250,11 @@ enc_block(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, in
 // cross-attention queries from a caller-supplied obs_rep (the transformer_act entry points start
 // from obs_rep, transformer_act.py:30,103,131,176): rep_in -> b.rep copy, Q2[blk] = attn2.query(rep)
 template <int RPT>
-__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int depth, int lpad, int for_decode) {
+__global__ void __launch_bounds__(NT, 2)
+q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int depth, int for_decode) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve<RPT>(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -314,11 +310,11 @@ __device__ __forceinline__ void build_emb_table(float* __restrict__ dst, const f
 // (transformer_act.py:103-111,176-181)
 // -------------------------------------------------------------------------------------------------
 template <int RPT>
-__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-dec_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, long n_tok, int L, int depth, int lpad) {
+__global__ void __launch_bounds__(NT, 2)
+dec_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, long n_tok, int L, int depth) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve<RPT>(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -349,11 +345,11 @@ dec_embed_qkv(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, lon
 // decoder block, first half: causal self-attention + proj + LN1, then K2/V2 of the result
 // (ma_transformer.py:113 and the key/value side of :114)
 template <int RPT>
-__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-dec_attn1(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, int depth, int lpad) {
+__global__ void __launch_bounds__(NT, 2)
+dec_attn1(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, int depth) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve<RPT>(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -364,7 +360,7 @@ dec_attn1(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, int depth, int
     load_tile<RPT>(s.sA, (tb.on ? tb.d_q1[blk] : b.Q) + tile0 * 64, 64, n_valid);
     __syncthreads();
     ring.prefetch();
-    attention<RPT, true>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse1[blk] + tile0 * 2 : nullptr, n_valid);
+    attention_rows<RPT, true>(s.sA, s.sB, s.kptr, s.vptr, s.nt, tb.on ? tb.d_lse1[blk] + tile0 * 2 : nullptr, n_valid);
     SaveOut sv1 = {nullptr, nullptr, nullptr};
     if (tb.on) {
         store_tile<RPT>(tb.d_y1[blk] + tile0 * 64, 64, s.sB, n_valid);
@@ -393,12 +389,12 @@ __device__ __forceinline__ void masked_logz(float l0, float l1, const float* ava
 // decoder block, second half: cross-attention (query = obs_rep) + proj + LN2(rep + .) + MLP + LN3;
 // block 0 then emits QKV1 of block 1, block 1 the logits head and the per-token log-prob / entropy.
 template <int RPT>
-__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
+__global__ void __launch_bounds__(NT, 2)
 dec_attn2(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ actions, const float* __restrict__ ava,
-          float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, int depth, int lpad) {
+          float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, int depth) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve<RPT>(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long tile0 = (long)blockIdx.x * TM;
     const int n_valid = (int)min((long)TM, n_tok - tile0);
@@ -409,7 +405,7 @@ dec_attn2(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ actions
     if (blk == 1) for (int i = tid; i < lay::DEC_H3_SIZE; i += NT) s.sSmall[i] = b.w[lay::DEC_H3 + i];
     __syncthreads();
     ring.prefetch();
-    attention<RPT, true>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.vptr, s.nt, L, tb.on ? tb.d_lse2[blk] + tile0 * 2 : nullptr, n_valid);
+    attention_rows<RPT, true>(s.sA, s.sB, s.kptr, s.vptr, s.nt, tb.on ? tb.d_lse2[blk] + tile0 * 2 : nullptr, n_valid);
     SaveOut sv1 = {nullptr, nullptr, nullptr}, sv2 = sv1, sv3 = sv1, sv4 = sv1;
     if (tb.on) {
         store_tile<RPT>(tb.d_y2[blk] + tile0 * 64, 64, s.sB, n_valid);
@@ -511,12 +507,22 @@ struct DecSched {
 // -------------------------------------------------------------------------------------------------
 // persistent KV-cached decode: one CTA owns 64 envs at a time and walks the schedule.
 // -------------------------------------------------------------------------------------------------
+// phase profiler: thread 0 of CTA 0 adds the cycles since the previous marker to slot K
+#define PHASE(K)                                                                     \
+    do {                                                                             \
+        if (a.phase_cycles && blockIdx.x == 0 && threadIdx.x == 0) {                 \
+            const long long now_ = clock64();                                        \
+            atomicAdd(a.phase_cycles + (K), (unsigned long long)(now_ - t_mark));    \
+            t_mark = now_;                                                           \
+        }                                                                            \
+    } while (0)
+
 template <int RPT>
-__global__ void __launch_bounds__(NT, RPT == 2 ? 2 : 1)
-decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
+__global__ void __launch_bounds__(NT, 2)
+decode_kernel(PolicyBufs b, DecodeArgs a, int depth) {
     constexpr int TM = 16 * RPT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem s = carve<RPT>(smem_raw, depth, lpad);
+    Smem s = carve<RPT>(smem_raw, depth);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const int L = a.L;
     const long n_tiles = (a.B + TM - 1) / TM;
@@ -532,6 +538,7 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
     __syncthreads();
     ring.prefetch();
 
+    long long t_mark = clock64();
     const long slot0 = (long)blockIdx.x * TM;
     const long slot_stride = 4L * L * 64;      // [blk 2][attn 2][L][64] cached attention inputs per env slot
     float* kv0 = b.kv + slot0 * slot_stride;
@@ -563,11 +570,13 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
                 *reinterpret_cast<float4*>(s.sX + r * XS + c * 4) = *reinterpret_cast<const float4*>(sEmb + sCode[r] * 64 + c * 4);
             }
             __syncthreads();
+            PHASE(0);
             for (int blk = 0; blk < 2; ++blk) {
                 float* cx1 = kv0 + (blk * 2 + 0) * (long)L * 64;     // self-attention inputs (block input x)
                 float* cx2 = kv0 + (blk * 2 + 1) * (long)L * 64;     // cross-attention key/value inputs (x after LN1)
                 // ---- self-attention: cache x_j, folded queries, attend over the cached inputs -----------
                 store_tile<RPT>(cx1 + (long)j * 64, slot_stride, s.sX, n_valid);
+                if (a.prefetch && blk == 0) prefetch_cache_rows<RPT>(cx1, slot_stride, n_valid, j);
                 stage<0, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg);
                 stage<0, RPT>(ring, s.sX, s.sB, XS, TM, rg, cg);
                 if (tid < TM) {
@@ -575,22 +584,32 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
                     s.nt[tid] = tid < n_valid ? j + 1 : 0;
                 }
                 __syncthreads(); ring.prefetch();
-                attention_absorbed<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.nt, j + 1);
+                PHASE(1);
+                attention_absorbed<RPT>(s.sA, s.sB, s.kptr, s.nt);
+                PHASE(2);
+                if (a.prefetch) prefetch_cache_rows<RPT>(cx2, slot_stride, n_valid, j);
                 stage2<EP_RES | EP_LN, RPT>(ring, s.sA, s.sB, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
+                PHASE(3);
                 // ---- cross-attention: cache x1_j, queries q2' precomputed from obs_rep --------------------
                 store_tile<RPT>(cx2 + (long)j * 64, slot_stride, s.sX, n_valid);
                 load_tile<RPT>(s.sA, b.Q2p[blk][0] + (env0 * L + j) * 64, (long)L * 64, n_valid);
                 load_tile<RPT>(s.sB, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64, n_valid);
                 if (tid < TM) s.kptr[tid] = cx2 + tid * slot_stride;
                 __syncthreads();
-                attention_absorbed<RPT>(s.sA, s.sB, s.sScore, s.sInv, lpad, s.kptr, s.nt, j + 1);
+                PHASE(4);
+                attention_absorbed<RPT>(s.sA, s.sB, s.kptr, s.nt);
+                PHASE(5);
                 stage2<EP_RES | EP_LN, RPT>(ring, s.sA, s.sB, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
+                PHASE(6);
+                if (a.prefetch && blk == 0) prefetch_cache_rows<RPT>(kv0 + 2 * (long)L * 64, slot_stride, n_valid, j);
                 stage<EP_GELU, RPT>(ring, s.sX, s.sA, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
+                PHASE(7);
                 stage<EP_RES | EP_LN, RPT>(ring, s.sA, s.sX, XS, TM, s.sX, XS, TM, rg, cg);
                 __syncthreads(); ring.prefetch();
+                PHASE(8);
             }
             // ---- logits head + action pick ---------------------------------------------------------
             if (st.emit) {
@@ -599,6 +618,7 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
                 ring.acquire(); ring.release();
             }
             __syncthreads(); ring.prefetch();
+            PHASE(9);
             if (st.emit && tid < n_valid) {
                 const long env = env0 + tid;
                 const long g = env * L + j;
@@ -639,6 +659,7 @@ decode_kernel(PolicyBufs b, DecodeArgs a, int depth, int lpad) {
                 }
             }
             __syncthreads();
+            PHASE(10);
         }
     }
 }
@@ -656,33 +677,42 @@ int set_smem(K kernel, size_t bytes) {
 // -------------------------------------------------------------------------------------------------
 // Tile geometry: 32-row tiles (2 rows per thread) with two CTAs per SM whenever both fit in shared
 // memory -- one CTA's attention (memory latency) then overlaps the other's GEMMs -- else 64-row tiles.
-int policy_launch_geometry(int L, int* rpt, int* depth, int* lpad, size_t* bytes, int kind) {
-    *lpad = L | 1;
-    const size_t two_per_sm = 115712;       // (228 KB - 2 x 1 KB reserved) / 2
-    // kind 0: token-parallel passes -- 64-row tiles, one CTA per SM, the rest of the SM's unified
-    //         L1/shared array caches the K/V rows that the tile's query rows share;
-    // kind 1: decode -- 32-row tiles, two CTAs per SM.  MATAS_RPT_TOKEN / MATAS_RPT_DECODE override (tuning).
+static int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 148;
+    }
+    return n;
+}
+
+int policy_launch_geometry(int L, long rows, int* rpt, int* depth, size_t* bytes, int kind) {
+    if (L > 256) {
+        matas_set_error("n_agent %d > 256 is not supported (per-env action bitset)", L);
+        return MATAS_ERR_LIMIT;
+    }
+    // Two CTAs per SM in every tile kernel (one CTA's attention / barriers overlap the other's GEMMs).
+    // kind 0: token-parallel passes; kind 1: decode.  MATAS_RPT_TOKEN / MATAS_RPT_DECODE (2 | 4) override the
+    // rows-per-thread choice for tuning: 4 -> 64-row tiles (4x4 outputs per thread), 2 -> 32-row tiles.
+    // 64-row tiles give the better GEMM (4x4 outputs per thread) but need enough tiles to fill the resident
+    // CTA slots; smaller problems use 32-row tiles (measured: C3 decode 9.8 vs 11.0 ms, 4096 x 101 13.6 vs 20.2 ms).
     const char* ov = getenv(kind == 0 ? "MATAS_RPT_TOKEN" : "MATAS_RPT_DECODE");
-    const int want = ov ? atoi(ov) : (kind == 0 ? 4 : 2);
-    if (want == 2 && smem_bytes(32, 3, *lpad) <= two_per_sm) {
-        *rpt = 2; *depth = 3; *bytes = smem_bytes(32, 3, *lpad);
-        return MATAS_OK;
-    }
-    for (int d = 4; d >= 3; --d) {
-        const size_t sb = smem_bytes(64, d, *lpad);
-        if (sb <= 232448) { *rpt = 4; *depth = d; *bytes = sb; return MATAS_OK; }
-    }
-    matas_set_error("n_agent %d needs more shared memory than a B200 SM has (max supported 201)", L);
-    return MATAS_ERR_LIMIT;
+    const long tiles64 = (rows + 63) / 64;
+    const long want = kind == 0 ? 2L * sm_count() : (3L * sm_count()) / 2;
+    *rpt = ov ? atoi(ov) : (tiles64 >= want ? 4 : 2);
+    if (*rpt != 2 && *rpt != 4) *rpt = 4;
+    *depth = 3;
+    *bytes = smem_bytes(16 * *rpt, *depth);
+    return MATAS_OK;
 }
 
 int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots) {
-    int rpt, depth, lpad; size_t bytes;
-    int rc = policy_launch_geometry(L, &rpt, &depth, &lpad, &bytes, 1);
+    int rpt, depth; size_t bytes;
+    int rc = policy_launch_geometry(L, B, &rpt, &depth, &bytes, 1);
     if (rc) return rc;
     const int tm = 16 * rpt;
     const long n_tiles = (B + tm - 1) / tm;
-    const long resident = (long)n_sm * (rpt == 2 ? 2 : 1);
+    const long resident = (long)n_sm * 2;
     *grid = (int)(n_tiles < resident ? n_tiles : resident);
     *slots = (long)*grid * tm;
     return MATAS_OK;
@@ -703,9 +733,9 @@ static TrainBufs train_or_off(const TrainBufs* tb) {
     return t;
 }
 
-#define GEOMETRY(L, KIND)                                             \
-    int rpt, depth, lpad; size_t bytes;                               \
-    { int rc_ = policy_launch_geometry(L, &rpt, &depth, &lpad, &bytes, KIND); if (rc_) return rc_; } \
+#define GEOMETRY(L, ROWS, KIND)                                       \
+    int rpt, depth; size_t bytes;                                     \
+    { int rc_ = policy_launch_geometry(L, ROWS, &rpt, &depth, &bytes, KIND); if (rc_) return rc_; } \
     const int tm = 16 * rpt
 // launch KERNEL<..., RPT> for the chosen geometry
 #define LAUNCH(KERNEL2, KERNEL4, GRID, ...)                           \
@@ -718,21 +748,21 @@ static TrainBufs train_or_off(const TrainBufs* tb) {
 int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
                    const TrainBufs* tbp, int for_decode) {
     const TrainBufs tb = train_or_off(tbp);
-    GEOMETRY(L, 0);
+    GEOMETRY(L, B * L, 0);
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
-    LAUNCH(enc_embed_qkv<2>, enc_embed_qkv<4>, grid, b, tb, obs, n_tok, obs_dim, depth, lpad);
-    LAUNCH((enc_block<0, 2>), (enc_block<0, 4>), grid, b, tb, values, n_tok, L, depth, lpad, 0);
-    LAUNCH((enc_block<1, 2>), (enc_block<1, 4>), grid, b, tb, values, n_tok, L, depth, lpad, for_decode);
+    LAUNCH(enc_embed_qkv<2>, enc_embed_qkv<4>, grid, b, tb, obs, n_tok, obs_dim, depth);
+    LAUNCH((enc_block<0, 2>), (enc_block<0, 4>), grid, b, tb, values, n_tok, L, depth, 0);
+    LAUNCH((enc_block<1, 2>), (enc_block<1, 4>), grid, b, tb, values, n_tok, L, depth, for_decode);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
 
 int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st, int for_decode) {
-    GEOMETRY(L, 0);
+    GEOMETRY(L, B * L, 0);
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
-    LAUNCH(q2_from_rep<2>, q2_from_rep<4>, grid, b, rep_in, n_tok, depth, lpad, for_decode);
+    LAUNCH(q2_from_rep<2>, q2_from_rep<4>, grid, b, rep_in, n_tok, depth, for_decode);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
@@ -740,23 +770,23 @@ int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, 
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
                           long B, int L, int mode, cudaStream_t st, const TrainBufs* tbp) {
     const TrainBufs tb = train_or_off(tbp);
-    GEOMETRY(L, 0);
+    GEOMETRY(L, B * L, 0);
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
     const int n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
-    LAUNCH(dec_embed_qkv<2>, dec_embed_qkv<4>, grid, b, tb, actions, n_tok, L, depth, lpad);
+    LAUNCH(dec_embed_qkv<2>, dec_embed_qkv<4>, grid, b, tb, actions, n_tok, L, depth);
     for (int blk = 0; blk < 2; ++blk) {
-        LAUNCH(dec_attn1<2>, dec_attn1<4>, grid, b, tb, blk, n_tok, L, depth, lpad);
-        LAUNCH(dec_attn2<2>, dec_attn2<4>, grid, b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, depth, lpad);
+        LAUNCH(dec_attn1<2>, dec_attn1<4>, grid, b, tb, blk, n_tok, L, depth);
+        LAUNCH(dec_attn2<2>, dec_attn2<4>, grid, b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, depth);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
 
 int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st) {
-    GEOMETRY(a.L, 1);
+    GEOMETRY(a.L, a.B, 1);
     (void)tm;
-    LAUNCH(decode_kernel<2>, decode_kernel<4>, grid, b, a, depth, lpad);
+    LAUNCH(decode_kernel<2>, decode_kernel<4>, grid, b, a, depth);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }

@@ -40,6 +40,8 @@ struct TrainBufs {
 struct DecodeArgs {
     long B;
     int L, mode, deterministic, stride, n_steps;
+    unsigned long long* phase_cycles;   // optional [16]: CTA 0 accumulates clock64 deltas per phase (measurement)
+    int prefetch;        // issue L2 prefetches of the cache rows ahead of each attention
     int phased_below;    // positions below this use the phased attention (short contexts), the rest the fused one
     uint64_t seed;
     uint32_t step;
@@ -55,7 +57,7 @@ struct matas_policy;
 struct PolicyView { int n_agent, mode, device, n_sm, weights_set; const float* packed; };
 int matas_policy_view(const matas_policy* p, PolicyView* v);
 
-int policy_launch_geometry(int L, int* rpt, int* depth, int* lpad, size_t* bytes, int kind);
+int policy_launch_geometry(int L, long rows, int* rpt, int* depth, size_t* bytes, int kind);
 int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots);
 int policy_decode_steps(int L, int mode, int deterministic, int stride);
 int policy_init_constants();

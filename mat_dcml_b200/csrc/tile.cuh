@@ -190,9 +190,8 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, f
 }
 
 // ---------------------------------------------------------------------------------------------
-// attention for a tile of query rows.  Row r attends to nt[r] keys K[r][t][:], V[r][t][:]
-// (t-major, 64 floats per key: head h uses columns 32h..32h+31) found at kptr[r] / vptr[r].
-// sScore: TM*2*lpad floats (lpad odd), sInv: TM*2 floats.  Three phases with CTA barriers.
+// attention over rows that live in global memory (K/V of the token-parallel passes, cached layer
+// inputs of the decode); head h uses columns 32h..32h+31 of a 64-float row.
 // ---------------------------------------------------------------------------------------------
 // K/V loads.  CACHED (token-parallel passes): the rows were written by an EARLIER kernel, so the
 // read-only path (ld.global.nc) is legal and the rows of an env are shared by all query rows of a tile.
@@ -201,289 +200,159 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, f
 // 16-byte requests a thread makes to one 128-byte row.
 template <bool CACHED> __device__ __forceinline__ float4 ld_kv(const float4* p) { return CACHED ? __ldg(p) : *p; }
 
-__device__ __forceinline__ float dot32(const float4 (&q)[8], const float4 (&k)[8]) {
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;     // four independent chains, 8 deep each
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        s0 = fmaf(q[i].x, k[i].x, s0); s1 = fmaf(q[i].y, k[i].y, s1);
-        s2 = fmaf(q[i].z, k[i].z, s2); s3 = fmaf(q[i].w, k[i].w, s3);
-    }
-    return (s0 + s1) + (s2 + s3);
-}
-
-// One (row, head) pair is owned by G = NT / (2 TM) adjacent lanes, which split its keys round-robin:
-// scores (q in registers, two key rows in flight) -> max / exp / sum with shuffles over the G lanes
-// -> P.V accumulated in registers and all-reduced over the G lanes.  No CTA barrier inside; one at
-// the end publishes sOut.  sScore holds the pair's scores (each lane only re-reads its own entries).
+// Attention for a tile of query rows over K/V rows in global memory (token-parallel passes).
+// One half-warp per query row: lane l holds columns 4l..4l+3 of the row (lanes 0-7 = head 0, lanes
+// 8-15 = head 1), so every K / V row is read coalesced (one float4 per lane, 256 B per half-warp) and
+// exactly once; the 8 lanes of a head reduce their partial dots with three shuffles and keep an
+// online softmax (running max, sum, context chunk) in registers.  The key loop is software-pipelined
+// (next 4 keys in flight).  No score buffer and no CTA barrier until sOut is published.
+// Row r attends to keys [0, nt[r]) at kptr[r] / vptr[r] (t-major, 64 floats per key).
 template <int RPT = 4, bool CACHED = false>
-__device__ __forceinline__ void attention(const float* __restrict__ sQ, float* __restrict__ sOut,
-                                          float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
-                                          const float* const* __restrict__ kptr, const float* const* __restrict__ vptr,
-                                          const int* __restrict__ nt, int nt_max, float* lse_out = nullptr,
-                                          int lse_valid = 0) {
+__device__ __forceinline__ void attention_rows(const float* __restrict__ sQ, float* __restrict__ sOut,
+                                               const float* const* __restrict__ kptr, const float* const* __restrict__ vptr,
+                                               const int* __restrict__ nt, float* lse_out = nullptr, int lse_valid = 0) {
     constexpr int TM = 16 * RPT;
-    constexpr int G = NT / (TM * 2);
-    const float scale = 0.17677669529663687f;   // 1/sqrt(32)
-    const int tid = threadIdx.x, rh = tid / G, sub = tid % G, r = rh >> 1, h = rh & 1;
-    const int n = nt[r];
-    const float4* kp = reinterpret_cast<const float4*>(kptr[r] + h * 32);
-    const float4* vp = reinterpret_cast<const float4*>(vptr[r] + h * 32);
-    float* sc = sScore + rh * lpad;
-    float m = -INFINITY;
-    {
-        float4 q[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) q[i] = *reinterpret_cast<const float4*>(sQ + r * XS + h * 32 + i * 4);
-        int t = sub;
-        for (; t + G < n; t += 2 * G) {
-            float4 k0[8], k1[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) k0[i] = ld_kv<CACHED>(kp + (long)t * 16 + i);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) k1[i] = ld_kv<CACHED>(kp + (long)(t + G) * 16 + i);
-            const float a0 = dot32(q, k0) * scale, a1 = dot32(q, k1) * scale;
-            sc[t] = a0; sc[t + G] = a1;
-            m = fmaxf(m, fmaxf(a0, a1));
-        }
-        if (t < n) {
-            float4 k0[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) k0[i] = ld_kv<CACHED>(kp + (long)t * 16 + i);
-            const float a0 = dot32(q, k0) * scale;
-            sc[t] = a0;
-            m = fmaxf(m, a0);
-        }
-    }
-#pragma unroll
-    for (int o = 1; o < G; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    float4 acc[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    float sum = 0.f;
-    {
-        int t = sub;
-        for (; t + G < n; t += 2 * G) {
-            float4 v0[8], v1[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v0[i] = ld_kv<CACHED>(vp + (long)t * 16 + i);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v1[i] = ld_kv<CACHED>(vp + (long)(t + G) * 16 + i);
-            const float p0 = expf(sc[t] - m), p1 = expf(sc[t + G] - m);
-            sum += p0 + p1;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                acc[i].x = fmaf(p0, v0[i].x, acc[i].x); acc[i].y = fmaf(p0, v0[i].y, acc[i].y);
-                acc[i].z = fmaf(p0, v0[i].z, acc[i].z); acc[i].w = fmaf(p0, v0[i].w, acc[i].w);
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                acc[i].x = fmaf(p1, v1[i].x, acc[i].x); acc[i].y = fmaf(p1, v1[i].y, acc[i].y);
-                acc[i].z = fmaf(p1, v1[i].z, acc[i].z); acc[i].w = fmaf(p1, v1[i].w, acc[i].w);
-            }
-        }
-        if (t < n) {
-            float4 v0[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v0[i] = ld_kv<CACHED>(vp + (long)t * 16 + i);
-            const float p0 = expf(sc[t] - m);
-            sum += p0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                acc[i].x = fmaf(p0, v0[i].x, acc[i].x); acc[i].y = fmaf(p0, v0[i].y, acc[i].y);
-                acc[i].z = fmaf(p0, v0[i].z, acc[i].z); acc[i].w = fmaf(p0, v0[i].w, acc[i].w);
-            }
-        }
-    }
-#pragma unroll
-    for (int o = 1; o < G; o <<= 1) {
-        sum += __shfl_xor_sync(0xffffffffu, sum, o);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            acc[i].x += __shfl_xor_sync(0xffffffffu, acc[i].x, o); acc[i].y += __shfl_xor_sync(0xffffffffu, acc[i].y, o);
-            acc[i].z += __shfl_xor_sync(0xffffffffu, acc[i].z, o); acc[i].w += __shfl_xor_sync(0xffffffffu, acc[i].w, o);
-        }
-    }
-    const float inv = n > 0 ? 1.0f / sum : 0.f;
-    // every lane holds the totals; lane `sub` stores its 8/G float4 share of the 32 outputs
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-        if (i / (8 / G) == sub)
-            *reinterpret_cast<float4*>(sOut + r * XS + h * 32 + i * 4) =
-                make_float4(acc[i].x * inv, acc[i].y * inv, acc[i].z * inv, acc[i].w * inv);
-    if (sub == 0 && lse_out && r < lse_valid) lse_out[rh] = m + logf(sum);     // [row][head], training only
-    __syncthreads();
-}
-
-// Phased variant (score items flattened over (row, head, key) -> softmax -> P.V with 8 lanes per
-// (row, head)): three CTA barriers, but every thread always has independent items, which wins when the
-// context is short (the decode's first ~64 positions) and the K/V rows stream from HBM.
-template <int RPT = 4>
-__device__ __forceinline__ void attention_phased(const float* __restrict__ sQ, float* __restrict__ sOut,
-                                          float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
-                                          const float* const* __restrict__ kptr, const float* const* __restrict__ vptr,
-                                          const int* __restrict__ nt, int nt_max, float* lse_out = nullptr,
-                                          int lse_valid = 0) {
-    constexpr int TM = 16 * RPT;
-    const int tid = threadIdx.x;
-    const float scale = 0.17677669529663687f;   // 1/sqrt(32)
-    // phase A: scores
-    for (int idx = tid; idx < TM * 2 * nt_max; idx += NT) {
-        const int t = idx % nt_max, rh = idx / nt_max, r = rh >> 1, h = rh & 1;
-        if (t < nt[r]) {
-            const float4* kp = reinterpret_cast<const float4*>(kptr[r] + (long)t * 64 + h * 32);
-            const float4* qp = reinterpret_cast<const float4*>(sQ + r * XS + h * 32);
-            float4 kk[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) kk[i] = kp[i];
-            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float4 q = qp[i];
-                s0 = fmaf(q.x, kk[i].x, s0); s1 = fmaf(q.y, kk[i].y, s1); s2 = fmaf(q.z, kk[i].z, s2); s3 = fmaf(q.w, kk[i].w, s3);
-            }
-            sScore[rh * lpad + t] = ((s0 + s1) + (s2 + s3)) * scale;
-        }
-    }
-    __syncthreads();
-    // phase B: softmax numerators + 1/sum; G = NT / (2 TM) adjacent lanes share one (row, head)
-    {
-        constexpr int G = NT / (TM * 2);
-        const int rh = tid / G, sub = tid % G;
-        const int n = nt[rh >> 1];
-        float* sc = sScore + rh * lpad;
-        float m = -INFINITY;
-        for (int t = sub; t < n; t += G) m = fmaxf(m, sc[t]);
-#pragma unroll
-        for (int o = 1; o < G; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        float sum = 0.f;
-        for (int t = sub; t < n; t += G) {
-            const float e = expf(sc[t] - m);
-            sc[t] = e;
-            sum += e;
-        }
-#pragma unroll
-        for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        if (sub == 0) {
-            sInv[rh] = n > 0 ? 1.0f / sum : 0.f;
-            if (lse_out && (rh >> 1) < lse_valid) lse_out[rh] = m + logf(sum);
-        }
-    }
-    __syncthreads();
-    // phase C: P.V  (8 threads per (row, head), 4 dims each)
-    for (int idx = tid; idx < TM * 2 * 8; idx += NT) {
-        const int dq = idx & 7, rh = idx >> 3, r = rh >> 1, h = rh & 1;
-        const int n = nt[r];
-        const float* sc = sScore + rh * lpad;
-        const float* vp = vptr[r] + h * 32 + dq * 4;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        int t = 0;
-        for (; t + 4 <= n; t += 4) {
-            float4 v[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const float4*>(vp + (long)(t + i) * 64);
+    const float scale = 0.17677669529663687f * 1.4426950408889634f;   // log2(e)/sqrt(32): softmax in the exp2 domain
+    const int tid = threadIdx.x, hw = tid >> 4, l = tid & 15;
+    const unsigned hmask = 0xffffu << (tid & 16);
+    for (int r = hw; r < TM; r += NT / 16) {
+        const int nr = nt[r];
+        float4 q = *reinterpret_cast<const float4*>(sQ + r * XS + l * 4);
+        q.x *= scale; q.y *= scale; q.z *= scale; q.w *= scale;
+        const float4* kp = reinterpret_cast<const float4*>(kptr[r]) + l;      // key t at kp[t * 16]
+        const float4* vp = reinterpret_cast<const float4*>(vptr[r]) + l;
+        float m = -INFINITY, sum = 0.f;
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+        auto batch = [&](const float4 (&k)[4], const float4 (&v)[4], int t0) {
+            float s[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const float p = sc[t + i];
-                acc.x = fmaf(p, v[i].x, acc.x); acc.y = fmaf(p, v[i].y, acc.y);
-                acc.z = fmaf(p, v[i].z, acc.z); acc.w = fmaf(p, v[i].w, acc.w);
+                float p = q.x * k[i].x + q.y * k[i].y + q.z * k[i].z + q.w * k[i].w;
+                p += __shfl_xor_sync(hmask, p, 4);
+                p += __shfl_xor_sync(hmask, p, 2);
+                p += __shfl_xor_sync(hmask, p, 1);
+                s[i] = t0 + i < nr ? p : -INFINITY;
             }
+            const float n = fmaxf(m, fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])));
+            const float a = exp2f(m - n);                   // 2^(-inf) = 0 on the first batch
+            sum *= a; c.x *= a; c.y *= a; c.z *= a; c.w *= a;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float p = exp2f(s[i] - n);
+                sum += p;
+                c.x = fmaf(p, v[i].x, c.x); c.y = fmaf(p, v[i].y, c.y); c.z = fmaf(p, v[i].z, c.z); c.w = fmaf(p, v[i].w, c.w);
+            }
+            m = n;
+        };
+        auto fetch = [&](float4 (&k)[4], float4 (&v)[4], int t0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const bool ok = t0 + i < nr;
+                k[i] = ok ? ld_kv<CACHED>(kp + (long)(t0 + i) * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+                v[i] = ok ? ld_kv<CACHED>(vp + (long)(t0 + i) * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        };
+        float4 ka[4], va[4], kb[4], vb[4];
+        fetch(ka, va, 0);
+        for (int t0 = 0; t0 < nr; t0 += 8) {
+            fetch(kb, vb, t0 + 4);
+            batch(ka, va, t0);
+            fetch(ka, va, t0 + 8);
+            if (t0 + 4 < nr) batch(kb, vb, t0 + 4);
         }
-        for (; t < n; ++t) {
-            const float4 v = *reinterpret_cast<const float4*>(vp + (long)t * 64);
-            const float p = sc[t];
-            acc.x = fmaf(p, v.x, acc.x); acc.y = fmaf(p, v.y, acc.y); acc.z = fmaf(p, v.z, acc.z); acc.w = fmaf(p, v.w, acc.w);
-        }
-        const float inv = sInv[rh];
-        *reinterpret_cast<float4*>(sOut + r * XS + h * 32 + dq * 4) =
-            make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+        const float inv = nr > 0 ? 1.0f / sum : 0.f;
+        *reinterpret_cast<float4*>(sOut + r * XS + l * 4) = make_float4(c.x * inv, c.y * inv, c.z * inv, c.w * inv);
+        // natural-log log-sum-exp of the scaled scores (m is in log2 units), training only
+        if ((l & 7) == 0 && lse_out && r < lse_valid) lse_out[r * 2 + (l >> 3)] = m * 0.6931471805599453f + logf(sum);
     }
     __syncthreads();
 }
 
+// L2 prefetch of the first n_rows cache rows (256 B each) of every valid env slot of the tile: issued
+// ahead of the GEMM stages that precede an attention, so its loads find the rows in L2 instead of HBM.
+template <int RPT>
+__device__ __forceinline__ void prefetch_cache_rows(const float* base, long slot_stride, int n_valid, int n_rows) {
+    const int lines = n_rows * 2;       // 128-byte lines per env
+    for (int idx = threadIdx.x; idx < n_valid * lines; idx += NT) {
+        const int r = idx / lines, l = idx - r * lines;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (long)r * slot_stride + l * 32));
+    }
+}
 
 // Absorbed attention (decode).  The cache row t of query row r is the 64-float INPUT x_t of this
 // attention (xptr[r] + t*64, written earlier by this CTA); sQ0 / sQ1 hold the folded queries q'_h
-// (scale and Wk_h^T already applied), so score_h(t) = q'_h . x_t and ctx_h = sum_t p_h(t) x_t; the
+// (log2(e)/sqrt(32) and Wk_h^T already applied: exp2-domain scores), so score_h(t) = q'_h . x_t and
+// ctx_h = sum_t p_h(t) x_t; the
 // folded output maps turn (ctx_0, ctx_1) into the attention block's output.  One cache row serves
 // both heads.  Outputs overwrite sQ0 / sQ1 with ctx_0 / ctx_1.
 template <int RPT = 4>
 __device__ __forceinline__ void attention_absorbed(float* __restrict__ sQ0, float* __restrict__ sQ1,
-                                                   float* __restrict__ sScore, float* __restrict__ sInv, int lpad,
-                                                   const float* const* __restrict__ xptr, const int* __restrict__ nt, int n) {
+                                                   const float* const* __restrict__ xptr, const int* __restrict__ nt) {
+    // One half-warp per env row: its 16 lanes read each 256-byte cache row coalesced (one float4 per
+    // lane, ONE pass over the cache), reduce the two heads' partial dots with shuffles, and keep an
+    // online softmax (running max / sum / context chunk) in registers.  No score buffer, no CTA barrier
+    // until the contexts are published.  (Thread-per-(row,key) scoring made every LDG.128 touch 32
+    // different 128-byte lines: ~8x the L1 wavefronts, the measured bottleneck of the v4 kernel.)
     constexpr int TM = 16 * RPT;
-    const int tid = threadIdx.x;
-    // phase A: both heads' scores for item (row, key)
-    for (int idx = tid; idx < TM * n; idx += NT) {
-        const int r = idx / n, t = idx - r * n;
-        if (t < nt[r]) {
-            const float4* xp = reinterpret_cast<const float4*>(xptr[r] + (long)t * 64);
-            float4 x[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) x[i] = xp[i];
-            const float4* q0 = reinterpret_cast<const float4*>(sQ0 + r * XS);
-            const float4* q1 = reinterpret_cast<const float4*>(sQ1 + r * XS);
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const float4 qa = q0[i], qb = q1[i];
-                a0 = fmaf(qa.x, x[i].x, a0); a1 = fmaf(qa.y, x[i].y, a1); a2 = fmaf(qa.z, x[i].z, a2); a3 = fmaf(qa.w, x[i].w, a3);
-                b0 = fmaf(qb.x, x[i].x, b0); b1 = fmaf(qb.y, x[i].y, b1); b2 = fmaf(qb.z, x[i].z, b2); b3 = fmaf(qb.w, x[i].w, b3);
-            }
-            sScore[(r * 2) * lpad + t] = (a0 + a1) + (a2 + a3);
-            sScore[(r * 2 + 1) * lpad + t] = (b0 + b1) + (b2 + b3);
-        }
-    }
-    __syncthreads();
-    // phase B: softmax numerators + 1/sum, G adjacent lanes per (row, head)
-    {
-        constexpr int G = NT / (TM * 2);
-        const int rh = tid / G, sub = tid % G;
-        const int m_n = nt[rh >> 1];
-        float* sc = sScore + rh * lpad;
-        float m = -INFINITY;
-        for (int t = sub; t < m_n; t += G) m = fmaxf(m, sc[t]);
-#pragma unroll
-        for (int o = 1; o < G; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        float sum = 0.f;
-        for (int t = sub; t < m_n; t += G) {
-            const float e = expf(sc[t] - m);
-            sc[t] = e;
-            sum += e;
-        }
-#pragma unroll
-        for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        if (sub == 0) sInv[rh] = m_n > 0 ? 1.0f / sum : 0.f;
-    }
-    __syncthreads();
-    // phase C: ctx_0, ctx_1 for item (row, 4-column chunk)
-    for (int idx = tid; idx < TM * 16; idx += NT) {
-        const int r = idx >> 4, dq = idx & 15;
-        const int m_n = nt[r];
-        const float* s0 = sScore + (r * 2) * lpad;
-        const float* s1 = s0 + lpad;
-        const float* xp = xptr[r] + dq * 4;
+    const int tid = threadIdx.x, hw = tid >> 4, l = tid & 15;
+    const unsigned hmask = 0xffffu << (tid & 16);
+    const bool hi8 = (l & 8) != 0;
+    for (int r = hw; r < TM; r += NT / 16) {
+        const int nr = nt[r];
+        const float4 q0 = *reinterpret_cast<const float4*>(sQ0 + r * XS + l * 4);
+        const float4 q1 = *reinterpret_cast<const float4*>(sQ1 + r * XS + l * 4);
+        const float4* xp = reinterpret_cast<const float4*>(xptr[r]) + l;      // row t at xp[t * 16]
+        float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
         float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
-        int t = 0;
-        for (; t + 4 <= m_n; t += 4) {
-            float4 x[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const float4*>(xp + (long)(t + i) * 64);
+        // 4 keys: dots, packed half-warp reduction (lanes 0-7 collect head 0, lanes 8-15 head 1, then swap),
+        // online-softmax update of (max, sum, context chunk) for both heads
+        auto batch = [&](const float4 (&x)[4], int t0) {
+            float s0[4], s1[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const float p0 = s0[t + i], p1 = s1[t + i];
+                const float p0 = q0.x * x[i].x + q0.y * x[i].y + q0.z * x[i].z + q0.w * x[i].w;
+                const float p1 = q1.x * x[i].x + q1.y * x[i].y + q1.z * x[i].z + q1.w * x[i].w;
+                float v = hi8 ? p1 : p0;
+                v += __shfl_xor_sync(hmask, hi8 ? p0 : p1, 8);
+                v += __shfl_xor_sync(hmask, v, 4);
+                v += __shfl_xor_sync(hmask, v, 2);
+                v += __shfl_xor_sync(hmask, v, 1);
+                const float o = __shfl_xor_sync(hmask, v, 8);
+                const bool ok = t0 + i < nr;
+                s0[i] = ok ? (hi8 ? o : v) : -INFINITY;
+                s1[i] = ok ? (hi8 ? v : o) : -INFINITY;
+            }
+            const float n0 = fmaxf(m0, fmaxf(fmaxf(s0[0], s0[1]), fmaxf(s0[2], s0[3])));
+            const float n1 = fmaxf(m1, fmaxf(fmaxf(s1[0], s1[1]), fmaxf(s1[2], s1[3])));
+            const float a0 = exp2f(m0 - n0), a1 = exp2f(m1 - n1);      // 2^(-inf) = 0 on the first batch
+            l0 *= a0; l1 *= a1;
+            c0.x *= a0; c0.y *= a0; c0.z *= a0; c0.w *= a0;
+            c1.x *= a1; c1.y *= a1; c1.z *= a1; c1.w *= a1;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float p0 = exp2f(s0[i] - n0), p1 = exp2f(s1[i] - n1);
+                l0 += p0; l1 += p1;
                 c0.x = fmaf(p0, x[i].x, c0.x); c0.y = fmaf(p0, x[i].y, c0.y); c0.z = fmaf(p0, x[i].z, c0.z); c0.w = fmaf(p0, x[i].w, c0.w);
                 c1.x = fmaf(p1, x[i].x, c1.x); c1.y = fmaf(p1, x[i].y, c1.y); c1.z = fmaf(p1, x[i].z, c1.z); c1.w = fmaf(p1, x[i].w, c1.w);
             }
+            m0 = n0; m1 = n1;
+        };
+        auto fetch = [&](float4 (&x)[4], int t0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x[i] = t0 + i < nr ? xp[(long)(t0 + i) * 16] : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        // software pipeline: the next 4 rows are in flight while the current 4 are reduced
+        float4 xa[4], xb[4];
+        fetch(xa, 0);
+        for (int t0 = 0; t0 < nr; t0 += 8) {
+            fetch(xb, t0 + 4);
+            batch(xa, t0);
+            fetch(xa, t0 + 8);
+            if (t0 + 4 < nr) batch(xb, t0 + 4);
         }
-        for (; t < m_n; ++t) {
-            const float4 x = *reinterpret_cast<const float4*>(xp + (long)t * 64);
-            const float p0 = s0[t], p1 = s1[t];
-            c0.x = fmaf(p0, x.x, c0.x); c0.y = fmaf(p0, x.y, c0.y); c0.z = fmaf(p0, x.z, c0.z); c0.w = fmaf(p0, x.w, c0.w);
-            c1.x = fmaf(p1, x.x, c1.x); c1.y = fmaf(p1, x.y, c1.y); c1.z = fmaf(p1, x.z, c1.z); c1.w = fmaf(p1, x.w, c1.w);
-        }
-        const float i0 = sInv[r * 2], i1 = sInv[r * 2 + 1];
-        *reinterpret_cast<float4*>(sQ0 + r * XS + dq * 4) = make_float4(c0.x * i0, c0.y * i0, c0.z * i0, c0.w * i0);
-        *reinterpret_cast<float4*>(sQ1 + r * XS + dq * 4) = make_float4(c1.x * i1, c1.y * i1, c1.z * i1, c1.w * i1);
+        const float i0 = nr > 0 ? 1.0f / l0 : 0.f, i1 = nr > 0 ? 1.0f / l1 : 0.f;
+        *reinterpret_cast<float4*>(sQ0 + r * XS + l * 4) = make_float4(c0.x * i0, c0.y * i0, c0.z * i0, c0.w * i0);
+        *reinterpret_cast<float4*>(sQ1 + r * XS + l * 4) = make_float4(c1.x * i1, c1.y * i1, c1.z * i1, c1.w * i1);
     }
     __syncthreads();
 }
