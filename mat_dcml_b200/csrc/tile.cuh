@@ -288,71 +288,84 @@ __device__ __forceinline__ void prefetch_cache_rows(const float* base, long slot
 template <int RPT = 4>
 __device__ __forceinline__ void attention_absorbed(float* __restrict__ sQ0, float* __restrict__ sQ1,
                                                    const float* const* __restrict__ xptr, const int* __restrict__ nt) {
-    // One half-warp per env row: its 16 lanes read each 256-byte cache row coalesced (one float4 per
-    // lane, ONE pass over the cache), reduce the two heads' partial dots with shuffles, and keep an
-    // online softmax (running max / sum / context chunk) in registers.  No score buffer, no CTA barrier
-    // until the contexts are published.  (Thread-per-(row,key) scoring made every LDG.128 touch 32
-    // different 128-byte lines: ~8x the L1 wavefronts, the measured bottleneck of the v4 kernel.)
+    // Eight lanes per env row: lane g holds columns 4g..4g+3 and 32+4g..32+4g+3 of every 64-float row, so
+    // the 8 lanes read each 256-byte cache row as two fully used 128-byte lines (coalesced, ONE pass over
+    // the cache), reduce the two heads' partial dots with 4 shuffles, and keep an online softmax (running
+    // max / sum / context chunks) in registers.  Fewer lanes per row than a half-warp halves the
+    // replicated per-lane work (shuffles, max, exp2, rescale), which is what bounds this loop (issue slots).
+    // The key loop is software-pipelined.  No score buffer, no CTA barrier until the contexts are published.
     constexpr int TM = 16 * RPT;
-    const int tid = threadIdx.x, hw = tid >> 4, l = tid & 15;
-    const unsigned hmask = 0xffffu << (tid & 16);
-    const bool hi8 = (l & 8) != 0;
-    for (int r = hw; r < TM; r += NT / 16) {
+    constexpr int KB = 2;                     // keys per batch (register budget: 128 per thread at 2 CTAs/SM)
+    const int tid = threadIdx.x, grp = tid >> 3, g = tid & 7;
+    const unsigned gmask = 0xffu << (tid & 24);
+    const bool up = (g & 4) != 0;
+    for (int r = grp; r < TM; r += NT / 8) {
         const int nr = nt[r];
-        const float4 q0 = *reinterpret_cast<const float4*>(sQ0 + r * XS + l * 4);
-        const float4 q1 = *reinterpret_cast<const float4*>(sQ1 + r * XS + l * 4);
-        const float4* xp = reinterpret_cast<const float4*>(xptr[r]) + l;      // row t at xp[t * 16]
+        const float4 qa0 = *reinterpret_cast<const float4*>(sQ0 + r * XS + g * 4);
+        const float4 qb0 = *reinterpret_cast<const float4*>(sQ0 + r * XS + 32 + g * 4);
+        const float4 qa1 = *reinterpret_cast<const float4*>(sQ1 + r * XS + g * 4);
+        const float4 qb1 = *reinterpret_cast<const float4*>(sQ1 + r * XS + 32 + g * 4);
+        const float4* xp = reinterpret_cast<const float4*>(xptr[r]) + g;      // row t: xp[t*16] and xp[t*16 + 8]
         float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-        float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
-        // 4 keys: dots, packed half-warp reduction (lanes 0-7 collect head 0, lanes 8-15 head 1, then swap),
-        // online-softmax update of (max, sum, context chunk) for both heads
-        auto batch = [&](const float4 (&x)[4], int t0) {
-            float s0[4], s1[4];
+        float4 ca0 = make_float4(0.f, 0.f, 0.f, 0.f), cb0 = ca0, ca1 = ca0, cb1 = ca0;
+        auto batch = [&](const float4 (&xa)[KB], const float4 (&xb)[KB], int t0) {
+            float s0[KB], s1[KB];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float p0 = q0.x * x[i].x + q0.y * x[i].y + q0.z * x[i].z + q0.w * x[i].w;
-                const float p1 = q1.x * x[i].x + q1.y * x[i].y + q1.z * x[i].z + q1.w * x[i].w;
-                float v = hi8 ? p1 : p0;
-                v += __shfl_xor_sync(hmask, hi8 ? p0 : p1, 8);
-                v += __shfl_xor_sync(hmask, v, 4);
-                v += __shfl_xor_sync(hmask, v, 2);
-                v += __shfl_xor_sync(hmask, v, 1);
-                const float o = __shfl_xor_sync(hmask, v, 8);
+            for (int i = 0; i < KB; ++i) {
+                const float p0 = qa0.x * xa[i].x + qa0.y * xa[i].y + qa0.z * xa[i].z + qa0.w * xa[i].w +
+                                 qb0.x * xb[i].x + qb0.y * xb[i].y + qb0.z * xb[i].z + qb0.w * xb[i].w;
+                const float p1 = qa1.x * xa[i].x + qa1.y * xa[i].y + qa1.z * xa[i].z + qa1.w * xa[i].w +
+                                 qb1.x * xb[i].x + qb1.y * xb[i].y + qb1.z * xb[i].z + qb1.w * xb[i].w;
+                // packed reduction: lanes 0-3 collect head 0, lanes 4-7 head 1, then swap the totals
+                float v = up ? p1 : p0;
+                v += __shfl_xor_sync(gmask, up ? p0 : p1, 4);
+                v += __shfl_xor_sync(gmask, v, 2);
+                v += __shfl_xor_sync(gmask, v, 1);
+                const float o = __shfl_xor_sync(gmask, v, 4);
                 const bool ok = t0 + i < nr;
-                s0[i] = ok ? (hi8 ? o : v) : -INFINITY;
-                s1[i] = ok ? (hi8 ? v : o) : -INFINITY;
+                s0[i] = ok ? (up ? o : v) : -INFINITY;
+                s1[i] = ok ? (up ? v : o) : -INFINITY;
             }
-            const float n0 = fmaxf(m0, fmaxf(fmaxf(s0[0], s0[1]), fmaxf(s0[2], s0[3])));
-            const float n1 = fmaxf(m1, fmaxf(fmaxf(s1[0], s1[1]), fmaxf(s1[2], s1[3])));
+            float n0 = m0, n1 = m1;
+#pragma unroll
+            for (int i = 0; i < KB; ++i) { n0 = fmaxf(n0, s0[i]); n1 = fmaxf(n1, s1[i]); }
             const float a0 = exp2f(m0 - n0), a1 = exp2f(m1 - n1);      // 2^(-inf) = 0 on the first batch
             l0 *= a0; l1 *= a1;
-            c0.x *= a0; c0.y *= a0; c0.z *= a0; c0.w *= a0;
-            c1.x *= a1; c1.y *= a1; c1.z *= a1; c1.w *= a1;
+            ca0.x *= a0; ca0.y *= a0; ca0.z *= a0; ca0.w *= a0; cb0.x *= a0; cb0.y *= a0; cb0.z *= a0; cb0.w *= a0;
+            ca1.x *= a1; ca1.y *= a1; ca1.z *= a1; ca1.w *= a1; cb1.x *= a1; cb1.y *= a1; cb1.z *= a1; cb1.w *= a1;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < KB; ++i) {
                 const float p0 = exp2f(s0[i] - n0), p1 = exp2f(s1[i] - n1);
                 l0 += p0; l1 += p1;
-                c0.x = fmaf(p0, x[i].x, c0.x); c0.y = fmaf(p0, x[i].y, c0.y); c0.z = fmaf(p0, x[i].z, c0.z); c0.w = fmaf(p0, x[i].w, c0.w);
-                c1.x = fmaf(p1, x[i].x, c1.x); c1.y = fmaf(p1, x[i].y, c1.y); c1.z = fmaf(p1, x[i].z, c1.z); c1.w = fmaf(p1, x[i].w, c1.w);
+                ca0.x = fmaf(p0, xa[i].x, ca0.x); ca0.y = fmaf(p0, xa[i].y, ca0.y); ca0.z = fmaf(p0, xa[i].z, ca0.z); ca0.w = fmaf(p0, xa[i].w, ca0.w);
+                cb0.x = fmaf(p0, xb[i].x, cb0.x); cb0.y = fmaf(p0, xb[i].y, cb0.y); cb0.z = fmaf(p0, xb[i].z, cb0.z); cb0.w = fmaf(p0, xb[i].w, cb0.w);
+                ca1.x = fmaf(p1, xa[i].x, ca1.x); ca1.y = fmaf(p1, xa[i].y, ca1.y); ca1.z = fmaf(p1, xa[i].z, ca1.z); ca1.w = fmaf(p1, xa[i].w, ca1.w);
+                cb1.x = fmaf(p1, xb[i].x, cb1.x); cb1.y = fmaf(p1, xb[i].y, cb1.y); cb1.z = fmaf(p1, xb[i].z, cb1.z); cb1.w = fmaf(p1, xb[i].w, cb1.w);
             }
             m0 = n0; m1 = n1;
         };
-        auto fetch = [&](float4 (&x)[4], int t0) {
+        auto fetch = [&](float4 (&xa)[KB], float4 (&xb)[KB], int t0) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) x[i] = t0 + i < nr ? xp[(long)(t0 + i) * 16] : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = 0; i < KB; ++i) {
+                const bool ok = t0 + i < nr;
+                xa[i] = ok ? xp[(long)(t0 + i) * 16] : make_float4(0.f, 0.f, 0.f, 0.f);
+                xb[i] = ok ? xp[(long)(t0 + i) * 16 + 8] : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
         };
-        // software pipeline: the next 4 rows are in flight while the current 4 are reduced
-        float4 xa[4], xb[4];
-        fetch(xa, 0);
-        for (int t0 = 0; t0 < nr; t0 += 8) {
-            fetch(xb, t0 + 4);
-            batch(xa, t0);
-            fetch(xa, t0 + 8);
-            if (t0 + 4 < nr) batch(xb, t0 + 4);
+        // software pipeline: the next KB rows are in flight while the current KB are reduced
+        float4 xa[KB], xb[KB], ya[KB], yb[KB];
+        fetch(xa, xb, 0);
+        for (int t0 = 0; t0 < nr; t0 += 2 * KB) {
+            fetch(ya, yb, t0 + KB);
+            batch(xa, xb, t0);
+            fetch(xa, xb, t0 + 2 * KB);
+            if (t0 + KB < nr) batch(ya, yb, t0 + KB);
         }
         const float i0 = nr > 0 ? 1.0f / l0 : 0.f, i1 = nr > 0 ? 1.0f / l1 : 0.f;
-        *reinterpret_cast<float4*>(sQ0 + r * XS + l * 4) = make_float4(c0.x * i0, c0.y * i0, c0.z * i0, c0.w * i0);
-        *reinterpret_cast<float4*>(sQ1 + r * XS + l * 4) = make_float4(c1.x * i1, c1.y * i1, c1.z * i1, c1.w * i1);
+        *reinterpret_cast<float4*>(sQ0 + r * XS + g * 4) = make_float4(ca0.x * i0, ca0.y * i0, ca0.z * i0, ca0.w * i0);
+        *reinterpret_cast<float4*>(sQ0 + r * XS + 32 + g * 4) = make_float4(cb0.x * i0, cb0.y * i0, cb0.z * i0, cb0.w * i0);
+        *reinterpret_cast<float4*>(sQ1 + r * XS + g * 4) = make_float4(ca1.x * i1, ca1.y * i1, ca1.z * i1, ca1.w * i1);
+        *reinterpret_cast<float4*>(sQ1 + r * XS + 32 + g * 4) = make_float4(cb1.x * i1, cb1.y * i1, cb1.z * i1, cb1.w * i1);
     }
     __syncthreads();
 }
