@@ -92,7 +92,7 @@ int matas_policy_evaluate(matas_policy* p, const float* obs, const float* ava, c
  * matas_policy_evaluate_train = matas_policy_evaluate that also keeps the activations;
  * matas_policy_evaluate_backward must directly follow it with the same batch: given dLoss/dvalues,
  * dLoss/dlogp, dLoss/dentropy [M*L] it ACCUMULATES dLoss/dparams into flat_grad (fp32, laid out like
- * the flat parameter vector; unused parameters keep zero).  n_agent <= 128. */
+ * the flat parameter vector; unused parameters keep zero).  n_agent <= 256. */
 int matas_policy_evaluate_train(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
                                 float* values, float* logp, float* entropy, void* stream);
 int matas_policy_evaluate_backward(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,

@@ -498,7 +498,7 @@ extern "C" int matas_policy_evaluate_train(matas_policy* p, const float* obs, co
     if (rc) return rc;
     ARG_CHECK(obs && actions && values && logp && entropy && M > 0, "bad argument (M=%ld)", M);
     const int L = p->cfg.n_agent;
-    if (L > 128) { matas_set_error("training supports n_agent <= 128 (got %d)", L); return MATAS_ERR_LIMIT; }
+    if (L > 256) { matas_set_error("training supports n_agent <= 256 (got %d)", L); return MATAS_ERR_LIMIT; }
     if ((rc = alloc_tokens(p, M * L))) return rc;
     if ((rc = alloc_train(p, M * L))) return rc;
     if ((rc = launch_encoder(p->bufs, obs, values, M, L, p->cfg.obs_dim, (cudaStream_t)stream, &p->tb))) return rc;

@@ -20,41 +20,31 @@ namespace {
 constexpr float HALF_LOG_2PI = 0.91893853320467274178f;
 constexpr float MASK_LOGIT = -1e10f;
 constexpr float SCALE = 0.17677669529663687f;   // 1/sqrt(32)
-constexpr int BDEPTH = 3;
+constexpr int BDEPTH = 3;          // ring depth of the 1-CTA/SM kernels
+constexpr int ADEPTH = 2;          // ring depth of bwd_attn (2 CTAs/SM)
+constexpr int NTILES = 4;
+constexpr float LOG2E = 1.4426950408889634f;
 
 struct BSmem {
-    float* ring;      // BDEPTH * BLOB
-    float* T[5];      // tiles [TM][XS]
-    float* sScore;    // TM*2*lpad
+    float* ring;      // depth * BLOB
+    float* T[NTILES]; // tiles [TM][XS]
     float* sSmall;    // 1024 floats
-    const float** p0; // per-row pointers
-    const float** p1;
-    int* r0;          // per-row ranges / metadata
-    int* r1;
-    long* env0;       // per-row first token of the env
     uint64_t* bars;
 };
 
-__host__ __device__ inline size_t bsmem_bytes(int lpad) {
-    size_t f = (size_t)BDEPTH * lay::BLOB + 5 * TILE_F + (size_t)TM * 2 * lpad + 1024;
-    f = (f + 3) & ~(size_t)3;
-    return f * 4 + TM * 8 * 3 + TM * 4 * 2 + 8 * 8 + 32;
+__host__ __device__ inline size_t bsmem_bytes(int depth) {
+    const size_t f = (size_t)depth * lay::BLOB + NTILES * TILE_F + 1024;
+    return f * 4 + 8 * 8 + 32;
 }
 
-__device__ inline BSmem bcarve(unsigned char* base, int lpad) {
+__device__ inline BSmem bcarve(unsigned char* base, int depth) {
     BSmem s;
     float* f = reinterpret_cast<float*>(base);
-    s.ring = f; f += (size_t)BDEPTH * lay::BLOB;
-    for (int i = 0; i < 5; ++i) { s.T[i] = f; f += TILE_F; }
+    s.ring = f; f += (size_t)depth * lay::BLOB;
+    for (int i = 0; i < NTILES; ++i) { s.T[i] = f; f += TILE_F; }
     s.sSmall = f; f += 1024;
-    s.sScore = f; f += (size_t)TM * 2 * lpad;
     uintptr_t p = (reinterpret_cast<uintptr_t>(f) + 15) & ~(uintptr_t)15;
-    s.bars = reinterpret_cast<uint64_t*>(p); p += 8 * 8;
-    s.p0 = reinterpret_cast<const float**>(p); p += TM * 8;
-    s.p1 = reinterpret_cast<const float**>(p); p += TM * 8;
-    s.env0 = reinterpret_cast<long*>(p); p += TM * 8;
-    s.r0 = reinterpret_cast<int*>(p); p += TM * 4;
-    s.r1 = reinterpret_cast<int*>(p);
+    s.bars = reinterpret_cast<uint64_t*>(p);
     return s;
 }
 
@@ -234,9 +224,9 @@ struct TailArgs {
 
 // [LN_F bwd -> MLP bwd ->] LN_M bwd -> residual grad -> projection bwd      (encoder E1, decoder K1 / K2b)
 __global__ void __launch_bounds__(NT, 1)
-bwd_mlp_proj(const float* __restrict__ packed, float* __restrict__ grad, TailArgs a, long n_tok, int lpad) {
+bwd_mlp_proj(const float* __restrict__ packed, float* __restrict__ grad, TailArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BSmem s = bcarve(smem_raw, lpad);
+    BSmem s = bcarve(smem_raw, BDEPTH);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long n_tiles = (n_tok + TM - 1) / TM;
     long mine = 0;
@@ -320,95 +310,104 @@ struct AttnArgs {
     int causal, L;
 };
 
-// scores for a tile of rows against the tokens [lo[r], hi[r]) of their env.
-// MODE 0 (query side): ds = p * (dY_r.V_t - D_r),  p = exp(scale q_r.K_t - lse_r)        rows are queries
-// MODE 1 (key side)  : p   = exp(scale Q_i.k_r - lse_i)                                   rows are keys
-// MODE 2 (key side)  : ds  = p * (dY_i.v_r - D_i)
-template <int MODE>
-__device__ __forceinline__ void score_pass(const BSmem& s, const AttnArgs& a, const float* __restrict__ tA,
-                                           const float* __restrict__ tB, int lpad, int span_max) {
-    const int tid = threadIdx.x;
-    for (int idx = tid; idx < TM * 2 * span_max; idx += NT) {
-        const int o = idx % span_max, rh = idx / span_max, r = rh >> 1, h = rh & 1;
-        const int t = s.r0[r] + o;
-        if (t < s.r1[r]) {
-            const long g = s.env0[r] + t;
-            const float4* ap = reinterpret_cast<const float4*>(tA + r * XS + h * 32);
-            float s1 = 0.f, s2 = 0.f;
-            if (MODE == 0) {
-                const float4* kp = reinterpret_cast<const float4*>(a.K + g * 64 + h * 32);
-                const float4* vp = reinterpret_cast<const float4*>(a.V + g * 64 + h * 32);
-                const float4* bp = reinterpret_cast<const float4*>(tB + r * XS + h * 32);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const float4 k = __ldcg(kp + i), v = __ldcg(vp + i), q = ap[i], dy = bp[i];
-                    s1 += q.x * k.x + q.y * k.y + q.z * k.z + q.w * k.w;
-                    s2 += dy.x * v.x + dy.y * v.y + dy.z * v.z + dy.w * v.w;
-                }
-                const float p = expf(s1 * SCALE - s.sSmall[768 + rh]);
-                s.sScore[rh * lpad + o] = p * (s2 - s.sSmall[896 + rh]);
-            } else {
-                const float4* qp = reinterpret_cast<const float4*>(a.Q + g * 64 + h * 32);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const float4 q = __ldcg(qp + i), k = ap[i];
-                    s1 += q.x * k.x + q.y * k.y + q.z * k.z + q.w * k.w;
-                }
-                const float p = expf(s1 * SCALE - __ldcg(a.lse + g * 2 + h));
-                if (MODE == 1) {
-                    s.sScore[rh * lpad + o] = p;
-                } else {
-                    const float4* dp = reinterpret_cast<const float4*>(a.gY + g * 64 + h * 32);
-                    const float4* vp = reinterpret_cast<const float4*>(tB + r * XS + h * 32);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 dy = __ldcg(dp + i), v = vp[i];
-                        s2 += dy.x * v.x + dy.y * v.y + dy.z * v.z + dy.w * v.w;
-                    }
-                    s.sScore[rh * lpad + o] = p * (s2 - __ldcg(a.gD + g * 2 + h));
-                }
-            }
-        }
-    }
-    __syncthreads();
+// Sum a and b over the 8 lanes of a head (lane bit 2 = `up`) with 4 shuffles instead of 6: the two
+// halves of the group reduce one value each, then swap the totals.
+__device__ __forceinline__ void head_sum2(float& a, float& b, unsigned mask, bool up) {
+    float keep = up ? b : a;
+    const float send = up ? a : b;
+    keep += __shfl_xor_sync(mask, send, 4);
+    keep += __shfl_xor_sync(mask, keep, 2);
+    keep += __shfl_xor_sync(mask, keep, 1);
+    const float other = __shfl_xor_sync(mask, keep, 4);
+    a = up ? other : keep;
+    b = up ? keep : other;
+}
+__device__ __forceinline__ float dot4(const float4& a, const float4& b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+__device__ __forceinline__ void axpy4(float4& acc, float p, const float4& v) {
+    acc.x = fmaf(p, v.x, acc.x); acc.y = fmaf(p, v.y, acc.y); acc.z = fmaf(p, v.z, acc.z); acc.w = fmaf(p, v.w, acc.w);
 }
 
-// out[r][h*32+d] = mul * sum_o score[r][h][o] * src[env0[r] + r0[r] + o][h*32+d]
-__device__ __forceinline__ void weighted_sum(const BSmem& s, const float* __restrict__ src, float* __restrict__ out, int lpad, float mul) {
-    for (int idx = threadIdx.x; idx < TM * 2 * 8; idx += NT) {
-        const int dq = idx & 7, rh = idx >> 3, r = rh >> 1, h = rh & 1;
-        const int n = s.r1[r] - s.r0[r];
-        const float* sc = s.sScore + rh * lpad;
-        const float* vp = src + (s.env0[r] + s.r0[r]) * 64 + h * 32 + dq * 4;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        int t = 0;
-        for (; t + 4 <= n; t += 4) {
-            float4 v[4];
+// Attention backward, one half-warp per row of the tile (lane l: columns 4l..4l+3, lanes 0-7 head 0,
+// lanes 8-15 head 1), every global row read coalesced; probabilities are recomputed from the saved
+// log-sum-exp, so there is no score buffer and no CTA barrier inside.
+//   query side, row = query i:  dq_i = scale * sum_t p_it (dY_i.v_t - D_i) k_t             t in [0, hi)
+//   key side,   row = key j  :  dv_j = sum_i p_ij dY_i ;  dk_j = scale * sum_i p_ij (dY_i.v_j - D_i) q_i   i in [lo, L)
+// with p = exp(scale q.k - lse) per head.
+template <int KB>
+__device__ __forceinline__ void attn_bwd_rows(const AttnArgs& a, long row0, long n_tok, float* __restrict__ sDq,
+                                              float* __restrict__ sDv, float* __restrict__ sDk) {
+    const int tid = threadIdx.x, hw = tid >> 4, l = tid & 15, h = l >> 3, L = a.L;
+    const bool up = (l & 4) != 0;
+    const unsigned hmask = 0xffffu << (tid & 16);
+    const float c2 = SCALE * LOG2E;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = hw; r < TM; r += NT / 16) {
+        const long g = row0 + r;
+        float4 dq = zero4, dv = zero4, dk = zero4;
+        if (g < n_tok) {
+            const long env = g / L, base = env * L;
+            const int pos = (int)(g - base);
+            const float4* Qe = reinterpret_cast<const float4*>(a.Q + base * 64) + l;     // row t of the env at [t * 16]
+            const float4* Ke = reinterpret_cast<const float4*>(a.K + base * 64) + l;
+            const float4* Ve = reinterpret_cast<const float4*>(a.V + base * 64) + l;
+            const float4* Ye = reinterpret_cast<const float4*>(a.gY + base * 64) + l;
+            const float* lse_e = a.lse + base * 2 + h;
+            const float* D_e = a.gD + base * 2 + h;
+            {   // ---- query side
+                const int hi = a.causal ? pos + 1 : L;
+                const float4 q = __ldg(Qe + pos * 16), dy = __ldg(Ye + pos * 16);
+                const float lse2 = __ldg(lse_e + pos * 2) * LOG2E, Dh = __ldg(D_e + pos * 2);
+                for (int t0 = 0; t0 < hi; t0 += KB) {
+                    float4 k[KB], v[KB];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(vp + (long)(t + i) * 64));
+                    for (int i = 0; i < KB; ++i) {
+                        const int t = min(t0 + i, hi - 1);
+                        k[i] = __ldg(Ke + t * 16); v[i] = __ldg(Ve + t * 16);
+                    }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float p = sc[t + i];
-                acc.x = fmaf(p, v[i].x, acc.x); acc.y = fmaf(p, v[i].y, acc.y); acc.z = fmaf(p, v[i].z, acc.z); acc.w = fmaf(p, v[i].w, acc.w);
+                    for (int i = 0; i < KB; ++i) {
+                        float s1 = dot4(q, k[i]), s2 = dot4(dy, v[i]);
+                        head_sum2(s1, s2, hmask, up);
+                        const float p = t0 + i < hi ? exp2f(fmaf(s1, c2, -lse2)) : 0.f;
+                        axpy4(dq, p * (s2 - Dh), k[i]);
+                    }
+                }
+            }
+            {   // ---- key side
+                const int lo = a.causal ? pos : 0;
+                const float4 k = __ldg(Ke + pos * 16), v = __ldg(Ve + pos * 16);
+                for (int i0 = lo; i0 < L; i0 += KB) {
+                    float4 q[KB], dy[KB];
+                    float ls[KB], dd[KB];
+#pragma unroll
+                    for (int i = 0; i < KB; ++i) {
+                        const int t = min(i0 + i, L - 1);
+                        q[i] = __ldg(Qe + t * 16); dy[i] = __ldg(Ye + t * 16);
+                        ls[i] = __ldg(lse_e + t * 2); dd[i] = __ldg(D_e + t * 2);
+                    }
+#pragma unroll
+                    for (int i = 0; i < KB; ++i) {
+                        float s1 = dot4(q[i], k), s2 = dot4(dy[i], v);
+                        head_sum2(s1, s2, hmask, up);
+                        const float p = i0 + i < L ? exp2f(fmaf(s1, c2, -ls[i] * LOG2E)) : 0.f;
+                        axpy4(dv, p, dy[i]);
+                        axpy4(dk, p * (s2 - dd[i]), q[i]);
+                    }
+                }
             }
         }
-        for (; t < n; ++t) {
-            const float4 v = __ldcg(reinterpret_cast<const float4*>(vp + (long)t * 64));
-            const float p = sc[t];
-            acc.x = fmaf(p, v.x, acc.x); acc.y = fmaf(p, v.y, acc.y); acc.z = fmaf(p, v.z, acc.z); acc.w = fmaf(p, v.w, acc.w);
-        }
-        *reinterpret_cast<float4*>(out + r * XS + h * 32 + dq * 4) = make_float4(acc.x * mul, acc.y * mul, acc.z * mul, acc.w * mul);
+        *reinterpret_cast<float4*>(sDq + r * XS + l * 4) = make_float4(dq.x * SCALE, dq.y * SCALE, dq.z * SCALE, dq.w * SCALE);
+        *reinterpret_cast<float4*>(sDv + r * XS + l * 4) = dv;
+        *reinterpret_cast<float4*>(sDk + r * XS + l * 4) = make_float4(dk.x * SCALE, dk.y * SCALE, dk.z * SCALE, dk.w * SCALE);
     }
-    __syncthreads();
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(NT, 1)
-bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a, long n_tok, int lpad) {
+__global__ void __launch_bounds__(NT, 2)
+bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BSmem s = bcarve(smem_raw, lpad);
+    BSmem s = bcarve(smem_raw, ADEPTH);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
-    const int L = a.L;
     const long n_tiles = (n_tok + TM - 1) / TM;
     long mine = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++mine;
@@ -416,77 +415,57 @@ bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a,
     if (tid < 3) sseq[tid] = a.seq[tid];
     if (a.ln >= 0) for (int i = tid; i < 128; i += NT) s.sSmall[i] = packed[a.ln + lay::B_LNW + i];
     Ring ring;
-    ring.init(s.ring, s.bars, packed, sseq, 3, (int)(mine * 3), BDEPTH, lay::BW_BYTES);
+    ring.init(s.ring, s.bars, packed, sseq, 3, (int)(mine * 3), ADEPTH, lay::BW_BYTES);
     __syncthreads();
     ring.prefetch();
+    float* sX = s.T[0];                                   // input of the projection being differentiated
+    float *sDq = s.T[1], *sDv = s.T[2], *sDk = s.T[3];
     DW dWq, dWk, dWv; dWq.zero(); dWk.zero(); dWv.zero();
     Col dbq, dbk, dbv; dbq.zero(); dbk.zero(); dbv.zero();
     for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long row0 = tile * TM;
         const int n_valid = (int)min((long)TM, n_tok - row0);
-        // ---- query side: dq -------------------------------------------------------------------
-        if (tid < TM) {
-            const long g = row0 + tid;
-            int lo = 0, hi = 0; long e0 = 0;
-            if (g < n_tok) {
-                const long env = g / L; const int pos = (int)(g - env * L);
-                e0 = env * L; lo = 0; hi = a.causal ? pos + 1 : L;
-            }
-            s.r0[tid] = lo; s.r1[tid] = hi; s.env0[tid] = e0;
-        }
-        if (tid < TM * 2) {
-            const long g = row0 + (tid >> 1);
-            s.sSmall[768 + tid] = g < n_tok ? a.lse[g * 2 + (tid & 1)] : 0.f;
-            s.sSmall[896 + tid] = g < n_tok ? a.gD[g * 2 + (tid & 1)] : 0.f;
-        }
-        load_tile(s.T[0], a.Q + row0 * 64, 64, n_valid);
-        load_tile(s.T[1], a.gY + row0 * 64, 64, n_valid);
-        __syncthreads();
-        score_pass<0>(s, a, s.T[0], s.T[1], lpad, L);
-        weighted_sum(s, a.K, s.T[2], lpad, SCALE);                    // dq -> T2
-        // ---- key side: dv, dk ------------------------------------------------------------------
-        if (tid < TM) {
-            const long g = row0 + tid;
-            int lo = 0, hi = 0;
-            if (g < n_tok) { const int pos = (int)(g - s.env0[tid]); lo = a.causal ? pos : 0; hi = L; }
-            s.r0[tid] = lo; s.r1[tid] = hi;
-        }
-        load_tile(s.T[0], a.K + row0 * 64, 64, n_valid);
-        load_tile(s.T[1], a.V + row0 * 64, 64, n_valid);
-        __syncthreads();
-        score_pass<1>(s, a, s.T[0], s.T[1], lpad, L);
-        weighted_sum(s, a.gY, s.T[3], lpad, 1.0f);                    // dv -> T3
-        score_pass<2>(s, a, s.T[0], s.T[1], lpad, L);
-        weighted_sum(s, a.Q, s.T[4], lpad, SCALE);                    // dk -> T4
+        attn_bwd_rows<4>(a, row0, n_tok, sDq, sDv, sDk);
         // ---- projections: dW, db, dX -------------------------------------------------------------
-        Frag xin, fq, fk, fv, dx;
-        if (a.ln >= 0) {
-            Frag xh;
-            frag_load_g(xh, a.xh, row0, n_valid, rg, cg);
-            ln_affine(xin, xh, s.sSmall, s.sSmall + 64, cg);
-        } else {
-            frag_load_g(xin, a.xin, row0, n_valid, rg, cg);
-        }
-        frag_store_s(xin, s.T[0], rg, cg);                             // k/v (and KIND 0: q) input
-        if (KIND == 1) load_tile(s.T[1], a.xin + row0 * 64, 64, n_valid);   // obs_rep: q input
-        frag_load_s(fq, s.T[2], rg, cg); frag_load_s(fv, s.T[3], rg, cg); frag_load_s(fk, s.T[4], rg, cg);
-        col_add(dbq, fq); col_add(dbk, fk); col_add(dbv, fv);
-        __syncthreads();
-        dw_acc(dWq, s.T[2], KIND == 1 ? s.T[1] : s.T[0], n_valid, rg, cg);
-        dw_acc(dWk, s.T[4], s.T[0], n_valid, rg, cg);
-        dw_acc(dWv, s.T[3], s.T[0], n_valid, rg, cg);
-        if (KIND == 0) {
-            gemm_dx(ring, s.T[2], dx, rg, cg, false);
-            gemm_dx(ring, s.T[4], dx, rg, cg, true);
-            gemm_dx(ring, s.T[3], dx, rg, cg, true);
-            frag_store_g(dx, a.gX, row0, n_valid, rg, cg, true);
-        } else {
-            gemm_dx(ring, s.T[2], dx, rg, cg, false);
+        Frag dx;
+        if (KIND == 1) {
+            load_tile(sX, a.xin + row0 * 64, 64, n_valid);             // obs_rep: the query input
+            __syncthreads();
+            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); }
+            dw_acc(dWq, sDq, sX, n_valid, rg, cg);
+            gemm_dx(ring, sDq, dx, rg, cg, false);
             frag_store_g(dx, a.gRep, row0, n_valid, rg, cg, true);
-            gemm_dx(ring, s.T[4], dx, rg, cg, false);
-            gemm_dx(ring, s.T[3], dx, rg, cg, true);
-            frag_store_g(dx, a.gX, row0, n_valid, rg, cg, false);
+            __syncthreads();
+            ring.prefetch();
         }
+        {
+            Frag xin;
+            if (a.ln >= 0) {
+                Frag xh;
+                frag_load_g(xh, a.xh, row0, n_valid, rg, cg);
+                ln_affine(xin, xh, s.sSmall, s.sSmall + 64, cg);
+            } else {
+                frag_load_g(xin, a.xin, row0, n_valid, rg, cg);
+            }
+            frag_store_s(xin, sX, rg, cg);                              // k/v (and KIND 0: q) input
+        }
+        __syncthreads();
+        if (KIND == 0) {
+            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); }
+            dw_acc(dWq, sDq, sX, n_valid, rg, cg);
+            gemm_dx(ring, sDq, dx, rg, cg, false);
+            __syncthreads();
+            ring.prefetch();
+        }
+        { Frag f; frag_load_s(f, sDk, rg, cg); col_add(dbk, f); }
+        dw_acc(dWk, sDk, sX, n_valid, rg, cg);
+        gemm_dx(ring, sDk, dx, rg, cg, KIND == 0);
+        __syncthreads();
+        ring.prefetch();
+        { Frag f; frag_load_s(f, sDv, rg, cg); col_add(dbv, f); }
+        dw_acc(dWv, sDv, sX, n_valid, rg, cg);
+        gemm_dx(ring, sDv, dx, rg, cg, true);
+        frag_store_g(dx, a.gX, row0, n_valid, rg, cg, KIND == 0);       // KIND 0: += ; KIND 1: =
         __syncthreads();
         ring.prefetch();
     }
@@ -514,9 +493,9 @@ struct HeadArgs {
 
 template <int DEC>
 __global__ void __launch_bounds__(NT, 1)
-bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a, long n_tok, int lpad) {
+bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BSmem s = bcarve(smem_raw, lpad);
+    BSmem s = bcarve(smem_raw, BDEPTH);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long n_tiles = (n_tok + TM - 1) / TM;
     long mine = 0;
@@ -644,9 +623,9 @@ struct EmbArgs {
 
 // encoder: x0 = LN(GELU(W_obs . LN7(obs) + b))      (ma_transformer.py:133-136,148-151)
 __global__ void __launch_bounds__(NT, 1)
-bwd_embed_enc(const float* __restrict__ packed, float* __restrict__ grad, EmbArgs a, long n_tok, int lpad) {
+bwd_embed_enc(const float* __restrict__ packed, float* __restrict__ grad, EmbArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BSmem s = bcarve(smem_raw, lpad);
+    BSmem s = bcarve(smem_raw, BDEPTH);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long n_tiles = (n_tok + TM - 1) / TM;
     for (int i = tid; i < lay::ENC_EMB_SIZE; i += NT) s.sSmall[i] = packed[lay::ENC_EMB + i];
@@ -709,9 +688,9 @@ bwd_embed_enc(const float* __restrict__ packed, float* __restrict__ grad, EmbArg
 
 // decoder: x0 = LN(GELU(W_a . shifted))   (ma_transformer.py:224-225); shifted row = start flag | one-hot(prev action)
 __global__ void __launch_bounds__(NT, 1)
-bwd_embed_dec(const float* __restrict__ packed, float* __restrict__ grad, EmbArgs a, long n_tok, int lpad) {
+bwd_embed_dec(const float* __restrict__ packed, float* __restrict__ grad, EmbArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BSmem s = bcarve(smem_raw, lpad);
+    BSmem s = bcarve(smem_raw, BDEPTH);
     const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
     const long n_tiles = (n_tok + TM - 1) / TM;
     // tables for the 3 reachable token codes (1 start, 2 action 0, 3 action 1): pre-GELU a, xhat, rstd
@@ -812,17 +791,17 @@ int set_smem(K kernel, size_t bytes) {
 int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const GradMap& gm, float* grad, const float* obs,
                              const float* actions, const float* ava, const float* d_values, const float* d_logp,
                              const float* d_ent, long M, int L, int obs_dim, int mode, int n_sm, cudaStream_t st) {
-    if (L > 128) {
-        matas_set_error("evaluate backward supports n_agent <= 128 (got %d)", L);
+    if (L > 256) {
+        matas_set_error("evaluate backward supports n_agent <= 256 (got %d)", L);
         return MATAS_ERR_LIMIT;
     }
-    const int lpad = L | 1;
-    const size_t bytes = bsmem_bytes(lpad);
+    const size_t bytes = bsmem_bytes(BDEPTH), abytes = bsmem_bytes(ADEPTH);
     const long n_tok = M * L;
     const long n_tiles = (n_tok + TM - 1) / TM;
     const unsigned grid = (unsigned)(n_tiles < n_sm ? n_tiles : n_sm);
+    const unsigned agrid = (unsigned)(n_tiles < 2 * n_sm ? n_tiles : 2 * n_sm);     // bwd_attn: two CTAs per SM
     int rc;
-    if ((rc = set_smem(bwd_mlp_proj, bytes)) || (rc = set_smem(bwd_attn<0>, bytes)) || (rc = set_smem(bwd_attn<1>, bytes)) ||
+    if ((rc = set_smem(bwd_mlp_proj, bytes)) || (rc = set_smem(bwd_attn<0>, abytes)) || (rc = set_smem(bwd_attn<1>, abytes)) ||
         (rc = set_smem(bwd_head<0>, bytes)) || (rc = set_smem(bwd_head<1>, bytes)) || (rc = set_smem(bwd_embed_enc, bytes)) ||
         (rc = set_smem(bwd_embed_dec, bytes)))
         return rc;
@@ -840,7 +819,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         h.gW0 = gm.w[idx(DEC_H0)]; h.gb0 = gm.b[idx(DEC_H0)]; h.glnw = gm.lnw[idx(DEC_H0)]; h.glnb = gm.lnb[idx(DEC_H0)];
         h.gW3 = gm.dec_h3_w; h.gb3 = gm.dec_h3_b; h.glogstd = gm.log_std;
         h.gOut = t.gX; h.L = L; h.n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
-        bwd_head<1><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok, lpad);
+        bwd_head<1><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
     }
     for (int k = 1; k >= 0; --k) {
         TailArgs ta = {};
@@ -853,7 +832,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(dec_blob(k, DM2))]; ta.glnFb = gm.lnb[idx(dec_blob(k, DM2))];
         ta.glnMw = gm.lnw[idx(dec_blob(k, DP2))]; ta.glnMb = gm.lnb[idx(dec_blob(k, DP2))];
         ta.gRes = t.gRep; ta.res_add = 1; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok, lpad);
+        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok);
 
         AttnArgs a2 = {};
         a2.Q = b.Q2[k]; a2.K = b.K2[k]; a2.V = b.V2[k]; a2.lse = t.d_lse2[k]; a2.gY = t.gYa; a2.gD = t.gDa;
@@ -863,7 +842,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a2.gWk = gm.w[idx(dec_blob(k, DK2))]; a2.gbk = gm.b[idx(dec_blob(k, DK2))];
         a2.gWv = gm.w[idx(dec_blob(k, DV2))]; a2.gbv = gm.b[idx(dec_blob(k, DV2))];
         a2.gX = t.gX; a2.gRep = t.gRep; a2.causal = 1; a2.L = L;
-        bwd_attn<1><<<grid, NT, bytes, st>>>(pk, grad, a2, n_tok, lpad);       // gX = grad wrt x1 (LN1 output)
+        bwd_attn<1><<<agrid, NT, abytes, st>>>(pk, grad, a2, n_tok);       // gX = grad wrt x1 (LN1 output)
 
         TailArgs tb = {};
         tb.gOut = t.gX; tb.xhM = t.d_xh1[k]; tb.rsM = t.d_rs1[k]; tb.Y = t.d_y1[k];
@@ -872,7 +851,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         tb.gWp = gm.w[idx(dec_blob(k, DP1))]; tb.gbp = gm.b[idx(dec_blob(k, DP1))];
         tb.glnMw = gm.lnw[idx(dec_blob(k, DP1))]; tb.glnMb = gm.lnb[idx(dec_blob(k, DP1))];
         tb.gRes = t.gX; tb.res_add = 0; tb.gY = t.gYb; tb.gD = t.gDb; tb.with_mlp = 0;
-        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, tb, n_tok, lpad);       // gX = grad wrt block input (residual part)
+        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, tb, n_tok);       // gX = grad wrt block input (residual part)
 
         AttnArgs a1 = {};
         a1.Q = t.d_q1[k]; a1.K = b.K1[k]; a1.V = b.V1[k]; a1.lse = t.d_lse1[k]; a1.gY = t.gYb; a1.gD = t.gDb;
@@ -883,13 +862,13 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(dec_blob(k, DK1))]; a1.gbk = gm.b[idx(dec_blob(k, DK1))];
         a1.gWv = gm.w[idx(dec_blob(k, DV1))]; a1.gbv = gm.b[idx(dec_blob(k, DV1))];
         a1.gX = t.gX; a1.causal = 1; a1.L = L;
-        bwd_attn<0><<<grid, NT, bytes, st>>>(pk, grad, a1, n_tok, lpad);       // gX += attention path
+        bwd_attn<0><<<agrid, NT, abytes, st>>>(pk, grad, a1, n_tok);       // gX += attention path
     }
     {
         EmbArgs e = {};
         e.gX = t.gX; e.actions = actions; e.L = L;
         e.gln_w = gm.dec_ln_w; e.gln_b = gm.dec_ln_b; e.gW = gm.dec_wa;
-        bwd_embed_dec<<<grid, NT, bytes, st>>>(pk, grad, e, n_tok, lpad);
+        bwd_embed_dec<<<grid, NT, bytes, st>>>(pk, grad, e, n_tok);
     }
     // ---- encoder ---------------------------------------------------------------------------------
     {
@@ -899,7 +878,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         h.gW0 = gm.w[idx(ENC_H0)]; h.gb0 = gm.b[idx(ENC_H0)]; h.glnw = gm.lnw[idx(ENC_H0)]; h.glnb = gm.lnb[idx(ENC_H0)];
         h.gW3 = gm.enc_h3_w; h.gb3 = gm.enc_h3_b; h.glogstd = -1;
         h.gOut = t.gRep; h.L = L;
-        bwd_head<0><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok, lpad);
+        bwd_head<0><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
     }
     for (int k = 1; k >= 0; --k) {
         TailArgs ta = {};
@@ -912,7 +891,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(enc_blob(k, EM2))]; ta.glnFb = gm.lnb[idx(enc_blob(k, EM2))];
         ta.glnMw = gm.lnw[idx(enc_blob(k, EP))]; ta.glnMb = gm.lnb[idx(enc_blob(k, EP))];
         ta.gRes = t.gX; ta.res_add = 0; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok, lpad);
+        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok);
 
         AttnArgs a1 = {};
         a1.Q = t.e_q[k]; a1.K = b.K[k]; a1.V = b.V[k]; a1.lse = t.e_lse[k]; a1.gY = t.gYa; a1.gD = t.gDa;
@@ -923,14 +902,14 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(enc_blob(k, EK))]; a1.gbk = gm.b[idx(enc_blob(k, EK))];
         a1.gWv = gm.w[idx(enc_blob(k, EV))]; a1.gbv = gm.b[idx(enc_blob(k, EV))];
         a1.gX = t.gX; a1.causal = 0; a1.L = L;
-        bwd_attn<0><<<grid, NT, bytes, st>>>(pk, grad, a1, n_tok, lpad);
+        bwd_attn<0><<<agrid, NT, abytes, st>>>(pk, grad, a1, n_tok);
     }
     {
         EmbArgs e = {};
         e.gX = t.gX; e.h0 = t.e_h0; e.xh0 = t.e_xh0; e.rs0 = t.e_rs0; e.obs = obs; e.obs_dim = obs_dim;
         e.gln_w = gm.enc_ln_w; e.gln_b = gm.enc_ln_b; e.gW = gm.enc_wobs; e.gb = gm.enc_bobs;
         e.gln7_w = gm.enc_ln7_w; e.gln7_b = gm.enc_ln7_b;
-        bwd_embed_enc<<<grid, NT, bytes, st>>>(pk, grad, e, n_tok, lpad);
+        bwd_embed_enc<<<grid, NT, bytes, st>>>(pk, grad, e, n_tok);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
