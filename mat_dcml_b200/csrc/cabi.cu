@@ -1,6 +1,7 @@
 // extern "C" entry points of libmatas_b200.so (declared in include/matas_b200.h): policy handle,
 // weight repacking, scratch management.  The DCML simulator and GAE entry points live in env.cu
 // and gae.cu.
+#include <cuda_fp16.h>
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
@@ -82,6 +83,24 @@ __global__ void fold_kernel(const float* __restrict__ flat, float* __restrict__ 
     }
 }
 
+// tensor-core copy of one forward / folded blob (layout.h: hb()): fp16 hi + scaled-lo parts of W[n][k],
+// K-major with the 128-byte swizzle tcgen05 shared-memory descriptors expect, plus the fp32 tail.
+__global__ void half_kernel(float* __restrict__ packed, const int* __restrict__ offs) {
+    const int off = offs[blockIdx.x];
+    const float* src = packed + off;                                  // Wt[k][n]
+    unsigned char* dst = reinterpret_cast<unsigned char*>(packed + lay::hb(off));
+    for (int idx = threadIdx.x; idx < 4096; idx += blockDim.x) {
+        const int n = idx >> 6, k = idx & 63;
+        const float w = src[k * 64 + n];
+        const __half hi = __float2half_rn(w);
+        const __half lo = __float2half_rn((w - __half2float(hi)) * 2048.0f);
+        const int byte = n * 128 + ((((k >> 3) ^ (n & 7)) << 4) | ((k & 7) * 2));
+        *reinterpret_cast<__half*>(dst + byte) = hi;
+        *reinterpret_cast<__half*>(dst + lay::HB_LO_BYTES + byte) = lo;
+    }
+    for (int i = threadIdx.x; i < 192; i += blockDim.x) packed[lay::hb(off) + lay::B_BIAS + i] = src[lay::B_BIAS + i];
+}
+
 struct matas_policy {
     matas_model_cfg cfg;
     int device;
@@ -91,6 +110,8 @@ struct matas_policy {
     PackEntry* d_table = nullptr;
     std::vector<FoldEntry> folds;
     FoldEntry* d_folds = nullptr;
+    int n_half = 0;
+    int* d_half = nullptr;       // float offsets of the blobs that get a tensor-core copy
     float* d_packed = nullptr;
     bool weights_set = false;
     // scratch
@@ -257,8 +278,17 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     if ((e = cudaMalloc(&p->d_folds, p->folds.size() * sizeof(FoldEntry))) != cudaSuccess) return fail(e, "cudaMalloc(folds)");
     if ((e = cudaMemcpy(p->d_folds, p->folds.data(), p->folds.size() * sizeof(FoldEntry), cudaMemcpyHostToDevice)) != cudaSuccess)
         return fail(e, "cudaMemcpy(folds)");
-    if ((e = cudaMalloc(&p->d_packed, lay::TOTAL_ALL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMalloc(packed)");
-    if ((e = cudaMemset(p->d_packed, 0, lay::TOTAL_ALL * sizeof(float))) != cudaSuccess) return fail(e, "cudaMemset(packed)");
+    {
+        std::vector<int> offs;
+        for (int o = lay::ENC_BLOBS; o < lay::TOTAL; o += lay::BLOB) offs.push_back(o);
+        for (int o = lay::FOLD_BASE; o < lay::TOTAL_ALL; o += lay::BLOB) offs.push_back(o);
+        p->n_half = (int)offs.size();
+        if ((e = cudaMalloc(&p->d_half, offs.size() * sizeof(int))) != cudaSuccess) return fail(e, "cudaMalloc(half table)");
+        if ((e = cudaMemcpy(p->d_half, offs.data(), offs.size() * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess)
+            return fail(e, "cudaMemcpy(half table)");
+    }
+    if ((e = cudaMalloc(&p->d_packed, lay::TOTAL_HB * sizeof(float))) != cudaSuccess) return fail(e, "cudaMalloc(packed)");
+    if ((e = cudaMemset(p->d_packed, 0, lay::TOTAL_HB * sizeof(float))) != cudaSuccess) return fail(e, "cudaMemset(packed)");
     p->bufs.w = p->d_packed;
     if ((rc = policy_init_constants())) { matas_policy_destroy(p); return rc; }
     *out = p;
@@ -267,7 +297,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
 
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
-    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train); cudaFree(p->d_phase);
+    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_half); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train); cudaFree(p->d_phase);
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
@@ -287,6 +317,7 @@ extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void
     ARG_CHECK(p && flat, "null argument");
     pack_kernel<<<(unsigned)p->table.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_table);
     fold_kernel<<<(unsigned)p->folds.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_folds);
+    half_kernel<<<(unsigned)p->n_half, 256, 0, (cudaStream_t)stream>>>(p->d_packed, p->d_half);
     CUDA_TRY(cudaGetLastError());
     p->weights_set = true;
     return MATAS_OK;

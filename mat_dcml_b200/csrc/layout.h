@@ -52,6 +52,15 @@ constexpr int FOLD_BASE = BW_BASE + N_BLOBS * BW_MAT;
 __host__ __device__ constexpr int fold_blob(int blk, int which) { return FOLD_BASE + (blk * FOLD_PER_BLOCK + which) * BLOB; }
 constexpr int DEC_FOLD_STEP_BLOBS = 2 * 8 + 1;        // per block: FA0 FA1 FB0 FB1 FC0 FC1 M0 M2 ; + head.0
 constexpr int TOTAL_ALL = FOLD_BASE + 2 * FOLD_PER_BLOCK * BLOB;
+// tensor-core ("half") blobs: for every forward / folded blob at float offset `off` the same 17152 bytes at
+// hb(off) hold the weight as tcgen05 B operands — W[n][k] in fp16, K-major, SWIZZLE_128B (row n at n*128 B,
+// 16-byte chunk index XOR (n % 8)): the hi part fp16(w) (8 KB), then the lo part fp16((w - hi) * 2^11) (8 KB) —
+// followed by the same fp32 bias | LN weight | LN bias tail (so B_BIAS / B_LNW / B_LNB index it unchanged).
+constexpr int HB_BASE = TOTAL_ALL;
+__host__ __device__ constexpr int hb(int blob_off) { return HB_BASE + (blob_off - ENC_BLOBS); }
+constexpr int TOTAL_HB = HB_BASE + (TOTAL_ALL - ENC_BLOBS);
+static_assert((HB_BASE - ENC_BLOBS) % 4 == 0 && ENC_BLOBS % 4 == 0, "half blobs must stay 16-byte aligned for cp.async.bulk");
+constexpr int HB_LO_BYTES = 8192;                     // byte offset of the lo part inside a half blob
 
 __host__ __device__ constexpr int enc_blob(int blk, int which) { return ENC_BLOBS + (blk * ENC_PER_BLOCK + which) * BLOB; }
 __host__ __device__ constexpr int dec_blob(int blk, int which) { return DEC_STEP + (blk * DEC_PER_BLOCK + which) * BLOB; }

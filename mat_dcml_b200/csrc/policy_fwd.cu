@@ -745,6 +745,13 @@ static TrainBufs train_or_off(const TrainBufs* tb) {
         else { if ((rc_ = set_smem(KERNEL4, bytes))) return rc_; KERNEL4<<<GRID, NT, bytes, st>>>(__VA_ARGS__); }          \
     } while (0)
 
+// MATAS_TC=0 keeps the dense stages of the token-parallel kernels on the fp32 SIMT path (A/B measurements)
+bool policy_use_tc() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("MATAS_TC"); v = e ? atoi(e) : 1; }
+    return v != 0;
+}
+
 int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
                    const TrainBufs* tbp, int for_decode) {
     const TrainBufs tb = train_or_off(tbp);
@@ -752,6 +759,7 @@ int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B,
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
     LAUNCH(enc_embed_qkv<2>, enc_embed_qkv<4>, grid, b, tb, obs, n_tok, obs_dim, depth);
+    if (policy_use_tc()) return launch_enc_blocks_tc(b, tb, values, n_tok, L, for_decode, st);
     LAUNCH((enc_block<0, 2>), (enc_block<0, 4>), grid, b, tb, values, n_tok, L, depth, 0);
     LAUNCH((enc_block<1, 2>), (enc_block<1, 4>), grid, b, tb, values, n_tok, L, depth, for_decode);
     CUDA_TRY(cudaGetLastError());

@@ -64,6 +64,9 @@ int policy_init_constants();
 int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
                    const TrainBufs* tb = nullptr, int for_decode = 0);
 int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st, int for_decode);
+// tensor-core (tcgen05) token-parallel kernels, policy_tc.cu
+bool policy_use_tc();
+int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st);
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
                           long B, int L, int mode, cudaStream_t st, const TrainBufs* tb = nullptr);
 int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st);

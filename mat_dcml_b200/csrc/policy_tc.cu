@@ -1,0 +1,208 @@
+// Tensor-core (tcgen05) versions of the token-parallel MAT-AS kernels for sm_100a: 128-token tiles, fp16
+// hi + scaled-lo operands in shared memory (tc.cuh), fp32 accumulators in tensor memory, thread-per-row
+// epilogues fusing bias / GELU / residual / LayerNorm, attention on the CUDA cores writing its output
+// straight into the next GEMM's operand.  Two CTAs per SM so that one CTA's attention / epilogue overlaps
+// the other's MMAs.
+//
+// Reference semantics: EncodeBlock / Encoder of mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:70-154.
+#include "policy_fwd.h"
+#include "tc.cuh"
+
+using namespace tile;
+
+namespace {
+
+constexpr int TC_DEPTH = 2;
+
+__constant__ int c_tc_enc_blk0[6] = {lay::hb(lay::enc_blob(0, lay::EP)), lay::hb(lay::enc_blob(0, lay::EM0)),
+                                     lay::hb(lay::enc_blob(0, lay::EM2)), lay::hb(lay::enc_blob(1, lay::EQ)),
+                                     lay::hb(lay::enc_blob(1, lay::EK)), lay::hb(lay::enc_blob(1, lay::EV))};
+__constant__ int c_tc_enc_blk1[6] = {lay::hb(lay::enc_blob(1, lay::EP)), lay::hb(lay::enc_blob(1, lay::EM0)),
+                                     lay::hb(lay::enc_blob(1, lay::EM2)), lay::hb(lay::ENC_H0), lay::hb(lay::dec_q2(0)),
+                                     lay::hb(lay::dec_q2(1))};
+__constant__ int c_tc_enc_blk1_dec[8] = {lay::hb(lay::enc_blob(1, lay::EP)), lay::hb(lay::enc_blob(1, lay::EM0)),
+                                         lay::hb(lay::enc_blob(1, lay::EM2)), lay::hb(lay::ENC_H0),
+                                         lay::hb(lay::fold_blob(0, lay::FQ0)), lay::hb(lay::fold_blob(0, lay::FQ1)),
+                                         lay::hb(lay::fold_blob(1, lay::FQ0)), lay::hb(lay::fold_blob(1, lay::FQ1))};
+
+__device__ __forceinline__ void add_bias32(float (&v)[32], const float* __restrict__ blob, int half) {
+    const float4* bias = reinterpret_cast<const float4*>(blob + lay::B_BIAS + half * 32);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float4 b = bias[j];
+        v[j * 4] += b.x; v[j * 4 + 1] += b.y; v[j * 4 + 2] += b.z; v[j * 4 + 3] += b.w;
+    }
+}
+
+// one GEMM stage: acquire the weights, publish the operand, issue, refill the ring, wait, read the
+// accumulator and add the bias.  `blob` stays valid until ring.release().
+struct Stage {
+    tc::Ctx& c;
+    Ring& ring;
+    __device__ __forceinline__ const float* run(float (&v)[32]) {
+        const float* blob = ring.acquire();
+        tc::gemm_issue(c, blob);
+        ring.prefetch();
+        tc::gemm_result(c, v);
+        add_bias32(v, blob, c.half);
+        return blob;
+    }
+};
+__device__ __forceinline__ void affine32(float (&v)[32], const float* __restrict__ blob, int half) {
+    const float4* w = reinterpret_cast<const float4*>(blob + lay::B_LNW + half * 32);
+    const float4* b = reinterpret_cast<const float4*>(blob + lay::B_LNB + half * 32);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float4 ww = w[j], bb = b[j];
+        v[j * 4] = fmaf(v[j * 4], ww.x, bb.x); v[j * 4 + 1] = fmaf(v[j * 4 + 1], ww.y, bb.y);
+        v[j * 4 + 2] = fmaf(v[j * 4 + 2], ww.z, bb.z); v[j * 4 + 3] = fmaf(v[j * 4 + 3], ww.w, bb.w);
+    }
+}
+__device__ __forceinline__ void save_row32(float* __restrict__ base, long tile0, int row, int half, int n_valid, const float (&v)[32]) {
+    if (base && row < n_valid) tc::row_store32(base + (tile0 + row) * 64 + half * 32, v);
+}
+
+// -------------------------------------------------------------------------------------------------
+// encoder block: attention (bidirectional) + proj + LN1 + MLP + LN2 (ma_transformer.py:89-92);
+// BLK 0 then emits QKV of block 1; BLK 1 emits obs_rep, the value head (:138-139) and the decoder's
+// cross-attention queries (plain Q2 for the teacher-forced passes, folded Q2' for the decode).
+// -------------------------------------------------------------------------------------------------
+template <int BLK>
+__global__ void __launch_bounds__(NT, 2)
+enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int for_decode) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
+    const int tid = threadIdx.x;
+    const long tile0 = (long)blockIdx.x * tc::TR;
+    const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
+    Ring ring;
+    if (BLK == 1 && for_decode) ring.init(s.ring, s.bars, b.w, c_tc_enc_blk1_dec, 8, 8, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    else ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_tc_enc_blk0 : c_tc_enc_blk1, 6, 6, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    tc::Ctx c;
+    tc::ctx_init(c, s);                  // ends with a CTA barrier: ring barriers are initialised
+    ring.prefetch();
+    if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[512 + i] = b.w[lay::ENC_H3 + i];
+    const int row = c.row, half = c.half;
+    float* sRed = s.sSmall;              // [2][TR][2] LayerNorm partials, [512 + ...) head.3
+    float* sTrow = s.sT + row * XS + half * 32;
+    Stage st = {c, ring};
+
+    tc::global_to_tile(s.sT, b.X + tile0 * 64, n_valid);         // residual stream
+    tc::attention_to_operand<false>(s.sA, (tb.on ? tb.e_q[BLK] : b.Q), b.K[BLK], b.V[BLK], tile0, n_tok, L,
+                                    tb.on ? tb.e_y[BLK] : nullptr, tb.on ? tb.e_lse[BLK] : nullptr);
+    float v[32], res[32];
+    // ---- proj + residual + LN1 ------------------------------------------------------------------
+    {
+        const float* blob = st.run(v);
+        tc::row_load32(sTrow, res);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += res[i];
+        const float rs = tc::layernorm_pair(v, sRed, row, half);
+        if (tb.on) {
+            save_row32(tb.e_xh1[BLK], tile0, row, half, n_valid, v);
+            if (half == 0 && row < n_valid) tb.e_rs1[BLK][tile0 + row] = rs;
+        }
+        affine32(v, blob, half);
+        ring.release();
+        tc::row_store32(sTrow, v);                                // x1: residual of the MLP
+        tc::store_operand32(s.sA, row, half, v);
+    }
+    // ---- mlp.0 + GELU ---------------------------------------------------------------------------
+    {
+        st.run(v);
+        ring.release();
+        if (tb.on) save_row32(tb.e_m0[BLK], tile0, row, half, n_valid, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        tc::store_operand32(s.sA, row, half, v);
+    }
+    // ---- mlp.2 + residual + LN2 -----------------------------------------------------------------
+    {
+        const float* blob = st.run(v);
+        tc::row_load32(sTrow, res);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += res[i];
+        const float rs = tc::layernorm_pair(v, sRed, row, half);
+        if (tb.on) {
+            save_row32(tb.e_xh2[BLK], tile0, row, half, n_valid, v);
+            if (half == 0 && row < n_valid) tb.e_rs2[BLK][tile0 + row] = rs;
+        }
+        affine32(v, blob, half);
+        ring.release();
+        tc::row_store32(sTrow, v);                                // block output
+        tc::store_operand32(s.sA, row, half, v);
+    }
+    // outputs that go to token-major global memory are staged through sT so that the stores coalesce
+    auto staged_out = [&](float* gdst) {
+        tc::row_store32(sTrow, v);
+        __syncthreads();
+        tc::tile_to_global(gdst + tile0 * 64, s.sT, n_valid);
+    };
+    if (BLK == 0) {
+        float* outs[3] = {tb.on ? tb.e_q[1] : b.Q, b.K[1], b.V[1]};
+#pragma unroll
+        for (int o = 0; o < 3; ++o) {
+            const float* blob = ring.acquire();
+            tc::gemm_issue(c, blob);                              // barrier: sT holds the complete previous output
+            ring.prefetch();
+            if (o == 0) tc::tile_to_global(b.X + tile0 * 64, s.sT, n_valid);
+            tc::gemm_result(c, v);
+            add_bias32(v, blob, half);
+            ring.release();
+            if (o == 0) __syncthreads();                          // every thread is done reading x2 from sT
+            staged_out(outs[o]);
+        }
+    } else {
+        // ---- value head: Linear -> GELU -> LN -> Linear(64 -> 1) --------------------------------------
+        {
+            const float* blob = ring.acquire();
+            tc::gemm_issue(c, blob);
+            ring.prefetch();
+            tc::tile_to_global(b.rep + tile0 * 64, s.sT, n_valid);
+            tc::gemm_result(c, v);
+            add_bias32(v, blob, half);
+            if (tb.on) save_row32(tb.e_hh, tile0, row, half, n_valid, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+            const float rs = tc::layernorm_pair(v, sRed, row, half);
+            if (tb.on) {
+                save_row32(tb.e_xhh, tile0, row, half, n_valid, v);
+                if (half == 0 && row < n_valid) tb.e_rsh[tile0 + row] = rs;
+            }
+            affine32(v, blob, half);
+            ring.release();
+            const float* w3 = s.sSmall + 512 + half * 32;
+            float d = 0.f;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) d = fmaf(v[i], w3[i], d);
+            sRed[row * 2 + half] = d;
+            __syncthreads();                                      // also: the rep store above has drained sT
+            if (half == 0 && row < n_valid) values[tile0 + row] = sRed[row * 2] + sRed[row * 2 + 1] + s.sSmall[512 + 64];
+        }
+        // ---- cross-attention queries from obs_rep (operand still holds it) ------------------------------
+        const int n_q = for_decode ? 4 : 2;
+        for (int o = 0; o < n_q; ++o) {
+            const float* blob = ring.acquire();
+            tc::gemm_issue(c, blob);
+            ring.prefetch();
+            tc::gemm_result(c, v);
+            add_bias32(v, blob, half);
+            ring.release();
+            staged_out(for_decode ? b.Q2p[o >> 1][o & 1] : b.Q2[o]);
+        }
+    }
+    tc::ctx_fini(c);
+}
+
+}  // namespace
+
+int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st) {
+    const size_t bytes = tc::smem_bytes(TC_DEPTH);
+    CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
+    enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0);
+    enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}

@@ -1,0 +1,303 @@
+// tcgen05 building blocks for the [128 tokens x 64] . [64 x 64] stages of the token-parallel kernels (sm_100a).
+//
+// Precision scheme ("fp16 hi + scaled lo", validated standalone in scripts/tc/tc_test_f16.cu: error below the
+// fp32 FMA chain's): every operand element x is stored as two halves, hi = fp16(x), lo = fp16((x - hi) * 2^11),
+// and a GEMM is three fp16 MMAs with fp32 accumulation in tensor memory,
+//      D1 = Ahi.Whi          D2 = Ahi.Wlo + Alo.Whi          D = D1 + 2^-11 D2
+// (the dropped lo.lo term is 2^-22 relative).  Activations on this path are LayerNorm / GELU / softmax-average
+// outputs and the weights are O(1), far inside fp16's range; values beyond 65504 would overflow.
+//
+// Shared-memory operands are K-major with the 128-byte swizzle: row r (token or output feature) occupies
+// 128 bytes = 64 halves at r*128, its 16-byte chunk c stored at chunk position c ^ (r % 8).
+// Thread layout of the epilogues: 256 threads, thread t owns row 32*(warp % 4) + lane (the TMEM lane its warp
+// may read) and the column half warp / 4 (32 accumulator columns), so LayerNorm needs one exchange with the
+// partner thread through shared memory and no shuffles.
+#pragma once
+#include <cuda_fp16.h>
+
+#include "tile.cuh"
+
+namespace tc {
+using namespace tile;
+
+constexpr int TR = 128;                       // rows (tokens) per tile
+constexpr int A_PART = TR * 128;              // bytes of one operand part (hi or lo) of the activation tile
+constexpr int SLOT_BYTES = 17408;             // ring slot stride: 1024-byte aligned, holds one 17152-byte half blob
+constexpr int SLOT_F = SLOT_BYTES / 4;
+constexpr int TILE_BYTES = TR * XS * 4;       // fp32 row-major staging / residual tile
+constexpr int TMEM_COLS = 128;                // D1: columns 0-63, D2: columns 64-127
+constexpr int MMA_BAR = 7;                    // index of the MMA-completion barrier in Smem::bars
+
+struct Smem {
+    unsigned char* sA;     // [hi | lo][128 rows][128 B]
+    float* ring;           // depth slots of SLOT_F floats
+    float* sT;             // [128][XS] fp32
+    float* sSmall;         // 1024 floats
+    uint64_t* bars;        // [0, depth): weight ring, [MMA_BAR]: MMA completion
+    uint32_t* tmem_slot;
+};
+__host__ __device__ constexpr size_t smem_bytes(int depth) {
+    return 1024 + 2 * (size_t)A_PART + (size_t)depth * SLOT_BYTES + TILE_BYTES + 4096 + 8 * 8 + 16;
+}
+__device__ inline Smem carve(unsigned char* raw, int depth) {
+    Smem s;
+    unsigned char* p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
+    s.sA = p; p += 2 * A_PART;
+    s.ring = reinterpret_cast<float*>(p); p += (size_t)depth * SLOT_BYTES;
+    s.sT = reinterpret_cast<float*>(p); p += TILE_BYTES;
+    s.sSmall = reinterpret_cast<float*>(p); p += 4096;
+    s.bars = reinterpret_cast<uint64_t*>(p); p += 8 * 8;
+    s.tmem_slot = reinterpret_cast<uint32_t*>(p);
+    return s;
+}
+
+// ---- raw tcgen05 / proxy helpers ------------------------------------------------------------------
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot) {   // one full warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t tmem) {  // one full warp
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+}
+// K-major SWIZZLE_128B shared-memory matrix descriptor: 8-row atoms of 1024 bytes
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n" ::"r"(tmem_d),
+        "l"(da), "l"(db), "r"(idesc), "r"(accum), "r"(0u)
+        : "memory");
+}
+#define TC_LD32(v, addr)                                                                                                       \
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                      \
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, " \
+                 "%24, %25, %26, %27, %28, %29, %30, %31}, [%32];"                                                              \
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),  \
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),       \
+                   "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),      \
+                   "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                    \
+                 : "r"(addr))
+
+// ---- per-CTA context --------------------------------------------------------------------------------
+struct Ctx {
+    uint32_t a_saddr;      // shared address of the activation operand (hi part; lo at + A_PART)
+    uint32_t tmem;         // TMEM base of this CTA's 128 columns
+    uint64_t* bar;         // MMA completion barrier
+    uint32_t phase;
+    int row, half;         // epilogue ownership of this thread
+};
+
+// CTA prologue: barrier init, TMEM allocation.  Ends with a __syncthreads().
+__device__ __forceinline__ void ctx_init(Ctx& c, const Smem& s) {
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (tid == 0) { mbar_init(&s.bars[MMA_BAR], 1); mbar_fence_init(); }
+    if (warp == 0) tmem_alloc(s.tmem_slot);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    c.a_saddr = smem_u32(s.sA);
+    c.tmem = *s.tmem_slot;
+    c.bar = &s.bars[MMA_BAR];
+    c.phase = 0;
+    c.row = (warp & 3) * 32 + (tid & 31);
+    c.half = warp >> 2;
+}
+__device__ __forceinline__ void ctx_fini(const Ctx& c) {
+    fence_before_sync();
+    __syncthreads();
+    if ((threadIdx.x >> 5) == 0) tmem_dealloc(c.tmem);
+}
+
+// Publish the activation operand the threads just wrote (generic proxy -> async proxy), then thread 0 issues
+// the three products against the half blob at `slot` (already acquired from the ring).  Contains the CTA
+// barrier that separates this stage from the previous one.
+__device__ __forceinline__ void gemm_issue(const Ctx& c, const float* slot) {
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    if (threadIdx.x == 0) {
+        // instruction descriptor: D f32, A/B f16, both K-major, N = 64, M = 128
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t a0 = c.a_saddr, b0 = smem_u32(slot);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) mma_f16(c.tmem, make_desc(a0 + ks * 32), make_desc(b0 + ks * 32), idesc, ks > 0);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+            mma_f16(c.tmem + 64, make_desc(a0 + ks * 32), make_desc(b0 + lay::HB_LO_BYTES + ks * 32), idesc, ks > 0);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) mma_f16(c.tmem + 64, make_desc(a0 + A_PART + ks * 32), make_desc(b0 + ks * 32), idesc, 1);
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(c.bar)) : "memory");
+    }
+}
+// Wait for the products and read this thread's 32 accumulator columns: v = D1 + 2^-11 D2
+__device__ __forceinline__ void gemm_result(Ctx& c, float (&v)[32]) {
+    mbar_wait(c.bar, c.phase);
+    c.phase ^= 1;
+    fence_after_sync();
+    uint32_t v1[32], v2[32];
+    const uint32_t taddr = c.tmem + ((uint32_t)(c.row & ~31) << 16) + c.half * 32;
+    TC_LD32(v1, taddr);
+    TC_LD32(v2, taddr + 64);
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = fmaf(__uint_as_float(v2[i]), 1.0f / 2048.0f, __uint_as_float(v1[i]));
+}
+
+// ---- operand stores -----------------------------------------------------------------------------------
+__device__ __forceinline__ void split2(float a, float b, __half2& hi, __half2& lo) {
+    hi = __floats2half2_rn(a, b);
+    const float2 f = __half22float2(hi);
+    lo = __floats2half2_rn((a - f.x) * 2048.0f, (b - f.y) * 2048.0f);
+}
+// 32 consecutive columns [32*half, 32*half + 32) of row `row`
+__device__ __forceinline__ void store_operand32(unsigned char* sA, int row, int half, const float (&v)[32]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        __half2 h[4], l[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split2(v[j * 8 + 2 * i], v[j * 8 + 2 * i + 1], h[i], l[i]);
+        const uint32_t off = row * 128 + (((half * 4 + j) ^ (row & 7)) << 4);
+        *reinterpret_cast<uint4*>(sA + off) = make_uint4(*reinterpret_cast<uint32_t*>(&h[0]), *reinterpret_cast<uint32_t*>(&h[1]),
+                                                         *reinterpret_cast<uint32_t*>(&h[2]), *reinterpret_cast<uint32_t*>(&h[3]));
+        *reinterpret_cast<uint4*>(sA + A_PART + off) = make_uint4(*reinterpret_cast<uint32_t*>(&l[0]), *reinterpret_cast<uint32_t*>(&l[1]),
+                                                                  *reinterpret_cast<uint32_t*>(&l[2]), *reinterpret_cast<uint32_t*>(&l[3]));
+    }
+}
+// 4 consecutive columns [4*l, 4*l + 4) of row `row` (the half-warp-per-row layout of the attention)
+__device__ __forceinline__ void store_operand4(unsigned char* sA, int row, int l, const float4& v) {
+    __half2 h0, h1, l0, l1;
+    split2(v.x, v.y, h0, l0);
+    split2(v.z, v.w, h1, l1);
+    const uint32_t off = row * 128 + ((((l >> 1) ^ (row & 7)) << 4) | ((l & 1) << 3));
+    *reinterpret_cast<uint2*>(sA + off) = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+    *reinterpret_cast<uint2*>(sA + A_PART + off) = make_uint2(*reinterpret_cast<uint32_t*>(&l0), *reinterpret_cast<uint32_t*>(&l1));
+}
+
+// ---- fp32 tile helpers (thread-per-row side) --------------------------------------------------------------
+__device__ __forceinline__ void row_load32(const float* __restrict__ p, float (&v)[32]) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float4 x = *reinterpret_cast<const float4*>(p + j * 4);
+        v[j * 4] = x.x; v[j * 4 + 1] = x.y; v[j * 4 + 2] = x.z; v[j * 4 + 3] = x.w;
+    }
+}
+__device__ __forceinline__ void row_store32(float* __restrict__ p, const float (&v)[32]) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(p + j * 4) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+}
+// cooperative, coalesced copies between the fp32 tile and token-major global memory
+__device__ __forceinline__ void tile_to_global(float* __restrict__ g, const float* __restrict__ sT, int n_valid) {
+    for (int idx = threadIdx.x; idx < TR * 16; idx += NT) {
+        const int r = idx >> 4, c = idx & 15;
+        if (r < n_valid) *reinterpret_cast<float4*>(g + (long)r * 64 + c * 4) = *reinterpret_cast<const float4*>(sT + r * XS + c * 4);
+    }
+}
+__device__ __forceinline__ void global_to_tile(float* __restrict__ sT, const float* g, int n_valid) {
+    for (int idx = threadIdx.x; idx < TR * 16; idx += NT) {
+        const int r = idx >> 4, c = idx & 15;
+        *reinterpret_cast<float4*>(sT + r * XS + c * 4) =
+            r < n_valid ? *reinterpret_cast<const float4*>(g + (long)r * 64 + c * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+// LayerNorm over a 64-column row held by two partner threads (32 columns each): two exchanges through
+// sRed[2][TR][2].  Contains two __syncthreads().  Returns rstd; v becomes x_hat (before the affine map).
+__device__ __forceinline__ float layernorm_pair(float (&v)[32], float* __restrict__ sRed, int row, int half) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) s += v[i];
+    sRed[row * 2 + half] = s;
+    __syncthreads();
+    const float mean = (sRed[row * 2] + sRed[row * 2 + 1]) * (1.0f / 64.0f);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) { v[i] -= mean; q = fmaf(v[i], v[i], q); }
+    sRed[2 * TR + row * 2 + half] = q;
+    __syncthreads();
+    const float rs = rsqrtf((sRed[2 * TR + row * 2] + sRed[2 * TR + row * 2 + 1]) * (1.0f / 64.0f) + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= rs;
+    return rs;
+}
+
+// Bidirectional / causal attention for a 128-token tile, one half-warp per query row (the layout of
+// tile::attention_rows), queries read from global memory, output written straight into the tensor-core
+// operand (and, in training mode, to y_out / lse_out).  Rows past n_tok produce zero operand rows.
+template <bool CAUSAL>
+__device__ __forceinline__ void attention_to_operand(unsigned char* sA, const float* __restrict__ Q, const float* __restrict__ K,
+                                                     const float* __restrict__ V, long tile0, long n_tok, int L,
+                                                     float* __restrict__ y_out, float* __restrict__ lse_out) {
+    const float scale = 0.17677669529663687f * 1.4426950408889634f;
+    const int tid = threadIdx.x, hw = tid >> 4, l = tid & 15;
+    const unsigned hmask = 0xffffu << (tid & 16);
+    for (int r = hw; r < TR; r += NT / 16) {
+        const long g = tile0 + r;
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g < n_tok) {
+            const long env = g / L;
+            const int pos = (int)(g - env * L);
+            const int nr = CAUSAL ? pos + 1 : L;
+            float4 q = __ldg(reinterpret_cast<const float4*>(Q + g * 64) + l);
+            q.x *= scale; q.y *= scale; q.z *= scale; q.w *= scale;
+            const float4* kp = reinterpret_cast<const float4*>(K + env * L * 64) + l;
+            const float4* vp = reinterpret_cast<const float4*>(V + env * L * 64) + l;
+            float m = -INFINITY, sum = 0.f;
+            auto batch = [&](const float4 (&k)[4], const float4 (&v)[4], int t0) {
+                float s[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float p = q.x * k[i].x + q.y * k[i].y + q.z * k[i].z + q.w * k[i].w;
+                    p += __shfl_xor_sync(hmask, p, 4);
+                    p += __shfl_xor_sync(hmask, p, 2);
+                    p += __shfl_xor_sync(hmask, p, 1);
+                    s[i] = t0 + i < nr ? p : -INFINITY;
+                }
+                const float n = fmaxf(m, fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])));
+                const float a = exp2f(m - n);
+                sum *= a; c.x *= a; c.y *= a; c.z *= a; c.w *= a;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float p = exp2f(s[i] - n);
+                    sum += p;
+                    c.x = fmaf(p, v[i].x, c.x); c.y = fmaf(p, v[i].y, c.y); c.z = fmaf(p, v[i].z, c.z); c.w = fmaf(p, v[i].w, c.w);
+                }
+                m = n;
+            };
+            auto fetch = [&](float4 (&k)[4], float4 (&v)[4], int t0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const bool ok = t0 + i < nr;
+                    k[i] = ok ? __ldg(kp + (long)(t0 + i) * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v[i] = ok ? __ldg(vp + (long)(t0 + i) * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            };
+            float4 ka[4], va[4], kb[4], vb[4];
+            fetch(ka, va, 0);
+            for (int t0 = 0; t0 < nr; t0 += 8) {
+                fetch(kb, vb, t0 + 4);
+                batch(ka, va, t0);
+                fetch(ka, va, t0 + 8);
+                if (t0 + 4 < nr) batch(kb, vb, t0 + 4);
+            }
+            const float inv = 1.0f / sum;
+            c.x *= inv; c.y *= inv; c.z *= inv; c.w *= inv;
+            if (y_out) *reinterpret_cast<float4*>(y_out + g * 64 + l * 4) = c;
+            if (lse_out && (l & 7) == 0) lse_out[g * 2 + (l >> 3)] = m * 0.6931471805599453f + logf(sum);
+        }
+        store_operand4(sA, r, l, c);
+    }
+}
+
+}  // namespace tc

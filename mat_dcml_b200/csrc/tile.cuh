@@ -23,11 +23,12 @@ struct Ring {
     float* slots; uint64_t* bars; const float* gw; const int* seq;   // seq: float offsets of the blobs, cyclic
     int seq_len, total, head, tail, depth;   // total: blobs this CTA consumes in its lifetime; tail: thread 0 only
     uint32_t bytes;                          // bytes per blob (forward blobs: BLOB_BYTES)
+    int stride;                              // floats between slots (tensor-core operands need 1024-byte aligned slots)
 
     __device__ void init(float* slots_, uint64_t* bars_, const float* gw_, const int* seq_, int seq_len_, int total_,
-                         int depth_, uint32_t bytes_ = lay::BLOB_BYTES) {
+                         int depth_, uint32_t bytes_ = lay::BLOB_BYTES, int stride_ = lay::BLOB) {
         slots = slots_; bars = bars_; gw = gw_; seq = seq_; seq_len = seq_len_; total = total_; depth = depth_;
-        head = 0; tail = 0; bytes = bytes_;
+        head = 0; tail = 0; bytes = bytes_; stride = stride_;
         if (threadIdx.x == 0) {
             for (int i = 0; i < depth; ++i) mbar_init(&bars[i], 1);
             mbar_fence_init();
@@ -38,7 +39,7 @@ struct Ring {
             while (tail < head + depth && tail < total) {
                 const int s = tail % depth;
                 mbar_expect_tx(&bars[s], bytes);
-                bulk_g2s(slots + (size_t)s * lay::BLOB, gw + seq[tail % seq_len], bytes, &bars[s]);
+                bulk_g2s(slots + (size_t)s * stride, gw + seq[tail % seq_len], bytes, &bars[s]);
                 ++tail;
             }
         }
@@ -46,7 +47,7 @@ struct Ring {
     __device__ const float* acquire() {
         const int s = head % depth;
         mbar_wait(&bars[s], (head / depth) & 1);
-        return slots + (size_t)s * lay::BLOB;
+        return slots + (size_t)s * stride;
     }
     __device__ void release() { ++head; }
 };
