@@ -262,7 +262,10 @@ def run_ours(ns):
     e2e_K = max(1, min(ns.steps, ns.e2e_steps))
     e2e_ms = timed(e2e_step, e2e_start, e2e_K, 1)
     e2e_value = world * B * e2e_K / (e2e_ms * 1e-3)
-    h2d = B * L * (7 + 2) * 4 + B * L * 4
+    # host -> device per step: policy inputs (obs, ava), env actions, and the buffer insert of host arrays
+    # (share_obs row, obs, ava, actions, log-probs, values, reward, mask); device -> host: values, actions,
+    # log-probs, and the env outputs (obs, ava, share_obs row, reward, done, delay, payment)
+    h2d = B * L * (7 + 2) * 4 + B * L * 4 + (B * (W + 2) + B * L * (7 + 2) + 3 * B * L + 2 * B) * 4
     d2h = 3 * B * L * 4 + B * L * (7 + 2) * 4 + B * (W + 2) * 4 + B * 13
 
     # ---- secondary metric: PPO update rows/s (BASELINE configs[3] shape per GPU) ----------------

@@ -100,9 +100,6 @@ class DcmlVecEnv:
         self.done = torch.empty(self.N, dtype=torch.uint8, device=self.device)
         self.delay = torch.empty(self.N, **f32)
         self.payment = torch.empty(self.N, **f32)
-        # pinned host staging for the reference-style numpy API
-        pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
-        self._host = {k: pin(getattr(self, k)) for k in ("obs", "sob", "ava", "reward", "done", "delay", "payment")}
         self._h_act = torch.empty(self.N, self.L, dtype=torch.float32, pin_memory=True)
 
     def close(self):
@@ -150,37 +147,44 @@ class DcmlVecEnv:
 
     # ---- the reference's host-side contract -------------------------------------------------
     def _fetch(self, names):
+        """Device -> host copies into FRESH pinned tensors (torch's caching host allocator recycles the
+        blocks), so the numpy arrays handed out below are zero-copy views the caller owns, as with the
+        reference's freshly allocated arrays."""
+        host = {}
         for k in names:
-            self._host[k].copy_(getattr(self, k), non_blocking=True)
+            src = getattr(self, k)
+            host[k] = torch.empty(src.shape, dtype=src.dtype, pin_memory=True).copy_(src, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
+        return host
 
-    def _host_obs(self):
+    def _host_obs(self, host):
         dt = self.host_dtype
-        obs = self._host["obs"].numpy().astype(dt)
-        row = self._host["sob"].numpy().astype(dt)[:, None, :]
+        obs = host["obs"].numpy().astype(dt, copy=False)
+        row = host["sob"].numpy().astype(dt, copy=False)[:, None, :]
         sob = np.repeat(row, self.L, axis=1) if self.replicate_share_obs else np.broadcast_to(row, (self.N, self.L, self.sob_dim))
-        ava = self._host["ava"].numpy().astype(np.int64 if dt == np.float64 else dt)
+        ava = host["ava"].numpy().astype(np.int64 if dt == np.float64 else dt, copy=False)
         return obs, sob, ava
 
     def reset(self):
         self.reset_device()
-        self._fetch(("obs", "sob", "ava"))
-        return self._host_obs()
+        return self._host_obs(self._fetch(("obs", "sob", "ava")))
 
     def step(self, actions):
-        if torch.is_tensor(actions):
-            self._h_act.copy_(actions.reshape(self.N, self.L))
-        else:
-            self._h_act.copy_(torch.from_numpy(np.ascontiguousarray(actions, dtype=np.float32).reshape(self.N, self.L)))
-        self.step_device(self._h_act.to(self.device, non_blocking=True))
-        self._fetch(("obs", "sob", "ava", "reward", "done", "delay", "payment"))
-        obs, sob, ava = self._host_obs()
+        if not torch.is_tensor(actions):
+            actions = torch.from_numpy(np.ascontiguousarray(actions, dtype=np.float32))
+        actions = actions.reshape(self.N, self.L)
+        if actions.device.type == "cpu" and not (actions.dtype == torch.float32 and actions.is_contiguous() and actions.is_pinned()):
+            self._h_act.copy_(actions)             # pageable / strided / non-fp32 input: stage through pinned memory
+            actions = self._h_act
+        self.step_device(actions.to(self.device, non_blocking=True))
+        host = self._fetch(("obs", "sob", "ava", "reward", "done", "delay", "payment"))
+        obs, sob, ava = self._host_obs(host)
         dt = self.host_dtype
-        rew = self._host["reward"].numpy().astype(dt)[:, None, None]
-        dones = self._host["done"].numpy().astype(bool)[:, None]
+        rew = host["reward"].numpy().astype(dt, copy=False)[:, None, None]
+        dones = host["done"].numpy().astype(bool)[:, None]
         if self.replicate_share_obs:
             rew, dones = np.repeat(rew, self.L, axis=1), np.repeat(dones, self.L, axis=1)
         else:
             rew, dones = np.broadcast_to(rew, (self.N, self.L, 1)), np.broadcast_to(dones, (self.N, self.L))
-        infos = _Infos(self._host["delay"].numpy().copy(), self._host["payment"].numpy().copy())
+        infos = _Infos(host["delay"].numpy(), host["payment"].numpy())
         return obs, sob, rew, dones, infos, ava

@@ -232,8 +232,14 @@ class MultiAgentTransformer(nn.Module):
             x = x.reshape(shape)
         return x.contiguous()
 
-    def _out(self, x):
-        return x if self.output_device.type == "cuda" else x.to(self.output_device)
+    def _out(self, *xs):
+        """Results on ``output_device``.  Host outputs go through fresh pinned tensors (recycled by torch's
+        caching host allocator) with one stream synchronisation for all of them."""
+        if self.output_device.type == "cuda":
+            return xs if len(xs) > 1 else xs[0]
+        hs = tuple(torch.empty(x.shape, dtype=x.dtype, pin_memory=True).copy_(x, non_blocking=True) for x in xs)
+        torch.cuda.current_stream(self.device).synchronize()
+        return hs if len(hs) > 1 else hs[0]
 
     # ---- the reference's methods ------------------------------------------------------------
     def get_values(self, state, obs, available_actions=None):
@@ -281,7 +287,8 @@ class MultiAgentTransformer(nn.Module):
                 _cabi.stream_ptr()))
         if self.action_type == "Discrete":
             actions = actions.long()          # transformer_act.py:135
-        return self._out(actions), self._out(logp), values
+        actions, logp = self._out(actions, logp)
+        return actions, logp, values
 
     def forward(self, state, obs, action, available_actions=None, THOP_FLAG=False):
         """ma_transformer.py:257-295 -> (action_log (B,L,1), v_loc (B,L,1), entropy (B,L,1)).

@@ -62,7 +62,7 @@ def semi_discrete_autoregreesive_act(decoder, obs_rep, obs, batch_size, n_agent,
         raise NotImplementedError("semi_index must be -1")
     m = _model(decoder)
     a, lp = _autoregressive(decoder, obs_rep, n_agent, available_actions, deterministic, stride, _cabi.MODE_SEMI)
-    return m._out(a), m._out(lp)
+    return m._out(a, lp)
 
 
 def semi_discrete_parallel_act(decoder, obs_rep, obs, action, batch_size, n_agent, action_dim, tpdv,
@@ -76,7 +76,7 @@ def discrete_autoregreesive_act(decoder, obs_rep, obs, batch_size, n_agent, acti
                                 available_actions=None, deterministic=False):
     m = _model(decoder)
     a, lp = _autoregressive(decoder, obs_rep, n_agent, available_actions, deterministic, 4, _cabi.MODE_DISCRETE)
-    return m._out(a.long()), m._out(lp)
+    return m._out(a.long(), lp)
 
 
 def discrete_parallel_act(decoder, obs_rep, obs, action, batch_size, n_agent, action_dim, tpdv,
