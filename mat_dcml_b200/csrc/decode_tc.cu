@@ -1,0 +1,519 @@
+// Tensor-core (tcgen05) autoregressive decode for sm_100a (get_actions / *_autoregreesive_act,
+// mat_src/mat/algorithms/utils/transformer_act.py:8-100,131-173; Decoder of ma_transformer.py:157-230).
+//
+// One persistent 512-thread CTA per SM owns a tile of up to 128 envs and walks the decode schedule
+// position by position.  Per position and decoder block:
+//     x -> operand U, self cache row        FA0|FA1: q'_0, q'_1 = folded queries       (2 MMA sets, TMEM 0-255)
+//     absorbed self-attention over the cached layer inputs (CUDA cores, 8 lanes per env) -> ctx_0 -> U, ctx_1 -> V
+//     FB0.ctx_0 + FB1.ctx_1 (one accumulator) + x -> LN1 -> x1 -> cross cache row
+//     absorbed cross-attention (queries q2' precomputed from obs_rep)                   -> ctx_0 -> U, ctx_1 -> V
+//     FC0.ctx_0 + FC1.ctx_1 + obs_rep -> LN2 -> x2 -> U     M0: GELU -> h -> V     M2 + x2 -> LN3 -> x3
+// then the logits head and the action pick.  All [128 x 64].[64 x 64] products are fp16 hi + scaled-lo MMAs
+// with fp32 accumulators in tensor memory (tc.cuh); epilogues are thread-per-row: warp w owns rows
+// 32*(w % 4) + lane and the 16 accumulator columns of quarter w / 4.
+#include "policy_fwd.h"
+#include "tc.cuh"
+
+using namespace tile;
+
+namespace {
+
+constexpr int NTD = 512;             // threads per CTA
+constexpr int MAXR = 128;            // env rows per tile (MMA M)
+constexpr int DEPTH = 4;             // weight ring slots
+constexpr int TMEM_D = 256;          // accumulator columns
+constexpr int OP_BYTES = 2 * tc::A_PART;
+
+__constant__ int c_tc_decode[lay::DEC_FOLD_STEP_BLOBS] = {
+    lay::hb(lay::fold_blob(0, lay::FA0)), lay::hb(lay::fold_blob(0, lay::FA1)), lay::hb(lay::fold_blob(0, lay::FB0)),
+    lay::hb(lay::fold_blob(0, lay::FB1)), lay::hb(lay::fold_blob(0, lay::FC0)), lay::hb(lay::fold_blob(0, lay::FC1)),
+    lay::hb(lay::dec_blob(0, lay::DM0)), lay::hb(lay::dec_blob(0, lay::DM2)),
+    lay::hb(lay::fold_blob(1, lay::FA0)), lay::hb(lay::fold_blob(1, lay::FA1)), lay::hb(lay::fold_blob(1, lay::FB0)),
+    lay::hb(lay::fold_blob(1, lay::FB1)), lay::hb(lay::fold_blob(1, lay::FC0)), lay::hb(lay::fold_blob(1, lay::FC1)),
+    lay::hb(lay::dec_blob(1, lay::DM0)), lay::hb(lay::dec_blob(1, lay::DM2)),
+    lay::hb(lay::DEC_H0)};
+
+struct DSmem {
+    unsigned char* U;      // operand buffers [hi | lo][128][128 B]
+    unsigned char* V;
+    float* ring;           // DEPTH slots
+    float* sQ0;            // [128][XS] folded self-attention queries, head 0 / head 1
+    float* sQ1;
+    float* sEmb;           // [6][64] token embedding table
+    float* sHead;          // DEC_H3 group
+    float* sRed;           // [2][128][4] LayerNorm partials
+    float* sLog;           // [128][4][2] logit partials
+    int* sCode;            // [128]
+    uint32_t* bits;        // [128][8] per-env action bitset
+    uint64_t* bars;        // [0, DEPTH): ring, [7]: MMA completion
+    uint32_t* tmem_slot;
+};
+constexpr size_t DSMEM_FLOATS = 384 + 160 + 1024 + 1024 + 128 + 1024;
+__host__ __device__ constexpr size_t dsmem_bytes() {
+    return 1024 + 2 * (size_t)OP_BYTES + (size_t)DEPTH * tc::SLOT_BYTES + 2 * (size_t)tc::TILE_BYTES + DSMEM_FLOATS * 4 + 8 * 8 + 16;
+}
+__device__ inline DSmem dcarve(unsigned char* raw) {
+    DSmem s;
+    unsigned char* p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
+    s.U = p; p += OP_BYTES;
+    s.V = p; p += OP_BYTES;
+    s.ring = reinterpret_cast<float*>(p); p += (size_t)DEPTH * tc::SLOT_BYTES;
+    s.sQ0 = reinterpret_cast<float*>(p); p += tc::TILE_BYTES;
+    s.sQ1 = reinterpret_cast<float*>(p); p += tc::TILE_BYTES;
+    float* f = reinterpret_cast<float*>(p);
+    s.sEmb = f; f += 384;
+    s.sHead = f; f += 160;
+    s.sRed = f; f += 1024;
+    s.sLog = f; f += 1024;
+    s.sCode = reinterpret_cast<int*>(f); f += 128;
+    s.bits = reinterpret_cast<uint32_t*>(f); f += 1024;
+    s.bars = reinterpret_cast<uint64_t*>(f);
+    s.tmem_slot = reinterpret_cast<uint32_t*>(s.bars + 8);
+    return s;
+}
+
+// ---- 16-column (quarter-row) helpers ---------------------------------------------------------------
+// v = D1 + 2^-11 D2 for this thread's row and quarter; accumulator set at TMEM column `cols`
+__device__ __forceinline__ void result16(uint32_t tmem, int cols, int row, int q, float (&v)[16]) {
+    uint32_t v1[16], v2[16];
+    const uint32_t taddr = tmem + ((uint32_t)(row & ~31) << 16) + cols + q * 16;
+    TC_LD16(v1, taddr);
+    TC_LD16(v2, taddr + 64);
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = fmaf(__uint_as_float(v2[i]), 1.0f / 2048.0f, __uint_as_float(v1[i]));
+}
+__device__ __forceinline__ void add16(float (&v)[16], const float* __restrict__ p) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float4 x = *reinterpret_cast<const float4*>(p + j * 4);
+        v[j * 4] += x.x; v[j * 4 + 1] += x.y; v[j * 4 + 2] += x.z; v[j * 4 + 3] += x.w;
+    }
+}
+__device__ __forceinline__ void load16(float (&v)[16], const float* __restrict__ p) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float4 x = *reinterpret_cast<const float4*>(p + j * 4);
+        v[j * 4] = x.x; v[j * 4 + 1] = x.y; v[j * 4 + 2] = x.z; v[j * 4 + 3] = x.w;
+    }
+}
+__device__ __forceinline__ void store16(float* __restrict__ p, const float (&v)[16]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) *reinterpret_cast<float4*>(p + j * 4) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+}
+__device__ __forceinline__ void affine16(float (&v)[16], const float* __restrict__ blob, int q) {
+    const float4* w = reinterpret_cast<const float4*>(blob + lay::B_LNW + q * 16);
+    const float4* b = reinterpret_cast<const float4*>(blob + lay::B_LNB + q * 16);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float4 ww = w[j], bb = b[j];
+        v[j * 4] = fmaf(v[j * 4], ww.x, bb.x); v[j * 4 + 1] = fmaf(v[j * 4 + 1], ww.y, bb.y);
+        v[j * 4 + 2] = fmaf(v[j * 4 + 2], ww.z, bb.z); v[j * 4 + 3] = fmaf(v[j * 4 + 3], ww.w, bb.w);
+    }
+}
+// columns [16q, 16q + 16) of row `row` as fp16 hi / scaled-lo operand chunks
+__device__ __forceinline__ void store_operand16(unsigned char* op, int row, int q, const float (&v)[16]) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        __half2 h[4], l[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tc::split2(v[j * 8 + 2 * i], v[j * 8 + 2 * i + 1], h[i], l[i]);
+        const uint32_t off = row * 128 + (((q * 2 + j) ^ (row & 7)) << 4);
+        *reinterpret_cast<uint4*>(op + off) = make_uint4(*reinterpret_cast<uint32_t*>(&h[0]), *reinterpret_cast<uint32_t*>(&h[1]),
+                                                         *reinterpret_cast<uint32_t*>(&h[2]), *reinterpret_cast<uint32_t*>(&h[3]));
+        *reinterpret_cast<uint4*>(op + tc::A_PART + off) = make_uint4(*reinterpret_cast<uint32_t*>(&l[0]), *reinterpret_cast<uint32_t*>(&l[1]),
+                                                                      *reinterpret_cast<uint32_t*>(&l[2]), *reinterpret_cast<uint32_t*>(&l[3]));
+    }
+}
+// the same columns back as fp32: hi + 2^-11 lo (equal to the stored value to 2^-22 relative)
+__device__ __forceinline__ void add_operand16(float (&v)[16], const unsigned char* op, int row, int q) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const uint32_t off = row * 128 + (((q * 2 + j) ^ (row & 7)) << 4);
+        const uint4 h = *reinterpret_cast<const uint4*>(op + off);
+        const uint4 l = *reinterpret_cast<const uint4*>(op + tc::A_PART + off);
+        const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hw[i]));
+            const float2 lf = __half22float2(*reinterpret_cast<const __half2*>(&lw[i]));
+            v[j * 8 + 2 * i] += fmaf(lf.x, 1.0f / 2048.0f, hf.x);
+            v[j * 8 + 2 * i + 1] += fmaf(lf.y, 1.0f / 2048.0f, hf.y);
+        }
+    }
+}
+// LayerNorm of a 64-column row held by four threads (16 columns each).  Two CTA barriers.  v becomes x_hat.
+__device__ __forceinline__ void layernorm_quad(float (&v)[16], float* __restrict__ sRed, int row, int q) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += v[i];
+    sRed[row * 4 + q] = s;
+    __syncthreads();
+    const float4 a = *reinterpret_cast<const float4*>(sRed + row * 4);
+    const float mean = (a.x + a.y + a.z + a.w) * (1.0f / 64.0f);
+    float d = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { v[i] -= mean; d = fmaf(v[i], v[i], d); }
+    sRed[4 * MAXR + row * 4 + q] = d;
+    __syncthreads();
+    const float4 c = *reinterpret_cast<const float4*>(sRed + 4 * MAXR + row * 4);
+    const float rs = rsqrtf((c.x + c.y + c.z + c.w) * (1.0f / 64.0f) + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] *= rs;
+}
+
+// Absorbed attention (tile::attention_absorbed) for 512 threads with tensor-core operand outputs: 8 lanes
+// per env, lane g holds columns 4g..4g+3 and 32+4g..35+4g of every 64-float row; folded queries from the
+// shared tiles (GQ = false) or from global rows q0 / q1 + r * q_stride (GQ = true); ctx_0 -> U, ctx_1 -> V.
+// Env row r attends to nk cached rows at cache + r * slot_stride (0 rows when r >= n_valid).
+template <bool GQ>
+__device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
+                                                      const float* cache, long slot_stride, int rows, int n_valid, int nk,
+                                                      unsigned char* U, unsigned char* V) {
+    constexpr int KB = 2;
+    const int tid = threadIdx.x, grp = tid >> 3, g = tid & 7;
+    const unsigned gmask = 0xffu << (tid & 24);
+    const bool up = (g & 4) != 0;
+    for (int r = grp; r < rows; r += NTD / 8) {
+        const int nr = r < n_valid ? nk : 0;
+        float4 qa0, qb0, qa1, qb1;
+        if (GQ) {
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4* p0 = reinterpret_cast<const float4*>(q0 + (long)r * q_stride);
+            const float4* p1 = reinterpret_cast<const float4*>(q1 + (long)r * q_stride);
+            qa0 = nr ? __ldg(p0 + g) : z; qb0 = nr ? __ldg(p0 + 8 + g) : z;
+            qa1 = nr ? __ldg(p1 + g) : z; qb1 = nr ? __ldg(p1 + 8 + g) : z;
+        } else {
+            qa0 = *reinterpret_cast<const float4*>(q0 + r * XS + g * 4);
+            qb0 = *reinterpret_cast<const float4*>(q0 + r * XS + 32 + g * 4);
+            qa1 = *reinterpret_cast<const float4*>(q1 + r * XS + g * 4);
+            qb1 = *reinterpret_cast<const float4*>(q1 + r * XS + 32 + g * 4);
+        }
+        const float4* xp = reinterpret_cast<const float4*>(cache + (long)r * slot_stride) + g;   // row t: xp[t*16], xp[t*16 + 8]
+        float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+        float4 ca0 = make_float4(0.f, 0.f, 0.f, 0.f), cb0 = ca0, ca1 = ca0, cb1 = ca0;
+        auto batch = [&](const float4 (&xa)[KB], const float4 (&xb)[KB], int t0) {
+            float s0[KB], s1[KB];
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                const float p0 = qa0.x * xa[i].x + qa0.y * xa[i].y + qa0.z * xa[i].z + qa0.w * xa[i].w +
+                                 qb0.x * xb[i].x + qb0.y * xb[i].y + qb0.z * xb[i].z + qb0.w * xb[i].w;
+                const float p1 = qa1.x * xa[i].x + qa1.y * xa[i].y + qa1.z * xa[i].z + qa1.w * xa[i].w +
+                                 qb1.x * xb[i].x + qb1.y * xb[i].y + qb1.z * xb[i].z + qb1.w * xb[i].w;
+                float v = up ? p1 : p0;
+                v += __shfl_xor_sync(gmask, up ? p0 : p1, 4);
+                v += __shfl_xor_sync(gmask, v, 2);
+                v += __shfl_xor_sync(gmask, v, 1);
+                const float o = __shfl_xor_sync(gmask, v, 4);
+                const bool ok = t0 + i < nr;
+                s0[i] = ok ? (up ? o : v) : -INFINITY;
+                s1[i] = ok ? (up ? v : o) : -INFINITY;
+            }
+            float n0 = m0, n1 = m1;
+#pragma unroll
+            for (int i = 0; i < KB; ++i) { n0 = fmaxf(n0, s0[i]); n1 = fmaxf(n1, s1[i]); }
+            const float a0 = exp2f(m0 - n0), a1 = exp2f(m1 - n1);
+            l0 *= a0; l1 *= a1;
+            ca0.x *= a0; ca0.y *= a0; ca0.z *= a0; ca0.w *= a0; cb0.x *= a0; cb0.y *= a0; cb0.z *= a0; cb0.w *= a0;
+            ca1.x *= a1; ca1.y *= a1; ca1.z *= a1; ca1.w *= a1; cb1.x *= a1; cb1.y *= a1; cb1.z *= a1; cb1.w *= a1;
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                const float p0 = exp2f(s0[i] - n0), p1 = exp2f(s1[i] - n1);
+                l0 += p0; l1 += p1;
+                ca0.x = fmaf(p0, xa[i].x, ca0.x); ca0.y = fmaf(p0, xa[i].y, ca0.y); ca0.z = fmaf(p0, xa[i].z, ca0.z); ca0.w = fmaf(p0, xa[i].w, ca0.w);
+                cb0.x = fmaf(p0, xb[i].x, cb0.x); cb0.y = fmaf(p0, xb[i].y, cb0.y); cb0.z = fmaf(p0, xb[i].z, cb0.z); cb0.w = fmaf(p0, xb[i].w, cb0.w);
+                ca1.x = fmaf(p1, xa[i].x, ca1.x); ca1.y = fmaf(p1, xa[i].y, ca1.y); ca1.z = fmaf(p1, xa[i].z, ca1.z); ca1.w = fmaf(p1, xa[i].w, ca1.w);
+                cb1.x = fmaf(p1, xb[i].x, cb1.x); cb1.y = fmaf(p1, xb[i].y, cb1.y); cb1.z = fmaf(p1, xb[i].z, cb1.z); cb1.w = fmaf(p1, xb[i].w, cb1.w);
+            }
+            m0 = n0; m1 = n1;
+        };
+        auto fetch = [&](float4 (&xa)[KB], float4 (&xb)[KB], int t0) {
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                const bool ok = t0 + i < nr;
+                xa[i] = ok ? xp[(long)(t0 + i) * 16] : make_float4(0.f, 0.f, 0.f, 0.f);
+                xb[i] = ok ? xp[(long)(t0 + i) * 16 + 8] : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        };
+        float4 xa[KB], xb[KB], ya[KB], yb[KB];
+        fetch(xa, xb, 0);
+        for (int t0 = 0; t0 < nr; t0 += 2 * KB) {
+            fetch(ya, yb, t0 + KB);
+            batch(xa, xb, t0);
+            fetch(xa, xb, t0 + 2 * KB);
+            if (t0 + KB < nr) batch(ya, yb, t0 + KB);
+        }
+        const float i0 = nr > 0 ? 1.0f / l0 : 0.f, i1 = nr > 0 ? 1.0f / l1 : 0.f;
+        tc::store_operand4(U, r, g, make_float4(ca0.x * i0, ca0.y * i0, ca0.z * i0, ca0.w * i0));
+        tc::store_operand4(U, r, 8 + g, make_float4(cb0.x * i0, cb0.y * i0, cb0.z * i0, cb0.w * i0));
+        tc::store_operand4(V, r, g, make_float4(ca1.x * i1, ca1.y * i1, ca1.z * i1, ca1.w * i1));
+        tc::store_operand4(V, r, 8 + g, make_float4(cb1.x * i1, cb1.y * i1, cb1.z * i1, cb1.w * i1));
+    }
+}
+
+__global__ void __launch_bounds__(NTD, 1)
+decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    DSmem s = dcarve(smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = (warp & 3) * 32 + (tid & 31), q = warp >> 2;
+    const int L = a.L;
+    const long n_tiles = (a.B + rows - 1) / rows;
+    long my_tiles = 0;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++my_tiles;
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_tc_decode, lay::DEC_FOLD_STEP_BLOBS, (int)(my_tiles * a.n_steps * lay::DEC_FOLD_STEP_BLOBS), DEPTH,
+              lay::BLOB_BYTES, tc::SLOT_F);
+    uint64_t* mma_bar = &s.bars[tc::MMA_BAR];
+    if (tid == 0) { mbar_init(mma_bar, 1); mbar_fence_init(); }
+    if (warp == 0) tc::tmem_alloc_n<TMEM_D>(s.tmem_slot);
+    build_emb_table(s.sEmb, b.w);
+    for (int i = tid; i < lay::DEC_H3_SIZE; i += NTD) s.sHead[i] = b.w[lay::DEC_H3 + i];
+    for (int i = tid; i < 2 * OP_BYTES / 16; i += NTD) reinterpret_cast<uint4*>(s.U)[i] = make_uint4(0u, 0u, 0u, 0u);   // U and V
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    ring.prefetch();
+    const uint32_t tmem = *s.tmem_slot;
+    const uint32_t uaddr = smem_u32(s.U), vaddr = smem_u32(s.V);
+    uint32_t phase = 0;
+    auto mma_wait = [&]() {
+        mbar_wait(mma_bar, phase);
+        phase ^= 1;
+        tc::fence_after_sync();
+    };
+
+    const long slot_stride = 4L * L * 64;      // [blk 2][self | cross][L][64] cached attention inputs per env slot
+    float* kv0 = b.kv + (long)blockIdx.x * rows * slot_stride;
+    const int nd = a.mode == MATAS_MODE_SEMI ? L - 1 : L;
+    const float sd1 = 0.5f / (1.0f + expf(-s.sHead[lay::DEC_H3_LOGSTD + 1]));
+    float* sQ0row = s.sQ0 + row * XS + q * 16;
+    float* sQ1row = s.sQ1 + row * XS + q * 16;
+
+    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long env0 = tile * rows;
+        const int n_valid = (int)min((long)rows, a.B - env0);
+        const bool live = row < n_valid;           // this thread's row maps to an env
+        for (int i = tid; i < MAXR * 8; i += NTD) s.bits[i] = 0u;
+        DecSched sched;
+        sched.init(L, a.mode, a.deterministic, a.stride);
+        DecStep st;
+        __syncthreads();
+        while (sched.next(st)) {
+            const int j = st.j;
+            // ---- input token of this position ------------------------------------------------------
+            if (tid < MAXR) {
+                int code;
+                const uint32_t* bt = s.bits + tid * 8;
+                if (st.kind == 1) code = j == 0 ? 1 : 0;
+                else if (st.kind == 0) code = j == 0 ? 1 : 2 + (int)((bt[(j - 1) >> 5] >> ((j - 1) & 31)) & 1u);
+                else code = (j == 0 ? 4 : 2) + (int)((bt[j >> 5] >> (j & 31)) & 1u);
+                s.sCode[tid] = code;
+            }
+            __syncthreads();
+            float v[16];
+            load16(v, s.sEmb + s.sCode[row] * 64 + q * 16);
+            for (int blk = 0; blk < 2; ++blk) {
+                float* cx1 = kv0 + (blk * 2 + 0) * (long)L * 64;     // self-attention inputs (block input x)
+                float* cx2 = kv0 + (blk * 2 + 1) * (long)L * 64;     // cross-attention inputs (x after LN1)
+                float* x_row = cx1 + (long)row * slot_stride + (long)j * 64 + q * 16;
+                // ---- folded self-attention queries ---------------------------------------------------
+                store_operand16(s.U, row, q, v);
+                if (live) store16(x_row, v);
+                {
+                    const float* w0 = ring.peek(0);
+                    const float* w1 = ring.peek(1);
+                    tc::publish();
+                    if (tid == 0) {
+                        tc::mma_set(tmem, uaddr, smem_u32(w0), false);
+                        tc::mma_set(tmem + 128, uaddr, smem_u32(w1), false);
+                        tc::mma_commit(mma_bar);
+                    }
+                    ring.prefetch();
+                    mma_wait();
+                    result16(tmem, 0, row, q, v);
+                    add16(v, w0 + lay::B_BIAS + q * 16);
+                    store16(sQ0row, v);
+                    result16(tmem, 128, row, q, v);
+                    add16(v, w1 + lay::B_BIAS + q * 16);
+                    store16(sQ1row, v);
+                    ring.release(); ring.release();
+                }
+                tc::fence_before_sync();
+                __syncthreads();
+                attention_absorbed_op<false>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                // ---- self-attention output maps + x -> LN1 -> cross cache row -------------------------
+                {
+                    const float* w0 = ring.peek(0);
+                    const float* w1 = ring.peek(1);
+                    tc::publish();
+                    if (tid == 0) {
+                        tc::mma_set(tmem, uaddr, smem_u32(w0), false);
+                        tc::mma_set(tmem, vaddr, smem_u32(w1), true);
+                        tc::mma_commit(mma_bar);
+                    }
+                    ring.prefetch();
+                    mma_wait();
+                    result16(tmem, 0, row, q, v);
+                    add16(v, w1 + lay::B_BIAS + q * 16);
+                    if (live) add16(v, x_row);
+                    layernorm_quad(v, s.sRed, row, q);
+                    affine16(v, w1, q);
+                    ring.release(); ring.release();
+                    if (live) store16(cx2 + (long)row * slot_stride + (long)j * 64 + q * 16, v);
+                }
+                tc::fence_before_sync();
+                __syncthreads();
+                // ---- cross-attention: folded queries q2' precomputed from obs_rep ------------------------
+                attention_absorbed_op<true>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64, cx2,
+                                            slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                {
+                    const float* w0 = ring.peek(0);
+                    const float* w1 = ring.peek(1);
+                    tc::publish();
+                    if (tid == 0) {
+                        tc::mma_set(tmem, uaddr, smem_u32(w0), false);
+                        tc::mma_set(tmem, vaddr, smem_u32(w1), true);
+                        tc::mma_commit(mma_bar);
+                    }
+                    ring.prefetch();
+                    mma_wait();
+                    result16(tmem, 0, row, q, v);
+                    add16(v, w1 + lay::B_BIAS + q * 16);
+                    if (live) add16(v, b.rep + ((env0 + row) * L + j) * 64 + q * 16);
+                    layernorm_quad(v, s.sRed, row, q);
+                    affine16(v, w1, q);
+                    ring.release(); ring.release();
+                    store_operand16(s.U, row, q, v);               // x2
+                }
+                // ---- MLP ---------------------------------------------------------------------------------
+                {
+                    const float* w0 = ring.peek(0);
+                    tc::publish();
+                    if (tid == 0) { tc::mma_set(tmem, uaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
+                    ring.prefetch();
+                    mma_wait();
+                    result16(tmem, 0, row, q, v);
+                    add16(v, w0 + lay::B_BIAS + q * 16);
+                    ring.release();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
+                    store_operand16(s.V, row, q, v);
+                }
+                {
+                    const float* w0 = ring.peek(0);
+                    tc::publish();
+                    if (tid == 0) { tc::mma_set(tmem, vaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
+                    ring.prefetch();
+                    mma_wait();
+                    result16(tmem, 0, row, q, v);
+                    add16(v, w0 + lay::B_BIAS + q * 16);
+                    add_operand16(v, s.U, row, q);                 // + x2
+                    layernorm_quad(v, s.sRed, row, q);
+                    affine16(v, w0, q);
+                    ring.release();
+                }
+            }
+            // ---- logits head + action pick -------------------------------------------------------------
+            if (st.emit) {
+                store_operand16(s.U, row, q, v);
+                const float* w0 = ring.peek(0);
+                tc::publish();
+                if (tid == 0) { tc::mma_set(tmem, uaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
+                ring.prefetch();
+                mma_wait();
+                result16(tmem, 0, row, q, v);
+                add16(v, w0 + lay::B_BIAS + q * 16);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
+                layernorm_quad(v, s.sRed, row, q);
+                affine16(v, w0, q);
+                ring.release();
+                float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    d0 = fmaf(v[i], s.sHead[q * 16 + i], d0);
+                    d1 = fmaf(v[i], s.sHead[64 + q * 16 + i], d1);
+                }
+                s.sLog[(row * 4 + q) * 2] = d0;
+                s.sLog[(row * 4 + q) * 2 + 1] = d1;
+                tc::fence_before_sync();
+                __syncthreads();
+                if (tid < n_valid) {
+                    const long env = env0 + tid;
+                    const long g = env * L + j;
+                    const float* lp = s.sLog + tid * 8;
+                    const float l0 = lp[0] + lp[2] + lp[4] + lp[6] + s.sHead[lay::DEC_H3_B];
+                    const float l1 = lp[1] + lp[3] + lp[5] + lp[7] + s.sHead[lay::DEC_H3_B + 1];
+                    if (j < nd) {
+                        float z0, z1;
+                        masked_logz(l0, l1, a.ava ? a.ava + g * 2 : nullptr, z0, z1);
+                        int act;
+                        if (a.deterministic) {
+                            act = z1 > z0;
+                        } else {
+                            const float zm = fmaxf(z0, z1);
+                            const float e0 = expf(z0 - zm), e1 = expf(z1 - zm);
+                            const float p0 = e0 / (e0 + e1);
+                            const float u = a.u ? a.u[g]
+                                                : u01f(philox4x32((uint32_t)(a.env_offset + env), a.step, rng_tag(S_POLICY, j), 0, a.seed).x);
+                            act = u >= p0;
+                        }
+                        a.actions[g] = (float)act;
+                        a.logp[g] = act ? z1 : z0;
+                        if (act) s.bits[tid * 8 + (j >> 5)] |= 1u << (j & 31);
+                        else s.bits[tid * 8 + (j >> 5)] &= ~(1u << (j & 31));
+                    } else {
+                        float z = 0.f;
+                        if (!a.deterministic) {
+                            if (a.z) z = a.z[env * 2 + 1];
+                            else {
+                                const uint4 x = philox4x32((uint32_t)(a.env_offset + env), a.step, rng_tag(S_POLICY, j), 0, a.seed);
+                                const float r1 = sqrtf(-2.0f * logf(((float)(x.z >> 8) + 1.0f) * (1.0f / 16777216.0f)));
+                                z = r1 * cospif(2.0f * ((float)(x.w >> 8) * (1.0f / 16777216.0f)));
+                            }
+                        }
+                        const float act = l1 + sd1 * z;
+                        const float d = act - l1;
+                        a.actions[g] = act;
+                        a.logp[g] = -(d * d) / (2.0f * sd1 * sd1) - logf(sd1) - HALF_LOG_2PI;
+                    }
+                }
+            } else {
+                ring.peek(0);
+                ring.release();
+            }
+            __syncthreads();
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc_n<TMEM_D>(tmem);
+}
+
+}  // namespace
+
+// rows per tile: spread the envs over the SMs (one CTA each), a multiple of 8, at most 128
+int decode_tc_rows(long B, int n_sm) {
+    long r = (B + n_sm - 1) / n_sm;
+    r = (r + 7) / 8 * 8;
+    if (r < 8) r = 8;
+    if (r > MAXR) r = MAXR;
+    return (int)r;
+}
+
+int decode_tc_geometry(long B, int n_sm, int* grid, long* slots) {
+    const int rows = decode_tc_rows(B, n_sm);
+    const long n_tiles = (B + rows - 1) / rows;
+    *grid = (int)(n_tiles < n_sm ? n_tiles : n_sm);
+    *slots = (long)*grid * rows;
+    return MATAS_OK;
+}
+
+int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st) {
+    const size_t bytes = dsmem_bytes();
+    CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    decode_tc_kernel<<<grid, NTD, bytes, st>>>(b, a, decode_tc_rows(a.B, n_sm));
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}

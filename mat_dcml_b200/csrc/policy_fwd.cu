@@ -17,8 +17,6 @@ using namespace tile;
 
 namespace {
 
-constexpr float MASK_LOGIT = -1e10f;
-constexpr float HALF_LOG_2PI = 0.91893853320467274178f;
 
 // dynamic shared memory carve-up common to all tile kernels
 struct Smem {
@@ -278,34 +276,6 @@ q2_from_rep(PolicyBufs b, const float* __restrict__ rep_in, long n_tok, int dept
 }
 
 // -------------------------------------------------------------------------------------------------
-// action-token embedding table: emb[c] = LN(GELU(Wa . vec(c))) (ma_transformer.py:224-225)
-//   code 0: zero row, 1: start token (1,0,0), 2/3: one-hot of action 0/1, 4/5: start + one-hot
-// written to dst[6][64] by the first 96 threads (one half-warp per code)
-// -------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void build_emb_table(float* __restrict__ dst, const float* __restrict__ w) {
-    const int tid = threadIdx.x;
-    if (tid < 96) {
-        const int c = tid >> 4, cg = tid & 15;
-        const float f0 = (c == 1 || c >= 4) ? 1.f : 0.f, f1 = (c == 2 || c == 4) ? 1.f : 0.f, f2 = (c == 3 || c == 5) ? 1.f : 0.f;
-        const float* Wt = w + lay::DEC_EMB + lay::DEC_EMB_WT;
-        float v[4];
-        for (int i = 0; i < 4; ++i) {
-            const int col = cg * 4 + i;
-            v[i] = gelu_erf(f0 * Wt[col] + f1 * Wt[64 + col] + f2 * Wt[128 + col]);
-        }
-        const float mean = half_warp_sum(v[0] + v[1] + v[2] + v[3]) * (1.0f / 64.0f);
-        float var = 0.f;
-        for (int i = 0; i < 4; ++i) { v[i] -= mean; var += v[i] * v[i]; }
-        var = half_warp_sum(var) * (1.0f / 64.0f);
-        const float rs = rsqrtf(var + 1e-5f);
-        for (int i = 0; i < 4; ++i) {
-            const int col = cg * 4 + i;
-            dst[c * 64 + col] = v[i] * rs * w[lay::DEC_EMB + lay::DEC_EMB_LNW + col] + w[lay::DEC_EMB + lay::DEC_EMB_LNB + col];
-        }
-    }
-}
-
-// -------------------------------------------------------------------------------------------------
 // teacher-forced decoder, stage 1: shifted-action embedding -> X ; QKV1 of block 0
 // (transformer_act.py:103-111,176-181)
 // -------------------------------------------------------------------------------------------------
@@ -375,17 +345,6 @@ dec_attn1(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, int depth) {
 // per-token distribution head shared by evaluate and decode (transformer_act.py:8-28,112-128)
 struct HeadParams { float w0[64]; float w1[64]; float b0, b1, ls0, ls1; };
 
-__device__ __forceinline__ void masked_logz(float l0, float l1, const float* ava2, float& z0, float& z1) {
-    if (ava2) {
-        if (ava2[0] == 0.f) l0 = MASK_LOGIT;
-        if (ava2[1] == 0.f) l1 = MASK_LOGIT;
-    }
-    const float m = fmaxf(l0, l1);
-    const float lse = m + logf(expf(l0 - m) + expf(l1 - m));
-    z0 = l0 - lse;
-    z1 = l1 - lse;
-}
-
 // decoder block, second half: cross-attention (query = obs_rep) + proj + LN2(rep + .) + MLP + LN3;
 // block 0 then emits QKV1 of block 1, block 1 the logits head and the per-token log-prob / entropy.
 template <int RPT>
@@ -449,60 +408,6 @@ dec_attn2(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ actions
         }
     }
 }
-
-// -------------------------------------------------------------------------------------------------
-// autoregressive decode schedule (transformer_act.py:37-98 and :138-172), shared by host and device
-// -------------------------------------------------------------------------------------------------
-struct DecStep { int j; int kind; int emit; };   // kind 0: true predecessor, 1: speculative zero row, 2: own action
-
-struct DecSched {
-    int L, nd, stride, mode, det;
-    int s, e, j, phase, go, started;
-    __host__ __device__ void init(int L_, int mode_, int det_, int stride_) {
-        L = L_; mode = mode_; det = det_; stride = stride_ < 1 ? 1 : stride_;
-        nd = mode == MATAS_MODE_SEMI ? L - 1 : L;
-        s = 0; e = 1; j = 0; phase = 0; go = 1; started = 0;
-    }
-    __host__ __device__ bool next(DecStep& st) {
-        if (!det) {
-            if (j >= L) return false;
-            st.j = j++; st.kind = 0; st.emit = 1;
-            return true;
-        }
-        for (;;) {
-            if (phase == 0) {           // entering a block
-                if (!(e <= L && go)) return false;
-                if (e == L) go = 0;
-                phase = 1; j = s;
-            }
-            if (phase == 1) {           // speculative pass over [s, e)
-                if (j < e) {
-                    st.j = j; st.emit = 1;
-                    st.kind = mode == MATAS_MODE_SEMI ? (j == s ? 0 : 1) : 1;
-                    ++j;
-                    return true;
-                }
-                const bool more = mode == MATAS_MODE_SEMI ? (go != 0) : (e < L);
-                if (!more) return false;
-                phase = 2; j = mode == MATAS_MODE_SEMI ? s + 1 : s;
-            }
-            if (phase == 2) {           // commit pass: recompute with the decided actions
-                if (j < e) {
-                    st.j = j; st.emit = 0; st.kind = mode == MATAS_MODE_SEMI ? 0 : 2;
-                    ++j;
-                    return true;
-                }
-                if (mode == MATAS_MODE_SEMI) {
-                    if (e < nd) { s = e; e = min(e + stride, nd); }
-                    else { s = e; e = min(e + 1, L); }
-                } else {
-                    s = e; e = min(e + 4, L);
-                }
-                phase = 0;
-            }
-        }
-    }
-};
 
 // -------------------------------------------------------------------------------------------------
 // persistent KV-cached decode: one CTA owns 64 envs at a time and walks the schedule.
@@ -707,6 +612,10 @@ int policy_launch_geometry(int L, long rows, int* rpt, int* depth, size_t* bytes
 }
 
 int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots) {
+    if (policy_use_tc()) {
+        if (L > 256) { matas_set_error("n_agent %d > 256 is not supported (per-env action bitset)", L); return MATAS_ERR_LIMIT; }
+        return decode_tc_geometry(B, n_sm, grid, slots);
+    }
     int rpt, depth; size_t bytes;
     int rc = policy_launch_geometry(L, B, &rpt, &depth, &bytes, 1);
     if (rc) return rc;
@@ -792,6 +701,13 @@ int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float
 }
 
 int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st) {
+    if (policy_use_tc()) {
+        if (a.phase_cycles) {
+            matas_set_error("the decode phase profiler instruments the SIMT kernel: set MATAS_TC=0");
+            return MATAS_ERR_UNSUPPORTED;
+        }
+        return launch_decode_tc(b, a, grid, sm_count(), st);
+    }
     GEOMETRY(a.L, a.B, 1);
     (void)tm;
     LAUNCH(decode_kernel<2>, decode_kernel<4>, grid, b, a, depth);

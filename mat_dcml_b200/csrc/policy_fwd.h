@@ -53,6 +53,75 @@ struct DecodeArgs {
     float* logp;         // [B][L]
 };
 
+constexpr float MASK_LOGIT = -1e10f;
+constexpr float HALF_LOG_2PI = 0.91893853320467274178f;
+
+// log-softmax of the two (availability-masked) logits of a discrete agent (transformer_act.py:13-22)
+__device__ __forceinline__ void masked_logz(float l0, float l1, const float* ava2, float& z0, float& z1) {
+    if (ava2) {
+        if (ava2[0] == 0.f) l0 = MASK_LOGIT;
+        if (ava2[1] == 0.f) l1 = MASK_LOGIT;
+    }
+    const float m = fmaxf(l0, l1);
+    const float lse = m + logf(expf(l0 - m) + expf(l1 - m));
+    z0 = l0 - lse;
+    z1 = l1 - lse;
+}
+
+// -------------------------------------------------------------------------------------------------
+// autoregressive decode schedule (transformer_act.py:37-98 and :138-172), shared by host and device
+// -------------------------------------------------------------------------------------------------
+struct DecStep { int j; int kind; int emit; };   // kind 0: true predecessor, 1: speculative zero row, 2: own action
+
+struct DecSched {
+    int L, nd, stride, mode, det;
+    int s, e, j, phase, go, started;
+    __host__ __device__ void init(int L_, int mode_, int det_, int stride_) {
+        L = L_; mode = mode_; det = det_; stride = stride_ < 1 ? 1 : stride_;
+        nd = mode == MATAS_MODE_SEMI ? L - 1 : L;
+        s = 0; e = 1; j = 0; phase = 0; go = 1; started = 0;
+    }
+    __host__ __device__ bool next(DecStep& st) {
+        if (!det) {
+            if (j >= L) return false;
+            st.j = j++; st.kind = 0; st.emit = 1;
+            return true;
+        }
+        for (;;) {
+            if (phase == 0) {           // entering a block
+                if (!(e <= L && go)) return false;
+                if (e == L) go = 0;
+                phase = 1; j = s;
+            }
+            if (phase == 1) {           // speculative pass over [s, e)
+                if (j < e) {
+                    st.j = j; st.emit = 1;
+                    st.kind = mode == MATAS_MODE_SEMI ? (j == s ? 0 : 1) : 1;
+                    ++j;
+                    return true;
+                }
+                const bool more = mode == MATAS_MODE_SEMI ? (go != 0) : (e < L);
+                if (!more) return false;
+                phase = 2; j = mode == MATAS_MODE_SEMI ? s + 1 : s;
+            }
+            if (phase == 2) {           // commit pass: recompute with the decided actions
+                if (j < e) {
+                    st.j = j; st.emit = 0; st.kind = mode == MATAS_MODE_SEMI ? 0 : 2;
+                    ++j;
+                    return true;
+                }
+                if (mode == MATAS_MODE_SEMI) {
+                    if (e < nd) { s = e; e = min(e + stride, nd); }
+                    else { s = e; e = min(e + 1, L); }
+                } else {
+                    s = e; e = min(e + 4, L);
+                }
+                phase = 0;
+            }
+        }
+    }
+};
+
 struct matas_policy;
 struct PolicyView { int n_agent, mode, device, n_sm, weights_set; const float* packed; };
 int matas_policy_view(const matas_policy* p, PolicyView* v);
@@ -66,6 +135,8 @@ int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B,
 int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st, int for_decode);
 // tensor-core (tcgen05) token-parallel kernels, policy_tc.cu
 bool policy_use_tc();
+int decode_tc_geometry(long B, int n_sm, int* grid, long* slots);
+int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st);
 int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st);
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
                           long B, int L, int mode, cudaStream_t st, const TrainBufs* tb = nullptr);

@@ -89,6 +89,45 @@ __device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t da, uint64_t d
                    "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                    \
                  : "r"(addr))
 
+#define TC_LD16(v, addr)                                                                                                       \
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "                                                                      \
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"                                \
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),  \
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])                     \
+                 : "r"(addr))
+
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc_n(uint32_t* slot) {   // one full warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "n"(COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc_n(uint32_t tmem) {  // one full warp
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(COLS) : "memory");
+}
+// one elected thread: (D1, D2) at TMEM columns [d, d+64), [d+64, d+128) (+)= A . W for the fp16 hi/lo operand at
+// shared address a (lo part at + A_PART) and the half blob at shared address w
+__device__ __forceinline__ void mma_set(uint32_t d, uint32_t a, uint32_t w, bool accumulate) {
+    const uint32_t idesc = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) mma_f16(d, make_desc(a + ks * 32), make_desc(w + ks * 32), idesc, (accumulate || ks > 0) ? 1u : 0u);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks)
+        mma_f16(d + 64, make_desc(a + ks * 32), make_desc(w + lay::HB_LO_BYTES + ks * 32), idesc, (accumulate || ks > 0) ? 1u : 0u);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) mma_f16(d + 64, make_desc(a + A_PART + ks * 32), make_desc(w + ks * 32), idesc, 1u);
+}
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// make the operand stores of all threads visible to the tensor core; CTA barrier
+__device__ __forceinline__ void publish() {
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+}
+
 // ---- per-CTA context --------------------------------------------------------------------------------
 struct Ctx {
     uint32_t a_saddr;      // shared address of the activation operand (hi part; lo at + A_PART)

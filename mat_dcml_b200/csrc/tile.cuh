@@ -49,6 +49,12 @@ struct Ring {
         mbar_wait(&bars[s], (head / depth) & 1);
         return slots + (size_t)s * stride;
     }
+    // k-th blob after the current head without consuming it (stages that need two blobs at once)
+    __device__ const float* peek(int k) {
+        const int h = head + k, s = h % depth;
+        mbar_wait(&bars[s], (h / depth) & 1);
+        return slots + (size_t)s * stride;
+    }
     __device__ void release() { ++head; }
 };
 
@@ -393,5 +399,32 @@ __device__ __forceinline__ float row_dot(const float* __restrict__ X, int r, con
         s = fmaf(x.x, ww.x, s); s = fmaf(x.y, ww.y, s); s = fmaf(x.z, ww.z, s); s = fmaf(x.w, ww.w, s);
     }
     return s;
+}
+// -------------------------------------------------------------------------------------------------
+// action-token embedding table: emb[c] = LN(GELU(Wa . vec(c))) (ma_transformer.py:224-225)
+//   code 0: zero row, 1: start token (1,0,0), 2/3: one-hot of action 0/1, 4/5: start + one-hot
+// written to dst[6][64] by the first 96 threads (one half-warp per code)
+// -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void build_emb_table(float* __restrict__ dst, const float* __restrict__ w) {
+    const int tid = threadIdx.x;
+    if (tid < 96) {
+        const int c = tid >> 4, cg = tid & 15;
+        const float f0 = (c == 1 || c >= 4) ? 1.f : 0.f, f1 = (c == 2 || c == 4) ? 1.f : 0.f, f2 = (c == 3 || c == 5) ? 1.f : 0.f;
+        const float* Wt = w + lay::DEC_EMB + lay::DEC_EMB_WT;
+        float v[4];
+        for (int i = 0; i < 4; ++i) {
+            const int col = cg * 4 + i;
+            v[i] = gelu_erf(f0 * Wt[col] + f1 * Wt[64 + col] + f2 * Wt[128 + col]);
+        }
+        const float mean = half_warp_sum(v[0] + v[1] + v[2] + v[3]) * (1.0f / 64.0f);
+        float var = 0.f;
+        for (int i = 0; i < 4; ++i) { v[i] -= mean; var += v[i] * v[i]; }
+        var = half_warp_sum(var) * (1.0f / 64.0f);
+        const float rs = rsqrtf(var + 1e-5f);
+        for (int i = 0; i < 4; ++i) {
+            const int col = cg * 4 + i;
+            dst[c * 64 + col] = v[i] * rs * w[lay::DEC_EMB + lay::DEC_EMB_LNW + col] + w[lay::DEC_EMB + lay::DEC_EMB_LNB + col];
+        }
+    }
 }
 }  // namespace tile
