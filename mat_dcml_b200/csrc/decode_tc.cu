@@ -11,6 +11,8 @@
 // then the logits head and the action pick.  All [128 x 64].[64 x 64] products are fp16 hi + scaled-lo MMAs
 // with fp32 accumulators in tensor memory (tc.cuh); epilogues are thread-per-row: warp w owns rows
 // 32*(w % 4) + lane and the 16 accumulator columns of quarter w / 4.
+#include <stdlib.h>
+
 #include "policy_fwd.h"
 #include "tc.cuh"
 
@@ -24,8 +26,9 @@ constexpr int DEPTH = 4;             // weight ring slots
 constexpr int TMEM_D = 256;          // accumulator columns
 constexpr int OP_BYTES = 2 * tc::A_PART;
 
-__constant__ int c_tc_decode[lay::DEC_FOLD_STEP_BLOBS] = {
-    lay::hb(lay::fold_blob(0, lay::FA0)), lay::hb(lay::fold_blob(0, lay::FA1)), lay::hb(lay::fold_blob(0, lay::FB0)),
+constexpr int STEP_BLOBS = lay::DEC_FOLD_STEP_BLOBS - 2;     // block 0 needs no query maps (see code_counts)
+__constant__ int c_tc_decode[STEP_BLOBS] = {
+    lay::hb(lay::fold_blob(0, lay::FB0)),
     lay::hb(lay::fold_blob(0, lay::FB1)), lay::hb(lay::fold_blob(0, lay::FC0)), lay::hb(lay::fold_blob(0, lay::FC1)),
     lay::hb(lay::dec_blob(0, lay::DM0)), lay::hb(lay::dec_blob(0, lay::DM2)),
     lay::hb(lay::fold_blob(1, lay::FA0)), lay::hb(lay::fold_blob(1, lay::FA1)), lay::hb(lay::fold_blob(1, lay::FB0)),
@@ -43,12 +46,13 @@ struct DSmem {
     float* sHead;          // DEC_H3 group
     float* sRed;           // [2][128][4] LayerNorm partials
     float* sLog;           // [128][4][2] logit partials
+    float* sS;             // [2 heads][6 query codes][6 key codes] block-0 self-attention scores (exp2 domain)
     int* sCode;            // [128]
     uint32_t* bits;        // [128][8] per-env action bitset
     uint64_t* bars;        // [0, DEPTH): ring, [7]: MMA completion
     uint32_t* tmem_slot;
 };
-constexpr size_t DSMEM_FLOATS = 384 + 160 + 1024 + 1024 + 128 + 1024;
+constexpr size_t DSMEM_FLOATS = 384 + 160 + 1024 + 1024 + 96 + 128 + 1024;
 __host__ __device__ constexpr size_t dsmem_bytes() {
     return 1024 + 2 * (size_t)OP_BYTES + (size_t)DEPTH * tc::SLOT_BYTES + 2 * (size_t)tc::TILE_BYTES + DSMEM_FLOATS * 4 + 8 * 8 + 16;
 }
@@ -65,6 +69,7 @@ __device__ inline DSmem dcarve(unsigned char* raw) {
     s.sHead = f; f += 160;
     s.sRed = f; f += 1024;
     s.sLog = f; f += 1024;
+    s.sS = f; f += 96;
     s.sCode = reinterpret_cast<int*>(f); f += 128;
     s.bits = reinterpret_cast<uint32_t*>(f); f += 1024;
     s.bars = reinterpret_cast<uint64_t*>(f);
@@ -162,11 +167,51 @@ __device__ __forceinline__ void layernorm_quad(float (&v)[16], float* __restrict
     for (int i = 0; i < 16; ++i) v[i] *= rs;
 }
 
+// Block-0 self-attention attends over TOKEN EMBEDDINGS, which take one of six values (codes: 0 zero row,
+// 1 start, 2/3 previous action 0/1, 4/5 start + own action of the Discrete variant, tile::build_emb_table), so
+// its softmax over positions 0..j is a softmax over codes weighted by how many visible positions carry each
+// code: no cached rows, no query GEMM.  n[c] = number of positions t <= j whose cached token is c at this
+// point of the decode schedule (DecSched: `s` is the first position of the current stride block).
+__device__ __forceinline__ int popc_range(const uint32_t* __restrict__ bt, int lo, int hi) {   // set bits in [lo, hi)
+    int n = 0;
+    if (hi <= lo) return 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        const int b0 = w * 32;
+        const int a = max(lo - b0, 0), e = min(hi - b0, 32);
+        if (e > a) {
+            uint32_t m = (e == 32 ? 0xffffffffu : ((1u << e) - 1u)) & ~((1u << a) - 1u);
+            n += __popc(bt[w] & m);
+        }
+    }
+    return n;
+}
+__device__ __forceinline__ void code_counts(const uint32_t* __restrict__ bt, int mode, int det, int kind, int j, int s, int (&n)[6]) {
+#pragma unroll
+    for (int c = 0; c < 6; ++c) n[c] = 0;
+    if (mode == MATAS_MODE_SEMI || !det) {
+        // predecessor codes (1 at t = 0, 2 + a[t-1] after); a speculative pass has zero rows behind the block start
+        const int ntrue = (det && kind == 1) ? s + 1 : j + 1;
+        const int ones = popc_range(bt, 0, ntrue - 1);
+        n[1] = 1; n[3] = ones; n[2] = ntrue - 1 - ones; n[0] = j + 1 - ntrue;
+    } else {
+        // Discrete deterministic decode: committed positions carry their OWN action (4/5 at t = 0, 2/3 after)
+        const int nown = kind == 2 ? j + 1 : s;
+        if (nown >= 1) {
+            const int ones = popc_range(bt, 1, nown);
+            n[4 + (int)(bt[0] & 1u)] = 1; n[3] = ones; n[2] = nown - 1 - ones;
+        }
+        if (kind != 2) {                       // speculative rows of the current block: start token at t = 0, else zero rows
+            if (s == 0) { n[1] = 1; n[0] = j; } else n[0] = j + 1 - s;
+        }
+    }
+}
+
 // Absorbed attention (tile::attention_absorbed) for 512 threads with tensor-core operand outputs: 8 lanes
 // per env, lane g holds columns 4g..4g+3 and 32+4g..35+4g of every 64-float row; folded queries from the
 // shared tiles (GQ = false) or from global rows q0 / q1 + r * q_stride (GQ = true); ctx_0 -> U, ctx_1 -> V.
 // Env row r attends to nk cached rows at cache + r * slot_stride (0 rows when r >= n_valid).
-template <bool GQ>
+template <bool GQ, int PF>
 __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                       const float* cache, long slot_stride, int rows, int n_valid, int nk,
                                                       unsigned char* U, unsigned char* V) {
@@ -233,9 +278,17 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
                 const bool ok = t0 + i < nr;
                 xa[i] = ok ? xp[(long)(t0 + i) * 16] : make_float4(0.f, 0.f, 0.f, 0.f);
                 xb[i] = ok ? xp[(long)(t0 + i) * 16 + 8] : make_float4(0.f, 0.f, 0.f, 0.f);
+                // pull the row PF positions ahead into L2 (lane 0: first 128-byte line, lane 4: second); no registers held
+                if (PF > 0 && (g & 3) == 0 && t0 + i + PF < nr) {
+                    const float4* pp = xp + (long)(t0 + i + PF) * 16 + (g ? 8 : 0);
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
+                }
             }
         };
         float4 xa[KB], xb[KB], ya[KB], yb[KB];
+        if (PF > 0 && (g & 3) == 0) {
+            for (int t = 2 * KB; t < PF + 0 && t < nr; ++t) asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + (long)t * 16 + (g ? 8 : 0)));
+        }
         fetch(xa, xb, 0);
         for (int t0 = 0; t0 < nr; t0 += 2 * KB) {
             fetch(ya, yb, t0 + KB);
@@ -251,6 +304,7 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
     }
 }
 
+template <int PFD>
 __global__ void __launch_bounds__(NTD, 1)
 decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -262,7 +316,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
     long my_tiles = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++my_tiles;
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_tc_decode, lay::DEC_FOLD_STEP_BLOBS, (int)(my_tiles * a.n_steps * lay::DEC_FOLD_STEP_BLOBS), DEPTH,
+    ring.init(s.ring, s.bars, b.w, c_tc_decode, STEP_BLOBS, (int)(my_tiles * a.n_steps * STEP_BLOBS), DEPTH,
               lay::BLOB_BYTES, tc::SLOT_F);
     uint64_t* mma_bar = &s.bars[tc::MMA_BAR];
     if (tid == 0) { mbar_init(mma_bar, 1); mbar_fence_init(); }
@@ -274,6 +328,22 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
     __syncthreads();
     tc::fence_after_sync();
     ring.prefetch();
+    // block-0 self-attention score table: S_h[cq][c] = q'_h(e_cq) . e_c with the folded query map FA_h (fp32 blob)
+    for (int idx = tid; idx < 2 * 6 * 64; idx += NTD) {
+        const int h = idx / 384, cq = (idx / 64) % 6, n = idx & 63;
+        const float* W = b.w + lay::fold_blob(0, h ? lay::FA1 : lay::FA0);      // Wt[k][n], bias at B_BIAS
+        float acc = W[lay::B_BIAS + n];
+        for (int k = 0; k < 64; ++k) acc = fmaf(s.sEmb[cq * 64 + k], W[k * 64 + n], acc);
+        s.sQ0[idx] = acc;
+    }
+    __syncthreads();
+    if (tid < 72) {
+        const int h = tid / 36, cq = (tid / 6) % 6, c = tid % 6;
+        float acc = 0.f;
+        for (int n = 0; n < 64; ++n) acc = fmaf(s.sQ0[(h * 6 + cq) * 64 + n], s.sEmb[c * 64 + n], acc);
+        s.sS[tid] = acc;
+    }
+    __syncthreads();
     const uint32_t tmem = *s.tmem_slot;
     const uint32_t uaddr = smem_u32(s.U), vaddr = smem_u32(s.V);
     uint32_t phase = 0;
@@ -317,6 +387,38 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
                 float* cx1 = kv0 + (blk * 2 + 0) * (long)L * 64;     // self-attention inputs (block input x)
                 float* cx2 = kv0 + (blk * 2 + 1) * (long)L * 64;     // cross-attention inputs (x after LN1)
                 float* x_row = cx1 + (long)row * slot_stride + (long)j * 64 + q * 16;
+                if (blk == 0) {
+                    // ---- block 0: softmax over token codes (see code_counts) -> ctx_0 -> U, ctx_1 -> V ------------
+                    const int cq = s.sCode[row];
+                    int cnt[6];
+                    code_counts(s.bits + row * 8, a.mode, a.deterministic, st.kind, j, sched.s, cnt);
+                    float wgt[2][6];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const float* S = s.sS + (h * 6 + cq) * 6;
+                        float m = -INFINITY;
+#pragma unroll
+                        for (int c = 0; c < 6; ++c) if (cnt[c] > 0) m = fmaxf(m, S[c]);
+                        float z = 0.f;
+#pragma unroll
+                        for (int c = 0; c < 6; ++c) { wgt[h][c] = cnt[c] > 0 ? (float)cnt[c] * exp2f(S[c] - m) : 0.f; z += wgt[h][c]; }
+                        const float iz = 1.0f / z;
+#pragma unroll
+                        for (int c = 0; c < 6; ++c) wgt[h][c] *= iz;
+                    }
+                    float c0[16], c1[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) { c0[i] = 0.f; c1[i] = 0.f; }
+#pragma unroll
+                    for (int c = 0; c < 6; ++c) {
+                        float e[16];
+                        load16(e, s.sEmb + c * 64 + q * 16);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) { c0[i] = fmaf(wgt[0][c], e[i], c0[i]); c1[i] = fmaf(wgt[1][c], e[i], c1[i]); }
+                    }
+                    store_operand16(s.U, row, q, c0);
+                    store_operand16(s.V, row, q, c1);
+                } else {
                 // ---- folded self-attention queries ---------------------------------------------------
                 store_operand16(s.U, row, q, v);
                 if (live) store16(x_row, v);
@@ -341,7 +443,8 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
                 }
                 tc::fence_before_sync();
                 __syncthreads();
-                attention_absorbed_op<false>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                attention_absorbed_op<false, PFD>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                }
                 // ---- self-attention output maps + x -> LN1 -> cross cache row -------------------------
                 {
                     const float* w0 = ring.peek(0);
@@ -356,7 +459,8 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
                     mma_wait();
                     result16(tmem, 0, row, q, v);
                     add16(v, w1 + lay::B_BIAS + q * 16);
-                    if (live) add16(v, x_row);
+                    if (blk == 0) add16(v, s.sEmb + s.sCode[row] * 64 + q * 16);
+                    else if (live) add16(v, x_row);
                     layernorm_quad(v, s.sRed, row, q);
                     affine16(v, w1, q);
                     ring.release(); ring.release();
@@ -365,7 +469,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
                 tc::fence_before_sync();
                 __syncthreads();
                 // ---- cross-attention: folded queries q2' precomputed from obs_rep ------------------------
-                attention_absorbed_op<true>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64, cx2,
+                attention_absorbed_op<true, PFD>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64, cx2,
                                             slot_stride, rows, n_valid, j + 1, s.U, s.V);
                 {
                     const float* w0 = ring.peek(0);
@@ -512,8 +616,18 @@ int decode_tc_geometry(long B, int n_sm, int* grid, long* slots) {
 
 int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st) {
     const size_t bytes = dsmem_bytes();
-    CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    decode_tc_kernel<<<grid, NTD, bytes, st>>>(b, a, decode_tc_rows(a.B, n_sm));
+    static int pf = -1;
+    if (pf < 0) { const char* e = getenv("MATAS_DECODE_PF"); pf = e ? atoi(e) : 4; }
+    const int rows = decode_tc_rows(a.B, n_sm);
+#define DECODE_TC_LAUNCH(P)                                                                                           \
+    do {                                                                                                              \
+        CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+        decode_tc_kernel<P><<<grid, NTD, bytes, st>>>(b, a, rows);                                                    \
+    } while (0)
+    if (pf == 0) DECODE_TC_LAUNCH(0);
+    else if (pf <= 4) DECODE_TC_LAUNCH(4);
+    else if (pf <= 8) DECODE_TC_LAUNCH(8);
+    else DECODE_TC_LAUNCH(16);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
