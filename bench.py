@@ -295,11 +295,12 @@ def run_ours(ns):
         traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(ns.workload)
     except (OSError, ValueError):
         pass
-    # HBM bound: the decode re-reads, at every position j of every pass, the j+1 cached 256-byte layer-input
-    # rows of 4 attentions (2 blocks x self/cross), writes 4 new rows, reads the 256-byte obs_rep row and
-    # writes the outputs; arithmetic intensity is ~7 flop/byte, below the fp32 ridge, so HBM is the roof.
+    # HBM bound: at every position j of every pass the decode re-reads the j+1 cached 256-byte layer-input rows
+    # of 3 attentions (block-0 cross, block-1 self and cross; block-0 self-attention runs on token-code counts and
+    # reads nothing), writes 3 new rows, reads 4 folded query rows + the obs_rep row (256 B each) and writes the
+    # outputs; arithmetic intensity is ~7 flop/byte, below the fp32 ridge, so HBM is the roof.
     visits = decode_schedule_positions(L, det, stride)
-    alg_bytes = B * (sum(4 * 256 * (j + 1) + 4 * 256 + 256 + 16 for j in visits))
+    alg_bytes = B * (sum(3 * 256 * (j + 1) + 3 * 256 + 5 * 256 + 16 for j in visits))
     hbm_peak = peaks.get("hbm_gbs", 6500.0)
     hbm_src = ("measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6.5 TB/s (B200_PROFILING.md)")
     achieved_gbs = alg_bytes / (dec_ms * 1e-3) / 1e9
