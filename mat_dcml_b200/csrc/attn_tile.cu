@@ -1,0 +1,174 @@
+// Register-tiled attention over one env's tokens (token-parallel passes, n_agent <= 64), sm_100a.
+//
+// SelfAttention of mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:24-67 for one env at a time: Q, K, V
+// rows [L][64] (two heads of 32) are staged in shared memory, then
+//   S phase : each thread owns a 4 x 4 block of (query, key) pairs of one head: 8 x (8 LDS.128 + 64 FFMA)
+//   softmax : four lanes per (head, query) row; probabilities are written transposed, PT[key][query]
+//   PV phase: each thread owns 4 queries x 4 output dims: per key 2 LDS.128 + 16 FFMA
+// i.e. about 270 instructions per (query, key) pair and lane less than the half-warp-per-row formulation
+// (tile::attention_rows), which spends most of its issue slots on shuffle reductions and per-key softmax updates.
+// The output Y [tok][64] (and, in training mode, the natural-log log-sum-exp [tok][2]) goes to global memory and
+// is picked up by the tensor-core block kernel as its first GEMM operand.
+#include "policy_fwd.h"
+#include "tile.cuh"
+
+namespace {
+
+constexpr int ANT = 128;     // threads per CTA
+constexpr int RS = 68;       // row stride of the Q / K / V tiles (floats): 16-byte aligned rows, 4-bank skew
+
+struct AttnGeom { int Lp, nb, SS, PS; size_t floats; };
+__host__ __device__ inline AttnGeom attn_geom(int L) {
+    AttnGeom g;
+    g.Lp = (L + 3) & ~3;
+    g.nb = g.Lp >> 2;
+    g.SS = (g.nb & 1) ? g.Lp : g.Lp + 4;                    // S row stride: (SS / 4) odd -> 8 rows x 4 keys hit 32 banks
+    g.PS = g.Lp + ((8 - (g.Lp & 15)) & 15);                  // PT row stride: PS = 8 (mod 16), >= Lp
+    const size_t qk = 2 * (size_t)g.Lp * RS, pt = 2 * (size_t)g.Lp * g.PS;
+    g.floats = (qk > pt ? qk : pt) + (size_t)g.Lp * RS + 2 * (size_t)g.Lp * g.SS;
+    return g;
+}
+
+template <bool CAUSAL>
+__global__ void __launch_bounds__(ANT)
+attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const float* __restrict__ V, float* __restrict__ Y,
+                float* __restrict__ lse, long n_env, int L) {
+    extern __shared__ __align__(16) float sm[];
+    const AttnGeom g = attn_geom(L);
+    const int Lp = g.Lp, nb = g.nb, SS = g.SS, PS = g.PS;
+    const size_t qk = 2 * (size_t)Lp * RS, pt = 2 * (size_t)Lp * PS;
+    float* sQ = sm;
+    float* sK = sm + (size_t)Lp * RS;
+    float* sPT = sm;                                          // aliases sQ / sK once the scores are done
+    float* sV = sm + (qk > pt ? qk : pt);
+    float* sS = sV + (size_t)Lp * RS;
+    const int tid = threadIdx.x;
+    const float scale = 0.17677669529663687f * 1.4426950408889634f;     // log2(e)/sqrt(32): exp2-domain scores
+    for (long env = blockIdx.x; env < n_env; env += gridDim.x) {
+        const long tok0 = env * L;
+        // ---- stage Q, K, V (rows >= L zero) ---------------------------------------------------------------
+        for (int idx = tid; idx < Lp * 16; idx += ANT) {
+            const int r = idx >> 4, c = idx & 15;
+            float4 q = make_float4(0.f, 0.f, 0.f, 0.f), k = q, v = q;
+            if (r < L) {
+                q = __ldg(reinterpret_cast<const float4*>(Q + (tok0 + r) * 64) + c);
+                k = __ldg(reinterpret_cast<const float4*>(K + (tok0 + r) * 64) + c);
+                v = __ldg(reinterpret_cast<const float4*>(V + (tok0 + r) * 64) + c);
+            }
+            *reinterpret_cast<float4*>(sQ + r * RS + c * 4) = q;
+            *reinterpret_cast<float4*>(sK + r * RS + c * 4) = k;
+            *reinterpret_cast<float4*>(sV + r * RS + c * 4) = v;
+        }
+        __syncthreads();
+        // ---- S = scale * Q K^T: thread block = queries {qb + nb*i} x keys {kb + nb*j} of head h ----------------
+        for (int task = tid; task < 2 * nb * nb; task += ANT) {
+            const int h = task / (nb * nb), rem = task - h * nb * nb, qb = rem / nb, kb = rem - qb * nb;
+            float acc[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+            const float* qp = sQ + qb * RS + h * 32;
+            const float* kp = sK + kb * RS + h * 32;
+#pragma unroll 2
+            for (int dc = 0; dc < 8; ++dc) {
+                float4 q4[4], k4[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) q4[i] = *reinterpret_cast<const float4*>(qp + i * nb * RS + dc * 4);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) k4[j] = *reinterpret_cast<const float4*>(kp + j * nb * RS + dc * 4);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        acc[i][j] = fmaf(q4[i].x, k4[j].x, acc[i][j]); acc[i][j] = fmaf(q4[i].y, k4[j].y, acc[i][j]);
+                        acc[i][j] = fmaf(q4[i].z, k4[j].z, acc[i][j]); acc[i][j] = fmaf(q4[i].w, k4[j].w, acc[i][j]);
+                    }
+            }
+            float* sp = sS + (size_t)h * Lp * SS;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) sp[(qb + nb * i) * SS + kb + nb * j] = acc[i][j] * scale;
+        }
+        __syncthreads();
+        // ---- softmax rows: 4 lanes per (head, query); normalised probabilities -> PT[h][key][query] ----------------
+        {
+            const int grp = tid >> 2, l4 = tid & 3;
+            const unsigned gmask = 0xfu << (tid & 28);
+            const int n_it = (2 * L + ANT / 4 - 1) / (ANT / 4);
+            for (int it = 0; it < n_it; ++it) {
+                const int rt = it * (ANT / 4) + grp;
+                const bool on = rt < 2 * L;
+                const int h = on ? rt / L : 0, qi = on ? rt - h * L : 0;
+                const int nk = CAUSAL ? qi + 1 : L;
+                const float* sr = sS + ((size_t)h * Lp + qi) * SS;
+                float m = -INFINITY;
+                for (int k = l4; k < nk; k += 4) m = fmaxf(m, sr[k]);
+                m = fmaxf(m, __shfl_xor_sync(gmask, m, 1));
+                m = fmaxf(m, __shfl_xor_sync(gmask, m, 2));
+                float sum = 0.f;
+                for (int k = l4; k < nk; k += 4) sum += exp2f(sr[k] - m);
+                sum += __shfl_xor_sync(gmask, sum, 1);
+                sum += __shfl_xor_sync(gmask, sum, 2);
+                if (on) {
+                    const float inv = 1.0f / sum;
+                    float* pc = sPT + (size_t)h * Lp * PS + qi;
+                    for (int k = l4; k < Lp; k += 4) pc[k * PS] = k < nk ? exp2f(sr[k] - m) * inv : 0.f;
+                    if (lse && l4 == 0) lse[(tok0 + qi) * 2 + h] = m * 0.6931471805599453f + logf(sum);
+                }
+            }
+        }
+        __syncthreads();
+        // ---- Y = P V: thread block = queries 4qb..4qb+3 x dims 4db..4db+3 of head h -------------------------------
+        for (int task = tid; task < 2 * nb * 8; task += ANT) {
+            const int h = task / (nb * 8), rem = task - h * nb * 8, qb = rem >> 3, db = rem & 7;
+            float acc[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+            const float* pp = sPT + (size_t)h * Lp * PS + qb * 4;
+            const float* vp = sV + h * 32 + db * 4;
+            const int nt = CAUSAL ? min(L, qb * 4 + 4) : L;
+#pragma unroll 4
+            for (int t = 0; t < nt; ++t) {
+                const float4 p = *reinterpret_cast<const float4*>(pp + t * PS);
+                const float4 v = *reinterpret_cast<const float4*>(vp + t * RS);
+                const float pv[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    acc[i][0] = fmaf(pv[i], v.x, acc[i][0]); acc[i][1] = fmaf(pv[i], v.y, acc[i][1]);
+                    acc[i][2] = fmaf(pv[i], v.z, acc[i][2]); acc[i][3] = fmaf(pv[i], v.w, acc[i][3]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int qi = qb * 4 + i;
+                if (qi < L)
+                    *reinterpret_cast<float4*>(Y + (tok0 + qi) * 64 + h * 32 + db * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+bool attn_tile_supported(int L) { return L <= 64; }
+
+int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
+                     cudaStream_t st) {
+    const AttnGeom g = attn_geom(L);
+    const size_t bytes = g.floats * sizeof(float);
+    const unsigned grid = (unsigned)(n_env < (1L << 30) ? n_env : (1L << 30));
+    if (causal) {
+        CUDA_TRY(cudaFuncSetAttribute(attn_env_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        attn_env_kernel<true><<<grid, ANT, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(attn_env_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        attn_env_kernel<false><<<grid, ANT, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}

@@ -329,12 +329,12 @@ static int alloc_tokens(matas_policy* p, long n_tok) {
     if (p->d_tok) CUDA_TRY(cudaFree(p->d_tok));
     p->d_tok = nullptr; p->tok_cap = 0;
     const long cap = n_tok + 64;
-    constexpr int NBUF = 21;
+    constexpr int NBUF = 22;
     CUDA_TRY(cudaMalloc(&p->d_tok, (size_t)cap * 64 * sizeof(float) * NBUF));
     float* f = p->d_tok;
     auto take = [&]() { float* r = f; f += cap * 64; return r; };
     PolicyBufs& b = p->bufs;
-    b.X = take(); b.Q = take(); b.rep = take(); b.Q2[0] = take(); b.Q2[1] = take();
+    b.X = take(); b.Q = take(); b.rep = take(); b.Y = take(); b.Q2[0] = take(); b.Q2[1] = take();
     for (int k = 0; k < 2; ++k) for (int h = 0; h < 2; ++h) b.Q2p[k][h] = take();
     for (int k = 0; k < 2; ++k) { b.K[k] = take(); b.V[k] = take(); b.K1[k] = take(); b.V1[k] = take(); b.K2[k] = take(); b.V2[k] = take(); }
     p->tok_cap = cap;

@@ -19,6 +19,7 @@ struct PolicyBufs {
     float* Q2[2];        // attn2.query(obs_rep) per decoder block (teacher-forced passes)
     float* Q2p[2][2];    // decode: folded cross-attention queries q2'_h per block and head
     float* rep;          // encoder output obs_rep
+    float* Y;            // attention output of the block being processed (register-tiled attention kernel, attn_tile.cu)
     float* kv;           // decode cache: [env slots][blk 2][attn 2][L][64] layer inputs of each attention
 };
 
@@ -137,6 +138,9 @@ int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, 
 bool policy_use_tc();
 int decode_tc_geometry(long B, int n_sm, int* grid, long* slots);
 int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st);
+bool attn_tile_supported(int L);
+int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
+                     cudaStream_t st);
 int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st);
 int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
                           long B, int L, int mode, cudaStream_t st, const TrainBufs* tb = nullptr);

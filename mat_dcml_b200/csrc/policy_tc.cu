@@ -5,6 +5,8 @@
 // the other's MMAs.
 //
 // Reference semantics: EncodeBlock / Encoder of mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:70-154.
+#include <stdlib.h>
+
 #include "policy_fwd.h"
 #include "tc.cuh"
 
@@ -69,7 +71,7 @@ __device__ __forceinline__ void save_row32(float* __restrict__ base, long tile0,
 // -------------------------------------------------------------------------------------------------
 template <int BLK>
 __global__ void __launch_bounds__(NT, 2)
-enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int for_decode) {
+enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int for_decode, const float* __restrict__ y_in) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
     const int tid = threadIdx.x;
@@ -88,8 +90,18 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     Stage st = {c, ring};
 
     tc::global_to_tile(s.sT, b.X + tile0 * 64, n_valid);         // residual stream
-    tc::attention_to_operand<false>(s.sA, (tb.on ? tb.e_q[BLK] : b.Q), b.K[BLK], b.V[BLK], tile0, n_tok, L,
-                                    tb.on ? tb.e_y[BLK] : nullptr, tb.on ? tb.e_lse[BLK] : nullptr);
+    if (y_in) {
+        // attention output computed by attn_tile.cu: token-major rows -> operand (one half-warp per row, coalesced)
+        const int hw = tid >> 4, l = tid & 15;
+        for (int r = hw; r < tc::TR; r += NT / 16) {
+            const long g = tile0 + r;
+            const float4 c = g < n_tok ? __ldg(reinterpret_cast<const float4*>(y_in + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+            tc::store_operand4(s.sA, r, l, c);
+        }
+    } else {
+        tc::attention_to_operand<false>(s.sA, (tb.on ? tb.e_q[BLK] : b.Q), b.K[BLK], b.V[BLK], tile0, n_tok, L,
+                                        tb.on ? tb.e_y[BLK] : nullptr, tb.on ? tb.e_lse[BLK] : nullptr);
+    }
     float v[32], res[32];
     // ---- proj + residual + LN1 ------------------------------------------------------------------
     {
@@ -201,8 +213,20 @@ int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
-    enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0);
-    enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode);
+    static int tiled = -1;           // MATAS_ATTN_TILE=0 keeps the attention fused into the block kernel (A/B measurements)
+    if (tiled < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tiled = e ? atoi(e) : 1; }
+    const bool use_tile = tiled && attn_tile_supported(L);
+    for (int blk = 0; blk < 2; ++blk) {
+        const float* y_in = nullptr;
+        if (use_tile) {
+            float* y = tb.on ? tb.e_y[blk] : b.Y;
+            int rc = launch_attn_tile(tb.on ? tb.e_q[blk] : b.Q, b.K[blk], b.V[blk], y, tb.on ? tb.e_lse[blk] : nullptr, n_tok / L, L, 0, st);
+            if (rc) return rc;
+            y_in = y;
+        }
+        if (blk == 0) enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0, y_in);
+        else enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode, y_in);
+    }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
