@@ -691,6 +691,7 @@ int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
     const int n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
+    if (policy_use_tc()) return launch_teacher_forced_tc(b, tb, actions, ava, logp, entropy, n_tok, L, n_disc, st);
     LAUNCH(dec_embed_qkv<2>, dec_embed_qkv<4>, grid, b, tb, actions, n_tok, L, depth);
     for (int blk = 0; blk < 2; ++blk) {
         LAUNCH(dec_attn1<2>, dec_attn1<4>, grid, b, tb, blk, n_tok, L, depth);

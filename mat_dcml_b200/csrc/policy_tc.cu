@@ -27,6 +27,17 @@ __constant__ int c_tc_enc_blk1_dec[8] = {lay::hb(lay::enc_blob(1, lay::EP)), lay
                                          lay::hb(lay::fold_blob(0, lay::FQ0)), lay::hb(lay::fold_blob(0, lay::FQ1)),
                                          lay::hb(lay::fold_blob(1, lay::FQ0)), lay::hb(lay::fold_blob(1, lay::FQ1))};
 
+__constant__ int c_tc_dec_embed[3] = {lay::hb(lay::dec_blob(0, lay::DQ1)), lay::hb(lay::dec_blob(0, lay::DK1)),
+                                      lay::hb(lay::dec_blob(0, lay::DV1))};
+__constant__ int c_tc_dec_attn1[2][3] = {
+    {lay::hb(lay::dec_blob(0, lay::DP1)), lay::hb(lay::dec_blob(0, lay::DK2)), lay::hb(lay::dec_blob(0, lay::DV2))},
+    {lay::hb(lay::dec_blob(1, lay::DP1)), lay::hb(lay::dec_blob(1, lay::DK2)), lay::hb(lay::dec_blob(1, lay::DV2))}};
+__constant__ int c_tc_dec_attn2[2][6] = {
+    {lay::hb(lay::dec_blob(0, lay::DP2)), lay::hb(lay::dec_blob(0, lay::DM0)), lay::hb(lay::dec_blob(0, lay::DM2)),
+     lay::hb(lay::dec_blob(1, lay::DQ1)), lay::hb(lay::dec_blob(1, lay::DK1)), lay::hb(lay::dec_blob(1, lay::DV1))},
+    {lay::hb(lay::dec_blob(1, lay::DP2)), lay::hb(lay::dec_blob(1, lay::DM0)), lay::hb(lay::dec_blob(1, lay::DM2)),
+     lay::hb(lay::DEC_H0), 0, 0}};
+
 __device__ __forceinline__ void add_bias32(float (&v)[32], const float* __restrict__ blob, int half) {
     const float4* bias = reinterpret_cast<const float4*>(blob + lay::B_BIAS + half * 32);
 #pragma unroll
@@ -206,16 +217,246 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     tc::ctx_fini(c);
 }
 
+// attention output rows computed by attn_tile.cu (token-major, global) -> operand, one half-warp per row
+__device__ __forceinline__ void rows_to_operand(unsigned char* sA, const float* __restrict__ y, long tile0, long n_tok) {
+    const int hw = threadIdx.x >> 4, l = threadIdx.x & 15;
+    for (int r = hw; r < tc::TR; r += NT / 16) {
+        const long g = tile0 + r;
+        const float4 c = g < n_tok ? __ldg(reinterpret_cast<const float4*>(y + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+        tc::store_operand4(sA, r, l, c);
+    }
+}
+
+// Tail shared by the kernels that end with three projections of the tile in the operand (x in sT):
+// x -> x_dst0 / x_dst1 (token-major), then out[o] = x . W_o + b_o for the next three ring blobs.
+__device__ __forceinline__ void qkv_tail(tc::Ctx& c, Ring& ring, const tc::Smem& s, float* sTrow, long tile0, int n_valid,
+                                         float* x_dst0, float* x_dst1, float* out0, float* out1, float* out2) {
+    float v[32];
+    float* outs[3] = {out0, out1, out2};
+#pragma unroll
+    for (int o = 0; o < 3; ++o) {
+        const float* blob = ring.acquire();
+        tc::gemm_issue(c, blob);                              // barrier: sT holds the complete previous output
+        ring.prefetch();
+        if (o == 0) {
+            if (x_dst0) tc::tile_to_global(x_dst0 + tile0 * 64, s.sT, n_valid);
+            if (x_dst1) tc::tile_to_global(x_dst1 + tile0 * 64, s.sT, n_valid);
+        }
+        tc::gemm_result(c, v);
+        add_bias32(v, blob, c.half);
+        ring.release();
+        if (o == 0) __syncthreads();                          // every thread is done reading x from sT
+        tc::row_store32(sTrow, v);
+        __syncthreads();
+        tc::tile_to_global(outs[o] + tile0 * 64, s.sT, n_valid);
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// teacher-forced decoder, stage 1: shifted-action embedding -> X ; QKV1 of block 0
+// (transformer_act.py:103-111,176-181)
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT, 2)
+dec_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, long n_tok, int L) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
+    const long tile0 = (long)blockIdx.x * tc::TR;
+    const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_tc_dec_embed, 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    build_emb_table(s.sSmall + 512, b.w);
+    tc::Ctx c;
+    tc::ctx_init(c, s);
+    ring.prefetch();
+    const int row = c.row, half = c.half;
+    float* sTrow = s.sT + row * XS + half * 32;
+    {
+        const long g = tile0 + row;
+        int code = 0;
+        if (g < n_tok) code = (g % L) == 0 ? 1 : (actions[g - 1] != 0.f ? 3 : 2);
+        float v[32];
+        tc::row_load32(s.sSmall + 512 + code * 64 + half * 32, v);
+        tc::row_store32(sTrow, v);
+        tc::store_operand32(s.sA, row, half, v);
+    }
+    qkv_tail(c, ring, s, sTrow, tile0, n_valid, b.X, tb.on ? tb.d_x0 : nullptr, tb.on ? tb.d_q1[0] : b.Q, b.K1[0], b.V1[0]);
+    tc::ctx_fini(c);
+}
+
+// decoder block, first half: causal self-attention + proj + LN1, then K2 / V2 of the result
+// (ma_transformer.py:113 and the key/value side of :114)
+__global__ void __launch_bounds__(NT, 2)
+dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float* __restrict__ y_in) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
+    const long tile0 = (long)blockIdx.x * tc::TR;
+    const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_tc_dec_attn1[blk], 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    tc::Ctx c;
+    tc::ctx_init(c, s);
+    ring.prefetch();
+    const int row = c.row, half = c.half;
+    float* sRed = s.sSmall;
+    float* sTrow = s.sT + row * XS + half * 32;
+    tc::global_to_tile(s.sT, b.X + tile0 * 64, n_valid);
+    if (y_in) rows_to_operand(s.sA, y_in, tile0, n_tok);
+    else tc::attention_to_operand<true>(s.sA, (tb.on ? tb.d_q1[blk] : b.Q), b.K1[blk], b.V1[blk], tile0, n_tok, L,
+                                        tb.on ? tb.d_y1[blk] : nullptr, tb.on ? tb.d_lse1[blk] : nullptr);
+    float v[32], res[32];
+    Stage st = {c, ring};
+    {
+        const float* blob = st.run(v);
+        tc::row_load32(sTrow, res);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += res[i];
+        const float rs = tc::layernorm_pair(v, sRed, row, half);
+        if (tb.on) {
+            save_row32(tb.d_xh1[blk], tile0, row, half, n_valid, v);
+            if (half == 0 && row < n_valid) tb.d_rs1[blk][tile0 + row] = rs;
+        }
+        affine32(v, blob, half);
+        ring.release();
+        tc::store_operand32(s.sA, row, half, v);                  // x1: input of the cross-attention keys / values
+    }
+    float* outs[2] = {b.K2[blk], b.V2[blk]};
+#pragma unroll
+    for (int o = 0; o < 2; ++o) {
+        const float* blob = ring.acquire();
+        tc::gemm_issue(c, blob);                                  // barrier: residual reads / previous store are done
+        ring.prefetch();
+        tc::gemm_result(c, v);
+        add_bias32(v, blob, half);
+        ring.release();
+        tc::row_store32(sTrow, v);
+        __syncthreads();
+        tc::tile_to_global(outs[o] + tile0 * 64, s.sT, n_valid);
+    }
+    tc::ctx_fini(c);
+}
+
+// decoder block, second half: cross-attention (query = obs_rep) + proj + LN2(rep + .) + MLP + LN3;
+// block 0 then emits QKV1 of block 1, block 1 the logits head and the per-token log-prob / entropy.
+__global__ void __launch_bounds__(NT, 2)
+dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ actions, const float* __restrict__ ava,
+             float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, const float* __restrict__ y_in) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
+    const int tid = threadIdx.x;
+    const long tile0 = (long)blockIdx.x * tc::TR;
+    const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_tc_dec_attn2[blk], blk == 0 ? 6 : 4, blk == 0 ? 6 : 4, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    tc::Ctx c;
+    tc::ctx_init(c, s);
+    ring.prefetch();
+    if (blk == 1) for (int i = tid; i < lay::DEC_H3_SIZE; i += NT) s.sSmall[512 + i] = b.w[lay::DEC_H3 + i];
+    const int row = c.row, half = c.half;
+    float* sRed = s.sSmall;
+    float* sTrow = s.sT + row * XS + half * 32;
+    tc::global_to_tile(s.sT, b.rep + tile0 * 64, n_valid);
+    if (y_in) rows_to_operand(s.sA, y_in, tile0, n_tok);
+    else tc::attention_to_operand<true>(s.sA, b.Q2[blk], b.K2[blk], b.V2[blk], tile0, n_tok, L, tb.on ? tb.d_y2[blk] : nullptr,
+                                        tb.on ? tb.d_lse2[blk] : nullptr);
+    float v[32], res[32];
+    Stage st = {c, ring};
+    {   // proj + obs_rep + LN2
+        const float* blob = st.run(v);
+        tc::row_load32(sTrow, res);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += res[i];
+        const float rs = tc::layernorm_pair(v, sRed, row, half);
+        if (tb.on) {
+            save_row32(tb.d_xh2[blk], tile0, row, half, n_valid, v);
+            if (half == 0 && row < n_valid) tb.d_rs2[blk][tile0 + row] = rs;
+        }
+        affine32(v, blob, half);
+        ring.release();
+        tc::row_store32(sTrow, v);
+        tc::store_operand32(s.sA, row, half, v);
+    }
+    {   // mlp.0 + GELU
+        st.run(v);
+        ring.release();
+        if (tb.on) save_row32(tb.d_m0[blk], tile0, row, half, n_valid, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        tc::store_operand32(s.sA, row, half, v);
+    }
+    {   // mlp.2 + residual + LN3
+        const float* blob = st.run(v);
+        tc::row_load32(sTrow, res);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += res[i];
+        const float rs = tc::layernorm_pair(v, sRed, row, half);
+        if (tb.on) {
+            save_row32(tb.d_xh3[blk], tile0, row, half, n_valid, v);
+            if (half == 0 && row < n_valid) tb.d_rs3[blk][tile0 + row] = rs;
+        }
+        affine32(v, blob, half);
+        ring.release();
+        tc::row_store32(sTrow, v);
+        tc::store_operand32(s.sA, row, half, v);
+    }
+    if (blk == 0) {
+        qkv_tail(c, ring, s, sTrow, tile0, n_valid, b.X, nullptr, tb.on ? tb.d_q1[1] : b.Q, b.K1[1], b.V1[1]);
+    } else {
+        // ---- logits head + per-token log-prob / entropy (transformer_act.py:112-128) -----------------------
+        const float* blob = st.run(v);
+        if (tb.on) save_row32(tb.d_hh, tile0, row, half, n_valid, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        const float rs = tc::layernorm_pair(v, sRed, row, half);
+        if (tb.on) {
+            save_row32(tb.d_xhh, tile0, row, half, n_valid, v);
+            if (half == 0 && row < n_valid) tb.d_rsh[tile0 + row] = rs;
+        }
+        affine32(v, blob, half);
+        ring.release();
+        const float* w3 = s.sSmall + 512;
+        float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            d0 = fmaf(v[i], w3[half * 32 + i], d0);
+            d1 = fmaf(v[i], w3[64 + half * 32 + i], d1);
+        }
+        float* sLog = s.sT;                                        // [128][2 halves][2 logits]; the x3 tile is dead in block 1
+        sLog[(row * 2 + half) * 2] = d0;
+        sLog[(row * 2 + half) * 2 + 1] = d1;
+        __syncthreads();
+        if (half == 0 && row < n_valid) {
+            const long g = tile0 + row;
+            const int pos = (int)(g % L);
+            const float l0 = sLog[row * 4] + sLog[row * 4 + 2] + w3[lay::DEC_H3_B];
+            const float l1 = sLog[row * 4 + 1] + sLog[row * 4 + 3] + w3[lay::DEC_H3_B + 1];
+            const float a = actions[g];
+            if (pos < n_disc) {
+                float z0, z1;
+                masked_logz(l0, l1, ava ? ava + g * 2 : nullptr, z0, z1);
+                logp[g] = a != 0.f ? z1 : z0;
+                const float c0 = fmaxf(z0, -3.4028234663852886e38f), c1 = fmaxf(z1, -3.4028234663852886e38f);
+                entropy[g] = -(expf(c0) * c0 + expf(c1) * c1);
+            } else {
+                const float sd = 0.5f / (1.0f + expf(-w3[lay::DEC_H3_LOGSTD + 1]));
+                const float d = a - l1;
+                logp[g] = -(d * d) / (2.0f * sd * sd) - logf(sd) - HALF_LOG_2PI;
+                entropy[g] = 0.5f + HALF_LOG_2PI + logf(sd);
+            }
+        }
+    }
+    tc::ctx_fini(c);
+}
+
 }  // namespace
+
+static bool use_attn_tile(int L);
 
 int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st) {
     const size_t bytes = tc::smem_bytes(TC_DEPTH);
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
-    static int tiled = -1;           // MATAS_ATTN_TILE=0 keeps the attention fused into the block kernel (A/B measurements)
-    if (tiled < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tiled = e ? atoi(e) : 1; }
-    const bool use_tile = tiled && attn_tile_supported(L);
+    const bool use_tile = use_attn_tile(L);
     for (int blk = 0; blk < 2; ++blk) {
         const float* y_in = nullptr;
         if (use_tile) {
@@ -226,6 +467,43 @@ int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values
         }
         if (blk == 0) enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0, y_in);
         else enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode, y_in);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
+static bool use_attn_tile(int L) {
+    static int tiled = -1;           // MATAS_ATTN_TILE=0 keeps the attention fused into the block kernels (A/B measurements)
+    if (tiled < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tiled = e ? atoi(e) : 1; }
+    return tiled && attn_tile_supported(L);
+}
+
+int launch_teacher_forced_tc(const PolicyBufs& b, const TrainBufs& tb, const float* actions, const float* ava, float* logp,
+                             float* entropy, long n_tok, int L, int n_disc, cudaStream_t st) {
+    const size_t bytes = tc::smem_bytes(TC_DEPTH);
+    CUDA_TRY(cudaFuncSetAttribute(dec_embed_qkv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    CUDA_TRY(cudaFuncSetAttribute(dec_attn1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    CUDA_TRY(cudaFuncSetAttribute(dec_attn2_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
+    const bool tile = use_attn_tile(L);
+    const long n_env = n_tok / L;
+    int rc;
+    dec_embed_qkv_tc<<<grid, NT, bytes, st>>>(b, tb, actions, n_tok, L);
+    for (int blk = 0; blk < 2; ++blk) {
+        const float* y_in = nullptr;
+        if (tile) {
+            float* y = tb.on ? tb.d_y1[blk] : b.Y;
+            if ((rc = launch_attn_tile(tb.on ? tb.d_q1[blk] : b.Q, b.K1[blk], b.V1[blk], y, tb.on ? tb.d_lse1[blk] : nullptr, n_env, L, 1, st)))
+                return rc;
+            y_in = y;
+        }
+        dec_attn1_tc<<<grid, NT, bytes, st>>>(b, tb, blk, n_tok, L, y_in);
+        if (tile) {
+            float* y = tb.on ? tb.d_y2[blk] : b.Y;
+            if ((rc = launch_attn_tile(b.Q2[blk], b.K2[blk], b.V2[blk], y, tb.on ? tb.d_lse2[blk] : nullptr, n_env, L, 1, st))) return rc;
+            y_in = y;
+        }
+        dec_attn2_tc<<<grid, NT, bytes, st>>>(b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, y_in);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
