@@ -260,7 +260,7 @@ def run_ours(ns):
     value = world * B * ns.steps / (ms * 1e-3)
     # end-to-end arm
     e2e_K = max(1, min(ns.steps, ns.e2e_steps))
-    e2e_ms = timed(e2e_step, e2e_start, e2e_K, 1)
+    e2e_ms = timed(e2e_step, e2e_start, e2e_K, 3)
     e2e_value = world * B * e2e_K / (e2e_ms * 1e-3)
     # host -> device per step: policy inputs (obs, ava), env actions, and the buffer insert of host arrays
     # (share_obs row, obs, ava, actions, log-probs, values, reward, mask); device -> host: values, actions,

@@ -2,6 +2,10 @@
 (mat_src/mat/utils/shared_buffer.py:22-314): same array names and (T+1 | T, N, L, dim) shapes,
 ``insert`` / ``compute_returns`` / ``after_update`` / ``feed_forward_generator_transformer``.
 
+Host arrays handed to ``insert`` (the reference's numpy contract) are uploaded on a side stream when they
+live in pinned memory, so the copies overlap the next step's kernels; every read of a buffer array first makes
+the current stream wait for pending uploads (the arrays below are properties for that reason).
+
 Differences, all layout-only: arrays are fp32 torch tensors on the GPU instead of numpy;
 ``share_obs`` keeps ONE (W+2) row per (t, env) and is exposed as a stride-0 expand
 (the model ignores it, ma_transformer.py:144-149); the dead ``rnn_states*`` arrays are
@@ -17,7 +21,25 @@ def _shape(space):
     return space.shape if space.__class__.__name__ == "Box" else space
 
 
+def _guarded(name):
+    key = "_t_" + name
+    def get(self):
+        self._join()
+        return self.__dict__[key]
+    def put(self, value):
+        self.__dict__[key] = value
+    return property(get, put)
+
+
 class SharedReplayBuffer:
+    # arrays that insert() may fill from the side stream
+    _share_obs = _guarded("_share_obs")
+    obs = _guarded("obs")
+    actions = _guarded("actions")
+    action_log_probs = _guarded("action_log_probs")
+    value_preds = _guarded("value_preds")
+    available_actions = _guarded("available_actions")
+
     def __init__(self, args, num_agents, obs_space, cent_obs_space, act_space, env_name, device="cuda"):
         self.episode_length, self.n_rollout_threads = args.episode_length, args.n_rollout_threads
         self.gamma, self.gae_lambda = args.gamma, args.gae_lambda
@@ -28,6 +50,10 @@ class SharedReplayBuffer:
             raise _cabi.MatasError("SharedReplayBuffer needs a CUDA device (there is no CPU fallback)")
         if not self._use_gae:
             raise NotImplementedError("only the GAE branch of compute_returns is built (config.py:260 default)")
+        self._copy_stream = torch.cuda.Stream(device=self.device)
+        self._dirty = False
+        self._inflight = []            # (event, source tensors) of uploads that may still be reading pinned memory
+        self._held = []
         T, N, L = self.episode_length, self.n_rollout_threads, num_agents
         obs_dim = _shape(obs_space)[0] if not isinstance(_shape(obs_space)[-1], list) else _shape(obs_space)[0][0]
         sob_dim = _shape(cent_obs_space)[0] if not isinstance(_shape(cent_obs_space)[-1], list) else _shape(cent_obs_space)[0][0]
@@ -54,21 +80,41 @@ class SharedReplayBuffer:
         T1, N, D = self._share_obs.shape
         return self._share_obs.unsqueeze(2).expand(T1, N, self.num_agents, D)
 
-    def _put(self, dst, src):
+    def _join(self):
+        """Order the current stream after the uploads issued so far."""
+        if self.__dict__.get("_dirty"):
+            torch.cuda.current_stream(self.device).wait_stream(self._copy_stream)
+            self._dirty = False
+
+    def _put(self, name, index, src):
+        """array[index] = src.  Pinned fp32 host sources are uploaded on the side stream."""
+        dst = self.__dict__["_t_" + name][index]
         src = torch.as_tensor(src) if not torch.is_tensor(src) else src
-        dst.copy_(src.to(device=self.device, dtype=torch.float32).reshape(dst.shape), non_blocking=True)
+        if (src.device.type == "cpu" and src.dtype == torch.float32 and src.is_contiguous() and src.numel() == dst.numel()
+                and src.is_pinned()):
+            cs = self._copy_stream
+            cs.wait_stream(torch.cuda.current_stream(self.device))      # kernels queued earlier may still read dst
+            with torch.cuda.stream(cs):
+                dst.copy_(src.reshape(dst.shape), non_blocking=True)
+            self._held.append(src)
+            self._dirty = True
+        else:
+            self._join()
+            dst.copy_(src.to(device=self.device, dtype=torch.float32).reshape(dst.shape), non_blocking=True)
 
     def insert(self, share_obs, obs, rnn_states_actor, rnn_states_critic, actions, action_log_probs, value_preds,
                rewards, masks, bad_masks=None, active_masks=None, available_actions=None):
         """shared_buffer.py:118-151.  ``share_obs`` may be (N, L, D) (the reference's replicated form;
         row 0 is kept) or (N, D); ``rewards`` / ``masks`` may be per env (N,) or (N, L, 1)."""
         s = self.step
+        self._inflight = [(e, h) for e, h in self._inflight if not e.query()]      # drop finished uploads
+        self._held = []
         so = torch.as_tensor(share_obs) if not torch.is_tensor(share_obs) else share_obs
-        self._put(self._share_obs[s + 1], so[:, 0, :] if so.dim() == 3 else so)
-        self._put(self.obs[s + 1], obs)
-        self._put(self.actions[s], actions)
-        self._put(self.action_log_probs[s], action_log_probs)
-        self._put(self.value_preds[s], value_preds)
+        self._put("_share_obs", s + 1, so[:, 0, :] if so.dim() == 3 else so)
+        self._put("obs", s + 1, obs)
+        self._put("actions", s, actions)
+        self._put("action_log_probs", s, action_log_probs)
+        self._put("value_preds", s, value_preds)
         self._bcast(self.rewards[s], rewards)
         self._bcast(self.masks[s + 1], masks)
         if bad_masks is not None:
@@ -76,7 +122,12 @@ class SharedReplayBuffer:
         if active_masks is not None:
             self._bcast(self.active_masks[s + 1], active_masks)
         if available_actions is not None:
-            self._put(self.available_actions[s + 1], available_actions)
+            self._put("available_actions", s + 1, available_actions)
+        if self._held:
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+            self._inflight.append((ev, self._held))
+        self._held = []
         self.step = (self.step + 1) % self.episode_length
 
     def _bcast(self, dst, src):
@@ -93,7 +144,13 @@ class SharedReplayBuffer:
 
     def compute_returns(self, next_value, value_normalizer=None):
         """shared_buffer.py:207-238 (GAE branch) on the device, ValueNorm denormalisation fused."""
-        self._put(self.value_preds[-1], next_value)
+        self._held = []
+        self._put("value_preds", -1, next_value)
+        if self._held:
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+            self._inflight.append((ev, self._held))
+            self._held = []
         use_vn = (self._use_popart or self._use_valuenorm) and value_normalizer is not None
         T, N, L = self.episode_length, self.n_rollout_threads, self.num_agents
         with torch.cuda.device(self.device):
