@@ -667,8 +667,11 @@ int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B,
     GEOMETRY(L, B * L, 0);
     const long n_tok = B * L;
     const unsigned grid = (unsigned)((n_tok + tm - 1) / tm);
+    if (policy_use_tc()) {
+        int rc_ = launch_enc_embed_tc(b, tb, obs, n_tok, obs_dim, st);
+        return rc_ ? rc_ : launch_enc_blocks_tc(b, tb, values, n_tok, L, for_decode, st);
+    }
     LAUNCH(enc_embed_qkv<2>, enc_embed_qkv<4>, grid, b, tb, obs, n_tok, obs_dim, depth);
-    if (policy_use_tc()) return launch_enc_blocks_tc(b, tb, values, n_tok, L, for_decode, st);
     LAUNCH((enc_block<0, 2>), (enc_block<0, 4>), grid, b, tb, values, n_tok, L, depth, 0);
     LAUNCH((enc_block<1, 2>), (enc_block<1, 4>), grid, b, tb, values, n_tok, L, depth, for_decode);
     CUDA_TRY(cudaGetLastError());

@@ -27,6 +27,8 @@ __constant__ int c_tc_enc_blk1_dec[8] = {lay::hb(lay::enc_blob(1, lay::EP)), lay
                                          lay::hb(lay::fold_blob(0, lay::FQ0)), lay::hb(lay::fold_blob(0, lay::FQ1)),
                                          lay::hb(lay::fold_blob(1, lay::FQ0)), lay::hb(lay::fold_blob(1, lay::FQ1))};
 
+__constant__ int c_tc_enc_embed[3] = {lay::hb(lay::enc_blob(0, lay::EQ)), lay::hb(lay::enc_blob(0, lay::EK)),
+                                      lay::hb(lay::enc_blob(0, lay::EV))};
 __constant__ int c_tc_dec_embed[3] = {lay::hb(lay::dec_blob(0, lay::DQ1)), lay::hb(lay::dec_blob(0, lay::DK1)),
                                       lay::hb(lay::dec_blob(0, lay::DV1))};
 __constant__ int c_tc_dec_attn1[2][3] = {
@@ -253,6 +255,73 @@ __device__ __forceinline__ void qkv_tail(tc::Ctx& c, Ring& ring, const tc::Smem&
 }
 
 // -------------------------------------------------------------------------------------------------
+// encoder stage 1: obs LayerNorm -> Linear(obs_dim->64) -> GELU -> LayerNorm -> X ; QKV of block 0
+// (ma_transformer.py:133-136,148-151 and :50-52).  The 7-wide input layer runs on the CUDA cores
+// (one thread per row and column half), the three projections on the tensor cores.
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT, 2)
+enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_tok, int obs_dim) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
+    const int tid = threadIdx.x;
+    const long tile0 = (long)blockIdx.x * tc::TR;
+    const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
+    Ring ring;
+    ring.init(s.ring, s.bars, b.w, c_tc_enc_embed, 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    float* sPar = s.sT;                                   // the small parameter group lives in sT until x0 is formed
+    for (int i = tid; i < lay::ENC_EMB_SIZE; i += NT) sPar[i] = b.w[lay::ENC_EMB + i];
+    tc::Ctx c;
+    tc::ctx_init(c, s);
+    ring.prefetch();
+    const int row = c.row, half = c.half;
+    float* sTrow = s.sT + row * XS + half * 32;
+    float v[32];
+    {
+        const long g = tile0 + row;
+        float o[8], mean = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { o[k] = (k < obs_dim && row < n_valid) ? obs[g * obs_dim + k] : 0.f; mean += o[k]; }
+        mean /= (float)obs_dim;
+        float var = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) if (k < obs_dim) var += (o[k] - mean) * (o[k] - mean);
+        const float rs7 = rsqrtf(var / (float)obs_dim + 1e-5f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = k < obs_dim ? (o[k] - mean) * rs7 * sPar[lay::ENC_EMB_LNW + k] + sPar[lay::ENC_EMB_LNB + k] : 0.f;
+        tc::row_load32(sPar + lay::ENC_EMB_B + half * 32, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (k < obs_dim) {
+                float w[32];
+                tc::row_load32(sPar + lay::ENC_EMB_WT + k * 64 + half * 32, w);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = fmaf(o[k], w[i], v[i]);
+            }
+        }
+        if (tb.on) save_row32(tb.e_h0, tile0, row, half, n_valid, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        const float rs = tc::layernorm_pair(v, s.sSmall, row, half);
+        if (tb.on) {
+            save_row32(tb.e_xh0, tile0, row, half, n_valid, v);
+            if (half == 0 && row < n_valid) tb.e_rs0[tile0 + row] = rs;
+        }
+        float lw[32];
+        tc::row_load32(sPar + lay::ENC_EMB_LN2W + half * 32, lw);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] *= lw[i];
+        tc::row_load32(sPar + lay::ENC_EMB_LN2B + half * 32, lw);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += lw[i];
+    }
+    __syncthreads();                                       // every thread is done with the parameters in sT
+    tc::row_store32(sTrow, v);
+    tc::store_operand32(s.sA, row, half, v);
+    qkv_tail(c, ring, s, sTrow, tile0, n_valid, b.X, tb.on ? tb.e_x0 : nullptr, tb.on ? tb.e_q[0] : b.Q, b.K[0], b.V[0]);
+    tc::ctx_fini(c);
+}
+
+// -------------------------------------------------------------------------------------------------
 // teacher-forced decoder, stage 1: shifted-action embedding -> X ; QKV1 of block 0
 // (transformer_act.py:103-111,176-181)
 // -------------------------------------------------------------------------------------------------
@@ -450,6 +519,14 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
 }  // namespace
 
 static bool use_attn_tile(int L);
+
+int launch_enc_embed_tc(const PolicyBufs& b, const TrainBufs& tb, const float* obs, long n_tok, int obs_dim, cudaStream_t st) {
+    const size_t bytes = tc::smem_bytes(TC_DEPTH);
+    CUDA_TRY(cudaFuncSetAttribute(enc_embed_qkv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    enc_embed_qkv_tc<<<(unsigned)((n_tok + tc::TR - 1) / tc::TR), NT, bytes, st>>>(b, tb, obs, n_tok, obs_dim);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
 
 int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st) {
     const size_t bytes = tc::smem_bytes(TC_DEPTH);
