@@ -207,6 +207,12 @@ __device__ __forceinline__ void code_counts(const uint32_t* __restrict__ bt, int
     }
 }
 
+__device__ __forceinline__ float ex2(float x) {          // 2^x, x <= 0 here; denormal results flush to zero
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // Absorbed attention (tile::attention_absorbed) for 512 threads with tensor-core operand outputs: 8 lanes
 // per env, lane g holds columns 4g..4g+3 and 32+4g..35+4g of every 64-float row; folded queries from the
 // shared tiles (GQ = false) or from global rows q0 / q1 + r * q_stride (GQ = true); ctx_0 -> U, ctx_1 -> V.
@@ -257,13 +263,13 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
             float n0 = m0, n1 = m1;
 #pragma unroll
             for (int i = 0; i < KB; ++i) { n0 = fmaxf(n0, s0[i]); n1 = fmaxf(n1, s1[i]); }
-            const float a0 = exp2f(m0 - n0), a1 = exp2f(m1 - n1);
+            const float a0 = ex2(m0 - n0), a1 = ex2(m1 - n1);      // 2^(-inf) = 0 on the first batch
             l0 *= a0; l1 *= a1;
             ca0.x *= a0; ca0.y *= a0; ca0.z *= a0; ca0.w *= a0; cb0.x *= a0; cb0.y *= a0; cb0.z *= a0; cb0.w *= a0;
             ca1.x *= a1; ca1.y *= a1; ca1.z *= a1; ca1.w *= a1; cb1.x *= a1; cb1.y *= a1; cb1.z *= a1; cb1.w *= a1;
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
-                const float p0 = exp2f(s0[i] - n0), p1 = exp2f(s1[i] - n1);
+                const float p0 = ex2(s0[i] - n0), p1 = ex2(s1[i] - n1);
                 l0 += p0; l1 += p1;
                 ca0.x = fmaf(p0, xa[i].x, ca0.x); ca0.y = fmaf(p0, xa[i].y, ca0.y); ca0.z = fmaf(p0, xa[i].z, ca0.z); ca0.w = fmaf(p0, xa[i].w, ca0.w);
                 cb0.x = fmaf(p0, xb[i].x, cb0.x); cb0.y = fmaf(p0, xb[i].y, cb0.y); cb0.z = fmaf(p0, xb[i].z, cb0.z); cb0.w = fmaf(p0, xb[i].w, cb0.w);
@@ -470,7 +476,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
                 __syncthreads();
                 // ---- cross-attention: folded queries q2' precomputed from obs_rep ------------------------
                 attention_absorbed_op<true, PFD>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64, cx2,
-                                            slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                                                 slot_stride, rows, n_valid, j + 1, s.U, s.V);
                 {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
