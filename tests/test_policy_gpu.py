@@ -205,3 +205,10 @@ def test_large_shapes_properties(L, B, cuda_device):
     if B <= 128:
         vo, ao, lpo = mo.get_actions(sd, obs.numpy(), ava.numpy(), L, deterministic=True, stride=1)
         assert_actions(_np(a), ao.numpy(), _np(lp), lpo.numpy(), L)
+
+
+@pytest.mark.gpu
+def test_graft_entry_smoke(cuda_device):
+    """The driver's round-end smoke() must stay green (it is not exercised by anything else)."""
+    import __graft_entry__
+    __graft_entry__.smoke()
