@@ -75,6 +75,7 @@ class DcmlVecEnv:
         self.num_envs = self.N = int(n_envs)
         self.W, self.L = int(n_workers), int(n_workers) + 1
         self.n_agents = self.L
+        self.env_offset = int(env_offset)
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _cabi.MatasError("DcmlVecEnv needs a CUDA device (there is no CPU fallback)")

@@ -1,0 +1,152 @@
+"""Device-resident runner for the MAT-AS / DCML training loop.
+
+Mirrors the reference's ``DCMLRunner.run / warmup / collect / insert`` (``dcml_runner.py:22-288``) and
+``Runner.compute / train`` (``mat_src/mat/runner/shared/base_runner.py:286-325,429-435``) for
+``algorithm_name == "mat"``: the same call order, the same arrays in the rollout buffer, the same masks, the same
+per-episode statistics (average reward / delay / payment of finished episodes).  What differs is where the data
+lives: observations, actions, rewards and masks stay on the GPU between the policy, the simulator and the buffer
+(no ``_t2n`` / ``np.concatenate`` / ``np.split`` per step), ``share_obs`` is kept as one row per env, and the
+statistics are accumulated on the device and read back once per logging interval.
+
+    runner = DcmlRunner(dict(all_args=args, envs=DcmlVecEnv(...), num_agents=L, device=torch.device("cuda")))
+    logs = runner.run()          # list of dicts, one per logged episode
+
+TensorBoard / W&B writers, model-directory handling and the evaluation loop of the reference runner are outside
+the hot path (SURVEY.md section 8 "not rebuilt"); ``log_train`` returns the numbers instead of writing them.
+"""
+import time
+
+import numpy as np
+import torch
+
+from . import _cabi
+from .mat_trainer import MATTrainer
+from .shared_buffer import SharedReplayBuffer
+from .transformer_policy import TransformerPolicy
+
+
+class DcmlRunner:
+    def __init__(self, config):
+        self.all_args = a = config["all_args"]
+        self.envs = config["envs"]
+        self.device = torch.device(config.get("device", "cuda"))
+        if self.device.type != "cuda":
+            raise _cabi.MatasError("DcmlRunner needs a CUDA device (there is no CPU fallback)")
+        self.num_agents = config["num_agents"]
+        if a.algorithm_name != "mat":
+            raise NotImplementedError("algorithm_name %r: only 'mat' is wired for DCML (base_runner.py:198)" % a.algorithm_name)
+        # base_runner.py:20-45
+        self.algorithm_name, self.experiment_name = a.algorithm_name, getattr(a, "experiment_name", "")
+        self.num_env_steps, self.episode_length = a.num_env_steps, a.episode_length
+        self.n_rollout_threads = a.n_rollout_threads
+        self.use_linear_lr_decay = getattr(a, "use_linear_lr_decay", False)
+        self.use_centralized_V = getattr(a, "use_centralized_V", True)
+        self.log_interval = getattr(a, "log_interval", 1)
+        self.save_interval = getattr(a, "save_interval", 0)
+        self.save_dir = config.get("save_dir")
+        env = self.envs
+        if env.N != self.n_rollout_threads or env.L != self.num_agents:
+            raise ValueError("env batch (%d x %d) does not match n_rollout_threads x num_agents (%d x %d)"
+                             % (env.N, env.L, self.n_rollout_threads, self.num_agents))
+        # base_runner.py:198-230
+        self.policy = TransformerPolicy(a, env.observation_space[0], env.share_observation_space[0], env.action_space[0],
+                                        self.num_agents, device=self.device)
+        self.policy.transformer.output_device = self.device          # keep actions / log-probs on the GPU
+        self.policy.transformer.env_offset = env.env_offset
+        self.trainer = MATTrainer(a, self.policy, self.num_agents, device=self.device)
+        self.buffer = SharedReplayBuffer(a, self.num_agents, env.observation_space[0], env.share_observation_space[0],
+                                         env.action_space[0], a.env_name, device=self.device)
+
+    # ---- dcml_runner.py:126-142 ------------------------------------------------------------------------
+    def warmup(self):
+        obs, share_obs, ava = self.envs.reset_device()
+        self.buffer.obs[0].copy_(obs)
+        self.buffer._share_obs[0].copy_(self.envs.sob if self.use_centralized_V else obs[:, 0])
+        self.buffer.available_actions[0].copy_(ava)
+
+    # ---- dcml_runner.py:144-245 ("mat" branch) -----------------------------------------------------------
+    @torch.no_grad()
+    def collect(self, step):
+        self.trainer.prep_rollout()
+        b, N, L = self.buffer, self.n_rollout_threads, self.num_agents
+        value, action, logp, _, _ = self.policy.get_actions(None, b.obs[step].reshape(N * L, -1), None, None, None,
+                                                            b.available_actions[step].reshape(N * L, -1))
+        return value.reshape(N, L, -1), action.reshape(N, L, -1), logp.reshape(N, L, -1), None, None
+
+    # ---- dcml_runner.py:247-288 ----------------------------------------------------------------------------
+    def insert(self, data):
+        obs, share_row, rewards, dones_env, available_actions, values, actions, action_log_probs = data
+        # every agent of an env finishes together (DCML_BID_FIRST_MA_ENV_SingleProcess.py:262-267), so
+        # masks = 1 - done per env and active_masks stay 1 (dcml_runner.py:264-268)
+        masks = 1.0 - dones_env.float()
+        self.buffer.insert(share_row, obs, None, None, actions, action_log_probs, values, rewards, masks, None, None,
+                           available_actions)
+
+    # ---- base_runner.py:286-325 ------------------------------------------------------------------------------
+    @torch.no_grad()
+    def compute(self):
+        self.trainer.prep_rollout()
+        b = self.buffer
+        next_values = self.policy.get_values(None, b.obs[-1].reshape(-1, b.obs.shape[-1]), None, None)
+        b.compute_returns(next_values.reshape(b.value_preds[-1].shape), self.trainer.value_normalizer)
+
+    # ---- base_runner.py:429-435 -------------------------------------------------------------------------------
+    def train(self):
+        self.trainer.prep_training()
+        train_infos = self.trainer.train(self.buffer)
+        self.buffer.after_update()
+        return train_infos
+
+    def save(self, episode):
+        if self.save_dir is not None:
+            self.policy.save(self.save_dir, episode)          # base_runner.py:437-449
+
+    def log_train(self, train_infos, total_num_steps):
+        train_infos = dict(train_infos)
+        train_infos["average_step_rewards"] = float(self.buffer.rewards.mean())     # dcml_runner.py:300-303
+        train_infos["total_num_steps"] = total_num_steps
+        return train_infos
+
+    # ---- dcml_runner.py:22-124 -----------------------------------------------------------------------------
+    def run(self, episodes=None, verbose=False):
+        self.warmup()
+        start = time.time()
+        if episodes is None:
+            episodes = int(self.num_env_steps) // self.episode_length // self.n_rollout_threads
+        N = self.n_rollout_threads
+        f64 = dict(dtype=torch.float64, device=self.device)
+        ep_reward, ep_delay, ep_payment = torch.zeros(N, **f64), torch.zeros(N, **f64), torch.zeros(N, **f64)
+        done_sum = torch.zeros(4, **f64)           # finished episodes: count, reward, delay, payment sums
+        logs = []
+        for episode in range(episodes):
+            if self.use_linear_lr_decay:
+                self.policy.lr_decay(episode, episodes)
+            for step in range(self.episode_length):
+                values, actions, action_log_probs, _, _ = self.collect(step)
+                obs, _, rewards, dones, delay, payment, ava = self.envs.step_device(actions)
+                d = dones.bool()
+                ep_reward += rewards.double(); ep_delay += delay.double(); ep_payment += payment.double()
+                dm = d.double()
+                done_sum += torch.stack([dm.sum(), (ep_reward * dm).sum(), (ep_delay * dm).sum(), (ep_payment * dm).sum()])
+                ep_reward.masked_fill_(d, 0.0); ep_delay.masked_fill_(d, 0.0); ep_payment.masked_fill_(d, 0.0)
+                self.insert((obs, self.envs.sob if self.use_centralized_V else obs[:, 0], rewards, dones, ava, values, actions,
+                             action_log_probs))
+            self.compute()
+            train_infos = self.train()
+            total_num_steps = (episode + 1) * self.episode_length * N
+            if self.save_interval and (episode % self.save_interval == 0 or episode == episodes - 1):
+                self.save(episode)
+            if episode % self.log_interval == 0:
+                info = self.log_train(train_infos, total_num_steps)
+                info["fps"] = int(total_num_steps / max(time.time() - start, 1e-9))
+                cnt, r, dl, pay = done_sum.tolist()
+                if cnt > 0:
+                    info.update(aver_episode_rewards=r / cnt, aver_episode_delays=dl / cnt, aver_episode_payments=pay / cnt,
+                                done_episodes=int(cnt))
+                    done_sum.zero_()
+                if verbose:
+                    print("updates %d/%d episodes, total num timesteps %d, FPS %d, %s"
+                          % (episode, episodes, total_num_steps, info["fps"], {k: (round(v, 5) if isinstance(v, float) else v)
+                                                                                   for k, v in info.items()}))
+                logs.append(info)
+        return logs

@@ -1,0 +1,100 @@
+"""Device-resident runner (mat_dcml_b200/dcml_runner.py) against a rollout composed from the oracle's pieces:
+same named Philox draws -> same actions, log-probs, values, rewards, masks and GAE returns in the buffer as the
+reference's DCMLRunner.collect / insert / compute would produce (dcml_runner.py:22-288, base_runner.py:286-325)."""
+import argparse
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import env_oracle as eo
+from oracle import mat_oracle as mo
+from oracle import philox as px
+from oracle import ppo_oracle as po
+
+pytestmark = pytest.mark.gpu
+
+
+def _args(**over):
+    ns = argparse.Namespace(algorithm_name="mat", env_name="DCML", lr=5e-4, opti_eps=1e-5, weight_decay=0,
+                            use_policy_active_masks=True, n_block=2, n_embd=64, n_head=2, encode_state=False,
+                            dec_actor=False, share_actor=False, clip_param=0.2, ppo_epoch=2, num_mini_batch=2,
+                            data_chunk_length=10, value_loss_coef=1.0, entropy_coef=0.01, max_grad_norm=10.0, huber_delta=10.0,
+                            use_recurrent_policy=False, use_naive_recurrent_policy=False, use_max_grad_norm=True,
+                            use_clipped_value_loss=True, use_huber_loss=True, use_valuenorm=True, use_value_active_masks=True,
+                            hidden_size=64, recurrent_N=1, gamma=0.99, gae_lambda=0.95, use_gae=True, use_popart=True,
+                            use_proper_time_limits=False, use_linear_lr_decay=True, use_centralized_V=True, log_interval=1,
+                            num_env_steps=0, episode_length=6, n_rollout_threads=8)
+    for k, v in over.items():
+        setattr(ns, k, v)
+    return ns
+
+
+def test_runner_rollout_matches_oracle_composition(cuda_device):
+    from mat_dcml_b200 import DcmlRunner, DcmlVecEnv
+    W, L, N, T, seed = 6, 7, 8, 6, 11
+    args = _args(episode_length=T, n_rollout_threads=N)
+    env = DcmlVecEnv(N, W, seed=seed)
+    runner = DcmlRunner(dict(all_args=args, envs=env, num_agents=L, device=torch.device("cuda")))
+    sd = mo.make_weights(5, L)
+    runner.policy.transformer.load_state_dict(mo.full_state_dict(sd, L))
+    runner.policy.transformer.rollout_seed = 777
+    runner.policy.transformer.rollout_step = 0
+    runner.warmup()
+    for step in range(T):
+        values, actions, logp, _, _ = runner.collect(step)
+        obs, _, rew, dones, delay, pay, ava = env.step_device(actions)
+        runner.insert((obs, env.sob, rew, dones, ava, values, actions, logp))
+    runner.compute()
+    b = runner.buffer
+    # ---- the same rollout from the oracle's pieces -----------------------------------------------------
+    ora = eo.DcmlEnvOracle(N, W, env.base_workload, seed=seed)
+    o_obs, o_sob, o_ava = ora.reset()
+    rewards, masks, vals = np.zeros((T, N, L, 1), np.float32), np.ones((T + 1, N, L, 1), np.float32), np.zeros((T + 1, N, L, 1), np.float32)
+    for step in range(T):
+        np.testing.assert_allclose(b.obs[step].cpu().numpy(), o_obs, rtol=1e-5, atol=1e-6)
+        u = px.policy_uniforms(777, step, N, L)
+        z = px.policy_normals(777, step, N, L - 1)
+        vo, ao, lpo = mo.get_actions(sd, o_obs, o_ava, L, deterministic=False, u=u, z=z)
+        a_gpu = b.actions[step].cpu().numpy().reshape(N, L)
+        a_ora = ao.numpy().reshape(N, L)
+        assert (a_gpu[:, :-1] == a_ora[:, :-1]).all(), "sampled discrete actions differ at step %d" % step
+        np.testing.assert_allclose(a_gpu[:, -1], a_ora[:, -1], atol=1e-4)
+        np.testing.assert_allclose(b.action_log_probs[step].cpu().numpy().reshape(N, L), lpo.numpy().reshape(N, L), atol=1e-4)
+        np.testing.assert_allclose(b.value_preds[step].cpu().numpy().reshape(N, L), vo.numpy().reshape(N, L), atol=1e-4)
+        vals[step] = vo.numpy().reshape(N, L, 1)
+        # feed the oracle env the GPU path's actions so that a last-ulp difference in the Gaussian agent cannot fork the rollout
+        o_obs, o_sob, o_rew, o_done, _, o_ava = ora.step(a_gpu.reshape(N, L, 1))
+        np.testing.assert_allclose(b.rewards[step].cpu().numpy(), np.asarray(o_rew, np.float32).reshape(N, L, 1), rtol=1e-5)
+        rewards[step] = np.asarray(o_rew, np.float32).reshape(N, L, 1)
+        masks[step + 1] = 1.0 - np.asarray(o_done, np.float32).reshape(N, L, 1)
+        np.testing.assert_array_equal(b.masks[step + 1].cpu().numpy(), masks[step + 1])
+        np.testing.assert_array_equal(b.active_masks[step + 1].cpu().numpy(), np.ones((N, L, 1), np.float32))
+    vals[T] = mo.get_values(sd, o_obs, L).numpy().reshape(N, L, 1)
+    # compute(): GAE through the (freshly initialised) ValueNorm, base_runner.py:286-325 + shared_buffer.py:207-238
+    adv_o, ret_o, _ = po.compute_returns(rewards, vals, masks, vals[T], vn=po.ValueNormState(), gamma=args.gamma, lam=args.gae_lambda)
+    np.testing.assert_allclose(b.returns[:-1].cpu().numpy(), ret_o[:-1], rtol=2e-4, atol=2e-4)
+    np.testing.assert_allclose(b.advantages.cpu().numpy(), adv_o, rtol=2e-4, atol=2e-4)
+    # train(): finite losses, weights move, buffer rolled over (shared_buffer.py:188-198)
+    w0 = runner.policy.transformer.flat_parameters().clone()
+    last_obs = b.obs[-1].clone()
+    info = runner.train()
+    assert all(np.isfinite(v) for v in info.values()), info
+    assert float((runner.policy.transformer.flat_parameters() - w0).abs().max()) > 0
+    assert torch.equal(b.obs[0], last_obs)
+
+
+def test_runner_run_loop(cuda_device):
+    from mat_dcml_b200 import DcmlRunner, DcmlVecEnv
+    W, L, N, T = 10, 11, 64, 10
+    args = _args(episode_length=T, n_rollout_threads=N, num_env_steps=3 * T * N)
+    runner = DcmlRunner(dict(all_args=args, envs=DcmlVecEnv(N, W, seed=2), num_agents=L, device=torch.device("cuda")))
+    logs = runner.run()
+    assert len(logs) == 3
+    for i, info in enumerate(logs):
+        assert info["total_num_steps"] == (i + 1) * T * N
+        assert np.isfinite(info["value_loss"]) and np.isfinite(info["policy_loss"]) and np.isfinite(info["average_step_rewards"])
+    # done episodes were seen (the simulator ends an episode with probability 1/2 per step ... SingleProcess.py:262-267)
+    assert any("aver_episode_rewards" in info for info in logs)
+    lrs = [g["lr"] for g in runner.policy.optimizer.param_groups]
+    assert lrs[0] < args.lr          # linear decay applied (transformer_policy.py:108-114)
