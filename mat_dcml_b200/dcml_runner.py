@@ -11,8 +11,9 @@ statistics are accumulated on the device and read back once per logging interval
     runner = DcmlRunner(dict(all_args=args, envs=DcmlVecEnv(...), num_agents=L, device=torch.device("cuda")))
     logs = runner.run()          # list of dicts, one per logged episode
 
-TensorBoard / W&B writers, model-directory handling and the evaluation loop of the reference runner are outside
-the hot path (SURVEY.md section 8 "not rebuilt"); ``log_train`` returns the numbers instead of writing them.
+``eval`` is the reference's deterministic evaluation loop (``dcml_runner.py:319-448``) on the same kernels.
+TensorBoard / W&B writers and model-directory handling are outside the hot path (SURVEY.md section 8 "not
+rebuilt"); ``log_train`` returns the numbers instead of writing them.
 """
 import time
 
@@ -106,6 +107,38 @@ class DcmlRunner:
         train_infos["average_step_rewards"] = float(self.buffer.rewards.mean())     # dcml_runner.py:300-303
         train_infos["total_num_steps"] = total_num_steps
         return train_infos
+
+    # ---- dcml_runner.py:319-448 ("mat" branch) ----------------------------------------------------------------
+    @torch.no_grad()
+    def eval(self, total_num_steps, stride=2, eval_envs=None):
+        """Deterministic evaluation: ``policy.act(deterministic=True, stride=stride)`` for ``total_num_steps`` steps of
+        the evaluation envs (preset contexts via ``DcmlVecEnv.set_context`` reproduce the reference's benchmark
+        mode).  Returns the reference's 4-tuple: mean reward / delay / payment over the episodes that finished,
+        and the mean time of one batched decision in seconds (measured on the device)."""
+        envs = self.envs if eval_envs is None else eval_envs
+        self.trainer.prep_rollout()
+        N, L = envs.N, envs.L
+        f64 = dict(dtype=torch.float64, device=self.device)
+        one_r, one_d, one_p = torch.zeros(N, **f64), torch.zeros(N, **f64), torch.zeros(N, **f64)
+        fin = torch.zeros(4, **f64)                  # finished episodes: count, reward, delay, payment sums
+        obs, _, ava = envs.reset_device()
+        t_ms, e0, e1 = 0.0, torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(total_num_steps):
+            e0.record()
+            actions, _ = self.policy.act(None, obs.reshape(N * L, -1), None, None, ava.reshape(N * L, -1), deterministic=True,
+                                         stride=stride)
+            e1.record()
+            obs, _, rewards, dones, delay, payment, ava = envs.step_device(actions.reshape(N, L, 1))
+            one_r += rewards.double(); one_d += delay.double(); one_p += payment.double()
+            d = dones.bool()
+            dm = d.double()
+            fin += torch.stack([dm.sum(), (one_r * dm).sum(), (one_d * dm).sum(), (one_p * dm).sum()])
+            one_r.masked_fill_(d, 0.0); one_d.masked_fill_(d, 0.0); one_p.masked_fill_(d, 0.0)
+            e1.synchronize()
+            t_ms += e0.elapsed_time(e1)
+        cnt, r, dl, pay = fin.tolist()
+        nan = float("nan")
+        return ((r / cnt, dl / cnt, pay / cnt) if cnt > 0 else (nan, nan, nan)) + (t_ms * 1e-3 / max(total_num_steps, 1),)
 
     # ---- dcml_runner.py:22-124 -----------------------------------------------------------------------------
     def run(self, episodes=None, verbose=False):

@@ -98,3 +98,55 @@ def test_runner_run_loop(cuda_device):
     assert any("aver_episode_rewards" in info for info in logs)
     lrs = [g["lr"] for g in runner.policy.optimizer.param_groups]
     assert lrs[0] < args.lr          # linear decay applied (transformer_policy.py:108-114)
+
+
+def test_runner_eval_matches_oracle_composition(cuda_device):
+    """DCMLRunner.eval (dcml_runner.py:319-448): deterministic stride-2 decisions on preset contexts."""
+    from mat_dcml_b200 import DcmlRunner, DcmlVecEnv
+    W, L, N, steps, seed = 6, 7, 16, 12, 5
+    args = _args(episode_length=4, n_rollout_threads=N)
+    sd = mo.make_weights(9, L)
+    R = np.linspace(5.0, 40.0, N)
+    C = np.linspace(0.5, 0.05, N)
+
+    def fresh():
+        env = DcmlVecEnv(N, W, seed=seed)
+        runner = DcmlRunner(dict(all_args=args, envs=env, num_agents=L, device=torch.device("cuda")))
+        runner.policy.transformer.load_state_dict(mo.full_state_dict(sd, L))
+        return env, runner
+
+    # step-by-step: GPU decisions against the oracle's, oracle env driven by the GPU actions
+    env, runner = fresh()
+    ora = eo.DcmlEnvOracle(N, W, env.base_workload, seed=seed)
+    obs, _, ava = env.reset_device()
+    o_obs, _, o_ava = ora.reset()
+    one = np.zeros((3, N)); fin = np.zeros(4)
+    same_rows = 0
+    for i in range(steps):
+        act, _ = runner.policy.act(None, obs.reshape(N * L, -1), None, None, ava.reshape(N * L, -1), deterministic=True, stride=2)
+        _, ao, _ = mo.get_actions(sd, o_obs, o_ava, L, deterministic=True, stride=2)
+        a_gpu, a_ora = act.cpu().numpy().reshape(N, L), ao.numpy().reshape(N, L)
+        same_rows += int((a_gpu[:, :-1] == a_ora[:, :-1]).all(1).sum())
+        obs, _, rew, dones, delay, pay, ava = env.step_device(act.reshape(N, L, 1))
+        o_obs, _, o_rew, o_done, o_info, o_ava = ora.step(a_gpu.reshape(N, L, 1))
+        np.testing.assert_allclose(rew.cpu().numpy(), np.asarray(o_rew)[:, 0, 0], rtol=1e-5)
+        one[0] += np.asarray(o_rew)[:, 0, 0]
+        one[1] += np.array([inf[0]["delay"] for inf in o_info]); one[2] += np.array([inf[0]["payment"] for inf in o_info])
+        d = np.asarray(o_done)[:, 0].astype(bool)
+        fin += [d.sum(), one[0][d].sum(), one[1][d].sum(), one[2][d].sum()]
+        one[:, d] = 0.0
+    assert same_rows >= 0.97 * steps * N, "deterministic actions differ from the oracle beyond near-ties"
+    assert fin[0] > 0
+    # the runner's own loop on a fresh env of the same seed reports the same finished-episode means
+    env2, runner2 = fresh()
+    r, dl, pay, t_dec = runner2.eval(steps, stride=2)
+    np.testing.assert_allclose([r, dl, pay], fin[1:] / fin[0], rtol=1e-5)
+    assert t_dec > 0
+    # preset contexts (Env(preset=True) / modify_preset): the evaluation runs from the given R / C
+    env3, runner3 = fresh()
+    env3.reset_device()
+    env3.set_context(R=R, C=C)
+    o3 = eo.DcmlEnvOracle(N, W, env3.base_workload, seed=seed)
+    o3.reset(); o3.set_context(R=R, C=C)
+    obs3, _, ava3 = env3.obs, None, env3.ava
+    np.testing.assert_allclose(obs3.cpu().numpy(), o3._observe_all()[0], rtol=1e-5, atol=1e-6)
