@@ -190,17 +190,19 @@ def run_ours(ns):
         buf.obs[0].copy_(obs); buf._share_obs[0].copy_(env.sob); buf.available_actions[0].copy_(ava)
         buf.step = 0
 
+    n_enc = 5 if L <= 64 else 3             # embed+QKV, then per block [tiled attention (n_agent <= 64)] + block kernel
+
     def device_step(i):
         mdl.output_device = dev
         a, lp, v = mdl.get_actions(None, state["obs"], state["ava"], deterministic=det, stride=stride)
         obs, sob, rew, done, delay, pay, ava = env.step_device(a)
         buf.insert(env.sob, obs, None, None, a, lp, v, rew, 1.0 - done.float(), None, None, ava)
-        launches["n"] += 1 + 3 + 1 + 1          # weight repack, encoder x3, decode, env step
+        launches["n"] += n_enc + 1 + 1          # encoder, decode, env step (the weight repack runs only when weights change)
         if buf.step == 0:                        # episode boundary: bootstrap + GAE (base_runner.py:286-325)
             nv = mdl.get_values(None, obs)
             buf.compute_returns(nv, vn)
             buf.after_update()
-            launches["n"] += 1 + 3 + 1
+            launches["n"] += n_enc + 1          # encoder, GAE
         state["obs"], state["ava"] = obs, ava
 
     # ---- end-to-end step through the reference-facing API with HOST arrays -------------------

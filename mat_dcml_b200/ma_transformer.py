@@ -160,6 +160,8 @@ class MultiAgentTransformer(nn.Module):
             p.data = flat[off:off + k].view(p.shape)
             off += k
         self._flat = flat
+        self._plist = params
+        self._packed_key = None
 
     def flat_parameters(self):
         return self._flat
@@ -218,10 +220,21 @@ class MultiAgentTransformer(nn.Module):
                 pass
 
     def sync_weights(self):
-        """Repack the flat parameters for the kernels (one small launch; called before every pass)."""
+        """Repack the flat parameters for the kernels (three small launches).  Called before every pass; skipped
+        when neither the flat tensor nor any parameter view has been written since the last repack (torch's version
+        counters: optimizer steps, ``load_state_dict`` and any other in-place torch update are seen; code that
+        writes the memory behind torch's back, e.g. a collective on ``flat_parameters()``, must call
+        ``invalidate_weights``)."""
         h = self._h()
-        _cabi.check(_cabi.lib().matas_policy_set_weights(h, _cabi.ptr(self._flat), _cabi.stream_ptr()))
+        # parameters are views created with ``p.data = flat[...]``: each keeps its own version counter
+        key = (self._flat._version, self._flat.data_ptr(), tuple(p._version for p in self._plist))
+        if key != getattr(self, "_packed_key", None):
+            _cabi.check(_cabi.lib().matas_policy_set_weights(h, _cabi.ptr(self._flat), _cabi.stream_ptr()))
+            self._packed_key = key
         return h
+
+    def invalidate_weights(self):
+        self._packed_key = None
 
     def _dev(self, x, shape=None):
         x = _check(x)

@@ -212,3 +212,30 @@ def test_graft_entry_smoke(cuda_device):
     """The driver's round-end smoke() must stay green (it is not exercised by anything else)."""
     import __graft_entry__
     __graft_entry__.smoke()
+
+
+@pytest.mark.gpu
+def test_weight_repack_is_skipped_only_when_unchanged(cuda_device):
+    """sync_weights() caches the repack on torch's version counters: every in-place update must be seen."""
+    L, B = 5, 6
+    sd = mo.make_weights(3, L)
+    m = make_model(L, sd)
+    obs = torch.rand(B, L, 7, device="cuda")
+    v0 = m.get_values(None, obs).clone()
+    assert torch.equal(m.get_values(None, obs), v0)                   # cached repack, same result
+    with torch.no_grad():
+        m.encoder.head[3].bias.add_(1.0)                              # in-place update of one parameter view
+    assert torch.allclose(m.get_values(None, obs), v0 + 1.0, atol=1e-6)
+    with torch.no_grad():
+        m.flat_parameters().mul_(1.0)                                 # write through the flat tensor
+        for p in m.parameters():
+            if p is m.encoder.head[3].bias:
+                p.sub_(1.0)
+    assert torch.allclose(m.get_values(None, obs), v0, atol=1e-6)
+    opt = torch.optim.SGD(m.parameters(), lr=0.5)
+    m.flat_grad(zero=True)
+    m.encoder.head[3].bias.grad.fill_(2.0)
+    opt.step()                                                        # optimizer step: bias -= 1.0
+    assert torch.allclose(m.get_values(None, obs), v0 - 1.0, atol=1e-6)
+    m.load_state_dict(mo.full_state_dict(sd, L))
+    assert torch.allclose(m.get_values(None, obs), v0, atol=1e-6)
