@@ -310,9 +310,87 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
     }
 }
 
+// The same attention with SIXTEEN lanes per env (lane l holds columns 4l..4l+3 of every row) for tiles of at most
+// 32 envs, where 8 lanes per env would leave half of the CTA's threads without work (small batches, large L).
+// Four keys per batch, the next batch in flight in registers.
+template <bool GQ, int PF>
+__device__ __forceinline__ void attention_absorbed_op16(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
+                                                        const float* cache, long slot_stride, int rows, int n_valid, int nk,
+                                                        unsigned char* U, unsigned char* V) {
+    constexpr int KB = 4;
+    const int tid = threadIdx.x, grp = tid >> 4, l = tid & 15;
+    const unsigned hmask = 0xffffu << (tid & 16);
+    const bool up = (l & 8) != 0;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = grp; r < rows; r += NTD / 16) {
+        const int nr = r < n_valid ? nk : 0;
+        float4 qa, qb;
+        if (GQ) {
+            qa = nr ? __ldg(reinterpret_cast<const float4*>(q0 + (long)r * q_stride) + l) : z4;
+            qb = nr ? __ldg(reinterpret_cast<const float4*>(q1 + (long)r * q_stride) + l) : z4;
+        } else {
+            qa = *reinterpret_cast<const float4*>(q0 + r * XS + l * 4);
+            qb = *reinterpret_cast<const float4*>(q1 + r * XS + l * 4);
+        }
+        const float4* xp = reinterpret_cast<const float4*>(cache + (long)r * slot_stride) + l;     // row t: xp[t * 16]
+        float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+        float4 c0 = z4, c1 = z4;
+        auto batch = [&](const float4 (&x)[KB], int t0) {
+            float s0[KB], s1[KB];
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                const float p0 = qa.x * x[i].x + qa.y * x[i].y + qa.z * x[i].z + qa.w * x[i].w;
+                const float p1 = qb.x * x[i].x + qb.y * x[i].y + qb.z * x[i].z + qb.w * x[i].w;
+                float v = up ? p1 : p0;                       // lanes 0-7 collect head 0, lanes 8-15 head 1
+                v += __shfl_xor_sync(hmask, up ? p0 : p1, 8);
+                v += __shfl_xor_sync(hmask, v, 4);
+                v += __shfl_xor_sync(hmask, v, 2);
+                v += __shfl_xor_sync(hmask, v, 1);
+                const float o = __shfl_xor_sync(hmask, v, 8);
+                const bool ok = t0 + i < nr;
+                s0[i] = ok ? (up ? o : v) : -INFINITY;
+                s1[i] = ok ? (up ? v : o) : -INFINITY;
+            }
+            float n0 = m0, n1 = m1;
+#pragma unroll
+            for (int i = 0; i < KB; ++i) { n0 = fmaxf(n0, s0[i]); n1 = fmaxf(n1, s1[i]); }
+            const float a0 = ex2(m0 - n0), a1 = ex2(m1 - n1);
+            l0 *= a0; l1 *= a1;
+            c0.x *= a0; c0.y *= a0; c0.z *= a0; c0.w *= a0;
+            c1.x *= a1; c1.y *= a1; c1.z *= a1; c1.w *= a1;
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                const float p0 = ex2(s0[i] - n0), p1 = ex2(s1[i] - n1);
+                l0 += p0; l1 += p1;
+                c0.x = fmaf(p0, x[i].x, c0.x); c0.y = fmaf(p0, x[i].y, c0.y); c0.z = fmaf(p0, x[i].z, c0.z); c0.w = fmaf(p0, x[i].w, c0.w);
+                c1.x = fmaf(p1, x[i].x, c1.x); c1.y = fmaf(p1, x[i].y, c1.y); c1.z = fmaf(p1, x[i].z, c1.z); c1.w = fmaf(p1, x[i].w, c1.w);
+            }
+            m0 = n0; m1 = n1;
+        };
+        auto fetch = [&](float4 (&x)[KB], int t0) {
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                x[i] = t0 + i < nr ? xp[(long)(t0 + i) * 16] : z4;
+                if (PF > 0 && (l & 7) == 0 && t0 + i + 2 * PF < nr) asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + (long)(t0 + i + 2 * PF) * 16));
+            }
+        };
+        float4 x[KB], y[KB];
+        fetch(x, 0);
+        for (int t0 = 0; t0 < nr; t0 += 2 * KB) {
+            fetch(y, t0 + KB);
+            batch(x, t0);
+            fetch(x, t0 + 2 * KB);
+            if (t0 + KB < nr) batch(y, t0 + KB);
+        }
+        const float i0 = nr > 0 ? 1.0f / l0 : 0.f, i1 = nr > 0 ? 1.0f / l1 : 0.f;
+        tc::store_operand4(U, r, l, make_float4(c0.x * i0, c0.y * i0, c0.z * i0, c0.w * i0));
+        tc::store_operand4(V, r, l, make_float4(c1.x * i1, c1.y * i1, c1.z * i1, c1.w * i1));
+    }
+}
+
 template <int PFD>
 __global__ void __launch_bounds__(NTD, 1)
-decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
+decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     DSmem s = dcarve(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -449,7 +527,8 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
                 }
                 tc::fence_before_sync();
                 __syncthreads();
-                attention_absorbed_op<false, PFD>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                if (rows <= rows16) attention_absorbed_op16<false, PFD>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                else attention_absorbed_op<false, PFD>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
                 }
                 // ---- self-attention output maps + x -> LN1 -> cross cache row -------------------------
                 {
@@ -475,8 +554,12 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows) {
                 tc::fence_before_sync();
                 __syncthreads();
                 // ---- cross-attention: folded queries q2' precomputed from obs_rep ------------------------
-                attention_absorbed_op<true, PFD>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64, cx2,
-                                                 slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                if (rows <= rows16)
+                    attention_absorbed_op16<true, PFD>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64,
+                                                       cx2, slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                else
+                    attention_absorbed_op<true, PFD>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64,
+                                                     cx2, slot_stride, rows, n_valid, j + 1, s.U, s.V);
                 {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
@@ -625,10 +708,12 @@ int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_s
     static int pf = -1;
     if (pf < 0) { const char* e = getenv("MATAS_DECODE_PF"); pf = e ? atoi(e) : 4; }
     const int rows = decode_tc_rows(a.B, n_sm);
+    static int rows16 = -1;          // tiles of at most this many envs use 16 lanes per env in the attention (MATAS_DECODE_ROWS16)
+    if (rows16 < 0) { const char* e = getenv("MATAS_DECODE_ROWS16"); rows16 = e ? atoi(e) : 32; }
 #define DECODE_TC_LAUNCH(P)                                                                                           \
     do {                                                                                                              \
         CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-        decode_tc_kernel<P><<<grid, NTD, bytes, st>>>(b, a, rows);                                                    \
+        decode_tc_kernel<P><<<grid, NTD, bytes, st>>>(b, a, rows, rows16);                                                   \
     } while (0)
     if (pf == 0) DECODE_TC_LAUNCH(0);
     else if (pf <= 4) DECODE_TC_LAUNCH(4);
