@@ -185,16 +185,18 @@ __device__ __forceinline__ void gelu_fwd(Frag& g, const Frag& h) {
 
 // projection backward shared by every attention: dS (grad of the proj output, fragment) ->
 // dWp, dbp, dY = dS.Wp stored to gY, D = rowsum_head(dY * Y) stored to gD
+template <bool TCW>
 __device__ __forceinline__ void proj_bwd(Ring& ring, const BSmem& s, const Frag& dS, const float* __restrict__ Y_g,
                                          float* __restrict__ gY, float* __restrict__ gD, long row0, int n_valid,
-                                         DW& dWp, Col& dbp, int rg, int cg) {
+                                         DW& dWp, Col& dbp, int rg, int cg, float* __restrict__ sY) {
     col_add(dbp, dS);
     frag_store_s(dS, s.T[0], rg, cg);
     Frag y;
     frag_load_g(y, Y_g, row0, n_valid, rg, cg);
-    frag_store_s(y, s.T[1], rg, cg);
+    if (TCW) frag_store_g(dS, sY, row0, n_valid, rg, cg, false);    // weight gradient on the tensor cores (bwd_dw_tc.cu)
+    else frag_store_s(y, s.T[1], rg, cg);
     __syncthreads();
-    dw_acc(dWp, s.T[0], s.T[1], n_valid, rg, cg);
+    if (!TCW) dw_acc(dWp, s.T[0], s.T[1], n_valid, rg, cg);
     Frag dY;
     gemm_dx(ring, s.T[0], dY, rg, cg, false);
     frag_store_g(dY, gY, row0, n_valid, rg, cg, false);
@@ -220,9 +222,11 @@ struct TailArgs {
     float* gRes; int res_add;
     float *gY, *gD;
     int with_mlp;
+    float* sY[3];          // non-null: write dS / dM0 / d(proj out) there instead of accumulating dW2 / dW0 / dWp here
 };
 
 // [LN_F bwd -> MLP bwd ->] LN_M bwd -> residual grad -> projection bwd      (encoder E1, decoder K1 / K2b)
+template <bool TCW>       // TCW: weight gradients on the tensor cores (bwd_dw_tc.cu): no dW accumulators here
 __global__ void __launch_bounds__(NT, 1)
 bwd_mlp_proj(const float* __restrict__ packed, float* __restrict__ grad, TailArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -257,23 +261,25 @@ bwd_mlp_proj(const float* __restrict__ packed, float* __restrict__ grad, TailArg
             col_add(db2, d);
             Frag h, g;
             frag_load_g(h, a.m0, row0, n_valid, rg, cg);
-            gelu_fwd(g, h);
+            if (!TCW) gelu_fwd(g, h);
             frag_store_s(d, s.T[0], rg, cg);
-            frag_store_s(g, s.T[1], rg, cg);
+            if (TCW) frag_store_g(d, a.sY[0], row0, n_valid, rg, cg, false);
+            else frag_store_s(g, s.T[1], rg, cg);
             __syncthreads();
-            dw_acc(dW2, s.T[0], s.T[1], n_valid, rg, cg);
+            if (!TCW) dw_acc(dW2, s.T[0], s.T[1], n_valid, rg, cg);
             Frag dm;
             gemm_dx(ring, s.T[0], dm, rg, cg, false);                                // dG = dS . W2
             gelu_bwd(dm, h);                                                          // dM0
             col_add(db0, dm);
             frag_load_g(xh, a.xhM, row0, n_valid, rg, cg);
             Frag xm;
-            ln_affine(xm, xh, lnMw, lnMb, cg);
+            if (!TCW) ln_affine(xm, xh, lnMw, lnMb, cg);
             frag_store_s(dm, s.T[2], rg, cg);
-            frag_store_s(xm, s.T[3], rg, cg);
+            if (TCW) frag_store_g(dm, a.sY[1], row0, n_valid, rg, cg, false);
+            else frag_store_s(xm, s.T[3], rg, cg);
             __syncthreads();
             ring.prefetch();
-            dw_acc(dW0, s.T[2], s.T[3], n_valid, rg, cg);
+            if (!TCW) dw_acc(dW0, s.T[2], s.T[3], n_valid, rg, cg);
             gemm_dx(ring, s.T[2], d, rg, cg, true);                                  // dX_M = dS + dM0 . W0
         } else {
             frag_load_g(xh, a.xhM, row0, n_valid, rg, cg);
@@ -282,14 +288,14 @@ bwd_mlp_proj(const float* __restrict__ packed, float* __restrict__ grad, TailArg
         frag_store_g(d, a.gRes, row0, n_valid, rg, cg, a.res_add != 0);
         __syncthreads();          // T[0]/T[1] free again (dw_acc above is done in every thread)
         ring.prefetch();
-        proj_bwd(ring, s, d, a.Y, a.gY, a.gD, row0, n_valid, dWp, dbp, rg, cg);
+        proj_bwd<TCW>(ring, s, d, a.Y, a.gY, a.gD, row0, n_valid, dWp, dbp, rg, cg, a.sY[2]);
     }
     if (a.with_mlp) {
-        dw_flush(dW2, grad, a.gW2, rg, cg); dw_flush(dW0, grad, a.gW0, rg, cg);
+        if (!TCW) { dw_flush(dW2, grad, a.gW2, rg, cg); dw_flush(dW0, grad, a.gW0, rg, cg); }
         col_flush(db2, grad, a.gb2, cg); col_flush(db0, grad, a.gb0, cg);
         col_flush(gFw, grad, a.glnFw, cg); col_flush(gFb, grad, a.glnFb, cg);
     }
-    dw_flush(dWp, grad, a.gWp, rg, cg);
+    if (!TCW) dw_flush(dWp, grad, a.gWp, rg, cg);
     col_flush(dbp, grad, a.gbp, cg);
     col_flush(gMw, grad, a.glnMw, cg); col_flush(gMb, grad, a.glnMb, cg);
 }
@@ -308,6 +314,7 @@ struct AttnArgs {
     float* gX;                                  // KIND 0: += ; KIND 1: = (grad wrt the k/v input)
     float* gRep;                                // KIND 1: += dq.Wq
     int causal, L;
+    float* sY[3];                               // non-null: write dq / dk / dv there instead of accumulating dWq / dWk / dWv here
 };
 
 // Sum a and b over the 8 lanes of a head (lane bit 2 = `up`) with 4 shuffles instead of 6: the two
@@ -402,7 +409,7 @@ __device__ __forceinline__ void attn_bwd_rows(const AttnArgs& a, long row0, long
     }
 }
 
-template <int KIND>
+template <int KIND, bool TCW>
 __global__ void __launch_bounds__(NT, 2)
 bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -428,17 +435,18 @@ bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a,
         attn_bwd_rows<4>(a, row0, n_tok, sDq, sDv, sDk);
         // ---- projections: dW, db, dX -------------------------------------------------------------
         Frag dx;
+        constexpr bool tcw = TCW;                                        // weight gradients on the tensor cores (bwd_dw_tc.cu)
         if (KIND == 1) {
-            load_tile(sX, a.xin + row0 * 64, 64, n_valid);             // obs_rep: the query input
+            if (!tcw) load_tile(sX, a.xin + row0 * 64, 64, n_valid);   // obs_rep: the query input
             __syncthreads();
-            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); }
-            dw_acc(dWq, sDq, sX, n_valid, rg, cg);
+            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (tcw) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
+            if (!tcw) dw_acc(dWq, sDq, sX, n_valid, rg, cg);
             gemm_dx(ring, sDq, dx, rg, cg, false);
             frag_store_g(dx, a.gRep, row0, n_valid, rg, cg, true);
             __syncthreads();
             ring.prefetch();
         }
-        {
+        if (!tcw) {
             Frag xin;
             if (a.ln >= 0) {
                 Frag xh;
@@ -451,25 +459,25 @@ bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a,
         }
         __syncthreads();
         if (KIND == 0) {
-            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); }
-            dw_acc(dWq, sDq, sX, n_valid, rg, cg);
+            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (tcw) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
+            if (!tcw) dw_acc(dWq, sDq, sX, n_valid, rg, cg);
             gemm_dx(ring, sDq, dx, rg, cg, false);
             __syncthreads();
             ring.prefetch();
         }
-        { Frag f; frag_load_s(f, sDk, rg, cg); col_add(dbk, f); }
-        dw_acc(dWk, sDk, sX, n_valid, rg, cg);
+        { Frag f; frag_load_s(f, sDk, rg, cg); col_add(dbk, f); if (tcw) frag_store_g(f, a.sY[1], row0, n_valid, rg, cg, false); }
+        if (!tcw) dw_acc(dWk, sDk, sX, n_valid, rg, cg);
         gemm_dx(ring, sDk, dx, rg, cg, KIND == 0);
         __syncthreads();
         ring.prefetch();
-        { Frag f; frag_load_s(f, sDv, rg, cg); col_add(dbv, f); }
-        dw_acc(dWv, sDv, sX, n_valid, rg, cg);
+        { Frag f; frag_load_s(f, sDv, rg, cg); col_add(dbv, f); if (tcw) frag_store_g(f, a.sY[2], row0, n_valid, rg, cg, false); }
+        if (!tcw) dw_acc(dWv, sDv, sX, n_valid, rg, cg);
         gemm_dx(ring, sDv, dx, rg, cg, true);
         frag_store_g(dx, a.gX, row0, n_valid, rg, cg, KIND == 0);       // KIND 0: += ; KIND 1: =
         __syncthreads();
         ring.prefetch();
     }
-    dw_flush(dWq, grad, a.gWq, rg, cg); dw_flush(dWk, grad, a.gWk, rg, cg); dw_flush(dWv, grad, a.gWv, rg, cg);
+    if (!TCW) { dw_flush(dWq, grad, a.gWq, rg, cg); dw_flush(dWk, grad, a.gWk, rg, cg); dw_flush(dWv, grad, a.gWv, rg, cg); }
     col_flush(dbq, grad, a.gbq, cg); col_flush(dbk, grad, a.gbk, cg); col_flush(dbv, grad, a.gbv, cg);
 }
 
@@ -489,9 +497,10 @@ struct HeadArgs {
     int gW0, gb0, glnw, glnb, gW3, gb3, glogstd;
     float* gOut;                     // DEC: gX (store); ENC: gRep (add)
     int L, n_disc;
+    float* sY;                       // non-null: write d(head.0 output) there instead of accumulating dW0 here
 };
 
-template <int DEC>
+template <int DEC, bool TCW>
 __global__ void __launch_bounds__(NT, 1)
 bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -591,16 +600,17 @@ bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a,
             frag_load_g(xin, a.rep, row0, n_valid, rg, cg);
         }
         frag_store_s(d, s.T[1], rg, cg);
-        frag_store_s(xin, s.T[2], rg, cg);
+        if (TCW) frag_store_g(d, a.sY, row0, n_valid, rg, cg, false);
+        else frag_store_s(xin, s.T[2], rg, cg);
         __syncthreads();
-        dw_acc(dW0, s.T[1], s.T[2], n_valid, rg, cg);
+        if (!TCW) dw_acc(dW0, s.T[1], s.T[2], n_valid, rg, cg);
         Frag dx;
         gemm_dx(ring, s.T[1], dx, rg, cg, false);
         frag_store_g(dx, a.gOut, row0, n_valid, rg, cg, DEC ? false : true);
         __syncthreads();
         ring.prefetch();
     }
-    dw_flush(dW0, grad, a.gW0, rg, cg);
+    if (!TCW) dw_flush(dW0, grad, a.gW0, rg, cg);
     col_flush(db0, grad, a.gb0, cg); col_flush(glw, grad, a.glnw, cg); col_flush(glb, grad, a.glnb, cg);
     col_flush(gw3a, grad, a.gW3, cg);
     if (DEC) col_flush(gw3b, grad, a.gW3 + 64, cg);
@@ -796,19 +806,45 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         return MATAS_ERR_LIMIT;
     }
     const size_t bytes = bsmem_bytes(BDEPTH), abytes = bsmem_bytes(ADEPTH);
+    const bool tcw = policy_use_tc();               // weight gradients on the tensor cores (bwd_dw_tc.cu)
     const long n_tok = M * L;
     const long n_tiles = (n_tok + TM - 1) / TM;
     const unsigned grid = (unsigned)(n_tiles < n_sm ? n_tiles : n_sm);
     const unsigned agrid = (unsigned)(n_tiles < 2 * n_sm ? n_tiles : 2 * n_sm);     // bwd_attn: two CTAs per SM
     int rc;
-    if ((rc = set_smem(bwd_mlp_proj, bytes)) || (rc = set_smem(bwd_attn<0>, abytes)) || (rc = set_smem(bwd_attn<1>, abytes)) ||
-        (rc = set_smem(bwd_head<0>, bytes)) || (rc = set_smem(bwd_head<1>, bytes)) || (rc = set_smem(bwd_embed_enc, bytes)) ||
-        (rc = set_smem(bwd_embed_dec, bytes)))
+    if ((rc = set_smem(bwd_mlp_proj<false>, bytes)) || (rc = set_smem(bwd_mlp_proj<true>, bytes)) ||
+        (rc = set_smem(bwd_attn<0, false>, abytes)) || (rc = set_smem(bwd_attn<1, false>, abytes)) ||
+        (rc = set_smem(bwd_attn<0, true>, abytes)) || (rc = set_smem(bwd_attn<1, true>, abytes)) ||
+        (rc = set_smem(bwd_head<0, false>, bytes)) || (rc = set_smem(bwd_head<1, false>, bytes)) ||
+        (rc = set_smem(bwd_head<0, true>, bytes)) || (rc = set_smem(bwd_head<1, true>, bytes)) ||
+        (rc = set_smem(bwd_embed_enc, bytes)) || (rc = set_smem(bwd_embed_dec, bytes)))
         return rc;
+// launch the instantiation with / without in-kernel weight-gradient accumulators
+#define BWD_LAUNCH(KERNEL, GRID, BYTES, ...)                                              \
+    do {                                                                                   \
+        if (tcw) KERNEL<true><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                        \
+        else KERNEL<false><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                           \
+    } while (0)
+#define BWD_LAUNCH2(KERNEL, K, GRID, BYTES, ...)                                          \
+    do {                                                                                   \
+        if (tcw) KERNEL<K, true><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                     \
+        else KERNEL<K, false><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                        \
+    } while (0)
     const float* pk = b.w;
     using namespace lay;
     auto idx = [](int blob) { return (blob - ENC_BLOBS) / BLOB; };
     CUDA_TRY(cudaMemsetAsync(t.gRep, 0, (size_t)n_tok * 64 * sizeof(float), st));
+    // Weight gradients: with the tensor-core path the fused kernels hand their layer-output gradients to
+    // bwd_dw_tc.cu through the three scratch buffers t.gS (consumed by the launch that follows each kernel).
+    auto job = [](const float* dY, const float* X, int recipe, int ln, int gW) {
+        DwJob j; j.dY = dY; j.X = X; j.recipe = recipe; j.ln = ln; j.gW = gW; return j;
+    };
+    auto dw = [&](const DwJob* js, int n) -> int {
+        if (!tcw) return MATAS_OK;
+        DwJobs J; J.n = n;
+        for (int i = 0; i < n; ++i) J.j[i] = js[i];
+        return launch_bwd_dw(pk, grad, J, n_tok, n_sm, st);
+    };
 
     // ---- decoder ---------------------------------------------------------------------------------
     {
@@ -819,7 +855,10 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         h.gW0 = gm.w[idx(DEC_H0)]; h.gb0 = gm.b[idx(DEC_H0)]; h.glnw = gm.lnw[idx(DEC_H0)]; h.glnb = gm.lnb[idx(DEC_H0)];
         h.gW3 = gm.dec_h3_w; h.gb3 = gm.dec_h3_b; h.glogstd = gm.log_std;
         h.gOut = t.gX; h.L = L; h.n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
-        bwd_head<1><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
+        h.sY = tcw ? t.gS[0] : nullptr;
+        BWD_LAUNCH2(bwd_head, 1, grid, bytes, pk, grad, h, n_tok);
+        const DwJob js[1] = {job(t.gS[0], t.d_xh3[1], DW_X_AFFINE, dec_blob(1, DM2), h.gW0)};
+        if ((rc = dw(js, 1))) return rc;
     }
     for (int k = 1; k >= 0; --k) {
         TailArgs ta = {};
@@ -832,7 +871,13 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(dec_blob(k, DM2))]; ta.glnFb = gm.lnb[idx(dec_blob(k, DM2))];
         ta.glnMw = gm.lnw[idx(dec_blob(k, DP2))]; ta.glnMb = gm.lnb[idx(dec_blob(k, DP2))];
         ta.gRes = t.gRep; ta.res_add = 1; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok);
+        if (tcw) { ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2]; }
+        BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
+        {
+            const DwJob js[3] = {job(t.gS[0], t.d_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.d_xh2[k], DW_X_AFFINE, dec_blob(k, DP2), ta.gW0),
+                                 job(t.gS[2], t.d_y2[k], DW_X_PLAIN, 0, ta.gWp)};
+            if ((rc = dw(js, 3))) return rc;
+        }
 
         AttnArgs a2 = {};
         a2.Q = b.Q2[k]; a2.K = b.K2[k]; a2.V = b.V2[k]; a2.lse = t.d_lse2[k]; a2.gY = t.gYa; a2.gD = t.gDa;
@@ -842,7 +887,13 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a2.gWk = gm.w[idx(dec_blob(k, DK2))]; a2.gbk = gm.b[idx(dec_blob(k, DK2))];
         a2.gWv = gm.w[idx(dec_blob(k, DV2))]; a2.gbv = gm.b[idx(dec_blob(k, DV2))];
         a2.gX = t.gX; a2.gRep = t.gRep; a2.causal = 1; a2.L = L;
-        bwd_attn<1><<<agrid, NT, abytes, st>>>(pk, grad, a2, n_tok);       // gX = grad wrt x1 (LN1 output)
+        if (tcw) { a2.sY[0] = t.gS[0]; a2.sY[1] = t.gS[1]; a2.sY[2] = t.gS[2]; }
+        BWD_LAUNCH2(bwd_attn, 1, agrid, abytes, pk, grad, a2, n_tok);       // gX = grad wrt x1 (LN1 output)
+        {
+            const DwJob js[3] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, a2.gWq), job(t.gS[1], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWk),
+                                 job(t.gS[2], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWv)};
+            if ((rc = dw(js, 3))) return rc;
+        }
 
         TailArgs tb = {};
         tb.gOut = t.gX; tb.xhM = t.d_xh1[k]; tb.rsM = t.d_rs1[k]; tb.Y = t.d_y1[k];
@@ -851,7 +902,12 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         tb.gWp = gm.w[idx(dec_blob(k, DP1))]; tb.gbp = gm.b[idx(dec_blob(k, DP1))];
         tb.glnMw = gm.lnw[idx(dec_blob(k, DP1))]; tb.glnMb = gm.lnb[idx(dec_blob(k, DP1))];
         tb.gRes = t.gX; tb.res_add = 0; tb.gY = t.gYb; tb.gD = t.gDb; tb.with_mlp = 0;
-        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, tb, n_tok);       // gX = grad wrt block input (residual part)
+        if (tcw) tb.sY[2] = t.gS[2];
+        BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, tb, n_tok);       // gX = grad wrt block input (residual part)
+        {
+            const DwJob js[1] = {job(t.gS[2], t.d_y1[k], DW_X_PLAIN, 0, tb.gWp)};
+            if ((rc = dw(js, 1))) return rc;
+        }
 
         AttnArgs a1 = {};
         a1.Q = t.d_q1[k]; a1.K = b.K1[k]; a1.V = b.V1[k]; a1.lse = t.d_lse1[k]; a1.gY = t.gYb; a1.gD = t.gDb;
@@ -862,7 +918,14 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(dec_blob(k, DK1))]; a1.gbk = gm.b[idx(dec_blob(k, DK1))];
         a1.gWv = gm.w[idx(dec_blob(k, DV1))]; a1.gbv = gm.b[idx(dec_blob(k, DV1))];
         a1.gX = t.gX; a1.causal = 1; a1.L = L;
-        bwd_attn<0><<<agrid, NT, abytes, st>>>(pk, grad, a1, n_tok);       // gX += attention path
+        if (tcw) { a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2]; }
+        BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);       // gX += attention path
+        {
+            const float* X = k == 1 ? t.d_xh3[0] : t.d_x0;
+            const int rcp = k == 1 ? DW_X_AFFINE : DW_X_PLAIN, ln = k == 1 ? dec_blob(0, DM2) : 0;
+            const DwJob js[3] = {job(t.gS[0], X, rcp, ln, a1.gWq), job(t.gS[1], X, rcp, ln, a1.gWk), job(t.gS[2], X, rcp, ln, a1.gWv)};
+            if ((rc = dw(js, 3))) return rc;
+        }
     }
     {
         EmbArgs e = {};
@@ -878,7 +941,10 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         h.gW0 = gm.w[idx(ENC_H0)]; h.gb0 = gm.b[idx(ENC_H0)]; h.glnw = gm.lnw[idx(ENC_H0)]; h.glnb = gm.lnb[idx(ENC_H0)];
         h.gW3 = gm.enc_h3_w; h.gb3 = gm.enc_h3_b; h.glogstd = -1;
         h.gOut = t.gRep; h.L = L;
-        bwd_head<0><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
+        h.sY = tcw ? t.gS[0] : nullptr;
+        BWD_LAUNCH2(bwd_head, 0, grid, bytes, pk, grad, h, n_tok);
+        const DwJob js[1] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, h.gW0)};
+        if ((rc = dw(js, 1))) return rc;
     }
     for (int k = 1; k >= 0; --k) {
         TailArgs ta = {};
@@ -891,7 +957,13 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(enc_blob(k, EM2))]; ta.glnFb = gm.lnb[idx(enc_blob(k, EM2))];
         ta.glnMw = gm.lnw[idx(enc_blob(k, EP))]; ta.glnMb = gm.lnb[idx(enc_blob(k, EP))];
         ta.gRes = t.gX; ta.res_add = 0; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        bwd_mlp_proj<<<grid, NT, bytes, st>>>(pk, grad, ta, n_tok);
+        if (tcw) { ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2]; }
+        BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
+        {
+            const DwJob js[3] = {job(t.gS[0], t.e_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.e_xh1[k], DW_X_AFFINE, enc_blob(k, EP), ta.gW0),
+                                 job(t.gS[2], t.e_y[k], DW_X_PLAIN, 0, ta.gWp)};
+            if ((rc = dw(js, 3))) return rc;
+        }
 
         AttnArgs a1 = {};
         a1.Q = t.e_q[k]; a1.K = b.K[k]; a1.V = b.V[k]; a1.lse = t.e_lse[k]; a1.gY = t.gYa; a1.gD = t.gDa;
@@ -902,7 +974,14 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(enc_blob(k, EK))]; a1.gbk = gm.b[idx(enc_blob(k, EK))];
         a1.gWv = gm.w[idx(enc_blob(k, EV))]; a1.gbv = gm.b[idx(enc_blob(k, EV))];
         a1.gX = t.gX; a1.causal = 0; a1.L = L;
-        bwd_attn<0><<<agrid, NT, abytes, st>>>(pk, grad, a1, n_tok);
+        if (tcw) { a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2]; }
+        BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);
+        {
+            const float* X = k == 1 ? t.e_xh2[0] : t.e_x0;
+            const int rcp = k == 1 ? DW_X_AFFINE : DW_X_PLAIN, ln = k == 1 ? enc_blob(0, EM2) : 0;
+            const DwJob js[3] = {job(t.gS[0], X, rcp, ln, a1.gWq), job(t.gS[1], X, rcp, ln, a1.gWk), job(t.gS[2], X, rcp, ln, a1.gWv)};
+            if ((rc = dw(js, 3))) return rc;
+        }
     }
     {
         EmbArgs e = {};

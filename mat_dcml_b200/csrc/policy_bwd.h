@@ -14,3 +14,15 @@ struct GradMap {
 int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const GradMap& gm, float* grad, const float* obs,
                              const float* actions, const float* ava, const float* d_values, const float* d_logp,
                              const float* d_ent, long M, int L, int obs_dim, int mode, int n_sm, cudaStream_t st);
+
+// ---- weight gradients on the tensor cores (bwd_dw_tc.cu) ------------------------------------------------
+enum { DW_X_PLAIN = 0, DW_X_AFFINE = 1, DW_X_GELU = 2 };     // how the layer input X is rebuilt from what the forward saved
+struct DwJob {
+    const float* dY;     // [tok][64] gradient w.r.t. the layer output (scratch written by the fused backward kernels)
+    const float* X;      // [tok][64] layer input as saved: the value itself, x_hat (AFFINE) or the pre-activation (GELU)
+    int recipe;
+    int ln;              // AFFINE: packed offset of the forward blob holding the LayerNorm weight | bias
+    int gW;              // offset of the [out][in] weight gradient in the flat gradient
+};
+struct DwJobs { DwJob j[4]; int n; };
+int launch_bwd_dw(const float* packed, float* grad, const DwJobs& jobs, long n_tok, int n_sm, cudaStream_t st);

@@ -35,6 +35,7 @@ struct TrainBufs {
     float *d_q1[2], *d_y1[2], *d_lse1[2], *d_xh1[2], *d_rs1[2];
     float *d_y2[2], *d_lse2[2], *d_xh2[2], *d_rs2[2], *d_m0[2], *d_xh3[2], *d_rs3[2];
     float *d_hh, *d_xhh, *d_rsh;                         // logits head
+    float *gS[3];                                        // backward: layer-output gradients handed to the weight-gradient kernel
     float *gX, *gRep, *gYa, *gYb, *gDa, *gDb;            // backward: residual-stream / obs_rep / attention-output grads, D [tok][2]
 };
 
