@@ -8,6 +8,7 @@
 // across tiles and are flushed with atomics once per CTA; dX = dY W streams the untransposed
 // weights through the same TMA ring as the forward.  Attention backward recomputes probabilities
 // from the saved Q/K and log-sum-exp (query side for dQ, key side for dK/dV; D = rowsum(dY*Y)).
+#include <stdlib.h>
 #include <string.h>
 
 #include "policy_bwd.h"
@@ -315,6 +316,7 @@ struct AttnArgs {
     float* gRep;                                // KIND 1: += dq.Wq
     int causal, L;
     float* sY[3];                               // non-null: write dq / dk / dv there instead of accumulating dWq / dWk / dWv here
+    int pre;                                    // dq / dk / dv were already computed into sY by attn_bwd_tile.cu: only the projections run here
 };
 
 // Sum a and b over the 8 lanes of a head (lane bit 2 = `up`) with 4 shuffles instead of 6: the two
@@ -432,14 +434,21 @@ bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a,
     for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long row0 = tile * TM;
         const int n_valid = (int)min((long)TM, n_tok - row0);
-        attn_bwd_rows<4>(a, row0, n_tok, sDq, sDv, sDk);
+        if (TCW && a.pre) {
+            load_tile(sDq, a.sY[0] + row0 * 64, 64, n_valid);
+            load_tile(sDk, a.sY[1] + row0 * 64, 64, n_valid);
+            load_tile(sDv, a.sY[2] + row0 * 64, 64, n_valid);
+        } else {
+            attn_bwd_rows<4>(a, row0, n_tok, sDq, sDv, sDk);
+        }
         // ---- projections: dW, db, dX -------------------------------------------------------------
         Frag dx;
         constexpr bool tcw = TCW;                                        // weight gradients on the tensor cores (bwd_dw_tc.cu)
+        const bool put = TCW && !a.pre;                                  // hand dq / dk / dv to the weight-gradient kernel
         if (KIND == 1) {
             if (!tcw) load_tile(sX, a.xin + row0 * 64, 64, n_valid);   // obs_rep: the query input
             __syncthreads();
-            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (tcw) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
+            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (put) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
             if (!tcw) dw_acc(dWq, sDq, sX, n_valid, rg, cg);
             gemm_dx(ring, sDq, dx, rg, cg, false);
             frag_store_g(dx, a.gRep, row0, n_valid, rg, cg, true);
@@ -459,18 +468,18 @@ bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a,
         }
         __syncthreads();
         if (KIND == 0) {
-            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (tcw) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
+            { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (put) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
             if (!tcw) dw_acc(dWq, sDq, sX, n_valid, rg, cg);
             gemm_dx(ring, sDq, dx, rg, cg, false);
             __syncthreads();
             ring.prefetch();
         }
-        { Frag f; frag_load_s(f, sDk, rg, cg); col_add(dbk, f); if (tcw) frag_store_g(f, a.sY[1], row0, n_valid, rg, cg, false); }
+        { Frag f; frag_load_s(f, sDk, rg, cg); col_add(dbk, f); if (put) frag_store_g(f, a.sY[1], row0, n_valid, rg, cg, false); }
         if (!tcw) dw_acc(dWk, sDk, sX, n_valid, rg, cg);
         gemm_dx(ring, sDk, dx, rg, cg, KIND == 0);
         __syncthreads();
         ring.prefetch();
-        { Frag f; frag_load_s(f, sDv, rg, cg); col_add(dbv, f); if (tcw) frag_store_g(f, a.sY[2], row0, n_valid, rg, cg, false); }
+        { Frag f; frag_load_s(f, sDv, rg, cg); col_add(dbv, f); if (put) frag_store_g(f, a.sY[2], row0, n_valid, rg, cg, false); }
         if (!tcw) dw_acc(dWv, sDv, sX, n_valid, rg, cg);
         gemm_dx(ring, sDv, dx, rg, cg, true);
         frag_store_g(dx, a.gX, row0, n_valid, rg, cg, KIND == 0);       // KIND 0: += ; KIND 1: =
@@ -807,6 +816,9 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
     }
     const size_t bytes = bsmem_bytes(BDEPTH), abytes = bsmem_bytes(ADEPTH);
     const bool tcw = policy_use_tc();               // weight gradients on the tensor cores (bwd_dw_tc.cu)
+    static int tile_env = -1;                       // MATAS_ATTN_TILE=0 keeps the attention backward inside bwd_attn (A/B runs)
+    if (tile_env < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tile_env = e ? atoi(e) : 1; }
+    const bool tiled = tcw && tile_env && attn_tile_supported(L);
     const long n_tok = M * L;
     const long n_tiles = (n_tok + TM - 1) / TM;
     const unsigned grid = (unsigned)(n_tiles < n_sm ? n_tiles : n_sm);
@@ -888,6 +900,10 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a2.gWv = gm.w[idx(dec_blob(k, DV2))]; a2.gbv = gm.b[idx(dec_blob(k, DV2))];
         a2.gX = t.gX; a2.gRep = t.gRep; a2.causal = 1; a2.L = L;
         if (tcw) { a2.sY[0] = t.gS[0]; a2.sY[1] = t.gS[1]; a2.sY[2] = t.gS[2]; }
+        if (tiled) {
+            if ((rc = launch_attn_bwd_tile(a2.Q, a2.K, a2.V, a2.gY, a2.lse, a2.gD, t.gS[0], t.gS[1], t.gS[2], M, L, 1, st))) return rc;
+            a2.pre = 1;
+        }
         BWD_LAUNCH2(bwd_attn, 1, agrid, abytes, pk, grad, a2, n_tok);       // gX = grad wrt x1 (LN1 output)
         {
             const DwJob js[3] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, a2.gWq), job(t.gS[1], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWk),
@@ -919,6 +935,10 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWv = gm.w[idx(dec_blob(k, DV1))]; a1.gbv = gm.b[idx(dec_blob(k, DV1))];
         a1.gX = t.gX; a1.causal = 1; a1.L = L;
         if (tcw) { a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2]; }
+        if (tiled) {
+            if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
+            a1.pre = 1;
+        }
         BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);       // gX += attention path
         {
             const float* X = k == 1 ? t.d_xh3[0] : t.d_x0;
@@ -975,6 +995,10 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWv = gm.w[idx(enc_blob(k, EV))]; a1.gbv = gm.b[idx(enc_blob(k, EV))];
         a1.gX = t.gX; a1.causal = 0; a1.L = L;
         if (tcw) { a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2]; }
+        if (tiled) {
+            if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
+            a1.pre = 1;
+        }
         BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);
         {
             const float* X = k == 1 ? t.e_xh2[0] : t.e_x0;

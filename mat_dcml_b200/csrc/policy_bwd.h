@@ -26,3 +26,7 @@ struct DwJob {
 };
 struct DwJobs { DwJob j[4]; int n; };
 int launch_bwd_dw(const float* packed, float* grad, const DwJobs& jobs, long n_tok, int n_sm, cudaStream_t st);
+
+// register-tiled per-env attention backward (attn_bwd_tile.cu), n_agent <= 64
+int launch_attn_bwd_tile(const float* Q, const float* K, const float* V, const float* gY, const float* lse, const float* D, float* dQ,
+                         float* dK, float* dV, long n_env, int L, int causal, cudaStream_t st);
