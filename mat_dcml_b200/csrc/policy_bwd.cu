@@ -819,6 +819,17 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
     static int tile_env = -1;                       // MATAS_ATTN_TILE=0 keeps the attention backward inside bwd_attn (A/B runs)
     if (tile_env < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tile_env = e ? atoi(e) : 1; }
     const bool tiled = tcw && tile_env && attn_tile_supported(L);
+    static int dx_env = -1;                         // MATAS_DX_TC=0: q/k/v input gradients stay in bwd_attn's SIMT GEMMs (A/B runs)
+    if (dx_env < 0) { const char* e = getenv("MATAS_DX_TC"); dx_env = e ? atoi(e) : 1; }
+    const bool dxtc = tiled && dx_env;
+    auto dx = [&](int kind, int bq, int bk, int bv, int gbq, int gbk, int gbv) -> int {
+        DxArgs d;
+        d.dq = t.gS[0]; d.dk = t.gS[1]; d.dv = t.gS[2];
+        d.blob[0] = bq; d.blob[1] = bk; d.blob[2] = bv;
+        d.gb[0] = gbq; d.gb[1] = gbk; d.gb[2] = gbv;
+        d.gX = t.gX; d.gRep = t.gRep;
+        return launch_bwd_qkv_dx(b.w, grad, d, M * L, kind, n_sm, st);
+    };
     const long n_tok = M * L;
     const long n_tiles = (n_tok + TM - 1) / TM;
     const unsigned grid = (unsigned)(n_tiles < n_sm ? n_tiles : n_sm);
@@ -904,7 +915,11 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
             if ((rc = launch_attn_bwd_tile(a2.Q, a2.K, a2.V, a2.gY, a2.lse, a2.gD, t.gS[0], t.gS[1], t.gS[2], M, L, 1, st))) return rc;
             a2.pre = 1;
         }
-        BWD_LAUNCH2(bwd_attn, 1, agrid, abytes, pk, grad, a2, n_tok);       // gX = grad wrt x1 (LN1 output)
+        if (dxtc) {
+            if ((rc = dx(1, dec_q2(k), dec_blob(k, DK2), dec_blob(k, DV2), a2.gbq, a2.gbk, a2.gbv))) return rc;
+        } else {
+            BWD_LAUNCH2(bwd_attn, 1, agrid, abytes, pk, grad, a2, n_tok);   // gX = grad wrt x1 (LN1 output)
+        }
         {
             const DwJob js[3] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, a2.gWq), job(t.gS[1], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWk),
                                  job(t.gS[2], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWv)};
@@ -939,7 +954,11 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
             if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
             a1.pre = 1;
         }
-        BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);       // gX += attention path
+        if (dxtc) {
+            if ((rc = dx(0, dec_blob(k, DQ1), dec_blob(k, DK1), dec_blob(k, DV1), a1.gbq, a1.gbk, a1.gbv))) return rc;
+        } else {
+            BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);   // gX += attention path
+        }
         {
             const float* X = k == 1 ? t.d_xh3[0] : t.d_x0;
             const int rcp = k == 1 ? DW_X_AFFINE : DW_X_PLAIN, ln = k == 1 ? dec_blob(0, DM2) : 0;
@@ -999,7 +1018,11 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
             if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
             a1.pre = 1;
         }
-        BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);
+        if (dxtc) {
+            if ((rc = dx(0, enc_blob(k, EQ), enc_blob(k, EK), enc_blob(k, EV), a1.gbq, a1.gbk, a1.gbv))) return rc;
+        } else {
+            BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);
+        }
         {
             const float* X = k == 1 ? t.e_xh2[0] : t.e_x0;
             const int rcp = k == 1 ? DW_X_AFFINE : DW_X_PLAIN, ln = k == 1 ? enc_blob(0, EM2) : 0;

@@ -30,3 +30,13 @@ int launch_bwd_dw(const float* packed, float* grad, const DwJobs& jobs, long n_t
 // register-tiled per-env attention backward (attn_bwd_tile.cu), n_agent <= 64
 int launch_attn_bwd_tile(const float* Q, const float* K, const float* V, const float* gY, const float* lse, const float* D, float* dQ,
                          float* dK, float* dV, long n_env, int L, int causal, cudaStream_t st);
+
+// input gradient of the q / k / v projections + their bias gradients on the tensor cores (bwd_dx_tc.cu)
+struct DxArgs {
+    const float *dq, *dk, *dv;   // [tok][64] from attn_bwd_tile.cu
+    int blob[3];                 // forward blob offsets (layout.h) of the q / k / v Linear layers
+    int gb[3];                   // bias-gradient offsets in the flat gradient
+    float* gX;                   // kind 0: += dq.Wq + dk.Wk + dv.Wv ; kind 1: = dk.Wk + dv.Wv
+    float* gRep;                 // kind 1: += dq.Wq
+};
+int launch_bwd_qkv_dx(const float* packed, float* grad, const DxArgs& a, long n_tok, int kind, int n_sm, cudaStream_t st);
