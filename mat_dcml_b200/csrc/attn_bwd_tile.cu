@@ -9,12 +9,14 @@
 // with the saved log-sum-exp and D = rowsum(dY * Y) of the forward / projection backward.  Several envs share a
 // CTA when they are short, so that the 4 x 4 tasks fill the threads.  dQ / dK / dV go to token-major global
 // buffers: the projection backward (policy_bwd.cu) and the weight-gradient kernel (bwd_dw_tc.cu) read them there.
+#include <stdlib.h>
+
 #include "policy_bwd.h"
 #include "tile.cuh"
 
 namespace {
 
-constexpr int BNT = 128;     // threads per CTA
+constexpr int BNT = 128;     // maximum threads per CTA (the launch may use fewer: loops stride by blockDim.x)
 constexpr int RS = 68;       // row stride of the Q / K / V / dY tiles (floats)
 constexpr float SCALE = 0.17677669529663687f;
 constexpr float LOG2E = 1.4426950408889634f;
@@ -38,7 +40,7 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
     const BGeom g = bgeom(L);
     const int Lp = g.Lp, nb = g.nb, SS = g.SS;
     const size_t EF = g.env_floats;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, nthr = blockDim.x;
     const float c2 = SCALE * LOG2E;
     // per env slot e: sQ | sK | sV | sY [Lp][RS], sP | sdS [Lp][SS], lse2[2][Lp], D[2][Lp]
     auto slot = [&](int e) { return sm + (size_t)e * EF; };
@@ -47,7 +49,7 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
     for (long env0 = (long)blockIdx.x * E; env0 < n_env; env0 += (long)gridDim.x * E) {
         const int ne = (int)min((long)E, n_env - env0);
         // ---- stage Q, K, V, dY (rows >= L zero), lse (log2 units), D ------------------------------------------
-        for (int idx = tid; idx < ne * Lp * 16; idx += BNT) {
+        for (int idx = tid; idx < ne * Lp * 16; idx += nthr) {
             const int e = idx / (Lp * 16), rem = idx - e * Lp * 16, r = rem >> 4, c = rem & 15;
             float4 q = make_float4(0.f, 0.f, 0.f, 0.f), k = q, v = q, y = q;
             if (r < L) {
@@ -61,7 +63,7 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
             *reinterpret_cast<float4*>(s + oV + r * RS + c * 4) = v;
             *reinterpret_cast<float4*>(s + oY + r * RS + c * 4) = y;
         }
-        for (int idx = tid; idx < ne * 2 * Lp; idx += BNT) {
+        for (int idx = tid; idx < ne * 2 * Lp; idx += nthr) {
             const int e = idx / (2 * Lp), rem = idx - e * 2 * Lp, h = rem / Lp, r = rem - h * Lp;
             const long t = (env0 + e) * L + r;
             slot(e)[oL + rem] = r < L ? __ldg(lse + t * 2 + h) * LOG2E : 0.f;
@@ -70,7 +72,7 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
         __syncthreads();
         for (int h = 0; h < 2; ++h) {
             // ---- phase 1: P and dS blocks (queries {qb + nb i} x keys {kb + nb j}) ---------------------------------
-            for (int task = tid; task < ne * nb * nb; task += BNT) {
+            for (int task = tid; task < ne * nb * nb; task += nthr) {
                 const int e = task / (nb * nb), rem = task - e * nb * nb, qb = rem / nb, kb = rem - qb * nb;
                 const float* s = slot(e);
                 float as[4][4], ap[4][4];
@@ -120,7 +122,7 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
             }
             __syncthreads();
             // ---- phase 2: dQ / dK / dV blocks of 4 rows x 4 dims -----------------------------------------------------
-            for (int task = tid; task < ne * 3 * nb * 8; task += BNT) {
+            for (int task = tid; task < ne * 3 * nb * 8; task += nthr) {
                 const int e = task / (3 * nb * 8), rem = task - e * 3 * nb * 8, kind = rem / (nb * 8), r2 = rem - kind * nb * 8;
                 const int rb = r2 >> 3, db = r2 & 7;
                 const float* s = slot(e);
@@ -177,7 +179,14 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
 int launch_attn_bwd_tile(const float* Q, const float* K, const float* V, const float* gY, const float* lse, const float* D, float* dQ,
                          float* dK, float* dV, long n_env, int L, int causal, cudaStream_t st) {
     const BGeom g = bgeom(L);
-    int E = BNT / (g.nb * g.nb);                        // envs per CTA: keep the 4 x 4 phase-1 tasks close to the thread count
+    static int e_env = -1, t_env = -1;                  // tuning overrides: MATAS_ABT_E (envs per CTA), MATAS_ABT_THREADS
+    if (e_env < 0) { const char* e = getenv("MATAS_ABT_E"); e_env = e ? atoi(e) : 0; }
+    if (t_env < 0) { const char* e = getenv("MATAS_ABT_THREADS"); t_env = e ? atoi(e) : 0; }
+    // measured on B200 (12800 x 21 / 4096 x 51): small CTAs with one env each beat packing several envs into a
+    // CTA (more resident CTAs hide the shared-memory latency): 64 threads up to 64 phase-1 tasks, else 128
+    const int tasks = g.nb * g.nb;
+    const int nthr = t_env ? t_env : (tasks > 64 ? BNT : 64);
+    int E = e_env ? e_env : (tasks >= 32 ? 1 : 32 / tasks);
     if (E < 1) E = 1;
     if (E > 4) E = 4;
     const size_t bytes = (size_t)E * g.env_floats * sizeof(float);
@@ -185,10 +194,10 @@ int launch_attn_bwd_tile(const float* Q, const float* K, const float* V, const f
     const unsigned grid = (unsigned)(groups < (1L << 20) ? groups : (1L << 20));
     if (causal) {
         CUDA_TRY(cudaFuncSetAttribute(attn_bwd_env_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        attn_bwd_env_kernel<true><<<grid, BNT, bytes, st>>>(Q, K, V, gY, lse, D, dQ, dK, dV, n_env, L, E);
+        attn_bwd_env_kernel<true><<<grid, nthr, bytes, st>>>(Q, K, V, gY, lse, D, dQ, dK, dV, n_env, L, E);
     } else {
         CUDA_TRY(cudaFuncSetAttribute(attn_bwd_env_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        attn_bwd_env_kernel<false><<<grid, BNT, bytes, st>>>(Q, K, V, gY, lse, D, dQ, dK, dV, n_env, L, E);
+        attn_bwd_env_kernel<false><<<grid, nthr, bytes, st>>>(Q, K, V, gY, lse, D, dQ, dK, dV, n_env, L, E);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;

@@ -9,12 +9,14 @@
 // (tile::attention_rows), which spends most of its issue slots on shuffle reductions and per-key softmax updates.
 // The output Y [tok][64] (and, in training mode, the natural-log log-sum-exp [tok][2]) goes to global memory and
 // is picked up by the tensor-core block kernel as its first GEMM operand.
+#include <stdlib.h>
+
 #include "policy_fwd.h"
 #include "tile.cuh"
 
 namespace {
 
-constexpr int ANT = 128;     // threads per CTA
+constexpr int ANT = 128;     // maximum threads per CTA (loops stride by blockDim.x)
 constexpr int RS = 68;       // row stride of the Q / K / V tiles (floats): 16-byte aligned rows, 4-bank skew
 
 struct AttnGeom { int Lp, nb, SS, PS; size_t floats; };
@@ -42,12 +44,12 @@ attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const 
     float* sPT = sm;                                          // aliases sQ / sK once the scores are done
     float* sV = sm + (qk > pt ? qk : pt);
     float* sS = sV + (size_t)Lp * RS;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, nthr = blockDim.x;
     const float scale = 0.17677669529663687f * 1.4426950408889634f;     // log2(e)/sqrt(32): exp2-domain scores
     for (long env = blockIdx.x; env < n_env; env += gridDim.x) {
         const long tok0 = env * L;
         // ---- stage Q, K, V (rows >= L zero) ---------------------------------------------------------------
-        for (int idx = tid; idx < Lp * 16; idx += ANT) {
+        for (int idx = tid; idx < Lp * 16; idx += nthr) {
             const int r = idx >> 4, c = idx & 15;
             float4 q = make_float4(0.f, 0.f, 0.f, 0.f), k = q, v = q;
             if (r < L) {
@@ -61,7 +63,7 @@ attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const 
         }
         __syncthreads();
         // ---- S = scale * Q K^T: thread block = queries {qb + nb*i} x keys {kb + nb*j} of head h ----------------
-        for (int task = tid; task < 2 * nb * nb; task += ANT) {
+        for (int task = tid; task < 2 * nb * nb; task += nthr) {
             const int h = task / (nb * nb), rem = task - h * nb * nb, qb = rem / nb, kb = rem - qb * nb;
             float acc[4][4];
 #pragma unroll
@@ -96,9 +98,9 @@ attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const 
         {
             const int grp = tid >> 2, l4 = tid & 3;
             const unsigned gmask = 0xfu << (tid & 28);
-            const int n_it = (2 * L + ANT / 4 - 1) / (ANT / 4);
+            const int n_it = (2 * L + nthr / 4 - 1) / (nthr / 4);
             for (int it = 0; it < n_it; ++it) {
-                const int rt = it * (ANT / 4) + grp;
+                const int rt = it * (nthr / 4) + grp;
                 const bool on = rt < 2 * L;
                 const int h = on ? rt / L : 0, qi = on ? rt - h * L : 0;
                 const int nk = CAUSAL ? qi + 1 : L;
@@ -121,7 +123,7 @@ attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const 
         }
         __syncthreads();
         // ---- Y = P V: thread block = queries 4qb..4qb+3 x dims 4db..4db+3 of head h -------------------------------
-        for (int task = tid; task < 2 * nb * 8; task += ANT) {
+        for (int task = tid; task < 2 * nb * 8; task += nthr) {
             const int h = task / (nb * 8), rem = task - h * nb * 8, qb = rem >> 3, db = rem & 7;
             float acc[4][4];
 #pragma unroll
@@ -162,12 +164,15 @@ int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, f
     const AttnGeom g = attn_geom(L);
     const size_t bytes = g.floats * sizeof(float);
     const unsigned grid = (unsigned)(n_env < (1L << 30) ? n_env : (1L << 30));
+    static int t_env = -1;                              // tuning override: MATAS_AT_THREADS
+    if (t_env < 0) { const char* e = getenv("MATAS_AT_THREADS"); t_env = e ? atoi(e) : 0; }
+    const int nthr = t_env ? t_env : ANT;
     if (causal) {
         CUDA_TRY(cudaFuncSetAttribute(attn_env_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        attn_env_kernel<true><<<grid, ANT, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
+        attn_env_kernel<true><<<grid, nthr, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
     } else {
         CUDA_TRY(cudaFuncSetAttribute(attn_env_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        attn_env_kernel<false><<<grid, ANT, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
+        attn_env_kernel<false><<<grid, nthr, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
