@@ -214,17 +214,6 @@ __device__ __forceinline__ void proj_bwd(Ring& ring, const BSmem& s, const Frag&
     ring.prefetch();
 }
 
-struct TailArgs {
-    const float* gOut;     // grad wrt the block output
-    const float *xhF, *rsF, *m0, *xhM, *rsM, *Y;
-    int lnF, lnM;          // packed offsets of the forward blobs that hold these LayerNorm params
-    int seq[3];            // backward weight offsets: W2, W0, Wp   (with_mlp) or Wp only
-    int gW2, gb2, gW0, gb0, gWp, gbp, glnFw, glnFb, glnMw, glnMb;   // flat-gradient offsets
-    float* gRes; int res_add;
-    float *gY, *gD;
-    int with_mlp;
-    float* sY[3];          // non-null: write dS / dM0 / d(proj out) there instead of accumulating dW2 / dW0 / dWp here
-};
 
 // [LN_F bwd -> MLP bwd ->] LN_M bwd -> residual grad -> projection bwd      (encoder E1, decoder K1 / K2b)
 template <bool TCW>       // TCW: weight gradients on the tensor cores (bwd_dw_tc.cu): no dW accumulators here
@@ -822,6 +811,9 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
     static int dx_env = -1;                         // MATAS_DX_TC=0: q/k/v input gradients stay in bwd_attn's SIMT GEMMs (A/B runs)
     if (dx_env < 0) { const char* e = getenv("MATAS_DX_TC"); dx_env = e ? atoi(e) : 1; }
     const bool dxtc = tiled && dx_env;
+    static int mlp_env = -1;                        // MATAS_MLP_TC=0: block tails stay on bwd_mlp_proj's SIMT GEMMs (A/B runs)
+    if (mlp_env < 0) { const char* e = getenv("MATAS_MLP_TC"); mlp_env = e ? atoi(e) : 1; }
+    const bool mlptc = tcw && mlp_env;
     auto dx = [&](int kind, int bq, int bk, int bv, int gbq, int gbk, int gbv) -> int {
         DxArgs d;
         d.dq = t.gS[0]; d.dk = t.gS[1]; d.dv = t.gS[2];
@@ -888,6 +880,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.gOut = t.gX; ta.xhF = t.d_xh3[k]; ta.rsF = t.d_rs3[k]; ta.m0 = t.d_m0[k]; ta.xhM = t.d_xh2[k]; ta.rsM = t.d_rs2[k];
         ta.Y = t.d_y2[k]; ta.lnF = dec_blob(k, DM2); ta.lnM = dec_blob(k, DP2);
         ta.seq[0] = bw(dec_blob(k, DM2)); ta.seq[1] = bw(dec_blob(k, DM0)); ta.seq[2] = bw(dec_blob(k, DP2));
+        ta.fW0 = dec_blob(k, DM0);
         ta.gW2 = gm.w[idx(dec_blob(k, DM2))]; ta.gb2 = gm.b[idx(dec_blob(k, DM2))];
         ta.gW0 = gm.w[idx(dec_blob(k, DM0))]; ta.gb0 = gm.b[idx(dec_blob(k, DM0))];
         ta.gWp = gm.w[idx(dec_blob(k, DP2))]; ta.gbp = gm.b[idx(dec_blob(k, DP2))];
@@ -895,7 +888,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnMw = gm.lnw[idx(dec_blob(k, DP2))]; ta.glnMb = gm.lnb[idx(dec_blob(k, DP2))];
         ta.gRes = t.gRep; ta.res_add = 1; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
         if (tcw) { ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2]; }
-        BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
+        if (mlptc) { if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc; }
+        else BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
         {
             const DwJob js[3] = {job(t.gS[0], t.d_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.d_xh2[k], DW_X_AFFINE, dec_blob(k, DP2), ta.gW0),
                                  job(t.gS[2], t.d_y2[k], DW_X_PLAIN, 0, ta.gWp)};
@@ -934,7 +928,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         tb.glnMw = gm.lnw[idx(dec_blob(k, DP1))]; tb.glnMb = gm.lnb[idx(dec_blob(k, DP1))];
         tb.gRes = t.gX; tb.res_add = 0; tb.gY = t.gYb; tb.gD = t.gDb; tb.with_mlp = 0;
         if (tcw) tb.sY[2] = t.gS[2];
-        BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, tb, n_tok);       // gX = grad wrt block input (residual part)
+        if (mlptc) { if ((rc = launch_bwd_mlp_tc(pk, grad, tb, n_tok, n_sm, st))) return rc; }
+        else BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, tb, n_tok);       // gX = grad wrt block input (residual part)
         {
             const DwJob js[1] = {job(t.gS[2], t.d_y1[k], DW_X_PLAIN, 0, tb.gWp)};
             if ((rc = dw(js, 1))) return rc;
@@ -990,6 +985,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.gOut = k == 1 ? t.gRep : t.gX; ta.xhF = t.e_xh2[k]; ta.rsF = t.e_rs2[k]; ta.m0 = t.e_m0[k];
         ta.xhM = t.e_xh1[k]; ta.rsM = t.e_rs1[k]; ta.Y = t.e_y[k]; ta.lnF = enc_blob(k, EM2); ta.lnM = enc_blob(k, EP);
         ta.seq[0] = bw(enc_blob(k, EM2)); ta.seq[1] = bw(enc_blob(k, EM0)); ta.seq[2] = bw(enc_blob(k, EP));
+        ta.fW0 = enc_blob(k, EM0);
         ta.gW2 = gm.w[idx(enc_blob(k, EM2))]; ta.gb2 = gm.b[idx(enc_blob(k, EM2))];
         ta.gW0 = gm.w[idx(enc_blob(k, EM0))]; ta.gb0 = gm.b[idx(enc_blob(k, EM0))];
         ta.gWp = gm.w[idx(enc_blob(k, EP))]; ta.gbp = gm.b[idx(enc_blob(k, EP))];
@@ -997,7 +993,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnMw = gm.lnw[idx(enc_blob(k, EP))]; ta.glnMb = gm.lnb[idx(enc_blob(k, EP))];
         ta.gRes = t.gX; ta.res_add = 0; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
         if (tcw) { ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2]; }
-        BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
+        if (mlptc) { if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc; }
+        else BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
         {
             const DwJob js[3] = {job(t.gS[0], t.e_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.e_xh1[k], DW_X_AFFINE, enc_blob(k, EP), ta.gW0),
                                  job(t.gS[2], t.e_y[k], DW_X_PLAIN, 0, ta.gWp)};

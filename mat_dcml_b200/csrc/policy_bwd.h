@@ -40,3 +40,20 @@ struct DxArgs {
     float* gRep;                 // kind 1: += dq.Wq
 };
 int launch_bwd_qkv_dx(const float* packed, float* grad, const DxArgs& a, long n_tok, int kind, int n_sm, cudaStream_t st);
+
+// [LN_F bwd -> MLP bwd ->] LN_M bwd -> residual grad -> projection bwd (encoder block tail, decoder block halves)
+struct TailArgs {
+    const float* gOut;     // grad wrt the block output
+    const float *xhF, *rsF, *m0, *xhM, *rsM, *Y;
+    int lnF, lnM;          // packed offsets of the forward blobs that hold these LayerNorm params
+    int seq[3];            // backward weight offsets: W2, W0, Wp   (with_mlp) or Wp only
+    int gW2, gb2, gW0, gb0, gWp, gbp, glnFw, glnFb, glnMw, glnMb;   // flat-gradient offsets
+    float* gRes; int res_add;
+    float *gY, *gD;
+    int with_mlp;
+    int fW0;               // forward blob offset of mlp.0 (mlp.2 and proj share lnF / lnM)
+    float* sY[3];          // non-null: write dS / dM0 / d(proj out) there instead of accumulating dW2 / dW0 / dWp here
+};
+
+// the same chain with its three dY.W products on the tensor cores (bwd_mlp_tc.cu); requires a.sY
+int launch_bwd_mlp_tc(const float* packed, float* grad, const TailArgs& a, long n_tok, int n_sm, cudaStream_t st);
