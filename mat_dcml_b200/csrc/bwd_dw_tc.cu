@@ -12,6 +12,8 @@
 // 64-feature atom of the A operand (reached through the descriptor's leading byte offset) is a block of zeros.
 // X is rebuilt from what the forward saved: as stored, x_hat * ln_w + ln_b, or GELU(pre-activation).
 // (scripts/tc/tc_test_dw.cu validated the accumulate-across-chunks scheme with transposed K-major operands.)
+#include <stdlib.h>
+
 #include "policy_bwd.h"
 #include "tc.cuh"
 
@@ -19,8 +21,8 @@ using namespace tile;
 
 namespace {
 
-constexpr int TK = 128;                      // tokens per chunk
-constexpr int OP_PART = TK * 128;            // bytes of one operand part: 128 tokens x 64 features x 2 B
+constexpr int TK = 64;                       // tokens per chunk (40 KB of operands: four CTAs per SM)
+constexpr int OP_PART = TK * 128;            // bytes of one operand part: TK tokens x 64 features x 2 B
 constexpr int A_BYTES = 3 * OP_PART;         // [hi][lo][zeros: the second 64-feature atom of both parts]
 constexpr int B_BYTES = 2 * OP_PART;         // [hi][lo]
 constexpr size_t DW_SMEM = 1024 + A_BYTES + B_BYTES + 2 * 64 * sizeof(float) + 64;
@@ -36,7 +38,7 @@ __device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr, uint32_t lbo_by
     return d;
 }
 
-__global__ void __launch_bounds__(NT, 2)
+__global__ void __launch_bounds__(NT, 4)
 bwd_dw_kernel(const float* __restrict__ packed, float* __restrict__ grad, DwJobs jobs, long n_tok, int splits) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -53,7 +55,6 @@ bwd_dw_kernel(const float* __restrict__ packed, float* __restrict__ grad, DwJobs
     if (c0 >= c1) return;
     if (tid == 0) { mbar_init(bar, 1); mbar_fence_init(); }
     if (warp == 0) tc::tmem_alloc_n<128>(tmem_slot);
-    static_assert(OP_PART == tc::A_PART, "store_operand32 puts the lo part at + tc::A_PART");
     for (int i = tid; i < (A_BYTES + B_BYTES) / 16; i += NT) reinterpret_cast<uint4*>(base)[i] = make_uint4(0u, 0u, 0u, 0u);
     if (job.recipe == DW_X_AFFINE && tid < 128) sLn[tid] = packed[job.ln + lay::B_LNW + tid];
     tc::fence_before_sync();
@@ -66,31 +67,32 @@ bwd_dw_kernel(const float* __restrict__ packed, float* __restrict__ grad, DwJobs
     if (job.recipe == DW_X_AFFINE) { lw = *reinterpret_cast<const float4*>(sLn + l * 4); lb = *reinterpret_cast<const float4*>(sLn + 64 + l * 4); }
     uint32_t phase = 0;
     for (long c = c0; c < c1; ++c) {
-        float4 a4[8], x4[8];
+        constexpr int NIT = TK / 16;
+        float4 a4[NIT], x4[NIT];
 #pragma unroll
-        for (int it = 0; it < 8; ++it) {               // coalesced: 256 bytes per half-warp and row
+        for (int it = 0; it < NIT; ++it) {             // coalesced: 256 bytes per half-warp and row
             const long g = c * TK + it * 16 + hw;
             const bool ok = g < n_tok;
             a4[it] = ok ? __ldg(reinterpret_cast<const float4*>(job.dY + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
             x4[it] = ok ? __ldg(reinterpret_cast<const float4*>(job.X + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
-        for (int it = 0; it < 8; ++it) {
+        for (int it = 0; it < NIT; ++it) {
             float4 x = x4[it];
             if (job.recipe == DW_X_AFFINE) {
                 x.x = fmaf(x.x, lw.x, lb.x); x.y = fmaf(x.y, lw.y, lb.y); x.z = fmaf(x.z, lw.z, lb.z); x.w = fmaf(x.w, lw.w, lb.w);
             } else if (job.recipe == DW_X_GELU) {
                 x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
             }
-            tc::store_operand4(sA, it * 16 + hw, l, a4[it]);        // hi at +0, lo at + tc::A_PART (= OP_PART)
-            tc::store_operand4(sB, it * 16 + hw, l, x);             // rows past n_tok: dY = 0, so X does not matter
+            tc::store_operand4(sA, it * 16 + hw, l, a4[it], OP_PART);   // hi at +0, lo at + OP_PART
+            tc::store_operand4(sB, it * 16 + hw, l, x, OP_PART);        // rows past n_tok: dY = 0, so X does not matter
         }
         tc::publish();
         if (tid == 0) {
             const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
             const uint32_t first = c == c0 ? 0u : 1u;
 #pragma unroll
-            for (int ks = 0; ks < 8; ++ks) {          // 8 K-steps of 16 tokens = two 8-token atoms = 2048 bytes
+            for (int ks = 0; ks < TK / 16; ++ks) {    // K-steps of 16 tokens = two 8-token atoms = 2048 bytes
                 const uint32_t ko = ks * 2048;
                 const uint32_t acc = (first || ks > 0) ? 1u : 0u;
                 const uint64_t ah = make_desc_mn(a0 + ko, 2 * OP_PART - ko), al = make_desc_mn(a0 + OP_PART + ko, OP_PART - ko);   // LBO -> the zero block
@@ -128,7 +130,9 @@ int launch_bwd_dw(const float* packed, float* grad, const DwJobs& jobs, long n_t
     if (jobs.n <= 0) return MATAS_OK;
     CUDA_TRY(cudaFuncSetAttribute(bwd_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM));
     const long n_chunks = (n_tok + TK - 1) / TK;
-    long splits = (2L * n_sm + jobs.n - 1) / jobs.n;           // two resident CTAs per SM, all jobs in one wave
+    static int per_sm = -1;                                     // CTAs per SM over all jobs of a launch (MATAS_DW_PER_SM)
+    if (per_sm < 0) { const char* e = getenv("MATAS_DW_PER_SM"); per_sm = e ? atoi(e) : 2; }     // measured: 2 beats 1 (parallelism) and 4 (twice the atomics)
+    long splits = ((long)per_sm * n_sm + jobs.n - 1) / jobs.n;
     if (splits > n_chunks) splits = n_chunks;
     if (splits < 1) splits = 1;
     bwd_dw_kernel<<<(unsigned)(jobs.n * splits), NT, DW_SMEM, st>>>(packed, grad, jobs, n_tok, (int)splits);

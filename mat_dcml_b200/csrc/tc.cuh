@@ -215,13 +215,13 @@ __device__ __forceinline__ void store_operand32(unsigned char* sA, int row, int 
     }
 }
 // 4 consecutive columns [4*l, 4*l + 4) of row `row` (the half-warp-per-row layout of the attention)
-__device__ __forceinline__ void store_operand4(unsigned char* sA, int row, int l, const float4& v) {
+__device__ __forceinline__ void store_operand4(unsigned char* sA, int row, int l, const float4& v, int lo_off = A_PART) {
     __half2 h0, h1, l0, l1;
     split2(v.x, v.y, h0, l0);
     split2(v.z, v.w, h1, l1);
     const uint32_t off = row * 128 + ((((l >> 1) ^ (row & 7)) << 4) | ((l & 1) << 3));
     *reinterpret_cast<uint2*>(sA + off) = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
-    *reinterpret_cast<uint2*>(sA + A_PART + off) = make_uint2(*reinterpret_cast<uint32_t*>(&l0), *reinterpret_cast<uint32_t*>(&l1));
+    *reinterpret_cast<uint2*>(sA + lo_off + off) = make_uint2(*reinterpret_cast<uint32_t*>(&l0), *reinterpret_cast<uint32_t*>(&l1));
 }
 
 // ---- fp32 tile helpers (thread-per-row side) --------------------------------------------------------------
