@@ -143,15 +143,21 @@ class MATTrainer:
 
     def train(self, buffer):
         """mat_trainer.py:158-217"""
-        info = dict(value_loss=0.0, policy_loss=0.0, dist_entropy=0.0, actor_grad_norm=0.0, critic_grad_norm=0.0, ratio=0.0)
+        # the statistics are accumulated on the device and read back once: a .item() per minibatch (as in the
+        # reference, mat_trainer.py:199-205) would stall the host after every update
+        acc = torch.zeros(6, dtype=torch.float64, device=self.device)
         for _ in range(self.ppo_epoch):
             next_values = self.policy.get_values(None, buffer.obs[-1].reshape(-1, buffer.obs.shape[-1]), None, None)
             buffer.compute_returns(next_values.reshape(buffer.value_preds[-1].shape), self.value_normalizer)
             advantages = self.normalize_advantages(buffer.advantages, buffer.active_masks[:-1])
             for sample in buffer.feed_forward_generator_transformer(advantages, self.num_mini_batch):
                 vl, cgn, pl, ent, agn, ratio = self.ppo_update(sample)
-                info["value_loss"] += vl.item(); info["policy_loss"] += pl.item(); info["dist_entropy"] += ent.item()
-                info["actor_grad_norm"] += float(agn); info["critic_grad_norm"] += float(cgn); info["ratio"] += ratio.mean().item()
+                with torch.no_grad():
+                    acc += torch.stack([vl.detach().double(), pl.detach().double(), ent.detach().double(),
+                                        torch.as_tensor(agn, device=self.device).double(), torch.as_tensor(cgn, device=self.device).double(),
+                                        ratio.detach().mean().double()])
+        keys = ("value_loss", "policy_loss", "dist_entropy", "actor_grad_norm", "critic_grad_norm", "ratio")
+        info = dict(zip(keys, acc.tolist()))
         n = self.ppo_epoch * self.num_mini_batch
         if _world() > 1:     # each rank logged its share of the global losses (global denominators)
             t = torch.tensor([info["value_loss"], info["policy_loss"], info["dist_entropy"]], dtype=torch.float64, device=self.device)

@@ -27,4 +27,4 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); tr.train(buf); e1.record(); torch.cuda.synchronize()
 print("one train() = %d epochs x %d minibatches: %.2f ms" % (tr.ppo_epoch, tr.num_mini_batch, e0.elapsed_time(e1)))
-print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=22, max_name_column_width=60))
+print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=60))
