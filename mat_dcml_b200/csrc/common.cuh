@@ -67,6 +67,33 @@ __host__ __device__ __forceinline__ uint32_t lane_of(const uint4& v, int i) {
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
 
 // reduce over the 16 lanes of a half-warp (xor 8,4,2,1 stays inside the half)
+// Packed fp32 arithmetic (sm_100: fma.rn.f32x2 -> SASS FFMA2).  Same FLOP rate as two FFMAs but ONE issue slot
+// (measured on B200, scripts/tc/ffma2_bench.cu: 73.7 vs 72.6 TFLOP/s), which is what issue-bound loops need.
+__device__ __forceinline__ void fma2(float& dx, float& dy, float ax, float ay, float bx, float by) {     // d += a * b
+    asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+        "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rd, {%0, %1};\n\t"
+        "fma.rn.f32x2 rd, ra, rb, rd;\n\t"
+        "mov.b64 {%0, %1}, rd;\n\t}"
+        : "+f"(dx), "+f"(dy) : "f"(ax), "f"(ay), "f"(bx), "f"(by));
+}
+__device__ __forceinline__ void mul2(float& dx, float& dy, float s) {                                    // d *= s
+    asm("{\n\t.reg .b64 rs, rd;\n\t"
+        "mov.b64 rs, {%2, %2};\n\tmov.b64 rd, {%0, %1};\n\t"
+        "mul.rn.f32x2 rd, rd, rs;\n\t"
+        "mov.b64 {%0, %1}, rd;\n\t}"
+        : "+f"(dx), "+f"(dy) : "f"(s));
+}
+// acc4 += p * x4 ;  acc4 *= a ;  dot of two float4 pairs
+__device__ __forceinline__ void axpy4_2(float4& c, float p, const float4& x) { fma2(c.x, c.y, p, p, x.x, x.y); fma2(c.z, c.w, p, p, x.z, x.w); }
+__device__ __forceinline__ void scale4_2(float4& c, float a) { mul2(c.x, c.y, a); mul2(c.z, c.w, a); }
+__device__ __forceinline__ float dot8_2(const float4& qa, const float4& xa, const float4& qb, const float4& xb) {
+    float sx = qa.x * xa.x, sy = qa.y * xa.y;
+    fma2(sx, sy, qa.z, qa.w, xa.z, xa.w);
+    fma2(sx, sy, qb.x, qb.y, xb.x, xb.y);
+    fma2(sx, sy, qb.z, qb.w, xb.z, xb.w);
+    return sx + sy;
+}
+
 __device__ __forceinline__ float half_warp_sum(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 8);
     v += __shfl_xor_sync(0xffffffffu, v, 4);

@@ -247,10 +247,8 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
             float s0[KB], s1[KB];
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
-                const float p0 = qa0.x * xa[i].x + qa0.y * xa[i].y + qa0.z * xa[i].z + qa0.w * xa[i].w +
-                                 qb0.x * xb[i].x + qb0.y * xb[i].y + qb0.z * xb[i].z + qb0.w * xb[i].w;
-                const float p1 = qa1.x * xa[i].x + qa1.y * xa[i].y + qa1.z * xa[i].z + qa1.w * xa[i].w +
-                                 qb1.x * xb[i].x + qb1.y * xb[i].y + qb1.z * xb[i].z + qb1.w * xb[i].w;
+                const float p0 = dot8_2(qa0, xa[i], qb0, xb[i]);       // packed FMAs: half the issue slots
+                const float p1 = dot8_2(qa1, xa[i], qb1, xb[i]);
                 float v = up ? p1 : p0;
                 v += __shfl_xor_sync(gmask, up ? p0 : p1, 4);
                 v += __shfl_xor_sync(gmask, v, 2);
@@ -265,16 +263,12 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
             for (int i = 0; i < KB; ++i) { n0 = fmaxf(n0, s0[i]); n1 = fmaxf(n1, s1[i]); }
             const float a0 = ex2(m0 - n0), a1 = ex2(m1 - n1);      // 2^(-inf) = 0 on the first batch
             l0 *= a0; l1 *= a1;
-            ca0.x *= a0; ca0.y *= a0; ca0.z *= a0; ca0.w *= a0; cb0.x *= a0; cb0.y *= a0; cb0.z *= a0; cb0.w *= a0;
-            ca1.x *= a1; ca1.y *= a1; ca1.z *= a1; ca1.w *= a1; cb1.x *= a1; cb1.y *= a1; cb1.z *= a1; cb1.w *= a1;
+            scale4_2(ca0, a0); scale4_2(cb0, a0); scale4_2(ca1, a1); scale4_2(cb1, a1);
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
                 const float p0 = ex2(s0[i] - n0), p1 = ex2(s1[i] - n1);
                 l0 += p0; l1 += p1;
-                ca0.x = fmaf(p0, xa[i].x, ca0.x); ca0.y = fmaf(p0, xa[i].y, ca0.y); ca0.z = fmaf(p0, xa[i].z, ca0.z); ca0.w = fmaf(p0, xa[i].w, ca0.w);
-                cb0.x = fmaf(p0, xb[i].x, cb0.x); cb0.y = fmaf(p0, xb[i].y, cb0.y); cb0.z = fmaf(p0, xb[i].z, cb0.z); cb0.w = fmaf(p0, xb[i].w, cb0.w);
-                ca1.x = fmaf(p1, xa[i].x, ca1.x); ca1.y = fmaf(p1, xa[i].y, ca1.y); ca1.z = fmaf(p1, xa[i].z, ca1.z); ca1.w = fmaf(p1, xa[i].w, ca1.w);
-                cb1.x = fmaf(p1, xb[i].x, cb1.x); cb1.y = fmaf(p1, xb[i].y, cb1.y); cb1.z = fmaf(p1, xb[i].z, cb1.z); cb1.w = fmaf(p1, xb[i].w, cb1.w);
+                axpy4_2(ca0, p0, xa[i]); axpy4_2(cb0, p0, xb[i]); axpy4_2(ca1, p1, xa[i]); axpy4_2(cb1, p1, xb[i]);
             }
             m0 = n0; m1 = n1;
         };
