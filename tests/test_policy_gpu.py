@@ -139,6 +139,28 @@ def test_ragged_batches_vs_oracle(B, cuda_device):
     np.testing.assert_allclose(_np(lp).reshape(B, L)[same], lpo.numpy().reshape(B, L)[same], atol=TOL)
 
 
+@pytest.mark.parametrize("L,B", [(2, 5), (64, 3), (65, 3), (33, 37)])
+def test_agent_count_boundaries_vs_oracle(L, B, cuda_device):
+    """n_agent around the tiled-attention limit (64) and tiles that straddle envs / end in a partial tile."""
+    sd = mo.make_weights(30 + L, L)
+    m = make_model(L, sd)
+    rng = np.random.RandomState(L)
+    obs = rng.uniform(0, 1.1, size=(B * L, 7)).astype(np.float32)
+    ava = np.ones((B * L, 2), np.float32)
+    ava[rng.uniform(size=B * L) < 0.2, 1] = 0
+    ava.reshape(B, L, 2)[:, -1, 1] = 1
+    u = rng.uniform(size=(B, L)).astype(np.float32)
+    z = rng.standard_normal((B, 2)).astype(np.float32)
+    a, lp, v = m.get_actions(None, obs, ava, deterministic=False, u=u, z=z)
+    vo, ao, lpo = mo.get_actions(sd, obs, ava, L, deterministic=False, u=u, z=z)
+    np.testing.assert_allclose(_np(v).reshape(-1, 1), vo.numpy(), atol=TOL)
+    assert_actions(_np(a), ao.numpy(), _np(lp), lpo.numpy(), L)
+    lp2, v2, ent2 = m(None, obs, ao.reshape(B, L, 1), ava)
+    ve, lpe, _ = mo.evaluate_actions(sd, obs, ao, ava, L)
+    np.testing.assert_allclose(_np(lp2).reshape(-1), lpe.detach().numpy().reshape(-1), atol=TOL)
+    np.testing.assert_allclose(_np(v2).reshape(-1), ve.detach().numpy().reshape(-1), atol=TOL)
+
+
 def test_act_level_entry_points(cuda_device):
     """transformer_act drop-ins take (decoder, obs_rep, ...) like the reference's."""
     from mat_dcml_b200 import transformer_act as ta

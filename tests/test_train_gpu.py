@@ -44,7 +44,8 @@ def _grad_check(model, sd_grads, rel=2e-3):
     return worst
 
 
-@pytest.mark.parametrize("L,M,semi", [(11, 6, True), (21, 13, True), (9, 70, False)])
+@pytest.mark.parametrize("L,M,semi", [(11, 6, True), (21, 13, True), (9, 70, False), (3, 1, True), (51, 5, True), (64, 3, True),
+                                          (65, 2, True), (64, 2, False)])
 def test_evaluate_backward_vs_autograd(L, M, semi, cuda_device):
     sd = mo.make_weights(50 + L, L, semi=semi)
     for v in sd.values():
