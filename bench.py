@@ -107,7 +107,7 @@ def run_reference(ns):
             "config": {"workload": ns.workload + ": " + desc, "sample": sample},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -331,7 +331,7 @@ def run_ours(ns):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_K, "ms_per_step": e2e_ms / e2e_K},
             "roofline": roofline, "cpu_baseline": cpu, "ppo_update": ppo}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -377,8 +377,25 @@ def ppo_block(ns, torch, dist, dev, world, rank):
             "value_loss": info["value_loss"], "grad_norm": info["actor_grad_norm"]}
 
 
+_STDOUT_FD = None
+
+
+def emit(line):
+    """The ONE JSON line of the contract, written to the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _STDOUT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_STDOUT_FD, data)
+
+
 def main():
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout to the one JSON line (NCCL prints its banner there)
+    # Libraries print to stdout behind our back (NCCL writes its version banner there when the communicator is
+    # created): point file descriptor 1 at stderr for the whole run and keep the original for the JSON line.
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
