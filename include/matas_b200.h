@@ -194,6 +194,21 @@ int dcml_env_set_context(dcml_env* e, const double* R, const double* C, const do
 int matas_gae(const float* rewards, const float* value_preds, const float* masks, const float* vn_stats,
               double gamma, double gae_lambda, int T, long n, float* advantages, float* returns, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Fused gradient clipping + Adam on the flat parameter vector: replaces
+ * nn.utils.clip_grad_norm_(policy.transformer.parameters(), max_grad_norm) followed by
+ * policy.optimizer.step() in MATTrainer.ppo_update (mat_src/mat/algorithms/mat/mat_trainer.py:149-154)
+ * for optimizer = torch.optim.Adam(lr, eps, weight_decay) (.../transformer_policy.py:103-105).
+ *   flat_params, flat_grad, exp_avg, exp_avg_sq  [n] fp32, 16-byte aligned; all four are updated in
+ *   place (the gradient is scaled by the clip coefficient, as clip_grad_norm_ does)
+ *   max_grad_norm <= 0: no clipping (get_gard_norm branch, mat_trainer.py:152); step: 1-based count
+ *   norm_out  device float[2]: {total gradient norm before clipping, applied coefficient}
+ * Call matas_policy_set_weights afterwards.
+ * ------------------------------------------------------------------------------------------ */
+int matas_adam_clip_step(float* flat_params, float* flat_grad, float* exp_avg, float* exp_avg_sq, long n,
+                         double lr, double beta1, double beta2, double eps, double weight_decay,
+                         double max_grad_norm, long step, float* norm_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

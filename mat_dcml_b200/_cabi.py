@@ -52,6 +52,8 @@ _SIGNATURES = {
     "dcml_env_reset": (ctypes.c_int, [_P, _P, _P, _P, _P]),
     "dcml_env_step": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "dcml_env_set_context": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "matas_adam_clip_step": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double,
+                                            ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_long, _P, _P]),
     "matas_gae": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_double, ctypes.c_double, ctypes.c_int, ctypes.c_long, _P, _P, _P]),
 }
 

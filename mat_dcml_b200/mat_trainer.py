@@ -123,12 +123,16 @@ class MATTrainer:
         loss.backward()                                              # CUDA backward -> flat gradient
         if _world() > 1:
             dist.all_reduce(model.flat_grad(), op=dist.ReduceOp.SUM)  # the one collective of the update
-        params = [p for p in model.parameters() if p.grad is not None]
-        if self._use_max_grad_norm:
-            grad_norm = nn.utils.clip_grad_norm_(params, self.max_grad_norm)
+        opt = self.policy.optimizer
+        if hasattr(opt, "clip_and_step"):                            # FlatAdam: clip + Adam in two launches
+            grad_norm = opt.clip_and_step(self.max_grad_norm if self._use_max_grad_norm else 0.0)
         else:
-            grad_norm = torch.sqrt(sum((p.grad ** 2).sum() for p in params))
-        self.policy.optimizer.step()
+            params = [p for p in model.parameters() if p.grad is not None]
+            if self._use_max_grad_norm:
+                grad_norm = nn.utils.clip_grad_norm_(params, self.max_grad_norm)
+            else:
+                grad_norm = torch.sqrt(sum((p.grad ** 2).sum() for p in params))
+            opt.step()
         return value_loss, grad_norm, policy_loss, dist_entropy, grad_norm, imp_weights
 
     def normalize_advantages(self, adv, active):

@@ -3,6 +3,8 @@
 argument meaning and return shapes; the model behind it is the CUDA-backed
 ``mat_dcml_b200.ma_transformer.MultiAgentTransformer``.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -58,8 +60,14 @@ class TransformerPolicy:
                                                  semi_index=-1 if semi_index is None else semi_index)
         if getattr(args, "env_name", None) == "hands":
             self.transformer.zero_std()
-        self.optimizer = torch.optim.Adam(self.transformer.parameters(), lr=self.lr, eps=self.opti_eps,
-                                          weight_decay=self.weight_decay)
+        if self.device.type == "cuda" and os.environ.get("MATAS_FUSED_ADAM", "1") != "0":
+            # same update as the reference's torch.optim.Adam (transformer_policy.py:103-105), fused with the
+            # gradient clipping over the flat parameter buffer (flat_adam.py, csrc/adam.cu)
+            from .flat_adam import FlatAdam
+            self.optimizer = FlatAdam(self.transformer, lr=self.lr, eps=self.opti_eps, weight_decay=self.weight_decay)
+        else:
+            self.optimizer = torch.optim.Adam(self.transformer.parameters(), lr=self.lr, eps=self.opti_eps,
+                                              weight_decay=self.weight_decay)
 
     def lr_decay(self, episode, episodes):
         lr = self.lr - (self.lr * (episode / float(episodes)))       # mat/utils/util.py:17-21

@@ -407,6 +407,28 @@ def gen_ppo(out, L, M, wseed):
     print("wrote", out)
 
 
+# ------------------------------------------------------------------------------------------
+# preset benchmark samples (Env(preset=True) reader + modify_preset)
+# ------------------------------------------------------------------------------------------
+def gen_preset(out, rows=24):
+    """What the reference's ``Env(preset=True)`` holds after reading ``data/dcml_benchmark/Sample_1*`` (the first
+    ``rows`` episodes) and after the benchmark script's ``modify_preset`` calls (DCML_MAT_ALT_Benchmark.py:39,122)."""
+    _ref_paths()
+    os.chdir(REF)                                     # the env opens data/... relative to the cwd
+    from DCML_BID_FIRST_MA_ENV_SingleProcess import Env
+    env = Env(preset=True)
+    res = {"n_rows": np.int64(len(env.master_status)), "master": env.master_status[:rows].astype(np.float64),
+           "worker_prs": env.worker_Prs[:rows].copy(), "disable_rates": env.disable_rates[:rows].copy()}
+    env.modify_preset(R=(2 ** 19), C=(9 * (2 ** 10) / 10))
+    res["master_RC"] = env.master_status[:rows].astype(np.float64)
+    env.modify_preset(disable_rate=3 * 8)
+    res["disable_rates_24"] = env.disable_rates[:rows].copy()
+    env.modify_preset(Pr=0.3)
+    res["worker_prs_03"] = env.worker_Prs[:rows].copy()
+    np.savez_compressed(out, **res)
+    print("wrote", out)
+
+
 FAMILIES = {
     "policy_L21_trained": lambda o: gen_policy(o, 21, 5, "trained", 3),
     "policy_L21_init": lambda o: gen_policy(o, 21, 5, "init", 4),
@@ -417,6 +439,7 @@ FAMILIES = {
     "env_W12_shannon": lambda o: gen_env(o, 12, 8, 1, 4, False, shannon=True),
     "gae": gen_gae,
     "ppo_L11": lambda o: gen_ppo(o, 11, 6, 8),
+    "preset_sample1": gen_preset,
 }
 
 if __name__ == "__main__":

@@ -150,3 +150,45 @@ def test_runner_eval_matches_oracle_composition(cuda_device):
     o3.reset(); o3.set_context(R=R, C=C)
     obs3, _, ava3 = env3.obs, None, env3.ava
     np.testing.assert_allclose(obs3.cpu().numpy(), o3._observe_all()[0], rtol=1e-5, atol=1e-6)
+
+
+def test_preset_benchmark_loop(cuda_device):
+    """run_benchmark (DCML_MAT_ALT_Benchmark.py:115-140): every env gets its preset row, the decisions are the
+    oracle's deterministic stride-10 decisions, and the sweep means are reproducible."""
+    from conftest import golden
+    from mat_dcml_b200 import DcmlVecEnv, TransformerPolicy
+    from mat_dcml_b200.benchmark import PresetSamples, run_benchmark, sweep
+    g = golden("preset_sample1")
+    samples = PresetSamples(g["master"], g["worker_prs"], g["disable_rates"])
+    W, L, N = 100, 101, 8
+    args = _args(episode_length=4, n_rollout_threads=N)
+    sd = mo.make_weights(11, L)
+
+    def fresh(seed=6):
+        env = DcmlVecEnv(N, W, seed=seed)
+        pol = TransformerPolicy(args, [7], [W + 2], env.action_space[0], L, device=torch.device("cuda"))
+        pol.transformer.load_state_dict(mo.full_state_dict(sd, L))
+        return env, pol
+
+    env, pol = fresh()
+    env.reset_device()
+    obs, _, ava = samples.apply(env, start=4)
+    ora = eo.DcmlEnvOracle(N, W, env.base_workload, seed=6)
+    ora.reset()
+    idx = 4 + np.arange(N)
+    o_obs, _, o_ava = ora.set_context(R=samples.master_status[idx, 0], C=samples.master_status[idx, 1],
+                                      Pr=samples.worker_Prs[idx], k_dis=samples.disable_rates[idx])
+    # the oracle keeps its disabled SET when only the count changes; compare what does not depend on the set
+    ob = obs.cpu().numpy()
+    np.testing.assert_allclose(ob[:, :, :2], o_obs[:, :, :2], rtol=1e-5, atol=1e-6)          # normalised R, C on every row
+    assert ((ava.cpu().numpy()[:, :W, 1] == 0).sum(1) == samples.disable_rates[idx]).all()   # preset disable counts
+    r1 = run_benchmark(pol, env, samples, n_episodes=20, stride=10)
+    assert r1["rewards"].numel() == 20 and np.isfinite([r1["reward"], r1["ct"], r1["payment"]]).all() and r1["decision_s"] > 0
+    ratio = (r1["rewards"] / (-99.0 * r1["cts"] - r1["payments"])).cpu().numpy()       # DCML_ENV_Functions.py:6-17; x1.5 when N = 0
+    assert (np.isclose(ratio, 1.0, rtol=1e-5) | np.isclose(ratio, 1.5, rtol=1e-5)).all()
+    env2, pol2 = fresh()
+    r2 = run_benchmark(pol2, env2, samples, n_episodes=20, stride=10)
+    np.testing.assert_array_equal(r1["rewards"].cpu().numpy(), r2["rewards"].cpu().numpy())
+    cts, pays, rews = sweep(pol, env, samples, [{"disable_rate": 8}, {"disable_rate": 64}], n_episodes=16)
+    assert cts.shape == (2, 1) and pays.shape == (2, 1) and np.isfinite(rews).all()
+    assert (samples.disable_rates == g["disable_rates"]).all()       # the sweep works on copies

@@ -144,3 +144,43 @@ def test_training_step_changes_weights_and_full_loop(cuda_device):
     assert all(np.isfinite(v) for v in info.values()), info
     assert float((pol.transformer.flat_parameters() - w0).abs().max()) > 0
     assert 0.5 < info["ratio"] < 1.5
+
+
+@pytest.mark.parametrize("max_norm,wd", [(0.5, 0.0), (1e9, 0.0), (0.0, 0.0), (10.0, 1e-3)])
+def test_fused_clip_adam_vs_torch(max_norm, wd, cuda_device):
+    """matas_adam_clip_step (FlatAdam) against nn.utils.clip_grad_norm_ + torch.optim.Adam on per-tensor copies
+    (the reference's update, mat_trainer.py:149-154 / transformer_policy.py:103-105) over three steps."""
+    from mat_dcml_b200.flat_adam import FlatAdam
+    L = 11
+    m = make_model(L, mo.make_weights(7, L))
+    opt = FlatAdam(m, lr=3e-3, eps=1e-5, weight_decay=wd)
+    ref = [torch.nn.Parameter(p.detach().clone()) for p in m.parameters()]
+    ropt = torch.optim.Adam(ref, lr=3e-3, eps=1e-5, weight_decay=wd)
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    for it in range(3):
+        g = torch.randn(m.flat_parameters().numel(), device="cuda", generator=gen) * (0.02 if it else 2.0)
+        m.flat_grad(zero=True).copy_(g)
+        off = 0
+        for p in ref:
+            p.grad = g[off:off + p.numel()].view(p.shape).clone()
+            off += p.numel()
+        if max_norm > 0:
+            want_norm = torch.nn.utils.clip_grad_norm_(ref, max_norm)
+        else:
+            want_norm = torch.sqrt(sum((p.grad ** 2).sum() for p in ref))
+        ropt.step()
+        ver = m.flat_parameters()._version
+        got_norm = opt.clip_and_step(max_norm)
+        assert abs(float(got_norm) - float(want_norm)) <= 1e-5 * float(want_norm)
+        want = torch.cat([p.detach().reshape(-1) for p in ref])
+        np.testing.assert_allclose(m.flat_parameters().cpu().numpy(), want.cpu().numpy(), rtol=2e-5, atol=2e-7)
+        want_g = torch.cat([p.grad.reshape(-1) for p in ref])
+        np.testing.assert_allclose(m.flat_grad().cpu().numpy(), want_g.cpu().numpy(), rtol=1e-5, atol=1e-9)
+        assert m._packed_key is None                      # the next pass repacks the weights
+    assert opt.state_dict()["step"] == 3
+    # the policy picks it up on a GPU, and lr_decay reaches it through param_groups
+    from mat_dcml_b200 import TransformerPolicy, Action_Space
+    pol = TransformerPolicy(_targs(lr=5e-4), [7], [L + 1], Action_Space(2, semi_index=-1, extra=True), L, device=torch.device("cuda"))
+    assert isinstance(pol.optimizer, FlatAdam)
+    pol.lr_decay(1, 2)
+    assert abs(pol.optimizer.param_groups[0]["lr"] - 2.5e-4) < 1e-12
