@@ -13,6 +13,8 @@
 // 32*(w % 4) + lane and the 16 accumulator columns of quarter w / 4.
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "policy_fwd.h"
 #include "tc.cuh"
 
@@ -216,91 +218,117 @@ __device__ __forceinline__ float ex2(float x) {          // 2^x, x <= 0 here; de
 // Absorbed attention (tile::attention_absorbed) for 512 threads with tensor-core operand outputs: 8 lanes
 // per env, lane g holds columns 4g..4g+3 and 32+4g..35+4g of every 64-float row; folded queries from the
 // shared tiles (GQ = false) or from global rows q0 / q1 + r * q_stride (GQ = true); ctx_0 -> U, ctx_1 -> V.
-// Env row r attends to nk cached rows at cache + r * slot_stride (0 rows when r >= n_valid).
+// Env row r attends to nk cached rows at cache + r * slot_stride; rows r >= n_valid store zero contexts.
+//
+// The key loop is the kernel's hot loop (three attentions x (j + 1) keys per position), so it is written for
+// instruction count: `rows` is a multiple of 8 (decode_tc_rows), hence whole warps enter and every loop bound is
+// warp-uniform (nk), which allows full-mask shuffles; each half of a lane group keeps the head it collects as
+// "own" and the other as "oth" (lanes 0-3: own = head 0, lanes 4-7: own = head 1), so no per-key selects are
+// needed; batches of two keys run unpredicated while six keys remain, and a predicated tail finishes the row.
 template <bool GQ, int PF>
 __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                       const float* cache, long slot_stride, int rows, int n_valid, int nk,
                                                       unsigned char* U, unsigned char* V) {
     constexpr int KB = 2;
+    constexpr unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, grp = tid >> 3, g = tid & 7;
-    const unsigned gmask = 0xffu << (tid & 24);
     const bool up = (g & 4) != 0;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int r = grp; r < rows; r += NTD / 8) {
-        const int nr = r < n_valid ? nk : 0;
-        float4 qa0, qb0, qa1, qb1;
+        const bool valid = r < n_valid;
+        const int rr = valid ? r : n_valid - 1;      // rows past the batch walk a live env's rows (same trip counts) and store zeros
+        float4 qa_own, qb_own, qa_oth, qb_oth;
         if (GQ) {
-            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-            const float4* p0 = reinterpret_cast<const float4*>(q0 + (long)r * q_stride);
-            const float4* p1 = reinterpret_cast<const float4*>(q1 + (long)r * q_stride);
-            qa0 = nr ? __ldg(p0 + g) : z; qb0 = nr ? __ldg(p0 + 8 + g) : z;
-            qa1 = nr ? __ldg(p1 + g) : z; qb1 = nr ? __ldg(p1 + 8 + g) : z;
+            const float4* po = reinterpret_cast<const float4*>((up ? q1 : q0) + (long)rr * q_stride);
+            const float4* pt = reinterpret_cast<const float4*>((up ? q0 : q1) + (long)rr * q_stride);
+            qa_own = __ldg(po + g); qb_own = __ldg(po + 8 + g);
+            qa_oth = __ldg(pt + g); qb_oth = __ldg(pt + 8 + g);
         } else {
-            qa0 = *reinterpret_cast<const float4*>(q0 + r * XS + g * 4);
-            qb0 = *reinterpret_cast<const float4*>(q0 + r * XS + 32 + g * 4);
-            qa1 = *reinterpret_cast<const float4*>(q1 + r * XS + g * 4);
-            qb1 = *reinterpret_cast<const float4*>(q1 + r * XS + 32 + g * 4);
+            const float* po = (up ? q1 : q0) + rr * XS;
+            const float* pt = (up ? q0 : q1) + rr * XS;
+            qa_own = *reinterpret_cast<const float4*>(po + g * 4);
+            qb_own = *reinterpret_cast<const float4*>(po + 32 + g * 4);
+            qa_oth = *reinterpret_cast<const float4*>(pt + g * 4);
+            qb_oth = *reinterpret_cast<const float4*>(pt + 32 + g * 4);
         }
-        const float4* xp = reinterpret_cast<const float4*>(cache + (long)r * slot_stride) + g;   // row t: xp[t*16], xp[t*16 + 8]
-        float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-        float4 ca0 = make_float4(0.f, 0.f, 0.f, 0.f), cb0 = ca0, ca1 = ca0, cb1 = ca0;
-        auto batch = [&](const float4 (&xa)[KB], const float4 (&xb)[KB], int t0) {
-            float s0[KB], s1[KB];
+        const float4* xp = reinterpret_cast<const float4*>(cache + (long)rr * slot_stride) + g;   // row t: xp[t*16], xp[t*16 + 8]
+        // L2 prefetch PF rows ahead by lanes 0 (first 128-byte line of the row) and 4 (second line); no registers held
+        const float4* pfp = xp + (g ? 8 : 0) + PF * 16;
+        const int pf_lim = (PF > 0 && (g & 3) == 0) ? nk - PF : -(1 << 30);       // prefetch row t + PF while t < pf_lim
+        float m_own = -INFINITY, m_oth = -INFINITY, l_own = 0.f, l_oth = 0.f;
+        float4 ca_own = z4, cb_own = z4, ca_oth = z4, cb_oth = z4;
+        auto batch = [&](const float4 (&xa)[KB], const float4 (&xb)[KB], int t0, auto masked) {
+            float so[KB], st[KB];
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
-                const float p0 = dot8_2(qa0, xa[i], qb0, xb[i]);       // packed FMAs: half the issue slots
-                const float p1 = dot8_2(qa1, xa[i], qb1, xb[i]);
-                float v = up ? p1 : p0;
-                v += __shfl_xor_sync(gmask, up ? p0 : p1, 4);
-                v += __shfl_xor_sync(gmask, v, 2);
-                v += __shfl_xor_sync(gmask, v, 1);
-                const float o = __shfl_xor_sync(gmask, v, 4);
-                const bool ok = t0 + i < nr;
-                s0[i] = ok ? (up ? o : v) : -INFINITY;
-                s1[i] = ok ? (up ? v : o) : -INFINITY;
-            }
-            float n0 = m0, n1 = m1;
-#pragma unroll
-            for (int i = 0; i < KB; ++i) { n0 = fmaxf(n0, s0[i]); n1 = fmaxf(n1, s1[i]); }
-            const float a0 = ex2(m0 - n0), a1 = ex2(m1 - n1);      // 2^(-inf) = 0 on the first batch
-            l0 *= a0; l1 *= a1;
-            scale4_2(ca0, a0); scale4_2(cb0, a0); scale4_2(ca1, a1); scale4_2(cb1, a1);
-#pragma unroll
-            for (int i = 0; i < KB; ++i) {
-                const float p0 = ex2(s0[i] - n0), p1 = ex2(s1[i] - n1);
-                l0 += p0; l1 += p1;
-                axpy4_2(ca0, p0, xa[i]); axpy4_2(cb0, p0, xb[i]); axpy4_2(ca1, p1, xa[i]); axpy4_2(cb1, p1, xb[i]);
-            }
-            m0 = n0; m1 = n1;
-        };
-        auto fetch = [&](float4 (&xa)[KB], float4 (&xb)[KB], int t0) {
-#pragma unroll
-            for (int i = 0; i < KB; ++i) {
-                const bool ok = t0 + i < nr;
-                xa[i] = ok ? xp[(long)(t0 + i) * 16] : make_float4(0.f, 0.f, 0.f, 0.f);
-                xb[i] = ok ? xp[(long)(t0 + i) * 16 + 8] : make_float4(0.f, 0.f, 0.f, 0.f);
-                // pull the row PF positions ahead into L2 (lane 0: first 128-byte line, lane 4: second); no registers held
-                if (PF > 0 && (g & 3) == 0 && t0 + i + PF < nr) {
-                    const float4* pp = xp + (long)(t0 + i + PF) * 16 + (g ? 8 : 0);
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
+                const float p_own = dot8_2(qa_own, xa[i], qb_own, xb[i]);       // packed FMAs: half the issue slots
+                const float p_oth = dot8_2(qa_oth, xa[i], qb_oth, xb[i]);
+                float v = p_own + __shfl_xor_sync(FULL, p_oth, 4);
+                v += __shfl_xor_sync(FULL, v, 2);
+                v += __shfl_xor_sync(FULL, v, 1);
+                const float o = __shfl_xor_sync(FULL, v, 4);
+                if (decltype(masked)::value) {
+                    const bool ok = t0 + i < nk;
+                    so[i] = ok ? v : -INFINITY;
+                    st[i] = ok ? o : -INFINITY;
+                } else {
+                    so[i] = v; st[i] = o;
                 }
+            }
+            const float n_own = fmaxf(m_own, fmaxf(so[0], so[1])), n_oth = fmaxf(m_oth, fmaxf(st[0], st[1]));
+            const float a_own = ex2(m_own - n_own), a_oth = ex2(m_oth - n_oth);      // 2^(-inf) = 0 on the first batch
+            l_own *= a_own; l_oth *= a_oth;
+            scale4_2(ca_own, a_own); scale4_2(cb_own, a_own); scale4_2(ca_oth, a_oth); scale4_2(cb_oth, a_oth);
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                const float p_own = ex2(so[i] - n_own), p_oth = ex2(st[i] - n_oth);
+                l_own += p_own; l_oth += p_oth;
+                axpy4_2(ca_own, p_own, xa[i]); axpy4_2(cb_own, p_own, xb[i]); axpy4_2(ca_oth, p_oth, xa[i]); axpy4_2(cb_oth, p_oth, xb[i]);
+            }
+            m_own = n_own; m_oth = n_oth;
+        };
+        auto fetch_masked = [&](float4 (&xa)[KB], float4 (&xb)[KB], int t0) {
+#pragma unroll
+            for (int i = 0; i < KB; ++i) {
+                const bool ok = t0 + i < nk;
+                xa[i] = ok ? xp[(long)(t0 + i) * 16] : z4;
+                xb[i] = ok ? xp[(long)(t0 + i) * 16 + 8] : z4;
+                if (t0 + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pfp + (long)(t0 + i) * 16));
             }
         };
         float4 xa[KB], xb[KB], ya[KB], yb[KB];
-        if (PF > 0 && (g & 3) == 0) {
-            for (int t = 2 * KB; t < PF + 0 && t < nr; ++t) asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + (long)t * 16 + (g ? 8 : 0)));
+        fetch_masked(xa, xb, 0);
+        int t0 = 0;
+        {   // unpredicated part: keys t0 .. t0 + 5 exist
+            const float4* xt = xp;
+            const float4* pt = pfp;
+            for (; t0 + 3 * KB <= nk; t0 += 2 * KB, xt += 2 * KB * 16, pt += 2 * KB * 16) {
+#pragma unroll
+                for (int i = 0; i < KB; ++i) { ya[i] = xt[(KB + i) * 16]; yb[i] = xt[(KB + i) * 16 + 8]; }
+                if (t0 + KB < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + KB * 16));
+                if (t0 + KB + 1 < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (KB + 1) * 16));
+                batch(xa, xb, t0, std::false_type{});
+#pragma unroll
+                for (int i = 0; i < KB; ++i) { xa[i] = xt[(2 * KB + i) * 16]; xb[i] = xt[(2 * KB + i) * 16 + 8]; }
+                if (t0 + 2 * KB < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + 2 * KB * 16));
+                if (t0 + 2 * KB + 1 < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (2 * KB + 1) * 16));
+                batch(ya, yb, t0 + KB, std::false_type{});
+            }
         }
-        fetch(xa, xb, 0);
-        for (int t0 = 0; t0 < nr; t0 += 2 * KB) {
-            fetch(ya, yb, t0 + KB);
-            batch(xa, xb, t0);
-            fetch(xa, xb, t0 + 2 * KB);
-            if (t0 + KB < nr) batch(ya, yb, t0 + KB);
+        for (; t0 < nk; t0 += 2 * KB) {          // predicated tail (at most 5 keys)
+            fetch_masked(ya, yb, t0 + KB);
+            batch(xa, xb, t0, std::true_type{});
+            fetch_masked(xa, xb, t0 + 2 * KB);
+            if (t0 + KB < nk) batch(ya, yb, t0 + KB, std::true_type{});
         }
-        const float i0 = nr > 0 ? 1.0f / l0 : 0.f, i1 = nr > 0 ? 1.0f / l1 : 0.f;
-        tc::store_operand4(U, r, g, make_float4(ca0.x * i0, ca0.y * i0, ca0.z * i0, ca0.w * i0));
-        tc::store_operand4(U, r, 8 + g, make_float4(cb0.x * i0, cb0.y * i0, cb0.z * i0, cb0.w * i0));
-        tc::store_operand4(V, r, g, make_float4(ca1.x * i1, ca1.y * i1, ca1.z * i1, ca1.w * i1));
-        tc::store_operand4(V, r, 8 + g, make_float4(cb1.x * i1, cb1.y * i1, cb1.z * i1, cb1.w * i1));
+        const float i_own = valid && nk > 0 ? 1.0f / l_own : 0.f, i_oth = valid && nk > 0 ? 1.0f / l_oth : 0.f;
+        if (!valid) { ca_own = z4; cb_own = z4; ca_oth = z4; cb_oth = z4; }       // NaN-safe: never multiply walked garbage
+        unsigned char* o_own = up ? V : U;
+        unsigned char* o_oth = up ? U : V;
+        tc::store_operand4(o_own, r, g, make_float4(ca_own.x * i_own, ca_own.y * i_own, ca_own.z * i_own, ca_own.w * i_own));
+        tc::store_operand4(o_own, r, 8 + g, make_float4(cb_own.x * i_own, cb_own.y * i_own, cb_own.z * i_own, cb_own.w * i_own));
+        tc::store_operand4(o_oth, r, g, make_float4(ca_oth.x * i_oth, ca_oth.y * i_oth, ca_oth.z * i_oth, ca_oth.w * i_oth));
+        tc::store_operand4(o_oth, r, 8 + g, make_float4(cb_oth.x * i_oth, cb_oth.y * i_oth, cb_oth.z * i_oth, cb_oth.w * i_oth));
     }
 }
 
