@@ -41,7 +41,7 @@ __device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr, uint32_t lbo_by
 __global__ void __launch_bounds__(NT, 4)
 bwd_dw_kernel(const float* __restrict__ packed, float* __restrict__ grad, DwJobs jobs, long n_tok, int splits) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* base = smem_align1024(smem_raw);
     unsigned char* sA = base;                         // hi: [128 tokens][128 B], lo the same, then 16 KB of zeros
     unsigned char* sB = base + A_BYTES;               // hi: [128 tokens][128 B], then lo
     float* sLn = reinterpret_cast<float*>(sB + B_BYTES);         // LN weight[64] | bias[64] of the affine recipe

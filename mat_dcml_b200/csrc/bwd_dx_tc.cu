@@ -36,7 +36,7 @@ template <int KIND>
 __global__ void __launch_bounds__(NT, 2)
 bwd_qkv_dx_kernel(const float* __restrict__ packed, float* __restrict__ grad, DxArgs a, long n_tok) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* base = smem_align1024(smem_raw);
     unsigned char* op = base;                                     // [hi | lo][128 tokens][128 B]
     unsigned char* sW = base + 2 * tc::A_PART;                    // 3 x [hi | lo][64 out rows][128 B]
     float* sCol = reinterpret_cast<float*>(sW + 3 * 2 * WPART);   // [3][16 half-warps][64] bias-gradient partials

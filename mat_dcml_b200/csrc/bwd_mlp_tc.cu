@@ -100,7 +100,7 @@ template <bool WITH_MLP>
 __global__ void __launch_bounds__(NT, 2)
 bwd_mlp_tc_kernel(const float* __restrict__ packed, float* __restrict__ grad, TailArgs a, long n_tok) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* base = smem_align1024(smem_raw);
     unsigned char* op = base;                                     // operand [hi | lo][128][128 B]  /  fp32 staging [128][256 B]
     unsigned char* sW = base + 2 * tc::A_PART;                    // forward half blobs of mlp.2, mlp.0, proj
     uint64_t* bar = reinterpret_cast<uint64_t*>(sW + 3 * 2 * WPART);

@@ -111,6 +111,13 @@ __device__ __forceinline__ float warp_sum(float v) {
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// 1024-byte aligned start of the dynamic shared memory (what SWIZZLE_128B operands need), derived by pointer
+// arithmetic from the array itself: an integer round trip would lose the shared address space and turn every
+// later access into a generic LD / ST with 64-bit address arithmetic.
+__device__ __forceinline__ unsigned char* smem_align1024(unsigned char* raw) {
+    return raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);
+}
+
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }

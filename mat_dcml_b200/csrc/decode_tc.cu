@@ -60,7 +60,7 @@ __host__ __device__ constexpr size_t dsmem_bytes() {
 }
 __device__ inline DSmem dcarve(unsigned char* raw) {
     DSmem s;
-    unsigned char* p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* p = smem_align1024(raw);
     s.U = p; p += OP_BYTES;
     s.V = p; p += OP_BYTES;
     s.ring = reinterpret_cast<float*>(p); p += (size_t)DEPTH * tc::SLOT_BYTES;

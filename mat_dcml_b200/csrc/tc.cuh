@@ -41,7 +41,7 @@ __host__ __device__ constexpr size_t smem_bytes(int depth) {
 }
 __device__ inline Smem carve(unsigned char* raw, int depth) {
     Smem s;
-    unsigned char* p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* p = smem_align1024(raw);
     s.sA = p; p += 2 * A_PART;
     s.ring = reinterpret_cast<float*>(p); p += (size_t)depth * SLOT_BYTES;
     s.sT = reinterpret_cast<float*>(p); p += TILE_BYTES;
