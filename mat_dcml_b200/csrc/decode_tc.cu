@@ -532,7 +532,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
                     tc::publish();
-                    if (tid == 0) {
+                    if (tc::mma_issuer()) {
                         tc::mma_set(tmem, uaddr, smem_u32(w0), false);
                         tc::mma_set(tmem + 128, uaddr, smem_u32(w1), false);
                         tc::mma_commit(mma_bar);
@@ -557,7 +557,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
                     tc::publish();
-                    if (tid == 0) {
+                    if (tc::mma_issuer()) {
                         tc::mma_set(tmem, uaddr, smem_u32(w0), false);
                         tc::mma_set(tmem, vaddr, smem_u32(w1), true);
                         tc::mma_commit(mma_bar);
@@ -586,7 +586,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
                     tc::publish();
-                    if (tid == 0) {
+                    if (tc::mma_issuer()) {
                         tc::mma_set(tmem, uaddr, smem_u32(w0), false);
                         tc::mma_set(tmem, vaddr, smem_u32(w1), true);
                         tc::mma_commit(mma_bar);
@@ -605,7 +605,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                 {
                     const float* w0 = ring.peek(0);
                     tc::publish();
-                    if (tid == 0) { tc::mma_set(tmem, uaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
+                    if (tc::mma_issuer()) { tc::mma_set(tmem, uaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
                     ring.prefetch();
                     mma_wait();
                     result16(tmem, 0, row, q, v);
@@ -618,7 +618,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                 {
                     const float* w0 = ring.peek(0);
                     tc::publish();
-                    if (tid == 0) { tc::mma_set(tmem, vaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
+                    if (tc::mma_issuer()) { tc::mma_set(tmem, vaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
                     ring.prefetch();
                     mma_wait();
                     result16(tmem, 0, row, q, v);
@@ -634,7 +634,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                 store_operand16(s.U, row, q, v);
                 const float* w0 = ring.peek(0);
                 tc::publish();
-                if (tid == 0) { tc::mma_set(tmem, uaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
+                if (tc::mma_issuer()) { tc::mma_set(tmem, uaddr, smem_u32(w0), false); tc::mma_commit(mma_bar); }
                 ring.prefetch();
                 mma_wait();
                 result16(tmem, 0, row, q, v);

@@ -117,6 +117,22 @@ __device__ __forceinline__ void mma_set(uint32_t d, uint32_t a, uint32_t w, bool
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) mma_f16(d + 64, make_desc(a + A_PART + ks * 32), make_desc(w + ks * 32), idesc, 1u);
 }
+// MMA issue in warp-uniform control flow.  Under a plain `threadIdx.x == 0` the compiler cannot keep the descriptors
+// in uniform registers and wraps every UTCHMMA in an ELECT / R2UR / branch loop (about 13 extra instructions and two
+// register-to-uniform moves per MMA on the serial issue path).  Instead: warp 0 enters (its index comes from a
+// shuffle, hence provably warp-uniform), reads the operand addresses through `uni` (lane-0 broadcasts, uniform by
+// construction) and one thread picked by elect.sync issues.
+__device__ __forceinline__ bool issuer_warp() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 0; }
+__device__ __forceinline__ uint32_t uni(uint32_t x) { return __shfl_sync(0xffffffffu, x, 0); }      // whole warp, inside issuer_warp()
+__device__ __forceinline__ bool elect_one() {                                                      // whole warp
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ bool mma_issuer() { return issuer_warp() && elect_one(); }               // exactly one thread of warp 0
+__device__ __forceinline__ void mma_commit_saddr(uint32_t bar_saddr) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_saddr) : "memory");
+}
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -166,18 +182,20 @@ __device__ __forceinline__ void gemm_issue(const Ctx& c, const float* slot) {
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    if (threadIdx.x == 0) {
-        // instruction descriptor: D f32, A/B f16, both K-major, N = 64, M = 128
-        const uint32_t idesc = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        const uint32_t a0 = c.a_saddr, b0 = smem_u32(slot);
+    if (issuer_warp()) {
+        const uint32_t a0 = uni(c.a_saddr), b0 = uni(smem_u32(slot)), d0 = uni(c.tmem), bar = uni(smem_u32(c.bar));
+        if (elect_one()) {
+            // instruction descriptor: D f32, A/B f16, both K-major, N = 64, M = 128
+            const uint32_t idesc = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) mma_f16(c.tmem, make_desc(a0 + ks * 32), make_desc(b0 + ks * 32), idesc, ks > 0);
+            for (int ks = 0; ks < 4; ++ks) mma_f16(d0, make_desc(a0 + ks * 32), make_desc(b0 + ks * 32), idesc, ks > 0);
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-            mma_f16(c.tmem + 64, make_desc(a0 + ks * 32), make_desc(b0 + lay::HB_LO_BYTES + ks * 32), idesc, ks > 0);
+            for (int ks = 0; ks < 4; ++ks)
+                mma_f16(d0 + 64, make_desc(a0 + ks * 32), make_desc(b0 + lay::HB_LO_BYTES + ks * 32), idesc, ks > 0);
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) mma_f16(c.tmem + 64, make_desc(a0 + A_PART + ks * 32), make_desc(b0 + ks * 32), idesc, 1);
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(c.bar)) : "memory");
+            for (int ks = 0; ks < 4; ++ks) mma_f16(d0 + 64, make_desc(a0 + A_PART + ks * 32), make_desc(b0 + ks * 32), idesc, 1);
+            mma_commit_saddr(bar);
+        }
     }
 }
 // Wait for the products and read this thread's 32 accumulator columns: v = D1 + 2^-11 D2
