@@ -19,47 +19,62 @@ namespace {
 constexpr int ANT = 128;     // maximum threads per CTA (loops stride by blockDim.x)
 constexpr int RS = 68;       // row stride of the Q / K / V tiles (floats): 16-byte aligned rows, 4-bank skew
 
-struct AttnGeom { int Lp, nb, SS, PS; size_t floats; };
-__host__ __device__ inline AttnGeom attn_geom(int L) {
+struct AttnGeom { int Lp, nb, SS, PS; size_t qk_floats, floats; };
+// vr = true: V waits in registers until the score tile is free and then takes its place (less shared memory: 48.8 KB
+// instead of 62.6 KB per env at n_agent 51, four resident CTAs per SM instead of three); vr = false: V has its own tile
+// (no extra barrier, fewer live registers -- better whenever shared memory does not limit the resident CTAs).
+__host__ __device__ inline AttnGeom attn_geom(int L, bool vr) {
     AttnGeom g;
     g.Lp = (L + 3) & ~3;
     g.nb = g.Lp >> 2;
     g.SS = (g.nb & 1) ? g.Lp : g.Lp + 4;                    // S row stride: (SS / 4) odd -> 8 rows x 4 keys hit 32 banks
     g.PS = g.Lp + ((8 - (g.Lp & 15)) & 15);                  // PT row stride: PS = 8 (mod 16), >= Lp
-    const size_t qk = 2 * (size_t)g.Lp * RS, pt = 2 * (size_t)g.Lp * g.PS;
-    g.floats = (qk > pt ? qk : pt) + (size_t)g.Lp * RS + 2 * (size_t)g.Lp * g.SS;
+    const size_t qk = 2 * (size_t)g.Lp * RS, pt = 2 * (size_t)g.Lp * g.PS;      // [Q | K], later PT
+    const size_t sc = 2 * (size_t)g.Lp * g.SS, vv = (size_t)g.Lp * RS;          // S and V
+    g.qk_floats = qk > pt ? qk : pt;
+    g.floats = g.qk_floats + (vr ? (sc > vv ? sc : vv) : sc + vv);
     return g;
 }
 
-template <bool CAUSAL>
+constexpr int VREG = 64 * 16 / ANT;      // float4 registers per thread that hold the V rows of one env (n_agent <= 64)
+
+template <bool CAUSAL, bool VR>
 __global__ void __launch_bounds__(ANT)
 attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const float* __restrict__ V, float* __restrict__ Y,
                 float* __restrict__ lse, long n_env, int L) {
     extern __shared__ __align__(16) float sm[];
-    const AttnGeom g = attn_geom(L);
+    const AttnGeom g = attn_geom(L, VR);
     const int Lp = g.Lp, nb = g.nb, SS = g.SS, PS = g.PS;
-    const size_t qk = 2 * (size_t)Lp * RS, pt = 2 * (size_t)Lp * PS;
     float* sQ = sm;
     float* sK = sm + (size_t)Lp * RS;
     float* sPT = sm;                                          // aliases sQ / sK once the scores are done
-    float* sV = sm + (qk > pt ? qk : pt);
-    float* sS = sV + (size_t)Lp * RS;
-    const int tid = threadIdx.x, nthr = blockDim.x;
+    float* sS = sm + g.qk_floats;
+    float* sV = VR ? sS : sS + 2 * (size_t)Lp * SS;           // VR: takes the place of the scores once the probabilities are written
+    const int tid = threadIdx.x, nthr = blockDim.x;           // nthr == ANT (launch_attn_tile)
     const float scale = 0.17677669529663687f * 1.4426950408889634f;     // log2(e)/sqrt(32): exp2-domain scores
     for (long env = blockIdx.x; env < n_env; env += gridDim.x) {
         const long tok0 = env * L;
-        // ---- stage Q, K, V (rows >= L zero) ---------------------------------------------------------------
+        // ---- stage Q, K, V (rows >= L zero) ----------------------------------------------------------------------
+        float4 vreg[VREG];
+        if (VR) {
+#pragma unroll
+            for (int i = 0; i < VREG; ++i) {
+                const int idx = tid + i * ANT, r = idx >> 4, c = idx & 15;
+                vreg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < L) vreg[i] = __ldg(reinterpret_cast<const float4*>(V + (tok0 + r) * 64) + c);
+            }
+        }
         for (int idx = tid; idx < Lp * 16; idx += nthr) {
             const int r = idx >> 4, c = idx & 15;
             float4 q = make_float4(0.f, 0.f, 0.f, 0.f), k = q, v = q;
             if (r < L) {
                 q = __ldg(reinterpret_cast<const float4*>(Q + (tok0 + r) * 64) + c);
                 k = __ldg(reinterpret_cast<const float4*>(K + (tok0 + r) * 64) + c);
-                v = __ldg(reinterpret_cast<const float4*>(V + (tok0 + r) * 64) + c);
+                if (!VR) v = __ldg(reinterpret_cast<const float4*>(V + (tok0 + r) * 64) + c);
             }
             *reinterpret_cast<float4*>(sQ + r * RS + c * 4) = q;
             *reinterpret_cast<float4*>(sK + r * RS + c * 4) = k;
-            *reinterpret_cast<float4*>(sV + r * RS + c * 4) = v;
+            if (!VR) *reinterpret_cast<float4*>(sV + r * RS + c * 4) = v;
         }
         __syncthreads();
         // ---- S = scale * Q K^T: thread block = queries {qb + nb*i} x keys {kb + nb*j} of head h ----------------
@@ -122,6 +137,14 @@ attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const 
             }
         }
         __syncthreads();
+        if (VR) {      // V: registers -> the tile the scores occupied
+#pragma unroll
+            for (int i = 0; i < VREG; ++i) {
+                const int idx = tid + i * ANT, r = idx >> 4, c = idx & 15;
+                if (r < Lp) *reinterpret_cast<float4*>(sV + r * RS + c * 4) = vreg[i];
+            }
+            __syncthreads();
+        }
         // ---- Y = P V: thread block = queries 4qb..4qb+3 x dims 4db..4db+3 of head h -------------------------------
         for (int task = tid; task < 2 * nb * 8; task += nthr) {
             const int h = task / (nb * 8), rem = task - h * nb * 8, qb = rem >> 3, db = rem & 7;
@@ -161,19 +184,22 @@ bool attn_tile_supported(int L) { return L <= 64; }
 
 int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
                      cudaStream_t st) {
-    const AttnGeom g = attn_geom(L);
-    const size_t bytes = g.floats * sizeof(float);
+    // V in registers only where it buys a resident CTA and shared memory is what limits them
+    const size_t smem_sm = 227 * 1024, b0 = attn_geom(L, false).floats * sizeof(float) + 1024,
+                 b1 = attn_geom(L, true).floats * sizeof(float) + 1024;
+    static int vr_env = -1;                             // tuning override: MATAS_AT_VREG = 0 / 1
+    if (vr_env < 0) { const char* e = getenv("MATAS_AT_VREG"); vr_env = e ? atoi(e) : 2; }
+    const bool vr = vr_env == 2 ? (smem_sm / b0 < 4 && smem_sm / b1 > smem_sm / b0) : vr_env != 0;
+    const size_t bytes = attn_geom(L, vr).floats * sizeof(float);
     const unsigned grid = (unsigned)(n_env < (1L << 30) ? n_env : (1L << 30));
-    static int t_env = -1;                              // tuning override: MATAS_AT_THREADS
-    if (t_env < 0) { const char* e = getenv("MATAS_AT_THREADS"); t_env = e ? atoi(e) : 0; }
-    const int nthr = t_env ? t_env : ANT;
-    if (causal) {
-        CUDA_TRY(cudaFuncSetAttribute(attn_env_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        attn_env_kernel<true><<<grid, nthr, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
-    } else {
-        CUDA_TRY(cudaFuncSetAttribute(attn_env_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        attn_env_kernel<false><<<grid, nthr, bytes, st>>>(Q, K, V, Y, lse, n_env, L);
-    }
+#define ATTN_LAUNCH(C, R)                                                                                              \
+    do {                                                                                                               \
+        CUDA_TRY(cudaFuncSetAttribute(attn_env_kernel<C, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+        attn_env_kernel<C, R><<<grid, ANT, bytes, st>>>(Q, K, V, Y, lse, n_env, L);                                    \
+    } while (0)
+    if (causal) { if (vr) ATTN_LAUNCH(true, true); else ATTN_LAUNCH(true, false); }
+    else { if (vr) ATTN_LAUNCH(false, true); else ATTN_LAUNCH(false, false); }
+#undef ATTN_LAUNCH
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
