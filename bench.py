@@ -34,7 +34,7 @@ METRIC, UNIT = "rollout_env_steps_per_sec", "env-steps/s"
 
 
 def decode_schedule_positions(L, det, stride):
-    """Agent positions the decode kernel visits in one launch (mirror of DecSched in csrc/policy_fwd.cu,
+    """Agent positions the decode kernel visits in one launch (mirror of DecSched in csrc/policy_fwd.h,
     Semi_Discrete mode): stochastic = every position once; deterministic = per stride block a speculative
     pass and, unless it was the last block, a commit pass (transformer_act.py:164-207)."""
     if not det:
@@ -121,7 +121,7 @@ class Clocks:
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -306,7 +306,7 @@ def run_ours(ns):
     hbm_peak = peaks.get("hbm_gbs", 6500.0)
     hbm_src = ("measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6.5 TB/s (B200_PROFILING.md)")
     achieved_gbs = alg_bytes / (dec_ms * 1e-3) / 1e9
-    roofline = {"kernel": "decode_kernel", "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+    roofline = {"kernel": "decode_tc_kernel", "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": hbm_src,
                 "launch_ms": dec_ms, "launches_timed": tn.value, "share_of_step": dec_ms / (ms / ns.steps),
                 "algorithmic_bytes_per_launch": alg_bytes,
@@ -398,7 +398,7 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))

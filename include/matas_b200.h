@@ -161,6 +161,10 @@ typedef struct {
     int shannon;       /* 1 = Shannon link rates (reset(shannon_enable=True): DCML_ENVs/DCML_Basic_Env.py:18-27,
                           DCML_Master.py:41-45, Shannon.py:14-21); share_obs rows are then 2W+2 wide
                           [Rn, Cn, upload/1e7 (W), download/1e7 (W)], …SingleProcess.py:248-250 */
+    int fixed;         /* 1 = Env(fixed=True), …SingleProcess.py:58-62: the actions are ignored, every available worker is
+                          selected and K = floor(0.7 N) */
+    int standalone;    /* 1 = every step takes the step(standalone=True) branch, …SingleProcess.py:81-92: the task runs
+                          uncoded on worker 0 (K = N = 1) and the reward is scaled by 1.5 */
 } dcml_env_cfg;
 
 /* Env.__init__ (…SingleProcess.py:16-55): base_workload_host is the workloads.txt table,

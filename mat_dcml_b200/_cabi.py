@@ -20,7 +20,8 @@ class ModelCfg(ctypes.Structure):
 
 class EnvCfg(ctypes.Structure):
     _fields_ = [("n_envs", ctypes.c_long), ("n_workers", ctypes.c_int), ("seed", ctypes.c_uint64),
-                ("env_offset", ctypes.c_long), ("double_reset", ctypes.c_int), ("shannon", ctypes.c_int)]
+                ("env_offset", ctypes.c_long), ("double_reset", ctypes.c_int), ("shannon", ctypes.c_int),
+                ("fixed", ctypes.c_int), ("standalone", ctypes.c_int)]
 
 
 _P = ctypes.c_void_p

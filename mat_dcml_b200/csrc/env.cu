@@ -33,6 +33,7 @@ struct EnvState {
     uint64_t seed;
     long env_offset;
     int double_reset;
+    int fixed, standalone; // Env(fixed=True) strategy; step(standalone=True) branch on every step
     int shannon;           // Shannon link rates instead of the fixed NON_SHANNON_DATA_RATE
     double* rate_down;     // [B][W] download rate used by Worker.process for both transfers (Shannon mode)
     double* rate_up;       // [B][W] upload rate (observed only)
@@ -166,7 +167,7 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
     if (what == ENV_STEP) {
         // ---- Env.step :65-74, 96-105 ---------------------------------------------------------
         if (active) {
-            e_sel[w] = io.actions[env * L + w];
+            e_sel[w] = st.fixed ? (st.disabled[env * W + w] ? 0.f : 1.f) : io.actions[env * L + w];   // :58-59 vs :73
             for (int i = 0; i < PERIOD; i += 2) {
                 const double2 v = *reinterpret_cast<const double2*>(glw + i);
                 my_lw[i] = v.x; my_lw[i + 1] = v.y;
@@ -178,8 +179,9 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
             for (int i = 0; i < W; ++i) sum = __fadd_rn(sum, e_sel[i]);
             int N = (int)sum;                                              // :71
             const float ratio = io.actions[env * L + W];
-            int K = (int)ceilf(__fmul_rn((float)N, ratio));               // :72 (fp32 product of fp32 actions)
-            si[2] = N == 0;
+            int K = st.fixed ? (int)floor((double)N * 0.7)                 // :61
+                             : (int)ceilf(__fmul_rn((float)N, ratio));     // :72 (fp32 product of fp32 actions)
+            si[2] = N == 0 || st.standalone;                               // :81
             N = min(max(N, 1), W);
             K = min(max(K, 1), N);
             if (si[2]) K = 1;                                              // :82 update_strategy(K=1,N=1)
@@ -458,6 +460,7 @@ extern "C" int dcml_env_create(const dcml_env_cfg* cfg, const double* base_host,
     st.Pr = reinterpret_cast<double*>(s + o_Pr); st.arrive = reinterpret_cast<int*>(s + o_arr); st.kdis = reinterpret_cast<int*>(s + o_k);
     st.disabled = s + o_dis;
     st.shannon = cfg->shannon ? 1 : 0;
+    st.fixed = cfg->fixed ? 1 : 0; st.standalone = cfg->standalone ? 1 : 0;
     st.rate_down = reinterpret_cast<double*>(s + o_rd); st.rate_up = reinterpret_cast<double*>(s + o_ru);
     *out = e;
     return MATAS_OK;

@@ -65,13 +65,16 @@ class _Infos:
 
 class DcmlVecEnv:
     def __init__(self, n_envs, n_workers=100, base_workload=None, seed=1, device="cuda", double_reset=True,
-                 env_offset=0, host_dtype=np.float64, replicate_share_obs=True, shannon=False):
+                 env_offset=0, host_dtype=np.float64, replicate_share_obs=True, shannon=False, fixed=False, standalone=False):
         """``host_dtype`` / ``replicate_share_obs`` only shape what ``reset`` / ``step`` hand back on the
         host: the reference returns float64 observations and L materialised copies of the share_obs row
         (…SingleProcess.py:270); float32 and a broadcast view avoid 0.35 GB of host copies per step at
         16384 x 50."""
         self.host_dtype, self.replicate_share_obs = host_dtype, replicate_share_obs
         self.shannon = bool(shannon)      # Shannon link rates on every reset (reference: reset(shannon_enable=True))
+        # Env(fixed=True): actions ignored, all available workers, K = floor(0.7 N) (…SingleProcess.py:58-62);
+        # standalone: every step is the reference's step(standalone=True) (uncoded on worker 0, reward x 1.5, :81-92)
+        self.fixed, self.standalone = bool(fixed), bool(standalone)
         self.num_envs = self.N = int(n_envs)
         self.W, self.L = int(n_workers), int(n_workers) + 1
         self.n_agents = self.L
@@ -87,7 +90,8 @@ class DcmlVecEnv:
         self.sob_dim = 2 * self.W + 2 if self.shannon else self.W + 2
         self.share_observation_space = [[self.sob_dim]]               # :45
         self.action_space = [Action_Space(2, semi_index=-1, extra=True)]   # :48-49
-        cfg = _cabi.EnvCfg(self.N, self.W, int(seed) & 0xFFFFFFFFFFFFFFFF, int(env_offset), int(bool(double_reset)), int(self.shannon))
+        cfg = _cabi.EnvCfg(self.N, self.W, int(seed) & 0xFFFFFFFFFFFFFFFF, int(env_offset), int(bool(double_reset)), int(self.shannon),
+                           int(self.fixed), int(self.standalone))
         h = ctypes.c_void_p()
         with torch.cuda.device(self.device):
             _cabi.check(_cabi.lib().dcml_env_create(ctypes.byref(cfg), self.base_workload.ctypes.data_as(ctypes.c_void_p),

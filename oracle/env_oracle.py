@@ -147,9 +147,11 @@ class DcmlEnvOracle:
     ``reset() -> (obs, share_obs, ava)``, ``step(actions) -> (obs, share_obs, rews, dones, infos, ava)``.
     ``double_reset`` reproduces ShareDummyVecEnv's second reset on done (VEC:730-736)."""
 
-    def __init__(self, n_envs, n_workers, base_workload=None, seed=1, double_reset=True, env0=0, shannon=False):
+    def __init__(self, n_envs, n_workers, base_workload=None, seed=1, double_reset=True, env0=0, shannon=False,
+                 fixed=False, standalone=False):
         self.B, self.W, self.L = n_envs, n_workers, n_workers + 1
         self.shannon = shannon
+        self.fixed, self.standalone = fixed, standalone       # Env(fixed=True) ENV:58-62; step(standalone=True) ENV:81
         self.rate_down = np.full((n_envs, n_workers), float(DATA_RATE))     # BASE:28-33 NON_SHANNON_DATA_RATE
         self.rate_up = np.full((n_envs, n_workers), float(DATA_RATE))
         self.seed, self.env0, self.double_reset = seed, env0, double_reset
@@ -243,16 +245,21 @@ class DcmlEnvOracle:
     def step_env(self, e, action, draw):
         W = self.W
         action = np.asarray(action).reshape(-1)
-        ratio = action[-1]
-        N = int(sum(action[:-1]))                                                 # ENV:71
-        K = int(math.ceil(N * ratio))                                             # ENV:72 (fp32 product if fp32 actions)
-        sel = action[:-1]
+        if self.fixed:                                                            # ENV:58-62: every available worker, K = 70 %
+            sel = np.array([0 if d else 1 for d in self.disabled[e]])
+            N = int(sum(sel))
+            K = int(np.floor(N * 0.7))
+        else:
+            ratio = action[-1]
+            N = int(sum(action[:-1]))                                             # ENV:71
+            K = int(math.ceil(N * ratio))                                         # ENV:72 (fp32 product if fp32 actions)
+            sel = action[:-1]
         arrive = int(self.arrive[e])
         R, C = self.R[e], self.C[e]
         R = int(R) if float(R).is_integer() else float(R)
         C = int(C) if float(C).is_integer() else float(C)
         jit = draw.jitter()
-        if N == 0:                                                                # ENV:81-92
+        if self.standalone or N == 0:                                             # ENV:81-92
             r = math.ceil(R / 1)
             _, delay, prices = process(self.lw[e, 0], self.Pr[e, 0], r, C, arrive, draw, 0, self.rate_down[e, 0])
             self.lw[e, 0] = jitter_workload(self.base[0], jit[0])

@@ -113,7 +113,7 @@ class _Ctx:
     pass
 
 
-def gen_env(out, W, B, steps, seed, real_workloads, shannon=False):
+def gen_env(out, W, B, steps, seed, real_workloads, shannon=False, variants=False):
     _ref_paths()
     import DCML_ENVs.DCML_utils.DCML_Config as cfg
     if W != 100 or shannon:                        # constants are star-imported
@@ -255,13 +255,43 @@ def gen_env(out, W, B, steps, seed, real_workloads, shannon=False):
     WK.Worker.__init__, WK.Worker.process = worker_init, worker_process
     ENV.Env.reset, ENV.Env.step = env_reset, env_step
 
-    def make(e):
+    def make(e, **kw):
         def fn():
             ctx.e, ctx.w = e, 0
-            env = ENV.Env()
+            env = ENV.Env(**kw)
             env._e = e
             return env
         return fn
+
+    if variants:
+        # Env(fixed=True) (ENV:58-62: actions ignored, all available workers, K = floor(0.7 N)) and step(standalone=True)
+        # (ENV:81-92: uncoded on worker 0, reward x 1.5), each env stepped directly (no vec wrapper, no second reset)
+        L = W + 1
+        res = {"W": W, "B": B, "steps": steps, "seed": seed, "base": base}
+        rng = np.random.RandomState(seed + 5)
+        for tag, kw, skw in (("fx", dict(fixed=True), {}), ("sa", {}, dict(standalone=True))):
+            ctx.draws.clear(); ctx.r.clear()
+            acc = {}
+            for e in range(B):
+                ctx.t = 0
+                env = make(e, **kw)()
+                ctx.r[e] = 0
+                obs, sob, ava = env.reset()
+                rows = {"obs": [obs], "sob": [sob[0]], "ava": [ava], "act": [], "rew": [], "delay": [], "pay": [], "done": []}
+                for t in range(1, steps + 1):
+                    ctx.t = t
+                    sel = (rng.uniform(size=W) < 0.6).astype(np.float32) * ava[:W, 1]
+                    act = np.concatenate([sel, [np.float32(rng.uniform(0.2, 1.0))]]).astype(np.float32)
+                    obs, sob, rew, dones, info, ava = env.step(act.reshape(L, 1), **skw)
+                    for k, v in zip(("obs", "sob", "ava", "act", "rew", "delay", "pay", "done"),
+                                    (obs, sob[0], ava, act, rew[0, 0], info[0]["delay"], info[0]["payment"], dones[0])):
+                        rows[k].append(v)
+                for k, v in rows.items():
+                    acc.setdefault(k, []).append(np.asarray(v))
+            res.update({tag + "_" + k: np.asarray(v) for k, v in acc.items()})      # [env][step ...]
+        np.savez_compressed(out, **res)
+        print("wrote", out)
+        return
 
     if shannon:
         # Shannon links (dormant in the shipped config): only an explicit reset(shannon_enable=True) and the
@@ -437,6 +467,7 @@ FAMILIES = {
     "env_W100": lambda o: gen_env(o, 100, 3, 6, 1, True),
     "env_W20": lambda o: gen_env(o, 20, 6, 8, 2, False),
     "env_W12_shannon": lambda o: gen_env(o, 12, 8, 1, 4, False, shannon=True),
+    "env_W16_variants": lambda o: gen_env(o, 16, 6, 5, 7, False, variants=True),
     "gae": gen_gae,
     "ppo_L11": lambda o: gen_ppo(o, 11, 6, 8),
     "preset_sample1": gen_preset,

@@ -200,3 +200,32 @@ def test_gae_vs_oracle(T, n, cuda_device):
                                       _cabi.ptr(da), _cabi.ptr(dret), _cabi.stream_ptr()))
     np.testing.assert_array_equal(da.cpu().numpy(), adv[..., 0, 0])
     np.testing.assert_array_equal(dret.cpu().numpy()[:-1], ret[:-1, :, 0, 0])
+
+
+@pytest.mark.parametrize("tag,kw", [("fx", dict(fixed=True)), ("sa", dict(standalone=True))])
+def test_env_variants_vs_reference_and_oracle(tag, kw, cuda_device):
+    """Env(fixed=True) and step(standalone=True) of the reference (fixture), then a larger ragged batch against the oracle."""
+    from mat_dcml_b200 import DcmlVecEnv
+    g = golden("env_W16_variants")
+    W, B, steps = int(g["W"]), int(g["B"]), int(g["steps"])
+    env = DcmlVecEnv(B, W, g["base"], seed=int(g["seed"]), double_reset=False, **kw)
+    obs, sob, ava = env.reset()
+    _close(obs, g[tag + "_obs"][:, 0], "obs0"); np.testing.assert_array_equal(ava, g[tag + "_ava"][:, 0])
+    for t in range(1, steps + 1):
+        obs, sob, rew, dones, infos, ava = env.step(g[tag + "_act"][:, t - 1])
+        _close([i[0]["delay"] for i in infos], g[tag + "_delay"][:, t - 1], "delay")
+        _close([i[0]["payment"] for i in infos], g[tag + "_pay"][:, t - 1], "payment")
+        _close(rew[:, 0, 0], g[tag + "_rew"][:, t - 1], "reward")
+        np.testing.assert_array_equal(dones[:, 0], g[tag + "_done"][:, t - 1])
+        _close(obs, g[tag + "_obs"][:, t], "obs"); _close(sob[:, 0], g[tag + "_sob"][:, t], "sob")
+        np.testing.assert_array_equal(ava, g[tag + "_ava"][:, t])
+    W, B = 37, 13
+    env = DcmlVecEnv(B, W, seed=4, **kw)
+    ora = eo.DcmlEnvOracle(B, W, env.base_workload, seed=4, **kw)
+    o1, s1, a1 = env.reset(); o2, s2, a2 = ora.reset()
+    rng = np.random.RandomState(2)
+    for t in range(3):
+        act = np.concatenate([(rng.uniform(size=(B, W)) < 0.5).astype(np.float32) * a2[:, :W, 1],
+                              rng.uniform(0.1, 1.0, size=(B, 1)).astype(np.float32)], 1)[:, :, None]
+        o1, s1, r1, d1, i1, a1 = env.step(act); o2, s2, r2, d2, i2, a2 = ora.step(act)
+        _close(r1, r2); _close(o1, o2); _close(s1, s2); np.testing.assert_array_equal(d1, d2)

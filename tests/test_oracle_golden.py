@@ -164,3 +164,23 @@ def test_ppo_loss_and_gradients_match_reference():
             np.testing.assert_allclose(gr, g["grad/" + str(name)], atol=1e-4 * scale, rtol=1e-4)
         sq += float((gr.astype(np.float64) ** 2).sum())
     assert abs(np.sqrt(sq) - float(g["grad_norm"])) < 1e-4 * float(g["grad_norm"])
+
+
+@pytest.mark.parametrize("tag,kw", [("fx", dict(fixed=True)), ("sa", dict(standalone=True))])
+def test_env_variants_match_reference(tag, kw):
+    """Env(fixed=True) (ENV:58-62) and step(standalone=True) (ENV:81-92), each env of the fixture stepped directly."""
+    g = golden("env_W16_variants")
+    W, B, steps = int(g["W"]), int(g["B"]), int(g["steps"])
+    env = eo.DcmlEnvOracle(B, W, g["base"], seed=int(g["seed"]), double_reset=False, **kw)
+    obs, sob, ava = env.reset()
+    np.testing.assert_allclose(obs, g[tag + "_obs"][:, 0], rtol=1e-12, atol=1e-14)
+    np.testing.assert_array_equal(ava, g[tag + "_ava"][:, 0])
+    for t in range(1, steps + 1):
+        obs, sob, rew, dones, infos, ava = env.step(g[tag + "_act"][:, t - 1])
+        np.testing.assert_allclose([i[0]["delay"] for i in infos], g[tag + "_delay"][:, t - 1], rtol=1e-12)
+        np.testing.assert_allclose([i[0]["payment"] for i in infos], g[tag + "_pay"][:, t - 1], rtol=1e-12)
+        np.testing.assert_allclose(rew[:, 0, 0], g[tag + "_rew"][:, t - 1], rtol=1e-12)
+        np.testing.assert_array_equal(dones[:, 0], g[tag + "_done"][:, t - 1])
+        np.testing.assert_allclose(obs, g[tag + "_obs"][:, t], rtol=1e-12, atol=1e-14)
+        np.testing.assert_allclose(sob[:, 0], g[tag + "_sob"][:, t], rtol=1e-12, atol=1e-14)
+        np.testing.assert_array_equal(ava, g[tag + "_ava"][:, t])
