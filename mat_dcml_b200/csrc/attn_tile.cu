@@ -184,6 +184,16 @@ bool attn_tile_supported(int L) { return L <= 64; }
 
 int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
                      cudaStream_t st) {
+    // tensor-core kernel (attn_tc.cu) unless MATAS_ATTN_TC=0 selects this register-tiled CUDA-core kernel (A/B switch)
+    static int use_tc = -1, n_sm = 0;
+    if (use_tc < 0) {
+        const char* e = getenv("MATAS_ATTN_TC");
+        int dev = 0;
+        CUDA_TRY(cudaGetDevice(&dev));
+        CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+        use_tc = e ? atoi(e) : 1;
+    }
+    if (use_tc) return launch_attn_tc(Q, K, V, Y, lse, n_env, L, causal, n_sm, st);
     // V in registers only where it buys a resident CTA and shared memory is what limits them
     const size_t smem_sm = 227 * 1024, b0 = attn_geom(L, false).floats * sizeof(float) + 1024,
                  b1 = attn_geom(L, true).floats * sizeof(float) + 1024;

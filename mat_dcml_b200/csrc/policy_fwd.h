@@ -142,6 +142,8 @@ int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_s
 bool attn_tile_supported(int L);
 int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
                      cudaStream_t st);
+int launch_attn_tc(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
+                   int n_sm, cudaStream_t st);
 int launch_teacher_forced_tc(const PolicyBufs& b, const TrainBufs& tb, const float* actions, const float* ava, float* logp,
                              float* entropy, long n_tok, int L, int n_disc, cudaStream_t st);
 int launch_enc_embed_tc(const PolicyBufs& b, const TrainBufs& tb, const float* obs, long n_tok, int obs_dim, cudaStream_t st);
