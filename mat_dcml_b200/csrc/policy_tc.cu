@@ -82,6 +82,13 @@ __device__ __forceinline__ void save_row32(float* __restrict__ base, long tile0,
 // BLK 0 then emits QKV of block 1; BLK 1 emits obs_rep, the value head (:138-139) and the decoder's
 // cross-attention queries (plain Q2 for the teacher-forced passes, folded Q2' for the decode).
 // -------------------------------------------------------------------------------------------------
+constexpr int PF_AHEAD = 2 * 148;        // tiles between a CTA and the one that takes its place (2 CTAs on each of 148 SMs)
+// L2 prefetch of the 128 token rows (256 B each) of one tile; 256 threads, two 128-byte lines each
+__device__ __forceinline__ void prefetch_tile_rows(const float* __restrict__ base, long tile0, long n_tok, int tid) {
+    const long g = tile0 + (tid >> 1);
+    if (g < n_tok) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + g * 64 + (tid & 1) * 32));
+}
+
 template <int BLK>
 __global__ void __launch_bounds__(NT, 2)
 enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int for_decode, const float* __restrict__ y_in) {
@@ -90,6 +97,13 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     const int tid = threadIdx.x;
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
+    // pull this tile's inputs, and those of the tile that will follow on this SM (CTAs start in index order, two per SM),
+    // into L2 while the prologue (TMEM allocation, barrier set-up, first weight blob) runs: the first loads of a tile
+    // are otherwise what its warps wait on longest
+    prefetch_tile_rows(b.X, tile0, n_tok, tid);
+    if (y_in) prefetch_tile_rows(y_in, tile0, n_tok, tid);
+    prefetch_tile_rows(b.X, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
+    if (y_in) prefetch_tile_rows(y_in, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
     Ring ring;
     if (BLK == 1 && for_decode) ring.init(s.ring, s.bars, b.w, c_tc_enc_blk1_dec, 8, 8, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
     else ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_tc_enc_blk0 : c_tc_enc_blk1, 6, 6, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
