@@ -75,6 +75,16 @@ attn_tc_kernel(const float* __restrict__ Q, const float* __restrict__ K, const f
         const long env0 = tile * EPT;
         const long tok0 = (env0 + e_row) * L;                               // first token of this row's env
         const bool row_live = q < L && env0 + e_row < n_env;
+        {   // L2 prefetch of the next tile's Q / K / V rows (EPT * L contiguous token rows each, two 128-byte lines per row)
+            const long nt0 = (tile + gridDim.x) * EPT * (long)L, n_tok = n_env * (long)L;
+            const int lines = EPT * L * 2;
+            for (int i = tid; i < 3 * lines; i += ATC_NT) {
+                const int mtx = i / lines, ln = i - mtx * lines;
+                const long tok = nt0 + (ln >> 1);
+                const float* src = mtx == 0 ? Q : (mtx == 1 ? K : V);
+                if (tok < n_tok) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + tok * 64 + (ln & 1) * 32));
+            }
+        }
         // ---- stage Q (block-diagonal over the heads), K, V as fp16 hi / lo operands; unused token slots are zero rows ------
 #pragma unroll
         for (int i = 0; i < 4; ++i) {

@@ -9,6 +9,8 @@
 // Philox draws (common.cuh / DESIGN.md).  HBM traffic per env-step is the 160 B/worker workload
 // table read + written, the Pr / flag state, and the observation rows.
 #include "../../include/matas_b200.h"
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -430,7 +432,11 @@ extern "C" int dcml_env_create(const dcml_env_cfg* cfg, const double* base_host,
         return MATAS_ERR_CUDA;
     }
     const int tpe = (W + 31) / 32 * 32;
-    e->epb = tpe >= 256 ? 1 : 256 / tpe;
+    // envs per CTA: the CTA barriers of a step wait for the slowest worker of every env in the block (the slot loops of
+    // Worker.process have data-dependent trip counts), so small blocks lose less to that imbalance (MATAS_ENV_THREADS tunes)
+    static int target = -1;
+    if (target < 0) { const char* ev = getenv("MATAS_ENV_THREADS"); target = ev ? atoi(ev) : 64; if (target < 32) target = 32; }
+    e->epb = tpe >= target ? 1 : target / tpe;
     e->block = e->epb * tpe;
     e->smem = (size_t)e->block * (LWS + 1 + 3 + 2) * 8 + (size_t)e->epb * 8 * 8 + (size_t)e->block * (4 + 4) +
               (size_t)e->epb * 8 * 4 + e->block + 16;
