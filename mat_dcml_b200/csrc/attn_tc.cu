@@ -197,10 +197,196 @@ attn_tc_kernel(const float* __restrict__ Q, const float* __restrict__ K, const f
     if (warp == 0) tc::tmem_dealloc(tmem);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// 64 < n_agent <= 256: one env per CTA pass, all of its K and V tiles (64 keys each) staged once; per query tile of 64
+// queries (128 rows = 2 heads) the scores against every visible key tile go to their own 128 TMEM columns, the row
+// maximum comes from a first pass over them, and a second pass turns one key tile at a time into probabilities (A
+// operand) and accumulates O += P_kt . V_kt in the columns the first score tile occupied (it has been consumed by then).
+// O is normalised in the epilogue.  512 TMEM columns and 163 KB of shared memory: one CTA per SM.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int LONG_KT = 4;                   // key / query tiles per env at most (n_agent <= 256)
+constexpr size_t ATC_LONG_SMEM = 1024 + 2 * (size_t)tc::A_PART + 2 * LONG_KT * 2 * (size_t)KV_PART + 2 * 128 * 2 * sizeof(float) + 64;
+
+template <bool CAUSAL>
+__global__ void __launch_bounds__(ATC_NT, 1)
+attn_tc_long_kernel(const float* __restrict__ Q, const float* __restrict__ K, const float* __restrict__ V, float* __restrict__ Y,
+                    float* __restrict__ lse, long n_env, int L) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* base = smem_align1024(smem_raw);
+    unsigned char* sA = base;                                       // block-diagonal Q tile, later one P tile at a time
+    unsigned char* sK = sA + 2 * tc::A_PART;                        // [key tile][hi | lo][64 keys][128 B]
+    unsigned char* sV = sK + LONG_KT * 2 * KV_PART;
+    float* sMax = reinterpret_cast<float*>(sV + LONG_KT * 2 * KV_PART);
+    float* sSum = sMax + 256;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sSum + 256);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = (warp & 3) * 32 + (tid & 31), half = warp >> 2;
+    const int h = row >> 6, q = row & 63;
+    if (tid == 0) { mbar_init(bar, 1); mbar_fence_init(); }
+    if (warp == 0) tc::tmem_alloc_n<512>(tmem_slot);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t a_addr = smem_u32(sA), k_addr = smem_u32(sK), v_addr = smem_u32(sV), bar_addr = smem_u32(bar);
+    const uint32_t idesc_mn = (1u << 4) | (1u << 16) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const float scale = 0.17677669529663687f * 1.4426950408889634f;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int n_t = (L + 63) >> 6;                                  // key tiles = query tiles
+    const uint32_t lane_base = tmem + ((uint32_t)(row & ~31) << 16) + half * 32;
+    uint32_t phase = 0;
+    auto wait_mma = [&]() {
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        tc::fence_after_sync();
+    };
+
+    for (long env = blockIdx.x; env < n_env; env += gridDim.x) {
+        const long tok0 = env * L;
+        // ---- stage every K / V tile of the env (token slots >= L are zero rows) ----------------------------------------
+        for (int idx = tid; idx < n_t * 64 * 16; idx += ATC_NT) {
+            const int t = idx >> 4, l = idx & 15, kt = t >> 6, r = t & 63;
+            float4 kv = z4, vv = z4;
+            if (t < L) {
+                kv = __ldg(reinterpret_cast<const float4*>(K + (tok0 + t) * 64) + l);
+                vv = __ldg(reinterpret_cast<const float4*>(V + (tok0 + t) * 64) + l);
+            }
+            tc::store_operand4(sK + kt * 2 * KV_PART, r, l, kv, KV_PART);
+            tc::store_operand4(sV + kt * 2 * KV_PART, r, l, vv, KV_PART);
+        }
+        for (int qt = 0; qt < n_t; ++qt) {
+            const int qg = qt * 64 + q;                             // this row's query
+            const bool row_live = qg < L;
+            const int nkt = CAUSAL ? qt + 1 : n_t;                  // visible key tiles
+            const int nk = CAUSAL ? min(qg + 1, L) : L;             // visible keys of this row
+            // ---- Q tile, block-diagonal over the heads ---------------------------------------------------------
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int idx = tid + i * ATC_NT, t = idx >> 4, l = idx & 15;
+                float4 qv = z4;
+                if (qt * 64 + t < L) qv = __ldg(reinterpret_cast<const float4*>(Q + (tok0 + qt * 64 + t) * 64) + l);
+                const int hh = l >> 3;
+                tc::store_operand4(sA, hh * 64 + t, l, qv);
+                tc::store_operand4(sA, (1 - hh) * 64 + t, l, z4);
+            }
+            tc::publish();
+            if (tc::issuer_warp()) {
+                const uint32_t au = tc::uni(a_addr), ku = tc::uni(k_addr), du = tc::uni(tmem), bu = tc::uni(bar_addr);
+                if (tc::elect_one()) {
+                    for (int kt = 0; kt < nkt; ++kt) tc::mma_set(du + kt * 128, au, ku + kt * 2 * KV_PART, false);
+                    tc::mma_commit_saddr(bu);
+                }
+            }
+            wait_mma();
+            // ---- pass 1: row maximum over every visible key ----------------------------------------------------
+            float m = -INFINITY;
+            for (int kt = 0; kt < nkt; ++kt) {
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v1[16], v2[16];
+                    TC_LD16(v1, lane_base + kt * 128 + c * 16);
+                    TC_LD16(v2, lane_base + kt * 128 + 64 + c * 16);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const int k0 = kt * 64 + half * 32 + c * 16;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float sc = fmaf(__uint_as_float(v2[i]), 1.0f / 2048.0f, __uint_as_float(v1[i])) * scale;
+                        if (k0 + i < nk) m = fmaxf(m, sc);
+                    }
+                }
+            }
+            sMax[row * 2 + half] = m;
+            __syncthreads();
+            m = fmaxf(sMax[row * 2], sMax[row * 2 + 1]);          // key 0 is always visible: finite
+            // ---- pass 2: one key tile at a time: probabilities -> A operand, O += P_kt . V_kt ---------------------------
+            float sum = 0.f;
+            for (int kt = 0; kt < nkt; ++kt) {
+                float p[32];
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v1[16], v2[16];
+                    TC_LD16(v1, lane_base + kt * 128 + c * 16);
+                    TC_LD16(v2, lane_base + kt * 128 + 64 + c * 16);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const int k0 = kt * 64 + half * 32 + c * 16;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float sc = fmaf(__uint_as_float(v2[i]), 1.0f / 2048.0f, __uint_as_float(v1[i])) * scale;
+                        p[c * 16 + i] = k0 + i < nk ? ex2f(sc - m) : 0.f;
+                        sum += p[c * 16 + i];
+                    }
+                }
+                if (kt > 0) wait_mma();                            // the previous product is done with the A operand
+                tc::store_operand32(sA, row, half, p);
+                tc::publish();                                     // also: every thread has read score tile 0 before O overwrites it
+                if (tc::issuer_warp()) {
+                    const uint32_t au = tc::uni(a_addr), vu = tc::uni(v_addr + kt * 2 * KV_PART), du = tc::uni(tmem), bu = tc::uni(bar_addr);
+                    if (tc::elect_one()) {
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint32_t acc = (kt > 0 || ks > 0) ? 1u : 0u;
+                            const uint64_t ah = tc::make_desc(au + ks * 32), al = tc::make_desc(au + tc::A_PART + ks * 32);
+                            const uint64_t bh = desc_mn(vu + ks * 2048), bl = desc_mn(vu + KV_PART + ks * 2048);
+                            tc::mma_f16(du, ah, bh, idesc_mn, acc);
+                            tc::mma_f16(du + 64, ah, bl, idesc_mn, acc);
+                            tc::mma_f16(du + 64, al, bh, idesc_mn, 1u);
+                        }
+                        tc::mma_commit_saddr(bu);
+                    }
+                }
+            }
+            sSum[row * 2 + half] = sum;
+            wait_mma();                                            // last product
+            __syncthreads();
+            sum = sSum[row * 2] + sSum[row * 2 + 1];
+            const float inv = 1.0f / sum;
+            if (lse && half == 0 && row_live) lse[(tok0 + qg) * 2 + h] = m * 0.6931471805599453f + logf(sum);
+            {
+                float4* y = reinterpret_cast<float4*>(Y + (tok0 + qg) * 64 + h * 32);
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v1[16], v2[16];
+                    TC_LD16(v1, lane_base + c * 16);
+                    TC_LD16(v2, lane_base + 64 + c * 16);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (row_live && half == h) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            y[c * 4 + j] = make_float4(fmaf(__uint_as_float(v2[4 * j]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j])) * inv,
+                                                       fmaf(__uint_as_float(v2[4 * j + 1]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 1])) * inv,
+                                                       fmaf(__uint_as_float(v2[4 * j + 2]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 2])) * inv,
+                                                       fmaf(__uint_as_float(v2[4 * j + 3]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 3])) * inv);
+                    }
+                }
+            }
+            // the next Q tile / env overwrites A and (after its publish barrier) the score columns
+        }
+        __syncthreads();                                           // K / V tiles are restaged for the next env
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc_n<512>(tmem);
+}
+
 }  // namespace
 
 int launch_attn_tc(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
                    int n_sm, cudaStream_t st) {
+    if (L > 64) {
+        ARG_CHECK(L <= 64 * LONG_KT, "attn_tc: n_agent %d > %d", L, 64 * LONG_KT);
+        const unsigned grid = (unsigned)(n_env < n_sm ? n_env : n_sm);
+        if (causal) {
+            CUDA_TRY(cudaFuncSetAttribute(attn_tc_long_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATC_LONG_SMEM));
+            attn_tc_long_kernel<true><<<grid, ATC_NT, ATC_LONG_SMEM, st>>>(Q, K, V, Y, lse, n_env, L);
+        } else {
+            CUDA_TRY(cudaFuncSetAttribute(attn_tc_long_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATC_LONG_SMEM));
+            attn_tc_long_kernel<false><<<grid, ATC_NT, ATC_LONG_SMEM, st>>>(Q, K, V, Y, lse, n_env, L);
+        }
+        CUDA_TRY(cudaGetLastError());
+        return MATAS_OK;
+    }
     const int lp = L <= 16 ? 16 : (L <= 32 ? 32 : 64);
     const long n_tiles = (n_env + 64 / lp - 1) / (64 / lp), resident = 3L * n_sm;
     const unsigned grid = (unsigned)(n_tiles < resident ? n_tiles : resident);

@@ -182,18 +182,25 @@ attn_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, const 
 
 bool attn_tile_supported(int L) { return L <= 64; }
 
+static bool attn_use_tc() {
+    static int use_tc = -1;          // MATAS_ATTN_TC=0 selects the register-tiled CUDA-core kernel below (A/B switch)
+    if (use_tc < 0) { const char* e = getenv("MATAS_ATTN_TC"); use_tc = e ? atoi(e) : 1; }
+    return use_tc != 0;
+}
+// forward passes can take the separate attention kernel up to n_agent 256 (tensor-core kernel with key tiles)
+bool attn_fwd_supported(int L) { return L <= 64 || (attn_use_tc() && L <= 256); }
+
 int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
                      cudaStream_t st) {
     // tensor-core kernel (attn_tc.cu) unless MATAS_ATTN_TC=0 selects this register-tiled CUDA-core kernel (A/B switch)
-    static int use_tc = -1, n_sm = 0;
-    if (use_tc < 0) {
-        const char* e = getenv("MATAS_ATTN_TC");
+    static int n_sm = 0;
+    if (n_sm == 0) {
         int dev = 0;
         CUDA_TRY(cudaGetDevice(&dev));
         CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-        use_tc = e ? atoi(e) : 1;
     }
-    if (use_tc) return launch_attn_tc(Q, K, V, Y, lse, n_env, L, causal, n_sm, st);
+    if (attn_use_tc()) return launch_attn_tc(Q, K, V, Y, lse, n_env, L, causal, n_sm, st);
+    ARG_CHECK(L <= 64, "attn_env_kernel: n_agent %d > 64", L);
     // V in registers only where it buys a resident CTA and shared memory is what limits them
     const size_t smem_sm = 227 * 1024, b0 = attn_geom(L, false).floats * sizeof(float) + 1024,
                  b1 = attn_geom(L, true).floats * sizeof(float) + 1024;

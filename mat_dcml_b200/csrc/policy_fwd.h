@@ -140,6 +140,7 @@ bool policy_use_tc();
 int decode_tc_geometry(long B, int n_sm, int* grid, long* slots);
 int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st);
 bool attn_tile_supported(int L);
+bool attn_fwd_supported(int L);
 int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
                      cudaStream_t st);
 int launch_attn_tc(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,

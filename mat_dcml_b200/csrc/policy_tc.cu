@@ -566,7 +566,7 @@ int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values
 static bool use_attn_tile(int L) {
     static int tiled = -1;           // MATAS_ATTN_TILE=0 keeps the attention fused into the block kernels (A/B measurements)
     if (tiled < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tiled = e ? atoi(e) : 1; }
-    return tiled && attn_tile_supported(L);
+    return tiled && attn_fwd_supported(L);
 }
 
 int launch_teacher_forced_tc(const PolicyBufs& b, const TrainBufs& tb, const float* actions, const float* ava, float* logp,
