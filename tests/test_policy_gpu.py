@@ -139,9 +139,10 @@ def test_ragged_batches_vs_oracle(B, cuda_device):
     np.testing.assert_allclose(_np(lp).reshape(B, L)[same], lpo.numpy().reshape(B, L)[same], atol=TOL)
 
 
-@pytest.mark.parametrize("L,B", [(2, 5), (64, 3), (65, 3), (33, 37)])
+@pytest.mark.parametrize("L,B", [(2, 5), (64, 3), (65, 3), (33, 37), (16, 9), (17, 5), (32, 7), (130, 2), (192, 1), (256, 1)])
 def test_agent_count_boundaries_vs_oracle(L, B, cuda_device):
-    """n_agent around the tiled-attention limit (64) and tiles that straddle envs / end in a partial tile."""
+    """n_agent around the limits of the attention kernels (16 / 32 / 64 token slots per env in one MMA tile, key tiles of 64
+    up to the maximum of 256 agents) and tiles that straddle envs / end in a partial tile."""
     sd = mo.make_weights(30 + L, L)
     m = make_model(L, sd)
     rng = np.random.RandomState(L)
