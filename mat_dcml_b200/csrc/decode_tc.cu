@@ -221,7 +221,7 @@ __device__ __forceinline__ float ex2(float x) {          // 2^x, x <= 0 here; de
 // Env row r attends to nk cached rows at cache + r * slot_stride; rows r >= n_valid store zero contexts.
 //
 // The key loop is the kernel's hot loop (three attentions x (j + 1) keys per position), so it is written for
-// instruction count: `rows` is a multiple of 8 (decode_tc_rows), hence whole warps enter and every loop bound is
+// instruction count: `rows` is a multiple of 4 (decode_tc_rows; a warp holds four lane groups), hence whole warps enter and every loop bound is
 // warp-uniform (nk), which allows full-mask shuffles; each half of a lane group keeps the head it collects as
 // "own" and the other as "oth" (lanes 0-3: own = head 0, lanes 4-7: own = head 1), so no per-key selects are
 // needed; batches of two keys run unpredicated while six keys remain, and a predicated tail finishes the row.
@@ -334,79 +334,105 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
 
 // The same attention with SIXTEEN lanes per env (lane l holds columns 4l..4l+3 of every row) for tiles of at most
 // 32 envs, where 8 lanes per env would leave half of the CTA's threads without work (small batches, large L).
-// Four keys per batch, the next batch in flight in registers.
+// Four keys per batch, the next batch in flight in registers; written like the 8-lane version: warp-uniform trip
+// counts (two lane groups per warp, `rows` even), full-mask shuffles, lanes 0-7 collect head 0 and lanes 8-15 head 1
+// ("own"), unpredicated batches while twelve keys remain and a predicated tail.
 template <bool GQ, int PF>
 __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                         const float* cache, long slot_stride, int rows, int n_valid, int nk,
                                                         unsigned char* U, unsigned char* V) {
     constexpr int KB = 4;
+    constexpr unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, grp = tid >> 4, l = tid & 15;
-    const unsigned hmask = 0xffffu << (tid & 16);
     const bool up = (l & 8) != 0;
     const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int r = grp; r < rows; r += NTD / 16) {
-        const int nr = r < n_valid ? nk : 0;
-        float4 qa, qb;
+        const bool valid = r < n_valid;
+        const int rr = valid ? r : n_valid - 1;      // rows past the batch walk a live env's rows (same trip counts) and store zeros
+        float4 q_own, q_oth;
         if (GQ) {
-            qa = nr ? __ldg(reinterpret_cast<const float4*>(q0 + (long)r * q_stride) + l) : z4;
-            qb = nr ? __ldg(reinterpret_cast<const float4*>(q1 + (long)r * q_stride) + l) : z4;
+            q_own = __ldg(reinterpret_cast<const float4*>((up ? q1 : q0) + (long)rr * q_stride) + l);
+            q_oth = __ldg(reinterpret_cast<const float4*>((up ? q0 : q1) + (long)rr * q_stride) + l);
         } else {
-            qa = *reinterpret_cast<const float4*>(q0 + r * XS + l * 4);
-            qb = *reinterpret_cast<const float4*>(q1 + r * XS + l * 4);
+            q_own = *reinterpret_cast<const float4*>((up ? q1 : q0) + rr * XS + l * 4);
+            q_oth = *reinterpret_cast<const float4*>((up ? q0 : q1) + rr * XS + l * 4);
         }
-        const float4* xp = reinterpret_cast<const float4*>(cache + (long)r * slot_stride) + l;     // row t: xp[t * 16]
-        float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-        float4 c0 = z4, c1 = z4;
-        auto batch = [&](const float4 (&x)[KB], int t0) {
-            float s0[KB], s1[KB];
+        const float4* xp = reinterpret_cast<const float4*>(cache + (long)rr * slot_stride) + l;     // row t: xp[t * 16]
+        const int pf_lim = (PF > 0 && (l & 7) == 0) ? nk - 2 * PF : -(1 << 30);                  // prefetch row t + 2 PF while t < pf_lim
+        const float4* pfp = xp + 2 * PF * 16;
+        float m_own = -INFINITY, m_oth = -INFINITY, l_own = 0.f, l_oth = 0.f;
+        float4 c_own = z4, c_oth = z4;
+        auto batch = [&](const float4 (&x)[KB], int t0, auto masked) {
+            float so[KB], st[KB];
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
-                const float p0 = qa.x * x[i].x + qa.y * x[i].y + qa.z * x[i].z + qa.w * x[i].w;
-                const float p1 = qb.x * x[i].x + qb.y * x[i].y + qb.z * x[i].z + qb.w * x[i].w;
-                float v = up ? p1 : p0;                       // lanes 0-7 collect head 0, lanes 8-15 head 1
-                v += __shfl_xor_sync(hmask, up ? p0 : p1, 8);
-                v += __shfl_xor_sync(hmask, v, 4);
-                v += __shfl_xor_sync(hmask, v, 2);
-                v += __shfl_xor_sync(hmask, v, 1);
-                const float o = __shfl_xor_sync(hmask, v, 8);
-                const bool ok = t0 + i < nr;
-                s0[i] = ok ? (up ? o : v) : -INFINITY;
-                s1[i] = ok ? (up ? v : o) : -INFINITY;
+                const float p_own = q_own.x * x[i].x + q_own.y * x[i].y + q_own.z * x[i].z + q_own.w * x[i].w;
+                const float p_oth = q_oth.x * x[i].x + q_oth.y * x[i].y + q_oth.z * x[i].z + q_oth.w * x[i].w;
+                float v = p_own + __shfl_xor_sync(FULL, p_oth, 8);
+                v += __shfl_xor_sync(FULL, v, 4);
+                v += __shfl_xor_sync(FULL, v, 2);
+                v += __shfl_xor_sync(FULL, v, 1);
+                const float o = __shfl_xor_sync(FULL, v, 8);
+                if (decltype(masked)::value) {
+                    const bool ok = t0 + i < nk;
+                    so[i] = ok ? v : -INFINITY;
+                    st[i] = ok ? o : -INFINITY;
+                } else {
+                    so[i] = v; st[i] = o;
+                }
             }
-            float n0 = m0, n1 = m1;
+            float n_own = m_own, n_oth = m_oth;
 #pragma unroll
-            for (int i = 0; i < KB; ++i) { n0 = fmaxf(n0, s0[i]); n1 = fmaxf(n1, s1[i]); }
-            const float a0 = ex2(m0 - n0), a1 = ex2(m1 - n1);
-            l0 *= a0; l1 *= a1;
-            c0.x *= a0; c0.y *= a0; c0.z *= a0; c0.w *= a0;
-            c1.x *= a1; c1.y *= a1; c1.z *= a1; c1.w *= a1;
+            for (int i = 0; i < KB; ++i) { n_own = fmaxf(n_own, so[i]); n_oth = fmaxf(n_oth, st[i]); }
+            const float a_own = ex2(m_own - n_own), a_oth = ex2(m_oth - n_oth);
+            l_own *= a_own; l_oth *= a_oth;
+            scale4_2(c_own, a_own); scale4_2(c_oth, a_oth);
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
-                const float p0 = ex2(s0[i] - n0), p1 = ex2(s1[i] - n1);
-                l0 += p0; l1 += p1;
-                c0.x = fmaf(p0, x[i].x, c0.x); c0.y = fmaf(p0, x[i].y, c0.y); c0.z = fmaf(p0, x[i].z, c0.z); c0.w = fmaf(p0, x[i].w, c0.w);
-                c1.x = fmaf(p1, x[i].x, c1.x); c1.y = fmaf(p1, x[i].y, c1.y); c1.z = fmaf(p1, x[i].z, c1.z); c1.w = fmaf(p1, x[i].w, c1.w);
+                const float p_own = ex2(so[i] - n_own), p_oth = ex2(st[i] - n_oth);
+                l_own += p_own; l_oth += p_oth;
+                axpy4_2(c_own, p_own, x[i]); axpy4_2(c_oth, p_oth, x[i]);
             }
-            m0 = n0; m1 = n1;
+            m_own = n_own; m_oth = n_oth;
         };
-        auto fetch = [&](float4 (&x)[KB], int t0) {
+        auto fetch_masked = [&](float4 (&x)[KB], int t0) {
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
-                x[i] = t0 + i < nr ? xp[(long)(t0 + i) * 16] : z4;
-                if (PF > 0 && (l & 7) == 0 && t0 + i + 2 * PF < nr) asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + (long)(t0 + i + 2 * PF) * 16));
+                x[i] = t0 + i < nk ? xp[(long)(t0 + i) * 16] : z4;
+                if (t0 + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pfp + (long)(t0 + i) * 16));
             }
         };
         float4 x[KB], y[KB];
-        fetch(x, 0);
-        for (int t0 = 0; t0 < nr; t0 += 2 * KB) {
-            fetch(y, t0 + KB);
-            batch(x, t0);
-            fetch(x, t0 + 2 * KB);
-            if (t0 + KB < nr) batch(y, t0 + KB);
+        fetch_masked(x, 0);
+        int t0 = 0;
+        {   // unpredicated part: keys t0 .. t0 + 11 exist
+            const float4* xt = xp;
+            const float4* pt = pfp;
+            for (; t0 + 3 * KB <= nk; t0 += 2 * KB, xt += 2 * KB * 16, pt += 2 * KB * 16) {
+#pragma unroll
+                for (int i = 0; i < KB; ++i) {
+                    y[i] = xt[(KB + i) * 16];
+                    if (t0 + KB + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (KB + i) * 16));
+                }
+                batch(x, t0, std::false_type{});
+#pragma unroll
+                for (int i = 0; i < KB; ++i) {
+                    x[i] = xt[(2 * KB + i) * 16];
+                    if (t0 + 2 * KB + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (2 * KB + i) * 16));
+                }
+                batch(y, t0 + KB, std::false_type{});
+            }
         }
-        const float i0 = nr > 0 ? 1.0f / l0 : 0.f, i1 = nr > 0 ? 1.0f / l1 : 0.f;
-        tc::store_operand4(U, r, l, make_float4(c0.x * i0, c0.y * i0, c0.z * i0, c0.w * i0));
-        tc::store_operand4(V, r, l, make_float4(c1.x * i1, c1.y * i1, c1.z * i1, c1.w * i1));
+        for (; t0 < nk; t0 += 2 * KB) {          // predicated tail (at most 11 keys)
+            fetch_masked(y, t0 + KB);
+            batch(x, t0, std::true_type{});
+            fetch_masked(x, t0 + 2 * KB);
+            if (t0 + KB < nk) batch(y, t0 + KB, std::true_type{});
+        }
+        const float i_own = valid && nk > 0 ? 1.0f / l_own : 0.f, i_oth = valid && nk > 0 ? 1.0f / l_oth : 0.f;
+        if (!valid) { c_own = z4; c_oth = z4; }       // NaN-safe: never multiply walked garbage
+        tc::store_operand4(up ? V : U, r, l, make_float4(c_own.x * i_own, c_own.y * i_own, c_own.z * i_own, c_own.w * i_own));
+        tc::store_operand4(up ? U : V, r, l, make_float4(c_oth.x * i_oth, c_oth.y * i_oth, c_oth.z * i_oth, c_oth.w * i_oth));
     }
 }
 
@@ -708,11 +734,12 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
 
 }  // namespace
 
-// rows per tile: spread the envs over the SMs (one CTA each), a multiple of 8, at most 128
+// rows per tile: spread the envs over the SMs (one CTA each), a multiple of 4 (whole warps of four 8-lane groups), at most
+// 128.  4096 envs on 148 SMs: 28 rows on 147 CTAs (a multiple of 8 would put 32 rows on 128 CTAs and leave 20 SMs idle)
 int decode_tc_rows(long B, int n_sm) {
     long r = (B + n_sm - 1) / n_sm;
-    r = (r + 7) / 8 * 8;
-    if (r < 8) r = 8;
+    r = (r + 3) / 4 * 4;
+    if (r < 4) r = 4;
     if (r > MAXR) r = MAXR;
     return (int)r;
 }
