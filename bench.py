@@ -298,18 +298,22 @@ def run_ours(ns):
     except (OSError, ValueError):
         pass
     # HBM bound: at every position j of every pass the decode re-reads the j+1 cached 256-byte layer-input rows
-    # of 3 attentions (block-0 cross, block-1 self and cross; block-0 self-attention runs on token-code counts and
-    # reads nothing), writes 3 new rows, reads 4 folded query rows + the obs_rep row (256 B each) and writes the
-    # outputs; arithmetic intensity is ~7 flop/byte, below the fp32 ridge, so HBM is the roof.
+    # of its cached attentions, writes one new row per cached attention, reads 4 folded query rows + the obs_rep row
+    # (256 B each) and writes the outputs; arithmetic intensity is ~7 flop/byte, below the fp32 ridge, so HBM is the
+    # roof.  Cached attentions: block-1 self and cross always (block-0 self-attention runs on token-code counts and
+    # reads nothing); block-0 cross only in the deterministic decode -- the stochastic decode gathers those keys from
+    # a shared L2-resident table (decode_tc.cu: x1_table_kernel, L(L+1) rows computed once per weight update).
     visits = decode_schedule_positions(L, det, stride)
-    alg_bytes = B * (sum(3 * 256 * (j + 1) + 3 * 256 + 5 * 256 + 16 for j in visits))
+    tab = (not det) and os.environ.get("MATAS_DECODE_TAB", "1") != "0" and os.environ.get("MATAS_TC", "1") != "0"
+    n_cached = 2 if tab else 3
+    alg_bytes = B * (sum(n_cached * 256 * (j + 1) + n_cached * 256 + 5 * 256 + 16 for j in visits))
     hbm_peak = peaks.get("hbm_gbs", 6500.0)
     hbm_src = ("measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6.5 TB/s (B200_PROFILING.md)")
     achieved_gbs = alg_bytes / (dec_ms * 1e-3) / 1e9
     roofline = {"kernel": "decode_tc_kernel", "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": hbm_src,
                 "launch_ms": dec_ms, "launches_timed": tn.value, "share_of_step": dec_ms / (ms / ns.steps),
-                "algorithmic_bytes_per_launch": alg_bytes,
+                "algorithmic_bytes_per_launch": alg_bytes, "cached_attentions": n_cached,
                 "compute": {"algorithmic_flops_per_launch": 2.0 * mac, "achieved_tflops": achieved,
                             "fp32_ffma_peak_tflops": fp32.value, "frac_fp32": achieved / fp32.value if fp32.value else None,
                             "bf16_tensor_peak_tflops": tensor_peak, "tensor_peak_source": peak_src,

@@ -119,7 +119,8 @@ struct matas_policy {
     float* d_tok = nullptr;      // 21 token buffers [cap][64]
     size_t kv_cap = 0;
     float* d_kv = nullptr;
-    PolicyBufs bufs;
+    float* d_x1tab = nullptr;    // [L (L + 1)][64] block-0 cross-attention inputs of the stochastic decode (decode_tc.cu)
+    PolicyBufs bufs = {};
     // training: saved activations + backward work buffers, gradient offsets
     GradMap gm;
     TrainBufs tb;
@@ -297,7 +298,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
 
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
-    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_half); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_train); cudaFree(p->d_phase);
+    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_half); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_x1tab); cudaFree(p->d_train); cudaFree(p->d_phase);
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
@@ -319,6 +320,13 @@ extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void
     fold_kernel<<<(unsigned)p->folds.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_folds);
     half_kernel<<<(unsigned)p->n_half, 256, 0, (cudaStream_t)stream>>>(p->d_packed, p->d_half);
     CUDA_TRY(cudaGetLastError());
+    if (policy_use_tc()) {
+        const int L = p->cfg.n_agent;
+        if (!p->d_x1tab) CUDA_TRY(cudaMalloc(&p->d_x1tab, (size_t)L * (L + 1) * 64 * sizeof(float)));
+        int rc_ = launch_x1_table(p->d_packed, p->d_x1tab, L, (cudaStream_t)stream);
+        if (rc_) return rc_;
+        p->bufs.x1tab = p->d_x1tab;
+    }
     p->weights_set = true;
     return MATAS_OK;
 }

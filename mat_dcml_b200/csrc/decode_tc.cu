@@ -38,6 +38,15 @@ __constant__ int c_tc_decode[STEP_BLOBS] = {
     lay::hb(lay::dec_blob(1, lay::DM0)), lay::hb(lay::dec_blob(1, lay::DM2)),
     lay::hb(lay::DEC_H0)};
 
+// the same sequence without block 0's output maps (their result comes from the table, x1_table_kernel)
+__constant__ int c_tc_decode_tab[STEP_BLOBS - 2] = {
+    lay::hb(lay::fold_blob(0, lay::FC0)), lay::hb(lay::fold_blob(0, lay::FC1)),
+    lay::hb(lay::dec_blob(0, lay::DM0)), lay::hb(lay::dec_blob(0, lay::DM2)),
+    lay::hb(lay::fold_blob(1, lay::FA0)), lay::hb(lay::fold_blob(1, lay::FA1)), lay::hb(lay::fold_blob(1, lay::FB0)),
+    lay::hb(lay::fold_blob(1, lay::FB1)), lay::hb(lay::fold_blob(1, lay::FC0)), lay::hb(lay::fold_blob(1, lay::FC1)),
+    lay::hb(lay::dec_blob(1, lay::DM0)), lay::hb(lay::dec_blob(1, lay::DM2)),
+    lay::hb(lay::DEC_H0)};
+
 struct DSmem {
     unsigned char* U;      // operand buffers [hi | lo][128][128 B]
     unsigned char* V;
@@ -225,10 +234,13 @@ __device__ __forceinline__ float ex2(float x) {          // 2^x, x <= 0 here; de
 // warp-uniform (nk), which allows full-mask shuffles; each half of a lane group keeps the head it collects as
 // "own" and the other as "oth" (lanes 0-3: own = head 0, lanes 4-7: own = head 1), so no per-key selects are
 // needed; batches of two keys run unpredicated while six keys remain, and a predicated tail finishes the row.
-template <bool GQ, int PF>
+// TAB: the keys are rows of the shared block-0 table (x1_table_kernel) instead of a per-env cache: key t of env r is
+// row t (t + 1) + 2 n3 + a_{t-1}, n3 = ones among the env's actions a_0 .. a_{t-1} (its bitset at bits + 8 r); the row
+// indices are produced in key order by a running popcount, and nothing is prefetched (the table lives in L2).
+template <bool GQ, int PF, bool TAB = false>
 __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                       const float* cache, long slot_stride, int rows, int n_valid, int nk,
-                                                      unsigned char* U, unsigned char* V) {
+                                                      unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr) {
     constexpr int KB = 2;
     constexpr unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, grp = tid >> 3, g = tid & 7;
@@ -251,10 +263,19 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
             qa_oth = *reinterpret_cast<const float4*>(pt + g * 4);
             qb_oth = *reinterpret_cast<const float4*>(pt + 32 + g * 4);
         }
-        const float4* xp = reinterpret_cast<const float4*>(cache + (long)rr * slot_stride) + g;   // row t: xp[t*16], xp[t*16 + 8]
+        const float4* xp = reinterpret_cast<const float4*>(TAB ? cache : cache + (long)rr * slot_stride) + g;   // row t: xp[t*16], xp[t*16 + 8]
         // L2 prefetch PF rows ahead by lanes 0 (first 128-byte line of the row) and 4 (second line); no registers held
         const float4* pfp = xp + (g ? 8 : 0) + PF * 16;
-        const int pf_lim = (PF > 0 && (g & 3) == 0) ? nk - PF : -(1 << 30);       // prefetch row t + PF while t < pf_lim
+        const int pf_lim = (!TAB && PF > 0 && (g & 3) == 0) ? nk - PF : -(1 << 30);       // prefetch row t + PF while t < pf_lim
+        const uint32_t* bt = TAB ? bits + rr * 8 : nullptr;
+        int tab_t = 0, tab_n3 = 0;                           // TAB: next key and the ones among the actions before it
+        auto tab_row = [&]() -> long {                        // table row of key tab_t, then advance (keys come in order)
+            const int ap = tab_t > 0 ? (int)((bt[(tab_t - 1) >> 5] >> ((tab_t - 1) & 31)) & 1u) : 0;
+            tab_n3 += ap;
+            const long row = (long)tab_t * (tab_t + 1) + 2 * tab_n3 + ap;
+            ++tab_t;
+            return row * 16;
+        };
         float m_own = -INFINITY, m_oth = -INFINITY, l_own = 0.f, l_oth = 0.f;
         float4 ca_own = z4, cb_own = z4, ca_oth = z4, cb_oth = z4;
         auto batch = [&](const float4 (&xa)[KB], const float4 (&xb)[KB], int t0, auto masked) {
@@ -291,9 +312,13 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
                 const bool ok = t0 + i < nk;
-                xa[i] = ok ? xp[(long)(t0 + i) * 16] : z4;
-                xb[i] = ok ? xp[(long)(t0 + i) * 16 + 8] : z4;
-                if (t0 + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pfp + (long)(t0 + i) * 16));
+                if (TAB) {
+                    if (ok) { const long o = tab_row(); xa[i] = xp[o]; xb[i] = xp[o + 8]; } else { xa[i] = z4; xb[i] = z4; }
+                } else {
+                    xa[i] = ok ? xp[(long)(t0 + i) * 16] : z4;
+                    xb[i] = ok ? xp[(long)(t0 + i) * 16 + 8] : z4;
+                    if (t0 + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pfp + (long)(t0 + i) * 16));
+                }
             }
         };
         float4 xa[KB], xb[KB], ya[KB], yb[KB];
@@ -304,12 +329,18 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
             const float4* pt = pfp;
             for (; t0 + 3 * KB <= nk; t0 += 2 * KB, xt += 2 * KB * 16, pt += 2 * KB * 16) {
 #pragma unroll
-                for (int i = 0; i < KB; ++i) { ya[i] = xt[(KB + i) * 16]; yb[i] = xt[(KB + i) * 16 + 8]; }
+                for (int i = 0; i < KB; ++i) {
+                    if (TAB) { const long o = tab_row(); ya[i] = xp[o]; yb[i] = xp[o + 8]; }
+                    else { ya[i] = xt[(KB + i) * 16]; yb[i] = xt[(KB + i) * 16 + 8]; }
+                }
                 if (t0 + KB < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + KB * 16));
                 if (t0 + KB + 1 < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (KB + 1) * 16));
                 batch(xa, xb, t0, std::false_type{});
 #pragma unroll
-                for (int i = 0; i < KB; ++i) { xa[i] = xt[(2 * KB + i) * 16]; xb[i] = xt[(2 * KB + i) * 16 + 8]; }
+                for (int i = 0; i < KB; ++i) {
+                    if (TAB) { const long o = tab_row(); xa[i] = xp[o]; xb[i] = xp[o + 8]; }
+                    else { xa[i] = xt[(2 * KB + i) * 16]; xb[i] = xt[(2 * KB + i) * 16 + 8]; }
+                }
                 if (t0 + 2 * KB < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + 2 * KB * 16));
                 if (t0 + 2 * KB + 1 < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (2 * KB + 1) * 16));
                 batch(ya, yb, t0 + KB, std::false_type{});
@@ -337,10 +368,10 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
 // Four keys per batch, the next batch in flight in registers; written like the 8-lane version: warp-uniform trip
 // counts (two lane groups per warp, `rows` even), full-mask shuffles, lanes 0-7 collect head 0 and lanes 8-15 head 1
 // ("own"), unpredicated batches while twelve keys remain and a predicated tail.
-template <bool GQ, int PF>
+template <bool GQ, int PF, bool TAB = false>
 __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                         const float* cache, long slot_stride, int rows, int n_valid, int nk,
-                                                        unsigned char* U, unsigned char* V) {
+                                                        unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr) {
     constexpr int KB = 4;
     constexpr unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, grp = tid >> 4, l = tid & 15;
@@ -357,8 +388,17 @@ __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict_
             q_own = *reinterpret_cast<const float4*>((up ? q1 : q0) + rr * XS + l * 4);
             q_oth = *reinterpret_cast<const float4*>((up ? q0 : q1) + rr * XS + l * 4);
         }
-        const float4* xp = reinterpret_cast<const float4*>(cache + (long)rr * slot_stride) + l;     // row t: xp[t * 16]
-        const int pf_lim = (PF > 0 && (l & 7) == 0) ? nk - 2 * PF : -(1 << 30);                  // prefetch row t + 2 PF while t < pf_lim
+        const float4* xp = reinterpret_cast<const float4*>(TAB ? cache : cache + (long)rr * slot_stride) + l;     // row t: xp[t * 16]
+        const int pf_lim = (!TAB && PF > 0 && (l & 7) == 0) ? nk - 2 * PF : -(1 << 30);          // prefetch row t + 2 PF while t < pf_lim
+        const uint32_t* bt = TAB ? bits + rr * 8 : nullptr;
+        int tab_t = 0, tab_n3 = 0;
+        auto tab_row = [&]() -> long {                        // see attention_absorbed_op
+            const int ap = tab_t > 0 ? (int)((bt[(tab_t - 1) >> 5] >> ((tab_t - 1) & 31)) & 1u) : 0;
+            tab_n3 += ap;
+            const long row = (long)tab_t * (tab_t + 1) + 2 * tab_n3 + ap;
+            ++tab_t;
+            return row * 16;
+        };
         const float4* pfp = xp + 2 * PF * 16;
         float m_own = -INFINITY, m_oth = -INFINITY, l_own = 0.f, l_oth = 0.f;
         float4 c_own = z4, c_oth = z4;
@@ -398,8 +438,12 @@ __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict_
         auto fetch_masked = [&](float4 (&x)[KB], int t0) {
 #pragma unroll
             for (int i = 0; i < KB; ++i) {
-                x[i] = t0 + i < nk ? xp[(long)(t0 + i) * 16] : z4;
-                if (t0 + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pfp + (long)(t0 + i) * 16));
+                if (TAB) {
+                    if (t0 + i < nk) x[i] = xp[tab_row()]; else x[i] = z4;
+                } else {
+                    x[i] = t0 + i < nk ? xp[(long)(t0 + i) * 16] : z4;
+                    if (t0 + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pfp + (long)(t0 + i) * 16));
+                }
             }
         };
         float4 x[KB], y[KB];
@@ -411,13 +455,13 @@ __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict_
             for (; t0 + 3 * KB <= nk; t0 += 2 * KB, xt += 2 * KB * 16, pt += 2 * KB * 16) {
 #pragma unroll
                 for (int i = 0; i < KB; ++i) {
-                    y[i] = xt[(KB + i) * 16];
+                    if (TAB) y[i] = xp[tab_row()]; else y[i] = xt[(KB + i) * 16];
                     if (t0 + KB + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (KB + i) * 16));
                 }
                 batch(x, t0, std::false_type{});
 #pragma unroll
                 for (int i = 0; i < KB; ++i) {
-                    x[i] = xt[(2 * KB + i) * 16];
+                    if (TAB) x[i] = xp[tab_row()]; else x[i] = xt[(2 * KB + i) * 16];
                     if (t0 + 2 * KB + i < pf_lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(pt + (2 * KB + i) * 16));
                 }
                 batch(y, t0 + KB, std::false_type{});
@@ -436,9 +480,76 @@ __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict_
     }
 }
 
-template <int PFD>
+// ---------------------------------------------------------------------------------------------------------------------
+// Block-0 cross-attention inputs as a TABLE (stochastic decode).  The row that block 0 caches for position t,
+// x1_t = LN1(e_c + out-map(softmax over token codes)), depends on the env only through the code of its own token (start
+// at t = 0, else the previous action a_{t-1}) and on how many of the earlier actions were 1 (code_counts): at most
+// 2 (t + 1) distinct rows per position, the same for every env.  They are computed once per weight update into
+// x1tab[t (t + 1) + 2 n3 + a_prev][64] (n3 = ones among a_0 .. a_{t-1}), 0.7 MB at n_agent 51, so that the decode neither
+// writes nor re-reads a per-env cache for this attention (a third of its HBM traffic), skips block 0's output-map stage
+// and its token-code softmax, and gathers the keys from an L2-resident table by prefix popcounts of the action bitset.
+// One CTA per position; fp32 CUDA-core arithmetic (the decode's own fp16 hi/lo stage agrees to ~1e-6).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+x1_table_kernel(const float* __restrict__ w, float* __restrict__ tab, int L) {
+    __shared__ float sEmb[6 * 64];
+    __shared__ float sQ[2 * 6 * 64];       // folded block-0 self-attention queries per (head, code)
+    __shared__ float sS[72];               // scores [head][query code][key code], exp2 domain
+    __shared__ float sP[2 * 6 * 64];       // P_h[c][n] = sum_k e_c[k] FB_h.Wt[k][n]
+    const int tid = threadIdx.x, t = blockIdx.x;
+    build_emb_table(sEmb, w);
+    __syncthreads();
+    for (int idx = tid; idx < 2 * 6 * 64; idx += 128) {
+        const int h = idx / 384, c = (idx / 64) % 6, n = idx & 63;
+        const float* WA = w + lay::fold_blob(0, h ? lay::FA1 : lay::FA0);
+        const float* WB = w + lay::fold_blob(0, h ? lay::FB1 : lay::FB0);
+        float qa = WA[lay::B_BIAS + n], pb = 0.f;
+        for (int k = 0; k < 64; ++k) { qa = fmaf(sEmb[c * 64 + k], WA[k * 64 + n], qa); pb = fmaf(sEmb[c * 64 + k], WB[k * 64 + n], pb); }
+        sQ[idx] = qa; sP[idx] = pb;
+    }
+    __syncthreads();
+    if (tid < 72) {
+        const int h = tid / 36, cq = (tid / 6) % 6, c = tid % 6;
+        float acc = 0.f;
+        for (int n = 0; n < 64; ++n) acc = fmaf(sQ[(h * 6 + cq) * 64 + n], sEmb[c * 64 + n], acc);
+        sS[tid] = acc;
+    }
+    __syncthreads();
+    const float* W1 = w + lay::fold_blob(0, lay::FB1);                 // bias, LN weight / bias of the stage
+    const int lane = tid & 31, wp = tid >> 5;
+    for (int e = wp; e < 2 * (t + 1); e += 4) {                        // one warp per table row, two columns per lane
+        const int n3 = e >> 1, ap = e & 1;
+        if (t == 0 ? e != 0 : (ap > n3)) continue;                     // unreachable states (a_prev = 1 needs n3 >= 1)
+        const int cq = t == 0 ? 1 : 2 + ap;
+        const int cnt[6] = {0, 1, t - n3, n3, 0, 0};
+        float y0 = W1[lay::B_BIAS + lane] + sEmb[cq * 64 + lane], y1 = W1[lay::B_BIAS + 32 + lane] + sEmb[cq * 64 + 32 + lane];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float* S = sS + (h * 6 + cq) * 6;
+            float m = -INFINITY, wg[6], z = 0.f;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) if (cnt[c] > 0) m = fmaxf(m, S[c]);
+#pragma unroll
+            for (int c = 0; c < 6; ++c) { wg[c] = cnt[c] > 0 ? (float)cnt[c] * exp2f(S[c] - m) : 0.f; z += wg[c]; }
+            const float iz = 1.0f / z;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+                y0 = fmaf(wg[c] * iz, sP[(h * 6 + c) * 64 + lane], y0);
+                y1 = fmaf(wg[c] * iz, sP[(h * 6 + c) * 64 + 32 + lane], y1);
+            }
+        }
+        const float mean = warp_sum(y0 + y1) * (1.0f / 64.0f);
+        y0 -= mean; y1 -= mean;
+        const float rs = rsqrtf(warp_sum(y0 * y0 + y1 * y1) * (1.0f / 64.0f) + 1e-5f);
+        float* dst = tab + ((long)t * (t + 1) + e) * 64;
+        dst[lane] = y0 * rs * W1[lay::B_LNW + lane] + W1[lay::B_LNB + lane];
+        dst[32 + lane] = y1 * rs * W1[lay::B_LNW + 32 + lane] + W1[lay::B_LNB + 32 + lane];
+    }
+}
+
+template <int PFD, bool TABK>
 __global__ void __launch_bounds__(NTD, 1)
-decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
+decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* __restrict__ x1tab) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     DSmem s = dcarve(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -447,8 +558,10 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
     const long n_tiles = (a.B + rows - 1) / rows;
     long my_tiles = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++my_tiles;
+    constexpr bool use_tab = TABK;               // stochastic decode: block 0's cross-attention keys come from the shared table
+    const int n_seq = use_tab ? STEP_BLOBS - 2 : STEP_BLOBS;
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_tc_decode, STEP_BLOBS, (int)(my_tiles * a.n_steps * STEP_BLOBS), DEPTH,
+    ring.init(s.ring, s.bars, b.w, use_tab ? c_tc_decode_tab : c_tc_decode, n_seq, (int)(my_tiles * a.n_steps * n_seq), DEPTH,
               lay::BLOB_BYTES, tc::SLOT_F);
     uint64_t* mma_bar = &s.bars[tc::MMA_BAR];
     if (tid == 0) { mbar_init(mma_bar, 1); mbar_fence_init(); }
@@ -519,6 +632,16 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                 float* cx1 = kv0 + (blk * 2 + 0) * (long)L * 64;     // self-attention inputs (block input x)
                 float* cx2 = kv0 + (blk * 2 + 1) * (long)L * 64;     // cross-attention inputs (x after LN1)
                 float* x_row = cx1 + (long)row * slot_stride + (long)j * 64 + q * 16;
+                if (blk == 0 && use_tab) {
+                    // ---- block 0 from the table: no token-code softmax, no output-map stage, no cache row; the
+                    //      cross-attention gathers its keys x1_t from x1tab by the env's action history ------------------
+                    if (rows <= rows16)
+                        attention_absorbed_op16<true, PFD, true>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
+                                                                 x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits);
+                    else
+                        attention_absorbed_op<true, PFD, true>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
+                                                               x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits);
+                } else {
                 if (blk == 0) {
                     // ---- block 0: softmax over token codes (see code_counts) -> ctx_0 -> U, ctx_1 -> V ------------
                     const int cq = s.sCode[row];
@@ -608,6 +731,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
                 else
                     attention_absorbed_op<true, PFD>(b.Q2p[blk][0] + (env0 * L + j) * 64, b.Q2p[blk][1] + (env0 * L + j) * 64, (long)L * 64,
                                                      cx2, slot_stride, rows, n_valid, j + 1, s.U, s.V);
+                }
                 {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
@@ -734,6 +858,12 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16) {
 
 }  // namespace
 
+int launch_x1_table(const float* packed, float* x1tab, int L, cudaStream_t st) {
+    x1_table_kernel<<<L, 128, 0, st>>>(packed, x1tab, L);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
 // rows per tile: spread the envs over the SMs (one CTA each), a multiple of 4 (whole warps of four 8-lane groups), at most
 // 128.  4096 envs on 148 SMs: 28 rows on 147 CTAs (a multiple of 8 would put 32 rows on 128 CTAs and leave 20 SMs idle)
 int decode_tc_rows(long B, int n_sm) {
@@ -759,10 +889,18 @@ int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_s
     const int rows = decode_tc_rows(a.B, n_sm);
     static int rows16 = -1;          // tiles of at most this many envs use 16 lanes per env in the attention (MATAS_DECODE_ROWS16)
     if (rows16 < 0) { const char* e = getenv("MATAS_DECODE_ROWS16"); rows16 = e ? atoi(e) : 32; }
+    static int use_tab = -1;         // MATAS_DECODE_TAB=0: block 0 keeps its per-env cache rows in the stochastic decode too (A/B switch)
+    if (use_tab < 0) { const char* e = getenv("MATAS_DECODE_TAB"); use_tab = e ? atoi(e) : 1; }
+    const float* tab = (use_tab && !a.deterministic) ? b.x1tab : nullptr;
 #define DECODE_TC_LAUNCH(P)                                                                                           \
     do {                                                                                                              \
-        CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-        decode_tc_kernel<P><<<grid, NTD, bytes, st>>>(b, a, rows, rows16);                                                   \
+        if (tab) {                                                                                                    \
+            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+            decode_tc_kernel<P, true><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab);                                 \
+        } else {                                                                                                      \
+            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+            decode_tc_kernel<P, false><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab);                                \
+        }                                                                                                             \
     } while (0)
     if (pf == 0) DECODE_TC_LAUNCH(0);
     else if (pf <= 4) DECODE_TC_LAUNCH(4);

@@ -21,6 +21,7 @@ struct PolicyBufs {
     float* rep;          // encoder output obs_rep
     float* Y;            // attention output of the block being processed (register-tiled attention kernel, attn_tile.cu)
     float* kv;           // decode cache: [env slots][blk 2][attn 2][L][64] layer inputs of each attention
+    const float* x1tab;  // block-0 cross-attention inputs by (position, ones so far, previous action) or null (decode_tc.cu)
 };
 
 // training-mode saves of the teacher-forced forward + work buffers of the backward; [n_tok][64] fp32
@@ -139,6 +140,7 @@ int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, 
 bool policy_use_tc();
 int decode_tc_geometry(long B, int n_sm, int* grid, long* slots);
 int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st);
+int launch_x1_table(const float* packed, float* x1tab, int L, cudaStream_t st);
 bool attn_tile_supported(int L);
 bool attn_fwd_supported(int L);
 int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
