@@ -616,18 +616,20 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
         __syncthreads();
         while (sched.next(st)) {
             const int j = st.j;
-            // ---- input token of this position ------------------------------------------------------
-            if (tid < MAXR) {
-                int code;
-                const uint32_t* bt = s.bits + tid * 8;
-                if (st.kind == 1) code = j == 0 ? 1 : 0;
-                else if (st.kind == 0) code = j == 0 ? 1 : 2 + (int)((bt[(j - 1) >> 5] >> ((j - 1) & 31)) & 1u);
-                else code = (j == 0 ? 4 : 2) + (int)((bt[j >> 5] >> (j & 31)) & 1u);
-                s.sCode[tid] = code;
-            }
-            __syncthreads();
+            // ---- input token of this position (with the table, block 0 never looks at it) -----------------------
             float v[16];
-            load16(v, s.sEmb + s.sCode[row] * 64 + q * 16);
+            if (!use_tab) {
+                if (tid < MAXR) {
+                    int code;
+                    const uint32_t* bt = s.bits + tid * 8;
+                    if (st.kind == 1) code = j == 0 ? 1 : 0;
+                    else if (st.kind == 0) code = j == 0 ? 1 : 2 + (int)((bt[(j - 1) >> 5] >> ((j - 1) & 31)) & 1u);
+                    else code = (j == 0 ? 4 : 2) + (int)((bt[j >> 5] >> (j & 31)) & 1u);
+                    s.sCode[tid] = code;
+                }
+                __syncthreads();
+                load16(v, s.sEmb + s.sCode[row] * 64 + q * 16);
+            }
             for (int blk = 0; blk < 2; ++blk) {
                 float* cx1 = kv0 + (blk * 2 + 0) * (long)L * 64;     // self-attention inputs (block input x)
                 float* cx2 = kv0 + (blk * 2 + 1) * (long)L * 64;     // cross-attention inputs (x after LN1)
