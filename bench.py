@@ -300,11 +300,11 @@ def run_ours(ns):
     # HBM bound: at every position j of every pass the decode re-reads the j+1 cached 256-byte layer-input rows
     # of its cached attentions, writes one new row per cached attention, reads 4 folded query rows + the obs_rep row
     # (256 B each) and writes the outputs; arithmetic intensity is ~7 flop/byte, below the fp32 ridge, so HBM is the
-    # roof.  Cached attentions: block-1 self and cross always (block-0 self-attention runs on token-code counts and
-    # reads nothing); block-0 cross only in the deterministic decode -- the stochastic decode gathers those keys from
-    # a shared L2-resident table (decode_tc.cu: x1_table_kernel, L(L+1) rows computed once per weight update).
+    # roof.  Cached attentions: block-1 self and cross (block-0 self-attention runs on token-code counts and reads
+    # nothing; block-0 cross-attention gathers its keys from shared L2-resident tables, decode_tc.cu: x1_table_kernel /
+    # x1_spec_table_kernel, computed once per weight update); with MATAS_DECODE_TAB=0 block-0 cross is cached per env too.
     visits = decode_schedule_positions(L, det, stride)
-    tab = (not det) and os.environ.get("MATAS_DECODE_TAB", "1") != "0" and os.environ.get("MATAS_TC", "1") != "0"
+    tab = os.environ.get("MATAS_DECODE_TAB", "1") != "0" and os.environ.get("MATAS_TC", "1") != "0"
     n_cached = 2 if tab else 3
     alg_bytes = B * (sum(n_cached * 256 * (j + 1) + n_cached * 256 + 5 * 256 + 16 for j in visits))
     hbm_peak = peaks.get("hbm_gbs", 6500.0)

@@ -120,6 +120,9 @@ struct matas_policy {
     size_t kv_cap = 0;
     float* d_kv = nullptr;
     float* d_x1tab = nullptr;    // [L (L + 1)][64] block-0 cross-attention inputs of the stochastic decode (decode_tc.cu)
+    float* d_x1spec = nullptr;   // speculative rows of the deterministic schedule for `spec_stride` (decode_tc.cu)
+    long spec_cap = 0;
+    int spec_stride = -1;        // -1: the rows must be recomputed (weights changed)
     PolicyBufs bufs = {};
     // training: saved activations + backward work buffers, gradient offsets
     GradMap gm;
@@ -298,7 +301,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
 
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
-    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_half); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_x1tab); cudaFree(p->d_train); cudaFree(p->d_phase);
+    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_half); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_x1tab); cudaFree(p->d_x1spec); cudaFree(p->d_train); cudaFree(p->d_phase);
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
@@ -326,6 +329,7 @@ extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void
         int rc_ = launch_x1_table(p->d_packed, p->d_x1tab, L, (cudaStream_t)stream);
         if (rc_) return rc_;
         p->bufs.x1tab = p->d_x1tab;
+        p->spec_stride = -1;
     }
     p->weights_set = true;
     return MATAS_OK;
@@ -371,6 +375,24 @@ static int run_decode(matas_policy* p, const float* ava, long B, int determinist
         p->kv_cap = need;
     }
     p->bufs.kv = p->d_kv;
+    p->bufs.x1spec = nullptr;
+    if (deterministic && p->bufs.x1tab && p->cfg.mode == MATAS_MODE_SEMI) {
+        // speculative block-0 rows of this stride's blocks (recomputed when the stride or the weights changed)
+        const int sd = stride < 1 ? 1 : stride;
+        const long rows = decode_tc_spec_rows(L, sd);
+        if (rows > p->spec_cap) {
+            if (p->d_x1spec) CUDA_TRY(cudaFree(p->d_x1spec));
+            p->d_x1spec = nullptr; p->spec_cap = 0; p->spec_stride = -1;
+            CUDA_TRY(cudaMalloc(&p->d_x1spec, (size_t)rows * 64 * sizeof(float)));
+            p->spec_cap = rows;
+        }
+        if (rows > 0 && p->spec_stride != sd) {
+            int rc_ = launch_x1_spec_table(p->d_packed, p->d_x1spec, L, sd, stream);
+            if (rc_) return rc_;
+            p->spec_stride = sd;
+        }
+        p->bufs.x1spec = p->d_x1spec ? p->d_x1spec : p->d_x1tab;      // no speculative rows (stride 1): any valid pointer
+    }
     DecodeArgs a;
     a.B = B; a.L = L; a.mode = p->cfg.mode; a.deterministic = deterministic ? 1 : 0; a.stride = stride;
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);

@@ -240,7 +240,8 @@ __device__ __forceinline__ float ex2(float x) {          // 2^x, x <= 0 here; de
 template <bool GQ, int PF, bool TAB = false>
 __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                       const float* cache, long slot_stride, int rows, int n_valid, int nk,
-                                                      unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr) {
+                                                      unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr,
+        const float* spec = nullptr, int spec_s = -1) {
     constexpr int KB = 2;
     constexpr unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, grp = tid >> 3, g = tid & 7;
@@ -269,7 +270,16 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
         const int pf_lim = (!TAB && PF > 0 && (g & 3) == 0) ? nk - PF : -(1 << 30);       // prefetch row t + PF while t < pf_lim
         const uint32_t* bt = TAB ? bits + rr * 8 : nullptr;
         int tab_t = 0, tab_n3 = 0;                           // TAB: next key and the ones among the actions before it
-        auto tab_row = [&]() -> long {                        // table row of key tab_t, then advance (keys come in order)
+        // float4 offset (relative to the standard table) of key tab_t's row, then advance (keys come in order).  In a
+        // speculative pass (spec_s >= 0) the keys behind the block start are that pass's own rows: `spec` holds them by
+        // (position, ones among the actions before the block start); xp and the spec rows share one pointer base.
+        const long spec_off = TAB && spec_s >= 0 ? (long)((spec - cache) >> 2) : 0;
+        auto tab_row = [&]() -> long {
+            if (spec_s >= 0 && tab_t > spec_s) {
+                const long row = (long)(tab_t - spec_s - 1) * (spec_s + 1) + tab_n3;
+                ++tab_t;
+                return spec_off + row * 16;
+            }
             const int ap = tab_t > 0 ? (int)((bt[(tab_t - 1) >> 5] >> ((tab_t - 1) & 31)) & 1u) : 0;
             tab_n3 += ap;
             const long row = (long)tab_t * (tab_t + 1) + 2 * tab_n3 + ap;
@@ -371,7 +381,8 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
 template <bool GQ, int PF, bool TAB = false>
 __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                         const float* cache, long slot_stride, int rows, int n_valid, int nk,
-                                                        unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr) {
+                                                        unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr,
+        const float* spec = nullptr, int spec_s = -1) {
     constexpr int KB = 4;
     constexpr unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, grp = tid >> 4, l = tid & 15;
@@ -392,7 +403,13 @@ __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict_
         const int pf_lim = (!TAB && PF > 0 && (l & 7) == 0) ? nk - 2 * PF : -(1 << 30);          // prefetch row t + 2 PF while t < pf_lim
         const uint32_t* bt = TAB ? bits + rr * 8 : nullptr;
         int tab_t = 0, tab_n3 = 0;
+        const long spec_off = TAB && spec_s >= 0 ? (long)((spec - cache) >> 2) : 0;
         auto tab_row = [&]() -> long {                        // see attention_absorbed_op
+            if (spec_s >= 0 && tab_t > spec_s) {
+                const long row = (long)(tab_t - spec_s - 1) * (spec_s + 1) + tab_n3;
+                ++tab_t;
+                return spec_off + row * 16;
+            }
             const int ap = tab_t > 0 ? (int)((bt[(tab_t - 1) >> 5] >> ((tab_t - 1) & 31)) & 1u) : 0;
             tab_n3 += ap;
             const long row = (long)tab_t * (tab_t + 1) + 2 * tab_n3 + ap;
@@ -490,66 +507,110 @@ __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict_
 // and its token-code softmax, and gathers the keys from an L2-resident table by prefix popcounts of the action bitset.
 // One CTA per position; fp32 CUDA-core arithmetic (the decode's own fp16 hi/lo stage agrees to ~1e-6).
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
-x1_table_kernel(const float* __restrict__ w, float* __restrict__ tab, int L) {
-    __shared__ float sEmb[6 * 64];
-    __shared__ float sQ[2 * 6 * 64];       // folded block-0 self-attention queries per (head, code)
-    __shared__ float sS[72];               // scores [head][query code][key code], exp2 domain
-    __shared__ float sP[2 * 6 * 64];       // P_h[c][n] = sum_k e_c[k] FB_h.Wt[k][n]
-    const int tid = threadIdx.x, t = blockIdx.x;
-    build_emb_table(sEmb, w);
+struct X1Smem {
+    float sEmb[6 * 64];
+    float sQ[2 * 6 * 64];        // folded block-0 self-attention queries per (head, code)
+    float sS[72];                // scores [head][query code][key code], exp2 domain
+    float sP[2 * 6 * 64];        // P_h[c][n] = sum_k e_c[k] FB_h.Wt[k][n]
+};
+__device__ __forceinline__ void x1_prologue(X1Smem& m, const float* __restrict__ w) {      // 128 threads
+    const int tid = threadIdx.x;
+    build_emb_table(m.sEmb, w);
     __syncthreads();
     for (int idx = tid; idx < 2 * 6 * 64; idx += 128) {
         const int h = idx / 384, c = (idx / 64) % 6, n = idx & 63;
         const float* WA = w + lay::fold_blob(0, h ? lay::FA1 : lay::FA0);
         const float* WB = w + lay::fold_blob(0, h ? lay::FB1 : lay::FB0);
         float qa = WA[lay::B_BIAS + n], pb = 0.f;
-        for (int k = 0; k < 64; ++k) { qa = fmaf(sEmb[c * 64 + k], WA[k * 64 + n], qa); pb = fmaf(sEmb[c * 64 + k], WB[k * 64 + n], pb); }
-        sQ[idx] = qa; sP[idx] = pb;
+        for (int k = 0; k < 64; ++k) { qa = fmaf(m.sEmb[c * 64 + k], WA[k * 64 + n], qa); pb = fmaf(m.sEmb[c * 64 + k], WB[k * 64 + n], pb); }
+        m.sQ[idx] = qa; m.sP[idx] = pb;
     }
     __syncthreads();
     if (tid < 72) {
         const int h = tid / 36, cq = (tid / 6) % 6, c = tid % 6;
         float acc = 0.f;
-        for (int n = 0; n < 64; ++n) acc = fmaf(sQ[(h * 6 + cq) * 64 + n], sEmb[c * 64 + n], acc);
-        sS[tid] = acc;
+        for (int n = 0; n < 64; ++n) acc = fmaf(m.sQ[(h * 6 + cq) * 64 + n], m.sEmb[c * 64 + n], acc);
+        m.sS[tid] = acc;
     }
     __syncthreads();
+}
+// one warp: x1 row for own token code cq and visible-code counts cnt -> dst[64] (two columns per lane)
+__device__ __forceinline__ void x1_row(const X1Smem& m, const float* __restrict__ w, int cq, const int (&cnt)[6], float* __restrict__ dst) {
     const float* W1 = w + lay::fold_blob(0, lay::FB1);                 // bias, LN weight / bias of the stage
-    const int lane = tid & 31, wp = tid >> 5;
-    for (int e = wp; e < 2 * (t + 1); e += 4) {                        // one warp per table row, two columns per lane
+    const int lane = threadIdx.x & 31;
+    float y0 = W1[lay::B_BIAS + lane] + m.sEmb[cq * 64 + lane], y1 = W1[lay::B_BIAS + 32 + lane] + m.sEmb[cq * 64 + 32 + lane];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const float* S = m.sS + (h * 6 + cq) * 6;
+        float mx = -INFINITY, wg[6], z = 0.f;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) if (cnt[c] > 0) mx = fmaxf(mx, S[c]);
+#pragma unroll
+        for (int c = 0; c < 6; ++c) { wg[c] = cnt[c] > 0 ? (float)cnt[c] * exp2f(S[c] - mx) : 0.f; z += wg[c]; }
+        const float iz = 1.0f / z;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            y0 = fmaf(wg[c] * iz, m.sP[(h * 6 + c) * 64 + lane], y0);
+            y1 = fmaf(wg[c] * iz, m.sP[(h * 6 + c) * 64 + 32 + lane], y1);
+        }
+    }
+    const float mean = warp_sum(y0 + y1) * (1.0f / 64.0f);
+    y0 -= mean; y1 -= mean;
+    const float rs = rsqrtf(warp_sum(y0 * y0 + y1 * y1) * (1.0f / 64.0f) + 1e-5f);
+    dst[lane] = y0 * rs * W1[lay::B_LNW + lane] + W1[lay::B_LNB + lane];
+    dst[32 + lane] = y1 * rs * W1[lay::B_LNW + 32 + lane] + W1[lay::B_LNB + 32 + lane];
+}
+
+__global__ void __launch_bounds__(128)
+x1_table_kernel(const float* __restrict__ w, float* __restrict__ tab, int L) {
+    __shared__ X1Smem m;
+    const int t = blockIdx.x;
+    x1_prologue(m, w);
+    for (int e = threadIdx.x >> 5; e < 2 * (t + 1); e += 4) {          // one warp per table row
         const int n3 = e >> 1, ap = e & 1;
         if (t == 0 ? e != 0 : (ap > n3)) continue;                     // unreachable states (a_prev = 1 needs n3 >= 1)
-        const int cq = t == 0 ? 1 : 2 + ap;
         const int cnt[6] = {0, 1, t - n3, n3, 0, 0};
-        float y0 = W1[lay::B_BIAS + lane] + sEmb[cq * 64 + lane], y1 = W1[lay::B_BIAS + 32 + lane] + sEmb[cq * 64 + 32 + lane];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const float* S = sS + (h * 6 + cq) * 6;
-            float m = -INFINITY, wg[6], z = 0.f;
-#pragma unroll
-            for (int c = 0; c < 6; ++c) if (cnt[c] > 0) m = fmaxf(m, S[c]);
-#pragma unroll
-            for (int c = 0; c < 6; ++c) { wg[c] = cnt[c] > 0 ? (float)cnt[c] * exp2f(S[c] - m) : 0.f; z += wg[c]; }
-            const float iz = 1.0f / z;
-#pragma unroll
-            for (int c = 0; c < 6; ++c) {
-                y0 = fmaf(wg[c] * iz, sP[(h * 6 + c) * 64 + lane], y0);
-                y1 = fmaf(wg[c] * iz, sP[(h * 6 + c) * 64 + 32 + lane], y1);
-            }
-        }
-        const float mean = warp_sum(y0 + y1) * (1.0f / 64.0f);
-        y0 -= mean; y1 -= mean;
-        const float rs = rsqrtf(warp_sum(y0 * y0 + y1 * y1) * (1.0f / 64.0f) + 1e-5f);
-        float* dst = tab + ((long)t * (t + 1) + e) * 64;
-        dst[lane] = y0 * rs * W1[lay::B_LNW + lane] + W1[lay::B_LNB + lane];
-        dst[32 + lane] = y1 * rs * W1[lay::B_LNW + 32 + lane] + W1[lay::B_LNB + 32 + lane];
+        x1_row(m, w, t == 0 ? 1 : 2 + ap, cnt, tab + ((long)t * (t + 1) + e) * 64);
+    }
+}
+
+// Stride blocks [s, e) of the deterministic Semi_Discrete schedule (DecSched) and, per block, the offset of its
+// speculative rows in the second table: a speculative pass writes rows t = s+1 .. e-1 with a zero-row token and the
+// counts (t - s zero rows, start, s - n3 zeros, n3 ones), n3 = ones among a_0 .. a_{s-1}: (e - s - 1)(s + 1) rows
+// [t - s - 1][n3] per block.
+struct SpecBlocks {
+    int L, nd, stride, s, e, go;
+    long base;
+    __host__ __device__ void init(int L_, int stride_) { L = L_; nd = L_ - 1; stride = stride_ < 1 ? 1 : stride_; s = 0; e = 1; go = 1; base = 0; }
+    __host__ __device__ bool valid() const { return e <= L && go; }
+    __host__ __device__ long rows() const { return (long)(e - s - 1) * (s + 1); }
+    __host__ __device__ void next() {                               // mirrors DecSched::next (Semi_Discrete)
+        base += rows();
+        if (e == L) { go = 0; return; }
+        if (e < nd) { s = e; e = min(e + stride, nd); }
+        else { s = e; e = min(e + 1, L); }
+    }
+};
+
+__global__ void __launch_bounds__(128)
+x1_spec_table_kernel(const float* __restrict__ w, float* __restrict__ spec, int L, int stride) {
+    __shared__ X1Smem m;
+    const int t = blockIdx.x;
+    SpecBlocks sb;
+    sb.init(L, stride);
+    while (sb.valid() && !(t >= sb.s && t < sb.e)) sb.next();          // the block that holds position t
+    if (!sb.valid() || t == sb.s) return;                              // block starts use their true predecessor
+    x1_prologue(m, w);
+    const int s = sb.s;
+    for (int n3 = threadIdx.x >> 5; n3 <= s; n3 += 4) {
+        const int cnt[6] = {t - s, 1, s - n3, n3, 0, 0};
+        x1_row(m, w, 0, cnt, spec + (sb.base + (long)(t - s - 1) * (s + 1) + n3) * 64);
     }
 }
 
 template <int PFD, bool TABK>
 __global__ void __launch_bounds__(NTD, 1)
-decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* __restrict__ x1tab) {
+decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* __restrict__ x1tab, const float* __restrict__ x1spec) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     DSmem s = dcarve(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -613,9 +674,12 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
         DecSched sched;
         sched.init(L, a.mode, a.deterministic, a.stride);
         DecStep st;
+        SpecBlocks sb;                             // table mode, deterministic decode: the current stride block and its rows
+        sb.init(L, a.stride);
         __syncthreads();
         while (sched.next(st)) {
             const int j = st.j;
+            if (use_tab && a.deterministic) while (sb.s != sched.s) sb.next();
             // ---- input token of this position (with the table, block 0 never looks at it) -----------------------
             float v[16];
             if (!use_tab) {
@@ -637,12 +701,15 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
                 if (blk == 0 && use_tab) {
                     // ---- block 0 from the table: no token-code softmax, no output-map stage, no cache row; the
                     //      cross-attention gathers its keys x1_t from x1tab by the env's action history ------------------
+                    // keys behind the block start in a speculative pass (kind 1) are that pass's rows (second table)
+                    const int spec_s = (a.deterministic && st.kind == 1) ? sched.s : -1;
+                    const float* spec = x1spec + sb.base * 64;
                     if (rows <= rows16)
                         attention_absorbed_op16<true, PFD, true>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
-                                                                 x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits);
+                                                                 x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits, spec, spec_s);
                     else
                         attention_absorbed_op<true, PFD, true>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
-                                                               x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits);
+                                                               x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits, spec, spec_s);
                 } else {
                 if (blk == 0) {
                     // ---- block 0: softmax over token codes (see code_counts) -> ctx_0 -> U, ctx_1 -> V ------------
@@ -860,6 +927,19 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
 
 }  // namespace
 
+long decode_tc_spec_rows(int L, int stride) {
+    SpecBlocks sb;
+    sb.init(L, stride);
+    while (sb.valid()) sb.next();
+    return sb.base;
+}
+
+int launch_x1_spec_table(const float* packed, float* x1spec, int L, int stride, cudaStream_t st) {
+    x1_spec_table_kernel<<<L, 128, 0, st>>>(packed, x1spec, L, stride);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
 int launch_x1_table(const float* packed, float* x1tab, int L, cudaStream_t st) {
     x1_table_kernel<<<L, 128, 0, st>>>(packed, x1tab, L);
     CUDA_TRY(cudaGetLastError());
@@ -893,15 +973,16 @@ int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_s
     if (rows16 < 0) { const char* e = getenv("MATAS_DECODE_ROWS16"); rows16 = e ? atoi(e) : 32; }
     static int use_tab = -1;         // MATAS_DECODE_TAB=0: block 0 keeps its per-env cache rows in the stochastic decode too (A/B switch)
     if (use_tab < 0) { const char* e = getenv("MATAS_DECODE_TAB"); use_tab = e ? atoi(e) : 1; }
-    const float* tab = (use_tab && !a.deterministic) ? b.x1tab : nullptr;
+    // stochastic decode: the standard table; deterministic Semi_Discrete decode: plus the speculative rows of its stride blocks
+    const float* tab = (use_tab && (!a.deterministic || (a.mode == MATAS_MODE_SEMI && b.x1spec))) ? b.x1tab : nullptr;
 #define DECODE_TC_LAUNCH(P)                                                                                           \
     do {                                                                                                              \
         if (tab) {                                                                                                    \
             CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-            decode_tc_kernel<P, true><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab);                                 \
+            decode_tc_kernel<P, true><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, b.x1spec);                                 \
         } else {                                                                                                      \
             CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-            decode_tc_kernel<P, false><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab);                                \
+            decode_tc_kernel<P, false><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, nullptr);                                \
         }                                                                                                             \
     } while (0)
     if (pf == 0) DECODE_TC_LAUNCH(0);

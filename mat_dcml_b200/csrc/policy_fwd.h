@@ -22,6 +22,7 @@ struct PolicyBufs {
     float* Y;            // attention output of the block being processed (register-tiled attention kernel, attn_tile.cu)
     float* kv;           // decode cache: [env slots][blk 2][attn 2][L][64] layer inputs of each attention
     const float* x1tab;  // block-0 cross-attention inputs by (position, ones so far, previous action) or null (decode_tc.cu)
+    const float* x1spec; // the same for the speculative rows of the deterministic schedule's stride blocks, or null
 };
 
 // training-mode saves of the teacher-forced forward + work buffers of the backward; [n_tok][64] fp32
@@ -141,6 +142,8 @@ bool policy_use_tc();
 int decode_tc_geometry(long B, int n_sm, int* grid, long* slots);
 int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st);
 int launch_x1_table(const float* packed, float* x1tab, int L, cudaStream_t st);
+long decode_tc_spec_rows(int L, int stride);
+int launch_x1_spec_table(const float* packed, float* x1spec, int L, int stride, cudaStream_t st);
 bool attn_tile_supported(int L);
 bool attn_fwd_supported(int L);
 int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
