@@ -237,7 +237,7 @@ __device__ __forceinline__ float ex2(float x) {          // 2^x, x <= 0 here; de
 // TAB: the keys are rows of the shared block-0 table (x1_table_kernel) instead of a per-env cache: key t of env r is
 // row t (t + 1) + 2 n3 + a_{t-1}, n3 = ones among the env's actions a_0 .. a_{t-1} (its bitset at bits + 8 r); the row
 // indices are produced in key order by a running popcount, and nothing is prefetched (the table lives in L2).
-template <bool GQ, int PF, bool TAB = false>
+template <bool GQ, int PF, int TAB = 0>
 __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                       const float* cache, long slot_stride, int rows, int n_valid, int nk,
                                                       unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr,
@@ -273,9 +273,9 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
         // float4 offset (relative to the standard table) of key tab_t's row, then advance (keys come in order).  In a
         // speculative pass (spec_s >= 0) the keys behind the block start are that pass's own rows: `spec` holds them by
         // (position, ones among the actions before the block start); xp and the spec rows share one pointer base.
-        const long spec_off = TAB && spec_s >= 0 ? (long)((spec - cache) >> 2) : 0;
+        const long spec_off = TAB == 2 && spec_s >= 0 ? (long)((spec - cache) >> 2) : 0;
         auto tab_row = [&]() -> long {
-            if (spec_s >= 0 && tab_t > spec_s) {
+            if (TAB == 2 && spec_s >= 0 && tab_t > spec_s) {
                 const long row = (long)(tab_t - spec_s - 1) * (spec_s + 1) + tab_n3;
                 ++tab_t;
                 return spec_off + row * 16;
@@ -378,7 +378,7 @@ __device__ __forceinline__ void attention_absorbed_op(const float* __restrict__ 
 // Four keys per batch, the next batch in flight in registers; written like the 8-lane version: warp-uniform trip
 // counts (two lane groups per warp, `rows` even), full-mask shuffles, lanes 0-7 collect head 0 and lanes 8-15 head 1
 // ("own"), unpredicated batches while twelve keys remain and a predicated tail.
-template <bool GQ, int PF, bool TAB = false>
+template <bool GQ, int PF, int TAB = 0>
 __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict__ q0, const float* __restrict__ q1, long q_stride,
                                                         const float* cache, long slot_stride, int rows, int n_valid, int nk,
                                                         unsigned char* U, unsigned char* V, const uint32_t* bits = nullptr,
@@ -403,9 +403,9 @@ __device__ __forceinline__ void attention_absorbed_op16(const float* __restrict_
         const int pf_lim = (!TAB && PF > 0 && (l & 7) == 0) ? nk - 2 * PF : -(1 << 30);          // prefetch row t + 2 PF while t < pf_lim
         const uint32_t* bt = TAB ? bits + rr * 8 : nullptr;
         int tab_t = 0, tab_n3 = 0;
-        const long spec_off = TAB && spec_s >= 0 ? (long)((spec - cache) >> 2) : 0;
+        const long spec_off = TAB == 2 && spec_s >= 0 ? (long)((spec - cache) >> 2) : 0;
         auto tab_row = [&]() -> long {                        // see attention_absorbed_op
-            if (spec_s >= 0 && tab_t > spec_s) {
+            if (TAB == 2 && spec_s >= 0 && tab_t > spec_s) {
                 const long row = (long)(tab_t - spec_s - 1) * (spec_s + 1) + tab_n3;
                 ++tab_t;
                 return spec_off + row * 16;
@@ -608,7 +608,9 @@ x1_spec_table_kernel(const float* __restrict__ w, float* __restrict__ spec, int 
     }
 }
 
-template <int PFD, bool TABK>
+// TABK: 0 = every attention cached per env; 1 = block-0 cross-attention from the table (stochastic decode);
+// 2 = the same plus the speculative rows of the deterministic stride blocks
+template <int PFD, int TABK>
 __global__ void __launch_bounds__(NTD, 1)
 decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* __restrict__ x1tab, const float* __restrict__ x1spec) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -619,7 +621,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
     const long n_tiles = (a.B + rows - 1) / rows;
     long my_tiles = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++my_tiles;
-    constexpr bool use_tab = TABK;               // stochastic decode: block 0's cross-attention keys come from the shared table
+    constexpr bool use_tab = TABK != 0;          // block 0's cross-attention keys come from the shared table(s)
     const int n_seq = use_tab ? STEP_BLOBS - 2 : STEP_BLOBS;
     Ring ring;
     ring.init(s.ring, s.bars, b.w, use_tab ? c_tc_decode_tab : c_tc_decode, n_seq, (int)(my_tiles * a.n_steps * n_seq), DEPTH,
@@ -679,7 +681,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
         __syncthreads();
         while (sched.next(st)) {
             const int j = st.j;
-            if (use_tab && a.deterministic) while (sb.s != sched.s) sb.next();
+            if (TABK == 2) while (sb.s != sched.s) sb.next();
             // ---- input token of this position (with the table, block 0 never looks at it) -----------------------
             float v[16];
             if (!use_tab) {
@@ -702,13 +704,13 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
                     // ---- block 0 from the table: no token-code softmax, no output-map stage, no cache row; the
                     //      cross-attention gathers its keys x1_t from x1tab by the env's action history ------------------
                     // keys behind the block start in a speculative pass (kind 1) are that pass's rows (second table)
-                    const int spec_s = (a.deterministic && st.kind == 1) ? sched.s : -1;
+                    const int spec_s = (TABK == 2 && st.kind == 1) ? sched.s : -1;
                     const float* spec = x1spec + sb.base * 64;
                     if (rows <= rows16)
-                        attention_absorbed_op16<true, PFD, true>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
+                        attention_absorbed_op16<true, PFD, TABK>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
                                                                  x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits, spec, spec_s);
                     else
-                        attention_absorbed_op<true, PFD, true>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
+                        attention_absorbed_op<true, PFD, TABK>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
                                                                x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits, spec, spec_s);
                 } else {
                 if (blk == 0) {
@@ -977,12 +979,15 @@ int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_s
     const float* tab = (use_tab && (!a.deterministic || (a.mode == MATAS_MODE_SEMI && b.x1spec))) ? b.x1tab : nullptr;
 #define DECODE_TC_LAUNCH(P)                                                                                           \
     do {                                                                                                              \
-        if (tab) {                                                                                                    \
-            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-            decode_tc_kernel<P, true><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, b.x1spec);                                 \
+        if (tab && a.deterministic) {                                                                                 \
+            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+            decode_tc_kernel<P, 2><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, b.x1spec);                         \
+        } else if (tab) {                                                                                             \
+            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+            decode_tc_kernel<P, 1><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, nullptr);                          \
         } else {                                                                                                      \
-            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-            decode_tc_kernel<P, false><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, nullptr);                                \
+            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+            decode_tc_kernel<P, 0><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, nullptr, nullptr);                      \
         }                                                                                                             \
     } while (0)
     if (pf == 0) DECODE_TC_LAUNCH(0);
