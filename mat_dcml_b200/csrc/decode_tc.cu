@@ -990,10 +990,8 @@ int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_s
             decode_tc_kernel<P, 0><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, nullptr, nullptr);                      \
         }                                                                                                             \
     } while (0)
-    if (pf == 0) DECODE_TC_LAUNCH(0);
-    else if (pf <= 4) DECODE_TC_LAUNCH(4);
-    else if (pf <= 8) DECODE_TC_LAUNCH(8);
-    else DECODE_TC_LAUNCH(16);
+    if (pf == 0) DECODE_TC_LAUNCH(0);        // MATAS_DECODE_PF=0: no in-loop L2 prefetch (A/B); distances of 8 and 16 rows measured slower than 4
+    else DECODE_TC_LAUNCH(4);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
