@@ -668,6 +668,11 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
     const long slot_stride = 4L * L * 64;      // [blk 2][self | cross][L][64] cached attention inputs per env slot
     float* kv0 = b.kv + (long)blockIdx.x * rows * slot_stride;
     const int nd = a.mode == MATAS_MODE_SEMI ? L - 1 : L;
+    // L2 prefetch of one token-major row per live env (two lines each) a phase before its first use: the folded
+    // cross-attention queries and the obs_rep rows are otherwise first touched at the head of a dependency chain
+    auto prefetch_env_rows = [&](const float* row0, int n_live) {
+        if (tid < 2 * n_live) asm volatile("prefetch.global.L2 [%0];" ::"l"(row0 + (long)(tid >> 1) * L * 64 + (tid & 1) * 32));
+    };
     const float sd1 = 0.5f / (1.0f + expf(-s.sHead[lay::DEC_H3_LOGSTD + 1]));
     float* sQ0row = s.sQ0 + row * XS + q * 16;
     float* sQ1row = s.sQ1 + row * XS + q * 16;
@@ -773,6 +778,8 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
                 }
                 tc::fence_before_sync();
                 __syncthreads();
+                prefetch_env_rows(b.Q2p[1][0] + (env0 * L + j) * 64, n_valid);
+                prefetch_env_rows(b.Q2p[1][1] + (env0 * L + j) * 64, n_valid);
                 if (rows <= rows16) attention_absorbed_op16<false, PFD>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
                 else attention_absorbed_op<false, PFD>(s.sQ0, s.sQ1, 0, cx1, slot_stride, rows, n_valid, j + 1, s.U, s.V);
                 }
@@ -853,6 +860,11 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* 
                     affine16(v, w0, q);
                     ring.release();
                 }
+            }
+            if (j + 1 < L) {
+                prefetch_env_rows(b.Q2p[0][0] + (env0 * L + j + 1) * 64, n_valid);
+                prefetch_env_rows(b.Q2p[0][1] + (env0 * L + j + 1) * 64, n_valid);
+                prefetch_env_rows(b.rep + (env0 * L + j + 1) * 64, n_valid);
             }
             // ---- logits head + action pick -------------------------------------------------------------
             if (st.emit) {
