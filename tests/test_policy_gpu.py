@@ -262,3 +262,14 @@ def test_weight_repack_is_skipped_only_when_unchanged(cuda_device):
     assert torch.allclose(m.get_values(None, obs), v0 - 1.0, atol=1e-6)
     m.load_state_dict(mo.full_state_dict(sd, L))
     assert torch.allclose(m.get_values(None, obs), v0, atol=1e-6)
+
+
+def test_table_decode_matches_cached_decode(cuda_device):
+    """The block-0 tables (stochastic and deterministic decode) against per-env cache rows (MATAS_DECODE_TAB=0) at bench
+    sizes: 16384 x 51, 4096 x 201, strides 1 / 2 / 7 / 10.  The switch is read once per process, hence two subprocesses
+    (scripts/tab_check.py)."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "tab_check.py")], cwd=root, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
