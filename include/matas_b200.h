@@ -133,12 +133,6 @@ int matas_policy_act_autoregressive_static(matas_policy* p, const float* obs_rep
  * waits for them and returns the summed device time and the launch count since enabling. */
 int matas_policy_timing(matas_policy* p, int enable);
 int matas_policy_decode_time(matas_policy* p, double* ms_total, long* launches);
-/* Decode phase profiler (no counterpart in the reference): while enabled, CTA 0 of every decode launch adds
- * the clock64 cycles it spends in each phase of a step to 16 counters (0 inputs, 1 query GEMMs, 2 self
- * attention, 3 output GEMMs + LN1, 4 cross inputs, 5 cross attention, 6 output GEMMs + LN2, 7 MLP.0,
- * 8 MLP.2 + LN3, 9 head GEMM, 10 action pick).  Returns the counters in out16 (may be NULL) and clears them. */
-int matas_policy_decode_phases(matas_policy* p, int enable, unsigned long long* out16);
-
 /* Measured fp32 FFMA throughput of the current device in TFLOP/s (no counterpart in the reference;
  * the roofline denominator of the SIMT kernels, which MEASURED_PEAKS.json does not hold). */
 int matas_fp32_peak(int iters, double* tflops);

@@ -84,6 +84,7 @@ extern "C" int matas_policy_act_autoregressive_static(matas_policy* p, const flo
     const long n_tok = B * L;
     PolicyBufs b = {};
     b.w = v.packed;
+    b.x1tab = v.x1tab;                        // block-0 table of the stochastic decode (allocated at set_weights)
     b.rep = const_cast<float*>(obs_rep);      // read-only here: q2_from_rep copies only when rep_in != rep
     for (int k = 0; k < 2; ++k)
         for (int h = 0; h < 2; ++h) b.Q2p[k][h] = scratch + (size_t)(k * 2 + h) * n_tok * 64;
@@ -93,13 +94,13 @@ extern "C" int matas_policy_act_autoregressive_static(matas_policy* p, const flo
     a.B = B; a.L = L; a.mode = v.mode; a.deterministic = deterministic ? 1 : 0; a.stride = stride;
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
     a.seed = seed; a.step = step; a.env_offset = env_offset;
-    { const char* e = getenv("MATAS_PHASED_BELOW"); a.phased_below = e ? atoi(e) : (1 << 30); }
-    { const char* e = getenv("MATAS_PREFETCH"); a.prefetch = e ? atoi(e) : 0; }
-    a.phase_cycles = nullptr;
     a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
-    int grid; long slots;
-    if ((rc = policy_decode_geometry(L, B, v.n_sm, &grid, &slots))) return rc;
-    // B*L <= 2048 keeps the tile count far below the resident CTA count: one CTA per tile, env slot ==
-    // env index, and only the B valid slots are ever touched, so the cache fits the array
-    return launch_decode(b, a, grid, (cudaStream_t)stream);
+    int grid, rows; long slots;
+    if ((rc = policy_decode_geometry(L, B, v.n_sm, &grid, &slots, &rows))) return rc;
+    // The kernel addresses the cache as [grid * rows env slots][4][L][64]; tiles are padded to a multiple of four envs,
+    // so the slot count can exceed B: the padded geometry must fit the part of the array behind the query rows.
+    ARG_CHECK((size_t)slots * 4 * L * 64 <= MATAS_STATIC_FLOATS - (size_t)MATAS_STATIC_MAX_TOKENS * 64 * 4,
+              "static scratch too small for %ld padded env slots x %d agents", slots, L);
+    a.rows = rows;
+    return launch_decode_tc(b, a, grid, (cudaStream_t)stream);
 }

@@ -176,18 +176,16 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
 
 }  // namespace
 
+bool attn_tile_supported(int L) { return L <= 64; }
+
 int launch_attn_bwd_tile(const float* Q, const float* K, const float* V, const float* gY, const float* lse, const float* D, float* dQ,
                          float* dK, float* dV, long n_env, int L, int causal, cudaStream_t st) {
     const BGeom g = bgeom(L);
-    static int e_env = -1, t_env = -1;                  // tuning overrides: MATAS_ABT_E (envs per CTA), MATAS_ABT_THREADS
-    if (e_env < 0) { const char* e = getenv("MATAS_ABT_E"); e_env = e ? atoi(e) : 0; }
-    if (t_env < 0) { const char* e = getenv("MATAS_ABT_THREADS"); t_env = e ? atoi(e) : 0; }
     // measured on B200 (12800 x 21 / 4096 x 51): small CTAs with one env each beat packing several envs into a
     // CTA (more resident CTAs hide the shared-memory latency): 64 threads up to 64 phase-1 tasks, else 128
     const int tasks = g.nb * g.nb;
-    const int nthr = t_env ? t_env : (tasks > 64 ? BNT : 64);
-    int E = e_env ? e_env : (tasks >= 32 ? 1 : 32 / tasks);
-    if (E < 1) E = 1;
+    const int nthr = tasks > 64 ? BNT : 64;
+    int E = tasks >= 32 ? 1 : 32 / tasks;
     if (E > 4) E = 4;
     const size_t bytes = (size_t)E * g.env_floats * sizeof(float);
     const long groups = (n_env + E - 1) / E;

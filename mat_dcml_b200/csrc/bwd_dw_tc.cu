@@ -130,8 +130,7 @@ int launch_bwd_dw(const float* packed, float* grad, const DwJobs& jobs, long n_t
     if (jobs.n <= 0) return MATAS_OK;
     CUDA_TRY(cudaFuncSetAttribute(bwd_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM));
     const long n_chunks = (n_tok + TK - 1) / TK;
-    static int per_sm = -1;                                     // CTAs per SM over all jobs of a launch (MATAS_DW_PER_SM)
-    if (per_sm < 0) { const char* e = getenv("MATAS_DW_PER_SM"); per_sm = e ? atoi(e) : 2; }     // measured: 2 beats 1 (parallelism) and 4 (twice the atomics)
+    constexpr int per_sm = 2;         // CTAs per SM over all jobs of a launch; measured: 2 beats 1 (parallelism) and 4 (twice the atomics)
     long splits = ((long)per_sm * n_sm + jobs.n - 1) / jobs.n;
     if (splits > n_chunks) splits = n_chunks;
     if (splits < 1) splits = 1;

@@ -130,7 +130,6 @@ struct matas_policy {
     long train_cap = 0;
     float* d_train = nullptr;
     long train_tokens = 0;        // > 0: the saved activations belong to a training forward of that many tokens
-    unsigned long long* d_phase = nullptr;   // decode phase profiler counters (matas_policy_decode_phases)
     // optional per-launch timing of the decode kernel (CUDA events on the launching stream)
     static constexpr int NEV = 64;
     bool timing = false;
@@ -241,8 +240,7 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     ARG_CHECK(cfg->n_agent >= 2, "n_agent %d < 2", cfg->n_agent);
     ARG_CHECK(cfg->state_dim >= 1, "state_dim %d < 1", cfg->state_dim);
     ARG_CHECK(cfg->mode == MATAS_MODE_SEMI || cfg->mode == MATAS_MODE_DISCRETE, "bad mode %d", cfg->mode);
-    int rpt, depth; size_t bytes;
-    int rc = policy_launch_geometry(cfg->n_agent, 1 << 20, &rpt, &depth, &bytes, 0);
+    int rc = policy_check_agents(cfg->n_agent);
     if (rc) return rc;
     matas_policy* p = new matas_policy();
     p->cfg = *cfg;
@@ -294,14 +292,13 @@ extern "C" int matas_policy_create(const matas_model_cfg* cfg, matas_policy** ou
     if ((e = cudaMalloc(&p->d_packed, lay::TOTAL_HB * sizeof(float))) != cudaSuccess) return fail(e, "cudaMalloc(packed)");
     if ((e = cudaMemset(p->d_packed, 0, lay::TOTAL_HB * sizeof(float))) != cudaSuccess) return fail(e, "cudaMemset(packed)");
     p->bufs.w = p->d_packed;
-    if ((rc = policy_init_constants())) { matas_policy_destroy(p); return rc; }
     *out = p;
     return MATAS_OK;
 }
 
 extern "C" int matas_policy_destroy(matas_policy* p) {
     if (!p) return MATAS_OK;
-    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_half); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_x1tab); cudaFree(p->d_x1spec); cudaFree(p->d_train); cudaFree(p->d_phase);
+    cudaFree(p->d_table); cudaFree(p->d_folds); cudaFree(p->d_half); cudaFree(p->d_packed); cudaFree(p->d_tok); cudaFree(p->d_kv); cudaFree(p->d_x1tab); cudaFree(p->d_x1spec); cudaFree(p->d_train);
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { cudaEventDestroy(p->ev0[i]); cudaEventDestroy(p->ev1[i]); }
     delete p;
     return MATAS_OK;
@@ -313,7 +310,7 @@ extern "C" long matas_policy_param_count(const matas_policy* p) { return p ? p->
 int matas_policy_view(const matas_policy* p, PolicyView* v) {
     ARG_CHECK(p && v, "null policy handle");
     v->n_agent = p->cfg.n_agent; v->mode = p->cfg.mode; v->device = p->device; v->n_sm = p->n_sm;
-    v->weights_set = p->weights_set ? 1 : 0; v->packed = p->d_packed;
+    v->weights_set = p->weights_set ? 1 : 0; v->packed = p->d_packed; v->x1tab = p->d_x1tab;
     return MATAS_OK;
 }
 
@@ -323,7 +320,7 @@ extern "C" int matas_policy_set_weights(matas_policy* p, const float* flat, void
     fold_kernel<<<(unsigned)p->folds.size(), 256, 0, (cudaStream_t)stream>>>(flat, p->d_packed, p->d_folds);
     half_kernel<<<(unsigned)p->n_half, 256, 0, (cudaStream_t)stream>>>(p->d_packed, p->d_half);
     CUDA_TRY(cudaGetLastError());
-    if (policy_use_tc()) {
+    {   // block-0 cross-attention inputs by (position, ones so far, previous action): decode_tc.cu
         const int L = p->cfg.n_agent;
         if (!p->d_x1tab) CUDA_TRY(cudaMalloc(&p->d_x1tab, (size_t)L * (L + 1) * 64 * sizeof(float)));
         int rc_ = launch_x1_table(p->d_packed, p->d_x1tab, L, (cudaStream_t)stream);
@@ -358,15 +355,15 @@ extern "C" int matas_policy_get_values(matas_policy* p, const float* obs, long B
     if (rc) return rc;
     ARG_CHECK(obs && values && B > 0, "bad argument (B=%ld)", B);
     if ((rc = alloc_tokens(p, B * p->cfg.n_agent))) return rc;
-    return launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream);
+    return launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, p->n_sm, (cudaStream_t)stream);
 }
 
 static int run_decode(matas_policy* p, const float* ava, long B, int deterministic, int stride, uint64_t seed,
                       uint32_t step, long env_offset, const float* u, const float* z, float* actions, float* logp,
                       cudaStream_t stream) {
     const int L = p->cfg.n_agent;
-    int grid; long slots;
-    { int rc_ = policy_decode_geometry(L, B, p->n_sm, &grid, &slots); if (rc_) return rc_; }
+    int grid, rows; long slots;
+    { int rc_ = policy_decode_geometry(L, B, p->n_sm, &grid, &slots, &rows); if (rc_) return rc_; }
     const size_t need = (size_t)slots * 4 * L * 64 * sizeof(float);
     if (need > p->kv_cap) {
         if (p->d_kv) CUDA_TRY(cudaFree(p->d_kv));
@@ -397,17 +394,15 @@ static int run_decode(matas_policy* p, const float* ava, long B, int determinist
     a.B = B; a.L = L; a.mode = p->cfg.mode; a.deterministic = deterministic ? 1 : 0; a.stride = stride;
     a.n_steps = policy_decode_steps(L, a.mode, a.deterministic, stride);
     a.seed = seed; a.step = step; a.env_offset = env_offset;
-    { const char* e = getenv("MATAS_PHASED_BELOW"); a.phased_below = e ? atoi(e) : (1 << 30); }
-    { const char* e = getenv("MATAS_PREFETCH"); a.prefetch = e ? atoi(e) : 0; }
-    a.phase_cycles = p->d_phase;
+    a.rows = rows;
     a.ava = ava; a.u = u; a.z = z; a.actions = actions; a.logp = logp;
-    if (!p->timing) return launch_decode(p->bufs, a, grid, stream);
+    if (!p->timing) return launch_decode_tc(p->bufs, a, grid, stream);
     const int i = p->ev_next;
     p->ev_next = (i + 1) % matas_policy::NEV;
     int rc = harvest(p, i);
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(p->ev0[i], stream));
-    rc = launch_decode(p->bufs, a, grid, stream);
+    rc = launch_decode_tc(p->bufs, a, grid, stream);
     CUDA_TRY(cudaEventRecord(p->ev1[i], stream));
     p->ev_pending[i] = true;
     return rc;
@@ -426,15 +421,6 @@ extern "C" int matas_policy_timing(matas_policy* p, int enable) {
     if (p->ev_made) for (int i = 0; i < matas_policy::NEV; ++i) { int rc = harvest(p, i); if (rc) return rc; }
     p->timing = enable != 0;
     p->t_ms = 0.0; p->t_n = 0;
-    return MATAS_OK;
-}
-
-extern "C" int matas_policy_decode_phases(matas_policy* p, int enable, unsigned long long* out16) {
-    ARG_CHECK(p != nullptr, "null policy handle");
-    if (out16 && p->d_phase) CUDA_TRY(cudaMemcpy(out16, p->d_phase, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-    if (enable && !p->d_phase) CUDA_TRY(cudaMalloc(&p->d_phase, 16 * sizeof(unsigned long long)));
-    if (p->d_phase) CUDA_TRY(cudaMemset(p->d_phase, 0, 16 * sizeof(unsigned long long)));
-    if (!enable && p->d_phase) { CUDA_TRY(cudaFree(p->d_phase)); p->d_phase = nullptr; }
     return MATAS_OK;
 }
 
@@ -495,7 +481,7 @@ extern "C" int matas_policy_get_actions(matas_policy* p, const float* obs, const
     if (rc) return rc;
     ARG_CHECK(obs && values && actions && logp && B > 0, "bad argument (B=%ld)", B);
     if ((rc = alloc_tokens(p, B * p->cfg.n_agent))) return rc;
-    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream, nullptr, 1))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, p->n_sm, (cudaStream_t)stream, nullptr, 1))) return rc;
     return run_decode(p, ava, B, deterministic, stride, seed, step, env_offset, u, z, actions, logp, (cudaStream_t)stream);
 }
 
@@ -519,7 +505,7 @@ extern "C" int matas_policy_act_parallel(matas_policy* p, const float* obs_rep, 
     const int L = p->cfg.n_agent;
     if ((rc = alloc_tokens(p, M * L))) return rc;
     if ((rc = launch_q2_from_rep(p->bufs, obs_rep, M, L, (cudaStream_t)stream, 0))) return rc;
-    return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream);
+    return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, p->n_sm, (cudaStream_t)stream);
 }
 
 static int alloc_train(matas_policy* p, long n_tok) {
@@ -563,8 +549,8 @@ extern "C" int matas_policy_evaluate_train(matas_policy* p, const float* obs, co
     if (L > 256) { matas_set_error("training supports n_agent <= 256 (got %d)", L); return MATAS_ERR_LIMIT; }
     if ((rc = alloc_tokens(p, M * L))) return rc;
     if ((rc = alloc_train(p, M * L))) return rc;
-    if ((rc = launch_encoder(p->bufs, obs, values, M, L, p->cfg.obs_dim, (cudaStream_t)stream, &p->tb))) return rc;
-    if ((rc = launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream, &p->tb))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, M, L, p->cfg.obs_dim, p->n_sm, (cudaStream_t)stream, &p->tb))) return rc;
+    if ((rc = launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, p->n_sm, (cudaStream_t)stream, &p->tb))) return rc;
     p->train_tokens = M * L;
     return MATAS_OK;
 }
@@ -592,7 +578,7 @@ extern "C" int matas_policy_encode(matas_policy* p, const float* obs, long B, fl
     ARG_CHECK(obs && values && obs_rep && B > 0, "bad argument (B=%ld)", B);
     const long n_tok = B * p->cfg.n_agent;
     if ((rc = alloc_tokens(p, n_tok))) return rc;
-    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, (cudaStream_t)stream))) return rc;
+    if ((rc = launch_encoder(p->bufs, obs, values, B, p->cfg.n_agent, p->cfg.obs_dim, p->n_sm, (cudaStream_t)stream))) return rc;
     CUDA_TRY(cudaMemcpyAsync(obs_rep, p->bufs.rep, (size_t)n_tok * 64 * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return MATAS_OK;
 }
@@ -604,6 +590,6 @@ extern "C" int matas_policy_evaluate(matas_policy* p, const float* obs, const fl
     ARG_CHECK(obs && actions && values && logp && entropy && M > 0, "bad argument (M=%ld)", M);
     const int L = p->cfg.n_agent;
     if ((rc = alloc_tokens(p, M * L))) return rc;
-    if ((rc = launch_encoder(p->bufs, obs, values, M, L, p->cfg.obs_dim, (cudaStream_t)stream))) return rc;
-    return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, (cudaStream_t)stream);
+    if ((rc = launch_encoder(p->bufs, obs, values, M, L, p->cfg.obs_dim, p->n_sm, (cudaStream_t)stream))) return rc;
+    return launch_teacher_forced(p->bufs, actions, ava, logp, entropy, M, L, p->cfg.mode, p->n_sm, (cudaStream_t)stream);
 }

@@ -31,6 +31,8 @@ constexpr int MAXR = 128;            // env rows per tile (MMA M)
 constexpr int DEPTH = 4;             // weight ring slots
 constexpr int TMEM_D = 256;          // accumulator columns
 constexpr int OP_BYTES = 2 * tc::A_PART;
+constexpr int ROWS16 = 32;          // tiles of at most this many envs use 16 lanes per env in the attention
+constexpr int PF_ROWS = 4;          // in-loop L2 prefetch distance of the cache-row loads (8 and 16 measured slower)
 
 constexpr int STEP_BLOBS = lay::DEC_FOLD_STEP_BLOBS - 2;     // block 0 needs no query maps (see code_counts)
 __constant__ int c_tc_decode[STEP_BLOBS] = {
@@ -616,12 +618,13 @@ x1_spec_table_kernel(const float* __restrict__ w, float* __restrict__ spec, int 
 // 2 = the same plus the speculative rows of the deterministic stride blocks
 template <int PFD, int TABK>
 __global__ void __launch_bounds__(NTD, 1)
-decode_tc_kernel(PolicyBufs b, DecodeArgs a, int rows, int rows16, const float* __restrict__ x1tab, const float* __restrict__ x1spec) {
+decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, const float* __restrict__ x1spec) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     DSmem s = dcarve(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5;
     const int row = (warp & 3) * 32 + (tid & 31), q = warp >> 2;
-    const int L = a.L;
+    const int L = a.L, rows = a.rows;
+    constexpr int rows16 = ROWS16;
     const long n_tiles = (a.B + rows - 1) / rows;
     long my_tiles = 0;
     for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++my_tiles;
@@ -974,40 +977,37 @@ int decode_tc_rows(long B, int n_sm) {
     return (int)r;
 }
 
-int decode_tc_geometry(long B, int n_sm, int* grid, long* slots) {
+int decode_tc_geometry(long B, int n_sm, int* grid, long* slots, int* rows_out) {
     const int rows = decode_tc_rows(B, n_sm);
     const long n_tiles = (B + rows - 1) / rows;
     *grid = (int)(n_tiles < n_sm ? n_tiles : n_sm);
     *slots = (long)*grid * rows;
+    *rows_out = rows;
     return MATAS_OK;
 }
 
-int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st) {
-    const size_t bytes = dsmem_bytes();
-    static int pf = -1;
-    if (pf < 0) { const char* e = getenv("MATAS_DECODE_PF"); pf = e ? atoi(e) : 4; }
-    const int rows = decode_tc_rows(a.B, n_sm);
-    static int rows16 = -1;          // tiles of at most this many envs use 16 lanes per env in the attention (MATAS_DECODE_ROWS16)
-    if (rows16 < 0) { const char* e = getenv("MATAS_DECODE_ROWS16"); rows16 = e ? atoi(e) : 32; }
-    static int use_tab = -1;         // MATAS_DECODE_TAB=0: block 0 keeps its per-env cache rows in the stochastic decode too (A/B switch)
+static int decode_use_tab() {
+    // MATAS_DECODE_TAB=0: block 0 keeps per-env cache rows instead of the shared tables -- the comparand of the
+    // table-mode regression test (scripts/tab_check.py, tests/test_policy_gpu.py)
+    static int use_tab = -1;
     if (use_tab < 0) { const char* e = getenv("MATAS_DECODE_TAB"); use_tab = e ? atoi(e) : 1; }
+    return use_tab;
+}
+
+int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st) {
+    const size_t bytes = dsmem_bytes();
     // stochastic decode: the standard table; deterministic Semi_Discrete decode: plus the speculative rows of its stride blocks
-    const float* tab = (use_tab && (!a.deterministic || (a.mode == MATAS_MODE_SEMI && b.x1spec))) ? b.x1tab : nullptr;
-#define DECODE_TC_LAUNCH(P)                                                                                           \
-    do {                                                                                                              \
-        if (tab && a.deterministic) {                                                                                 \
-            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-            decode_tc_kernel<P, 2><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, b.x1spec);                         \
-        } else if (tab) {                                                                                             \
-            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-            decode_tc_kernel<P, 1><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, tab, nullptr);                          \
-        } else {                                                                                                      \
-            CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<P, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-            decode_tc_kernel<P, 0><<<grid, NTD, bytes, st>>>(b, a, rows, rows16, nullptr, nullptr);                      \
-        }                                                                                                             \
-    } while (0)
-    if (pf == 0) DECODE_TC_LAUNCH(0);        // MATAS_DECODE_PF=0: no in-loop L2 prefetch (A/B); distances of 8 and 16 rows measured slower than 4
-    else DECODE_TC_LAUNCH(4);
+    const float* tab = (decode_use_tab() && b.x1tab && (!a.deterministic || (a.mode == MATAS_MODE_SEMI && b.x1spec))) ? b.x1tab : nullptr;
+    if (tab && a.deterministic) {
+        CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<PF_ROWS, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        decode_tc_kernel<PF_ROWS, 2><<<grid, NTD, bytes, st>>>(b, a, tab, b.x1spec);
+    } else if (tab) {
+        CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<PF_ROWS, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        decode_tc_kernel<PF_ROWS, 1><<<grid, NTD, bytes, st>>>(b, a, tab, nullptr);
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(decode_tc_kernel<PF_ROWS, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        decode_tc_kernel<PF_ROWS, 0><<<grid, NTD, bytes, st>>>(b, a, nullptr, nullptr);
+    }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }

@@ -18,7 +18,6 @@ using namespace tile;
 
 namespace {
 
-constexpr float HALF_LOG_2PI = 0.91893853320467274178f;
 constexpr float MASK_LOGIT = -1e10f;
 constexpr float SCALE = 0.17677669529663687f;   // 1/sqrt(32)
 constexpr int BDEPTH = 3;          // ring depth of the 1-CTA/SM kernels
@@ -104,28 +103,6 @@ __device__ __forceinline__ void col_flush(const Col& c, float* __restrict__ grad
     for (int j = 0; j < 4; ++j) atomicAdd(grad + off + cg * 4 + j, c.v[j]);
 }
 
-// weight-gradient accumulator: dW[4rg+i][4cg+j] += sum_t dY[t][4rg+i] * X[t][4cg+j]
-struct DW { float v[4][4]; __device__ void zero() { for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) v[i][j] = 0.f; } };
-__device__ __forceinline__ void dw_acc(DW& w, const float* __restrict__ dY, const float* __restrict__ X, int n_valid, int rg, int cg) {
-#pragma unroll 4
-    for (int t = 0; t < n_valid; ++t) {
-        const float4 a = *reinterpret_cast<const float4*>(dY + t * XS + rg * 4);
-        const float4 b = *reinterpret_cast<const float4*>(X + t * XS + cg * 4);
-        const float av[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            w.v[i][0] = fmaf(av[i], b.x, w.v[i][0]); w.v[i][1] = fmaf(av[i], b.y, w.v[i][1]);
-            w.v[i][2] = fmaf(av[i], b.z, w.v[i][2]); w.v[i][3] = fmaf(av[i], b.w, w.v[i][3]);
-        }
-    }
-}
-__device__ __forceinline__ void dw_flush(const DW& w, float* __restrict__ grad, int off, int rg, int cg) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) atomicAdd(grad + off + (rg * 4 + i) * 64 + cg * 4 + j, w.v[i][j]);
-}
-
 // dX fragment = dY(tile in shared) . W (untransposed weights from the ring)
 __device__ __forceinline__ void gemm_dx(Ring& ring, const float* __restrict__ dY, Frag& out, int rg, int cg, bool accumulate) {
     const float* W = ring.acquire();
@@ -177,119 +154,6 @@ __device__ __forceinline__ void gelu_bwd(Frag& d, const Frag& h) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) d.v[i][j] *= gelu_grad(h.v[i][j]);
 }
-__device__ __forceinline__ void gelu_fwd(Frag& g, const Frag& h) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) g.v[i][j] = gelu_erf(h.v[i][j]);
-}
-
-// projection backward shared by every attention: dS (grad of the proj output, fragment) ->
-// dWp, dbp, dY = dS.Wp stored to gY, D = rowsum_head(dY * Y) stored to gD
-template <bool TCW>
-__device__ __forceinline__ void proj_bwd(Ring& ring, const BSmem& s, const Frag& dS, const float* __restrict__ Y_g,
-                                         float* __restrict__ gY, float* __restrict__ gD, long row0, int n_valid,
-                                         DW& dWp, Col& dbp, int rg, int cg, float* __restrict__ sY) {
-    col_add(dbp, dS);
-    frag_store_s(dS, s.T[0], rg, cg);
-    Frag y;
-    frag_load_g(y, Y_g, row0, n_valid, rg, cg);
-    if (TCW) frag_store_g(dS, sY, row0, n_valid, rg, cg, false);    // weight gradient on the tensor cores (bwd_dw_tc.cu)
-    else frag_store_s(y, s.T[1], rg, cg);
-    __syncthreads();
-    if (!TCW) dw_acc(dWp, s.T[0], s.T[1], n_valid, rg, cg);
-    Frag dY;
-    gemm_dx(ring, s.T[0], dY, rg, cg, false);
-    frag_store_g(dY, gY, row0, n_valid, rg, cg, false);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        float p = dY.v[i][0] * y.v[i][0] + dY.v[i][1] * y.v[i][1] + dY.v[i][2] * y.v[i][2] + dY.v[i][3] * y.v[i][3];
-        p += __shfl_xor_sync(0xffffffffu, p, 4);
-        p += __shfl_xor_sync(0xffffffffu, p, 2);
-        p += __shfl_xor_sync(0xffffffffu, p, 1);
-        const int r = rg * 4 + i;
-        if ((cg & 7) == 0 && r < n_valid) gD[(row0 + r) * 2 + (cg >> 3)] = p;
-    }
-    __syncthreads();
-    ring.prefetch();
-}
-
-
-// [LN_F bwd -> MLP bwd ->] LN_M bwd -> residual grad -> projection bwd      (encoder E1, decoder K1 / K2b)
-template <bool TCW>       // TCW: weight gradients on the tensor cores (bwd_dw_tc.cu): no dW accumulators here
-__global__ void __launch_bounds__(NT, 1)
-bwd_mlp_proj(const float* __restrict__ packed, float* __restrict__ grad, TailArgs a, long n_tok) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    BSmem s = bcarve(smem_raw, BDEPTH);
-    const int tid = threadIdx.x, rg = tid >> 4, cg = tid & 15;
-    const long n_tiles = (n_tok + TM - 1) / TM;
-    long mine = 0;
-    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) ++mine;
-    int* sseq = reinterpret_cast<int*>(s.sSmall + 512);
-    const int nseq = a.with_mlp ? 3 : 1;
-    if (tid < nseq) sseq[tid] = a.with_mlp ? a.seq[tid] : a.seq[2];
-    for (int i = tid; i < 128; i += NT) {
-        s.sSmall[i] = packed[a.lnF + lay::B_LNW + i];        // lnF w | b
-        s.sSmall[128 + i] = packed[a.lnM + lay::B_LNW + i];  // lnM w | b
-    }
-    Ring ring;
-    ring.init(s.ring, s.bars, packed, sseq, nseq, (int)(mine * nseq), BDEPTH, lay::BW_BYTES);
-    __syncthreads();
-    ring.prefetch();
-    const float *lnFw = s.sSmall, *lnMw = s.sSmall + 128, *lnMb = s.sSmall + 192;
-    DW dW2, dW0, dWp; dW2.zero(); dW0.zero(); dWp.zero();
-    Col db2, db0, dbp, gFw, gFb, gMw, gMb;
-    db2.zero(); db0.zero(); dbp.zero(); gFw.zero(); gFb.zero(); gMw.zero(); gMb.zero();
-    for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long row0 = tile * TM;
-        const int n_valid = (int)min((long)TM, n_tok - row0);
-        Frag d, xh;
-        frag_load_g(d, a.gOut, row0, n_valid, rg, cg);
-        if (a.with_mlp) {
-            frag_load_g(xh, a.xhF, row0, n_valid, rg, cg);
-            ln_bwd(d, xh, a.rsF, row0, n_valid, lnFw, gFw, gFb, rg, cg);            // d = dS (grad of x_M + mlp(x_M))
-            col_add(db2, d);
-            Frag h, g;
-            frag_load_g(h, a.m0, row0, n_valid, rg, cg);
-            if (!TCW) gelu_fwd(g, h);
-            frag_store_s(d, s.T[0], rg, cg);
-            if (TCW) frag_store_g(d, a.sY[0], row0, n_valid, rg, cg, false);
-            else frag_store_s(g, s.T[1], rg, cg);
-            __syncthreads();
-            if (!TCW) dw_acc(dW2, s.T[0], s.T[1], n_valid, rg, cg);
-            Frag dm;
-            gemm_dx(ring, s.T[0], dm, rg, cg, false);                                // dG = dS . W2
-            gelu_bwd(dm, h);                                                          // dM0
-            col_add(db0, dm);
-            frag_load_g(xh, a.xhM, row0, n_valid, rg, cg);
-            Frag xm;
-            if (!TCW) ln_affine(xm, xh, lnMw, lnMb, cg);
-            frag_store_s(dm, s.T[2], rg, cg);
-            if (TCW) frag_store_g(dm, a.sY[1], row0, n_valid, rg, cg, false);
-            else frag_store_s(xm, s.T[3], rg, cg);
-            __syncthreads();
-            ring.prefetch();
-            if (!TCW) dw_acc(dW0, s.T[2], s.T[3], n_valid, rg, cg);
-            gemm_dx(ring, s.T[2], d, rg, cg, true);                                  // dX_M = dS + dM0 . W0
-        } else {
-            frag_load_g(xh, a.xhM, row0, n_valid, rg, cg);
-        }
-        ln_bwd(d, xh, a.rsM, row0, n_valid, lnMw, gMw, gMb, rg, cg);                 // d = grad of (residual + proj)
-        frag_store_g(d, a.gRes, row0, n_valid, rg, cg, a.res_add != 0);
-        __syncthreads();          // T[0]/T[1] free again (dw_acc above is done in every thread)
-        ring.prefetch();
-        proj_bwd<TCW>(ring, s, d, a.Y, a.gY, a.gD, row0, n_valid, dWp, dbp, rg, cg, a.sY[2]);
-    }
-    if (a.with_mlp) {
-        if (!TCW) { dw_flush(dW2, grad, a.gW2, rg, cg); dw_flush(dW0, grad, a.gW0, rg, cg); }
-        col_flush(db2, grad, a.gb2, cg); col_flush(db0, grad, a.gb0, cg);
-        col_flush(gFw, grad, a.glnFw, cg); col_flush(gFb, grad, a.glnFb, cg);
-    }
-    if (!TCW) dw_flush(dWp, grad, a.gWp, rg, cg);
-    col_flush(dbp, grad, a.gbp, cg);
-    col_flush(gMw, grad, a.glnMw, cg); col_flush(gMb, grad, a.glnMb, cg);
-}
-
 // -------------------------------------------------------------------------------------------------
 // attention backward.  KIND 0: q, k, v all project the same input (encoder attention, decoder
 // self-attention); KIND 1: decoder cross-attention (q from obs_rep, k/v from the decoder stream).
@@ -400,7 +264,7 @@ __device__ __forceinline__ void attn_bwd_rows(const AttnArgs& a, long row0, long
     }
 }
 
-template <int KIND, bool TCW>
+template <int KIND>
 __global__ void __launch_bounds__(NT, 2)
 bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -416,14 +280,12 @@ bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a,
     ring.init(s.ring, s.bars, packed, sseq, 3, (int)(mine * 3), ADEPTH, lay::BW_BYTES);
     __syncthreads();
     ring.prefetch();
-    float* sX = s.T[0];                                   // input of the projection being differentiated
     float *sDq = s.T[1], *sDv = s.T[2], *sDk = s.T[3];
-    DW dWq, dWk, dWv; dWq.zero(); dWk.zero(); dWv.zero();
     Col dbq, dbk, dbv; dbq.zero(); dbk.zero(); dbv.zero();
     for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long row0 = tile * TM;
         const int n_valid = (int)min((long)TM, n_tok - row0);
-        if (TCW && a.pre) {
+        if (a.pre) {
             load_tile(sDq, a.sY[0] + row0 * 64, 64, n_valid);
             load_tile(sDk, a.sY[1] + row0 * 64, 64, n_valid);
             load_tile(sDv, a.sY[2] + row0 * 64, 64, n_valid);
@@ -432,50 +294,32 @@ bwd_attn(const float* __restrict__ packed, float* __restrict__ grad, AttnArgs a,
         }
         // ---- projections: dW, db, dX -------------------------------------------------------------
         Frag dx;
-        constexpr bool tcw = TCW;                                        // weight gradients on the tensor cores (bwd_dw_tc.cu)
-        const bool put = TCW && !a.pre;                                  // hand dq / dk / dv to the weight-gradient kernel
+        const bool put = !a.pre;                                         // hand dq / dk / dv to the weight-gradient kernel (bwd_dw_tc.cu)
         if (KIND == 1) {
-            if (!tcw) load_tile(sX, a.xin + row0 * 64, 64, n_valid);   // obs_rep: the query input
             __syncthreads();
             { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (put) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
-            if (!tcw) dw_acc(dWq, sDq, sX, n_valid, rg, cg);
             gemm_dx(ring, sDq, dx, rg, cg, false);
             frag_store_g(dx, a.gRep, row0, n_valid, rg, cg, true);
             __syncthreads();
             ring.prefetch();
         }
-        if (!tcw) {
-            Frag xin;
-            if (a.ln >= 0) {
-                Frag xh;
-                frag_load_g(xh, a.xh, row0, n_valid, rg, cg);
-                ln_affine(xin, xh, s.sSmall, s.sSmall + 64, cg);
-            } else {
-                frag_load_g(xin, a.xin, row0, n_valid, rg, cg);
-            }
-            frag_store_s(xin, sX, rg, cg);                              // k/v (and KIND 0: q) input
-        }
         __syncthreads();
         if (KIND == 0) {
             { Frag f; frag_load_s(f, sDq, rg, cg); col_add(dbq, f); if (put) frag_store_g(f, a.sY[0], row0, n_valid, rg, cg, false); }
-            if (!tcw) dw_acc(dWq, sDq, sX, n_valid, rg, cg);
             gemm_dx(ring, sDq, dx, rg, cg, false);
             __syncthreads();
             ring.prefetch();
         }
         { Frag f; frag_load_s(f, sDk, rg, cg); col_add(dbk, f); if (put) frag_store_g(f, a.sY[1], row0, n_valid, rg, cg, false); }
-        if (!tcw) dw_acc(dWk, sDk, sX, n_valid, rg, cg);
         gemm_dx(ring, sDk, dx, rg, cg, KIND == 0);
         __syncthreads();
         ring.prefetch();
         { Frag f; frag_load_s(f, sDv, rg, cg); col_add(dbv, f); if (put) frag_store_g(f, a.sY[2], row0, n_valid, rg, cg, false); }
-        if (!tcw) dw_acc(dWv, sDv, sX, n_valid, rg, cg);
         gemm_dx(ring, sDv, dx, rg, cg, true);
         frag_store_g(dx, a.gX, row0, n_valid, rg, cg, KIND == 0);       // KIND 0: += ; KIND 1: =
         __syncthreads();
         ring.prefetch();
     }
-    if (!TCW) { dw_flush(dWq, grad, a.gWq, rg, cg); dw_flush(dWk, grad, a.gWk, rg, cg); dw_flush(dWv, grad, a.gWv, rg, cg); }
     col_flush(dbq, grad, a.gbq, cg); col_flush(dbk, grad, a.gbk, cg); col_flush(dbv, grad, a.gbv, cg);
 }
 
@@ -498,7 +342,7 @@ struct HeadArgs {
     float* sY;                       // non-null: write d(head.0 output) there instead of accumulating dW0 here
 };
 
-template <int DEC, bool TCW>
+template <int DEC>
 __global__ void __launch_bounds__(NT, 1)
 bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a, long n_tok) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -520,7 +364,6 @@ bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a,
     ring.prefetch();
     const float* w3 = s.sSmall + 256;     // DEC: w0[64] w1[64] b[2] log_std[2];  ENC: w[64] b[1]
     float* sdl = s.sSmall + 640;          // [TM][2] d(logits) / d(value)
-    DW dW0; dW0.zero();
     Col db0, glw, glb, gw3a, gw3b; db0.zero(); glw.zero(); glb.zero(); gw3a.zero(); gw3b.zero();
     float gb3a = 0.f, gb3b = 0.f, gls = 0.f;
     for (long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -590,25 +433,15 @@ bwd_head(const float* __restrict__ packed, float* __restrict__ grad, HeadArgs a,
         frag_load_g(h, a.hh, row0, n_valid, rg, cg);
         gelu_bwd(d, h);                                                    // d = d(pre-GELU of head.0)
         col_add(db0, d);
-        Frag xin;
-        if (DEC) {
-            frag_load_g(xh, a.xh_in, row0, n_valid, rg, cg);
-            ln_affine(xin, xh, s.sSmall + 128, s.sSmall + 192, cg);
-        } else {
-            frag_load_g(xin, a.rep, row0, n_valid, rg, cg);
-        }
         frag_store_s(d, s.T[1], rg, cg);
-        if (TCW) frag_store_g(d, a.sY, row0, n_valid, rg, cg, false);
-        else frag_store_s(xin, s.T[2], rg, cg);
+        frag_store_g(d, a.sY, row0, n_valid, rg, cg, false);               // weight gradient: bwd_dw_tc.cu
         __syncthreads();
-        if (!TCW) dw_acc(dW0, s.T[1], s.T[2], n_valid, rg, cg);
         Frag dx;
         gemm_dx(ring, s.T[1], dx, rg, cg, false);
         frag_store_g(dx, a.gOut, row0, n_valid, rg, cg, DEC ? false : true);
         __syncthreads();
         ring.prefetch();
     }
-    if (!TCW) dw_flush(dW0, grad, a.gW0, rg, cg);
     col_flush(db0, grad, a.gb0, cg); col_flush(glw, grad, a.glnw, cg); col_flush(glb, grad, a.glnb, cg);
     col_flush(gw3a, grad, a.gW3, cg);
     if (DEC) col_flush(gw3b, grad, a.gW3 + 64, cg);
@@ -804,16 +637,9 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         return MATAS_ERR_LIMIT;
     }
     const size_t bytes = bsmem_bytes(BDEPTH), abytes = bsmem_bytes(ADEPTH);
-    const bool tcw = policy_use_tc();               // weight gradients on the tensor cores (bwd_dw_tc.cu)
-    static int tile_env = -1;                       // MATAS_ATTN_TILE=0 keeps the attention backward inside bwd_attn (A/B runs)
-    if (tile_env < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tile_env = e ? atoi(e) : 1; }
-    const bool tiled = tcw && tile_env && attn_tile_supported(L);
-    static int dx_env = -1;                         // MATAS_DX_TC=0: q/k/v input gradients stay in bwd_attn's SIMT GEMMs (A/B runs)
-    if (dx_env < 0) { const char* e = getenv("MATAS_DX_TC"); dx_env = e ? atoi(e) : 1; }
-    const bool dxtc = tiled && dx_env;
-    static int mlp_env = -1;                        // MATAS_MLP_TC=0: block tails stay on bwd_mlp_proj's SIMT GEMMs (A/B runs)
-    if (mlp_env < 0) { const char* e = getenv("MATAS_MLP_TC"); mlp_env = e ? atoi(e) : 1; }
-    const bool mlptc = tcw && mlp_env;
+    // n_agent <= 64: register-tiled attention backward (attn_bwd_tile.cu) + q/k/v input gradients on the tensor cores
+    // (bwd_dx_tc.cu); larger n_agent: the half-warp-per-row attention backward inside bwd_attn with SIMT input gradients
+    const bool tiled = attn_tile_supported(L);
     auto dx = [&](int kind, int bq, int bk, int bv, int gbq, int gbk, int gbv) -> int {
         DxArgs d;
         d.dq = t.gS[0]; d.dk = t.gS[1]; d.dv = t.gS[2];
@@ -827,35 +653,20 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
     const unsigned grid = (unsigned)(n_tiles < n_sm ? n_tiles : n_sm);
     const unsigned agrid = (unsigned)(n_tiles < 2 * n_sm ? n_tiles : 2 * n_sm);     // bwd_attn: two CTAs per SM
     int rc;
-    if ((rc = set_smem(bwd_mlp_proj<false>, bytes)) || (rc = set_smem(bwd_mlp_proj<true>, bytes)) ||
-        (rc = set_smem(bwd_attn<0, false>, abytes)) || (rc = set_smem(bwd_attn<1, false>, abytes)) ||
-        (rc = set_smem(bwd_attn<0, true>, abytes)) || (rc = set_smem(bwd_attn<1, true>, abytes)) ||
-        (rc = set_smem(bwd_head<0, false>, bytes)) || (rc = set_smem(bwd_head<1, false>, bytes)) ||
-        (rc = set_smem(bwd_head<0, true>, bytes)) || (rc = set_smem(bwd_head<1, true>, bytes)) ||
+    if ((rc = set_smem(bwd_attn<0>, abytes)) || (rc = set_smem(bwd_attn<1>, abytes)) ||
+        (rc = set_smem(bwd_head<0>, bytes)) || (rc = set_smem(bwd_head<1>, bytes)) ||
         (rc = set_smem(bwd_embed_enc, bytes)) || (rc = set_smem(bwd_embed_dec, bytes)))
         return rc;
-// launch the instantiation with / without in-kernel weight-gradient accumulators
-#define BWD_LAUNCH(KERNEL, GRID, BYTES, ...)                                              \
-    do {                                                                                   \
-        if (tcw) KERNEL<true><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                        \
-        else KERNEL<false><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                           \
-    } while (0)
-#define BWD_LAUNCH2(KERNEL, K, GRID, BYTES, ...)                                          \
-    do {                                                                                   \
-        if (tcw) KERNEL<K, true><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                     \
-        else KERNEL<K, false><<<GRID, NT, BYTES, st>>>(__VA_ARGS__);                        \
-    } while (0)
     const float* pk = b.w;
     using namespace lay;
     auto idx = [](int blob) { return (blob - ENC_BLOBS) / BLOB; };
     CUDA_TRY(cudaMemsetAsync(t.gRep, 0, (size_t)n_tok * 64 * sizeof(float), st));
-    // Weight gradients: with the tensor-core path the fused kernels hand their layer-output gradients to
+    // Weight gradients: the fused kernels hand their layer-output gradients to
     // bwd_dw_tc.cu through the three scratch buffers t.gS (consumed by the launch that follows each kernel).
     auto job = [](const float* dY, const float* X, int recipe, int ln, int gW) {
         DwJob j; j.dY = dY; j.X = X; j.recipe = recipe; j.ln = ln; j.gW = gW; return j;
     };
     auto dw = [&](const DwJob* js, int n) -> int {
-        if (!tcw) return MATAS_OK;
         DwJobs J; J.n = n;
         for (int i = 0; i < n; ++i) J.j[i] = js[i];
         return launch_bwd_dw(pk, grad, J, n_tok, n_sm, st);
@@ -870,8 +681,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         h.gW0 = gm.w[idx(DEC_H0)]; h.gb0 = gm.b[idx(DEC_H0)]; h.glnw = gm.lnw[idx(DEC_H0)]; h.glnb = gm.lnb[idx(DEC_H0)];
         h.gW3 = gm.dec_h3_w; h.gb3 = gm.dec_h3_b; h.glogstd = gm.log_std;
         h.gOut = t.gX; h.L = L; h.n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
-        h.sY = tcw ? t.gS[0] : nullptr;
-        BWD_LAUNCH2(bwd_head, 1, grid, bytes, pk, grad, h, n_tok);
+        h.sY = t.gS[0];
+        bwd_head<1><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
         const DwJob js[1] = {job(t.gS[0], t.d_xh3[1], DW_X_AFFINE, dec_blob(1, DM2), h.gW0)};
         if ((rc = dw(js, 1))) return rc;
     }
@@ -887,9 +698,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(dec_blob(k, DM2))]; ta.glnFb = gm.lnb[idx(dec_blob(k, DM2))];
         ta.glnMw = gm.lnw[idx(dec_blob(k, DP2))]; ta.glnMb = gm.lnb[idx(dec_blob(k, DP2))];
         ta.gRes = t.gRep; ta.res_add = 1; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        if (tcw) { ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2]; }
-        if (mlptc) { if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc; }
-        else BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
+        ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2];
+        if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc;
         {
             const DwJob js[3] = {job(t.gS[0], t.d_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.d_xh2[k], DW_X_AFFINE, dec_blob(k, DP2), ta.gW0),
                                  job(t.gS[2], t.d_y2[k], DW_X_PLAIN, 0, ta.gWp)};
@@ -904,15 +714,15 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a2.gWk = gm.w[idx(dec_blob(k, DK2))]; a2.gbk = gm.b[idx(dec_blob(k, DK2))];
         a2.gWv = gm.w[idx(dec_blob(k, DV2))]; a2.gbv = gm.b[idx(dec_blob(k, DV2))];
         a2.gX = t.gX; a2.gRep = t.gRep; a2.causal = 1; a2.L = L;
-        if (tcw) { a2.sY[0] = t.gS[0]; a2.sY[1] = t.gS[1]; a2.sY[2] = t.gS[2]; }
+        a2.sY[0] = t.gS[0]; a2.sY[1] = t.gS[1]; a2.sY[2] = t.gS[2];
         if (tiled) {
             if ((rc = launch_attn_bwd_tile(a2.Q, a2.K, a2.V, a2.gY, a2.lse, a2.gD, t.gS[0], t.gS[1], t.gS[2], M, L, 1, st))) return rc;
             a2.pre = 1;
         }
-        if (dxtc) {
+        if (tiled) {
             if ((rc = dx(1, dec_q2(k), dec_blob(k, DK2), dec_blob(k, DV2), a2.gbq, a2.gbk, a2.gbv))) return rc;
         } else {
-            BWD_LAUNCH2(bwd_attn, 1, agrid, abytes, pk, grad, a2, n_tok);   // gX = grad wrt x1 (LN1 output)
+            bwd_attn<1><<<agrid, NT, abytes, st>>>(pk, grad, a2, n_tok);   // gX = grad wrt x1 (LN1 output)
         }
         {
             const DwJob js[3] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, a2.gWq), job(t.gS[1], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWk),
@@ -927,9 +737,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         tb.gWp = gm.w[idx(dec_blob(k, DP1))]; tb.gbp = gm.b[idx(dec_blob(k, DP1))];
         tb.glnMw = gm.lnw[idx(dec_blob(k, DP1))]; tb.glnMb = gm.lnb[idx(dec_blob(k, DP1))];
         tb.gRes = t.gX; tb.res_add = 0; tb.gY = t.gYb; tb.gD = t.gDb; tb.with_mlp = 0;
-        if (tcw) tb.sY[2] = t.gS[2];
-        if (mlptc) { if ((rc = launch_bwd_mlp_tc(pk, grad, tb, n_tok, n_sm, st))) return rc; }
-        else BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, tb, n_tok);       // gX = grad wrt block input (residual part)
+        tb.sY[2] = t.gS[2];
+        if ((rc = launch_bwd_mlp_tc(pk, grad, tb, n_tok, n_sm, st))) return rc;
         {
             const DwJob js[1] = {job(t.gS[2], t.d_y1[k], DW_X_PLAIN, 0, tb.gWp)};
             if ((rc = dw(js, 1))) return rc;
@@ -944,15 +753,15 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(dec_blob(k, DK1))]; a1.gbk = gm.b[idx(dec_blob(k, DK1))];
         a1.gWv = gm.w[idx(dec_blob(k, DV1))]; a1.gbv = gm.b[idx(dec_blob(k, DV1))];
         a1.gX = t.gX; a1.causal = 1; a1.L = L;
-        if (tcw) { a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2]; }
+        a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2];
         if (tiled) {
             if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
             a1.pre = 1;
         }
-        if (dxtc) {
+        if (tiled) {
             if ((rc = dx(0, dec_blob(k, DQ1), dec_blob(k, DK1), dec_blob(k, DV1), a1.gbq, a1.gbk, a1.gbv))) return rc;
         } else {
-            BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);   // gX += attention path
+            bwd_attn<0><<<agrid, NT, abytes, st>>>(pk, grad, a1, n_tok);   // gX += attention path
         }
         {
             const float* X = k == 1 ? t.d_xh3[0] : t.d_x0;
@@ -975,8 +784,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         h.gW0 = gm.w[idx(ENC_H0)]; h.gb0 = gm.b[idx(ENC_H0)]; h.glnw = gm.lnw[idx(ENC_H0)]; h.glnb = gm.lnb[idx(ENC_H0)];
         h.gW3 = gm.enc_h3_w; h.gb3 = gm.enc_h3_b; h.glogstd = -1;
         h.gOut = t.gRep; h.L = L;
-        h.sY = tcw ? t.gS[0] : nullptr;
-        BWD_LAUNCH2(bwd_head, 0, grid, bytes, pk, grad, h, n_tok);
+        h.sY = t.gS[0];
+        bwd_head<0><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
         const DwJob js[1] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, h.gW0)};
         if ((rc = dw(js, 1))) return rc;
     }
@@ -992,9 +801,8 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(enc_blob(k, EM2))]; ta.glnFb = gm.lnb[idx(enc_blob(k, EM2))];
         ta.glnMw = gm.lnw[idx(enc_blob(k, EP))]; ta.glnMb = gm.lnb[idx(enc_blob(k, EP))];
         ta.gRes = t.gX; ta.res_add = 0; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        if (tcw) { ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2]; }
-        if (mlptc) { if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc; }
-        else BWD_LAUNCH(bwd_mlp_proj, grid, bytes, pk, grad, ta, n_tok);
+        ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2];
+        if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc;
         {
             const DwJob js[3] = {job(t.gS[0], t.e_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.e_xh1[k], DW_X_AFFINE, enc_blob(k, EP), ta.gW0),
                                  job(t.gS[2], t.e_y[k], DW_X_PLAIN, 0, ta.gWp)};
@@ -1010,15 +818,15 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(enc_blob(k, EK))]; a1.gbk = gm.b[idx(enc_blob(k, EK))];
         a1.gWv = gm.w[idx(enc_blob(k, EV))]; a1.gbv = gm.b[idx(enc_blob(k, EV))];
         a1.gX = t.gX; a1.causal = 0; a1.L = L;
-        if (tcw) { a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2]; }
+        a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2];
         if (tiled) {
             if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
             a1.pre = 1;
         }
-        if (dxtc) {
+        if (tiled) {
             if ((rc = dx(0, enc_blob(k, EQ), enc_blob(k, EK), enc_blob(k, EV), a1.gbq, a1.gbk, a1.gbv))) return rc;
         } else {
-            BWD_LAUNCH2(bwd_attn, 0, agrid, abytes, pk, grad, a1, n_tok);
+            bwd_attn<0><<<agrid, NT, abytes, st>>>(pk, grad, a1, n_tok);
         }
         {
             const float* X = k == 1 ? t.e_xh2[0] : t.e_x0;

@@ -44,9 +44,7 @@ struct TrainBufs {
 struct DecodeArgs {
     long B;
     int L, mode, deterministic, stride, n_steps;
-    unsigned long long* phase_cycles;   // optional [16]: CTA 0 accumulates clock64 deltas per phase (measurement)
-    int prefetch;        // issue L2 prefetches of the cache rows ahead of each attention
-    int phased_below;    // positions below this use the phased attention (short contexts), the rest the fused one
+    int rows;            // envs per CTA tile (decode_tc_geometry); the cache scratch holds grid * rows env slots
     uint64_t seed;
     uint32_t step;
     long env_offset;
@@ -127,33 +125,29 @@ struct DecSched {
 };
 
 struct matas_policy;
-struct PolicyView { int n_agent, mode, device, n_sm, weights_set; const float* packed; };
+struct PolicyView { int n_agent, mode, device, n_sm, weights_set; const float* packed; const float* x1tab; };
 int matas_policy_view(const matas_policy* p, PolicyView* v);
 
-int policy_launch_geometry(int L, long rows, int* rpt, int* depth, size_t* bytes, int kind);
-int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots);
+int policy_check_agents(int L);
+// decode launch geometry for B envs on n_sm SMs: CTAs, env slots of cache scratch (grid * rows), envs per CTA tile
+int policy_decode_geometry(int L, long B, int n_sm, int* grid, long* slots, int* rows);
 int policy_decode_steps(int L, int mode, int deterministic, int stride);
-int policy_init_constants();
-int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, cudaStream_t st,
+int launch_encoder(const PolicyBufs& b, const float* obs, float* values, long B, int L, int obs_dim, int n_sm, cudaStream_t st,
                    const TrainBufs* tb = nullptr, int for_decode = 0);
 int launch_q2_from_rep(const PolicyBufs& b, const float* rep_in, long B, int L, cudaStream_t st, int for_decode);
-// tensor-core (tcgen05) token-parallel kernels, policy_tc.cu
-bool policy_use_tc();
-int decode_tc_geometry(long B, int n_sm, int* grid, long* slots);
-int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, int n_sm, cudaStream_t st);
+int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
+                          long B, int L, int mode, int n_sm, cudaStream_t st, const TrainBufs* tb = nullptr);
+// tensor-core (tcgen05) kernels: policy_tc.cu, attn_tc.cu, decode_tc.cu
+int decode_tc_geometry(long B, int n_sm, int* grid, long* slots, int* rows);
+int launch_decode_tc(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st);
 int launch_x1_table(const float* packed, float* x1tab, int L, cudaStream_t st);
 long decode_tc_spec_rows(int L, int stride);
 int launch_x1_spec_table(const float* packed, float* x1spec, int L, int stride, cudaStream_t st);
-bool attn_tile_supported(int L);
-bool attn_fwd_supported(int L);
-int launch_attn_tile(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
-                     cudaStream_t st);
+bool attn_tile_supported(int L);      // n_agent <= 64: the register-tiled attention backward (attn_bwd_tile.cu)
 int launch_attn_tc(const float* Q, const float* K, const float* V, float* Y, float* lse, long n_env, int L, int causal,
                    int n_sm, cudaStream_t st);
 int launch_teacher_forced_tc(const PolicyBufs& b, const TrainBufs& tb, const float* actions, const float* ava, float* logp,
-                             float* entropy, long n_tok, int L, int n_disc, cudaStream_t st);
+                             float* entropy, long n_tok, int L, int n_disc, int n_sm, cudaStream_t st);
 int launch_enc_embed_tc(const PolicyBufs& b, const TrainBufs& tb, const float* obs, long n_tok, int obs_dim, cudaStream_t st);
-int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st);
-int launch_teacher_forced(const PolicyBufs& b, const float* actions, const float* ava, float* logp, float* entropy,
-                          long B, int L, int mode, cudaStream_t st, const TrainBufs* tb = nullptr);
-int launch_decode(const PolicyBufs& b, const DecodeArgs& a, int grid, cudaStream_t st);
+int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, int n_sm,
+                         cudaStream_t st);

@@ -1,7 +1,7 @@
-// Tensor-core (tcgen05) versions of the token-parallel MAT-AS kernels for sm_100a: 128-token tiles, fp16
+// Tensor-core (tcgen05) token-parallel MAT-AS kernels for sm_100a: 128-token tiles, fp16
 // hi + scaled-lo operands in shared memory (tc.cuh), fp32 accumulators in tensor memory, thread-per-row
-// epilogues fusing bias / GELU / residual / LayerNorm, attention on the CUDA cores writing its output
-// straight into the next GEMM's operand.  Two CTAs per SM so that one CTA's attention / epilogue overlaps
+// epilogues fusing bias / GELU / residual / LayerNorm; the attention of each block is attn_tc.cu's kernel, whose
+// output rows are this file's first GEMM operand.  Two CTAs per SM so that one CTA's attention / epilogue overlaps
 // the other's MMAs.
 //
 // Reference semantics: EncodeBlock / Encoder of mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:70-154.
@@ -89,6 +89,16 @@ __device__ __forceinline__ void prefetch_tile_rows(const float* __restrict__ bas
     if (g < n_tok) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + g * 64 + (tid & 1) * 32));
 }
 
+// attention output rows computed by attn_tc.cu (token-major, global) -> operand, one half-warp per row
+__device__ __forceinline__ void rows_to_operand(unsigned char* sA, const float* __restrict__ y, long tile0, long n_tok) {
+    const int hw = threadIdx.x >> 4, l = threadIdx.x & 15;
+    for (int r = hw; r < tc::TR; r += NT / 16) {
+        const long g = tile0 + r;
+        const float4 c = g < n_tok ? __ldg(reinterpret_cast<const float4*>(y + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+        tc::store_operand4(sA, r, l, c);
+    }
+}
+
 template <int BLK>
 __global__ void __launch_bounds__(NT, 2)
 enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int for_decode, const float* __restrict__ y_in) {
@@ -101,9 +111,9 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     // into L2 while the prologue (TMEM allocation, barrier set-up, first weight blob) runs: the first loads of a tile
     // are otherwise what its warps wait on longest
     prefetch_tile_rows(b.X, tile0, n_tok, tid);
-    if (y_in) prefetch_tile_rows(y_in, tile0, n_tok, tid);
+    prefetch_tile_rows(y_in, tile0, n_tok, tid);
     prefetch_tile_rows(b.X, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
-    if (y_in) prefetch_tile_rows(y_in, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
+    prefetch_tile_rows(y_in, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
     Ring ring;
     if (BLK == 1 && for_decode) ring.init(s.ring, s.bars, b.w, c_tc_enc_blk1_dec, 8, 8, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
     else ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_tc_enc_blk0 : c_tc_enc_blk1, 6, 6, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
@@ -117,18 +127,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     Stage st = {c, ring};
 
     tc::global_to_tile(s.sT, b.X + tile0 * 64, n_valid);         // residual stream
-    if (y_in) {
-        // attention output computed by attn_tile.cu: token-major rows -> operand (one half-warp per row, coalesced)
-        const int hw = tid >> 4, l = tid & 15;
-        for (int r = hw; r < tc::TR; r += NT / 16) {
-            const long g = tile0 + r;
-            const float4 c = g < n_tok ? __ldg(reinterpret_cast<const float4*>(y_in + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
-            tc::store_operand4(s.sA, r, l, c);
-        }
-    } else {
-        tc::attention_to_operand<false>(s.sA, (tb.on ? tb.e_q[BLK] : b.Q), b.K[BLK], b.V[BLK], tile0, n_tok, L,
-                                        tb.on ? tb.e_y[BLK] : nullptr, tb.on ? tb.e_lse[BLK] : nullptr);
-    }
+    rows_to_operand(s.sA, y_in, tile0, n_tok);                   // attention output of attn_tc.cu -> first operand
     float v[32], res[32];
     // ---- proj + residual + LN1 ------------------------------------------------------------------
     {
@@ -231,16 +230,6 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
         }
     }
     tc::ctx_fini(c);
-}
-
-// attention output rows computed by attn_tile.cu (token-major, global) -> operand, one half-warp per row
-__device__ __forceinline__ void rows_to_operand(unsigned char* sA, const float* __restrict__ y, long tile0, long n_tok) {
-    const int hw = threadIdx.x >> 4, l = threadIdx.x & 15;
-    for (int r = hw; r < tc::TR; r += NT / 16) {
-        const long g = tile0 + r;
-        const float4 c = g < n_tok ? __ldg(reinterpret_cast<const float4*>(y + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
-        tc::store_operand4(sA, r, l, c);
-    }
 }
 
 // Tail shared by the kernels that end with three projections of the tile in the operand (x in sT):
@@ -383,9 +372,7 @@ dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float
     float* sRed = s.sSmall;
     float* sTrow = s.sT + row * XS + half * 32;
     tc::global_to_tile(s.sT, b.X + tile0 * 64, n_valid);
-    if (y_in) rows_to_operand(s.sA, y_in, tile0, n_tok);
-    else tc::attention_to_operand<true>(s.sA, (tb.on ? tb.d_q1[blk] : b.Q), b.K1[blk], b.V1[blk], tile0, n_tok, L,
-                                        tb.on ? tb.d_y1[blk] : nullptr, tb.on ? tb.d_lse1[blk] : nullptr);
+    rows_to_operand(s.sA, y_in, tile0, n_tok);
     float v[32], res[32];
     Stage st = {c, ring};
     {
@@ -438,9 +425,7 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
     float* sRed = s.sSmall;
     float* sTrow = s.sT + row * XS + half * 32;
     tc::global_to_tile(s.sT, b.rep + tile0 * 64, n_valid);
-    if (y_in) rows_to_operand(s.sA, y_in, tile0, n_tok);
-    else tc::attention_to_operand<true>(s.sA, b.Q2[blk], b.K2[blk], b.V2[blk], tile0, n_tok, L, tb.on ? tb.d_y2[blk] : nullptr,
-                                        tb.on ? tb.d_lse2[blk] : nullptr);
+    rows_to_operand(s.sA, y_in, tile0, n_tok);
     float v[32], res[32];
     Stage st = {c, ring};
     {   // proj + obs_rep + LN2
@@ -532,8 +517,6 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
 
 }  // namespace
 
-static bool use_attn_tile(int L);
-
 int launch_enc_embed_tc(const PolicyBufs& b, const TrainBufs& tb, const float* obs, long n_tok, int obs_dim, cudaStream_t st) {
     const size_t bytes = tc::smem_bytes(TC_DEPTH);
     CUDA_TRY(cudaFuncSetAttribute(enc_embed_qkv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
@@ -542,59 +525,41 @@ int launch_enc_embed_tc(const PolicyBufs& b, const TrainBufs& tb, const float* o
     return MATAS_OK;
 }
 
-int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, cudaStream_t st) {
+int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values, long n_tok, int L, int for_decode, int n_sm,
+                         cudaStream_t st) {
     const size_t bytes = tc::smem_bytes(TC_DEPTH);
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
-    const bool use_tile = use_attn_tile(L);
     for (int blk = 0; blk < 2; ++blk) {
-        const float* y_in = nullptr;
-        if (use_tile) {
-            float* y = tb.on ? tb.e_y[blk] : b.Y;
-            int rc = launch_attn_tile(tb.on ? tb.e_q[blk] : b.Q, b.K[blk], b.V[blk], y, tb.on ? tb.e_lse[blk] : nullptr, n_tok / L, L, 0, st);
-            if (rc) return rc;
-            y_in = y;
-        }
-        if (blk == 0) enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0, y_in);
-        else enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode, y_in);
+        float* y = tb.on ? tb.e_y[blk] : b.Y;
+        int rc = launch_attn_tc(tb.on ? tb.e_q[blk] : b.Q, b.K[blk], b.V[blk], y, tb.on ? tb.e_lse[blk] : nullptr, n_tok / L, L, 0, n_sm, st);
+        if (rc) return rc;
+        if (blk == 0) enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0, y);
+        else enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode, y);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
 
-static bool use_attn_tile(int L) {
-    static int tiled = -1;           // MATAS_ATTN_TILE=0 keeps the attention fused into the block kernels (A/B measurements)
-    if (tiled < 0) { const char* e = getenv("MATAS_ATTN_TILE"); tiled = e ? atoi(e) : 1; }
-    return tiled && attn_fwd_supported(L);
-}
-
 int launch_teacher_forced_tc(const PolicyBufs& b, const TrainBufs& tb, const float* actions, const float* ava, float* logp,
-                             float* entropy, long n_tok, int L, int n_disc, cudaStream_t st) {
+                             float* entropy, long n_tok, int L, int n_disc, int n_sm, cudaStream_t st) {
     const size_t bytes = tc::smem_bytes(TC_DEPTH);
     CUDA_TRY(cudaFuncSetAttribute(dec_embed_qkv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     CUDA_TRY(cudaFuncSetAttribute(dec_attn1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     CUDA_TRY(cudaFuncSetAttribute(dec_attn2_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
-    const bool tile = use_attn_tile(L);
     const long n_env = n_tok / L;
     int rc;
     dec_embed_qkv_tc<<<grid, NT, bytes, st>>>(b, tb, actions, n_tok, L);
     for (int blk = 0; blk < 2; ++blk) {
-        const float* y_in = nullptr;
-        if (tile) {
-            float* y = tb.on ? tb.d_y1[blk] : b.Y;
-            if ((rc = launch_attn_tile(tb.on ? tb.d_q1[blk] : b.Q, b.K1[blk], b.V1[blk], y, tb.on ? tb.d_lse1[blk] : nullptr, n_env, L, 1, st)))
-                return rc;
-            y_in = y;
-        }
-        dec_attn1_tc<<<grid, NT, bytes, st>>>(b, tb, blk, n_tok, L, y_in);
-        if (tile) {
-            float* y = tb.on ? tb.d_y2[blk] : b.Y;
-            if ((rc = launch_attn_tile(b.Q2[blk], b.K2[blk], b.V2[blk], y, tb.on ? tb.d_lse2[blk] : nullptr, n_env, L, 1, st))) return rc;
-            y_in = y;
-        }
-        dec_attn2_tc<<<grid, NT, bytes, st>>>(b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, y_in);
+        float* y = tb.on ? tb.d_y1[blk] : b.Y;
+        if ((rc = launch_attn_tc(tb.on ? tb.d_q1[blk] : b.Q, b.K1[blk], b.V1[blk], y, tb.on ? tb.d_lse1[blk] : nullptr, n_env, L, 1, n_sm, st)))
+            return rc;
+        dec_attn1_tc<<<grid, NT, bytes, st>>>(b, tb, blk, n_tok, L, y);
+        y = tb.on ? tb.d_y2[blk] : b.Y;
+        if ((rc = launch_attn_tc(b.Q2[blk], b.K2[blk], b.V2[blk], y, tb.on ? tb.d_lse2[blk] : nullptr, n_env, L, 1, n_sm, st))) return rc;
+        dec_attn2_tc<<<grid, NT, bytes, st>>>(b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, y);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;

@@ -289,72 +289,4 @@ __device__ __forceinline__ float layernorm_pair(float (&v)[32], float* __restric
     return rs;
 }
 
-// Bidirectional / causal attention for a 128-token tile, one half-warp per query row (the layout of
-// tile::attention_rows), queries read from global memory, output written straight into the tensor-core
-// operand (and, in training mode, to y_out / lse_out).  Rows past n_tok produce zero operand rows.
-template <bool CAUSAL>
-__device__ __forceinline__ void attention_to_operand(unsigned char* sA, const float* __restrict__ Q, const float* __restrict__ K,
-                                                     const float* __restrict__ V, long tile0, long n_tok, int L,
-                                                     float* __restrict__ y_out, float* __restrict__ lse_out) {
-    const float scale = 0.17677669529663687f * 1.4426950408889634f;
-    const int tid = threadIdx.x, hw = tid >> 4, l = tid & 15;
-    const unsigned hmask = 0xffffu << (tid & 16);
-    for (int r = hw; r < TR; r += NT / 16) {
-        const long g = tile0 + r;
-        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (g < n_tok) {
-            const long env = g / L;
-            const int pos = (int)(g - env * L);
-            const int nr = CAUSAL ? pos + 1 : L;
-            float4 q = __ldg(reinterpret_cast<const float4*>(Q + g * 64) + l);
-            q.x *= scale; q.y *= scale; q.z *= scale; q.w *= scale;
-            const float4* kp = reinterpret_cast<const float4*>(K + env * L * 64) + l;
-            const float4* vp = reinterpret_cast<const float4*>(V + env * L * 64) + l;
-            float m = -INFINITY, sum = 0.f;
-            auto batch = [&](const float4 (&k)[4], const float4 (&v)[4], int t0) {
-                float s[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    float p = q.x * k[i].x + q.y * k[i].y + q.z * k[i].z + q.w * k[i].w;
-                    p += __shfl_xor_sync(hmask, p, 4);
-                    p += __shfl_xor_sync(hmask, p, 2);
-                    p += __shfl_xor_sync(hmask, p, 1);
-                    s[i] = t0 + i < nr ? p : -INFINITY;
-                }
-                const float n = fmaxf(m, fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])));
-                const float a = exp2f(m - n);
-                sum *= a; c.x *= a; c.y *= a; c.z *= a; c.w *= a;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float p = exp2f(s[i] - n);
-                    sum += p;
-                    c.x = fmaf(p, v[i].x, c.x); c.y = fmaf(p, v[i].y, c.y); c.z = fmaf(p, v[i].z, c.z); c.w = fmaf(p, v[i].w, c.w);
-                }
-                m = n;
-            };
-            auto fetch = [&](float4 (&k)[4], float4 (&v)[4], int t0) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const bool ok = t0 + i < nr;
-                    k[i] = ok ? __ldg(kp + (long)(t0 + i) * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    v[i] = ok ? __ldg(vp + (long)(t0 + i) * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-            };
-            float4 ka[4], va[4], kb[4], vb[4];
-            fetch(ka, va, 0);
-            for (int t0 = 0; t0 < nr; t0 += 8) {
-                fetch(kb, vb, t0 + 4);
-                batch(ka, va, t0);
-                fetch(ka, va, t0 + 8);
-                if (t0 + 4 < nr) batch(kb, vb, t0 + 4);
-            }
-            const float inv = 1.0f / sum;
-            c.x *= inv; c.y *= inv; c.z *= inv; c.w *= inv;
-            if (y_out) *reinterpret_cast<float4*>(y_out + g * 64 + l * 4) = c;
-            if (lse_out && (l & 7) == 0) lse_out[g * 2 + (l >> 3)] = m * 0.6931471805599453f + logf(sum);
-        }
-        store_operand4(sA, r, l, c);
-    }
-}
-
 }  // namespace tc

@@ -23,6 +23,10 @@ class FlatAdam(torch.optim.Optimizer):
         self.exp_avg_sq = torch.zeros_like(flat)
         self.norm = torch.zeros(2, dtype=torch.float32, device=flat.device)     # {gradient norm, clip coefficient}
         self.step_count = 0
+        # encoder.state_encoder.* and decoder.obs_encoder.* never receive a gradient (encode_state / dec_actor are off):
+        # torch.optim.Adam skips parameters whose .grad is None, so weight decay must not touch them either
+        self._frozen = [p for n, p in model.named_parameters()
+                        if n.startswith("encoder.state_encoder.") or n.startswith("decoder.obs_encoder.")]
 
     def zero_grad(self, set_to_none=False):
         self._model.flat_grad(zero=True)
@@ -33,12 +37,16 @@ class FlatAdam(torch.optim.Optimizer):
         m = self._model
         g = self.param_groups[0]
         self.step_count += 1
+        keep = [p.detach().clone() for p in self._frozen] if g["weight_decay"] != 0 else None
         with torch.cuda.device(m.device):
             _cabi.check(_cabi.lib().matas_adam_clip_step(
                 _cabi.ptr(m.flat_parameters()), _cabi.ptr(m.flat_grad()), _cabi.ptr(self.exp_avg), _cabi.ptr(self.exp_avg_sq),
                 m.flat_parameters().numel(), float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
                 float(g["weight_decay"]), float(max_grad_norm or 0.0), self.step_count, _cabi.ptr(self.norm),
                 _cabi.stream_ptr()))
+        if keep is not None:
+            for p, k in zip(self._frozen, keep):
+                p.data.copy_(k)
         m.invalidate_weights()              # the kernel wrote the parameters behind torch's version counters
         return self.norm[0].clone()
 

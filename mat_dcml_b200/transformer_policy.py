@@ -60,12 +60,13 @@ class TransformerPolicy:
                                                  semi_index=-1 if semi_index is None else semi_index)
         if getattr(args, "env_name", None) == "hands":
             self.transformer.zero_std()
-        if self.device.type == "cuda" and os.environ.get("MATAS_FUSED_ADAM", "1") != "0":
+        if self.device.type == "cuda":
             # same update as the reference's torch.optim.Adam (transformer_policy.py:103-105), fused with the
             # gradient clipping over the flat parameter buffer (flat_adam.py, csrc/adam.cu)
             from .flat_adam import FlatAdam
             self.optimizer = FlatAdam(self.transformer, lr=self.lr, eps=self.opti_eps, weight_decay=self.weight_decay)
         else:
+            # a CPU-resident policy only holds parameters (checkpoint conversion): nothing here can produce gradients
             self.optimizer = torch.optim.Adam(self.transformer.parameters(), lr=self.lr, eps=self.opti_eps,
                                               weight_decay=self.weight_decay)
 
