@@ -133,6 +133,19 @@ int matas_policy_act_autoregressive_static(matas_policy* p, const float* obs_rep
  * waits for them and returns the summed device time and the launch count since enabling. */
 int matas_policy_timing(matas_policy* p, int enable);
 int matas_policy_decode_time(matas_policy* p, double* ms_total, long* launches);
+/* Minibatch gather: replaces the per-array fancy indexing of SharedReplayBuffer.feed_forward_generator_transformer
+ * (mat_src/mat/utils/shared_buffer.py:265-314).  For each of n_arrays (<= 12) device arrays: dst[a][i] = src[a][idx[i]]
+ * for i < n_rows, a row being width[a] floats, written repeat[a] times back to back (share_obs: one (W+2) row per
+ * (t, env) sample replicated n_agent times, shared_buffer.py:265-266).  src / dst / width / repeat are HOST arrays of
+ * device pointers / ints; idx is a device int64 vector (the slice of torch.randperm, shared_buffer.py:260-261). */
+int matas_gather_rows(int n_arrays, const float* const* src, float* const* dst, const int* width, const int* repeat,
+                      const long* idx, long n_rows, void* stream);
+
+/* Philox4x32-10 exactly as the kernels draw it (csrc/common.cuh; no counterpart in the reference, whose Python `random` /
+ * `numpy.random` streams cannot be replayed in parallel -- see DESIGN.md "Random streams"): n device rows of
+ * {counter[4], key[2]} -> n rows of 4 output words.  Test hook for the Random123 known-answer vectors. */
+int matas_philox4x32_10(const uint32_t* counter_key, uint32_t* out, long n, void* stream);
+
 /* Measured fp32 FFMA throughput of the current device in TFLOP/s (no counterpart in the reference;
  * the roofline denominator of the SIMT kernels, which MEASURED_PEAKS.json does not hold). */
 int matas_fp32_peak(int iters, double* tflops);

@@ -431,6 +431,22 @@ extern "C" int matas_policy_decode_time(matas_policy* p, double* ms_total, long*
     return MATAS_OK;
 }
 
+// the device copy of the named-draw generator (common.cuh), exposed so that tests can pin it to the Random123 known answers
+__global__ void philox_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, long n) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t* c = in + i * 6;
+    const uint4 x = philox4x32(c[0], c[1], c[2], c[3], (uint64_t)c[4] | ((uint64_t)c[5] << 32));
+    out[i * 4] = x.x; out[i * 4 + 1] = x.y; out[i * 4 + 2] = x.z; out[i * 4 + 3] = x.w;
+}
+
+extern "C" int matas_philox4x32_10(const uint32_t* counter_key, uint32_t* out, long n, void* stream) {
+    ARG_CHECK(counter_key && out && n > 0, "bad argument (n=%ld)", n);
+    philox_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(counter_key, out, n);
+    CUDA_TRY(cudaGetLastError());
+    return MATAS_OK;
+}
+
 // dependent-FFMA probe: 8 independent chains per thread, 2 FLOP per FFMA
 __global__ void fp32_peak_kernel(float* out, int iters) {
     float a[8];

@@ -11,6 +11,8 @@ Differences, all layout-only: arrays are fp32 torch tensors on the GPU instead o
 (the model ignores it, ma_transformer.py:144-149); the dead ``rnn_states*`` arrays are
 (T+1, N, L, 1, 1) zeros.  ``compute_returns`` is the GAE kernel (csrc/gae.cu).
 """
+import ctypes
+
 import numpy as np
 import torch
 
@@ -48,8 +50,8 @@ class SharedReplayBuffer:
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _cabi.MatasError("SharedReplayBuffer needs a CUDA device (there is no CPU fallback)")
-        if not self._use_gae:
-            raise NotImplementedError("only the GAE branch of compute_returns is built (config.py:260 default)")
+        # use_gae is stored like the reference does and, like there, never read: compute_returns only has GAE branches
+        # (shared_buffer.py:207-238)
         self._copy_stream = torch.cuda.Stream(device=self.device)
         self._dirty = False
         self._inflight = []            # (event, source tensors) of uploads that may still be reading pinned memory
@@ -168,15 +170,26 @@ class SharedReplayBuffer:
             assert batch_size >= num_mini_batch, "PPO requires N*T >= num_mini_batch"
             mini_batch_size = batch_size // num_mini_batch
         rand = torch.randperm(batch_size, device=self.device)
-        flat = lambda x: x.reshape(batch_size, *x.shape[2:])
-        share = flat(self._share_obs[:-1])
-        obs, act, ava = flat(self.obs[:-1]), flat(self.actions), flat(self.available_actions[:-1])
-        vp, ret, msk = flat(self.value_preds[:-1]), flat(self.returns[:-1]), flat(self.masks[:-1])
-        am, lp = flat(self.active_masks[:-1]), flat(self.action_log_probs)
-        adv = None if advantages is None else flat(torch.as_tensor(advantages).to(self.device))
+        flat = lambda x: x.reshape(batch_size, -1)
+        adv = None if advantages is None else torch.as_tensor(advantages).to(device=self.device, dtype=torch.float32).contiguous()
+        # (source viewed as [batch][row], floats per row, copies per row): share_obs is kept as one row per sample and
+        # replicated over the agents on the way out, everything else carries its L agents in the row
+        srcs = [(flat(self._share_obs[:-1]), L), (flat(self.obs[:-1]), 1), (flat(self.actions), 1), (flat(self.value_preds[:-1]), 1),
+                (flat(self.returns[:-1]), 1), (flat(self.masks[:-1]), 1), (flat(self.active_masks[:-1]), 1),
+                (flat(self.action_log_probs), 1), (flat(self.available_actions[:-1]), 1)]
+        if adv is not None:
+            srcs.append((flat(adv), 1))
+        n = len(srcs)
+        c_src = (ctypes.c_void_p * n)(*[s.data_ptr() for s, _ in srcs])
+        c_w = (ctypes.c_int * n)(*[s.shape[1] for s, _ in srcs])
+        c_rep = (ctypes.c_int * n)(*[r for _, r in srcs])
         for i in range(num_mini_batch):
-            idx = rand[i * mini_batch_size:(i + 1) * mini_batch_size]
-            g = lambda x: x[idx].reshape(-1, *x.shape[2:])
-            so = share[idx].unsqueeze(1).expand(-1, L, -1).reshape(-1, share.shape[-1])
-            yield (so, g(obs), None, None, g(act), g(vp), g(ret), g(msk), g(am), g(lp),
-                   None if adv is None else g(adv), g(ava))
+            idx = rand[i * mini_batch_size:(i + 1) * mini_batch_size].contiguous()
+            M = idx.numel()
+            # (M * L, dim) outputs, as the reference's `x[indices].reshape(-1, *x.shape[2:])`
+            outs = [torch.empty(M * L, s.shape[1] * r // L, dtype=torch.float32, device=self.device) for s, r in srcs]
+            c_dst = (ctypes.c_void_p * n)(*[o.data_ptr() for o in outs])
+            with torch.cuda.device(self.device):
+                _cabi.check(_cabi.lib().matas_gather_rows(n, c_src, c_dst, c_w, c_rep, _cabi.ptr(idx), M, _cabi.stream_ptr()))
+            so, ob, act, vp, ret, msk, am, lp, ava = outs[:9]
+            yield (so, ob, None, None, act, vp, ret, msk, am, lp, outs[9] if adv is not None else None, ava)

@@ -437,6 +437,55 @@ def gen_ppo(out, L, M, wseed):
     print("wrote", out)
 
 
+def gen_buffer(out):
+    """SharedReplayBuffer.insert / after_update / feed_forward_generator_transformer of the reference on random content
+    with an injected permutation (``torch.randperm`` replaced for the call): the 12-tuples of three minibatches."""
+    _ref_paths()
+    import torch
+    from mat.utils.shared_buffer import SharedReplayBuffer
+    from DCML_ENVs.DCML_utils.DCML_ActionSpace import Action_Space
+    import mat.utils.shared_buffer as SB
+
+    T, N, L, W = 6, 4, 5, 4
+    rng = np.random.RandomState(23)
+    args = _args(episode_length=T, n_rollout_threads=N, use_valuenorm=False, use_popart=False)
+    buf = SharedReplayBuffer(args, L, [7], [W + 2], Action_Space(2, semi_index=-1, extra=True), "DCML")
+    f32 = lambda *sh: rng.standard_normal(sh).astype(np.float32)
+    res = {"T": T, "N": N, "L": L, "W": W}
+    first = {"share_obs": f32(N, L, W + 2), "obs": f32(N, L, 7), "ava": (rng.uniform(size=(N, L, 2)) > 0.3).astype(np.float32)}
+    first["share_obs"][:] = first["share_obs"][:, :1]                 # the env replicates one row over the agents
+    buf.share_obs[0], buf.obs[0], buf.available_actions[0] = first["share_obs"], first["obs"], first["ava"]
+    res.update({"first_" + k: v for k, v in first.items()})
+    for t in range(T):
+        so = f32(N, 1, W + 2).repeat(L, axis=1)
+        step = dict(share_obs=so, obs=f32(N, L, 7), actions=f32(N, L, 1), logp=f32(N, L, 1), values=f32(N, L, 1),
+                    rewards=f32(N, 1, 1).repeat(L, axis=1), masks=(rng.uniform(size=(N, 1, 1)) > 0.3).astype(np.float32).repeat(L, axis=1),
+                    ava=(rng.uniform(size=(N, L, 2)) > 0.3).astype(np.float32))
+        buf.insert(step["share_obs"], step["obs"], np.zeros((N, L, 1, 64), np.float32), np.zeros((N, L, 1, 64), np.float32),
+                   step["actions"], step["logp"], step["values"], step["rewards"], step["masks"], None, None, step["ava"])
+        res.update({"s%d_%s" % (t, k): v for k, v in step.items()})
+    buf.compute_returns(f32(N, L, 1), None)
+    res["next_value"] = buf.value_preds[-1].copy()
+    adv = f32(T, N, L, 1)
+    perm = rng.permutation(T * N)
+    res["adv"], res["perm"] = adv, perm.astype(np.int64)
+    real = torch.randperm
+    torch.randperm = lambda n, **k: torch.from_numpy(perm.copy())
+    try:
+        names = ("share_obs", "obs", "rnn", "rnn_c", "actions", "value_preds", "returns", "masks", "active", "old_logp", "adv", "ava")
+        for i, sample in enumerate(buf.feed_forward_generator_transformer(adv, num_mini_batch=3)):
+            for k, v in zip(names, sample):
+                if not k.startswith("rnn"):
+                    res["mb%d_%s" % (i, k)] = np.asarray(v)
+    finally:
+        torch.randperm = real
+    buf.after_update()
+    res["after_obs0"], res["after_share0"], res["after_masks0"], res["after_ava0"] = (
+        buf.obs[0].copy(), buf.share_obs[0, :, 0].copy(), buf.masks[0].copy(), buf.available_actions[0].copy())
+    np.savez_compressed(out, **res)
+    print("wrote", out)
+
+
 # ------------------------------------------------------------------------------------------
 # preset benchmark samples (Env(preset=True) reader + modify_preset)
 # ------------------------------------------------------------------------------------------
@@ -466,9 +515,14 @@ FAMILIES = {
     "policy_L13_discrete": lambda o: gen_policy(o, 13, 4, "trained", 6, semi=False),
     "env_W100": lambda o: gen_env(o, 100, 3, 6, 1, True),
     "env_W20": lambda o: gen_env(o, 20, 6, 8, 2, False),
+    # wider families (32 envs x 16 steps): several hundred reference env-steps through every floor / ceil / % branch of
+    # Worker.process at the default worker count (real workloads.txt) and at the C3 bench shape (50 workers)
+    "env_W100_wide": lambda o: gen_env(o, 100, 32, 16, 11, True),
+    "env_W50_wide": lambda o: gen_env(o, 50, 32, 16, 12, False),
     "env_W12_shannon": lambda o: gen_env(o, 12, 8, 1, 4, False, shannon=True),
     "env_W16_variants": lambda o: gen_env(o, 16, 6, 5, 7, False, variants=True),
     "gae": gen_gae,
+    "buffer": gen_buffer,
     "ppo_L11": lambda o: gen_ppo(o, 11, 6, 8),
     "preset_sample1": gen_preset,
 }

@@ -16,7 +16,7 @@ def _close(got, want, name=""):
     np.testing.assert_allclose(np.asarray(got, np.float64), np.asarray(want, np.float64), rtol=RTOL, atol=1e-6, err_msg=name)
 
 
-@pytest.mark.parametrize("case", ["env_W20", "env_W100"])
+@pytest.mark.parametrize("case", ["env_W20", "env_W100", "env_W50_wide", "env_W100_wide"])
 def test_env_vs_reference(case, cuda_device):
     from mat_dcml_b200 import DcmlVecEnv
     g = golden(case)
@@ -109,17 +109,34 @@ def test_env_preset_context(cuda_device):
 
 
 def test_env_full_size_properties(cuda_device):
-    """C3 shape (16384 x 50): invariants of the simulator that hold at any size."""
+    """C3 shape (16384 x 50): invariants of the simulator that hold at any size, and the oracle itself on three runs of
+    envs taken from the start, the middle and the end of the batch (envs are independent: named draws by env index)."""
     from mat_dcml_b200 import DcmlVecEnv
     W, B = 50, 16384
     env = DcmlVecEnv(B, W, seed=5)
+    starts = (0, B // 2 - 11, B - 21)
+    oras = [eo.DcmlEnvOracle(21, W, env.base_workload, seed=5, env0=s0) for s0 in starts]
     obs, sob, ava = env.reset_device()
+    for s0, ora in zip(starts, oras):
+        o2, s2, a2 = ora.reset()
+        _close(obs[s0:s0 + 21].cpu().numpy(), o2, "obs0"); _close(env.sob[s0:s0 + 21].cpu().numpy(), s2[:, 0], "sob0")
+        np.testing.assert_array_equal(ava[s0:s0 + 21].cpu().numpy(), a2)
     dones = []
     for t in range(3):
         sel = ava[:, :W, 1] * (torch.rand(B, W, device="cuda") < 0.6)
         act = torch.cat([sel, torch.full((B, 1), 0.7, device="cuda")], 1)
+        if t == 1:
+            act[0, :W] = 0                                  # the N == 0 branch in the first tile
         obs, sob, rew, done, delay, pay, ava = env.step_device(act)
-        n_sel = sel.sum(1)
+        for s0, ora in zip(starts, oras):
+            o2, s2, r2, d2, i2, a2 = ora.step(act[s0:s0 + 21].cpu().numpy()[:, :, None])
+            _close(rew[s0:s0 + 21].cpu().numpy(), r2[:, 0, 0], "reward")
+            _close(delay[s0:s0 + 21].cpu().numpy(), [i[0]["delay"] for i in i2], "delay")
+            _close(pay[s0:s0 + 21].cpu().numpy(), [i[0]["payment"] for i in i2], "payment")
+            np.testing.assert_array_equal(done[s0:s0 + 21].cpu().numpy().astype(bool), d2[:, 0])
+            _close(obs[s0:s0 + 21].cpu().numpy(), o2, "obs"); _close(env.sob[s0:s0 + 21].cpu().numpy(), s2[:, 0], "sob")
+            np.testing.assert_array_equal(ava[s0:s0 + 21].cpu().numpy(), a2)
+        n_sel = act[:, :W].sum(1)
         scale = torch.where(n_sel == 0, 1.5, 1.0)
         assert torch.allclose(rew, scale * (-99 * delay - pay), rtol=1e-5, atol=1e-4)
         assert bool((delay > 0).all()) and bool((pay >= 0).all()) and torch.isfinite(rew).all()
@@ -229,3 +246,23 @@ def test_env_variants_vs_reference_and_oracle(tag, kw, cuda_device):
                               rng.uniform(0.1, 1.0, size=(B, 1)).astype(np.float32)], 1)[:, :, None]
         o1, s1, r1, d1, i1, a1 = env.step(act); o2, s2, r2, d2, i2, a2 = ora.step(act)
         _close(r1, r2); _close(o1, o2); _close(s1, s2); np.testing.assert_array_equal(d1, d2)
+
+
+def test_philox_device_known_answers(cuda_device):
+    """csrc/common.cuh draws the same Philox4x32-10 words as Random123's known-answer vectors and as oracle/philox.py."""
+    from mat_dcml_b200 import _cabi
+    from oracle import philox as px
+    from test_oracle_golden import PHILOX_KAT
+    rows = [list(c) + list(k) for c, k, _ in PHILOX_KAT]
+    rng = np.random.RandomState(0)
+    extra = rng.randint(0, 2 ** 32, size=(1000, 6), dtype=np.uint64)
+    inp32 = torch.from_numpy(np.concatenate([np.array(rows, np.uint64), extra]).astype(np.uint32).view(np.int32)).cuda()
+    out = torch.empty(inp32.shape[0], 4, dtype=torch.int32, device="cuda")
+    _cabi.check(_cabi.lib().matas_philox4x32_10(_cabi.ptr(inp32), _cabi.ptr(out), inp32.shape[0], _cabi.stream_ptr()))
+    got = out.cpu().numpy().view(np.uint32)
+    for i, (_, _, want) in enumerate(PHILOX_KAT):
+        assert tuple(int(x) for x in got[i]) == want
+    e = extra.astype(np.uint64)
+    for i in range(0, 1000, 37):
+        w = px.philox4x32(int(e[i, 0]), int(e[i, 1]), int(e[i, 2]), int(e[i, 3]), seed=int(e[i, 4]) | (int(e[i, 5]) << 32))
+        assert [int(x) for x in got[3 + i]] == [int(x) for x in w]

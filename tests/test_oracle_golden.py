@@ -8,6 +8,7 @@ from conftest import golden
 from oracle import env_oracle as eo
 from oracle import mat_oracle as mo
 from oracle import ppo_oracle as po
+from oracle import philox as px
 
 POLICY_CASES = ["policy_L21_trained", "policy_L21_init", "policy_L101_trained"]
 
@@ -82,7 +83,7 @@ def test_policy_stochastic_injection_is_self_consistent():
     assert 0.05 < a[:, :-1][ava[:, :-1, 1] == 1].mean() < 0.95
 
 
-@pytest.mark.parametrize("case", ["env_W20", "env_W100"])
+@pytest.mark.parametrize("case", ["env_W20", "env_W100", "env_W50_wide", "env_W100_wide"])
 def test_env_matches_reference(case):
     g = golden(case)
     W, B, steps = int(g["W"]), int(g["B"]), int(g["steps"])
@@ -184,3 +185,26 @@ def test_env_variants_match_reference(tag, kw):
         np.testing.assert_allclose(obs, g[tag + "_obs"][:, t], rtol=1e-12, atol=1e-14)
         np.testing.assert_allclose(sob[:, 0], g[tag + "_sob"][:, t], rtol=1e-12, atol=1e-14)
         np.testing.assert_array_equal(ava, g[tag + "_ava"][:, t])
+
+# Random123 (Salmon et al., SC'11) known-answer vectors of Philox4x32-10: (counter[4], key[2]) -> output[4]
+PHILOX_KAT = (
+    ((0x00000000, 0x00000000, 0x00000000, 0x00000000), (0x00000000, 0x00000000),
+     (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+    ((0xffffffff, 0xffffffff, 0xffffffff, 0xffffffff), (0xffffffff, 0xffffffff),
+     (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+    ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+     (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1)),
+)
+
+
+def test_philox_known_answers():
+    """oracle/philox.py is the Philox4x32-10 of Random123 (the named draws of DESIGN.md section 4 rest on it)."""
+    for ctr, key, want in PHILOX_KAT:
+        got = px.philox4x32(*ctr, seed=key[0] | (key[1] << 32))
+        assert tuple(int(x) for x in got) == want
+    # vectorised over counters: same words as the scalar calls
+    c0 = np.arange(5, dtype=np.uint32)
+    got = px.philox4x32(c0, 7, 9, 11, seed=0x0123456789ABCDEF)
+    for i in range(5):
+        one = px.philox4x32(int(c0[i]), 7, 9, 11, seed=0x0123456789ABCDEF)
+        assert [int(g[i]) for g in got] == [int(x) for x in one]

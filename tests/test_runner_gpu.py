@@ -192,3 +192,45 @@ def test_preset_benchmark_loop(cuda_device):
     cts, pays, rews = sweep(pol, env, samples, [{"disable_rate": 8}, {"disable_rate": 64}], n_episodes=16)
     assert cts.shape == (2, 1) and pays.shape == (2, 1) and np.isfinite(rews).all()
     assert (samples.disable_rates == g["disable_rates"]).all()       # the sweep works on copies
+
+
+def test_buffer_generator_vs_reference(cuda_device, monkeypatch):
+    """SharedReplayBuffer.insert / compute_returns / feed_forward_generator_transformer / after_update against the reference's
+    buffer on the same content with the same injected permutation (fixture `buffer`, shared_buffer.py:118-151,188-198,
+    240-314): the 12-tuple of every minibatch -- row-to-sample grouping, agent order, share_obs replication -- bit for bit.
+    use_gae=False is accepted and ignored like in the reference (compute_returns only has GAE branches)."""
+    from conftest import golden
+    from mat_dcml_b200 import SharedReplayBuffer, Action_Space
+    g = golden("buffer")
+    T, N, L, W = int(g["T"]), int(g["N"]), int(g["L"]), int(g["W"])
+    buf = SharedReplayBuffer(_args(episode_length=T, n_rollout_threads=N, use_valuenorm=False, use_popart=False, use_gae=False),
+                             L, [7], [W + 2], Action_Space(2, semi_index=-1, extra=True), "DCML", device=cuda_device)
+    dev = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(cuda_device)
+    buf._share_obs[0].copy_(dev(g["first_share_obs"][:, 0])); buf.obs[0].copy_(dev(g["first_obs"]))
+    buf.available_actions[0].copy_(dev(g["first_ava"]))
+    for t in range(T):
+        s = lambda k: g["s%d_%s" % (t, k)]
+        # host numpy inputs in the reference's replicated layout (share_obs (N, L, D), rewards / masks (N, L, 1))
+        buf.insert(s("share_obs"), s("obs"), None, None, s("actions"), s("logp"), s("values"), s("rewards"), s("masks"), None, None,
+                   s("ava"))
+    buf.compute_returns(dev(g["next_value"]), None)
+    perm = torch.from_numpy(g["perm"]).to(cuda_device)
+    monkeypatch.setattr(torch, "randperm", lambda n, **k: perm.clone())
+    names = ("share_obs", "obs", "rnn", "rnn_c", "actions", "value_preds", "returns", "masks", "active", "old_logp", "adv", "ava")
+    n_mb = 0
+    for i, sample in enumerate(buf.feed_forward_generator_transformer(dev(g["adv"]), num_mini_batch=3)):
+        n_mb += 1
+        assert len(sample) == 12 and sample[2] is None and sample[3] is None
+        for k, v in zip(names, sample):
+            if k.startswith("rnn"):
+                continue
+            want = g["mb%d_%s" % (i, k)]
+            assert tuple(v.shape) == want.shape, (k, v.shape, want.shape)
+            np.testing.assert_array_equal(v.cpu().numpy(), want, err_msg="minibatch %d %s" % (i, k))
+    assert n_mb == 3
+    monkeypatch.undo()
+    buf.after_update()
+    np.testing.assert_array_equal(buf.obs[0].cpu().numpy(), g["after_obs0"])
+    np.testing.assert_array_equal(buf._share_obs[0].cpu().numpy(), g["after_share0"])
+    np.testing.assert_array_equal(buf.masks[0].cpu().numpy(), g["after_masks0"])
+    np.testing.assert_array_equal(buf.available_actions[0].cpu().numpy(), g["after_ava0"])
