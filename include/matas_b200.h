@@ -183,6 +183,12 @@ int dcml_env_destroy(dcml_env* e);
  * the L agents, …SingleProcess.py:270), ava [B*L*2]. */
 int dcml_env_reset(dcml_env* e, float* obs, float* share_obs, float* ava, void* stream);
 
+/* Env.reset(binary=True) (…SingleProcess.py:164-172): the task size enters share_obs as the 32-bit strings of R and C
+ * (most significant bit first) instead of the two normalised values, so a share_obs row is 62 floats wider
+ * ([B*(W+64)], Shannon mode [B*(2W+64)]), and observation features 0 / 1 of every agent are that row's first two entries
+ * (the two top bits of R, :203).  Only this call is binary: the reset inside a step is not (:139), as in the reference. */
+int dcml_env_reset_binary(dcml_env* e, float* obs, float* share_obs_bits, float* ava, void* stream);
+
 /* Env.step: actions [B*L] -> next obs/share_obs/ava plus reward [B], done [B] (uint8),
  * delay [B], payment [B] (the info dict, …SingleProcess.py:143); the reference broadcasts
  * reward/done over the L agents (DCML_ENVs/DCML_Basic_Env.py:9-13). */

@@ -52,6 +52,7 @@ _SIGNATURES = {
     "dcml_env_create": (ctypes.c_int, [ctypes.POINTER(EnvCfg), _P, ctypes.POINTER(_P)]),
     "dcml_env_destroy": (ctypes.c_int, [_P]),
     "dcml_env_reset": (ctypes.c_int, [_P, _P, _P, _P, _P]),
+    "dcml_env_reset_binary": (ctypes.c_int, [_P, _P, _P, _P, _P]),
     "dcml_env_step": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "dcml_env_set_context": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "matas_adam_clip_step": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double,

@@ -27,7 +27,7 @@ constexpr double B_TOTAL = 100e9;                 // DCML_Master.py:29
 constexpr int RETRY_CAP = 4096, SLOT_CAP = 4096;
 constexpr int LWS = 21;                      // padded per-thread stride of the shared workload copy
 
-enum { ENV_INIT = 0, ENV_STEP = 1, ENV_OBSERVE = 2 };
+enum { ENV_INIT = 0, ENV_STEP = 1, ENV_OBSERVE = 2, ENV_RESET = 3 };   // RESET: a new context, workload tables kept
 
 struct EnvState {
     long B;
@@ -58,6 +58,7 @@ struct EnvIO {
     uint8_t* done;         // [B]
     float* delay;          // [B]
     float* payment;        // [B]
+    int binary;            // reset(binary=True): share_obs rows start with the 32 + 32 bits of R and C (then width + 62 wide)
 };
 
 struct RetryStream {
@@ -313,6 +314,12 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
     // ---- observation :180-271 -------------------------------------------------------------------
     const double Rn = env_ok ? (sc[2] - (double)R_MIN) / (double)(R_MAX - R_MIN) : 0.0;   // DCML_Master.py:54
     const double Cn = env_ok ? (sc[3] - (double)C_MIN) / (double)(C_MAX - C_MIN) : 0.0;
+    // reset(binary=True) :164-172: share_obs starts with R and C as 32-bit strings (most significant bit first) and the
+    // observation rows carry its first two entries -- the two top bits of R -- where Rn, Cn would be (:203 shared_obs[:2])
+    const uint32_t Rb = env_ok ? (uint32_t)sc[2] : 0u, Cb = env_ok ? (uint32_t)sc[3] : 0u;
+    const float o0 = io.binary ? (float)(Rb >> 31) : (float)Rn, o1 = io.binary ? (float)((Rb >> 30) & 1u) : (float)Cn;
+    const long sw = (st.shannon ? 2 * W + 2 : W + 2) + (io.binary ? 62 : 0);    // floats per share_obs row
+    const int s0 = io.binary ? 64 : 2;                                          // first per-worker column
     double* my_f = s_f + (size_t)threadIdx.x * 3;
     if (active) {
         const int a = si[3];
@@ -321,7 +328,7 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
         for (int j = 0; j < w; ++j) en_before += !e_dis[j];
         const int n_en = W - si[4];
         float* o = io.obs + (env * L + w) * 7;
-        o[0] = (float)Rn; o[1] = (float)Cn;
+        o[0] = o0; o[1] = o1;
         if (dis) {
             // :207-213: ones, then the previous row's 7th feature (0 for the first row)
             const double f7 = en_before > 0 ? (double)(en_before - 1) / (double)n_en : 0.0;
@@ -339,26 +346,30 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
         io.ava[(env * L + w) * 2] = 1.f;                                   // Worker.get_availability :144-148
         io.ava[(env * L + w) * 2 + 1] = dis ? 0.f : 1.f;
         if (st.shannon) {                                                  // :248-250
-            io.sob[env * (2 * W + 2) + 2 + w] = (float)(e_ru[w] / 1e7);
-            io.sob[env * (2 * W + 2) + 2 + W + w] = (float)(e_rd[w] / 1e7);
+            io.sob[env * sw + s0 + w] = (float)(e_ru[w] / 1e7);
+            io.sob[env * sw + s0 + W + w] = (float)(e_rd[w] / 1e7);
         } else {
-            io.sob[env * (W + 2) + 2 + w] = (float)e_d[w];                 // :252-253
+            io.sob[env * sw + s0 + w] = (float)e_d[w];                     // :252-253
+        }
+        if (io.binary && w < 64) {
+            const int bit = 31 - (w & 31);
+            io.sob[env * sw + w] = (float)(((w < 32 ? Rb : Cb) >> bit) & 1u);
         }
     }
     __syncthreads();
     if (env_ok && w == 0) {
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, sp = 0.0;
+        double m0 = 0.0, m1 = 0.0, m2 = 0.0, sp = 0.0;
         const double* ef = s_f + (size_t)(le * tpe) * 3;
         for (int j = 0; j < W; ++j)
-            if (!e_dis[j]) { s0 += ef[j * 3]; s1 += ef[j * 3 + 1]; s2 += ef[j * 3 + 2]; sp += e_d[j]; }
+            if (!e_dis[j]) { m0 += ef[j * 3]; m1 += ef[j * 3 + 1]; m2 += ef[j * 3 + 2]; sp += e_d[j]; }
         const double n_en = (double)(W - si[4]);
         float* o = io.obs + (env * L + W) * 7;                             // :235-239
-        o[0] = (float)Rn; o[1] = (float)Cn;
-        o[2] = (float)(s0 / n_en); o[3] = (float)(s1 / n_en); o[4] = (float)(s2 / n_en);
+        o[0] = o0; o[1] = o1;
+        o[2] = (float)(m0 / n_en); o[3] = (float)(m1 / n_en); o[4] = (float)(m2 / n_en);
         o[5] = (float)(sp / n_en); o[6] = 1.1f;
         io.ava[(env * L + W) * 2] = 1.f; io.ava[(env * L + W) * 2 + 1] = 1.f;
-        const long sw = st.shannon ? 2 * W + 2 : W + 2;
-        io.sob[env * sw] = (float)Rn; io.sob[env * sw + 1] = (float)Cn;
+        if (!io.binary) { io.sob[env * sw] = (float)Rn; io.sob[env * sw + 1] = (float)Cn; }
+        else for (int b = W; b < 64; ++b) io.sob[env * sw + b] = (float)(((b < 32 ? Rb : Cb) >> (31 - (b & 31))) & 1u);   // W < 64
     }
 }
 
@@ -479,15 +490,27 @@ extern "C" int dcml_env_destroy(dcml_env* e) {
     return MATAS_OK;
 }
 
-extern "C" int dcml_env_reset(dcml_env* e, float* obs, float* share_obs, float* ava, void* stream) {
+static int env_reset(dcml_env* e, float* obs, float* share_obs, float* ava, int binary, void* stream) {
     int rc = env_check(e);
     if (rc) return rc;
     ARG_CHECK(obs && share_obs && ava, "null output");
     EnvIO io = {};
-    io.obs = obs; io.sob = share_obs; io.ava = ava;
-    e->t = 0;
+    io.obs = obs; io.sob = share_obs; io.ava = ava; io.binary = binary;
+    // The first reset builds the workers (Worker.__init__: step-0 jitter stream).  A later reset is the reference's
+    // env.reset() on a live env: a fresh context from the next step's named draws, the carried workload tables untouched --
+    // it never rewinds the step counter, so no context is ever replayed.
+    const int what = e->reset_done ? ENV_RESET : ENV_INIT;
+    if (e->reset_done) e->t += 1; else e->t = 0;
     e->reset_done = true;
-    return env_launch(e, io, ENV_INIT, (cudaStream_t)stream);
+    return env_launch(e, io, what, (cudaStream_t)stream);
+}
+
+extern "C" int dcml_env_reset(dcml_env* e, float* obs, float* share_obs, float* ava, void* stream) {
+    return env_reset(e, obs, share_obs, ava, 0, stream);
+}
+
+extern "C" int dcml_env_reset_binary(dcml_env* e, float* obs, float* share_obs_bits, float* ava, void* stream) {
+    return env_reset(e, obs, share_obs_bits, ava, 1, stream);
 }
 
 extern "C" int dcml_env_step(dcml_env* e, const float* actions, float* obs, float* share_obs, float* ava, float* reward,
@@ -496,7 +519,7 @@ extern "C" int dcml_env_step(dcml_env* e, const float* actions, float* obs, floa
     if (rc) return rc;
     ARG_CHECK(e->reset_done, "dcml_env_step before dcml_env_reset");
     ARG_CHECK(actions && obs && share_obs && ava && reward && done && delay && payment, "null argument");
-    EnvIO io;
+    EnvIO io = {};
     io.actions = actions; io.obs = obs; io.sob = share_obs; io.ava = ava; io.reward = reward; io.done = done;
     io.delay = delay; io.payment = payment;
     e->t += 1;

@@ -65,7 +65,8 @@ class _Infos:
 
 class DcmlVecEnv:
     def __init__(self, n_envs, n_workers=100, base_workload=None, seed=1, device="cuda", double_reset=True,
-                 env_offset=0, host_dtype=np.float64, replicate_share_obs=True, shannon=False, fixed=False, standalone=False):
+                 env_offset=0, host_dtype=np.float64, replicate_share_obs=True, shannon=False, fixed=False, standalone=False,
+                 multi_agent=True):
         """``host_dtype`` / ``replicate_share_obs`` only shape what ``reset`` / ``step`` hand back on the
         host: the reference returns float64 observations and L materialised copies of the share_obs row
         (…SingleProcess.py:270); float32 and a broadcast view avoid 0.35 GB of host copies per step at
@@ -75,10 +76,15 @@ class DcmlVecEnv:
         # Env(fixed=True): actions ignored, all available workers, K = floor(0.7 N) (…SingleProcess.py:58-62);
         # standalone: every step is the reference's step(standalone=True) (uncoded on worker 0, reward x 1.5, :81-92)
         self.fixed, self.standalone = bool(fixed), bool(standalone)
+        # Env(multi_agent=False) (…SingleProcess.py:42-47, 270-274; DCML_Basic_Env.py:14-17): ONE learner sees the whole env --
+        # the host contract hands out obs as one (L*7) vector per env, the share_obs row once, reward (N, 1), dones (N, 1);
+        # the simulator itself is unchanged
+        self.multi_agent = bool(multi_agent)
         self.num_envs = self.N = int(n_envs)
         self.W, self.L = int(n_workers), int(n_workers) + 1
         self.n_agents = self.L
         self.env_offset = int(env_offset)
+        self.seed, self.double_reset = int(seed), bool(double_reset)
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _cabi.MatasError("DcmlVecEnv needs a CUDA device (there is no CPU fallback)")
@@ -86,10 +92,11 @@ class DcmlVecEnv:
         if base.shape != (self.W, PERIOD):
             raise ValueError("base_workload must be (%d, %d)" % (self.W, PERIOD))
         self.base_workload = np.ascontiguousarray(base)
-        self.observation_space = [[7]] * self.L                       # …SingleProcess.py:41
+        self.observation_space = [[7]] * self.L if self.multi_agent else [[7 * self.L]]     # …SingleProcess.py:41-44
         self.sob_dim = 2 * self.W + 2 if self.shannon else self.W + 2
         self.share_observation_space = [[self.sob_dim]]               # :45
-        self.action_space = [Action_Space(2, semi_index=-1, extra=True)]   # :48-49
+        self.action_space = ([Action_Space(2, semi_index=-1, extra=True)] if self.multi_agent else   # :46-49
+                             [Action_Space(2, semi_index=-1, extra=True, mixed=True, low=0, high=self.W)])
         cfg = _cabi.EnvCfg(self.N, self.W, int(seed) & 0xFFFFFFFFFFFFFFFF, int(env_offset), int(bool(double_reset)), int(self.shannon),
                            int(self.fixed), int(self.standalone))
         h = ctypes.c_void_p()
@@ -143,6 +150,10 @@ class DcmlVecEnv:
         R = dev(R, torch.float64, (self.N,))
         C = dev(C, torch.float64, (self.N,))
         pr = dev(worker_pr, torch.float64, (self.N, self.W))
+        if n_disabled is not None:
+            k = np.asarray(n_disabled)
+            if k.min() < 0 or k.max() >= self.W:      # W - k enabled workers divide the 7th feature and the master row means
+                raise ValueError("n_disabled must be in [0, %d)" % self.W)
         nd = dev(n_disabled, torch.int32, (self.N,))
         with torch.cuda.device(self.device):
             _cabi.check(_cabi.lib().dcml_env_set_context(self._h, _cabi.ptr(R), _cabi.ptr(C), _cabi.ptr(pr), _cabi.ptr(nd),
@@ -162,17 +173,29 @@ class DcmlVecEnv:
         torch.cuda.current_stream(self.device).synchronize()
         return host
 
-    def _host_obs(self, host):
+    def _host_obs(self, host, sob_key="sob"):
         dt = self.host_dtype
         obs = host["obs"].numpy().astype(dt, copy=False)
-        row = host["sob"].numpy().astype(dt, copy=False)[:, None, :]
-        sob = np.repeat(row, self.L, axis=1) if self.replicate_share_obs else np.broadcast_to(row, (self.N, self.L, self.sob_dim))
         ava = host["ava"].numpy().astype(np.int64 if dt == np.float64 else dt, copy=False)
+        if not self.multi_agent:                                      # …SingleProcess.py:272-274: flat obs, one share_obs row
+            return obs.reshape(self.N, self.L * 7), host[sob_key].numpy().astype(dt, copy=False), ava
+        row = host[sob_key].numpy().astype(dt, copy=False)[:, None, :]
+        sob = np.repeat(row, self.L, axis=1) if self.replicate_share_obs else np.broadcast_to(row, (self.N, self.L, row.shape[-1]))
         return obs, sob, ava
 
-    def reset(self):
-        self.reset_device()
-        return self._host_obs(self._fetch(("obs", "sob", "ava")))
+    def reset(self, binary=False):
+        """Env.reset through the vec-env.  ``binary=True`` is the reference's ``reset(binary=True)``
+        (…SingleProcess.py:164-172): R and C enter share_obs as two 32-bit strings, which makes its rows 62 wider, and the
+        first two features of every observation row are that row's first two entries.  Only this observation is binary: a
+        step's own reset is not (:139)."""
+        if not binary:
+            self.reset_device()
+            return self._host_obs(self._fetch(("obs", "sob", "ava")))
+        self.sob_bits = torch.empty(self.N, self.sob_dim + 62, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib().dcml_env_reset_binary(self._h, _cabi.ptr(self.obs), _cabi.ptr(self.sob_bits), _cabi.ptr(self.ava),
+                                                          _cabi.stream_ptr()))
+        return self._host_obs(self._fetch(("obs", "sob_bits", "ava")), "sob_bits")
 
     def step(self, actions):
         if not torch.is_tensor(actions):
@@ -187,9 +210,11 @@ class DcmlVecEnv:
         dt = self.host_dtype
         rew = host["reward"].numpy().astype(dt, copy=False)[:, None, None]
         dones = host["done"].numpy().astype(bool)[:, None]
+        infos = _Infos(host["delay"].numpy(), host["payment"].numpy())
+        if not self.multi_agent:                                      # DCML_Basic_Env.py:14-17: one reward / done per env
+            return obs, sob, rew[:, :, 0], dones, infos, ava
         if self.replicate_share_obs:
             rew, dones = np.repeat(rew, self.L, axis=1), np.repeat(dones, self.L, axis=1)
         else:
             rew, dones = np.broadcast_to(rew, (self.N, self.L, 1)), np.broadcast_to(dones, (self.N, self.L))
-        infos = _Infos(host["delay"].numpy(), host["payment"].numpy())
         return obs, sob, rew, dones, infos, ava

@@ -30,6 +30,7 @@ class DcmlRunner:
     def __init__(self, config):
         self.all_args = a = config["all_args"]
         self.envs = config["envs"]
+        self._eval_envs = config.get("eval_envs")
         self.device = torch.device(config.get("device", "cuda"))
         if self.device.type != "cuda":
             raise _cabi.MatasError("DcmlRunner needs a CUDA device (there is no CPU fallback)")
@@ -42,6 +43,10 @@ class DcmlRunner:
         self.n_rollout_threads = a.n_rollout_threads
         self.use_linear_lr_decay = getattr(a, "use_linear_lr_decay", False)
         self.use_centralized_V = getattr(a, "use_centralized_V", True)
+        if not self.use_centralized_V:
+            # base_runner.py:190-193 would hand the 7-wide local observation to the critic input; the MAT encoder ignores
+            # that input (encode_state=False) and the buffer here is sized for the (W+2)-wide share_obs row
+            raise NotImplementedError("use_centralized_V=False is not wired (the MAT policy never reads share_obs)")
         self.log_interval = getattr(a, "log_interval", 1)
         self.save_interval = getattr(a, "save_interval", 0)
         self.save_dir = config.get("save_dir")
@@ -57,6 +62,15 @@ class DcmlRunner:
         self.trainer = MATTrainer(a, self.policy, self.num_agents, device=self.device)
         self.buffer = SharedReplayBuffer(a, self.num_agents, env.observation_space[0], env.share_observation_space[0],
                                          env.action_space[0], a.env_name, device=self.device)
+
+    @property
+    def eval_envs(self):
+        """Evaluation envs (config["eval_envs"], else a second batch like the training one on another seed, built on first use)."""
+        if self._eval_envs is None:
+            e = self.envs
+            self._eval_envs = type(e)(e.N, e.W, e.base_workload, seed=e.seed + 1, device=self.device, double_reset=e.double_reset,
+                                      env_offset=e.env_offset, shannon=e.shannon, fixed=e.fixed, standalone=e.standalone)
+        return self._eval_envs
 
     # ---- dcml_runner.py:126-142 ------------------------------------------------------------------------
     def warmup(self):
@@ -115,7 +129,11 @@ class DcmlRunner:
         the evaluation envs (preset contexts via ``DcmlVecEnv.set_context`` reproduce the reference's benchmark
         mode).  Returns the reference's 4-tuple: mean reward / delay / payment over the episodes that finished,
         and the mean time of one batched decision in seconds (measured on the device)."""
-        envs = self.envs if eval_envs is None else eval_envs
+        envs = self.eval_envs if eval_envs is None else eval_envs
+        if envs is self.envs:
+            # the reference evaluates on separate eval_envs (dcml_runner.py:319-338); resetting the training envs here would
+            # leave buffer.obs[0] describing a context the envs no longer hold
+            raise ValueError("eval() needs evaluation envs of its own, not the training envs")
         self.trainer.prep_rollout()
         N, L = envs.N, envs.L
         f64 = dict(dtype=torch.float64, device=self.device)

@@ -191,8 +191,9 @@ class DcmlEnvOracle:
             up, down = shannon_rates(W, 50 + (60 - 50) * pm, 10 + (20 - 10) * pw, 10 + (100 - 10) * d)
             self.rate_up[e], self.rate_down[e] = up, down
 
-    def observe(self, e):
-        """ENV:180-271 -> obs (L,7), share_obs row (W+2,), ava (L,2)."""
+    def observe(self, e, binary=False):
+        """ENV:180-271 -> obs (L,7), share_obs row (W+2,), ava (L,2).  ``binary`` (ENV:164-172): R and C as 32-bit strings
+        at the head of share_obs (row 62 wider); observation features 0 / 1 are that row's first two entries (ENV:203)."""
         W, a = self.W, int(self.arrive[e])
         Rn = (self.R[e] - R_MIN) / (R_MAX - R_MIN)                                # MASTER:54
         Cn = (self.C[e] - C_MIN) / (C_MAX - C_MIN)
@@ -218,21 +219,30 @@ class DcmlEnvOracle:
             prev7 = row[6]
             obs[i] = row
         obs[W] = [Rn, Cn, sums[0] / n_en, sums[1] / n_en, sums[2] / n_en, sum_pr / n_en, 1.1]   # ENV:235-239
+        head = [Rn, Cn]
+        if binary:                                                                # ENV:164-172
+            head = [int(c) for c in "{:032b}".format(int(self.R[e]))] + [int(c) for c in "{:032b}".format(int(self.C[e]))]
+            obs[:, 0], obs[:, 1] = head[0], head[1]                               # ENV:203,246 shared_obs[:2]
         if self.shannon:
-            sob = np.concatenate([[Rn, Cn], self.rate_up[e] / 10 ** 7, self.rate_down[e] / 10 ** 7])   # ENV:248-250
+            sob = np.concatenate([head, self.rate_up[e] / 10 ** 7, self.rate_down[e] / 10 ** 7])   # ENV:248-250
         else:
-            sob = np.concatenate([[Rn, Cn], self.Pr[e]])                          # ENV:252-253
+            sob = np.concatenate([head, self.Pr[e]])                              # ENV:252-253
         return obs, sob, ava
 
-    def _observe_all(self):
-        o, s, a = zip(*[self.observe(e) for e in range(self.B)])
+    def _observe_all(self, binary=False):
+        o, s, a = zip(*[self.observe(e, binary) for e in range(self.B)])
         sob = np.stack(s)[:, None, :].repeat(self.L, axis=1)                      # ENV:270 replicate over agents
         return np.stack(o), sob, np.stack(a)
 
-    def reset(self):
+    def reset(self, binary=False):
+        # a reset of a live env draws a fresh context from the next step's named streams and keeps the workload tables
+        # (Env.reset on an existing env, ENV:157-274); only the first reset is "step 0"
+        if getattr(self, "_was_reset", False):
+            self.t += 1
+        self._was_reset = True
         for e in range(self.B):
             self._reset_env(e, _Draws(self.seed, self.env0 + e, self.t, self.W), 0)
-        return self._observe_all()
+        return self._observe_all(binary)
 
     def set_context(self, R=None, C=None, Pr=None, k_dis=None, disabled=None, arrive=None):
         """Preset contexts (ENV:174-178,191-194 ``preset=True``); arrays indexed by env."""

@@ -113,7 +113,7 @@ class _Ctx:
     pass
 
 
-def gen_env(out, W, B, steps, seed, real_workloads, shannon=False, variants=False):
+def gen_env(out, W, B, steps, seed, real_workloads, shannon=False, variants=False, single=False):
     _ref_paths()
     import DCML_ENVs.DCML_utils.DCML_Config as cfg
     if W != 100 or shannon:                        # constants are star-imported
@@ -289,6 +289,38 @@ def gen_env(out, W, B, steps, seed, real_workloads, shannon=False, variants=Fals
                 for k, v in rows.items():
                     acc.setdefault(k, []).append(np.asarray(v))
             res.update({tag + "_" + k: np.asarray(v) for k, v in acc.items()})      # [env][step ...]
+        np.savez_compressed(out, **res)
+        print("wrote", out)
+        return
+
+    if single:
+        # Env(multi_agent=False) (ENV:42-47,272-274; BASE:14-17) with a first reset(binary=True) (ENV:164-172): flat observation,
+        # ONE share_obs row (64 + W wide after the binary reset, W + 2 after a step), one reward / done per env
+        L = W + 1
+        res = {"W": W, "B": B, "steps": steps, "seed": seed, "base": base}
+        rng = np.random.RandomState(seed + 5)
+        acc = {}
+        for e in range(B):
+            ctx.t = 0
+            env = make(e, multi_agent=False)()
+            ctx.r[e] = 0
+            assert env.observation_space == [[7 * L]] and env.action_space[0].mixed and env.action_space[0].high == W
+            obs, sob, ava = env.reset(binary=True)
+            assert obs.shape == (7 * L,) and sob.shape == (64 + W,) and ava.shape == (L, 2)
+            rows = {"obs": [], "sob": [], "ava": [ava], "act": [], "rew": [], "delay": [], "pay": [], "done": []}
+            acc.setdefault("obs0", []).append(obs); acc.setdefault("sob0", []).append(sob)
+            for t in range(1, steps + 1):
+                ctx.t = t
+                sel = (rng.uniform(size=W) < 0.6).astype(np.float32) * ava[:W, 1]
+                act = np.concatenate([sel, [np.float32(rng.uniform(0.2, 1.0))]]).astype(np.float32)
+                obs, sob, rew, dones, info, ava = env.step(act.reshape(L, 1))
+                assert obs.shape == (7 * L,) and sob.shape == (W + 2,) and rew.shape == (1,) and dones.shape == (1,)
+                for k, v in zip(("obs", "sob", "ava", "act", "rew", "delay", "pay", "done"),
+                                (obs, sob, ava, act, rew[0], info[0]["delay"], info[0]["payment"], dones[0])):
+                    rows[k].append(v)
+            for k, v in rows.items():
+                acc.setdefault(k, []).append(np.asarray(v))
+        res.update({k: np.asarray(v) for k, v in acc.items()})          # [env][step ...]
         np.savez_compressed(out, **res)
         print("wrote", out)
         return
@@ -521,6 +553,7 @@ FAMILIES = {
     "env_W50_wide": lambda o: gen_env(o, 50, 32, 16, 12, False),
     "env_W12_shannon": lambda o: gen_env(o, 12, 8, 1, 4, False, shannon=True),
     "env_W16_variants": lambda o: gen_env(o, 16, 6, 5, 7, False, variants=True),
+    "env_W16_single_binary": lambda o: gen_env(o, 16, 6, 4, 9, False, single=True),
     "gae": gen_gae,
     "buffer": gen_buffer,
     "ppo_L11": lambda o: gen_ppo(o, 11, 6, 8),

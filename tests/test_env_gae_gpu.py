@@ -88,6 +88,54 @@ def test_env_shannon_vs_reference_and_oracle(cuda_device):
         _close(r1, r2); _close(o1, o2); _close(s1, s2); np.testing.assert_array_equal(d1, d2)
 
 
+def test_env_single_agent_binary_vs_reference(cuda_device):
+    """DcmlVecEnv(multi_agent=False).reset(binary=True) + steps against the reference's Env(multi_agent=False)
+    (…SingleProcess.py:42-47,164-172,272-274; DCML_Basic_Env.py:14-17)."""
+    from mat_dcml_b200 import DcmlVecEnv
+    g = golden("env_W16_single_binary")
+    W, B, steps = int(g["W"]), int(g["B"]), int(g["steps"])
+    L = W + 1
+    env = DcmlVecEnv(B, W, g["base"], seed=int(g["seed"]), double_reset=False, multi_agent=False)
+    assert env.observation_space == [[7 * L]] and env.action_space[0].mixed and env.action_space[0].high == W
+    obs, sob, ava = env.reset(binary=True)
+    assert obs.shape == (B, 7 * L) and sob.shape == (B, 64 + W) and ava.shape == (B, L, 2)
+    _close(obs, g["obs0"], "obs0"); _close(sob, g["sob0"], "sob0")
+    np.testing.assert_array_equal(ava, g["ava"][:, 0])
+    for t in range(steps):
+        obs, sob, rew, dones, infos, ava = env.step(g["act"][:, t])
+        assert obs.shape == (B, 7 * L) and sob.shape == (B, W + 2) and rew.shape == (B, 1) and dones.shape == (B, 1)
+        _close(rew[:, 0], g["rew"][:, t], "reward")
+        _close([i[0]["delay"] for i in infos], g["delay"][:, t]); _close([i[0]["payment"] for i in infos], g["pay"][:, t])
+        np.testing.assert_array_equal(dones[:, 0], g["done"][:, t])
+        _close(obs, g["obs"][:, t], "obs"); _close(sob, g["sob"][:, t], "sob")
+        np.testing.assert_array_equal(ava, g["ava"][:, t + 1])
+    # the multi-agent contract after a binary reset: the wider row replicated over the agents
+    env2 = DcmlVecEnv(B, W, g["base"], seed=int(g["seed"]), double_reset=False)
+    o2, s2, a2 = env2.reset(binary=True)
+    assert s2.shape == (B, L, 64 + W)
+    _close(o2.reshape(B, 7 * L), g["obs0"]); _close(s2[:, 3], g["sob0"])
+
+
+def test_env_repeated_reset_draws_a_new_context(cuda_device):
+    """A second reset() is the reference's env.reset() on a live env: fresh context, workload tables kept, no replay."""
+    from mat_dcml_b200 import DcmlVecEnv
+    W, B = 12, 9
+    env = DcmlVecEnv(B, W, seed=21)
+    ora = eo.DcmlEnvOracle(B, W, env.base_workload, seed=21)
+    o1, _, a1 = env.reset(); p1, _, b1 = ora.reset()
+    _close(o1, p1); np.testing.assert_array_equal(a1, b1)
+    act = np.concatenate([a1[:, :W, 1].astype(np.float32), np.full((B, 1), 0.6, np.float32)], 1)[:, :, None]
+    env.step(act); ora.step(act)
+    o2, _, a2 = env.reset(); p2, _, b2 = ora.reset()
+    _close(o2, p2); np.testing.assert_array_equal(a2, b2)
+    assert not np.allclose(o1[:, 0, :2], o2[:, 0, :2])            # new (R, C)
+    act = np.concatenate([a2[:, :W, 1].astype(np.float32), np.full((B, 1), 0.6, np.float32)], 1)[:, :, None]
+    _, _, r1, d1, _, _ = env.step(act); _, _, r2, d2, _, _ = ora.step(act)
+    _close(r1, r2); np.testing.assert_array_equal(d1, d2)
+    with pytest.raises(ValueError):
+        env.set_context(n_disabled=np.full(B, W))
+
+
 def test_env_preset_context(cuda_device):
     from mat_dcml_b200 import DcmlVecEnv
     W, B = 20, 5

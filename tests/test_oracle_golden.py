@@ -103,6 +103,28 @@ def test_env_matches_reference(case):
         np.testing.assert_array_equal(ava, g["ava%d" % t])
 
 
+def test_env_single_agent_binary_matches_reference():
+    """Env(multi_agent=False) + reset(binary=True): the reference's flat single-learner contract is a reshape of the same
+    simulator; the binary reset changes share_obs (64 + W wide) and observation features 0 / 1 (fixture env_W16_single_binary)."""
+    g = golden("env_W16_single_binary")
+    W, B, steps = int(g["W"]), int(g["B"]), int(g["steps"])
+    L = W + 1
+    env = eo.DcmlEnvOracle(B, W, g["base"], seed=int(g["seed"]), double_reset=False)
+    obs, sob, ava = env.reset(binary=True)
+    np.testing.assert_allclose(obs.reshape(B, L * 7), g["obs0"], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(sob[:, 0], g["sob0"], rtol=1e-12, atol=1e-14)
+    np.testing.assert_array_equal(ava, g["ava"][:, 0])
+    for t in range(steps):
+        act = g["act"][:, t]
+        obs, sob, rew, dones, infos, ava = env.step(act[:, :, None])
+        np.testing.assert_allclose(rew[:, 0, 0], g["rew"][:, t], rtol=1e-12)
+        np.testing.assert_allclose([i[0]["delay"] for i in infos], g["delay"][:, t], rtol=1e-12)
+        np.testing.assert_array_equal(dones[:, 0], g["done"][:, t])
+        np.testing.assert_allclose(obs.reshape(B, L * 7), g["obs"][:, t], rtol=1e-12, atol=1e-14)
+        np.testing.assert_allclose(sob[:, 0], g["sob"][:, t], rtol=1e-12, atol=1e-14)
+        np.testing.assert_array_equal(ava, g["ava"][:, t + 1])
+
+
 def test_env_shannon_matches_reference():
     g = golden("env_W12_shannon")
     W, B = int(g["W"]), int(g["B"])
