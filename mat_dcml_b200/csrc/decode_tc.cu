@@ -164,24 +164,22 @@ __device__ __forceinline__ void add_operand16(float (&v)[16], const unsigned cha
         }
     }
 }
-// LayerNorm of a 64-column row held by four threads (16 columns each).  Two CTA barriers.  v becomes x_hat.
+// LayerNorm of a 64-column row held by four threads (16 columns each): ONE exchange of (sum, sum of squares) through
+// shared memory and ONE CTA barrier; var = E[x^2] - mean^2 (inputs are residual sums of O(1) rows: the cancellation costs
+// a few ulp of the variance).  v becomes x_hat.  Two calls must be separated by a CTA barrier (every stage has one).
 __device__ __forceinline__ void layernorm_quad(float (&v)[16], float* __restrict__ sRed, int row, int q) {
-    float s = 0.f;
+    float s = 0.f, d = 0.f;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) s += v[i];
-    sRed[row * 4 + q] = s;
+    for (int i = 0; i < 16; ++i) { s += v[i]; d = fmaf(v[i], v[i], d); }
+    reinterpret_cast<float2*>(sRed)[row * 4 + q] = make_float2(s, d);
     __syncthreads();
-    const float4 a = *reinterpret_cast<const float4*>(sRed + row * 4);
-    const float mean = (a.x + a.y + a.z + a.w) * (1.0f / 64.0f);
-    float d = 0.f;
+    const float4 a = *reinterpret_cast<const float4*>(sRed + row * 8);
+    const float4 c = *reinterpret_cast<const float4*>(sRed + row * 8 + 4);
+    const float mean = (a.x + a.z + c.x + c.z) * (1.0f / 64.0f);
+    const float var = fmaxf((a.y + a.w + c.y + c.w) * (1.0f / 64.0f) - mean * mean, 0.f);
+    const float rs = rsqrtf(var + 1e-5f);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { v[i] -= mean; d = fmaf(v[i], v[i], d); }
-    sRed[4 * MAXR + row * 4 + q] = d;
-    __syncthreads();
-    const float4 c = *reinterpret_cast<const float4*>(sRed + 4 * MAXR + row * 4);
-    const float rs = rsqrtf((c.x + c.y + c.z + c.w) * (1.0f / 64.0f) + 1e-5f);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] *= rs;
+    for (int i = 0; i < 16; ++i) v[i] = (v[i] - mean) * rs;
 }
 
 // Block-0 self-attention attends over TOKEN EMBEDDINGS, which take one of six values (codes: 0 zero row,
@@ -693,6 +691,10 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
         __syncthreads();
         while (sched.next(st)) {
             const int j = st.j;
+            // availability of (env = tid, agent j) for the pick at the end of the position: loaded a position's worth of
+            // stages ahead of its use
+            float2 av = make_float2(1.f, 1.f);
+            if (a.ava && tid < n_valid) av = __ldg(reinterpret_cast<const float2*>(a.ava + ((env0 + tid) * L + j) * 2));
             if (TABK == 2) while (sb.s != sched.s) sb.next();
             // ---- input token of this position (with the table, block 0 never looks at it) -----------------------
             float v[16];
@@ -797,11 +799,20 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                         tc::mma_commit(mma_bar);
                     }
                     ring.prefetch();
+                    // the residual row comes from global memory (this thread stored it two stages ago): issue the loads
+                    // before waiting for the tensor core so that their latency is off the stage's critical path
+                    float res[16];
+                    if (blk != 0 && live) load16(res, x_row);
+                    else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) res[i] = 0.f;
+                    }
                     mma_wait();
                     result16(tmem, 0, row, q, v);
                     add16(v, w1 + lay::B_BIAS + q * 16);
                     if (blk == 0) add16(v, s.sEmb + s.sCode[row] * 64 + q * 16);
-                    else if (live) add16(v, x_row);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += res[i];
                     layernorm_quad(v, s.sRed, row, q);
                     affine16(v, w1, q);
                     ring.release(); ring.release();
@@ -827,10 +838,17 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                         tc::mma_commit(mma_bar);
                     }
                     ring.prefetch();
+                    float res[16];                                 // obs_rep row: loaded under the MMAs (see LN1 above)
+                    if (live) load16(res, b.rep + ((env0 + row) * L + j) * 64 + q * 16);
+                    else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) res[i] = 0.f;
+                    }
                     mma_wait();
                     result16(tmem, 0, row, q, v);
                     add16(v, w1 + lay::B_BIAS + q * 16);
-                    if (live) add16(v, b.rep + ((env0 + row) * L + j) * 64 + q * 16);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += res[i];
                     layernorm_quad(v, s.sRed, row, q);
                     affine16(v, w1, q);
                     ring.release(); ring.release();
@@ -902,7 +920,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                     const float l1 = lp[1] + lp[3] + lp[5] + lp[7] + s.sHead[lay::DEC_H3_B + 1];
                     if (j < nd) {
                         float z0, z1;
-                        masked_logz(l0, l1, a.ava ? a.ava + g * 2 : nullptr, z0, z1);
+                        masked_logz(l0, l1, &av.x, z0, z1);
                         int act;
                         if (a.deterministic) {
                             act = z1 > z0;
