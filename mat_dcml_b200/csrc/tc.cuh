@@ -108,14 +108,16 @@ __device__ __forceinline__ void tmem_dealloc_n(uint32_t tmem) {  // one full war
 // one elected thread: (D1, D2) at TMEM columns [d, d+64), [d+64, d+128) (+)= A . W for the fp16 hi/lo operand at
 // shared address a (lo part at + A_PART) and the half blob at shared address w
 __device__ __forceinline__ void mma_set(uint32_t d, uint32_t a, uint32_t w, bool accumulate) {
-    const uint32_t idesc = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    // The half blob holds Whi (64 rows) and Wlo (64 rows) back to back, i.e. ONE 128-row K-major tile, and D1 | D2 are adjacent
+    // accumulator columns: Ahi . [Whi | Wlo] is a single N = 128 product (the A tile is read from shared memory once for
+    // both), then Alo . Whi accumulates into D2: 8 MMA instructions per [128 x 64].[64 x 64] stage instead of 12.
+    const uint32_t idesc128 = (1u << 4) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t idesc64 = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    static_assert(lay::HB_LO_BYTES == 64 * 128, "Wlo must follow Whi as rows 64..127 of one swizzled tile");
 #pragma unroll
-    for (int ks = 0; ks < 4; ++ks) mma_f16(d, make_desc(a + ks * 32), make_desc(w + ks * 32), idesc, (accumulate || ks > 0) ? 1u : 0u);
+    for (int ks = 0; ks < 4; ++ks) mma_f16(d, make_desc(a + ks * 32), make_desc(w + ks * 32), idesc128, (accumulate || ks > 0) ? 1u : 0u);
 #pragma unroll
-    for (int ks = 0; ks < 4; ++ks)
-        mma_f16(d + 64, make_desc(a + ks * 32), make_desc(w + lay::HB_LO_BYTES + ks * 32), idesc, (accumulate || ks > 0) ? 1u : 0u);
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks) mma_f16(d + 64, make_desc(a + A_PART + ks * 32), make_desc(w + ks * 32), idesc, 1u);
+    for (int ks = 0; ks < 4; ++ks) mma_f16(d + 64, make_desc(a + A_PART + ks * 32), make_desc(w + ks * 32), idesc64, 1u);
 }
 // MMA issue in warp-uniform control flow.  Under a plain `threadIdx.x == 0` the compiler cannot keep the descriptors
 // in uniform registers and wraps every UTCHMMA in an ELECT / R2UR / branch loop (about 13 extra instructions and two
@@ -185,15 +187,13 @@ __device__ __forceinline__ void gemm_issue(const Ctx& c, const float* slot) {
     if (issuer_warp()) {
         const uint32_t a0 = uni(c.a_saddr), b0 = uni(smem_u32(slot)), d0 = uni(c.tmem), bar = uni(smem_u32(c.bar));
         if (elect_one()) {
-            // instruction descriptor: D f32, A/B f16, both K-major, N = 64, M = 128
-            const uint32_t idesc = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            // instruction descriptors: D f32, A/B f16, both K-major, M = 128; Ahi . [Whi | Wlo] as one N = 128 product (see mma_set)
+            const uint32_t idesc128 = (1u << 4) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            const uint32_t idesc64 = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) mma_f16(d0, make_desc(a0 + ks * 32), make_desc(b0 + ks * 32), idesc, ks > 0);
+            for (int ks = 0; ks < 4; ++ks) mma_f16(d0, make_desc(a0 + ks * 32), make_desc(b0 + ks * 32), idesc128, ks > 0);
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-                mma_f16(d0 + 64, make_desc(a0 + ks * 32), make_desc(b0 + lay::HB_LO_BYTES + ks * 32), idesc, ks > 0);
-#pragma unroll
-            for (int ks = 0; ks < 4; ++ks) mma_f16(d0 + 64, make_desc(a0 + A_PART + ks * 32), make_desc(b0 + ks * 32), idesc, 1);
+            for (int ks = 0; ks < 4; ++ks) mma_f16(d0 + 64, make_desc(a0 + A_PART + ks * 32), make_desc(b0 + ks * 32), idesc64, 1);
             mma_commit_saddr(bar);
         }
     }
