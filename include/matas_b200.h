@@ -87,6 +87,17 @@ int matas_policy_get_actions(matas_policy* p, const float* obs, const float* ava
 int matas_policy_evaluate(matas_policy* p, const float* obs, const float* ava, const float* actions, long M,
                           float* values, float* logp, float* entropy, void* stream);
 
+/* MultiAgentTransformer.get_actions (ma_transformer.py:298-329) in two parts, for callers whose observations arrive from
+ * the host in slices (ma_transformer.py:304-307 copies them in one piece): matas_policy_encode_slice runs the encoder
+ * for the envs [env0, env0 + n_env) of a batch of B_total envs (obs / values point at the slice's first row; the first
+ * slice must be env0 = 0) and matas_policy_decode, once every slice is in, the autoregressive act of the whole batch
+ * (arguments as matas_policy_get_actions).  Together they compute exactly what matas_policy_get_actions computes. */
+int matas_policy_encode_slice(matas_policy* p, const float* obs, long env0, long n_env, long B_total, float* values,
+                              void* stream);
+int matas_policy_decode(matas_policy* p, const float* ava, long B, int deterministic, int stride, uint64_t seed,
+                        uint32_t step, long env_offset, const float* u, const float* z, float* actions, float* logp,
+                        void* stream);
+
 /* Training-mode forward + backward of MultiAgentTransformer.forward, replacing torch autograd in
  * MATTrainer.ppo_update (mat_src/mat/algorithms/mat/mat_trainer.py:120-147).
  * matas_policy_evaluate_train = matas_policy_evaluate that also keeps the activations;
@@ -194,6 +205,12 @@ int dcml_env_reset_binary(dcml_env* e, float* obs, float* share_obs_bits, float*
  * reward/done over the L agents (DCML_ENVs/DCML_Basic_Env.py:9-13). */
 int dcml_env_step(dcml_env* e, const float* actions, float* obs, float* share_obs, float* ava, float* reward,
                   uint8_t* done, float* delay, float* payment, void* stream);
+/* The same step for the envs [env0, env0 + n_env) only (all pointers are those of the FULL arrays): a host-facing wrapper
+ * issues the batch as a few slices so that the device-to-host copy of one slice's outputs runs under the next slice's
+ * kernel (env_wrappers.py:722-739 returns host arrays).  A step is complete when every env was covered exactly once;
+ * `first` = 1 on the slice that opens a step (it advances the step counter of the named random draws). */
+int dcml_env_step_slice(dcml_env* e, const float* actions, long env0, long n_env, int first, float* obs, float* share_obs,
+                        float* ava, float* reward, uint8_t* done, float* delay, float* payment, void* stream);
 
 /* Preset contexts (Env(preset=True) / modify_preset, …SingleProcess.py:25-32,174-194,344-353):
  * overwrite the context the next step will run against and re-emit the observation.

@@ -44,6 +44,9 @@ _SIGNATURES = {
     "matas_policy_act_autoregressive_static": (ctypes.c_int, [_P, _P, _P, ctypes.c_long, ctypes.c_int, ctypes.c_int,
                                                               ctypes.c_uint64, ctypes.c_uint32, ctypes.c_long, _P, _P, _P, _P, _P]),
     "matas_policy_act_parallel": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, _P, _P, _P]),
+    "matas_policy_encode_slice": (ctypes.c_int, [_P, _P, ctypes.c_long, ctypes.c_long, ctypes.c_long, _P, _P]),
+    "matas_policy_decode": (ctypes.c_int, [_P, _P, ctypes.c_long, ctypes.c_int, ctypes.c_int, ctypes.c_uint64, ctypes.c_uint32,
+                                           ctypes.c_long, _P, _P, _P, _P, _P]),
     "matas_policy_timing": (ctypes.c_int, [_P, ctypes.c_int]),
     "matas_policy_decode_time": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_long)]),
     "matas_gather_rows": (ctypes.c_int, [ctypes.c_int, _P, _P, _P, _P, _P, ctypes.c_long, _P]),
@@ -54,6 +57,7 @@ _SIGNATURES = {
     "dcml_env_reset": (ctypes.c_int, [_P, _P, _P, _P, _P]),
     "dcml_env_reset_binary": (ctypes.c_int, [_P, _P, _P, _P, _P]),
     "dcml_env_step": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "dcml_env_step_slice": (ctypes.c_int, [_P, _P, ctypes.c_long, ctypes.c_long, ctypes.c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
     "dcml_env_set_context": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "matas_adam_clip_step": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double,
                                             ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_long, _P, _P]),

@@ -501,6 +501,47 @@ extern "C" int matas_policy_get_actions(matas_policy* p, const float* obs, const
     return run_decode(p, ava, B, deterministic, stride, seed, step, env_offset, u, z, actions, logp, (cudaStream_t)stream);
 }
 
+// PolicyBufs whose token buffers start `tok0` tokens in (one env-aligned slice of a larger batch)
+static PolicyBufs shifted(const PolicyBufs& b, long tok0) {
+    PolicyBufs s = b;
+    const long o = tok0 * 64;
+    s.X += o; s.Q += o; s.rep += o; s.Y += o;
+    for (int k = 0; k < 2; ++k) {
+        s.K[k] += o; s.V[k] += o; s.K1[k] += o; s.V1[k] += o; s.K2[k] += o; s.V2[k] += o; s.Q2[k] += o;
+        for (int h = 0; h < 2; ++h) s.Q2p[k][h] += o;
+    }
+    return s;
+}
+
+/* get_actions in two parts, so that a caller whose observations arrive from the host in slices can run the encoder of
+ * one slice while the next slice is still on the PCIe bus: encoder of envs [env0, env0 + n_env) of a batch of B_total
+ * (obs, values point at the slice's first row), then -- once every slice is in -- the decode of the whole batch. */
+extern "C" int matas_policy_encode_slice(matas_policy* p, const float* obs, long env0, long n_env, long B_total, float* values,
+                                         void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(obs && values && n_env > 0 && env0 >= 0 && env0 + n_env <= B_total, "bad slice (env0=%ld n_env=%ld B=%ld)", env0, n_env, B_total);
+    const int L = p->cfg.n_agent;
+    if (B_total * L > p->tok_cap) {
+        ARG_CHECK(env0 == 0, "the first slice must start at env 0 (it sizes the token buffers)");
+        if ((rc = alloc_tokens(p, B_total * L))) return rc;
+    } else {
+        p->train_tokens = 0;
+    }
+    const PolicyBufs b = shifted(p->bufs, env0 * L);
+    return launch_encoder(b, obs, values, n_env, L, p->cfg.obs_dim, p->n_sm, (cudaStream_t)stream, nullptr, 1);
+}
+
+extern "C" int matas_policy_decode(matas_policy* p, const float* ava, long B, int deterministic, int stride, uint64_t seed,
+                                   uint32_t step, long env_offset, const float* u, const float* z, float* actions, float* logp,
+                                   void* stream) {
+    int rc = check_handle(p);
+    if (rc) return rc;
+    ARG_CHECK(actions && logp && B > 0, "bad argument (B=%ld)", B);
+    ARG_CHECK(B * p->cfg.n_agent <= p->tok_cap, "matas_policy_decode: the token buffers hold no encoder output for %ld envs", B);
+    return run_decode(p, ava, B, deterministic, stride, seed, step, env_offset, u, z, actions, logp, (cudaStream_t)stream);
+}
+
 extern "C" int matas_policy_act_autoregressive(matas_policy* p, const float* obs_rep, const float* ava, long B,
                                                int deterministic, int stride, uint64_t seed, uint32_t step,
                                                long env_offset, const float* u, const float* z, float* actions,

@@ -121,14 +121,14 @@ __device__ double price_after(const double* lw, const ProcOut& o, int m) {
     return price;
 }
 
-__global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t) {
+__global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env_first, long env_end) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int W = st.W, L = W + 1, tpe = st.tpe;
     const int epb = blockDim.x / tpe;
     const int le = threadIdx.x / tpe;            // local env
     const int w = threadIdx.x - le * tpe;        // worker (>= W: idle lane)
-    const long env = (long)blockIdx.x * epb + le;
-    const bool env_ok = env < st.B;
+    const long env = env_first + (long)blockIdx.x * epb + le;
+    const bool env_ok = env < env_end;
     const bool active = env_ok && w < W;
     const uint32_t genv = (uint32_t)(st.env_offset + env);
 
@@ -414,9 +414,10 @@ struct dcml_env {
     bool reset_done = false;
 };
 
-static int env_launch(dcml_env* e, const EnvIO& io, int what, cudaStream_t stream) {
-    const unsigned grid = (unsigned)((e->cfg.n_envs + e->epb - 1) / e->epb);
-    env_kernel<<<grid, e->block, e->smem, stream>>>(e->st, io, what, e->t);
+static int env_launch(dcml_env* e, const EnvIO& io, int what, cudaStream_t stream, long env0 = 0, long n_env = -1) {
+    if (n_env < 0) n_env = e->cfg.n_envs;
+    const unsigned grid = (unsigned)((n_env + e->epb - 1) / e->epb);
+    env_kernel<<<grid, e->block, e->smem, stream>>>(e->st, io, what, e->t, env0, env0 + n_env);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
@@ -524,6 +525,20 @@ extern "C" int dcml_env_step(dcml_env* e, const float* actions, float* obs, floa
     io.delay = delay; io.payment = payment;
     e->t += 1;
     return env_launch(e, io, ENV_STEP, (cudaStream_t)stream);
+}
+
+extern "C" int dcml_env_step_slice(dcml_env* e, const float* actions, long env0, long n_env, int first, float* obs, float* share_obs,
+                                   float* ava, float* reward, uint8_t* done, float* delay, float* payment, void* stream) {
+    int rc = env_check(e);
+    if (rc) return rc;
+    ARG_CHECK(e->reset_done, "dcml_env_step_slice before dcml_env_reset");
+    ARG_CHECK(actions && obs && share_obs && ava && reward && done && delay && payment, "null argument");
+    ARG_CHECK(env0 >= 0 && n_env > 0 && env0 + n_env <= e->cfg.n_envs, "bad slice (env0=%ld n_env=%ld of %ld)", env0, n_env, e->cfg.n_envs);
+    EnvIO io = {};
+    io.actions = actions; io.obs = obs; io.sob = share_obs; io.ava = ava; io.reward = reward; io.done = done;
+    io.delay = delay; io.payment = payment;
+    if (first) e->t += 1;
+    return env_launch(e, io, ENV_STEP, (cudaStream_t)stream, env0, n_env);
 }
 
 extern "C" int dcml_env_set_context(dcml_env* e, const double* R, const double* C, const double* worker_pr,

@@ -162,26 +162,80 @@ class DcmlVecEnv:
         return self.obs, self.share_obs_view(), self.ava
 
     # ---- the reference's host-side contract -------------------------------------------------
+    def _final(self, name, s0, s1):
+        """Rows [s0, s1) of output `name` as the DEVICE tensor the host contract hands out: dtype conversion (the reference
+        returns float64 observations / rewards and int64 flags) and the replication of the per-env share_obs row, reward and
+        done flag over the L agents (…SingleProcess.py:270, DCML_Basic_Env.py:9-13) are done on the GPU, so that the host
+        side is one pinned copy per array and no numpy pass over hundreds of megabytes."""
+        f64 = self.host_dtype == np.float64
+        dt = torch.float64 if f64 else torch.float32
+        ma, rep, n = self.multi_agent, self.replicate_share_obs and self.multi_agent, s1 - s0
+        src = getattr(self, name)[s0:s1]
+        if name == "obs":
+            x = src.to(dt)
+            return x if ma else x.reshape(n, self.L * 7)
+        if name in ("sob", "sob_bits"):
+            x = src.to(dt)
+            return x.unsqueeze(1).expand(n, self.L, x.shape[-1]).contiguous() if rep else x
+        if name == "ava":
+            return src.to(torch.int64 if f64 else torch.float32)
+        if name == "reward":
+            x = src.to(dt)
+            return x[:, None, None].expand(n, self.L, 1).contiguous() if rep else x
+        if name == "done":
+            x = src.bool()
+            return x[:, None].expand(n, self.L).contiguous() if rep else x
+        return src
+
     def _fetch(self, names):
-        """Device -> host copies into FRESH pinned tensors (torch's caching host allocator recycles the
-        blocks), so the numpy arrays handed out below are zero-copy views the caller owns, as with the
-        reference's freshly allocated arrays."""
+        """Device -> host copies into FRESH pinned tensors (torch's caching host allocator recycles the blocks), so the
+        numpy arrays handed out are zero-copy views the caller owns, as with the reference's freshly allocated arrays."""
         host = {}
         for k in names:
-            src = getattr(self, k)
-            host[k] = torch.empty(src.shape, dtype=src.dtype, pin_memory=True).copy_(src, non_blocking=True)
+            x = self._final(k, 0, self.N)
+            host[k] = torch.empty(x.shape, dtype=x.dtype, pin_memory=True).copy_(x, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return host
 
     def _host_obs(self, host, sob_key="sob"):
-        dt = self.host_dtype
-        obs = host["obs"].numpy().astype(dt, copy=False)
-        ava = host["ava"].numpy().astype(np.int64 if dt == np.float64 else dt, copy=False)
-        if not self.multi_agent:                                      # …SingleProcess.py:272-274: flat obs, one share_obs row
-            return obs.reshape(self.N, self.L * 7), host[sob_key].numpy().astype(dt, copy=False), ava
-        row = host[sob_key].numpy().astype(dt, copy=False)[:, None, :]
-        sob = np.repeat(row, self.L, axis=1) if self.replicate_share_obs else np.broadcast_to(row, (self.N, self.L, row.shape[-1]))
+        obs, sob, ava = host["obs"].numpy(), host[sob_key].numpy(), host["ava"].numpy()
+        if self.multi_agent and not self.replicate_share_obs:
+            sob = np.broadcast_to(sob[:, None, :], (self.N, self.L, sob.shape[-1]))
         return obs, sob, ava
+
+    HOST_SLICES = 4            # a large batch is stepped in this many env slices when the results go to the host
+    HOST_SLICE_MIN = 2048
+
+    def _step_sliced(self, a_dev, names):
+        """One step issued as env slices (dcml_env_step_slice): the device-to-host copies of a slice's output arrays run on
+        a copy stream under the next slice's kernel.  Same kernel, same named draws, same results as step_device."""
+        dev = self.device
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        a_dev = a_dev.to(dtype=torch.float32).reshape(self.N, self.L).contiguous()
+        n = self.HOST_SLICES
+        bounds = [self.N * k // n for k in range(n + 1)]
+        lib = _cabi.lib()
+        host = {}
+        cur, cs = torch.cuda.current_stream(dev), self._copy_stream
+        with torch.cuda.device(dev):
+            for k in range(n):
+                s0, s1 = bounds[k], bounds[k + 1]
+                _cabi.check(lib.dcml_env_step_slice(self._h, _cabi.ptr(a_dev), s0, s1 - s0, int(k == 0), _cabi.ptr(self.obs), _cabi.ptr(self.sob),
+                                                    _cabi.ptr(self.ava), _cabi.ptr(self.reward), _cabi.ptr(self.done), _cabi.ptr(self.delay),
+                                                    _cabi.ptr(self.payment), _cabi.stream_ptr()))
+                parts = {name: self._final(name, s0, s1) for name in names}
+                ev = cur.record_event()
+                with torch.cuda.stream(cs):
+                    cs.wait_event(ev)
+                    for name, x in parts.items():
+                        if name not in host:
+                            host[name] = torch.empty((self.N,) + tuple(x.shape[1:]), dtype=x.dtype, pin_memory=True)
+                        host[name][s0:s1].copy_(x, non_blocking=True)
+                        x.record_stream(cs)
+        cur.wait_stream(cs)            # later kernels overwrite the output buffers: order them behind the copies
+        cs.synchronize()
+        return host
 
     def reset(self, binary=False):
         """Env.reset through the vec-env.  ``binary=True`` is the reference's ``reset(binary=True)``
@@ -204,17 +258,17 @@ class DcmlVecEnv:
         if actions.device.type == "cpu" and not (actions.dtype == torch.float32 and actions.is_contiguous() and actions.is_pinned()):
             self._h_act.copy_(actions)             # pageable / strided / non-fp32 input: stage through pinned memory
             actions = self._h_act
-        self.step_device(actions.to(self.device, non_blocking=True))
-        host = self._fetch(("obs", "sob", "ava", "reward", "done", "delay", "payment"))
+        names = ("obs", "sob", "ava", "reward", "done", "delay", "payment")
+        if self.N >= self.HOST_SLICE_MIN:
+            host = self._step_sliced(actions.to(self.device, non_blocking=True), names)
+        else:
+            self.step_device(actions.to(self.device, non_blocking=True))
+            host = self._fetch(names)
         obs, sob, ava = self._host_obs(host)
-        dt = self.host_dtype
-        rew = host["reward"].numpy().astype(dt, copy=False)[:, None, None]
-        dones = host["done"].numpy().astype(bool)[:, None]
+        rew, dones = host["reward"].numpy(), host["done"].numpy()
         infos = _Infos(host["delay"].numpy(), host["payment"].numpy())
         if not self.multi_agent:                                      # DCML_Basic_Env.py:14-17: one reward / done per env
-            return obs, sob, rew[:, :, 0], dones, infos, ava
-        if self.replicate_share_obs:
-            rew, dones = np.repeat(rew, self.L, axis=1), np.repeat(dones, self.L, axis=1)
-        else:
-            rew, dones = np.broadcast_to(rew, (self.N, self.L, 1)), np.broadcast_to(dones, (self.N, self.L))
+            return obs, sob, rew[:, None], dones[:, None], infos, ava
+        if not self.replicate_share_obs:
+            rew, dones = np.broadcast_to(rew[:, None, None], (self.N, self.L, 1)), np.broadcast_to(dones[:, None], (self.N, self.L))
         return obs, sob, rew, dones, infos, ava

@@ -276,14 +276,88 @@ class MultiAgentTransformer(nn.Module):
             _cabi.check(_cabi.lib().matas_policy_encode(h, _cabi.ptr(obs), B, _cabi.ptr(values), _cabi.ptr(rep), _cabi.stream_ptr()))
         return values, rep
 
+    HOST_SLICES = 4            # host observations of large batches are uploaded in this many env slices (see _get_actions_host)
+    HOST_SLICE_MIN = 2048      # envs below which one copy is as good
+
+    def _get_actions_host(self, obs, ava, deterministic, stride):
+        """get_actions for HOST inputs of a large batch (the reference's contract, ma_transformer.py:304-307): the
+        observations go up in env slices on a copy stream and the encoder of slice k runs while slice k + 1 is still on
+        the bus; the availability flags, which only the decode reads, follow behind the last slice.  Same kernels and same
+        results as the one-piece path (matas_policy_encode_slice + matas_policy_decode)."""
+        B, L = obs.shape[0], self.n_agent
+        dev = self.device
+        cur = torch.cuda.current_stream(dev)
+        cs = getattr(self, "_copy_stream", None)
+        if cs is None:
+            cs = self._copy_stream = torch.cuda.Stream(device=dev)
+        obs_d = torch.empty(B, L, self.obs_dim, **self.tpdv)
+        ava_d = torch.empty(B, L, self.action_dim, **self.tpdv)
+        values = torch.empty(B, L, 1, **self.tpdv)
+        actions = torch.empty(B, L, 1, **self.tpdv)
+        logp = torch.empty(B, L, 1, **self.tpdv)
+        obs_d.record_stream(cs); ava_d.record_stream(cs)
+        cs.wait_stream(cur)
+        step = self.rollout_step
+        self.rollout_step = (self.rollout_step + 1) & 0xFFFFFFFF
+        n = self.HOST_SLICES
+        bounds = [B * k // n for k in range(n + 1)]
+        lib = _cabi.lib()
+        with self._ctx():
+            h = self.sync_weights()
+            for k in range(n):
+                s0, s1 = bounds[k], bounds[k + 1]
+                with torch.cuda.stream(cs):
+                    self._upload(obs_d[s0:s1], obs[s0:s1])
+                    ev = cs.record_event()
+                cur.wait_event(ev)
+                _cabi.check(lib.matas_policy_encode_slice(h, _cabi.ptr(obs_d[s0:s1]), s0, s1 - s0, B, _cabi.ptr(values[s0:s1]),
+                                                          _cabi.stream_ptr()))
+            with torch.cuda.stream(cs):
+                self._upload(ava_d, ava)
+                ev = cs.record_event()
+            cur.wait_event(ev)
+            _cabi.check(lib.matas_policy_decode(h, _cabi.ptr(ava_d), B, int(bool(deterministic)), int(stride), self.rollout_seed, step,
+                                                self.env_offset, None, None, _cabi.ptr(actions), _cabi.ptr(logp), _cabi.stream_ptr()))
+        return actions, logp, values
+
+    @staticmethod
+    def _upload(dst, src):
+        """dst (device fp32) = src (host) on the current stream.  The env's own host contract is float64 observations and
+        int64 flags: those go up as they are and are converted on the device (a dtype-changing copy_ would convert on the
+        host first)."""
+        if src.dtype == dst.dtype:
+            dst.copy_(src, non_blocking=True)
+        else:
+            stage = torch.empty(src.shape, dtype=src.dtype, device=dst.device)
+            stage.copy_(src, non_blocking=True)
+            dst.copy_(stage)
+
+    @staticmethod
+    def _host_f32(x, shape):
+        """x as a contiguous CPU tensor of `shape` (fp32, or the float64 / int64 of the reference's env) without a copy, or None."""
+        x = _check(x)
+        if not torch.is_tensor(x) or x.device.type != "cpu" or x.dtype not in (torch.float32, torch.float64, torch.int64):
+            return None
+        x = x.reshape(shape)
+        return x if x.is_contiguous() else None
+
     def get_actions(self, state, obs, available_actions=None, deterministic=False, stride=2, u=None, z=None):
         """ma_transformer.py:298-329 -> (actions (B,L,1), log_probs (B,L,1), v_loc (B,L,1)).
         ``u`` / ``z`` optionally inject the uniforms / normals of the stochastic branch."""
-        obs = self._dev(obs, (-1, self.n_agent, self.obs_dim))
-        B, L = obs.shape[0], self.n_agent
         if available_actions is None:
             # the reference crashes here (transformer_act.py:13-22, SURVEY 8b "Errors"); be explicit
             raise TypeError("available_actions is required by the discrete act path")
+        if u is None and z is None and self.device.type == "cuda":
+            oh = self._host_f32(obs, (-1, self.n_agent, self.obs_dim))
+            ah = None if oh is None else self._host_f32(available_actions, (oh.shape[0], self.n_agent, self.action_dim))
+            if oh is not None and ah is not None and oh.shape[0] >= self.HOST_SLICE_MIN:
+                actions, logp, values = self._get_actions_host(oh, ah, deterministic, stride)
+                if self.action_type == "Discrete":
+                    actions = actions.long()
+                actions, logp = self._out(actions, logp)
+                return actions, logp, values
+        obs = self._dev(obs, (-1, self.n_agent, self.obs_dim))
+        B, L = obs.shape[0], self.n_agent
         ava = self._dev(available_actions, (B, L, self.action_dim))
         u = None if u is None else self._dev(u, (B, L))
         z = None if z is None else self._dev(z, (B, 2))
