@@ -254,6 +254,13 @@ class MultiAgentTransformer(nn.Module):
         torch.cuda.current_stream(self.device).synchronize()
         return hs if len(hs) > 1 else hs[0]
 
+    def to_host(self, *xs):
+        """Device tensors -> pinned host tensors with ONE stream synchronisation (what a host-side caller that wants numpy
+        values, like the reference's runner with ``_t2n``, should use instead of one ``.cpu()`` per tensor)."""
+        hs = tuple(torch.empty(x.shape, dtype=x.dtype, pin_memory=True).copy_(x, non_blocking=True) for x in xs)
+        torch.cuda.current_stream(self.device).synchronize()
+        return hs if len(hs) > 1 else hs[0]
+
     # ---- the reference's methods ------------------------------------------------------------
     def get_values(self, state, obs, available_actions=None):
         """ma_transformer.py:331-339 -> v_loc (B, L, 1) on the model device."""

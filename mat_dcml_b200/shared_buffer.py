@@ -12,6 +12,7 @@ Differences, all layout-only: arrays are fp32 torch tensors on the GPU instead o
 (T+1, N, L, 1, 1) zeros.  ``compute_returns`` is the GAE kernel (csrc/gae.cu).
 """
 import ctypes
+import warnings
 
 import numpy as np
 import torch
@@ -21,6 +22,18 @@ from . import _cabi
 
 def _shape(space):
     return space.shape if space.__class__.__name__ == "Box" else space
+
+
+def _as_tensor(x):
+    """torch view of a host array without the "not writable" warning: env outputs may be read-only broadcast views (the
+    share_obs row / reward replicated over the agents), and the buffer only ever reads them."""
+    if torch.is_tensor(x):
+        return x
+    if isinstance(x, np.ndarray) and not x.flags.writeable:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore", UserWarning)
+            return torch.as_tensor(x)
+    return torch.as_tensor(x)
 
 
 def _guarded(name):
@@ -41,6 +54,10 @@ class SharedReplayBuffer:
     action_log_probs = _guarded("action_log_probs")
     value_preds = _guarded("value_preds")
     available_actions = _guarded("available_actions")
+    rewards = _guarded("rewards")
+    masks = _guarded("masks")
+    bad_masks = _guarded("bad_masks")
+    active_masks = _guarded("active_masks")
 
     def __init__(self, args, num_agents, obs_space, cent_obs_space, act_space, env_name, device="cuda"):
         self.episode_length, self.n_rollout_threads = args.episode_length, args.n_rollout_threads
@@ -91,7 +108,7 @@ class SharedReplayBuffer:
     def _put(self, name, index, src):
         """array[index] = src.  Pinned fp32 host sources are uploaded on the side stream."""
         dst = self.__dict__["_t_" + name][index]
-        src = torch.as_tensor(src) if not torch.is_tensor(src) else src
+        src = _as_tensor(src)
         if (src.device.type == "cpu" and src.dtype == torch.float32 and src.is_contiguous() and src.numel() == dst.numel()
                 and src.is_pinned()):
             cs = self._copy_stream
@@ -111,18 +128,19 @@ class SharedReplayBuffer:
         s = self.step
         self._inflight = [(e, h) for e, h in self._inflight if not e.query()]      # drop finished uploads
         self._held = []
-        so = torch.as_tensor(share_obs) if not torch.is_tensor(share_obs) else share_obs
+        so = _as_tensor(share_obs)
         self._put("_share_obs", s + 1, so[:, 0, :] if so.dim() == 3 else so)
         self._put("obs", s + 1, obs)
         self._put("actions", s, actions)
         self._put("action_log_probs", s, action_log_probs)
         self._put("value_preds", s, value_preds)
-        self._bcast(self.rewards[s], rewards)
-        self._bcast(self.masks[s + 1], masks)
+        raw = self.__dict__                        # unguarded tensors: _bcast orders its own writes
+        self._bcast(raw["_t_rewards"][s], rewards)
+        self._bcast(raw["_t_masks"][s + 1], masks)
         if bad_masks is not None:
-            self._bcast(self.bad_masks[s + 1], bad_masks)
+            self._bcast(raw["_t_bad_masks"][s + 1], bad_masks)
         if active_masks is not None:
-            self._bcast(self.active_masks[s + 1], active_masks)
+            self._bcast(raw["_t_active_masks"][s + 1], active_masks)
         if available_actions is not None:
             self._put("available_actions", s + 1, available_actions)
         if self._held:
@@ -133,7 +151,21 @@ class SharedReplayBuffer:
         self.step = (self.step + 1) % self.episode_length
 
     def _bcast(self, dst, src):
-        src = torch.as_tensor(src) if not torch.is_tensor(src) else src
+        """dst (N, L, 1) = src, given per env (N,) or per agent (N, L, 1).  Host sources are staged through a small pinned
+        tensor and uploaded on the side stream (a pageable source would make the copy synchronous with the host)."""
+        src = _as_tensor(src)
+        if src.device.type == "cpu":
+            pin = torch.empty(src.shape, dtype=torch.float32, pin_memory=True)
+            pin.copy_(src)
+            cs = self._copy_stream
+            cs.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(cs):
+                d = pin.to(self.device, non_blocking=True)
+                d = d.reshape(-1, 1, 1).expand_as(dst) if d.numel() == dst.shape[0] else d.reshape(dst.shape)
+                dst.copy_(d)
+            self._held.append(pin)
+            self._dirty = True
+            return
         src = src.to(device=self.device, dtype=torch.float32)
         if src.numel() == dst.shape[0]:
             src = src.reshape(-1, 1, 1).expand_as(dst)
