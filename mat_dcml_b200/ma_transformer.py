@@ -169,7 +169,10 @@ class MultiAgentTransformer(nn.Module):
     def flat_grad(self, zero=False):
         """One flat fp32 gradient buffer; every parameter's .grad is a view into it."""
         if self._flat_grad is None:
-            self._flat_grad = torch.zeros_like(self._flat)
+            # four spare slots behind the gradient carry the loss denominators / numerators of a sharded minibatch through
+            # the gradient all-reduce (mat_trainer.ppo_update); flat_grad() is the gradient itself
+            self._flat_grad_comm = torch.zeros(self._flat.numel() + 4, dtype=torch.float32, device=self._flat.device)
+            self._flat_grad = self._flat_grad_comm[:self._flat.numel()]
             off = 0
             for p in self.parameters():
                 k = p.numel()
@@ -178,6 +181,11 @@ class MultiAgentTransformer(nn.Module):
         elif zero:
             self._flat_grad.zero_()
         return self._flat_grad
+
+    def flat_grad_comm(self):
+        """The gradient buffer with its four spare slots (see flat_grad)."""
+        self.flat_grad()
+        return self._flat_grad_comm
 
     def zero_std(self):
         self.decoder.zero_std()

@@ -58,23 +58,29 @@ class MATTrainer:
             x = torch.from_numpy(x)
         return x.to(**self.tpdv)
 
-    def _vn_update(self, returns):
-        """ValueNorm.update over the GLOBAL minibatch (valuenorm.py:39-56)."""
+    def _vn_update(self, returns, moments=None):
+        """ValueNorm.update over the GLOBAL minibatch (valuenorm.py:39-56).  ``moments`` = (sum, sum of squares, count) of the
+        global minibatch's returns when the caller has already reduced them (train() does it once per epoch for all
+        minibatches: they depend on the returns and the permutation only)."""
         if _world() == 1:
             self.value_normalizer.update(returns)
             return
-        m = torch.stack([returns.sum(), (returns ** 2).sum(), torch.tensor(float(returns.numel()), **self.tpdv)])
-        _allsum(m)
+        if moments is not None:
+            m = moments
+        else:
+            m = torch.stack([returns.sum(), (returns ** 2).sum(), torch.tensor(float(returns.numel()), **self.tpdv)])
+            _allsum(m)
         vn, w = self.value_normalizer, self.value_normalizer.beta
         vn.stats[0:1].mul_(w).add_((m[0] / m[2]) * (1.0 - w))
         vn.stats[1:2].mul_(w).add_((m[1] / m[2]) * (1.0 - w))
         vn.stats[2].mul_(w).add_(1.0 * (1.0 - w))
 
-    def cal_value_loss(self, values, value_preds_batch, return_batch, active_masks_batch):
-        """mat_trainer.py:54-94"""
+    def cal_value_loss(self, values, value_preds_batch, return_batch, active_masks_batch, vn_moments=None, numerator_only=False):
+        """mat_trainer.py:54-94.  ``numerator_only``: the masked SUM of the loss without the division by the active count
+        (ppo_update divides the all-reduced gradient once instead, see there)."""
         value_pred_clipped = value_preds_batch + (values - value_preds_batch).clamp(-self.clip_param, self.clip_param)
         if self._use_valuenorm:
-            self._vn_update(return_batch)
+            self._vn_update(return_batch, vn_moments)
             error_clipped = self.value_normalizer.normalize(return_batch) - value_pred_clipped
             error_original = self.value_normalizer.normalize(return_batch) - values
         else:
@@ -85,6 +91,8 @@ class MATTrainer:
         else:
             vl_clipped, vl_original = mse_loss(error_clipped), mse_loss(error_original)
         value_loss = torch.max(vl_original, vl_clipped) if self._use_clipped_value_loss else vl_original
+        if numerator_only:
+            return (value_loss * active_masks_batch).sum() if self._use_value_active_masks else value_loss.sum()
         if self._use_value_active_masks:
             return (value_loss * active_masks_batch).sum() / self._active_sum(active_masks_batch)
         return value_loss.sum() / self._count(value_loss)
@@ -95,10 +103,12 @@ class MATTrainer:
     def _count(self, x):
         return _allsum(torch.tensor(float(x.numel()), **self.tpdv))
 
-    def ppo_update(self, sample):
-        """mat_trainer.py:96-156.  Under torch.distributed every rank passes its local minibatch; the
-        losses are normalised by global denominators and the flat gradient is summed over ranks, so all
-        replicas take the step the reference would take on the concatenated batch."""
+    def ppo_update(self, sample, vn_moments=None):
+        """mat_trainer.py:96-156.  Under torch.distributed every rank passes its local minibatch and all replicas take the
+        step the reference would take on the concatenated batch, with ONE collective: the three loss terms share one
+        denominator (the global active count, or the global element count), so each rank back-propagates the un-normalised
+        numerators, the flat gradient travels with the local count and the three numerators appended, and the sum is
+        divided once (``vn_moments``: the ValueNorm batch moments of the global minibatch, reduced per epoch by train())."""
         share_obs_batch, obs_batch, rnn_states_batch, rnn_states_critic_batch, actions_batch, \
             value_preds_batch, return_batch, masks_batch, active_masks_batch, old_action_log_probs_batch, \
             adv_targ, available_actions_batch = sample
@@ -107,22 +117,35 @@ class MATTrainer:
         return_batch, active_masks_batch = self._t(return_batch), self._t(active_masks_batch)
         model = self.policy.transformer
         model.flat_grad(zero=True)                                   # optimizer.zero_grad()
+        fused = _world() > 1 and self._use_policy_active_masks == self._use_value_active_masks
+        one = torch.ones((), **self.tpdv)
+        den = one if fused else self._active_sum(active_masks_batch)
         values, action_log_probs, dist_entropy = self.policy.evaluate_actions(
             share_obs_batch, obs_batch, rnn_states_batch, rnn_states_critic_batch, actions_batch, masks_batch,
-            available_actions_batch, active_masks_batch, active_denominator=self._active_sum(active_masks_batch))
+            available_actions_batch, active_masks_batch, active_denominator=den)
+        if fused and not self._use_policy_active_masks:
+            dist_entropy = dist_entropy * float(action_log_probs.shape[0])       # .mean() back to a sum
         imp_weights = torch.exp(action_log_probs - old_action_log_probs_batch)
         surr1 = imp_weights * adv_targ
         surr2 = torch.clamp(imp_weights, 1.0 - self.clip_param, 1.0 + self.clip_param) * adv_targ
         if self._use_policy_active_masks:
-            policy_loss = (-torch.sum(torch.min(surr1, surr2) * active_masks_batch, dim=-1, keepdim=True)).sum() \
-                / self._active_sum(active_masks_batch)
+            policy_loss = (-torch.sum(torch.min(surr1, surr2) * active_masks_batch, dim=-1, keepdim=True)).sum() / den
         else:
-            policy_loss = -torch.sum(torch.min(surr1, surr2), dim=-1, keepdim=True).sum() / self._count(surr1)
-        value_loss = self.cal_value_loss(values, value_preds_batch, return_batch, active_masks_batch)
+            policy_loss = -torch.sum(torch.min(surr1, surr2), dim=-1, keepdim=True).sum() / (one if fused else self._count(surr1))
+        value_loss = self.cal_value_loss(values, value_preds_batch, return_batch, active_masks_batch, vn_moments, numerator_only=fused)
         loss = policy_loss - dist_entropy * self.entropy_coef + value_loss * self.value_loss_coef
         loss.backward()                                              # CUDA backward -> flat gradient
-        if _world() > 1:
-            dist.all_reduce(model.flat_grad(), op=dist.ReduceOp.SUM)  # the one collective of the update
+        if fused:
+            # the one collective of the update: [flat gradient | local denominator, policy / value / entropy numerators]
+            comm = model.flat_grad_comm()
+            cnt = active_masks_batch.sum() if self._use_policy_active_masks else torch.tensor(float(surr1.numel()), **self.tpdv)
+            comm[-4:] = torch.stack([cnt.detach(), policy_loss.detach(), value_loss.detach(), dist_entropy.detach()])
+            dist.all_reduce(comm, op=dist.ReduceOp.SUM)
+            inv = 1.0 / comm[-4]
+            comm[:-4].mul_(inv)                                      # = model.flat_grad(): gradient of the global-batch loss
+            policy_loss, value_loss, dist_entropy = comm[-3] * inv, comm[-2] * inv, comm[-1] * inv
+        elif _world() > 1:
+            dist.all_reduce(model.flat_grad(), op=dist.ReduceOp.SUM)
         opt = self.policy.optimizer
         if hasattr(opt, "clip_and_step"):                            # FlatAdam: clip + Adam in two launches
             grad_norm = opt.clip_and_step(self.max_grad_norm if self._use_max_grad_norm else 0.0)
@@ -136,14 +159,29 @@ class MATTrainer:
         return value_loss, grad_norm, policy_loss, dist_entropy, grad_norm, imp_weights
 
     def normalize_advantages(self, adv, active):
-        """mat_trainer.py:193-197: (adv - nanmean) / (nanstd + 1e-5) over active entries of the GLOBAL batch."""
-        m = torch.stack([(adv * active).sum(), active.sum()]).double()
+        """mat_trainer.py:193-197: (adv - nanmean) / (nanstd + 1e-5) over active entries of the GLOBAL batch; one collective
+        (count, sum, sum of squares in float64) when the batch is sharded."""
+        if _world() == 1:
+            m = torch.stack([(adv * active).sum(), active.sum()]).double()
+            mean = m[0] / m[1]
+            std = torch.sqrt((((adv.double() - mean) ** 2) * active).sum() / m[1])
+            return ((adv - mean.float()) / (std.float() + 1e-5))
+        a = adv.double()
+        m = torch.stack([(a * active).sum(), (a * a * active).sum(), active.sum().double()])
         _allsum(m)
-        mean = m[0] / m[1]
-        v = (((adv.double() - mean) ** 2) * active).sum().reshape(1)
-        _allsum(v)
-        std = torch.sqrt(v[0] / m[1])
+        mean = m[0] / m[2]
+        std = torch.sqrt((m[1] / m[2] - mean * mean).clamp(min=0.0))
         return ((adv - mean.float()) / (std.float() + 1e-5))
+
+    def minibatch_moments(self, samples):
+        """ValueNorm batch moments (sum, sum of squares, count of the returns, valuenorm.py:45-46) of every minibatch of an
+        epoch over the GLOBAL batch: one collective per epoch instead of one per minibatch."""
+        if _world() == 1 or not self._use_valuenorm:
+            return [None] * len(samples)
+        m = torch.stack([torch.stack([self._t(s[6]).sum(), (self._t(s[6]) ** 2).sum(),
+                                      torch.tensor(float(self._t(s[6]).numel()), **self.tpdv)]) for s in samples])
+        _allsum(m)
+        return list(m)
 
     def train(self, buffer):
         """mat_trainer.py:158-217"""
@@ -154,8 +192,12 @@ class MATTrainer:
             next_values = self.policy.get_values(None, buffer.obs[-1].reshape(-1, buffer.obs.shape[-1]), None, None)
             buffer.compute_returns(next_values.reshape(buffer.value_preds[-1].shape), self.value_normalizer)
             advantages = self.normalize_advantages(buffer.advantages, buffer.active_masks[:-1])
-            for sample in buffer.feed_forward_generator_transformer(advantages, self.num_mini_batch):
-                vl, cgn, pl, ent, agn, ratio = self.ppo_update(sample)
+            samples = buffer.feed_forward_generator_transformer(advantages, self.num_mini_batch)
+            if _world() > 1:
+                samples = list(samples)                              # the epoch's minibatches: their ValueNorm moments in one collective
+                moments = self.minibatch_moments(samples)
+            for k, sample in enumerate(samples):
+                vl, cgn, pl, ent, agn, ratio = self.ppo_update(sample, moments[k] if _world() > 1 else None)
                 with torch.no_grad():
                     acc += torch.stack([vl.detach().double(), pl.detach().double(), ent.detach().double(),
                                         torch.as_tensor(agn, device=self.device).double(), torch.as_tensor(cgn, device=self.device).double(),
@@ -163,7 +205,8 @@ class MATTrainer:
         keys = ("value_loss", "policy_loss", "dist_entropy", "actor_grad_norm", "critic_grad_norm", "ratio")
         info = dict(zip(keys, acc.tolist()))
         n = self.ppo_epoch * self.num_mini_batch
-        if _world() > 1:     # each rank logged its share of the global losses (global denominators)
+        if _world() > 1 and self._use_policy_active_masks != self._use_value_active_masks:
+            # (mixed denominators take the per-term collectives: each rank logged its share of the global losses)
             t = torch.tensor([info["value_loss"], info["policy_loss"], info["dist_entropy"]], dtype=torch.float64, device=self.device)
             _allsum(t)
             info["value_loss"], info["policy_loss"], info["dist_entropy"] = t.tolist()

@@ -24,7 +24,7 @@ rows = slice(rank * (M // world) * L, (rank + 1) * (M // world) * L)
 f = lambda k, dt=np.float32: g[k][rows].astype(dt)
 sample = (None, f("obs"), None, None, f("actions"), f("value_preds"), f("returns"), None, f("active"), f("old_logp"), f("adv"), f("ava"))
 vl, gn, pl, ent, _, ratio = tr.ppo_update(sample)
-tot = torch.stack([vl.detach(), pl.detach(), ent.detach()]); dist.all_reduce(tot)   # each rank holds its share of the global losses
+tot = torch.stack([vl.detach(), pl.detach(), ent.detach()])          # every rank holds the global losses (they ride on the gradient all-reduce)
 ok = abs(tot[0].item() - float(g["value_loss"])) < 1e-4 * max(1, abs(float(g["value_loss"]))) and \
      abs(tot[1].item() - float(g["policy_loss"])) < 1e-4 and abs(tot[2].item() - float(g["entropy"])) < 1e-4 and \
      abs(float(gn) - float(g["grad_norm"])) < 2e-3 * float(g["grad_norm"])

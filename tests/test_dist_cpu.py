@@ -43,6 +43,15 @@ def _worker(rank, world, port, q):
         e1 = ref_vn.normalize(ret) - val
         e2 = ref_vn.normalize(ret) - (vpred + (val - vpred).clamp(-0.2, 0.2))
         want = (torch.max(po.huber(e1, 10.0), po.huber(e2, 10.0)) * am).sum() / am.sum()
+        # the same with the ValueNorm moments of the epoch's minibatches reduced up front (what train() does): one collective
+        tr2 = MATTrainer(args, None, 5, device=torch.device("cpu"))
+        mom = tr2.minibatch_moments([(None,) * 6 + (ret[half],) + (None,) * 5])
+        vl2 = tr2.cal_value_loss(val[half], vpred[half], ret[half], am[half], vn_moments=mom[0], numerator_only=True)
+        cnt = am[half].sum()
+        both = torch.stack([vl2, cnt])
+        dist.all_reduce(both)
+        assert abs(float(both[0] / both[1]) - float(want)) < 1e-5 * max(1.0, abs(float(want)))
+        np.testing.assert_allclose(tr2.value_normalizer.stats.numpy(), ref_vn.stats(), rtol=1e-5)
         nadv = tr.normalize_advantages(adv[:, rank * 2:rank * 2 + 2], act[:, rank * 2:rank * 2 + 2])
         want_adv = po.normalize_advantages(adv.numpy(), torch.cat([act, act[:1]]).numpy())[:, rank * 2:rank * 2 + 2]
         q.put((rank, float(tot), float(want), tr.value_normalizer.stats.numpy().copy(), ref_vn.stats(),
