@@ -122,7 +122,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     ring.prefetch();
     if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[512 + i] = b.w[lay::ENC_H3 + i];
     const int row = c.row, half = c.half;
-    float* sRed = s.sSmall;              // [2][TR][2] LayerNorm partials, [512 + ...) head.3
+    float* sRed = s.sSmall;              // [TR][2] float2 LayerNorm partials, [512 + ...) head.3, [640 + ...) head dot partials
     float* sTrow = s.sT + row * XS + half * 32;
     Stage st = {c, ring};
 
@@ -213,9 +213,10 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
             float d = 0.f;
 #pragma unroll
             for (int i = 0; i < 32; ++i) d = fmaf(v[i], w3[i], d);
-            sRed[row * 2 + half] = d;
+            float* sDot = s.sSmall + 640;                         // clear of the LayerNorm exchange [0, 512) other rows may still read
+            sDot[row * 2 + half] = d;
             __syncthreads();                                      // also: the rep store above has drained sT
-            if (half == 0 && row < n_valid) values[tile0 + row] = sRed[row * 2] + sRed[row * 2 + 1] + s.sSmall[512 + 64];
+            if (half == 0 && row < n_valid) values[tile0 + row] = sDot[row * 2] + sDot[row * 2 + 1] + s.sSmall[512 + 64];
         }
         // ---- cross-attention queries from obs_rep (operand still holds it) ------------------------------
         const int n_q = for_decode ? 4 : 2;

@@ -269,23 +269,21 @@ __device__ __forceinline__ void global_to_tile(float* __restrict__ sT, const flo
     }
 }
 
-// LayerNorm over a 64-column row held by two partner threads (32 columns each): two exchanges through
-// sRed[2][TR][2].  Contains two __syncthreads().  Returns rstd; v becomes x_hat (before the affine map).
+// LayerNorm over a 64-column row held by two partner threads (32 columns each): ONE exchange of (sum, sum of squares)
+// through sRed[TR][2] float2 and ONE __syncthreads(); var = E[x^2] - mean^2 (residual sums of O(1) rows: the cancellation
+// costs a few ulp of the variance).  Two calls must be separated by a CTA barrier (every GEMM stage has one).
+// Returns rstd; v becomes x_hat (before the affine map).
 __device__ __forceinline__ float layernorm_pair(float (&v)[32], float* __restrict__ sRed, int row, int half) {
-    float s = 0.f;
+    float s = 0.f, q = 0.f;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) s += v[i];
-    sRed[row * 2 + half] = s;
+    for (int i = 0; i < 32; ++i) { s += v[i]; q = fmaf(v[i], v[i], q); }
+    reinterpret_cast<float2*>(sRed)[row * 2 + half] = make_float2(s, q);
     __syncthreads();
-    const float mean = (sRed[row * 2] + sRed[row * 2 + 1]) * (1.0f / 64.0f);
-    float q = 0.f;
+    const float4 a = *reinterpret_cast<const float4*>(sRed + row * 4);
+    const float mean = (a.x + a.z) * (1.0f / 64.0f);
+    const float rs = rsqrtf(fmaxf((a.y + a.w) * (1.0f / 64.0f) - mean * mean, 0.f) + 1e-5f);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) { v[i] -= mean; q = fmaf(v[i], v[i], q); }
-    sRed[2 * TR + row * 2 + half] = q;
-    __syncthreads();
-    const float rs = rsqrtf((sRed[2 * TR + row * 2] + sRed[2 * TR + row * 2 + 1]) * (1.0f / 64.0f) + 1e-5f);
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] *= rs;
+    for (int i = 0; i < 32; ++i) v[i] = (v[i] - mean) * rs;
     return rs;
 }
 
