@@ -16,7 +16,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 # env.cu / gae.cu restate float arithmetic whose branches / bits depend on unfused rounding
-EXTRA_FLAGS = {"env.cu": ["-fmad=false"], "gae.cu": ["-fmad=false"]}
+EXTRA_FLAGS = {"env.cu": ["-fmad=false", "-maxrregcount=64"], "gae.cu": ["-fmad=false"]}
 
 
 def _sources():

@@ -61,37 +61,73 @@ struct EnvIO {
     int binary;            // reset(binary=True): share_obs rows start with the 32 + 32 bits of R and C (then width + 62 wide)
 };
 
+// The n-th geometric-retry uniform of a worker (stream RETRY: block n / 4, lane n % 4), consumed as the comparison
+// u < Pr.  u = m 2^-24 with m the draw's top 24 bits, so u < Pr  <=>  m < ceil(Pr 2^24): an integer compare, no float64
+// conversion per draw.  Two Philox blocks are kept: the one being consumed and the next, which `ensure()` generates at
+// points where the warp is converged (loop entry, every fourth trip) -- the lanes of a warp sit at different draw
+// indices, and a refill inside the per-draw path would make the whole warp pay a Philox call on almost every trip.
 struct RetryStream {
-    uint32_t env, step, tag;
+    uint32_t env, step, tag, thr;
     uint64_t seed;
-    uint4 cur;
-    int k;
-    __device__ void init(uint32_t env_, uint32_t step_, int w, uint64_t seed_) {
-        env = env_; step = step_; tag = rng_tag(S_RETRY, (uint32_t)w); seed = seed_; k = 0;
+    uint4 b0, b1;
+    int k, blk;
+    bool have1;
+    __device__ void init(uint32_t env_, uint32_t step_, int w, uint64_t seed_, double Pr) {
+        env = env_; step = step_; tag = rng_tag(S_RETRY, (uint32_t)w); seed = seed_; k = 0; blk = 0; have1 = false;
+        thr = (uint32_t)ceil(Pr * 16777216.0);
+        b0 = philox4x32(env, step, tag, 0u, seed);
     }
-    __device__ double next() {
-        if ((k & 3) == 0) cur = philox4x32(env, step, tag, (uint32_t)(k >> 2), seed);
-        const double u = u01d(lane_of(cur, k & 3));
-        ++k;
-        return u;
+    __device__ void ensure() {
+        if (!have1) { b1 = philox4x32(env, step, tag, (uint32_t)(blk + 1), seed); have1 = true; }
+    }
+    __device__ void advance() { ensure(); b0 = b1; ++blk; have1 = false; }
+    // Consume draws up to and including the first one that is >= Pr (`while U < Pr: n++`, WORKER:54-56,100-102) and return
+    // the number of draws that were below: a whole Philox block is compared at once and the first failure found with a
+    // find-first-set, so a geometric retry costs one short trip per FOUR draws instead of a dependent chain per draw.
+    // At most `room` retries are counted (the RETRY_CAP guard of the per-draw loop, which stops after the draw that
+    // reaches the cap).
+    __device__ int run(int room) {
+        int c = 0;
+        for (;;) {
+            const uint32_t lt = (uint32_t)((b0.x >> 8) < thr) | ((uint32_t)((b0.y >> 8) < thr) << 1) |
+                                ((uint32_t)((b0.z >> 8) < thr) << 2) | ((uint32_t)((b0.w >> 8) < thr) << 3);
+            const int lane = k & 3;
+            const uint32_t fail = (~lt >> lane) & (0xFu >> lane);       // bit i: draw lane + i is >= Pr
+            if (fail) {
+                const int f = __ffs(fail) - 1;
+                if (c + f < room) {
+                    c += f; k += f + 1;
+                    if (lane + f == 3) advance();
+                    return c;
+                }
+            }
+            const int take = fail ? room - c : min(4 - lane, room - c); // successes taken from this block
+            if (c + take >= room) {                                     // the cap: the draw that reached it was the last one consumed
+                k += take;
+                if (((k - 1) & 3) == 3 && take > 0) advance();
+                return room;
+            }
+            c += take; k += take;
+            advance();
+        }
     }
 };
 
 struct ProcOut { double delay, price0; int tp0, nslots; };
 
 // Worker.process, DCML_Worker_TIMESLOT_MultiProcess.py:46-112; lw = this worker's 20 local slots
-__device__ ProcOut process(const double* lw, double Pr, double r, double c, int arrive, RetryStream& rs, double DATA_RATE) {
+__device__ ProcOut process(const double* lw, double r, double c, int arrive, RetryStream& rs, double DATA_RATE) {
     ProcOut o;
     double cost = ceil((9.0 * r - 3.0) * c) / FREQUENCY;                    // :49-50
-    int n = 1;
-    while (rs.next() < Pr && n < RETRY_CAP) ++n;                            // :54-56
+    rs.ensure();
+    int n = 1 + rs.run(RETRY_CAP - 1);                                      // :54-56
     const double t_down = ((ceil((r + 1.0) * c) * 1.0 * 4.0) / DATA_RATE + 0.001) * (double)n;   // :60
     double price = floor(t_down) * 0.1;                                     // :65
     const int slot = (int)floor(t_down + (double)arrive);                   // :66
     int tp = slot % PERIOD;                                                 // :67-69
     int finish = slot;
     double avail = 0.0;
-    const double frac = fmod(t_down, 1.0);
+    const double frac = t_down - floor(t_down);                             // t_down % 1 (exact: t_down > 0)
     if (frac > lw[tp]) cost += frac - lw[tp];                               // :85-86
     o.price0 = price; o.tp0 = tp;
     int nslots = 0;
@@ -102,7 +138,9 @@ __device__ ProcOut process(const double* lw, double Pr, double r, double c, int 
         avail += fr;
         ++nslots; ++finish; ++tp;
         if (tp > PERIOD - 1) tp -= PERIOD;
-        while (rs.next() < Pr && n < RETRY_CAP) ++n;
+        rs.ensure();
+        if (n < RETRY_CAP) n += rs.run(RETRY_CAP - n);
+        else rs.run(0);
         t_up = ((ceil(r) * 1.0 * 4.0) / DATA_RATE + 0.001) * (double)n + 0.02;
     }
     o.nslots = nslots;
@@ -200,9 +238,9 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
         const bool runs = active && (!n0 || w == 0);                       // :83 vs :106-111
         if (runs) {
             RetryStream rs;
-            rs.init(genv, t, w, st.seed);
+            rs.init(genv, t, w, st.seed, st.Pr[env * W + w]);
             const double r = ceil(sc[2] / (double)si[1]);                  // Master.get_workload, DCML_Master.py:39-40
-            po = process(my_lw, st.Pr[env * W + w], r, sc[3], si[3], rs, st.shannon ? st.rate_down[env * W + w] : DATA_RATE);
+            po = process(my_lw, r, sc[3], si[3], rs, st.shannon ? st.rate_down[env * W + w] : DATA_RATE);
             e_d[w] = po.delay;
             // Worker.process :111 redraw the workload (step-t jitter stream)
             for (int blk = 0; blk < 5; ++blk) {
