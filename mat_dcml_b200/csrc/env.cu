@@ -181,6 +181,32 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
     int* s_i = reinterpret_cast<int*>(s_sel + blockDim.x);              // [epb][8] int scalars
     uint8_t* s_dis = reinterpret_cast<uint8_t*>(s_i + (size_t)epb * 8); // [threads]
 
+    // reductions over the threads of one env (tpe / 32 whole warps): warp shuffles, then the env's warp partials through
+    // shared memory; every thread of the CTA takes part (two CTA barriers)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwe = tpe >> 5, w0e = le * nwe;
+    double* s_red = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(s_dis + blockDim.x) + 15) & ~(uintptr_t)15);   // [warps][4]
+    auto env_sum4 = [&](double (&v)[4]) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            for (int o = 16; o; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+        if (lane == 0) { s_red[warp * 4] = v[0]; s_red[warp * 4 + 1] = v[1]; s_red[warp * 4 + 2] = v[2]; s_red[warp * 4 + 3] = v[3]; }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = 0.0;
+        for (int j = 0; j < nwe; ++j) { v[0] += s_red[(w0e + j) * 4]; v[1] += s_red[(w0e + j) * 4 + 1]; v[2] += s_red[(w0e + j) * 4 + 2]; v[3] += s_red[(w0e + j) * 4 + 3]; }
+        __syncthreads();
+    };
+    // count of `pred` over the env, and the count over the env's threads BEFORE this one
+    auto env_count = [&](bool pred, int& before) -> int {
+        const unsigned m = __ballot_sync(0xffffffffu, pred);
+        int* s_cnt = reinterpret_cast<int*>(s_red);
+        if (lane == 0) s_cnt[warp] = __popc(m);
+        __syncthreads();
+        int tot = 0; before = __popc(m & ((1u << lane) - 1u));
+        for (int j = 0; j < nwe; ++j) { const int c = s_cnt[w0e + j]; tot += c; if (w0e + j < warp) before += c; }
+        __syncthreads();
+        return tot;
+    };
     double* my_lw = s_lw + (size_t)threadIdx.x * LWS;
     double* sc = s_sc + le * 8;     // 0 final delay, 1 payment, 2 R, 3 C
     int* si = s_i + le * 8;         // 0 N, 1 K, 2 n0 flag, 3 arrive, 4 kdis, 5 done
@@ -214,33 +240,43 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
                 my_lw[i] = v.x; my_lw[i + 1] = v.y;
             }
         }
-        __syncthreads();
-        if (env_ok && w == 0) {
-            float sum = 0.f;
-            for (int i = 0; i < W; ++i) sum = __fadd_rn(sum, e_sel[i]);
-            int N = (int)sum;                                              // :71
-            const float ratio = io.actions[env * L + W];
-            int K = st.fixed ? (int)floor((double)N * 0.7)                 // :61
-                             : (int)ceilf(__fmul_rn((float)N, ratio));     // :72 (fp32 product of fp32 actions)
-            si[2] = N == 0 || st.standalone;                               // :81
+        // N = int(sum(action[:-1])) (:71).  The reference adds fp32 values in order; the policy's selections are exactly 0 / 1,
+        // for which a count is that sum -- anything else takes the in-order sum by one thread
+        const float selv = active ? e_sel[w] : 0.f;
+        const bool odd = selv != 0.f && selv != 1.f;
+        int before_;
+        int N = env_count(selv == 1.f, before_);
+        if (__syncthreads_or(odd)) {
+            if (env_ok && w == 0) {
+                float sum = 0.f;
+                for (int i = 0; i < W; ++i) sum = __fadd_rn(sum, e_sel[i]);
+                si[0] = (int)sum;
+            }
+            __syncthreads();
+            if (env_ok) N = si[0];
+        }
+        const double Rv = env_ok ? st.R[env] : 1.0, Cv = env_ok ? st.C[env] : 1.0;
+        const int arr = env_ok ? st.arrive[env] : 0;
+        int K;
+        bool n0 = false;
+        {
+            const float ratio = env_ok ? io.actions[env * L + W] : 0.f;
+            K = st.fixed ? (int)floor((double)N * 0.7)                     // :61
+                         : (int)ceilf(__fmul_rn((float)N, ratio));         // :72 (fp32 product of fp32 actions)
+            n0 = env_ok && (N == 0 || st.standalone);                      // :81
             N = min(max(N, 1), W);
             K = min(max(K, 1), N);
-            if (si[2]) K = 1;                                              // :82 update_strategy(K=1,N=1)
-            si[0] = N; si[1] = K;
-            sc[0] = 0.0;
-            sc[2] = st.R[env]; sc[3] = st.C[env];
-            si[3] = st.arrive[env];
+            if (n0) K = 1;                                                 // :82 update_strategy(K=1,N=1)
         }
-        __syncthreads();
-        const bool n0 = env_ok && si[2];
+        if (env_ok && w == 0) sc[0] = 0.0;
         ProcOut po;
         po.delay = 0.0; po.price0 = 0.0; po.tp0 = 0; po.nslots = 0;
         const bool runs = active && (!n0 || w == 0);                       // :83 vs :106-111
         if (runs) {
             RetryStream rs;
             rs.init(genv, t, w, st.seed, st.Pr[env * W + w]);
-            const double r = ceil(sc[2] / (double)si[1]);                  // Master.get_workload, DCML_Master.py:39-40
-            po = process(my_lw, r, sc[3], si[3], rs, st.shannon ? st.rate_down[env * W + w] : DATA_RATE);
+            const double r = ceil(Rv / (double)K);                         // Master.get_workload, DCML_Master.py:39-40
+            po = process(my_lw, r, Cv, arr, rs, st.shannon ? st.rate_down[env * W + w] : DATA_RATE);
             e_d[w] = po.delay;
             // Worker.process :111 redraw the workload (step-t jitter stream)
             for (int blk = 0; blk < 5; ++blk) {
@@ -266,20 +302,20 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
                     const double dj = e_d[j];
                     rank += (dj < d) || (dj == d && j < w);
                 }
-            if (rank == si[1] - 1) sc[0] = d;
+            if (rank == K - 1) sc[0] = d;
         }
         __syncthreads();
         // ---- payment :130-137 ----------------------------------------------------------------
+        double red[4] = {0.0, 0.0, 0.0, 0.0};
         if (runs) {
             const int e = (int)ceil(sc[0]);
             const int m = n0 ? po.nslots : (po.nslots >= e ? e : po.nslots);
-            e_d[w] = price_after(my_lw, po, m);
+            const double price = price_after(my_lw, po, m);
+            red[0] = n0 ? price : (double)e_sel[w] * price;
         }
-        __syncthreads();
+        env_sum4(red);                                                     // the reference adds in worker order: a tree here, fp32 out
         if (env_ok && w == 0) {
-            double pay = 0.0;
-            if (n0) pay = e_d[0];
-            else for (int i = 0; i < W; ++i) pay += (double)e_sel[i] * e_d[i];
+            const double pay = red[0];
             const double fd = sc[0];
             double rew = -(fd * 99.0) - (pay * 1.0);                       // DCML_ENV_Functions.py:15-17
             if (n0) rew = 1.5 * rew;                                       // :88
@@ -359,11 +395,11 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
     const long sw = (st.shannon ? 2 * W + 2 : W + 2) + (io.binary ? 62 : 0);    // floats per share_obs row
     const int s0 = io.binary ? 64 : 2;                                          // first per-worker column
     double* my_f = s_f + (size_t)threadIdx.x * 3;
+    int en_before = 0;
+    env_count(active && !e_dis[w], en_before);                             // enabled workers with a smaller index (:226 i - disabled)
     if (active) {
         const int a = si[3];
         const bool dis = e_dis[w];
-        int en_before = 0;
-        for (int j = 0; j < w; ++j) en_before += !e_dis[j];
         const int n_en = W - si[4];
         float* o = io.obs + (env * L + w) * 7;
         o[0] = o0; o[1] = o1;
@@ -394,12 +430,11 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
             io.sob[env * sw + w] = (float)(((w < 32 ? Rb : Cb) >> bit) & 1u);
         }
     }
-    __syncthreads();
+    double mean[4] = {0.0, 0.0, 0.0, 0.0};                                 // :235-239 sums over the enabled workers
+    if (active && !e_dis[w]) { mean[0] = my_f[0]; mean[1] = my_f[1]; mean[2] = my_f[2]; mean[3] = e_d[w]; }
+    env_sum4(mean);
     if (env_ok && w == 0) {
-        double m0 = 0.0, m1 = 0.0, m2 = 0.0, sp = 0.0;
-        const double* ef = s_f + (size_t)(le * tpe) * 3;
-        for (int j = 0; j < W; ++j)
-            if (!e_dis[j]) { m0 += ef[j * 3]; m1 += ef[j * 3 + 1]; m2 += ef[j * 3 + 2]; sp += e_d[j]; }
+        const double m0 = mean[0], m1 = mean[1], m2 = mean[2], sp = mean[3];
         const double n_en = (double)(W - si[4]);
         float* o = io.obs + (env * L + W) * 7;                             // :235-239
         o[0] = o0; o[1] = o1;
@@ -489,7 +524,7 @@ extern "C" int dcml_env_create(const dcml_env_cfg* cfg, const double* base_host,
     e->epb = tpe >= target ? 1 : target / tpe;
     e->block = e->epb * tpe;
     e->smem = (size_t)e->block * (LWS + 1 + 3 + 2) * 8 + (size_t)e->epb * 8 * 8 + (size_t)e->block * (4 + 4) +
-              (size_t)e->epb * 8 * 4 + e->block + 16;
+              (size_t)e->epb * 8 * 4 + e->block + 16 + (size_t)(e->block / 32) * 32 + 32;
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_lw = carve((size_t)B * W * PERIOD * 8), o_R = carve(B * 8), o_C = carve(B * 8), o_Pr = carve((size_t)B * W * 8),
