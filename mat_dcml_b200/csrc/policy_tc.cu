@@ -274,8 +274,20 @@ enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long
     ring.init(s.ring, s.bars, b.w, c_tc_enc_embed, 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
     float* sPar = s.sT;                                   // the small parameter group lives in sT until x0 is formed
     for (int i = tid; i < lay::ENC_EMB_SIZE; i += NT) sPar[i] = b.w[lay::ENC_EMB + i];
+    // The tile's observations (n_valid rows of obs_dim floats, contiguous in the env-major / agent-minor layout of the
+    // policy API) are staged with ONE TMA bulk copy into shared memory behind the parameters instead of eight strided scalar
+    // loads per thread; a tile whose byte range is not 16-byte aligned (odd slice offsets, the ragged last tile) keeps the loads.
+    float* sObs = s.sT + 1024;
+    uint64_t* obs_bar = &s.bars[6];
+    const uint32_t obs_bytes = (uint32_t)n_valid * obs_dim * 4u;
+    const bool obs_tma = ((reinterpret_cast<uintptr_t>(obs + tile0 * obs_dim) | obs_bytes) & 15) == 0;
+    if (tid == 0) mbar_init(obs_bar, 1);
     tc::Ctx c;
-    tc::ctx_init(c, s);
+    tc::ctx_init(c, s);                                   // fences the barrier initialisations, CTA barrier
+    if (tid == 0 && obs_tma) {
+        mbar_expect_tx(obs_bar, obs_bytes);
+        bulk_g2s(sObs, obs + tile0 * obs_dim, obs_bytes, obs_bar);
+    }
     ring.prefetch();
     const int row = c.row, half = c.half;
     float* sTrow = s.sT + row * XS + half * 32;
@@ -283,8 +295,12 @@ enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long
     {
         const long g = tile0 + row;
         float o[8], mean = 0.f;
+        if (obs_tma) mbar_wait(obs_bar, 0);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) { o[k] = (k < obs_dim && row < n_valid) ? obs[g * obs_dim + k] : 0.f; mean += o[k]; }
+        for (int k = 0; k < 8; ++k) {
+            o[k] = (k < obs_dim && row < n_valid) ? (obs_tma ? sObs[row * obs_dim + k] : obs[g * obs_dim + k]) : 0.f;
+            mean += o[k];
+        }
         mean /= (float)obs_dim;
         float var = 0.f;
 #pragma unroll

@@ -5,7 +5,8 @@ whose GPU memory is owned by another framework's allocator, or a latency-critica
 take the device-wide sync of cudaMalloc/cudaFree): its scratch is a fixed array inside the library.
 This file is collected last on purpose, and the test also passes when run alone in a fresh process.
 It calls the entry point through the C ABI twice in a row -- the second call finds the first call's
-leftovers in the shared array -- and checks each result against the regular, allocating entry point.
+leftovers in the shared array -- and checks each result against the regular, allocating entry point and
+against the CPU oracle (same named Philox draws for the stochastic call).
 """
 import ctypes
 
@@ -14,6 +15,8 @@ import pytest
 import torch
 
 from oracle import mat_oracle as mo
+from oracle import philox as px
+from test_policy_gpu import assert_actions
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-4      # the log-prob tolerance of the other policy tests
@@ -36,7 +39,8 @@ def test_static_scratch_matches_allocating_entry_point(cuda_device):
     lib = _cabi.lib()
     L = 21
     m = MultiAgentTransformer(L + 1, 7, 2, L, 2, 64, 2, device=torch.device("cuda"), action_type="Semi_Discrete")
-    m.load_state_dict(mo.full_state_dict(mo.make_weights(41, L), L))
+    sd = mo.make_weights(41, L)
+    m.load_state_dict(mo.full_state_dict(sd, L))
     m.sync_weights()
     rng = np.random.RandomState(5)
     # two calls in a row: different batch sizes, inputs and modes, so stale scratch would show
@@ -52,6 +56,11 @@ def test_static_scratch_matches_allocating_entry_point(cuda_device):
         np.testing.assert_array_equal(a_new[:, :-1], a_old[:, :-1])
         np.testing.assert_allclose(a_new[:, -1], a_old[:, -1], atol=TOL)
         np.testing.assert_allclose(lp_new, lp_old, atol=TOL)
+        # ... and against the oracle: the stochastic call with the kernel's own named draws (seed 4242, env offset 3)
+        u = None if det else px.policy_uniforms(4242, 10 + call, B, L, env0=3)
+        z = None if det else px.policy_normals(4242, 10 + call, B, L - 1, env0=3)
+        _, ao, lpo = mo.get_actions(sd, obs.cpu().numpy().reshape(-1, 7), ava.cpu().numpy(), L, deterministic=det, stride=stride, u=u, z=z)
+        assert_actions(a_new, ao.numpy(), lp_new, lpo.numpy(), L, u=u)
     # beyond the stated limit (2048 env x agent pairs) the call is refused, not redirected
     B = 2048 // L + 1
     rep = torch.zeros(B, L, 64, device="cuda")
