@@ -216,17 +216,26 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
     uint8_t* e_dis = s_dis + le * tpe;
     double* e_rd = s_rate + le * tpe;
     double* e_ru = s_rate + blockDim.x + le * tpe;
-    double* glw = st.lw + (env * W + w) * PERIOD;
+    // workload table of the env, slot-pair major: double2 (slots 2i, 2i+1) of worker w at [i][w], so that the lanes of a
+    // warp read / write consecutive 16-byte words (coalesced 128-bit accesses) instead of 160-byte-strided rows
+    double2* glw2 = reinterpret_cast<double2*>(st.lw) + env * (long)(PERIOD / 2) * W + w;
+    auto lw_at = [&](int slot) -> double {
+        const double2 v = glw2[(long)(slot >> 1) * W];
+        return (slot & 1) ? v.y : v.x;
+    };
 
     if (what == ENV_INIT) {
         // Worker.__init__ :39  all_workload = clip(base * U(0.8,1.2), 0, 1), step-0 jitter stream
         if (active) {
             for (int blk = 0; blk < 5; ++blk) {
                 const uint4 x = philox4x32(genv, 0u, rng_tag(S_JITTER, (uint32_t)w), (uint32_t)blk, st.seed);
+                double nv[4];
                 for (int i = 0; i < 4; ++i) {
                     const double v = st.base[w * PERIOD + blk * 4 + i] * (0.8 + (1.2 - 0.8) * u01d(lane_of(x, i)));
-                    glw[blk * 4 + i] = fmin(fmax(v, 0.0), 1.0);
+                    nv[i] = fmin(fmax(v, 0.0), 1.0);
                 }
+                glw2[(long)(blk * 2) * W] = make_double2(nv[0], nv[1]);
+                glw2[(long)(blk * 2 + 1) * W] = make_double2(nv[2], nv[3]);
             }
         }
     }
@@ -236,7 +245,7 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
         if (active) {
             e_sel[w] = st.fixed ? (st.disabled[env * W + w] ? 0.f : 1.f) : io.actions[env * L + w];   // :58-59 vs :73
             for (int i = 0; i < PERIOD; i += 2) {
-                const double2 v = *reinterpret_cast<const double2*>(glw + i);
+                const double2 v = glw2[(long)(i >> 1) * W];
                 my_lw[i] = v.x; my_lw[i + 1] = v.y;
             }
         }
@@ -286,23 +295,37 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
                     const double v = st.base[w * PERIOD + blk * 4 + i] * (0.8 + (1.2 - 0.8) * u01d(lane_of(x, i)));
                     nv[i] = fmin(fmax(v, 0.0), 1.0);
                 }
-                *reinterpret_cast<double2*>(glw + blk * 4) = make_double2(nv[0], nv[1]);
-                *reinterpret_cast<double2*>(glw + blk * 4 + 2) = make_double2(nv[2], nv[3]);
+                glw2[(long)(blk * 2) * W] = make_double2(nv[0], nv[1]);
+                glw2[(long)(blk * 2 + 1) * W] = make_double2(nv[2], nv[3]);
             }
         }
         __syncthreads();
         // ---- k-of-n completion order statistic :128-129 -------------------------------------
-        if (env_ok && n0) {
-            if (w == 0) sc[0] = po.delay;
-        } else if (active && e_sel[w] != 0.f) {
-            const double d = po.delay;
+        // final_delay = K-th smallest delay among the selected workers: every thread ranks its own delay (unselected
+        // workers carry +inf) -- against its own warp by register shuffles, against the env's other warps through the
+        // delays in shared memory -- and the thread of rank K-1 publishes it.  Ties break by worker index (a stable sort).
+        {
+            const bool selected = active && !n0 && e_sel[w] != 0.f;
+            const double d = selected ? po.delay : INFINITY;
+            if (active) e_d[w] = d;                         // other warps read the padded key
             int rank = 0;
-            for (int j = 0; j < W; ++j)
-                if (e_sel[j] != 0.f) {
-                    const double dj = e_d[j];
-                    rank += (dj < d) || (dj == d && j < w);
+#pragma unroll 8
+            for (int j = 0; j < 32; ++j) {
+                const double dj = __shfl_sync(0xffffffffu, d, j);
+                rank += (dj < d) || (dj == d && j < lane);
+            }
+            __syncthreads();
+            const int wi = w >> 5;
+            for (int ow = 0; ow < nwe; ++ow) {
+                if (ow == wi) continue;
+                const int lim = min(32, W - ow * 32);
+                for (int j = 0; j < lim; ++j) {
+                    const double dj = e_d[ow * 32 + j];
+                    rank += (dj < d) || (dj == d && ow < wi);
                 }
-            if (rank == K - 1) sc[0] = d;
+            }
+            if (env_ok && n0 && w == 0) sc[0] = po.delay;
+            if (selected && rank == K - 1) sc[0] = d;
         }
         __syncthreads();
         // ---- payment :130-137 ----------------------------------------------------------------
@@ -410,7 +433,7 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
             my_f[0] = 0.0; my_f[1] = 0.0; my_f[2] = 0.0;
         } else {
             for (int s = 0; s < 3; ++s) {                                  // :222
-                const double v = glw[(a + s) % PERIOD];
+                const double v = lw_at((a + s) % PERIOD);
                 my_f[s] = v;
                 o[2 + s] = (float)v;
             }
