@@ -66,6 +66,20 @@ struct EnvIO {
 // conversion per draw.  Two Philox blocks are kept: the one being consumed and the next, which `ensure()` generates at
 // points where the warp is converged (loop entry, every fourth trip) -- the lanes of a warp sit at different draw
 // indices, and a refill inside the per-draw path would make the whole warp pay a Philox call on almost every trip.
+__device__ __noinline__ uint4 philox_nl(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint64_t seed) {
+    return philox4x32(c0, c1, c2, c3, seed);
+}
+// Shannon.upload / download (Shannon.py:14-21) for one worker; kept out of line: pow / log2 in float64 are long
+// instruction sequences that the default (non-Shannon) configuration never executes
+__device__ __noinline__ void shannon_rates(double u_master, double u_worker, double u_dist, int W, double& down, double& up) {
+    const double pm = 50.0 + (60.0 - 50.0) * u_master;
+    const double pw = 10.0 + (20.0 - 10.0) * u_worker;
+    const double dist = 10.0 + (100.0 - 10.0) * u_dist;
+    const double d4 = pow(dist, -4.0);
+    const double bw = B_TOTAL / (double)W;
+    down = bw * log2(1.0 + (pm * d4) / NOISE);
+    up = bw * log2(1.0 + (pw * d4) / NOISE);
+}
 struct RetryStream {
     uint32_t env, step, tag, thr;
     uint64_t seed;
@@ -75,10 +89,10 @@ struct RetryStream {
     __device__ void init(uint32_t env_, uint32_t step_, int w, uint64_t seed_, double Pr) {
         env = env_; step = step_; tag = rng_tag(S_RETRY, (uint32_t)w); seed = seed_; k = 0; blk = 0; have1 = false;
         thr = (uint32_t)ceil(Pr * 16777216.0);
-        b0 = philox4x32(env, step, tag, 0u, seed);
+        b0 = philox_nl(env, step, tag, 0u, seed);
     }
     __device__ void ensure() {
-        if (!have1) { b1 = philox4x32(env, step, tag, (uint32_t)(blk + 1), seed); have1 = true; }
+        if (!have1) { b1 = philox_nl(env, step, tag, (uint32_t)(blk + 1), seed); have1 = true; }
     }
     __device__ void advance() { ensure(); b0 = b1; ++blk; have1 = false; }
     // Consume draws up to and including the first one that is >= Pr (`while U < Pr: n++`, WORKER:54-56,100-102) and return
@@ -227,8 +241,9 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
     if (what == ENV_INIT) {
         // Worker.__init__ :39  all_workload = clip(base * U(0.8,1.2), 0, 1), step-0 jitter stream
         if (active) {
+#pragma unroll 1
             for (int blk = 0; blk < 5; ++blk) {
-                const uint4 x = philox4x32(genv, 0u, rng_tag(S_JITTER, (uint32_t)w), (uint32_t)blk, st.seed);
+                const uint4 x = philox_nl(genv, 0u, rng_tag(S_JITTER, (uint32_t)w), (uint32_t)blk, st.seed);
                 double nv[4];
                 for (int i = 0; i < 4; ++i) {
                     const double v = st.base[w * PERIOD + blk * 4 + i] * (0.8 + (1.2 - 0.8) * u01d(lane_of(x, i)));
@@ -288,8 +303,9 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
             po = process(my_lw, r, Cv, arr, rs, st.shannon ? st.rate_down[env * W + w] : DATA_RATE);
             e_d[w] = po.delay;
             // Worker.process :111 redraw the workload (step-t jitter stream)
+#pragma unroll 1
             for (int blk = 0; blk < 5; ++blk) {
-                const uint4 x = philox4x32(genv, t, rng_tag(S_JITTER, (uint32_t)w), (uint32_t)blk, st.seed);
+                const uint4 x = philox_nl(genv, t, rng_tag(S_JITTER, (uint32_t)w), (uint32_t)blk, st.seed);
                 double nv[4];
                 for (int i = 0; i < 4; ++i) {
                     const double v = st.base[w * PERIOD + blk * 4 + i] * (0.8 + (1.2 - 0.8) * u01d(lane_of(x, i)));
@@ -345,7 +361,7 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
             io.reward[env] = (float)rew;
             io.delay[env] = (float)fd;
             io.payment[env] = (float)pay;
-            const uint4 x = philox4x32(genv, t, rng_tag(S_RESET, 0), 1u, st.seed);
+            const uint4 x = philox_nl(genv, t, rng_tag(S_RESET, 0), 1u, st.seed);
             const int dn = u01d(x.y) < DONE_P;                             // :142
             si[5] = dn;
             io.done[env] = (uint8_t)dn;
@@ -355,10 +371,11 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
 
     // ---- Env.reset :157-199 (twice when done under ShareDummyVecEnv) ---------------------------
     if (what != ENV_OBSERVE) {
+#pragma unroll 1
         for (int r = 0; r < 2; ++r) {
             const bool apply = env_ok && (r == 0 || (what == ENV_STEP && st.double_reset && si[5]));
             if (apply && w == 0) {
-                const uint4 x = philox4x32(genv, t, rng_tag(S_RESET, 0), (uint32_t)(16 * r), st.seed);
+                const uint4 x = philox_nl(genv, t, rng_tag(S_RESET, 0), (uint32_t)(16 * r), st.seed);
                 const int kmax = (int)floor(0.8 * (double)W);
                 si[4] = 1 + (int)bounded(x.x, (uint32_t)kmax);                              // :158
                 si[3] = (int)bounded(x.y, PERIOD);                                           // :160
@@ -366,19 +383,13 @@ __global__ void env_kernel(EnvState st, EnvIO io, int what, uint32_t t, long env
                 sc[3] = (double)(C_MIN + (int)bounded(x.w, (uint32_t)(C_HI - C_MIN + 1)));   // DCML_Master.py:48
             }
             if (apply && w < W) {
-                const uint4 x = philox4x32(genv, t, rng_tag(S_WORKER, (uint32_t)w), (uint32_t)r, st.seed);
+                const uint4 x = philox_nl(genv, t, rng_tag(S_WORKER, (uint32_t)w), (uint32_t)r, st.seed);
                 e_d[w] = 0.0 + (PR_MAX - 0.0) * u01d(x.x);                                   // :197
                 e_key[w] = x.y;
                 if (st.shannon) {
                     // update_workers_transmission(True): DCML_Basic_Env.py:18-27, DCML_Master.py:41-45, Shannon.py:14-21
-                    const uint4 xm = philox4x32(genv, t, rng_tag(S_RESET, 0), (uint32_t)(16 * r + 2), st.seed);
-                    const double pm = 50.0 + (60.0 - 50.0) * u01d(xm.x);
-                    const double pw = 10.0 + (20.0 - 10.0) * u01d(x.z);
-                    const double dist = 10.0 + (100.0 - 10.0) * u01d(x.w);
-                    const double d4 = pow(dist, -4.0);
-                    const double bw = B_TOTAL / (double)W;
-                    e_rd[w] = bw * log2(1.0 + (pm * d4) / NOISE);
-                    e_ru[w] = bw * log2(1.0 + (pw * d4) / NOISE);
+                    const uint4 xm = philox_nl(genv, t, rng_tag(S_RESET, 0), (uint32_t)(16 * r + 2), st.seed);
+                    shannon_rates(u01d(xm.x), u01d(x.z), u01d(x.w), W, e_rd[w], e_ru[w]);
                 }
             }
             __syncthreads();
@@ -487,10 +498,10 @@ __global__ void redraw_disabled_kernel(EnvState st, uint32_t t) {
     const long env = i / st.W;
     const int w = (int)(i - env * st.W);
     const uint32_t genv = (uint32_t)(st.env_offset + env);
-    const uint32_t key = philox4x32(genv, t, rng_tag(S_WORKER, (uint32_t)w), 0u, st.seed).y;
+    const uint32_t key = philox_nl(genv, t, rng_tag(S_WORKER, (uint32_t)w), 0u, st.seed).y;
     int rank = 0;
     for (int j = 0; j < st.W; ++j) {
-        const uint32_t kj = philox4x32(genv, t, rng_tag(S_WORKER, (uint32_t)j), 0u, st.seed).y;
+        const uint32_t kj = philox_nl(genv, t, rng_tag(S_WORKER, (uint32_t)j), 0u, st.seed).y;
         rank += (kj < key) || (kj == key && j < w);
     }
     st.disabled[i] = rank < st.kdis[env];
