@@ -164,6 +164,16 @@ __device__ __forceinline__ void add_operand16(float (&v)[16], const unsigned cha
         }
     }
 }
+// Cache rows leave through a shared fp32 tile.  In the epilogue layout a warp's store instruction would write 16 bytes
+// of 32 different rows (32 half-used sectors; measured ~2,000 cycles per row store); staged, each warp instruction writes
+// two whole 256-byte rows.  Row r of the tile goes to dst + r * slot_stride.
+__device__ __forceinline__ void tile_rows_to_cache(const float* __restrict__ sT, float* __restrict__ dst, long slot_stride, int n_valid) {
+    for (int idx = threadIdx.x; idx < n_valid * 16; idx += NTD) {
+        const int r = idx >> 4, c = idx & 15;
+        *reinterpret_cast<float4*>(dst + (long)r * slot_stride + c * 4) = *reinterpret_cast<const float4*>(sT + r * XS + c * 4);
+    }
+}
+
 // LayerNorm of a 64-column row held by four threads (16 columns each): ONE exchange of (sum, sum of squares) through
 // shared memory and ONE CTA barrier; var = E[x^2] - mean^2 (inputs are residual sums of O(1) rows: the cancellation costs
 // a few ulp of the variance).  v becomes x_hat.  Two calls must be separated by a CTA barrier (every stage has one).
@@ -629,8 +639,10 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
     constexpr bool use_tab = TABK != 0;          // block 0's cross-attention keys come from the shared table(s)
     const int n_seq = use_tab ? STEP_BLOBS - 2 : STEP_BLOBS;
     Ring ring;
+    // the weight ring is fed by the CTA's last thread: thread 0 issues the MMAs of a stage, and with the bulk copies on it
+    // as well every stage waited for its ~700 cycles of mbarrier / copy issue
     ring.init(s.ring, s.bars, b.w, use_tab ? c_tc_decode_tab : c_tc_decode, n_seq, (int)(my_tiles * a.n_steps * n_seq), DEPTH,
-              lay::BLOB_BYTES, tc::SLOT_F);
+              lay::BLOB_BYTES, tc::SLOT_F, NTD - 1);
     uint64_t* mma_bar = &s.bars[tc::MMA_BAR];
     if (tid == 0) { mbar_init(mma_bar, 1); mbar_fence_init(); }
     if (warp == 0) tc::tmem_alloc_n<TMEM_D>(s.tmem_slot);
@@ -761,7 +773,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                 } else {
                 // ---- folded self-attention queries ---------------------------------------------------
                 store_operand16(s.U, row, q, v);
-                if (live) store16(x_row, v);
+                store16(sQ1row, v);                               // the block's input row, on its way to the self cache
                 {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
@@ -772,6 +784,8 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                         tc::mma_commit(mma_bar);
                     }
                     ring.prefetch();
+                    tile_rows_to_cache(s.sQ1, cx1 + (long)j * 64, slot_stride, n_valid);     // under the MMAs
+                    __syncthreads();                              // the query tiles are rewritten below
                     mma_wait();
                     result16(tmem, 0, row, q, v);
                     add16(v, w0 + lay::B_BIAS + q * 16);
@@ -816,9 +830,11 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                     layernorm_quad(v, s.sRed, row, q);
                     affine16(v, w1, q);
                     ring.release(); ring.release();
-                    if (live) store16(cx2 + (long)row * slot_stride + (long)j * 64 + q * 16, v);
+                    store16(sQ0row, v);                            // x1 row, on its way to the cross cache (the query tiles are free)
                 }
                 tc::fence_before_sync();
+                __syncthreads();
+                tile_rows_to_cache(s.sQ0, cx2 + (long)j * 64, slot_stride, n_valid);
                 __syncthreads();
                 // ---- cross-attention: folded queries q2' precomputed from obs_rep ------------------------
                 if (rows <= rows16)

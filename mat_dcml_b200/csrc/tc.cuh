@@ -72,6 +72,12 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
+// Descriptors of the K = 16 slices of one operand differ only in the start-address field: build the low word once
+// (desc_lo) and step it by 32 bytes >> 4 = 2 per slice; the high word is a constant.  Operands are 1024-byte aligned,
+// so the step never carries out of the 14-bit field.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3fffu) | (1u << 16); }
+constexpr uint32_t DESC_HI = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint64_t desc_at(uint32_t lo, int ks) { return ((uint64_t)DESC_HI << 32) | (uint64_t)(lo + 2u * (uint32_t)ks); }
 __device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -114,10 +120,11 @@ __device__ __forceinline__ void mma_set(uint32_t d, uint32_t a, uint32_t w, bool
     const uint32_t idesc128 = (1u << 4) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const uint32_t idesc64 = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     static_assert(lay::HB_LO_BYTES == 64 * 128, "Wlo must follow Whi as rows 64..127 of one swizzled tile");
+    const uint32_t da = desc_lo(a), dl = desc_lo(a + A_PART), dw = desc_lo(w);
 #pragma unroll
-    for (int ks = 0; ks < 4; ++ks) mma_f16(d, make_desc(a + ks * 32), make_desc(w + ks * 32), idesc128, (accumulate || ks > 0) ? 1u : 0u);
+    for (int ks = 0; ks < 4; ++ks) mma_f16(d, desc_at(da, ks), desc_at(dw, ks), idesc128, (accumulate || ks > 0) ? 1u : 0u);
 #pragma unroll
-    for (int ks = 0; ks < 4; ++ks) mma_f16(d + 64, make_desc(a + A_PART + ks * 32), make_desc(w + ks * 32), idesc64, 1u);
+    for (int ks = 0; ks < 4; ++ks) mma_f16(d + 64, desc_at(dl, ks), desc_at(dw, ks), idesc64, 1u);
 }
 // MMA issue in warp-uniform control flow.  Under a plain `threadIdx.x == 0` the compiler cannot keep the descriptors
 // in uniform registers and wraps every UTCHMMA in an ELECT / R2UR / branch loop (about 13 extra instructions and two
@@ -190,10 +197,11 @@ __device__ __forceinline__ void gemm_issue(const Ctx& c, const float* slot) {
             // instruction descriptors: D f32, A/B f16, both K-major, M = 128; Ahi . [Whi | Wlo] as one N = 128 product (see mma_set)
             const uint32_t idesc128 = (1u << 4) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             const uint32_t idesc64 = (1u << 4) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            const uint32_t da = desc_lo(a0), dl = desc_lo(a0 + A_PART), dw = desc_lo(b0);
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) mma_f16(d0, make_desc(a0 + ks * 32), make_desc(b0 + ks * 32), idesc128, ks > 0);
+            for (int ks = 0; ks < 4; ++ks) mma_f16(d0, desc_at(da, ks), desc_at(dw, ks), idesc128, ks > 0);
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) mma_f16(d0 + 64, make_desc(a0 + A_PART + ks * 32), make_desc(b0 + ks * 32), idesc64, 1);
+            for (int ks = 0; ks < 4; ++ks) mma_f16(d0 + 64, desc_at(dl, ks), desc_at(dw, ks), idesc64, 1);
             mma_commit_saddr(bar);
         }
     }

@@ -21,41 +21,54 @@ enum { EP_GELU = 1, EP_RES = 2, EP_LN = 4 };
 // ---------------------------------------------------------------------------------------------
 struct Ring {
     float* slots; uint64_t* bars; const float* gw; const int* seq;   // seq: float offsets of the blobs, cyclic
-    int seq_len, total, head, tail, depth;   // total: blobs this CTA consumes in its lifetime; tail: thread 0 only
+    int seq_len, total, depth;               // total: blobs this CTA consumes in its lifetime
     uint32_t bytes;                          // bytes per blob (forward blobs: BLOB_BYTES)
     int stride;                              // floats between slots (tensor-core operands need 1024-byte aligned slots)
+    int producer;                            // the thread that issues the bulk copies
+    // consumer side (every thread keeps the same values): blobs released so far, its slot and that slot's parity.
+    // Slot / sequence positions advance by compare-and-wrap: no division by the run-time depth on the stage path.
+    int head, head_slot; uint32_t head_par;
+    int tail, tail_slot, tail_seq;           // producer side: blobs requested so far, the next slot / sequence position
 
     __device__ void init(float* slots_, uint64_t* bars_, const float* gw_, const int* seq_, int seq_len_, int total_,
-                         int depth_, uint32_t bytes_ = lay::BLOB_BYTES, int stride_ = lay::BLOB) {
+                         int depth_, uint32_t bytes_ = lay::BLOB_BYTES, int stride_ = lay::BLOB, int producer_ = 0) {
         slots = slots_; bars = bars_; gw = gw_; seq = seq_; seq_len = seq_len_; total = total_; depth = depth_;
-        head = 0; tail = 0; bytes = bytes_; stride = stride_;
+        bytes = bytes_; stride = stride_; producer = producer_;
+        head = 0; head_slot = 0; head_par = 0; tail = 0; tail_slot = 0; tail_seq = 0;
         if (threadIdx.x == 0) {
             for (int i = 0; i < depth; ++i) mbar_init(&bars[i], 1);
             mbar_fence_init();
         }
     }
+    // Refill every slot released so far.  A slot is rewritten only after the producer itself has passed the stage that
+    // consumed it (it waits for the MMAs like every thread) and a CTA barrier has closed that stage's epilogue reads.
     __device__ void prefetch() {
-        if (threadIdx.x == 0) {
+        if ((int)threadIdx.x == producer) {
             while (tail < head + depth && tail < total) {
-                const int s = tail % depth;
-                mbar_expect_tx(&bars[s], bytes);
-                bulk_g2s(slots + (size_t)s * stride, gw + seq[tail % seq_len], bytes, &bars[s]);
+                mbar_expect_tx(&bars[tail_slot], bytes);
+                bulk_g2s(slots + (size_t)tail_slot * stride, gw + seq[tail_seq], bytes, &bars[tail_slot]);
                 ++tail;
+                if (++tail_slot == depth) tail_slot = 0;
+                if (++tail_seq == seq_len) tail_seq = 0;
             }
         }
     }
     __device__ const float* acquire() {
-        const int s = head % depth;
-        mbar_wait(&bars[s], (head / depth) & 1);
-        return slots + (size_t)s * stride;
+        mbar_wait(&bars[head_slot], head_par);
+        return slots + (size_t)head_slot * stride;
     }
-    // k-th blob after the current head without consuming it (stages that need two blobs at once)
+    // k-th blob after the current head without consuming it (stages that need two blobs at once); k < depth
     __device__ const float* peek(int k) {
-        const int h = head + k, s = h % depth;
-        mbar_wait(&bars[s], (h / depth) & 1);
+        int s = head_slot + k;
+        uint32_t par = head_par;
+        if (s >= depth) { s -= depth; par ^= 1u; }
+        mbar_wait(&bars[s], par);
         return slots + (size_t)s * stride;
     }
-    __device__ void release() { ++head; }
+    __device__ void release() {
+        ++head;
+        if (++head_slot == depth) { head_slot = 0; head_par ^= 1u; }
+    }
 };
 
 // ---------------------------------------------------------------------------------------------
