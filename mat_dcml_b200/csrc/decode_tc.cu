@@ -29,7 +29,7 @@ namespace {
 constexpr int NTD = 512;             // threads per CTA
 constexpr int MAXR = 128;            // env rows per tile (MMA M)
 constexpr int DEPTH = 4;             // weight ring slots
-constexpr int TMEM_D = 256;          // accumulator columns
+constexpr int TMEM_D = 512;          // columns 0-255: accumulators; 256-319: the block input row parked for the LN1 residual
 constexpr int OP_BYTES = 2 * tc::A_PART;
 constexpr int ROWS16 = 32;          // tiles of at most this many envs use 16 lanes per env in the attention
 constexpr int PF_ROWS = 4;          // in-loop L2 prefetch distance of the cache-row loads (8 and 16 measured slower)
@@ -105,6 +105,34 @@ __device__ __forceinline__ void result16(uint32_t tmem, int cols, int row, int q
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = fmaf(__uint_as_float(v2[i]), 1.0f / 2048.0f, __uint_as_float(v1[i]));
 }
+// park / fetch this thread's 16 fp32 values in its own TMEM lane (columns cols + 16 q ..): a residual that survives the
+// stages in between without registers, shared memory or a scattered global reload
+__device__ __forceinline__ void tmem_park16(uint32_t tmem, int cols, int row, int q, const float (&v)[16]) {
+    uint32_t u[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) u[i] = __float_as_uint(v[i]);
+    const uint32_t taddr = tmem + ((uint32_t)(row & ~31) << 16) + cols + q * 16;
+    TC_ST16(taddr, u);
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_fetch16(uint32_t tmem, int cols, int row, int q, float (&v)[16]) {
+    uint32_t u[16];
+    const uint32_t taddr = tmem + ((uint32_t)(row & ~31) << 16) + cols + q * 16;
+    TC_LD16(u, taddr);
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(u[i]);
+}
+// token-major global rows (row r at src + r * row_stride floats) -> shared fp32 tile, asynchronously (no registers held):
+// whole 256-byte rows per half-warp.  Complete after cp_async_wait_all() + a CTA barrier.
+__device__ __forceinline__ void rows_to_tile_async(float* sT, const float* __restrict__ src, long row_stride, int n_valid) {
+    for (int idx = threadIdx.x; idx < n_valid * 16; idx += NTD) {
+        const int r = idx >> 4, c = idx & 15;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(sT + r * XS + c * 4)), "l"(src + (long)r * row_stride + c * 4) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void add16(float (&v)[16], const float* __restrict__ p) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -725,13 +753,13 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
             for (int blk = 0; blk < 2; ++blk) {
                 float* cx1 = kv0 + (blk * 2 + 0) * (long)L * 64;     // self-attention inputs (block input x)
                 float* cx2 = kv0 + (blk * 2 + 1) * (long)L * 64;     // cross-attention inputs (x after LN1)
-                float* x_row = cx1 + (long)row * slot_stride + (long)j * 64 + q * 16;
                 if (blk == 0 && use_tab) {
                     // ---- block 0 from the table: no token-code softmax, no output-map stage, no cache row; the
                     //      cross-attention gathers its keys x1_t from x1tab by the env's action history ------------------
                     // keys behind the block start in a speculative pass (kind 1) are that pass's rows (second table)
                     const int spec_s = (TABK == 2 && st.kind == 1) ? sched.s : -1;
                     const float* spec = x1spec + sb.base * 64;
+                    rows_to_tile_async(s.sQ1, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid);       // LN2's residual rows
                     if (rows <= rows16)
                         attention_absorbed_op16<true, PFD, TABK>(b.Q2p[0][0] + (env0 * L + j) * 64, b.Q2p[0][1] + (env0 * L + j) * 64, (long)L * 64,
                                                                  x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits, spec, spec_s);
@@ -774,6 +802,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                 // ---- folded self-attention queries ---------------------------------------------------
                 store_operand16(s.U, row, q, v);
                 store16(sQ1row, v);                               // the block's input row, on its way to the self cache
+                tmem_park16(tmem, 256, row, q, v);                // and kept for the LN1 residual
                 {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
@@ -813,20 +842,16 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                         tc::mma_commit(mma_bar);
                     }
                     ring.prefetch();
-                    // the residual row comes from global memory (this thread stored it two stages ago): issue the loads
-                    // before waiting for the tensor core so that their latency is off the stage's critical path
-                    float res[16];
-                    if (blk != 0 && live) load16(res, x_row);
-                    else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) res[i] = 0.f;
-                    }
                     mma_wait();
                     result16(tmem, 0, row, q, v);
                     add16(v, w1 + lay::B_BIAS + q * 16);
                     if (blk == 0) add16(v, s.sEmb + s.sCode[row] * 64 + q * 16);
+                    else {
+                        float res[16];                             // the block input, parked in tensor memory two stages ago
+                        tmem_fetch16(tmem, 256, row, q, res);
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += res[i];
+                        for (int i = 0; i < 16; ++i) v[i] += res[i];
+                    }
                     layernorm_quad(v, s.sRed, row, q);
                     affine16(v, w1, q);
                     ring.release(); ring.release();
@@ -835,6 +860,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                 tc::fence_before_sync();
                 __syncthreads();
                 tile_rows_to_cache(s.sQ0, cx2 + (long)j * 64, slot_stride, n_valid);
+                rows_to_tile_async(s.sQ1, b.rep + (env0 * L + j) * 64, (long)L * 64, n_valid);           // LN2's residual rows
                 __syncthreads();
                 // ---- cross-attention: folded queries q2' precomputed from obs_rep ------------------------
                 if (rows <= rows16)
@@ -847,6 +873,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                 {
                     const float* w0 = ring.peek(0);
                     const float* w1 = ring.peek(1);
+                    cp_async_wait_all();                           // this thread's share of the obs_rep rows has landed in sQ1
                     tc::publish();
                     if (tc::mma_issuer()) {
                         tc::mma_set(tmem, uaddr, smem_u32(w0), false);
@@ -854,17 +881,10 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                         tc::mma_commit(mma_bar);
                     }
                     ring.prefetch();
-                    float res[16];                                 // obs_rep row: loaded under the MMAs (see LN1 above)
-                    if (live) load16(res, b.rep + ((env0 + row) * L + j) * 64 + q * 16);
-                    else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) res[i] = 0.f;
-                    }
                     mma_wait();
                     result16(tmem, 0, row, q, v);
                     add16(v, w1 + lay::B_BIAS + q * 16);
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += res[i];
+                    if (live) add16(v, sQ1row);                    // + obs_rep (rows past the batch hold stale data)
                     layernorm_quad(v, s.sRed, row, q);
                     affine16(v, w1, q);
                     ring.release(); ring.release();
