@@ -901,7 +901,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                     add16(v, w0 + lay::B_BIAS + q * 16);
                     ring.release();
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
+                    for (int i = 0; i < 16; i += 2) gelu_erf_x2(v[i], v[i + 1]);
                     store_operand16(s.V, row, q, v);
                 }
                 {
@@ -934,7 +934,7 @@ decode_tc_kernel(PolicyBufs b, DecodeArgs a, const float* __restrict__ x1tab, co
                 result16(tmem, 0, row, q, v);
                 add16(v, w0 + lay::B_BIAS + q * 16);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
+                for (int i = 0; i < 16; i += 2) gelu_erf_x2(v[i], v[i + 1]);
                 layernorm_quad(v, s.sRed, row, q);
                 affine16(v, w0, q);
                 ring.release();

@@ -115,8 +115,8 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     prefetch_tile_rows(b.X, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
     prefetch_tile_rows(y_in, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
     Ring ring;
-    if (BLK == 1 && for_decode) ring.init(s.ring, s.bars, b.w, c_tc_enc_blk1_dec, 8, 8, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
-    else ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_tc_enc_blk0 : c_tc_enc_blk1, 6, 6, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    if (BLK == 1 && for_decode) ring.init(s.ring, s.bars, b.w, c_tc_enc_blk1_dec, 8, 8, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
+    else ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_tc_enc_blk0 : c_tc_enc_blk1, 6, 6, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
     tc::Ctx c;
     tc::ctx_init(c, s);                  // ends with a CTA barrier: ring barriers are initialised
     ring.prefetch();
@@ -151,7 +151,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
         ring.release();
         if (tb.on) save_row32(tb.e_m0[BLK], tile0, row, half, n_valid, v);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        for (int i = 0; i < 32; i += 2) gelu_erf_x2(v[i], v[i + 1]);
         tc::store_operand32(s.sA, row, half, v);
     }
     // ---- mlp.2 + residual + LN2 -----------------------------------------------------------------
@@ -201,7 +201,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
             add_bias32(v, blob, half);
             if (tb.on) save_row32(tb.e_hh, tile0, row, half, n_valid, v);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+            for (int i = 0; i < 32; i += 2) gelu_erf_x2(v[i], v[i + 1]);
             const float rs = tc::layernorm_pair(v, sRed, row, half);
             if (tb.on) {
                 save_row32(tb.e_xhh, tile0, row, half, n_valid, v);
@@ -271,7 +271,7 @@ enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_tc_enc_embed, 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    ring.init(s.ring, s.bars, b.w, c_tc_enc_embed, 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
     float* sPar = s.sT;                                   // the small parameter group lives in sT until x0 is formed
     for (int i = tid; i < lay::ENC_EMB_SIZE; i += NT) sPar[i] = b.w[lay::ENC_EMB + i];
     // The tile's observations (n_valid rows of obs_dim floats, contiguous in the env-major / agent-minor layout of the
@@ -320,7 +320,7 @@ enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long
         }
         if (tb.on) save_row32(tb.e_h0, tile0, row, half, n_valid, v);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        for (int i = 0; i < 32; i += 2) gelu_erf_x2(v[i], v[i + 1]);
         const float rs = tc::layernorm_pair(v, s.sSmall, row, half);
         if (tb.on) {
             save_row32(tb.e_xh0, tile0, row, half, n_valid, v);
@@ -352,7 +352,7 @@ dec_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, 
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_tc_dec_embed, 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    ring.init(s.ring, s.bars, b.w, c_tc_dec_embed, 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
     build_emb_table(s.sSmall + 512, b.w);
     tc::Ctx c;
     tc::ctx_init(c, s);
@@ -381,7 +381,7 @@ dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_tc_dec_attn1[blk], 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    ring.init(s.ring, s.bars, b.w, c_tc_dec_attn1[blk], 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
     tc::Ctx c;
     tc::ctx_init(c, s);
     ring.prefetch();
@@ -433,7 +433,7 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
     Ring ring;
-    ring.init(s.ring, s.bars, b.w, c_tc_dec_attn2[blk], blk == 0 ? 6 : 4, blk == 0 ? 6 : 4, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F);
+    ring.init(s.ring, s.bars, b.w, c_tc_dec_attn2[blk], blk == 0 ? 6 : 4, blk == 0 ? 6 : 4, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
     tc::Ctx c;
     tc::ctx_init(c, s);
     ring.prefetch();
@@ -465,7 +465,7 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
         ring.release();
         if (tb.on) save_row32(tb.d_m0[blk], tile0, row, half, n_valid, v);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        for (int i = 0; i < 32; i += 2) gelu_erf_x2(v[i], v[i + 1]);
         tc::store_operand32(s.sA, row, half, v);
     }
     {   // mlp.2 + residual + LN3
@@ -490,7 +490,7 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
         const float* blob = st.run(v);
         if (tb.on) save_row32(tb.d_hh, tile0, row, half, n_valid, v);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+        for (int i = 0; i < 32; i += 2) gelu_erf_x2(v[i], v[i + 1]);
         const float rs = tc::layernorm_pair(v, sRed, row, half);
         if (tb.on) {
             save_row32(tb.d_xhh, tile0, row, half, n_valid, v);
