@@ -130,9 +130,11 @@ __device__ __forceinline__ void gelu_erf_x2(float& x0, float& x1) {
     mul2v(p0, p1, p0, p1, p0, p1);
     mul2v(p0, p1, p0, p1, p0, p1);
     mul2v(p0, p1, p0, p1, p0, p1);
-    const float y0 = __fdividef(-0.5f * a0, p0), y1 = __fdividef(-0.5f * a1, p1);       // -|x| / 2 . P^-16 (P^16 = inf -> 0)
-    x0 = fmaxf(x0, 0.f) + y0;
-    x1 = fmaxf(x1, 0.f) + y1;
+    float r0, r1;                                        // P^-16; P >= 1, and P^16 = inf gives 0: no range fix-ups needed
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(p0));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(p1));
+    x0 = fmaf(-0.5f * a0, r0, fmaxf(x0, 0.f));
+    x1 = fmaf(-0.5f * a1, r1, fmaxf(x1, 0.f));
 }
 
 // acc4 += p * x4 ;  acc4 *= a ;  dot of two float4 pairs
