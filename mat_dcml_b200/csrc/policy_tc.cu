@@ -92,11 +92,15 @@ __device__ __forceinline__ void prefetch_tile_rows(const float* __restrict__ bas
 // attention output rows computed by attn_tc.cu (token-major, global) -> operand, one half-warp per row
 __device__ __forceinline__ void rows_to_operand(unsigned char* sA, const float* __restrict__ y, long tile0, long n_tok) {
     const int hw = threadIdx.x >> 4, l = threadIdx.x & 15;
-    for (int r = hw; r < tc::TR; r += NT / 16) {
-        const long g = tile0 + r;
-        const float4 c = g < n_tok ? __ldg(reinterpret_cast<const float4*>(y + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
-        tc::store_operand4(sA, r, l, c);
+    constexpr int N = tc::TR * 16 / NT;
+    float4 c[N];                                                  // all loads in flight before the first conversion / store
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const long g = tile0 + hw + i * (NT / 16);
+        c[i] = g < n_tok ? __ldg(reinterpret_cast<const float4*>(y + g * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+#pragma unroll
+    for (int i = 0; i < N; ++i) tc::store_operand4(sA, hw + i * (NT / 16), l, c[i]);
 }
 
 template <int BLK>

@@ -168,11 +168,17 @@ __device__ __forceinline__ void stage(Ring& ring, const float* __restrict__ X, f
 // load a [16*RPT][64] tile from global rows (row r at src + r*stride) into a shared tile; invalid rows -> 0
 template <int RPT = 4>
 __device__ __forceinline__ void load_tile(float* __restrict__ dst, const float* __restrict__ src, long stride, int n_valid) {
-    for (int idx = threadIdx.x; idx < 16 * RPT * 16; idx += NT) {
-        const int r = idx >> 4, c = idx & 15;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < n_valid) v = __ldcg(reinterpret_cast<const float4*>(src + (long)r * stride + c * 4));
-        *reinterpret_cast<float4*>(dst + r * XS + c * 4) = v;
+    constexpr int N = 16 * RPT * 16 / NT;             // all loads in flight before the first shared store
+    float4 v[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const int idx = threadIdx.x + i * NT, r = idx >> 4, c = idx & 15;
+        v[i] = r < n_valid ? __ldcg(reinterpret_cast<const float4*>(src + (long)r * stride + c * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const int idx = threadIdx.x + i * NT, r = idx >> 4, c = idx & 15;
+        *reinterpret_cast<float4*>(dst + r * XS + c * 4) = v[i];
     }
 }
 
