@@ -560,7 +560,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-envs", type=int, default=64, help="envs in the bounded CPU sample")
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=25)
     ap.add_argument("--extra-steps", type=int, default=10, help="timed steps of each of the other BASELINE shapes")
     ap.add_argument("--no-ppo", dest="ppo", action="store_false", help="skip the PPO-update block")
     ap.add_argument("--no-extras", dest="extras", action="store_false",

@@ -9,6 +9,7 @@
 
 #include "policy_fwd.h"
 #include "tc.cuh"
+#include "tma.cuh"
 
 using namespace tile;
 
@@ -103,40 +104,62 @@ __device__ __forceinline__ void rows_to_operand(unsigned char* sA, const float* 
     for (int i = 0; i < N; ++i) tc::store_operand4(sA, hw + i * (NT / 16), l, c[i]);
 }
 
+// Token-major tiles move by tensor-map TMA (tma.cuh): the residual stream arrives as two swizzled boxes in the dense tile
+// sD while the prologue runs, and every token-major output (x, Q / K / V, obs_rep, the cross-attention queries) leaves from
+// sD as two box stores issued by one thread, so no thread spends load / store slots on them and the store drains under the
+// next stage's MMAs.  maps.m: [0] X; BLK 0: [1..3] Q, K, V of block 1; BLK 1: [1] obs_rep, [2..] the query outputs.
 template <int BLK>
 __global__ void __launch_bounds__(NT, 2)
-enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int for_decode, const float* __restrict__ y_in) {
+enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok, int L, int for_decode, const float* __restrict__ y_in,
+             const __grid_constant__ tma::RowMaps maps) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
     const int tid = threadIdx.x;
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
-    // pull this tile's inputs, and those of the tile that will follow on this SM (CTAs start in index order, two per SM),
-    // into L2 while the prologue (TMEM allocation, barrier set-up, first weight blob) runs: the first loads of a tile
-    // are otherwise what its warps wait on longest
-    prefetch_tile_rows(b.X, tile0, n_tok, tid);
+    constexpr int TMA_T = NT - 1;        // the thread that issues the tile copies (thread 0 issues the MMAs)
+    // pull this tile's attention rows, and the inputs of the tile that will follow on this SM (CTAs start in index order,
+    // two per SM), into L2 while the prologue (TMEM allocation, barrier set-up, first weight blob) runs
     prefetch_tile_rows(y_in, tile0, n_tok, tid);
     prefetch_tile_rows(b.X, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
     prefetch_tile_rows(y_in, tile0 + (long)PF_AHEAD * tc::TR, n_tok, tid);
     Ring ring;
     if (BLK == 1 && for_decode) ring.init(s.ring, s.bars, b.w, c_tc_enc_blk1_dec, 8, 8, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
     else ring.init(s.ring, s.bars, b.w, BLK == 0 ? c_tc_enc_blk0 : c_tc_enc_blk1, 6, 6, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
+    uint64_t* x_bar = &s.bars[6];
+    if (tid == 0) mbar_init(x_bar, 1);
     tc::Ctx c;
-    tc::ctx_init(c, s);                  // ends with a CTA barrier: ring barriers are initialised
+    tc::ctx_init(c, s);                  // fences the barrier initialisations; ends with a CTA barrier
+    float* sD = s.sT;                    // dense swizzled tile: two boxes of [128][32] floats (1024-byte aligned, see tc::carve)
+    const uint32_t d0 = smem_u32(sD), d1 = smem_u32(sD + tma::BOX_FLOATS);
+    if (tid == TMA_T) {                  // residual stream -> sD
+        mbar_expect_tx(x_bar, 2 * tma::BOX_FLOATS * 4);
+        tma::load_box(d0, &maps.m[0], 0, (int)tile0, smem_u32(x_bar));
+        tma::load_box(d1, &maps.m[0], 32, (int)tile0, smem_u32(x_bar));
+    }
     ring.prefetch();
     if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[512 + i] = b.w[lay::ENC_H3 + i];
     const int row = c.row, half = c.half;
     float* sRed = s.sSmall;              // [TR][2] float2 LayerNorm partials, [512 + ...) head.3, [640 + ...) head dot partials
-    float* sTrow = s.sT + row * XS + half * 32;
     Stage st = {c, ring};
+    // sD -> the array of map mi (issued after a barrier that follows the writers' proxy fence); sD may be rewritten after
+    // tile_free() by the same thread and one more CTA barrier
+    auto store_tile = [&](int mi) {
+        if (tid == TMA_T) {
+            tma::store_box(&maps.m[mi], d0, 0, (int)tile0);
+            tma::store_box(&maps.m[mi], d1, 32, (int)tile0);
+            tma::store_commit();
+        }
+    };
+    auto tile_free = [&]() { if (tid == TMA_T) tma::store_wait_read(); };
 
-    tc::global_to_tile(s.sT, b.X + tile0 * 64, n_valid);         // residual stream
     rows_to_operand(s.sA, y_in, tile0, n_tok);                   // attention output of attn_tc.cu -> first operand
     float v[32], res[32];
     // ---- proj + residual + LN1 ------------------------------------------------------------------
     {
         const float* blob = st.run(v);
-        tc::row_load32(sTrow, res);
+        mbar_wait(x_bar, 0);                                      // the residual tile has landed
+        tma::row_load32(sD, row, half, res);
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] += res[i];
         const float rs = tc::layernorm_pair(v, sRed, row, half);
@@ -146,7 +169,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
         }
         affine32(v, blob, half);
         ring.release();
-        tc::row_store32(sTrow, v);                                // x1: residual of the MLP
+        tma::row_store32(sD, row, half, v);                       // x1: residual of the MLP (each thread rewrites what it read)
         tc::store_operand32(s.sA, row, half, v);
     }
     // ---- mlp.0 + GELU ---------------------------------------------------------------------------
@@ -161,7 +184,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     // ---- mlp.2 + residual + LN2 -----------------------------------------------------------------
     {
         const float* blob = st.run(v);
-        tc::row_load32(sTrow, res);
+        tma::row_load32(sD, row, half, res);
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] += res[i];
         const float rs = tc::layernorm_pair(v, sRed, row, half);
@@ -171,28 +194,29 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
         }
         affine32(v, blob, half);
         ring.release();
-        tc::row_store32(sTrow, v);                                // block output
+        tma::row_store32(sD, row, half, v);                       // block output
         tc::store_operand32(s.sA, row, half, v);
     }
-    // outputs that go to token-major global memory are staged through sT so that the stores coalesce
-    auto staged_out = [&](float* gdst) {
-        tc::row_store32(sTrow, v);
+    // a stage result -> sD -> global: the writers fence towards the async proxy, a barrier, one thread stores
+    auto tile_out = [&](int mi) {
+        tma::row_store32(sD, row, half, v);
+        tc::fence_proxy_async();
         __syncthreads();
-        tc::tile_to_global(gdst + tile0 * 64, s.sT, n_valid);
+        store_tile(mi);
     };
     if (BLK == 0) {
-        float* outs[3] = {tb.on ? tb.e_q[1] : b.Q, b.K[1], b.V[1]};
 #pragma unroll
         for (int o = 0; o < 3; ++o) {
             const float* blob = ring.acquire();
-            tc::gemm_issue(c, blob);                              // barrier: sT holds the complete previous output
+            if (o > 0) tile_free();                               // before the barrier inside gemm_issue
+            tc::gemm_issue(c, blob);                              // proxy fence + barrier: sD holds the complete previous output
             ring.prefetch();
-            if (o == 0) tc::tile_to_global(b.X + tile0 * 64, s.sT, n_valid);
+            if (o == 0) store_tile(0);                            // x2 -> X
             tc::gemm_result(c, v);
             add_bias32(v, blob, half);
             ring.release();
-            if (o == 0) __syncthreads();                          // every thread is done reading x2 from sT
-            staged_out(outs[o]);
+            if (o == 0) { tile_free(); __syncthreads(); }         // the X store has read sD
+            tile_out(1 + o);
         }
     } else {
         // ---- value head: Linear -> GELU -> LN -> Linear(64 -> 1) --------------------------------------
@@ -200,7 +224,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
             const float* blob = ring.acquire();
             tc::gemm_issue(c, blob);
             ring.prefetch();
-            tc::tile_to_global(b.rep + tile0 * 64, s.sT, n_valid);
+            store_tile(1);                                        // x2 -> obs_rep
             tc::gemm_result(c, v);
             add_bias32(v, blob, half);
             if (tb.on) save_row32(tb.e_hh, tile0, row, half, n_valid, v);
@@ -219,21 +243,24 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
             for (int i = 0; i < 32; ++i) d = fmaf(v[i], w3[i], d);
             float* sDot = s.sSmall + 640;                         // clear of the LayerNorm exchange [0, 512) other rows may still read
             sDot[row * 2 + half] = d;
-            __syncthreads();                                      // also: the rep store above has drained sT
+            tile_free();                                          // the obs_rep store has read sD
+            __syncthreads();
             if (half == 0 && row < n_valid) values[tile0 + row] = sDot[row * 2] + sDot[row * 2 + 1] + s.sSmall[512 + 64];
         }
         // ---- cross-attention queries from obs_rep (operand still holds it) ------------------------------
         const int n_q = for_decode ? 4 : 2;
         for (int o = 0; o < n_q; ++o) {
             const float* blob = ring.acquire();
+            if (o > 0) tile_free();
             tc::gemm_issue(c, blob);
             ring.prefetch();
             tc::gemm_result(c, v);
             add_bias32(v, blob, half);
             ring.release();
-            staged_out(for_decode ? b.Q2p[o >> 1][o & 1] : b.Q2[o]);
+            tile_out(2 + o);
         }
     }
+    tile_free();                                                  // shared memory must outlive the last store's reads
     tc::ctx_fini(c);
 }
 
@@ -552,12 +579,23 @@ int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     CUDA_TRY(cudaFuncSetAttribute(enc_block_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
+    int rc;
     for (int blk = 0; blk < 2; ++blk) {
         float* y = tb.on ? tb.e_y[blk] : b.Y;
-        int rc = launch_attn_tc(tb.on ? tb.e_q[blk] : b.Q, b.K[blk], b.V[blk], y, tb.on ? tb.e_lse[blk] : nullptr, n_tok / L, L, 0, n_sm, st);
-        if (rc) return rc;
-        if (blk == 0) enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0, y);
-        else enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode, y);
+        if ((rc = launch_attn_tc(tb.on ? tb.e_q[blk] : b.Q, b.K[blk], b.V[blk], y, tb.on ? tb.e_lse[blk] : nullptr, n_tok / L, L, 0, n_sm, st)))
+            return rc;
+        tma::RowMaps maps;
+        const float* outs[tma::MAX_MAPS] = {b.X, nullptr, nullptr, nullptr, nullptr, nullptr};
+        if (blk == 0) { outs[1] = tb.on ? tb.e_q[1] : b.Q; outs[2] = b.K[1]; outs[3] = b.V[1]; }
+        else {
+            outs[1] = b.rep;
+            if (for_decode) { outs[2] = b.Q2p[0][0]; outs[3] = b.Q2p[0][1]; outs[4] = b.Q2p[1][0]; outs[5] = b.Q2p[1][1]; }
+            else { outs[2] = b.Q2[0]; outs[3] = b.Q2[1]; }
+        }
+        for (int i = 0; i < tma::MAX_MAPS; ++i)
+            if ((rc = tma::rows_map(&maps.m[i], outs[i], n_tok))) return rc;
+        if (blk == 0) enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0, y, maps);
+        else enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode, y, maps);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
