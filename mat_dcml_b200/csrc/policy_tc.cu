@@ -104,6 +104,42 @@ __device__ __forceinline__ void rows_to_operand(unsigned char* sA, const float* 
     for (int i = 0; i < N; ++i) tc::store_operand4(sA, hw + i * (NT / 16), l, c[i]);
 }
 
+// The dense swizzled tile of a CTA (tma.cuh) and the launch's tensor maps: loads and stores of whole token-major tiles by
+// one thread (the last: thread 0 issues the MMAs).  A store may be issued after a CTA barrier that follows the writers'
+// proxy fence; the tile may be rewritten after free() by the issuing thread and one more CTA barrier.
+struct TileIO {
+    float* sD;
+    uint32_t d0, d1;
+    const tma::RowMaps* maps;
+    int tile0;
+    bool issuer;
+    __device__ __forceinline__ void init(float* tile, const tma::RowMaps* m, long t0) {
+        sD = tile; d0 = smem_u32(tile); d1 = smem_u32(tile + tma::BOX_FLOATS); maps = m; tile0 = (int)t0; issuer = threadIdx.x == NT - 1;
+    }
+    __device__ __forceinline__ void load(int mi, uint64_t* bar) const {          // completes on `bar` (32 KB of transaction bytes)
+        if (issuer) {
+            mbar_expect_tx(bar, 2 * tma::BOX_FLOATS * 4);
+            tma::load_box(d0, &maps->m[mi], 0, tile0, smem_u32(bar));
+            tma::load_box(d1, &maps->m[mi], 32, tile0, smem_u32(bar));
+        }
+    }
+    __device__ __forceinline__ void store(int mi) const {
+        if (issuer) {
+            tma::store_box(&maps->m[mi], d0, 0, tile0);
+            tma::store_box(&maps->m[mi], d1, 32, tile0);
+            tma::store_commit();
+        }
+    }
+    __device__ __forceinline__ void free() const { if (issuer) tma::store_wait_read(); }
+    // a stage result -> tile -> global
+    __device__ __forceinline__ void out(int mi, int row, int half, const float (&v)[32]) const {
+        tma::row_store32(sD, row, half, v);
+        tc::fence_proxy_async();
+        __syncthreads();
+        store(mi);
+    }
+};
+
 // Token-major tiles move by tensor-map TMA (tma.cuh): the residual stream arrives as two swizzled boxes in the dense tile
 // sD while the prologue runs, and every token-major output (x, Q / K / V, obs_rep, the cross-attention queries) leaves from
 // sD as two box stores issued by one thread, so no thread spends load / store slots on them and the store drains under the
@@ -117,7 +153,6 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     const int tid = threadIdx.x;
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
-    constexpr int TMA_T = NT - 1;        // the thread that issues the tile copies (thread 0 issues the MMAs)
     // pull this tile's attention rows, and the inputs of the tile that will follow on this SM (CTAs start in index order,
     // two per SM), into L2 while the prologue (TMEM allocation, barrier set-up, first weight blob) runs
     prefetch_tile_rows(y_in, tile0, n_tok, tid);
@@ -130,29 +165,15 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
     if (tid == 0) mbar_init(x_bar, 1);
     tc::Ctx c;
     tc::ctx_init(c, s);                  // fences the barrier initialisations; ends with a CTA barrier
-    float* sD = s.sT;                    // dense swizzled tile: two boxes of [128][32] floats (1024-byte aligned, see tc::carve)
-    const uint32_t d0 = smem_u32(sD), d1 = smem_u32(sD + tma::BOX_FLOATS);
-    if (tid == TMA_T) {                  // residual stream -> sD
-        mbar_expect_tx(x_bar, 2 * tma::BOX_FLOATS * 4);
-        tma::load_box(d0, &maps.m[0], 0, (int)tile0, smem_u32(x_bar));
-        tma::load_box(d1, &maps.m[0], 32, (int)tile0, smem_u32(x_bar));
-    }
+    TileIO io;
+    io.init(s.sT, &maps, tile0);         // dense swizzled tile: two boxes of [128][32] floats (1024-byte aligned, see tc::carve)
+    float* sD = io.sD;
+    io.load(0, x_bar);                   // residual stream -> sD
     ring.prefetch();
     if (BLK == 1) for (int i = tid; i < lay::ENC_H3_SIZE; i += NT) s.sSmall[512 + i] = b.w[lay::ENC_H3 + i];
     const int row = c.row, half = c.half;
     float* sRed = s.sSmall;              // [TR][2] float2 LayerNorm partials, [512 + ...) head.3, [640 + ...) head dot partials
     Stage st = {c, ring};
-    // sD -> the array of map mi (issued after a barrier that follows the writers' proxy fence); sD may be rewritten after
-    // tile_free() by the same thread and one more CTA barrier
-    auto store_tile = [&](int mi) {
-        if (tid == TMA_T) {
-            tma::store_box(&maps.m[mi], d0, 0, (int)tile0);
-            tma::store_box(&maps.m[mi], d1, 32, (int)tile0);
-            tma::store_commit();
-        }
-    };
-    auto tile_free = [&]() { if (tid == TMA_T) tma::store_wait_read(); };
-
     rows_to_operand(s.sA, y_in, tile0, n_tok);                   // attention output of attn_tc.cu -> first operand
     float v[32], res[32];
     // ---- proj + residual + LN1 ------------------------------------------------------------------
@@ -197,26 +218,19 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
         tma::row_store32(sD, row, half, v);                       // block output
         tc::store_operand32(s.sA, row, half, v);
     }
-    // a stage result -> sD -> global: the writers fence towards the async proxy, a barrier, one thread stores
-    auto tile_out = [&](int mi) {
-        tma::row_store32(sD, row, half, v);
-        tc::fence_proxy_async();
-        __syncthreads();
-        store_tile(mi);
-    };
     if (BLK == 0) {
 #pragma unroll
         for (int o = 0; o < 3; ++o) {
             const float* blob = ring.acquire();
-            if (o > 0) tile_free();                               // before the barrier inside gemm_issue
+            if (o > 0) io.free();                               // before the barrier inside gemm_issue
             tc::gemm_issue(c, blob);                              // proxy fence + barrier: sD holds the complete previous output
             ring.prefetch();
-            if (o == 0) store_tile(0);                            // x2 -> X
+            if (o == 0) io.store(0);                            // x2 -> X
             tc::gemm_result(c, v);
             add_bias32(v, blob, half);
             ring.release();
-            if (o == 0) { tile_free(); __syncthreads(); }         // the X store has read sD
-            tile_out(1 + o);
+            if (o == 0) { io.free(); __syncthreads(); }         // the X store has read sD
+            io.out(1 + o, row, half, v);
         }
     } else {
         // ---- value head: Linear -> GELU -> LN -> Linear(64 -> 1) --------------------------------------
@@ -224,7 +238,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
             const float* blob = ring.acquire();
             tc::gemm_issue(c, blob);
             ring.prefetch();
-            store_tile(1);                                        // x2 -> obs_rep
+            io.store(1);                                        // x2 -> obs_rep
             tc::gemm_result(c, v);
             add_bias32(v, blob, half);
             if (tb.on) save_row32(tb.e_hh, tile0, row, half, n_valid, v);
@@ -243,7 +257,7 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
             for (int i = 0; i < 32; ++i) d = fmaf(v[i], w3[i], d);
             float* sDot = s.sSmall + 640;                         // clear of the LayerNorm exchange [0, 512) other rows may still read
             sDot[row * 2 + half] = d;
-            tile_free();                                          // the obs_rep store has read sD
+            io.free();                                          // the obs_rep store has read sD
             __syncthreads();
             if (half == 0 && row < n_valid) values[tile0 + row] = sDot[row * 2] + sDot[row * 2 + 1] + s.sSmall[512 + 64];
         }
@@ -251,42 +265,40 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
         const int n_q = for_decode ? 4 : 2;
         for (int o = 0; o < n_q; ++o) {
             const float* blob = ring.acquire();
-            if (o > 0) tile_free();
+            if (o > 0) io.free();
             tc::gemm_issue(c, blob);
             ring.prefetch();
             tc::gemm_result(c, v);
             add_bias32(v, blob, half);
             ring.release();
-            tile_out(2 + o);
+            io.out(2 + o, row, half, v);
         }
     }
-    tile_free();                                                  // shared memory must outlive the last store's reads
+    io.free();                                                  // shared memory must outlive the last store's reads
     tc::ctx_fini(c);
 }
 
-// Tail shared by the kernels that end with three projections of the tile in the operand (x in sT):
-// x -> x_dst0 / x_dst1 (token-major), then out[o] = x . W_o + b_o for the next three ring blobs.
-__device__ __forceinline__ void qkv_tail(tc::Ctx& c, Ring& ring, const tc::Smem& s, float* sTrow, long tile0, int n_valid,
-                                         float* x_dst0, float* x_dst1, float* out0, float* out1, float* out2) {
+// Tail shared by the kernels that end with three projections of the tile in the operand (x also in the dense tile):
+// x -> maps mx0 / mx1 (token-major; mx1 < 0: none), then out[o] = x . W_o + b_o for the next three ring blobs -> maps mo + o.
+__device__ __forceinline__ void qkv_tail(tc::Ctx& c, Ring& ring, const TileIO& io, int mx0, int mx1, int mo) {
     float v[32];
-    float* outs[3] = {out0, out1, out2};
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
         const float* blob = ring.acquire();
-        tc::gemm_issue(c, blob);                              // barrier: sT holds the complete previous output
+        if (o > 0) io.free();                                 // before the barrier inside gemm_issue
+        tc::gemm_issue(c, blob);                              // proxy fence + barrier: the tile holds the complete previous output
         ring.prefetch();
         if (o == 0) {
-            if (x_dst0) tc::tile_to_global(x_dst0 + tile0 * 64, s.sT, n_valid);
-            if (x_dst1) tc::tile_to_global(x_dst1 + tile0 * 64, s.sT, n_valid);
+            io.store(mx0);
+            if (mx1 >= 0) io.store(mx1);
         }
         tc::gemm_result(c, v);
         add_bias32(v, blob, c.half);
         ring.release();
-        if (o == 0) __syncthreads();                          // every thread is done reading x from sT
-        tc::row_store32(sTrow, v);
-        __syncthreads();
-        tc::tile_to_global(outs[o] + tile0 * 64, s.sT, n_valid);
+        if (o == 0) { io.free(); __syncthreads(); }           // the x stores have read the tile
+        io.out(mo + o, c.row, c.half, v);
     }
+    io.free();                                                // shared memory must outlive the last store's reads
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -295,7 +307,7 @@ __device__ __forceinline__ void qkv_tail(tc::Ctx& c, Ring& ring, const tc::Smem&
 // (one thread per row and column half), the three projections on the tensor cores.
 // -------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NT, 2)
-enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_tok, int obs_dim) {
+enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long n_tok, int obs_dim, const __grid_constant__ tma::RowMaps maps) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
     const int tid = threadIdx.x;
@@ -321,7 +333,6 @@ enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long
     }
     ring.prefetch();
     const int row = c.row, half = c.half;
-    float* sTrow = s.sT + row * XS + half * 32;
     float v[32];
     {
         const long g = tile0 + row;
@@ -366,9 +377,11 @@ enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long
         for (int i = 0; i < 32; ++i) v[i] += lw[i];
     }
     __syncthreads();                                       // every thread is done with the parameters in sT
-    tc::row_store32(sTrow, v);
+    TileIO io;
+    io.init(s.sT, &maps, tile0);
+    tma::row_store32(io.sD, row, half, v);
     tc::store_operand32(s.sA, row, half, v);
-    qkv_tail(c, ring, s, sTrow, tile0, n_valid, b.X, tb.on ? tb.e_x0 : nullptr, tb.on ? tb.e_q[0] : b.Q, b.K[0], b.V[0]);
+    qkv_tail(c, ring, io, 0, tb.on ? 1 : -1, 2);          // maps: X, e_x0, Q, K, V of block 0
     tc::ctx_fini(c);
 }
 
@@ -377,7 +390,7 @@ enc_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ obs, long
 // (transformer_act.py:103-111,176-181)
 // -------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NT, 2)
-dec_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, long n_tok, int L) {
+dec_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, long n_tok, int L, const __grid_constant__ tma::RowMaps maps) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
     const long tile0 = (long)blockIdx.x * tc::TR;
@@ -389,43 +402,48 @@ dec_embed_qkv_tc(PolicyBufs b, TrainBufs tb, const float* __restrict__ actions, 
     tc::ctx_init(c, s);
     ring.prefetch();
     const int row = c.row, half = c.half;
-    float* sTrow = s.sT + row * XS + half * 32;
+    TileIO io;
+    io.init(s.sT, &maps, tile0);
     {
         const long g = tile0 + row;
         int code = 0;
         if (g < n_tok) code = (g % L) == 0 ? 1 : (actions[g - 1] != 0.f ? 3 : 2);
         float v[32];
         tc::row_load32(s.sSmall + 512 + code * 64 + half * 32, v);
-        tc::row_store32(sTrow, v);
+        tma::row_store32(io.sD, row, half, v);
         tc::store_operand32(s.sA, row, half, v);
     }
-    qkv_tail(c, ring, s, sTrow, tile0, n_valid, b.X, tb.on ? tb.d_x0 : nullptr, tb.on ? tb.d_q1[0] : b.Q, b.K1[0], b.V1[0]);
+    qkv_tail(c, ring, io, 0, tb.on ? 1 : -1, 2);          // maps: X, d_x0, Q1, K1, V1 of block 0
     tc::ctx_fini(c);
 }
 
 // decoder block, first half: causal self-attention + proj + LN1, then K2 / V2 of the result
 // (ma_transformer.py:113 and the key/value side of :114)
 __global__ void __launch_bounds__(NT, 2)
-dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float* __restrict__ y_in) {
+dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float* __restrict__ y_in, const __grid_constant__ tma::RowMaps maps) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
     const long tile0 = (long)blockIdx.x * tc::TR;
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
     Ring ring;
     ring.init(s.ring, s.bars, b.w, c_tc_dec_attn1[blk], 3, 3, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
+    uint64_t* x_bar = &s.bars[6];
+    if (threadIdx.x == 0) mbar_init(x_bar, 1);
     tc::Ctx c;
     tc::ctx_init(c, s);
+    TileIO io;
+    io.init(s.sT, &maps, tile0);                              // maps: X, K2, V2 of this block
+    io.load(0, x_bar);                                        // residual stream
     ring.prefetch();
     const int row = c.row, half = c.half;
     float* sRed = s.sSmall;
-    float* sTrow = s.sT + row * XS + half * 32;
-    tc::global_to_tile(s.sT, b.X + tile0 * 64, n_valid);
     rows_to_operand(s.sA, y_in, tile0, n_tok);
     float v[32], res[32];
     Stage st = {c, ring};
     {
         const float* blob = st.run(v);
-        tc::row_load32(sTrow, res);
+        mbar_wait(x_bar, 0);
+        tma::row_load32(io.sD, row, half, res);
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] += res[i];
         const float rs = tc::layernorm_pair(v, sRed, row, half);
@@ -437,19 +455,18 @@ dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float
         ring.release();
         tc::store_operand32(s.sA, row, half, v);                  // x1: input of the cross-attention keys / values
     }
-    float* outs[2] = {b.K2[blk], b.V2[blk]};
 #pragma unroll
     for (int o = 0; o < 2; ++o) {
         const float* blob = ring.acquire();
+        if (o > 0) io.free();
         tc::gemm_issue(c, blob);                                  // barrier: residual reads / previous store are done
         ring.prefetch();
         tc::gemm_result(c, v);
         add_bias32(v, blob, half);
         ring.release();
-        tc::row_store32(sTrow, v);
-        __syncthreads();
-        tc::tile_to_global(outs[o] + tile0 * 64, s.sT, n_valid);
+        io.out(1 + o, row, half, v);
     }
+    io.free();
     tc::ctx_fini(c);
 }
 
@@ -457,7 +474,8 @@ dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float
 // block 0 then emits QKV1 of block 1, block 1 the logits head and the per-token log-prob / entropy.
 __global__ void __launch_bounds__(NT, 2)
 dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ actions, const float* __restrict__ ava,
-             float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, const float* __restrict__ y_in) {
+             float* __restrict__ logp, float* __restrict__ entropy, long n_tok, int L, int n_disc, const float* __restrict__ y_in,
+             const __grid_constant__ tma::RowMaps maps) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     tc::Smem s = tc::carve(smem_raw, TC_DEPTH);
     const int tid = threadIdx.x;
@@ -465,20 +483,24 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
     const int n_valid = (int)min((long)tc::TR, n_tok - tile0);
     Ring ring;
     ring.init(s.ring, s.bars, b.w, c_tc_dec_attn2[blk], blk == 0 ? 6 : 4, blk == 0 ? 6 : 4, TC_DEPTH, lay::BLOB_BYTES, tc::SLOT_F, NT - 1);
+    uint64_t* x_bar = &s.bars[6];
+    if (tid == 0) mbar_init(x_bar, 1);
     tc::Ctx c;
     tc::ctx_init(c, s);
+    TileIO io;
+    io.init(s.sT, &maps, tile0);                              // maps: obs_rep; block 0: X, Q1 / K1 / V1 of block 1
+    io.load(0, x_bar);                                        // obs_rep: the residual of LN2
     ring.prefetch();
     if (blk == 1) for (int i = tid; i < lay::DEC_H3_SIZE; i += NT) s.sSmall[512 + i] = b.w[lay::DEC_H3 + i];
     const int row = c.row, half = c.half;
     float* sRed = s.sSmall;
-    float* sTrow = s.sT + row * XS + half * 32;
-    tc::global_to_tile(s.sT, b.rep + tile0 * 64, n_valid);
     rows_to_operand(s.sA, y_in, tile0, n_tok);
     float v[32], res[32];
     Stage st = {c, ring};
     {   // proj + obs_rep + LN2
         const float* blob = st.run(v);
-        tc::row_load32(sTrow, res);
+        mbar_wait(x_bar, 0);
+        tma::row_load32(io.sD, row, half, res);
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] += res[i];
         const float rs = tc::layernorm_pair(v, sRed, row, half);
@@ -488,7 +510,7 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
         }
         affine32(v, blob, half);
         ring.release();
-        tc::row_store32(sTrow, v);
+        tma::row_store32(io.sD, row, half, v);
         tc::store_operand32(s.sA, row, half, v);
     }
     {   // mlp.0 + GELU
@@ -501,7 +523,7 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
     }
     {   // mlp.2 + residual + LN3
         const float* blob = st.run(v);
-        tc::row_load32(sTrow, res);
+        tma::row_load32(io.sD, row, half, res);
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] += res[i];
         const float rs = tc::layernorm_pair(v, sRed, row, half);
@@ -511,11 +533,11 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
         }
         affine32(v, blob, half);
         ring.release();
-        tc::row_store32(sTrow, v);
+        tma::row_store32(io.sD, row, half, v);
         tc::store_operand32(s.sA, row, half, v);
     }
     if (blk == 0) {
-        qkv_tail(c, ring, s, sTrow, tile0, n_valid, b.X, nullptr, tb.on ? tb.d_q1[1] : b.Q, b.K1[1], b.V1[1]);
+        qkv_tail(c, ring, io, 1, -1, 2);
     } else {
         // ---- logits head + per-token log-prob / entropy (transformer_act.py:112-128) -----------------------
         const float* blob = st.run(v);
@@ -565,10 +587,23 @@ dec_attn2_tc(PolicyBufs b, TrainBufs tb, int blk, const float* __restrict__ acti
 
 }  // namespace
 
+// tensor maps of up to MAX_MAPS token-major arrays of this launch (null entries are never used by the kernel)
+static int build_maps(tma::RowMaps& maps, const float* const (&arrs)[tma::MAX_MAPS], long n_tok) {
+    for (int i = 0; i < tma::MAX_MAPS; ++i) {
+        const int rc = tma::rows_map(&maps.m[i], arrs[i], n_tok);
+        if (rc) return rc;
+    }
+    return MATAS_OK;
+}
+
 int launch_enc_embed_tc(const PolicyBufs& b, const TrainBufs& tb, const float* obs, long n_tok, int obs_dim, cudaStream_t st) {
     const size_t bytes = tc::smem_bytes(TC_DEPTH);
     CUDA_TRY(cudaFuncSetAttribute(enc_embed_qkv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    enc_embed_qkv_tc<<<(unsigned)((n_tok + tc::TR - 1) / tc::TR), NT, bytes, st>>>(b, tb, obs, n_tok, obs_dim);
+    tma::RowMaps maps;
+    const float* const arrs[tma::MAX_MAPS] = {b.X, tb.on ? tb.e_x0 : nullptr, tb.on ? tb.e_q[0] : b.Q, b.K[0], b.V[0], nullptr};
+    const int rc = build_maps(maps, arrs, n_tok);
+    if (rc) return rc;
+    enc_embed_qkv_tc<<<(unsigned)((n_tok + tc::TR - 1) / tc::TR), NT, bytes, st>>>(b, tb, obs, n_tok, obs_dim, maps);
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }
@@ -585,15 +620,10 @@ int launch_enc_blocks_tc(const PolicyBufs& b, const TrainBufs& tb, float* values
         if ((rc = launch_attn_tc(tb.on ? tb.e_q[blk] : b.Q, b.K[blk], b.V[blk], y, tb.on ? tb.e_lse[blk] : nullptr, n_tok / L, L, 0, n_sm, st)))
             return rc;
         tma::RowMaps maps;
-        const float* outs[tma::MAX_MAPS] = {b.X, nullptr, nullptr, nullptr, nullptr, nullptr};
-        if (blk == 0) { outs[1] = tb.on ? tb.e_q[1] : b.Q; outs[2] = b.K[1]; outs[3] = b.V[1]; }
-        else {
-            outs[1] = b.rep;
-            if (for_decode) { outs[2] = b.Q2p[0][0]; outs[3] = b.Q2p[0][1]; outs[4] = b.Q2p[1][0]; outs[5] = b.Q2p[1][1]; }
-            else { outs[2] = b.Q2[0]; outs[3] = b.Q2[1]; }
-        }
-        for (int i = 0; i < tma::MAX_MAPS; ++i)
-            if ((rc = tma::rows_map(&maps.m[i], outs[i], n_tok))) return rc;
+        const float* const blk0[tma::MAX_MAPS] = {b.X, tb.on ? tb.e_q[1] : b.Q, b.K[1], b.V[1], nullptr, nullptr};
+        const float* const blk1d[tma::MAX_MAPS] = {b.X, b.rep, b.Q2p[0][0], b.Q2p[0][1], b.Q2p[1][0], b.Q2p[1][1]};
+        const float* const blk1[tma::MAX_MAPS] = {b.X, b.rep, b.Q2[0], b.Q2[1], nullptr, nullptr};
+        if ((rc = build_maps(maps, blk == 0 ? blk0 : (for_decode ? blk1d : blk1), n_tok))) return rc;
         if (blk == 0) enc_block_tc<0><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, 0, y, maps);
         else enc_block_tc<1><<<grid, NT, bytes, st>>>(b, tb, values, n_tok, L, for_decode, y, maps);
     }
@@ -610,15 +640,28 @@ int launch_teacher_forced_tc(const PolicyBufs& b, const TrainBufs& tb, const flo
     const unsigned grid = (unsigned)((n_tok + tc::TR - 1) / tc::TR);
     const long n_env = n_tok / L;
     int rc;
-    dec_embed_qkv_tc<<<grid, NT, bytes, st>>>(b, tb, actions, n_tok, L);
+    tma::RowMaps maps;
+    {
+        const float* const arrs[tma::MAX_MAPS] = {b.X, tb.on ? tb.d_x0 : nullptr, tb.on ? tb.d_q1[0] : b.Q, b.K1[0], b.V1[0], nullptr};
+        if ((rc = build_maps(maps, arrs, n_tok))) return rc;
+    }
+    dec_embed_qkv_tc<<<grid, NT, bytes, st>>>(b, tb, actions, n_tok, L, maps);
     for (int blk = 0; blk < 2; ++blk) {
         float* y = tb.on ? tb.d_y1[blk] : b.Y;
         if ((rc = launch_attn_tc(tb.on ? tb.d_q1[blk] : b.Q, b.K1[blk], b.V1[blk], y, tb.on ? tb.d_lse1[blk] : nullptr, n_env, L, 1, n_sm, st)))
             return rc;
-        dec_attn1_tc<<<grid, NT, bytes, st>>>(b, tb, blk, n_tok, L, y);
+        {
+            const float* const arrs[tma::MAX_MAPS] = {b.X, b.K2[blk], b.V2[blk], nullptr, nullptr, nullptr};
+            if ((rc = build_maps(maps, arrs, n_tok))) return rc;
+        }
+        dec_attn1_tc<<<grid, NT, bytes, st>>>(b, tb, blk, n_tok, L, y, maps);
         y = tb.on ? tb.d_y2[blk] : b.Y;
         if ((rc = launch_attn_tc(b.Q2[blk], b.K2[blk], b.V2[blk], y, tb.on ? tb.d_lse2[blk] : nullptr, n_env, L, 1, n_sm, st))) return rc;
-        dec_attn2_tc<<<grid, NT, bytes, st>>>(b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, y);
+        {
+            const float* const arrs[tma::MAX_MAPS] = {b.rep, b.X, tb.on ? tb.d_q1[1] : b.Q, b.K1[1], b.V1[1], nullptr};
+            if ((rc = build_maps(maps, arrs, n_tok))) return rc;
+        }
+        dec_attn2_tc<<<grid, NT, bytes, st>>>(b, tb, blk, actions, ava, logp, entropy, n_tok, L, n_disc, y, maps);
     }
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
