@@ -131,8 +131,12 @@ struct TileIO {
         }
     }
     __device__ __forceinline__ void free() const { if (issuer) tma::store_wait_read(); }
-    // a stage result -> tile -> global
+    // a stage result -> tile -> global.  The wait for the previous store's reads sits here, a stage's MMA round trip and
+    // accumulator read after that store was issued (a 32 KB store takes ~1,500 cycles to leave shared memory), not before
+    // the stage's first barrier.
     __device__ __forceinline__ void out(int mi, int row, int half, const float (&v)[32]) const {
+        free();
+        __syncthreads();
         tma::row_store32(sD, row, half, v);
         tc::fence_proxy_async();
         __syncthreads();
@@ -222,14 +226,12 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
 #pragma unroll
         for (int o = 0; o < 3; ++o) {
             const float* blob = ring.acquire();
-            if (o > 0) io.free();                               // before the barrier inside gemm_issue
-            tc::gemm_issue(c, blob);                              // proxy fence + barrier: sD holds the complete previous output
+            tc::gemm_issue(c, blob);                              // proxy fence + barrier: sD holds the complete x2
             ring.prefetch();
-            if (o == 0) io.store(0);                            // x2 -> X
+            if (o == 0) io.store(0);                              // x2 -> X
             tc::gemm_result(c, v);
             add_bias32(v, blob, half);
             ring.release();
-            if (o == 0) { io.free(); __syncthreads(); }         // the X store has read sD
             io.out(1 + o, row, half, v);
         }
     } else {
@@ -257,7 +259,6 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
             for (int i = 0; i < 32; ++i) d = fmaf(v[i], w3[i], d);
             float* sDot = s.sSmall + 640;                         // clear of the LayerNorm exchange [0, 512) other rows may still read
             sDot[row * 2 + half] = d;
-            io.free();                                          // the obs_rep store has read sD
             __syncthreads();
             if (half == 0 && row < n_valid) values[tile0 + row] = sDot[row * 2] + sDot[row * 2 + 1] + s.sSmall[512 + 64];
         }
@@ -265,7 +266,6 @@ enc_block_tc(PolicyBufs b, TrainBufs tb, float* __restrict__ values, long n_tok,
         const int n_q = for_decode ? 4 : 2;
         for (int o = 0; o < n_q; ++o) {
             const float* blob = ring.acquire();
-            if (o > 0) io.free();
             tc::gemm_issue(c, blob);
             ring.prefetch();
             tc::gemm_result(c, v);
@@ -285,8 +285,7 @@ __device__ __forceinline__ void qkv_tail(tc::Ctx& c, Ring& ring, const TileIO& i
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
         const float* blob = ring.acquire();
-        if (o > 0) io.free();                                 // before the barrier inside gemm_issue
-        tc::gemm_issue(c, blob);                              // proxy fence + barrier: the tile holds the complete previous output
+        tc::gemm_issue(c, blob);                              // proxy fence + barrier: the tile holds the complete x
         ring.prefetch();
         if (o == 0) {
             io.store(mx0);
@@ -295,7 +294,6 @@ __device__ __forceinline__ void qkv_tail(tc::Ctx& c, Ring& ring, const TileIO& i
         tc::gemm_result(c, v);
         add_bias32(v, blob, c.half);
         ring.release();
-        if (o == 0) { io.free(); __syncthreads(); }           // the x stores have read the tile
         io.out(mo + o, c.row, c.half, v);
     }
     io.free();                                                // shared memory must outlive the last store's reads
@@ -458,8 +456,7 @@ dec_attn1_tc(PolicyBufs b, TrainBufs tb, int blk, long n_tok, int L, const float
 #pragma unroll
     for (int o = 0; o < 2; ++o) {
         const float* blob = ring.acquire();
-        if (o > 0) io.free();
-        tc::gemm_issue(c, blob);                                  // barrier: residual reads / previous store are done
+        tc::gemm_issue(c, blob);                                  // barrier: the residual reads are done
         ring.prefetch();
         tc::gemm_result(c, v);
         add_bias32(v, blob, half);

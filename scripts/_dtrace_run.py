@@ -4,8 +4,8 @@ exec(open('scripts/decode_sweep.py').read())
 from mat_dcml_b200 import _cabi
 lib = ctypes.CDLL('mat_dcml_b200/lib/libmatas_b200.so')
 buf = (ctypes.c_longlong * (3 * 256))()
-lib.matas_debug_dtrace.argtypes = [ctypes.c_void_p]
-rc = lib.matas_debug_dtrace(buf)
+lib.matas_debug_etrace.argtypes = [ctypes.c_void_p]
+rc = lib.matas_debug_etrace(buf)
 labels = json.load(open('scripts/_dtrace_labels.json'))
 out = []
 for who in range(3):
@@ -19,5 +19,5 @@ for who in range(3):
     out.append('== thread %s' % ['0', '33', '511'][who])
     for t, i in rows:
         out.append('%-22s %8d  +%d' % (labels[i], t - t0, t - prev)); prev = t
-open('gpurun_out/dtrace.txt', 'w').write('\n'.join(out))
+open('gpurun_out/etrace.txt', 'w').write('\n'.join(out))
 print('rc', rc, len(out))
