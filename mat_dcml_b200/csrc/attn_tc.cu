@@ -173,7 +173,7 @@ attn_tc_kernel(const float* __restrict__ Q, const float* __restrict__ K, const f
         // ---- a row of head h keeps columns 32 h .. 32 h + 31: the thread whose column half equals its head stores them --------
         {   // the TMEM loads are warp-collective: every thread loads its half, the store is what is predicated
             const uint32_t taddr = tmem + ((uint32_t)(row & ~31) << 16) + half * 32;
-            float4* y = reinterpret_cast<float4*>(Y + (tok0 + q) * 64 + h * 32);
+            float* y = Y + (tok0 + q) * 64 + h * 32;
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint32_t v1[16], v2[16];
@@ -181,12 +181,13 @@ attn_tc_kernel(const float* __restrict__ Q, const float* __restrict__ K, const f
                 TC_LD16(v2, taddr + 64 + c * 16);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (row_live && half == h) {
+                    float o[16];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        y[c * 4 + j] = make_float4(fmaf(__uint_as_float(v2[4 * j]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j])),
-                                                   fmaf(__uint_as_float(v2[4 * j + 1]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 1])),
-                                                   fmaf(__uint_as_float(v2[4 * j + 2]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 2])),
-                                                   fmaf(__uint_as_float(v2[4 * j + 3]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 3])));
+                    for (int i = 0; i < 16; ++i) o[i] = fmaf(__uint_as_float(v2[i]), 1.0f / 2048.0f, __uint_as_float(v1[i]));
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)                  // whole 32-byte sectors (thread-per-row: 128 bytes of one token row)
+                        st_global_256(y + c * 16 + j * 8, o[j * 8], o[j * 8 + 1], o[j * 8 + 2], o[j * 8 + 3], o[j * 8 + 4], o[j * 8 + 5],
+                                      o[j * 8 + 6], o[j * 8 + 7]);
                 }
             }
         }
@@ -344,7 +345,7 @@ attn_tc_long_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
             const float inv = 1.0f / sum;
             if (lse && half == 0 && row_live) lse[(tok0 + qg) * 2 + h] = m * 0.6931471805599453f + logf(sum);
             {
-                float4* y = reinterpret_cast<float4*>(Y + (tok0 + qg) * 64 + h * 32);
+                float* y = Y + (tok0 + qg) * 64 + h * 32;
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
                     uint32_t v1[16], v2[16];
@@ -352,12 +353,13 @@ attn_tc_long_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
                     TC_LD16(v2, lane_base + 64 + c * 16);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     if (row_live && half == h) {
+                        float o[16];
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            y[c * 4 + j] = make_float4(fmaf(__uint_as_float(v2[4 * j]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j])) * inv,
-                                                       fmaf(__uint_as_float(v2[4 * j + 1]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 1])) * inv,
-                                                       fmaf(__uint_as_float(v2[4 * j + 2]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 2])) * inv,
-                                                       fmaf(__uint_as_float(v2[4 * j + 3]), 1.0f / 2048.0f, __uint_as_float(v1[4 * j + 3])) * inv);
+                        for (int i = 0; i < 16; ++i) o[i] = fmaf(__uint_as_float(v2[i]), 1.0f / 2048.0f, __uint_as_float(v1[i])) * inv;
+#pragma unroll
+                        for (int j = 0; j < 2; ++j)
+                            st_global_256(y + c * 16 + j * 8, o[j * 8], o[j * 8 + 1], o[j * 8 + 2], o[j * 8 + 3], o[j * 8 + 4], o[j * 8 + 5],
+                                          o[j * 8 + 6], o[j * 8 + 7]);
                     }
                 }
             }

@@ -80,6 +80,15 @@ __device__ __forceinline__ float erf_as(float x) {
 }
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erf_as(x * 0.70710678118654752f)); }
 
+// 256-bit global store (sm_100: st.global.v8.f32 -> STG.E.256): a thread that owns 32 or more consecutive bytes of a
+// row writes whole 32-byte sectors, where two 128-bit stores would each write half a sector of a different instruction.
+// p must be 32-byte aligned.
+__device__ __forceinline__ void st_global_256(float* p, float a, float b, float c, float d, float e, float f, float g, float h) {
+    asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "f"(e), "f"(f), "f"(g),
+                 "f"(h)
+                 : "memory");
+}
+
 // reduce over the 16 lanes of a half-warp (xor 8,4,2,1 stays inside the half)
 // Packed fp32 arithmetic (sm_100: fma.rn.f32x2 -> SASS FFMA2).  Same FLOP rate as two FFMAs but ONE issue slot
 // (measured on B200, scripts/tc/ffma2_bench.cu: 73.7 vs 72.6 TFLOP/s), which is what issue-bound loops need.

@@ -75,7 +75,12 @@ __device__ __forceinline__ void affine32(float (&v)[32], const float* __restrict
     }
 }
 __device__ __forceinline__ void save_row32(float* __restrict__ base, long tile0, int row, int half, int n_valid, const float (&v)[32]) {
-    if (base && row < n_valid) tc::row_store32(base + (tile0 + row) * 64 + half * 32, v);
+    if (base && row < n_valid) {                     // thread-per-row: 128 contiguous bytes as four whole-sector stores
+        float* p = base + (tile0 + row) * 64 + half * 32;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            st_global_256(p + j * 8, v[j * 8], v[j * 8 + 1], v[j * 8 + 2], v[j * 8 + 3], v[j * 8 + 4], v[j * 8 + 5], v[j * 8 + 6], v[j * 8 + 7]);
+    }
 }
 
 // -------------------------------------------------------------------------------------------------

@@ -269,30 +269,6 @@ __device__ __forceinline__ void row_store32(float* __restrict__ p, const float (
 #pragma unroll
     for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(p + j * 4) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
 }
-// cooperative, coalesced copies between the fp32 tile and token-major global memory
-__device__ __forceinline__ void tile_to_global(float* __restrict__ g, const float* __restrict__ sT, int n_valid) {
-    for (int idx = threadIdx.x; idx < TR * 16; idx += NT) {
-        const int r = idx >> 4, c = idx & 15;
-        if (r < n_valid) *reinterpret_cast<float4*>(g + (long)r * 64 + c * 4) = *reinterpret_cast<const float4*>(sT + r * XS + c * 4);
-    }
-}
-// All of a thread's loads are issued before its first shared store (eight 16-byte loads in flight per thread): written as
-// one load-store loop the copy ran as eight dependent global round trips, 18,000 cycles at the head of every tile.
-__device__ __forceinline__ void global_to_tile(float* __restrict__ sT, const float* __restrict__ g, int n_valid) {
-    constexpr int N = TR * 16 / NT;
-    float4 x[N];
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-        const int idx = threadIdx.x + i * NT, r = idx >> 4, c = idx & 15;
-        x[i] = r < n_valid ? __ldg(reinterpret_cast<const float4*>(g + (long)r * 64 + c * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-        const int idx = threadIdx.x + i * NT, r = idx >> 4, c = idx & 15;
-        *reinterpret_cast<float4*>(sT + r * XS + c * 4) = x[i];
-    }
-}
-
 // LayerNorm over a 64-column row held by two partner threads (32 columns each): ONE exchange of (sum, sum of squares)
 // through sRed[TR][2] float2 and ONE __syncthreads(); var = E[x^2] - mean^2 (residual sums of O(1) rows: the cancellation
 // costs a few ulp of the variance).  Two calls must be separated by a CTA barrier (every GEMM stage has one).
