@@ -69,11 +69,17 @@ bwd_qkv_dx_kernel(const float* __restrict__ packed, float* __restrict__ grad, Dx
 #pragma unroll
         for (int m = 0; m < 3; ++m) {
             // gradient tile -> operand (coalesced), column sums for the bias gradient
-            for (int r = hw; r < tc::TR; r += NT / 16) {
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (r < n_valid) v = __ldg(reinterpret_cast<const float4*>(src[m] + (tile0 + r) * 64) + l);
-                cs[m].x += v.x; cs[m].y += v.y; cs[m].z += v.z; cs[m].w += v.w;
-                tc::store_operand4(op, r, l, v);
+            constexpr int NR = tc::TR * 16 / NT;          // rows per half-warp: all loads in flight before the first use
+            float4 g4[NR];
+#pragma unroll
+            for (int i = 0; i < NR; ++i) {
+                const int r = hw + i * (NT / 16);
+                g4[i] = r < n_valid ? __ldg(reinterpret_cast<const float4*>(src[m] + (tile0 + r) * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int i = 0; i < NR; ++i) {
+                cs[m].x += g4[i].x; cs[m].y += g4[i].y; cs[m].z += g4[i].z; cs[m].w += g4[i].w;
+                tc::store_operand4(op, hw + i * (NT / 16), l, g4[i]);
             }
             tc::publish();
             if (tid == 0) {
@@ -116,11 +122,20 @@ bwd_qkv_dx_kernel(const float* __restrict__ packed, float* __restrict__ grad, Dx
             __syncthreads();
             float* dst = (o == 1) ? a.gRep : a.gX;
             const bool add = (o == 1) || KIND == 0;                 // KIND 1 main output overwrites gX
-            for (int r = hw; r < n_valid; r += NT / 16) {
-                float4 x = *stage_at(op, r, l);
-                float4* gp = reinterpret_cast<float4*>(dst + (tile0 + r) * 64) + l;
-                if (add) { const float4 g = *gp; x.x += g.x; x.y += g.y; x.z += g.z; x.w += g.w; }
-                *gp = x;
+            constexpr int NR = tc::TR * 16 / NT;
+            float4 g4[NR];                                          // the read-modify-write's reads, all in flight at once
+#pragma unroll
+            for (int i = 0; i < NR; ++i) {
+                const int r = hw + i * (NT / 16);
+                g4[i] = (add && r < n_valid) ? *(reinterpret_cast<const float4*>(dst + (tile0 + r) * 64) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int i = 0; i < NR; ++i) {
+                const int r = hw + i * (NT / 16);
+                if (r < n_valid) {
+                    const float4 x = *stage_at(op, r, l);
+                    *(reinterpret_cast<float4*>(dst + (tile0 + r) * 64) + l) = make_float4(x.x + g4[i].x, x.y + g4[i].y, x.z + g4[i].z, x.w + g4[i].w);
+                }
             }
             tc::fence_before_sync();
             __syncthreads();                                        // staging is free again (next epilogue / next tile's operand)
