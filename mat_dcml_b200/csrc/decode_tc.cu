@@ -11,6 +11,9 @@
 // then the logits head and the action pick.  All [128 x 64].[64 x 64] products are fp16 hi + scaled-lo MMAs
 // with fp32 accumulators in tensor memory (tc.cuh); epilogues are thread-per-row: warp w owns rows
 // 32*(w % 4) + lane and the 16 accumulator columns of quarter w / 4.
+// Row traffic of the stage path: the two cache rows a position produces leave through a shared fp32 tile as whole 256-byte
+// rows (tile_rows_to_cache), the block input is parked in 64 spare tensor-memory columns for the LN1 residual, obs_rep rows
+// arrive by cp.async during the attention; the weight ring is fed by the CTA's last thread (thread 0 issues the MMAs).
 // Block 0 is shorter than that: its self-attention attends over token embeddings (six possible rows), so it is a
 // softmax over token-code counts, and with the tables of x1_table_kernel / x1_spec_table_kernel (TABK = 1 / 2) its
 // x1 rows are not computed or cached per env at all: the cross-attention gathers them from an L2-resident table by

@@ -1,8 +1,10 @@
 // Tensor-core (tcgen05) token-parallel MAT-AS kernels for sm_100a: 128-token tiles, fp16
 // hi + scaled-lo operands in shared memory (tc.cuh), fp32 accumulators in tensor memory, thread-per-row
 // epilogues fusing bias / GELU / residual / LayerNorm; the attention of each block is attn_tc.cu's kernel, whose
-// output rows are this file's first GEMM operand.  Two CTAs per SM so that one CTA's attention / epilogue overlaps
-// the other's MMAs.
+// output rows are this file's first GEMM operand.  Two CTAs per SM so that one CTA's epilogue overlaps the other's MMAs.
+// Token-major [128 x 64] fp32 tiles (residual stream in, every token-major output out) move by tensor-map TMA between
+// global memory and a dense swizzled shared tile (tma.cuh, struct TileIO below); weights stream through a two-slot ring of
+// 1-D bulk copies fed by the CTA's last thread (thread 0 issues the MMAs).
 //
 // Reference semantics: EncodeBlock / Encoder of mat_src/mat/algorithms/mat/algorithm/ma_transformer.py:70-154.
 #include <stdlib.h>

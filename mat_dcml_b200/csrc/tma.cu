@@ -20,9 +20,11 @@ EncodeTiled encode_fn() {
     }
     return fn;
 }
-// the encode is pure host arithmetic, but a rollout step builds the same dozen maps every time: keep the last ones
+// the encode is pure host arithmetic, but a rollout step builds the same maps every time (15 per encoder pass, times the
+// four env slices of a host-array call): keep the last ones
+constexpr int N_CACHED = 128;
 struct Cached { const float* base; long n_rows; CUtensorMap map; };
-thread_local Cached t_cache[32];
+thread_local Cached t_cache[N_CACHED];
 thread_local int t_next = 0;
 }  // namespace
 
@@ -31,7 +33,7 @@ int rows_map(CUtensorMap* out, const float* base, long n_rows) {
         memset(out, 0, sizeof(*out));
         return MATAS_OK;
     }
-    for (int i = 0; i < 32; ++i)
+    for (int i = 0; i < N_CACHED; ++i)
         if (t_cache[i].base == base && t_cache[i].n_rows == n_rows) { *out = t_cache[i].map; return MATAS_OK; }
     EncodeTiled fn = encode_fn();
     if (!fn) {
@@ -50,7 +52,7 @@ int rows_map(CUtensorMap* out, const float* base, long n_rows) {
         return MATAS_ERR_CUDA;
     }
     Cached& c = t_cache[t_next];
-    t_next = (t_next + 1) & 31;
+    t_next = (t_next + 1) % N_CACHED;
     c.base = base; c.n_rows = n_rows; c.map = *out;
     return MATAS_OK;
 }
