@@ -152,6 +152,23 @@ int matas_policy_decode_time(matas_policy* p, double* ms_total, long* launches);
 int matas_gather_rows(int n_arrays, const float* const* src, float* const* dst, const int* width, const int* repeat,
                       const long* idx, long n_rows, void* stream);
 
+/* PPO losses and their gradients in one launch: replaces the element-wise expressions of MATTrainer.ppo_update
+ * (mat_src/mat/algorithms/mat/mat_trainer.py:121-137: importance weights, clipped surrogate, masked mean) and
+ * cal_value_loss (:54-94: clipped value prediction, ValueNorm-normalised target, huber_loss / mse_loss of
+ * mat_src/mat/utils/util.py:23-29, max of clipped and unclipped loss, masked mean), and the autograd pass through them.
+ * All arrays are device vectors of n = M * n_agent floats; `active` may be NULL when neither mask flag is set;
+ * vn_mean_std = {mean, sqrt(var)} of ValueNorm.running_mean_var() after its update (valuenorm.py:32-36,58-67), or NULL
+ * (use_valuenorm False); denominators = {policy denominator, value denominator} (active_masks.sum() or the element count:
+ * mat_trainer.py:88-91,127-132), device floats so that no host read is needed.  Outputs: g_logp = d loss / d logp and
+ * g_values = d loss / d values for loss = policy_loss + value_loss_coef * value_loss (the entropy term is linear in the
+ * entropy the policy returns), ratio = the importance weights, sums = {sum of min(surr1, surr2) * mask, sum of
+ * value loss * mask} in float64: policy_loss = -sums[0] / denominators[0], value_loss = sums[1] / denominators[1]. */
+int matas_ppo_loss(long n, const float* logp, const float* old_logp, const float* adv, const float* active, const float* values,
+                   const float* value_preds, const float* returns, const float* vn_mean_std, const float* denominators,
+                   float clip_param, float huber_delta, float value_loss_coef, int use_huber, int use_clipped_value_loss,
+                   int policy_active_masks, int value_active_masks, float* g_logp, float* g_values, float* ratio, double* sums,
+                   void* stream);
+
 /* Philox4x32-10 exactly as the kernels draw it (csrc/common.cuh; no counterpart in the reference, whose Python `random` /
  * `numpy.random` streams cannot be replayed in parallel -- see DESIGN.md "Random streams"): n device rows of
  * {counter[4], key[2]} -> n rows of 4 output words.  Test hook for the Random123 known-answer vectors. */

@@ -51,6 +51,8 @@ _SIGNATURES = {
     "matas_policy_decode_time": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_long)]),
     "matas_gather_rows": (ctypes.c_int, [ctypes.c_int, _P, _P, _P, _P, _P, ctypes.c_long, _P]),
     "matas_philox4x32_10": (ctypes.c_int, [_P, _P, ctypes.c_long, _P]),
+    "matas_ppo_loss": (ctypes.c_int, [ctypes.c_long, _P, _P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_float, ctypes.c_float, ctypes.c_float,
+                                      ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, _P, _P, _P, _P]),
     "matas_fp32_peak": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
     "dcml_env_create": (ctypes.c_int, [ctypes.POINTER(EnvCfg), _P, ctypes.POINTER(_P)]),
     "dcml_env_destroy": (ctypes.c_int, [_P]),

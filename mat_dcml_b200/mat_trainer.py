@@ -125,20 +125,26 @@ class MATTrainer:
             available_actions_batch, active_masks_batch, active_denominator=den)
         if fused and not self._use_policy_active_masks:
             dist_entropy = dist_entropy * float(action_log_probs.shape[0])       # .mean() back to a sum
-        imp_weights = torch.exp(action_log_probs - old_action_log_probs_batch)
-        surr1 = imp_weights * adv_targ
-        surr2 = torch.clamp(imp_weights, 1.0 - self.clip_param, 1.0 + self.clip_param) * adv_targ
-        if self._use_policy_active_masks:
-            policy_loss = (-torch.sum(torch.min(surr1, surr2) * active_masks_batch, dim=-1, keepdim=True)).sum() / den
+        if values.is_cuda:
+            policy_loss, value_loss, imp_weights, cnt = self._loss_backward_cuda(
+                values, action_log_probs, dist_entropy, old_action_log_probs_batch, adv_targ, value_preds_batch, return_batch,
+                active_masks_batch, den, fused, vn_moments)
         else:
-            policy_loss = -torch.sum(torch.min(surr1, surr2), dim=-1, keepdim=True).sum() / (one if fused else self._count(surr1))
-        value_loss = self.cal_value_loss(values, value_preds_batch, return_batch, active_masks_batch, vn_moments, numerator_only=fused)
-        loss = policy_loss - dist_entropy * self.entropy_coef + value_loss * self.value_loss_coef
-        loss.backward()                                              # CUDA backward -> flat gradient
+            # host tensors (the gloo tests of the sharded update): the reference's expressions, walked back by autograd
+            imp_weights = torch.exp(action_log_probs - old_action_log_probs_batch)
+            surr1 = imp_weights * adv_targ
+            surr2 = torch.clamp(imp_weights, 1.0 - self.clip_param, 1.0 + self.clip_param) * adv_targ
+            if self._use_policy_active_masks:
+                policy_loss = (-torch.sum(torch.min(surr1, surr2) * active_masks_batch, dim=-1, keepdim=True)).sum() / den
+            else:
+                policy_loss = -torch.sum(torch.min(surr1, surr2), dim=-1, keepdim=True).sum() / (one if fused else self._count(surr1))
+            value_loss = self.cal_value_loss(values, value_preds_batch, return_batch, active_masks_batch, vn_moments, numerator_only=fused)
+            loss = policy_loss - dist_entropy * self.entropy_coef + value_loss * self.value_loss_coef
+            loss.backward()                                          # CUDA backward -> flat gradient
+            cnt = active_masks_batch.sum() if self._use_policy_active_masks else torch.tensor(float(surr1.numel()), **self.tpdv)
         if fused:
             # the one collective of the update: [flat gradient | local denominator, policy / value / entropy numerators]
             comm = model.flat_grad_comm()
-            cnt = active_masks_batch.sum() if self._use_policy_active_masks else torch.tensor(float(surr1.numel()), **self.tpdv)
             comm[-4:] = torch.stack([cnt.detach(), policy_loss.detach(), value_loss.detach(), dist_entropy.detach()])
             dist.all_reduce(comm, op=dist.ReduceOp.SUM)
             inv = 1.0 / comm[-4]
@@ -157,6 +163,47 @@ class MATTrainer:
                 grad_norm = torch.sqrt(sum((p.grad ** 2).sum() for p in params))
             opt.step()
         return value_loss, grad_norm, policy_loss, dist_entropy, grad_norm, imp_weights
+
+    def _loss_backward_cuda(self, values, action_log_probs, dist_entropy, old_logp, adv, value_preds, returns, active, den, fused,
+                            vn_moments):
+        """The surrogate, the value loss and autograd's pass through them as ONE launch (``matas_ppo_loss``,
+        mat_trainer.py:54-94,121-137), then the model's backward from the three gradients.  Returns
+        (policy_loss, value_loss, importance weights, local denominator); with ``fused`` (sharded minibatch) the two losses are
+        the un-normalised numerators, as in ppo_update's collective."""
+        from . import _cabi
+        n = values.numel()
+        c = lambda t: t.contiguous().view(-1)
+        if self._use_valuenorm:
+            self._vn_update(returns, vn_moments)                     # cal_value_loss updates the running statistics first
+            mean, var = self.value_normalizer.running_mean_var()
+            vn = torch.cat([mean.view(1), torch.sqrt(var).view(1)]).to(**self.tpdv)
+        else:
+            vn = None
+        count = torch.tensor(float(n), **self.tpdv)
+        cnt = active.sum() if self._use_policy_active_masks else count
+        if fused:
+            dens = torch.ones(2, **self.tpdv)
+        else:
+            den_p = den if self._use_policy_active_masks else self._count(values)
+            den_v = den if self._use_value_active_masks else self._count(values)
+            dens = torch.stack([den_p.reshape(()), den_v.reshape(())]).to(**self.tpdv)
+        g_lp, g_v = torch.empty_like(action_log_probs), torch.empty_like(values)
+        ratio = torch.empty_like(action_log_probs)
+        sums = torch.empty(2, dtype=torch.float64, device=values.device)
+        lp, vv = action_log_probs.detach(), values.detach()
+        assert lp.is_contiguous() and vv.is_contiguous()
+        a_old, a_adv, a_act, a_vp, a_ret = c(old_logp), c(adv), c(active), c(value_preds), c(returns)
+        _cabi.check(_cabi.lib().matas_ppo_loss(
+            n, _cabi.ptr(lp), _cabi.ptr(a_old), _cabi.ptr(a_adv), _cabi.ptr(a_act), _cabi.ptr(vv), _cabi.ptr(a_vp), _cabi.ptr(a_ret),
+            _cabi.ptr(vn) if vn is not None else None, _cabi.ptr(dens), float(self.clip_param), float(self.huber_delta),
+            float(self.value_loss_coef), int(self._use_huber_loss), int(self._use_clipped_value_loss),
+            int(self._use_policy_active_masks), int(self._use_value_active_masks), _cabi.ptr(g_lp), _cabi.ptr(g_v), _cabi.ptr(ratio),
+            _cabi.ptr(sums), _cabi.stream_ptr()))
+        policy_loss = (-sums[0] / dens[0]).float()
+        value_loss = (sums[1] / dens[1]).float()
+        g_ent = torch.full_like(dist_entropy, -self.entropy_coef)
+        torch.autograd.backward([action_log_probs, values, dist_entropy], [g_lp, g_v, g_ent])   # CUDA backward -> flat gradient
+        return policy_loss, value_loss, ratio, cnt
 
     def normalize_advantages(self, adv, active):
         """mat_trainer.py:193-197: (adv - nanmean) / (nanstd + 1e-5) over active entries of the GLOBAL batch; one collective

@@ -191,3 +191,68 @@ def test_fused_clip_adam_vs_torch(max_norm, wd, cuda_device):
     assert isinstance(pol.optimizer, FlatAdam)
     pol.lr_decay(1, 2)
     assert abs(pol.optimizer.param_groups[0]["lr"] - 2.5e-4) < 1e-12
+
+
+@pytest.mark.parametrize("flags", [(1, 1, 1, 1), (0, 1, 1, 1), (1, 0, 0, 1), (1, 1, 0, 0), (0, 0, 1, 0)])
+@pytest.mark.parametrize("valuenorm", [True, False])
+def test_ppo_loss_kernel_vs_torch_autograd(flags, valuenorm, cuda_device):
+    """matas_ppo_loss (one launch: surrogate + value loss + their gradients) against the reference's element-wise expressions
+    (mat_trainer.py:54-94,121-137; util.py:23-29) walked back by torch autograd, on inputs that hit every branch: ratios inside /
+    outside / exactly on the clip bounds, exact min / max ties, errors beyond +-huber_delta, dead (masked) agents."""
+    import ctypes
+    from mat_dcml_b200 import _cabi
+    from mat_dcml_b200.mat_trainer import huber_loss, mse_loss
+    use_huber, use_clipped, pol_mask, val_mask = flags
+    dev = cuda_device
+    g = torch.Generator(device="cpu").manual_seed(5)
+    n = 40_000
+    clip, delta, vcoef = 0.2, 10.0, 0.7
+    old = torch.randn(n, 1, generator=g) * 0.5 - 1.0
+    lp = old + torch.randn(n, 1, generator=g) * 0.25
+    lp[:500] = old[:500]                                            # ratio exactly 1: min tie inside the clip range
+    lp[500:600] = old[500:600] + float(np.log(1.2))                  # (nearly) on the upper bound
+    adv = torch.randn(n, 1, generator=g)
+    adv[600:700] = 0.0                                              # both surrogates zero
+    vp = torch.randn(n, 1, generator=g) * 3
+    v = vp + torch.randn(n, 1, generator=g) * 0.3
+    v[700:900] = vp[700:900]                                        # clipped == unclipped: max tie
+    ret = torch.randn(n, 1, generator=g) * 40 - 100                  # normalised: O(1); raw: errors far beyond +-delta
+    act = (torch.rand(n, 1, generator=g) > 0.1).float()
+    lp, old, adv, vp, v, ret, act = [t.to(dev) for t in (lp, old, adv, vp, v, ret, act)]
+    mean, std = torch.tensor([-98.0], device=dev), torch.tensor([37.5], device=dev)
+    # ---- torch ----
+    lp_t, v_t = lp.clone().requires_grad_(True), v.clone().requires_grad_(True)
+    r = torch.exp(lp_t - old)
+    m = torch.min(r * adv, torch.clamp(r, 1.0 - clip, 1.0 + clip) * adv)
+    den_p = act.sum() if pol_mask else torch.tensor(float(n), device=dev)
+    den_v = act.sum() if val_mask else torch.tensor(float(n), device=dev)
+    pol_num = (m * act).sum() if pol_mask else m.sum()
+    tgt = (ret - mean) / std if valuenorm else ret
+    vc = vp + (v_t - vp).clamp(-clip, clip)
+    L = (lambda e: huber_loss(e, delta)) if use_huber else mse_loss
+    lo, lc = L(tgt - v_t), L(tgt - vc)
+    vl = torch.max(lo, lc) if use_clipped else lo
+    val_num = (vl * act).sum() if val_mask else vl.sum()
+    (-pol_num / den_p + vcoef * val_num / den_v).backward()
+    # ---- kernel ----
+    g_lp, g_v, ratio = torch.empty_like(lp), torch.empty_like(v), torch.empty_like(lp)
+    sums = torch.empty(2, dtype=torch.float64, device=dev)
+    dens = torch.stack([den_p, den_v]).float()
+    vn = torch.cat([mean, std]) if valuenorm else None
+    P = _cabi.ptr
+    _cabi.check(_cabi.lib().matas_ppo_loss(n, P(lp), P(old), P(adv), P(act), P(v), P(vp), P(ret), P(vn) if vn is not None else None, P(dens),
+                                           clip, delta, vcoef, use_huber, use_clipped, pol_mask, val_mask, P(g_lp), P(g_v), P(ratio), P(sums),
+                                           _cabi.stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.allclose(ratio, r.detach(), rtol=1e-6, atol=0)
+    pol_num, val_num = pol_num.detach(), val_num.detach()
+    assert abs(float(sums[0]) - float(pol_num)) <= 1e-5 * abs(float(pol_num)) + 1e-3
+    assert abs(float(sums[1]) - float(val_num)) <= 1e-5 * abs(float(val_num)) + 1e-3
+    scale_p, scale_v = float(lp_t.grad.abs().max()), float(v_t.grad.abs().max())
+    assert float((g_lp - lp_t.grad).abs().max()) <= 2e-6 * scale_p + 1e-12
+    assert float((g_v - v_t.grad).abs().max()) <= 2e-6 * scale_v + 1e-12
+    # branches were hit
+    rr = r.detach()
+    assert int(((rr < 1 - clip) | (rr > 1 + clip)).sum()) > 100 and int((rr == 1.0).sum()) >= 500
+    if not valuenorm and use_huber:
+        assert int(((ret - v) > delta).sum()) > 0 and int(((ret - v) < -delta).sum()) > 100
