@@ -33,7 +33,7 @@ __device__ __forceinline__ float4* stage_at(unsigned char* op, int r, int c4) {
     return reinterpret_cast<float4*>(op + r * 256 + ((c4 ^ (r & 15)) << 4));
 }
 __device__ __forceinline__ float gelu_grad(float h) {
-    const float cdf = 0.5f * (1.0f + erff(h * 0.70710678118654752f));
+    const float cdf = 0.5f * (1.0f + erf_as(h * 0.70710678118654752f));       // A&S 7.1.26: 1.5e-7 absolute
     return cdf + h * 0.3989422804014327f * expf(-0.5f * h * h);
 }
 __device__ __forceinline__ void add4(float4& a, const float4& b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }

@@ -145,7 +145,7 @@ __device__ __forceinline__ void ln_bwd(Frag& d, const Frag& xh, const float* __r
 }
 
 __device__ __forceinline__ float gelu_grad(float h) {
-    const float cdf = 0.5f * (1.0f + erff(h * 0.70710678118654752f));
+    const float cdf = 0.5f * (1.0f + erf_as(h * 0.70710678118654752f));       // A&S 7.1.26: 1.5e-7 absolute
     return cdf + h * 0.3989422804014327f * expf(-0.5f * h * h);
 }
 __device__ __forceinline__ void gelu_bwd(Frag& d, const Frag& h) {
