@@ -75,33 +75,44 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
             for (int task = tid; task < ne * nb * nb; task += nthr) {
                 const int e = task / (nb * nb), rem = task - e * nb * nb, qb = rem / nb, kb = rem - qb * nb;
                 const float* s = slot(e);
+                // S = q . k and dP = dY . v as packed fp32x2 products (two partial sums per entry: the x|z and y|w dims), one
+                // 4 x 4 block at a time so that the doubled accumulators fit the register budget
                 float as[4][4], ap[4][4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) { as[i][j] = 0.f; ap[i][j] = 0.f; }
                 const float* qp = s + qb * RS + h * 32;
                 const float* kp = s + oK + kb * RS + h * 32;
                 const float* vp = s + oV + kb * RS + h * 32;
                 const float* yp = s + oY + qb * RS + h * 32;
-#pragma unroll 2
-                for (int dc = 0; dc < 8; ++dc) {
-                    float4 q4[4], k4[4], y4[4], v4[4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        q4[i] = *reinterpret_cast<const float4*>(qp + i * nb * RS + dc * 4);
-                        y4[i] = *reinterpret_cast<const float4*>(yp + i * nb * RS + dc * 4);
-                        k4[i] = *reinterpret_cast<const float4*>(kp + i * nb * RS + dc * 4);
-                        v4[i] = *reinterpret_cast<const float4*>(vp + i * nb * RS + dc * 4);
+                for (int pass = 0; pass < 2; ++pass) {
+                    const float* ap_ = pass == 0 ? qp : yp;
+                    const float* bp_ = pass == 0 ? kp : vp;
+                    float sx[4][4], sy[4][4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { sx[i][j] = 0.f; sy[i][j] = 0.f; }
+#pragma unroll 2
+                    for (int dc = 0; dc < 8; ++dc) {
+                        float4 a4[4], b4[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            a4[i] = *reinterpret_cast<const float4*>(ap_ + i * nb * RS + dc * 4);
+                            b4[i] = *reinterpret_cast<const float4*>(bp_ + i * nb * RS + dc * 4);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                fma2(sx[i][j], sy[i][j], a4[i].x, a4[i].y, b4[j].x, b4[j].y);
+                                fma2(sx[i][j], sy[i][j], a4[i].z, a4[i].w, b4[j].z, b4[j].w);
+                            }
                     }
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            as[i][j] = fmaf(q4[i].x, k4[j].x, as[i][j]); as[i][j] = fmaf(q4[i].y, k4[j].y, as[i][j]);
-                            as[i][j] = fmaf(q4[i].z, k4[j].z, as[i][j]); as[i][j] = fmaf(q4[i].w, k4[j].w, as[i][j]);
-                            ap[i][j] = fmaf(y4[i].x, v4[j].x, ap[i][j]); ap[i][j] = fmaf(y4[i].y, v4[j].y, ap[i][j]);
-                            ap[i][j] = fmaf(y4[i].z, v4[j].z, ap[i][j]); ap[i][j] = fmaf(y4[i].w, v4[j].w, ap[i][j]);
+                            if (pass == 0) as[i][j] = sx[i][j] + sy[i][j];
+                            else ap[i][j] = sx[i][j] + sy[i][j];
                         }
                 }
                 float* sp = slot(e) + oP;
@@ -139,9 +150,9 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
                         const float4 k4 = *reinterpret_cast<const float4*>(kp + t * RS);
                         const float w[4] = {sd[t], sd[SS + t], sd[2 * SS + t], sd[3 * SS + t]};
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            acc[i][0] = fmaf(w[i], k4.x, acc[i][0]); acc[i][1] = fmaf(w[i], k4.y, acc[i][1]);
-                            acc[i][2] = fmaf(w[i], k4.z, acc[i][2]); acc[i][3] = fmaf(w[i], k4.w, acc[i][3]);
+                        for (int i = 0; i < 4; ++i) {                 // packed: scalar weight x two dims per instruction
+                            fma2(acc[i][0], acc[i][1], w[i], w[i], k4.x, k4.y);
+                            fma2(acc[i][2], acc[i][3], w[i], w[i], k4.z, k4.w);
                         }
                     }
                 } else {                               // dK / dV rows (keys) 4rb..: sum over queries t of dS|P[t][row] q_t|dY_t
@@ -154,8 +165,8 @@ attn_bwd_env_kernel(const float* __restrict__ Q, const float* __restrict__ K, co
                         const float w[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            acc[i][0] = fmaf(w[i], x4.x, acc[i][0]); acc[i][1] = fmaf(w[i], x4.y, acc[i][1]);
-                            acc[i][2] = fmaf(w[i], x4.z, acc[i][2]); acc[i][3] = fmaf(w[i], x4.w, acc[i][3]);
+                            fma2(acc[i][0], acc[i][1], w[i], w[i], x4.x, x4.y);
+                            fma2(acc[i][2], acc[i][3], w[i], w[i], x4.z, x4.w);
                         }
                     }
                 }
