@@ -570,14 +570,14 @@ static int alloc_train(matas_policy* p, long n_tok) {
         if (p->d_train) CUDA_TRY(cudaFree(p->d_train));
         p->d_train = nullptr; p->train_cap = 0;
         const long cap = n_tok + 64;
-        constexpr int WIDE = 39, NARROW = 27;
+        constexpr int WIDE = 45, NARROW = 27;
         CUDA_TRY(cudaMalloc(&p->d_train, (size_t)cap * (WIDE * 64 + NARROW + 5) * sizeof(float)));
         float* f = p->d_train;
         auto wide = [&]() { float* r = f; f += cap * 64; return r; };
         TrainBufs& t = p->tb;
         t.e_h0 = wide(); t.e_xh0 = wide(); t.e_x0 = wide(); t.d_x0 = wide(); t.e_hh = wide(); t.e_xhh = wide();
         t.d_hh = wide(); t.d_xhh = wide(); t.gX = wide(); t.gRep = wide(); t.gYa = wide(); t.gYb = wide();
-        for (int k = 0; k < 3; ++k) t.gS[k] = wide();
+        for (int k = 0; k < 9; ++k) t.gS[k] = wide();
         for (int k = 0; k < 2; ++k) {
             t.e_q[k] = wide(); t.e_y[k] = wide(); t.e_xh1[k] = wide(); t.e_m0[k] = wide(); t.e_xh2[k] = wide();
             t.d_q1[k] = wide(); t.d_y1[k] = wide(); t.d_xh1[k] = wide(); t.d_y2[k] = wide(); t.d_xh2[k] = wide();

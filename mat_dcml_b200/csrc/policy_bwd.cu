@@ -640,9 +640,10 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
     // n_agent <= 64: register-tiled attention backward (attn_bwd_tile.cu) + q/k/v input gradients on the tensor cores
     // (bwd_dx_tc.cu); larger n_agent: the half-warp-per-row attention backward inside bwd_attn with SIMT input gradients
     const bool tiled = attn_tile_supported(L);
+    float* const* S = t.gS;                              // the current set of layer-output gradient buffers (see take_set)
     auto dx = [&](int kind, int bq, int bk, int bv, int gbq, int gbk, int gbv) -> int {
         DxArgs d;
-        d.dq = t.gS[0]; d.dk = t.gS[1]; d.dv = t.gS[2];
+        d.dq = S[0]; d.dk = S[1]; d.dv = S[2];
         d.blob[0] = bq; d.blob[1] = bk; d.blob[2] = bv;
         d.gb[0] = gbq; d.gb[1] = gbk; d.gb[2] = gbv;
         d.gX = t.gX; d.gRep = t.gRep;
@@ -666,14 +667,34 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
     auto job = [](const float* dY, const float* X, int recipe, int ln, int gW) {
         DwJob j; j.dY = dY; j.X = X; j.recipe = recipe; j.ln = ln; j.gW = gW; return j;
     };
+    // The weight-gradient launches are DEFERRED: the fused kernels write their layer-output gradients into one of three
+    // rotating sets of scratch buffers, the jobs queue up, and one bwd_dw launch takes everything queued when a set is about
+    // to be reused (up to two sets = six layers per launch instead of one to three: each launch carries ~35 us of prologue,
+    // accumulator read-out and atomics whatever its size).
+    DwJobs pending; pending.n = 0;
+    int pending_set[8];
+    int cur_set = 2;
+    auto flush = [&]() -> int {
+        if (pending.n == 0) return MATAS_OK;
+        const int r = launch_bwd_dw(pk, grad, pending, n_tok, n_sm, st);
+        pending.n = 0;
+        return r;
+    };
+    auto take_set = [&]() -> int {                       // the next set becomes S; its queued jobs are launched first
+        cur_set = (cur_set + 1) % 3;
+        S = t.gS + 3 * cur_set;
+        for (int i = 0; i < pending.n; ++i)
+            if (pending_set[i] == cur_set) return flush();
+        return MATAS_OK;
+    };
     auto dw = [&](const DwJob* js, int n) -> int {
-        DwJobs J; J.n = n;
-        for (int i = 0; i < n; ++i) J.j[i] = js[i];
-        return launch_bwd_dw(pk, grad, J, n_tok, n_sm, st);
+        for (int i = 0; i < n; ++i) { pending.j[pending.n] = js[i]; pending_set[pending.n] = cur_set; ++pending.n; }
+        return MATAS_OK;
     };
 
     // ---- decoder ---------------------------------------------------------------------------------
     {
+        if ((rc = take_set())) return rc;
         HeadArgs h = {};
         h.d_a = d_logp; h.d_b = d_ent; h.actions = actions; h.ava = ava;
         h.hh = t.d_hh; h.xhh = t.d_xhh; h.rsh = t.d_rsh; h.xh_in = t.d_xh3[1]; h.rs_in = t.d_rs3[1];
@@ -681,12 +702,13 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         h.gW0 = gm.w[idx(DEC_H0)]; h.gb0 = gm.b[idx(DEC_H0)]; h.glnw = gm.lnw[idx(DEC_H0)]; h.glnb = gm.lnb[idx(DEC_H0)];
         h.gW3 = gm.dec_h3_w; h.gb3 = gm.dec_h3_b; h.glogstd = gm.log_std;
         h.gOut = t.gX; h.L = L; h.n_disc = mode == MATAS_MODE_SEMI ? L - 1 : L;
-        h.sY = t.gS[0];
+        h.sY = S[0];
         bwd_head<1><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
-        const DwJob js[1] = {job(t.gS[0], t.d_xh3[1], DW_X_AFFINE, dec_blob(1, DM2), h.gW0)};
+        const DwJob js[1] = {job(S[0], t.d_xh3[1], DW_X_AFFINE, dec_blob(1, DM2), h.gW0)};
         if ((rc = dw(js, 1))) return rc;
     }
     for (int k = 1; k >= 0; --k) {
+        if ((rc = take_set())) return rc;
         TailArgs ta = {};
         ta.gOut = t.gX; ta.xhF = t.d_xh3[k]; ta.rsF = t.d_rs3[k]; ta.m0 = t.d_m0[k]; ta.xhM = t.d_xh2[k]; ta.rsM = t.d_rs2[k];
         ta.Y = t.d_y2[k]; ta.lnF = dec_blob(k, DM2); ta.lnM = dec_blob(k, DP2);
@@ -698,14 +720,15 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(dec_blob(k, DM2))]; ta.glnFb = gm.lnb[idx(dec_blob(k, DM2))];
         ta.glnMw = gm.lnw[idx(dec_blob(k, DP2))]; ta.glnMb = gm.lnb[idx(dec_blob(k, DP2))];
         ta.gRes = t.gRep; ta.res_add = 1; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2];
+        ta.sY[0] = S[0]; ta.sY[1] = S[1]; ta.sY[2] = S[2];
         if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc;
         {
-            const DwJob js[3] = {job(t.gS[0], t.d_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.d_xh2[k], DW_X_AFFINE, dec_blob(k, DP2), ta.gW0),
-                                 job(t.gS[2], t.d_y2[k], DW_X_PLAIN, 0, ta.gWp)};
+            const DwJob js[3] = {job(S[0], t.d_m0[k], DW_X_GELU, 0, ta.gW2), job(S[1], t.d_xh2[k], DW_X_AFFINE, dec_blob(k, DP2), ta.gW0),
+                                 job(S[2], t.d_y2[k], DW_X_PLAIN, 0, ta.gWp)};
             if ((rc = dw(js, 3))) return rc;
         }
 
+        if ((rc = take_set())) return rc;
         AttnArgs a2 = {};
         a2.Q = b.Q2[k]; a2.K = b.K2[k]; a2.V = b.V2[k]; a2.lse = t.d_lse2[k]; a2.gY = t.gYa; a2.gD = t.gDa;
         a2.xh = t.d_xh1[k]; a2.rs = t.d_rs1[k]; a2.ln = dec_blob(k, DP1); a2.xin = b.rep;
@@ -714,9 +737,9 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a2.gWk = gm.w[idx(dec_blob(k, DK2))]; a2.gbk = gm.b[idx(dec_blob(k, DK2))];
         a2.gWv = gm.w[idx(dec_blob(k, DV2))]; a2.gbv = gm.b[idx(dec_blob(k, DV2))];
         a2.gX = t.gX; a2.gRep = t.gRep; a2.causal = 1; a2.L = L;
-        a2.sY[0] = t.gS[0]; a2.sY[1] = t.gS[1]; a2.sY[2] = t.gS[2];
+        a2.sY[0] = S[0]; a2.sY[1] = S[1]; a2.sY[2] = S[2];
         if (tiled) {
-            if ((rc = launch_attn_bwd_tile(a2.Q, a2.K, a2.V, a2.gY, a2.lse, a2.gD, t.gS[0], t.gS[1], t.gS[2], M, L, 1, st))) return rc;
+            if ((rc = launch_attn_bwd_tile(a2.Q, a2.K, a2.V, a2.gY, a2.lse, a2.gD, S[0], S[1], S[2], M, L, 1, st))) return rc;
             a2.pre = 1;
         }
         if (tiled) {
@@ -725,11 +748,12 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
             bwd_attn<1><<<agrid, NT, abytes, st>>>(pk, grad, a2, n_tok);   // gX = grad wrt x1 (LN1 output)
         }
         {
-            const DwJob js[3] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, a2.gWq), job(t.gS[1], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWk),
-                                 job(t.gS[2], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWv)};
+            const DwJob js[3] = {job(S[0], b.rep, DW_X_PLAIN, 0, a2.gWq), job(S[1], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWk),
+                                 job(S[2], t.d_xh1[k], DW_X_AFFINE, dec_blob(k, DP1), a2.gWv)};
             if ((rc = dw(js, 3))) return rc;
         }
 
+        if ((rc = take_set())) return rc;
         TailArgs tb = {};
         tb.gOut = t.gX; tb.xhM = t.d_xh1[k]; tb.rsM = t.d_rs1[k]; tb.Y = t.d_y1[k];
         tb.lnF = dec_blob(k, DP1); tb.lnM = dec_blob(k, DP1);
@@ -737,13 +761,14 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         tb.gWp = gm.w[idx(dec_blob(k, DP1))]; tb.gbp = gm.b[idx(dec_blob(k, DP1))];
         tb.glnMw = gm.lnw[idx(dec_blob(k, DP1))]; tb.glnMb = gm.lnb[idx(dec_blob(k, DP1))];
         tb.gRes = t.gX; tb.res_add = 0; tb.gY = t.gYb; tb.gD = t.gDb; tb.with_mlp = 0;
-        tb.sY[2] = t.gS[2];
+        tb.sY[2] = S[2];
         if ((rc = launch_bwd_mlp_tc(pk, grad, tb, n_tok, n_sm, st))) return rc;
         {
-            const DwJob js[1] = {job(t.gS[2], t.d_y1[k], DW_X_PLAIN, 0, tb.gWp)};
+            const DwJob js[1] = {job(S[2], t.d_y1[k], DW_X_PLAIN, 0, tb.gWp)};
             if ((rc = dw(js, 1))) return rc;
         }
 
+        if ((rc = take_set())) return rc;
         AttnArgs a1 = {};
         a1.Q = t.d_q1[k]; a1.K = b.K1[k]; a1.V = b.V1[k]; a1.lse = t.d_lse1[k]; a1.gY = t.gYb; a1.gD = t.gDb;
         if (k == 1) { a1.xh = t.d_xh3[0]; a1.rs = t.d_rs3[0]; a1.ln = dec_blob(0, DM2); }
@@ -753,9 +778,9 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(dec_blob(k, DK1))]; a1.gbk = gm.b[idx(dec_blob(k, DK1))];
         a1.gWv = gm.w[idx(dec_blob(k, DV1))]; a1.gbv = gm.b[idx(dec_blob(k, DV1))];
         a1.gX = t.gX; a1.causal = 1; a1.L = L;
-        a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2];
+        a1.sY[0] = S[0]; a1.sY[1] = S[1]; a1.sY[2] = S[2];
         if (tiled) {
-            if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
+            if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, S[0], S[1], S[2], M, L, a1.causal, st))) return rc;
             a1.pre = 1;
         }
         if (tiled) {
@@ -766,7 +791,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         {
             const float* X = k == 1 ? t.d_xh3[0] : t.d_x0;
             const int rcp = k == 1 ? DW_X_AFFINE : DW_X_PLAIN, ln = k == 1 ? dec_blob(0, DM2) : 0;
-            const DwJob js[3] = {job(t.gS[0], X, rcp, ln, a1.gWq), job(t.gS[1], X, rcp, ln, a1.gWk), job(t.gS[2], X, rcp, ln, a1.gWv)};
+            const DwJob js[3] = {job(S[0], X, rcp, ln, a1.gWq), job(S[1], X, rcp, ln, a1.gWk), job(S[2], X, rcp, ln, a1.gWv)};
             if ((rc = dw(js, 3))) return rc;
         }
     }
@@ -778,18 +803,20 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
     }
     // ---- encoder ---------------------------------------------------------------------------------
     {
+        if ((rc = take_set())) return rc;
         HeadArgs h = {};
         h.d_a = d_values; h.hh = t.e_hh; h.xhh = t.e_xhh; h.rsh = t.e_rsh; h.rep = b.rep;
         h.blob_h0 = ENC_H0; h.h3 = ENC_H3;
         h.gW0 = gm.w[idx(ENC_H0)]; h.gb0 = gm.b[idx(ENC_H0)]; h.glnw = gm.lnw[idx(ENC_H0)]; h.glnb = gm.lnb[idx(ENC_H0)];
         h.gW3 = gm.enc_h3_w; h.gb3 = gm.enc_h3_b; h.glogstd = -1;
         h.gOut = t.gRep; h.L = L;
-        h.sY = t.gS[0];
+        h.sY = S[0];
         bwd_head<0><<<grid, NT, bytes, st>>>(pk, grad, h, n_tok);
-        const DwJob js[1] = {job(t.gS[0], b.rep, DW_X_PLAIN, 0, h.gW0)};
+        const DwJob js[1] = {job(S[0], b.rep, DW_X_PLAIN, 0, h.gW0)};
         if ((rc = dw(js, 1))) return rc;
     }
     for (int k = 1; k >= 0; --k) {
+        if ((rc = take_set())) return rc;
         TailArgs ta = {};
         ta.gOut = k == 1 ? t.gRep : t.gX; ta.xhF = t.e_xh2[k]; ta.rsF = t.e_rs2[k]; ta.m0 = t.e_m0[k];
         ta.xhM = t.e_xh1[k]; ta.rsM = t.e_rs1[k]; ta.Y = t.e_y[k]; ta.lnF = enc_blob(k, EM2); ta.lnM = enc_blob(k, EP);
@@ -801,14 +828,15 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         ta.glnFw = gm.lnw[idx(enc_blob(k, EM2))]; ta.glnFb = gm.lnb[idx(enc_blob(k, EM2))];
         ta.glnMw = gm.lnw[idx(enc_blob(k, EP))]; ta.glnMb = gm.lnb[idx(enc_blob(k, EP))];
         ta.gRes = t.gX; ta.res_add = 0; ta.gY = t.gYa; ta.gD = t.gDa; ta.with_mlp = 1;
-        ta.sY[0] = t.gS[0]; ta.sY[1] = t.gS[1]; ta.sY[2] = t.gS[2];
+        ta.sY[0] = S[0]; ta.sY[1] = S[1]; ta.sY[2] = S[2];
         if ((rc = launch_bwd_mlp_tc(pk, grad, ta, n_tok, n_sm, st))) return rc;
         {
-            const DwJob js[3] = {job(t.gS[0], t.e_m0[k], DW_X_GELU, 0, ta.gW2), job(t.gS[1], t.e_xh1[k], DW_X_AFFINE, enc_blob(k, EP), ta.gW0),
-                                 job(t.gS[2], t.e_y[k], DW_X_PLAIN, 0, ta.gWp)};
+            const DwJob js[3] = {job(S[0], t.e_m0[k], DW_X_GELU, 0, ta.gW2), job(S[1], t.e_xh1[k], DW_X_AFFINE, enc_blob(k, EP), ta.gW0),
+                                 job(S[2], t.e_y[k], DW_X_PLAIN, 0, ta.gWp)};
             if ((rc = dw(js, 3))) return rc;
         }
 
+        if ((rc = take_set())) return rc;
         AttnArgs a1 = {};
         a1.Q = t.e_q[k]; a1.K = b.K[k]; a1.V = b.V[k]; a1.lse = t.e_lse[k]; a1.gY = t.gYa; a1.gD = t.gDa;
         if (k == 1) { a1.xh = t.e_xh2[0]; a1.rs = t.e_rs2[0]; a1.ln = enc_blob(0, EM2); }
@@ -818,9 +846,9 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         a1.gWk = gm.w[idx(enc_blob(k, EK))]; a1.gbk = gm.b[idx(enc_blob(k, EK))];
         a1.gWv = gm.w[idx(enc_blob(k, EV))]; a1.gbv = gm.b[idx(enc_blob(k, EV))];
         a1.gX = t.gX; a1.causal = 0; a1.L = L;
-        a1.sY[0] = t.gS[0]; a1.sY[1] = t.gS[1]; a1.sY[2] = t.gS[2];
+        a1.sY[0] = S[0]; a1.sY[1] = S[1]; a1.sY[2] = S[2];
         if (tiled) {
-            if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, t.gS[0], t.gS[1], t.gS[2], M, L, a1.causal, st))) return rc;
+            if ((rc = launch_attn_bwd_tile(a1.Q, a1.K, a1.V, a1.gY, a1.lse, a1.gD, S[0], S[1], S[2], M, L, a1.causal, st))) return rc;
             a1.pre = 1;
         }
         if (tiled) {
@@ -831,7 +859,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         {
             const float* X = k == 1 ? t.e_xh2[0] : t.e_x0;
             const int rcp = k == 1 ? DW_X_AFFINE : DW_X_PLAIN, ln = k == 1 ? enc_blob(0, EM2) : 0;
-            const DwJob js[3] = {job(t.gS[0], X, rcp, ln, a1.gWq), job(t.gS[1], X, rcp, ln, a1.gWk), job(t.gS[2], X, rcp, ln, a1.gWv)};
+            const DwJob js[3] = {job(S[0], X, rcp, ln, a1.gWq), job(S[1], X, rcp, ln, a1.gWk), job(S[2], X, rcp, ln, a1.gWv)};
             if ((rc = dw(js, 3))) return rc;
         }
     }
@@ -842,6 +870,7 @@ int launch_evaluate_backward(const PolicyBufs& b, const TrainBufs& t, const Grad
         e.gln7_w = gm.enc_ln7_w; e.gln7_b = gm.enc_ln7_b;
         bwd_embed_enc<<<grid, NT, bytes, st>>>(pk, grad, e, n_tok);
     }
+    if ((rc = flush())) return rc;
     CUDA_TRY(cudaGetLastError());
     return MATAS_OK;
 }

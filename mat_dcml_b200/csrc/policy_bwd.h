@@ -24,7 +24,7 @@ struct DwJob {
     int ln;              // AFFINE: packed offset of the forward blob holding the LayerNorm weight | bias
     int gW;              // offset of the [out][in] weight gradient in the flat gradient
 };
-struct DwJobs { DwJob j[4]; int n; };
+struct DwJobs { DwJob j[8]; int n; };
 int launch_bwd_dw(const float* packed, float* grad, const DwJobs& jobs, long n_tok, int n_sm, cudaStream_t st);
 
 // register-tiled per-env attention backward (attn_bwd_tile.cu), n_agent <= 64

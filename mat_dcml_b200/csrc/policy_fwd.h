@@ -37,7 +37,8 @@ struct TrainBufs {
     float *d_q1[2], *d_y1[2], *d_lse1[2], *d_xh1[2], *d_rs1[2];
     float *d_y2[2], *d_lse2[2], *d_xh2[2], *d_rs2[2], *d_m0[2], *d_xh3[2], *d_rs3[2];
     float *d_hh, *d_xhh, *d_rsh;                         // logits head
-    float *gS[3];                                        // backward: layer-output gradients handed to the weight-gradient kernel
+    float *gS[9];                                        // backward: three rotating sets of three layer-output gradient buffers handed to
+                                                         // the weight-gradient kernel (a set is reused only after its jobs were launched)
     float *gX, *gRep, *gYa, *gYb, *gDa, *gDb;            // backward: residual-stream / obs_rep / attention-output grads, D [tok][2]
 };
 
