@@ -7,10 +7,10 @@ def L(name):
     labels.append(name); return 'DT(%d);' % (len(labels) - 1)
 hdr = '''
 __device__ long long g_dtrace[3][256];
-#define DT(id) do { if (tr_on && tk < 256) g_dtrace[tr_who][tk] = (clock64() << 8) | (id); ++tk; } while (0)
-'''
+#define TRACE_J %s\n#define DT(id) do { if (tr_on && tk < 256) g_dtrace[tr_who][tk] = (clock64() << 8) | (id); ++tk; } while (0)
+''' % __import__('os').environ.get('TRACE_J', '25')
 s = s.replace('namespace {\n\nconstexpr int NTD = 512;', 'namespace {\n' + hdr + '\nconstexpr int NTD = 512;', 1)
-s = s.replace('            const int j = st.j;\n', '            const int j = st.j;\n            const bool tr_on = blockIdx.x == 0 && j == 25 && (tid == 0 || tid == 33 || tid == 511);\n            const int tr_who = tid == 0 ? 0 : tid == 33 ? 1 : 2; int tk = 0; ' + L('pos_start') + '\n', 1)
+s = s.replace('            const int j = st.j;\n', '            const int j = st.j;\n            const bool tr_on = blockIdx.x == 0 && j == TRACE_J && (tid == 0 || tid == 33 || tid == 511);\n            const int tr_who = tid == 0 ? 0 : tid == 33 ? 1 : 2; int tk = 0; ' + L('pos_start') + '\n', 1)
 # table attention end: the statement after the if/else of block 0 table is "} else {\n                if (blk == 0) {"
 s = s.replace('                                                               x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits, spec, spec_s);\n                } else {',
               '                                                               x1tab, 0, rows, n_valid, j + 1, s.U, s.V, s.bits, spec, spec_s);\n                ' + L('tab_attn_end') + '\n                } else {', 1)

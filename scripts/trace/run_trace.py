@@ -9,7 +9,8 @@ Three threads of one CTA (0, 33 and the last) store (clock64 << 8 | label) at ev
 """
 import sys, json, ctypes
 which = sys.argv[1] if len(sys.argv) > 1 else "decode"
-sys.argv = ['x', '16384', '50']
+import os
+sys.argv = ['x'] + os.environ.get('TRACE_SHAPE', '16384 50').split()
 exec(open('scripts/decode_sweep.py').read())
 lib = ctypes.CDLL('mat_dcml_b200/lib/libmatas_b200.so')
 buf = (ctypes.c_longlong * (3 * 256))()
